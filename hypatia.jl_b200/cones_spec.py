@@ -1,0 +1,270 @@
+"""Cone descriptors and the integer index maps of the hot path.
+
+A descriptor says WHAT a cone is (type, dimension, parameters, barrier side,
+initial point); the oracles live in a backend: ``oracle/cones.py`` (CPU
+checker) or the CUDA library (``gpu.py``).  Index maps follow the reference
+bit-exactly (0-based here, 1-based there):
+
+  svec_length / svec_side / svec_idx / block_idxs   src/Cones/arrayutilities.jl:75,93-97,119-124,132
+  smat_to_svec / svec_to_smat / scale_svec(_incr)   src/Cones/arrayutilities.jl:140-176,183-197,236-251
+  build_cone_idxs                                   src/Models/Models.jl:63-73
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass, field
+from typing import List, Sequence
+
+import numpy as np
+
+# type codes shared with include/hypatia_b200.h (hyb_cone_type)
+NONNEGATIVE = 0
+EPINORMEUCL = 1
+EPIPERSQUARE = 2
+POSSEMIDEFTRI = 3
+WSOSINTERPNONNEGATIVE = 4
+WSOSINTERPPOSSEMIDEFTRI = 5
+EPINORMINF = 6
+
+RT2 = math.sqrt(2.0)
+
+
+# ----------------------------------------------------------------------------
+# index maps (arrayutilities.jl)
+# ----------------------------------------------------------------------------
+def svec_length(side: int) -> int:
+    """arrayutilities.jl:75"""
+    return (side * (side + 1)) // 2
+
+
+def svec_side(length: int) -> int:
+    """arrayutilities.jl:93-97 (isqrt-based inverse, asserted exact)."""
+    side = math.isqrt(1 + 8 * length) // 2
+    assert side * (side + 1) == 2 * length, "not a triangular number"
+    return side
+
+
+def svec_idx(row: int, col: int) -> int:
+    """1-based svec index of (row, col), arrayutilities.jl:119-124."""
+    if row < col:
+        row, col = col, row
+    return ((row - 1) * row) // 2 + col
+
+
+def block_idxs(incr: int, block: int) -> range:
+    """1-based block -> 0-based python range, arrayutilities.jl:132."""
+    return range(incr * (block - 1), incr * block)
+
+
+def smat_to_svec(mat: np.ndarray, rt2: float = RT2) -> np.ndarray:
+    """Upper triangle, column by column, off-diagonals * rt2 (arrayutilities.jl:183-197)."""
+    m = mat.shape[0]
+    out = np.empty(svec_length(m), dtype=mat.dtype)
+    k = 0
+    for j in range(m):
+        out[k : k + j] = mat[:j, j] * rt2
+        out[k + j] = mat[j, j]
+        k += j + 1
+    return out
+
+
+def svec_to_smat(vec: np.ndarray, rt2: float = RT2, full: bool = True) -> np.ndarray:
+    """Inverse of smat_to_svec (arrayutilities.jl:236-251); ``full`` mirrors copytri!."""
+    m = svec_side(vec.shape[0])
+    mat = np.zeros((m, m), dtype=vec.dtype)
+    inv = 1.0 / rt2
+    k = 0
+    for j in range(m):
+        mat[:j, j] = vec[k : k + j] * inv
+        mat[j, j] = vec[k + j]
+        k += j + 1
+    if full:
+        mat = mat + np.triu(mat, 1).T
+    return mat
+
+
+def scale_svec(arr: np.ndarray, scal: float) -> np.ndarray:
+    """In place: off-diagonal rows *= scal (arrayutilities.jl:140-152)."""
+    n = arr.shape[0]
+    k = 0
+    for i in range(1, svec_side(n) + 1):
+        arr[k : k + i - 1] *= scal
+        k += i
+    assert k == n
+    return arr
+
+
+def scale_svec_incr(arr: np.ndarray, scal: float, incr: int) -> np.ndarray:
+    """Blocked variant (arrayutilities.jl:160-176)."""
+    n = arr.shape[0]
+    d, r = divmod(n, incr)
+    assert r == 0
+    k = 0
+    for i in range(1, svec_side(d) + 1):
+        arr[k : k + incr * (i - 1)] *= scal
+        k += incr * i
+    assert k == n
+    return arr
+
+
+# ----------------------------------------------------------------------------
+# descriptors
+# ----------------------------------------------------------------------------
+@dataclass
+class ConeSpec:
+    dim: int
+    type_code: int = field(init=False, default=-1)
+    use_dual_barrier: bool = field(init=False, default=False)
+
+    @property
+    def nu(self) -> float:
+        raise NotImplementedError
+
+    def initial_point(self) -> np.ndarray:
+        raise NotImplementedError
+
+    # scalar per cone for rescale_data unless per-row (process.jl:41-52)
+    per_row_h_scale = False
+
+
+@dataclass
+class Nonnegative(ConeSpec):
+    """src/Cones/nonnegative.jl:16-53"""
+
+    per_row_h_scale = True
+
+    def __post_init__(self):
+        assert self.dim >= 1
+        self.type_code = NONNEGATIVE
+
+    @property
+    def nu(self):
+        return float(self.dim)
+
+    def initial_point(self):
+        return np.ones(self.dim)
+
+
+@dataclass
+class EpiNormEucl(ConeSpec):
+    """src/Cones/epinormeucl.jl:16-59"""
+
+    def __post_init__(self):
+        assert self.dim >= 2
+        self.type_code = EPINORMEUCL
+
+    @property
+    def nu(self):
+        return 2.0
+
+    def initial_point(self):
+        arr = np.zeros(self.dim)
+        arr[0] = math.sqrt(2.0)
+        return arr
+
+
+@dataclass
+class EpiPerSquare(ConeSpec):
+    """src/Cones/epipersquare.jl:17-70"""
+
+    def __post_init__(self):
+        assert self.dim >= 3
+        self.type_code = EPIPERSQUARE
+
+    @property
+    def nu(self):
+        return 2.0
+
+    def initial_point(self):
+        arr = np.zeros(self.dim)
+        arr[:2] = 1.0
+        return arr
+
+
+@dataclass
+class PosSemidefTri(ConeSpec):
+    """Real svec PSD cone, src/Cones/possemideftri.jl:17-87"""
+
+    side: int = field(init=False, default=0)
+
+    def __post_init__(self):
+        assert self.dim >= 1
+        self.type_code = POSSEMIDEFTRI
+        self.side = svec_side(self.dim)
+
+    @property
+    def nu(self):
+        return float(self.side)
+
+    def initial_point(self):
+        arr = np.zeros(self.dim)
+        k = 0
+        for i in range(1, self.side + 1):  # possemideftri.jl:78-87
+            arr[k] = 1.0
+            k += i + 1
+        return arr
+
+
+@dataclass
+class WSOSInterpNonnegative(ConeSpec):
+    """src/Cones/wsosinterpnonnegative.jl:17-97; dual barrier unless use_dual."""
+
+    Ps: Sequence[np.ndarray] = ()
+    use_dual: bool = False
+
+    def __post_init__(self):
+        self.type_code = WSOSINTERPNONNEGATIVE
+        self.Ps = [np.asfortranarray(P, dtype=np.float64) for P in self.Ps]
+        for P in self.Ps:
+            assert P.shape[0] == self.dim
+        self.use_dual_barrier = not self.use_dual
+
+    @property
+    def nu(self):
+        return float(sum(P.shape[1] for P in self.Ps))
+
+    def initial_point(self):
+        return np.ones(self.dim)
+
+
+@dataclass
+class WSOSInterpPosSemidefTri(ConeSpec):
+    """src/Cones/wsosinterppossemideftri.jl:17-123; dim = U*R(R+1)/2."""
+
+    R: int = 1
+    U: int = 0
+    Ps: Sequence[np.ndarray] = ()
+    use_dual: bool = False
+
+    def __post_init__(self):
+        self.type_code = WSOSINTERPPOSSEMIDEFTRI
+        self.Ps = [np.asfortranarray(P, dtype=np.float64) for P in self.Ps]
+        for P in self.Ps:
+            assert P.shape[0] == self.U
+        assert self.dim == self.U * svec_length(self.R)
+        self.use_dual_barrier = not self.use_dual
+
+    @property
+    def nu(self):
+        return float(self.R * sum(P.shape[1] for P in self.Ps))
+
+    def initial_point(self):
+        arr = np.zeros(self.dim)
+        block = 1
+        for i in range(1, self.R + 1):  # wsosinterppossemideftri.jl:115-123
+            arr[block_idxs(self.U, block).start : block_idxs(self.U, block).stop] = 1.0
+            block += i + 1
+        return arr
+
+
+def wsos_psd(R: int, U: int, Ps, use_dual: bool = False) -> WSOSInterpPosSemidefTri:
+    return WSOSInterpPosSemidefTri(dim=U * svec_length(R), R=R, U=U, Ps=Ps, use_dual=use_dual)
+
+
+def build_cone_idxs(q: int, cones: List[ConeSpec]) -> np.ndarray:
+    """Offsets array of length K+1 (cone k owns [off[k], off[k+1])); Models.jl:63-73."""
+    offs = np.zeros(len(cones) + 1, dtype=np.int64)
+    for k, cone in enumerate(cones):
+        offs[k + 1] = offs[k] + cone.dim
+    assert offs[-1] == q, "sum of cone dimensions must equal q"
+    return offs

@@ -1,0 +1,265 @@
+"""Combined predict-and-center stepper, RHS builders and step-distance search
+(host side; callers of the hot path — SURVEY §8a-D).
+
+Follows src/Solvers/steppers/combined.jl:13-196, steppers/common.jl:14-119 and
+src/Solvers/search.jl:12-162.  Per-cone scalar work (s'z gates, dder3 identity
+gate) is vectorised over the cone offsets with fixed-order segment sums.
+"""
+from __future__ import annotations
+
+import math
+import time
+
+import numpy as np
+
+from .models import Point
+from .syscommon import get_directions
+
+EPS = float(np.finfo(np.float64).eps)
+
+# search.jl:48-69
+DEFAULT_ALPHA_SCHED = (
+    0.9999, 0.999, 0.99, 0.97, 0.95, 0.9, 0.85, 0.8, 0.7, 0.6, 0.5, 0.3, 0.1, 0.05, 0.01, 0.005, 0.001, 0.0005,
+)
+
+
+class StepSearcher:
+    """search.jl:12-46"""
+
+    def __init__(self, nu: float, min_prox=0.01, prox_bound=0.99, use_max_prox=True, alpha_sched=DEFAULT_ALPHA_SCHED):
+        self.min_prox = min_prox
+        self.prox_bound = prox_bound
+        self.use_max_prox = use_max_prox
+        self.alpha_sched = tuple(alpha_sched)
+        self.nup1 = nu + 1.0
+        self.prev_sched = 0
+        self.prox = 0.0
+
+
+class CombinedStepper:
+    def __init__(self, shift_sched: int = 0, **searcher_options):
+        self.shift_sched = shift_sched
+        self.searcher_options = searcher_options
+        self.last_num_cand = 0
+        self.last_num_ref = 0
+
+    def load(self, solver) -> None:  # combined.jl:41-58
+        m = solver.model
+        self.prev_alpha = 1.0
+        self.rhs = Point(m.n, m.p, m.q)
+        self.dir = Point(m.n, m.p, m.q)
+        self.temp = Point(m.n, m.p, m.q)
+        self.dir_cent = Point(m.n, m.p, m.q)
+        self.dir_centadj = Point(m.n, m.p, m.q)
+        self.dir_pred = Point(m.n, m.p, m.q)
+        self.dir_predadj = Point(m.n, m.p, m.q)
+        self.dir_temp = np.zeros_like(self.rhs.vec)
+        self.searcher = StepSearcher(m.nu, **self.searcher_options)
+        self.unadj_only = self.cent_only = False
+
+    def expect_improvement(self) -> bool:
+        return True
+
+    # ---- one iteration (combined.jl:60-125) ------------------------------
+    def step(self, solver) -> bool:
+        point = solver.point
+        rhs, dir_ = self.rhs, self.dir
+        self.last_num_cand = 0
+        self.last_num_ref = 0
+
+        t0 = time.time()
+        solver.syssolver.update_lhs(solver)
+        solver.time_upsys += time.time() - t0
+
+        for builder, store, needs_dir in (
+            (update_rhs_cent, self.dir_cent, False),
+            (update_rhs_centadj, self.dir_centadj, True),
+            (update_rhs_pred, self.dir_pred, False),
+            (update_rhs_predadj, self.dir_predadj, True),
+        ):
+            t0 = time.time()
+            if needs_dir:
+                builder(solver, rhs, dir_)
+            else:
+                builder(solver, rhs)
+            solver.time_uprhs += time.time() - t0
+            t0 = time.time()
+            get_directions(self, solver)
+            solver.time_getdir += time.time() - t0
+            store.vec[:] = dir_.vec
+
+        self.unadj_only = self.cent_only = False
+        t0 = time.time()
+        alpha = self.search_alpha(point, solver)
+        if alpha == 0.0:
+            self.unadj_only = True  # combined without adjustment
+            alpha = self.search_alpha(point, solver)
+            if alpha == 0.0:
+                self.cent_only = True  # centering with adjustment
+                self.unadj_only = False
+                alpha = self.search_alpha(point, solver)
+                if alpha == 0.0:
+                    self.unadj_only = True  # centering without adjustment
+                    alpha = self.search_alpha(point, solver)
+                    if alpha == 0.0:
+                        print("warning: cannot step in centering direction")
+                        solver.status = "NumericalFailure"
+                        self.prev_alpha = alpha
+                        solver.time_search += time.time() - t0
+                        return False
+        solver.time_search += time.time() - t0
+        self.update_stepper_points(alpha, point, False)
+        self.prev_alpha = alpha
+        return True
+
+    # ---- combined.jl:129-177 ----------------------------------------------
+    def update_stepper_points(self, alpha: float, point: Point, ztsk_only: bool) -> None:
+        if ztsk_only:
+            cand = self.temp.ztsk
+            cand[:] = point.ztsk
+            sel = lambda pt: pt.ztsk  # noqa: E731
+        else:
+            cand = point.vec
+            sel = lambda pt: pt.vec  # noqa: E731
+        dir_cent, dir_pred = sel(self.dir_cent), sel(self.dir_pred)
+        if self.unadj_only:
+            if self.cent_only:
+                cand += alpha * dir_cent
+            else:
+                cand += alpha * dir_pred + (1 - alpha) * dir_cent
+        else:
+            dir_centadj = sel(self.dir_centadj)
+            alpha_sqr = alpha * alpha
+            if self.cent_only:
+                cand += alpha * dir_cent + alpha_sqr * dir_centadj
+            else:
+                dir_predadj = sel(self.dir_predadj)
+                am1 = 1 - alpha
+                cand += alpha * dir_pred + alpha_sqr * dir_predadj + am1 * dir_cent + (am1 * am1) * dir_centadj
+
+    def start_sched(self) -> int:  # combined.jl:179-182 (1-based)
+        if self.shift_sched <= 0:
+            return 1
+        return max(1, self.searcher.prev_sched - self.shift_sched)
+
+    # ---- search.jl:72-95 ---------------------------------------------------
+    def search_alpha(self, point: Point, solver) -> float:
+        searcher = self.searcher
+        sched = self.start_sched()
+        while sched <= len(searcher.alpha_sched):
+            alpha = searcher.alpha_sched[sched - 1]
+            self.update_stepper_points(alpha, point, True)
+            self.last_num_cand += 1
+            if self.check_cone_points(solver):
+                searcher.prev_sched = sched
+                return alpha
+            sched += 1
+        searcher.prev_sched = sched
+        return 0.0
+
+    # ---- search.jl:100-162 -------------------------------------------------
+    def check_cone_points(self, solver) -> bool:
+        searcher = self.searcher
+        cand = self.temp
+        cones = solver.cones
+        min_prox = searcher.min_prox
+        proxsqr_bound = searcher.prox_bound**2
+
+        tau, kap = cand.tau, cand.kap
+        taukap = tau * kap
+        if min(tau, kap, taukap) < EPS:
+            return False
+        primal = cones.primal_of(cand.z, cand.s)
+        dual = cones.dual_of(cand.z, cand.s)
+        szk = cones.cone_dots(primal, dual)
+        if szk.size and float(szk.min()) < EPS:
+            return False
+        mu = (float(szk.sum()) + taukap) / searcher.nup1
+        if mu < EPS:
+            return False
+        taukap_rel = taukap / mu
+        if taukap_rel < min_prox:
+            return False
+        taukap_proxsqr = (taukap_rel - 1.0) ** 2
+        if taukap_proxsqr > proxsqr_bound:
+            return False
+        if szk.size:
+            sz_rel = szk / (mu * cones.nus)
+            if np.any(sz_rel < min_prox) or np.any(cones.nus * (sz_rel - 1.0) ** 2 > proxsqr_bound):
+                return False
+
+        irtmu = 1.0 / math.sqrt(mu)
+        cones.load_point(primal, irtmu)
+        cones.load_dual_point(dual)
+        cones.reset_data()
+        ok, agg = cones.check_neighborhood(irtmu, searcher.use_max_prox, taukap_proxsqr, proxsqr_bound)
+        if not ok:
+            return False
+        searcher.prox = math.sqrt(agg)
+        return True
+
+
+# ---------------------------------------------------------------------------
+# RHS builders (steppers/common.jl)
+# ---------------------------------------------------------------------------
+def update_rhs_pred(solver, rhs: Point) -> Point:  # common.jl:14-28
+    rhs.x[:] = solver.x_residual
+    rhs.y[:] = solver.y_residual
+    rhs.z[:] = solver.z_residual
+    rhs.tau = solver.tau_residual
+    cones, point = solver.cones, solver.point
+    rhs.s[:] = -cones.dual_of(point.z, point.s)
+    rhs.kap = -point.kap
+    return rhs
+
+
+def update_rhs_cent(solver, rhs: Point) -> Point:  # common.jl:66-83
+    rhs.x[:] = 0
+    rhs.y[:] = 0
+    rhs.z[:] = 0
+    rhs.tau = 0.0
+    cones, point = solver.cones, solver.point
+    rtmu = math.sqrt(solver.mu)
+    rhs.s[:] = -cones.dual_of(point.z, point.s) - rtmu * cones.grad()
+    rhs.kap = -point.kap + solver.mu / point.tau
+    return rhs
+
+
+def _adj_common(solver, rhs: Point, dir_: Point, pred: bool) -> Point:
+    """update_rhs_predadj (common.jl:30-63) / update_rhs_centadj (:86-119)."""
+    rhs.vec[:] = 0
+    cones = solver.cones
+    rteps = math.sqrt(EPS)
+    irtrtmu = 1.0 / math.sqrt(math.sqrt(solver.mu))
+    prim_dir = cones.primal_of(dir_.z, dir_.s)
+    prim_scal = irtrtmu * prim_dir
+    if pred:
+        H_prim = cones.hess_prod_slow(prim_dir)
+    else:
+        H_prim = cones.hess_prod_slow(prim_scal)
+    dder3 = cones.dder3(prim_scal)
+    dot1 = cones.cone_dots(dder3, cones.point())
+    dot2 = cones.cone_dots(prim_scal, H_prim)
+    if pred:
+        dot2 = irtrtmu * dot2
+    viol = np.abs(dot1 - dot2) / (rteps + np.abs(dot2))
+    keep = cones.expand((viol < 1e-4) & cones.use_dder3())
+    if pred:
+        rhs.s[:] = np.where(keep, H_prim + dder3, 0.0)
+    else:
+        rhs.s[:] = np.where(keep, dder3, 0.0)
+    taubar = solver.point.tau
+    tau_dir_tau = dir_.tau / taubar
+    if pred:
+        rhs.kap = tau_dir_tau * solver.mu / taubar * (1 + tau_dir_tau)
+    else:
+        rhs.kap = tau_dir_tau * solver.mu / taubar * tau_dir_tau
+    return rhs
+
+
+def update_rhs_predadj(solver, rhs: Point, dir_: Point) -> Point:
+    return _adj_common(solver, rhs, dir_, True)
+
+
+def update_rhs_centadj(solver, rhs: Point, dir_: Point) -> Point:
+    return _adj_common(solver, rhs, dir_, False)

@@ -1,0 +1,136 @@
+"""Oracle identities of the reference's cone tests (test/cone.jl:31-129) applied to
+the CPU oracle cones at the reference's sizes (test/runconetests.jl).  Tolerance
+1e3*eps as in the reference (:35) unless noted."""
+import numpy as np
+import pytest
+
+import hypatia_b200  # noqa: F401
+from hypatia_b200 import cones_spec as cs
+from hypatia_b200 import polyutils as pu
+from oracle.cones import make_cone
+
+EPS = float(np.finfo(np.float64).eps)
+
+
+def perturb_scale(point, rng, noise, scale):
+    point = point + 2 * noise * rng.random(point.size) - noise
+    return point * scale
+
+
+def run_oracle_identities(spec, tol=1e3 * EPS, noise=0.1, scale=0.1, init_tol=None):
+    rng = np.random.default_rng(1)
+    init_tol = tol if init_tol is None else init_tol
+    cone = make_cone(spec)
+    dim = spec.dim
+    cone.setup_data()
+    cone.reset_data()
+    close = lambda a, b, t=tol: np.allclose(a, b, atol=t, rtol=t)  # noqa: E731
+
+    point = spec.initial_point()
+    cone.load_point(point)
+    assert cone.is_feas()
+    dual_point = -cone.grad()
+    cone.load_dual_point(dual_point)
+    assert cone.is_dual_feas()
+    assert cone.get_proxsqr(1.0, True) <= 1
+    assert cone.get_proxsqr(1.0, False) <= dim
+    if np.isfinite(init_tol):
+        assert close(point, dual_point, init_tol)  # centrality of the initial point
+
+    hess = cone.hess()
+    assert close(hess @ point, dual_point)
+    assert close(cone.hess_prod(point), dual_point)
+    inv_hess = cone.inv_hess()
+    assert close(inv_hess @ dual_point, point)
+    assert close(cone.inv_hess_prod(dual_point), point)
+    assert close(hess @ inv_hess, np.eye(dim))
+
+    point = perturb_scale(point, rng, noise, scale)
+    dual_point = perturb_scale(dual_point, rng, noise, 1 / scale)
+    cone.reset_data()
+    cone.load_point(point)
+    assert cone.is_feas()
+    cone.load_dual_point(dual_point)
+    assert cone.is_dual_feas()
+
+    nu = spec.nu
+    grad = cone.grad()
+    assert close(point @ grad, -nu)
+    hess = np.array(cone.hess())
+    inv_hess = np.array(cone.inv_hess())
+    assert close(hess @ inv_hess, np.eye(dim))
+    assert close(hess @ point, -grad)
+    assert close(cone.hess_prod(point), -grad)
+    assert close(cone.inv_hess_prod(grad), -point)
+    assert close(cone.hess_prod(inv_hess), np.eye(dim))
+    assert close(cone.inv_hess_prod(hess), np.eye(dim))
+
+    psi = dual_point + grad
+    proxsqr = psi @ cone.inv_hess_prod(psi)
+    assert close(cone.get_proxsqr(1.0, False), proxsqr)
+
+    if hasattr(cone, "use_hess_prod_slow"):
+        cone.update_use_hess_prod_slow()
+        assert cone.use_hess_prod_slow_updated and not cone.use_hess_prod_slow
+        cone.use_hess_prod_slow = True
+        assert close(cone.hess_prod_slow(inv_hess), np.eye(dim))
+
+    if cone.use_sqrt_hess_oracles(dim + 1):
+        prod_mat2 = cone.sqrt_hess_prod(inv_hess).T.copy()
+        assert close(cone.sqrt_hess_prod(prod_mat2), np.eye(dim))
+        prod_mat2 = cone.inv_sqrt_hess_prod(np.eye(dim))
+        assert close(prod_mat2.T @ prod_mat2, inv_hess)
+
+    assert close(-cone.dder3(point), grad)
+    direction = perturb_scale(np.zeros(dim), rng, noise, 1.0)
+    dder3 = cone.dder3(direction)
+    assert close(dder3 @ point, direction @ hess @ direction)
+
+
+@pytest.mark.parametrize("dim", [1, 2, 6])
+def test_nonnegative(dim):  # test/cone.jl:343-347
+    run_oracle_identities(cs.Nonnegative(dim))
+
+
+@pytest.mark.parametrize("side", [1, 2, 3, 5])
+def test_possemideftri(side):  # :357-361
+    run_oracle_identities(cs.PosSemidefTri(cs.svec_length(side)))
+
+
+@pytest.mark.parametrize("dw", [1, 2, 5])
+def test_epinormeucl(dw):  # :485-489
+    run_oracle_identities(cs.EpiNormEucl(1 + dw))
+
+
+@pytest.mark.parametrize("dw", [1, 2, 5])
+def test_epipersquare(dw):  # :502-506
+    run_oracle_identities(cs.EpiPerSquare(2 + dw))
+
+
+@pytest.mark.parametrize("n,halfdeg", [(1, 1), (1, 3), (2, 1), (2, 2), (3, 1)])
+def test_wsosinterpnonnegative(n, halfdeg):  # :795-800
+    U, _, Ps = pu.interpolate(pu.BoxDomain(-np.ones(n), np.ones(n)), halfdeg, sample=False)  # rand_interp, :323-328
+    run_oracle_identities(cs.WSOSInterpNonnegative(U, Ps), init_tol=np.inf)
+
+
+@pytest.mark.parametrize("n,halfdeg,R", [(1, 1, 1), (1, 1, 4), (2, 2, 1), (3, 1, 2)])
+def test_wsosinterppossemideftri(n, halfdeg, R):  # :813-818
+    U, _, Ps = pu.interpolate(pu.BoxDomain(-np.ones(n), np.ones(n)), halfdeg, sample=False)
+    run_oracle_identities(cs.wsos_psd(R, U, Ps), init_tol=np.inf)
+
+
+def test_index_maps():
+    """arrayutilities.jl index maps, bit-exact."""
+    for side in range(1, 40):
+        assert cs.svec_side(cs.svec_length(side)) == side
+    assert [cs.svec_idx(r, c) for r, c in [(1, 1), (2, 1), (1, 2), (2, 2), (3, 1), (3, 3)]] == [1, 2, 2, 3, 4, 6]
+    assert list(cs.block_idxs(5, 3)) == [10, 11, 12, 13, 14]
+    M = np.arange(16.0).reshape(4, 4)
+    M = M + M.T
+    v = cs.smat_to_svec(M)
+    assert v.size == 10 and v[0] == M[0, 0] and v[1] == M[0, 1] * np.sqrt(2) and v[2] == M[1, 1]
+    assert np.allclose(cs.svec_to_smat(v), M)
+    assert np.array_equal(cs.PosSemidefTri(10).initial_point(), cs.smat_to_svec(np.eye(4)))
+    w = np.ones(12)
+    cs.scale_svec_incr(w, 2.0, 4)
+    assert np.array_equal(w, [1, 1, 1, 1, 2, 2, 2, 2, 1, 1, 1, 1])
