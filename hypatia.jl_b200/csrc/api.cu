@@ -1,0 +1,552 @@
+// C-ABI of the hypatia_b200 library (include/hypatia_b200.h): context, model load,
+// cone batch, Schur assembly + factorization, solves.
+#include <cstdarg>
+#include <cmath>
+
+#include "../../include/hypatia_b200.h"
+#include "common.cuh"
+#include "cones.cuh"
+#include "tma.cuh"
+
+int hyb_copy_upper(cudaStream_t st, const double* src, int64_t lds_, double* dst, int64_t ldd, int64_t N);
+
+// ----------------------------------------------------------------------------- errors
+static thread_local char g_err[1024] = "";
+void hyb_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+const char* hyb_get_error() { return g_err; }
+
+// ----------------------------------------------------------------------------- tensor maps
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static PFN_encodeTiled g_encode = nullptr;
+
+int hyb_make_tmap_2d_f64(CUtensorMap* tm, const double* base, uint64_t inner, uint64_t outer, uint64_t ld,
+                         uint32_t box_inner, uint32_t box_outer) {
+    if (!g_encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        HYB_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+        if (qres != cudaDriverEntryPointSuccess || !fn) {
+            hyb_set_error("cuTensorMapEncodeTiled is not available from the driver");
+            return -1;
+        }
+        g_encode = (PFN_encodeTiled)fn;
+    }
+    cuuint64_t dims[2] = {inner, outer};
+    cuuint64_t strides[1] = {ld * sizeof(double)};
+    cuuint32_t box[2] = {box_inner, box_outer};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = g_encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, (void*)base, dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        hyb_set_error("cuTensorMapEncodeTiled failed (CUresult %d) inner=%llu outer=%llu ld=%llu", (int)r,
+                      (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)ld);
+        return -1;
+    }
+    return 0;
+}
+
+// ----------------------------------------------------------------------------- small kernels
+static int64_t g_misc_launches = 0;
+
+__global__ void axpby_kernel(int64_t n, double a, const double* __restrict__ x, double b, const double* __restrict__ y,
+                             double* __restrict__ out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = a * x[i] + b * y[i];
+}
+// increase_diag! (dense.jl:100-107)
+__global__ void increase_diag_kernel(int64_t n, double* A, int64_t ld) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        const double d = A[i + i * ld];
+        A[i + i * ld] = (1.0 + 1e-5) * fmax(d, 1000.0 * HYB_EPS);
+    }
+}
+
+// ----------------------------------------------------------------------------- context
+struct hyb_ctx {
+    int device = 0;
+    cudaStream_t st = nullptr;
+    bool loaded = false;
+    int64_t q = 0, N = 0, ldq = 0, ldS = 0;
+    double* GQ2 = nullptr;
+    double* HGQ2 = nullptr;
+    double* S = nullptr;
+    HybChol chol;
+    HybCones cones;
+    double* in_primal = nullptr;
+    double* in_dual = nullptr;
+    double *vq1 = nullptr, *vq2 = nullptr, *vq3 = nullptr, *vn1 = nullptr, *vn2 = nullptr;
+    double* gemv_scratch = nullptr;
+    double loaded_scal = 1.0;
+    double updated_irtmu = NAN;
+    bool point_loaded = false;
+    bool fact_ok = false;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
+};
+
+static void free_model(hyb_ctx* c) {
+    cudaFree(c->GQ2);
+    cudaFree(c->HGQ2);
+    cudaFree(c->S);
+    cudaFree(c->in_primal);
+    cudaFree(c->in_dual);
+    cudaFree(c->vq1);
+    cudaFree(c->vq2);
+    cudaFree(c->vq3);
+    cudaFree(c->vn1);
+    cudaFree(c->vn2);
+    cudaFree(c->gemv_scratch);
+    c->GQ2 = c->HGQ2 = c->S = c->in_primal = c->in_dual = nullptr;
+    c->vq1 = c->vq2 = c->vq3 = c->vn1 = c->vn2 = c->gemv_scratch = nullptr;
+    if (c->loaded) {
+        hyb_chol_free(c->chol);
+        hybi_cones_free(c->cones);
+    }
+    c->loaded = false;
+}
+
+static int ensure_updated(hyb_ctx* c, double irtmu) {
+    if (!c->point_loaded) {
+        hyb_set_error("no point loaded: call hyb_cones_load_point first");
+        return -3;
+    }
+    if (c->updated_irtmu == irtmu) return 0;
+    HYB_CHECK(hybi_cones_update(c->st, c->cones, c->in_primal, c->in_dual, c->loaded_scal, irtmu, 1));
+    c->updated_irtmu = irtmu;
+    return 0;
+}
+
+extern "C" {
+
+hyb_ctx* hyb_ctx_create(int device) {
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        hyb_set_error("no CUDA device available (%s): hypatia_b200 has no CPU fallback", cudaGetErrorString(e));
+        return nullptr;
+    }
+    if (device < 0 || device >= ndev) {
+        hyb_set_error("device %d out of range (found %d)", device, ndev);
+        return nullptr;
+    }
+    if (cudaSetDevice(device) != cudaSuccess) {
+        hyb_set_error("cudaSetDevice(%d) failed", device);
+        return nullptr;
+    }
+    hyb_ctx* c = new hyb_ctx();
+    c->device = device;
+    if (cudaStreamCreate(&c->st) != cudaSuccess || cudaEventCreate(&c->ev0) != cudaSuccess ||
+        cudaEventCreate(&c->ev1) != cudaSuccess || cudaEventCreate(&c->ev2) != cudaSuccess) {
+        hyb_set_error("stream / event creation failed");
+        delete c;
+        return nullptr;
+    }
+    return c;
+}
+
+void hyb_ctx_destroy(hyb_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->st);
+    free_model(c);
+    cudaEventDestroy(c->ev0);
+    cudaEventDestroy(c->ev1);
+    cudaEventDestroy(c->ev2);
+    cudaStreamDestroy(c->st);
+    delete c;
+}
+
+const char* hyb_last_error(hyb_ctx*) { return hyb_get_error(); }
+
+int64_t hyb_launch_count(void) { return hyb_gemm_launch_count() + hybi_cones_launch_count() + g_misc_launches; }
+
+int hyb_model_load(hyb_ctx* c, int64_t q, int64_t N, const double* GQ2, int64_t ncones, const hyb_cone_desc* descs) {
+    if (!c) return -1;
+    HYB_CUDA(cudaSetDevice(c->device));
+    free_model(c);
+    c->q = q;
+    c->N = N;
+    c->ldq = hyb_round_up(q > 0 ? q : 1, 16);
+    c->ldS = hyb_round_up(N > 0 ? N : 1, 16);
+    const int64_t ncol = N > 0 ? N : 1;
+    HYB_CUDA(cudaMalloc(&c->GQ2, sizeof(double) * c->ldq * ncol));
+    HYB_CUDA(cudaMalloc(&c->HGQ2, sizeof(double) * c->ldq * ncol));
+    HYB_CUDA(cudaMalloc(&c->S, sizeof(double) * c->ldS * ncol));
+    HYB_CUDA(cudaMemset(c->HGQ2, 0, sizeof(double) * c->ldq * ncol));
+    if (q > 0 && N > 0)
+        HYB_CUDA(cudaMemcpy2D(c->GQ2, sizeof(double) * c->ldq, GQ2, sizeof(double) * q, sizeof(double) * q, N,
+                              cudaMemcpyHostToDevice));
+    const int64_t qa = q > 0 ? q : 1, Na = N > 0 ? N : 1;
+    HYB_CUDA(cudaMalloc(&c->in_primal, sizeof(double) * qa));
+    HYB_CUDA(cudaMalloc(&c->in_dual, sizeof(double) * qa));
+    HYB_CUDA(cudaMalloc(&c->vq1, sizeof(double) * qa));
+    HYB_CUDA(cudaMalloc(&c->vq2, sizeof(double) * qa));
+    HYB_CUDA(cudaMalloc(&c->vq3, sizeof(double) * qa));
+    HYB_CUDA(cudaMalloc(&c->vn1, sizeof(double) * Na));
+    HYB_CUDA(cudaMalloc(&c->vn2, sizeof(double) * Na));
+    HYB_CUDA(cudaMalloc(&c->gemv_scratch, sizeof(double) * qa * HYB_GEMV_SPLITS));
+
+    // group consecutive identical cones into blocks
+    HybCones& cs = c->cones;
+    cs = HybCones();
+    cs.q = q;
+    cs.K = ncones;
+    int64_t expect = 0;
+    for (int64_t k = 0; k < ncones; ++k) {
+        const hyb_cone_desc& d = descs[k];
+        if (d.offset != expect || d.dim <= 0) {
+            hyb_set_error("cone %lld: offset %lld does not continue the previous cone (expected %lld)", (long long)k,
+                          (long long)d.offset, (long long)expect);
+            return -3;
+        }
+        expect += d.dim;
+        const bool mergeable = d.type != HYB_CONE_WSOSINTERPNONNEGATIVE && d.type != HYB_CONE_WSOSINTERPPOSSEMIDEFTRI;
+        if (!cs.blocks.empty() && mergeable) {
+            HybConeBlock& b = cs.blocks.back();
+            if (b.type == d.type && b.dim == d.dim && b.use_dual == d.use_dual_barrier) {
+                b.count += 1;
+                continue;
+            }
+            // adjacent nonnegative cones of different sizes are one elementwise block only if
+            // they stay separate cones for the neighbourhood test: keep them separate.
+        }
+        HybConeBlock b;
+        b.type = d.type;
+        b.dim = (int)d.dim;
+        b.side = (int)d.side_or_R;
+        b.use_dual = d.use_dual_barrier;
+        b.count = 1;
+        b.offset = d.offset;
+        b.cone0 = k;
+        cs.blocks.push_back(b);
+    }
+    if (expect != q) {
+        hyb_set_error("cone dimensions sum to %lld but q = %lld", (long long)expect, (long long)q);
+        return -3;
+    }
+    HYB_CHECK(hybi_cones_alloc(cs));
+    HYB_CHECK(hyb_chol_alloc(c->chol, N));
+    c->loaded = true;
+    c->point_loaded = false;
+    c->fact_ok = false;
+    c->updated_irtmu = NAN;
+    return 0;
+}
+
+int hyb_cones_load_point(hyb_ctx* c, const double* primal, const double* dual, double scal) {
+    if (!c || !c->loaded) return -1;
+    HYB_CUDA(cudaSetDevice(c->device));
+    if (c->q > 0) {
+        HYB_CUDA(cudaMemcpyAsync(c->in_primal, primal, sizeof(double) * c->q, cudaMemcpyHostToDevice, c->st));
+        HYB_CUDA(cudaMemcpyAsync(c->in_dual, dual, sizeof(double) * c->q, cudaMemcpyHostToDevice, c->st));
+    }
+    c->loaded_scal = scal;
+    c->point_loaded = true;
+    c->updated_irtmu = NAN;
+    // in the line search scal == irtmu (search.jl:144), so this is normally the only update
+    HYB_CHECK(ensure_updated(c, scal));
+    HYB_CUDA(cudaStreamSynchronize(c->st));
+    return 0;
+}
+
+int hyb_cones_is_feas(hyb_ctx* c, int* is_feas, int* is_dual_feas) {
+    if (!c || !c->loaded) return -1;
+    HYB_CUDA(cudaSetDevice(c->device));
+    if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(ensure_updated(c, c->loaded_scal));
+    int flags = 0;
+    double agg = 0.0;
+    HYB_CHECK(hybi_cones_reduce(c->st, c->cones, 1, &flags, &agg));
+    if (is_feas) *is_feas = (flags & HYB_ST_FEAS) ? 1 : 0;
+    if (is_dual_feas) *is_dual_feas = (flags & HYB_ST_DUAL_FEAS) ? 1 : 0;
+    return 0;
+}
+
+int hyb_cones_check(hyb_ctx* c, double irtmu, int use_max_prox, double agg0, double proxsqr_bound, int* ok,
+                    double* agg) {
+    if (!c || !c->loaded) return -1;
+    HYB_CUDA(cudaSetDevice(c->device));
+    HYB_CHECK(ensure_updated(c, irtmu));
+    int flags = 0;
+    double a = 0.0;
+    HYB_CHECK(hybi_cones_reduce(c->st, c->cones, use_max_prox, &flags, &a));
+    const double total = use_max_prox ? fmax(agg0, a) : agg0 + a;
+    *agg = total;
+    *ok = (flags == HYB_ST_ALL) && (total < proxsqr_bound) ? 1 : 0;
+    return 0;
+}
+
+int hyb_cones_grad(hyb_ctx* c, double* grad) {
+    if (!c || !c->loaded) return -1;
+    HYB_CUDA(cudaSetDevice(c->device));
+    if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(ensure_updated(c, c->loaded_scal));
+    if (c->q > 0) HYB_CUDA(cudaMemcpyAsync(grad, c->cones.grad, sizeof(double) * c->q, cudaMemcpyDeviceToHost, c->st));
+    HYB_CUDA(cudaStreamSynchronize(c->st));
+    return 0;
+}
+
+int hyb_cones_hess_prod(hyb_ctx* c, int which, const double* arr, double* prod, int64_t m) {
+    if (!c || !c->loaded) return -1;
+    HYB_CUDA(cudaSetDevice(c->device));
+    if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(ensure_updated(c, c->loaded_scal));
+    if (which == 6) which = 0;  // hess_prod_slow! == hess_prod! for the cones batched here (Cones.jl:229-231)
+    if (which < 0 || which > 5) {
+        hyb_set_error("hyb_cones_hess_prod: bad selector %d", which);
+        return -3;
+    }
+    const int64_t q = c->q;
+    if (q == 0 || m <= 0) return 0;
+    double *din = c->vq1, *dout = c->vq2;
+    const bool big = m > 1;
+    if (big) {
+        HYB_CUDA(cudaMalloc(&din, sizeof(double) * q * m));
+        HYB_CUDA(cudaMalloc(&dout, sizeof(double) * q * m));
+    }
+    HYB_CUDA(cudaMemcpyAsync(din, arr, sizeof(double) * q * m, cudaMemcpyHostToDevice, c->st));
+    int rc = hybi_cones_prod(c->st, c->cones, which, din, q, dout, q, m);
+    if (rc == 0) {
+        cudaError_t e = cudaMemcpyAsync(prod, dout, sizeof(double) * q * m, cudaMemcpyDeviceToHost, c->st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c->st);
+        if (e != cudaSuccess) {
+            hyb_set_error("hyb_cones_hess_prod: %s", cudaGetErrorString(e));
+            rc = -1;
+        }
+    }
+    if (big) {
+        cudaFree(din);
+        cudaFree(dout);
+    }
+    return rc;
+}
+
+int hyb_cones_dder3(hyb_ctx* c, const double* dir, double* out) {
+    if (!c || !c->loaded) return -1;
+    HYB_CUDA(cudaSetDevice(c->device));
+    if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(ensure_updated(c, c->loaded_scal));
+    if (c->q == 0) return 0;
+    HYB_CUDA(cudaMemcpyAsync(c->vq1, dir, sizeof(double) * c->q, cudaMemcpyHostToDevice, c->st));
+    HYB_CHECK(hybi_cones_dder3(c->st, c->cones, c->vq1, c->vq2));
+    HYB_CUDA(cudaMemcpyAsync(out, c->vq2, sizeof(double) * c->q, cudaMemcpyDeviceToHost, c->st));
+    HYB_CUDA(cudaStreamSynchronize(c->st));
+    return 0;
+}
+
+int hyb_schur_update(hyb_ctx* c, double* t_assemble_ms, double* t_fact_ms, int* fact_kind) {
+    if (!c || !c->loaded) return -1;
+    HYB_CUDA(cudaSetDevice(c->device));
+    if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(ensure_updated(c, c->loaded_scal));
+    const int64_t q = c->q, N = c->N;
+    if (N == 0) {
+        if (t_assemble_ms) *t_assemble_ms = 0;
+        if (t_fact_ms) *t_fact_ms = 0;
+        if (fact_kind) *fact_kind = 0;
+        c->fact_ok = true;
+        return 0;
+    }
+    HYB_CUDA(cudaEventRecord(c->ev0, c->st));
+    // HGQ2 = W * GQ2 with W'W = H (primal barrier) or H^-1 (dual barrier): qrchol.jl:228-241
+    HYB_CHECK(hybi_cones_prod(c->st, c->cones, 5, c->GQ2, c->ldq, c->HGQ2, c->ldq, N));
+    // lhs = HGQ2' HGQ2, upper (outer_prod!, qrchol.jl:242)
+    HYB_CHECK(hyb_gemm_tn(c->st, N, N, q, 1.0, c->HGQ2, c->ldq, c->HGQ2, c->ldq, 0.0, c->S, c->ldS, HYB_GEMM_UPPER));
+    HYB_CUDA(cudaEventRecord(c->ev1, c->st));
+    // posdef_fact_copy! (dense.jl:228-249)
+    int info = 0, kind = 0;
+    HYB_CHECK(hyb_copy_upper(c->st, c->S, c->ldS, c->chol.F, c->chol.ld, N));
+    ++g_misc_launches;
+    HYB_CHECK(hyb_potrf(c->st, c->chol, &info));
+    if (info != 0) {
+        HYB_CHECK(hyb_copy_upper(c->st, c->S, c->ldS, c->chol.F, c->chol.ld, N));
+        increase_diag_kernel<<<(unsigned)((N + 255) / 256), 256, 0, c->st>>>(N, c->chol.F, c->chol.ld);
+        g_misc_launches += 2;
+        HYB_CUDA(cudaGetLastError());
+        HYB_CHECK(hyb_potrf(c->st, c->chol, &info));
+        kind = (info == 0) ? 2 : -1;
+    }
+    HYB_CUDA(cudaEventRecord(c->ev2, c->st));
+    HYB_CUDA(cudaEventSynchronize(c->ev2));
+    float ta = 0, tf = 0;
+    HYB_CUDA(cudaEventElapsedTime(&ta, c->ev0, c->ev1));
+    HYB_CUDA(cudaEventElapsedTime(&tf, c->ev1, c->ev2));
+    if (t_assemble_ms) *t_assemble_ms = ta;
+    if (t_fact_ms) *t_fact_ms = tf;
+    if (fact_kind) *fact_kind = kind;
+    c->fact_ok = (kind >= 0);
+    return kind < 0 ? 1 : 0;
+}
+
+int hyb_schur_get(hyb_ctx* c, double* lhs) {
+    if (!c || !c->loaded) return -1;
+    HYB_CUDA(cudaSetDevice(c->device));
+    if (c->N == 0) return 0;
+    HYB_CUDA(cudaMemcpy2D(lhs, sizeof(double) * c->N, c->S, sizeof(double) * c->ldS, sizeof(double) * c->N, c->N,
+                          cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+int hyb_schur_solve(hyb_ctx* c, const double* rhs, double* x, int64_t nrhs) {
+    if (!c || !c->loaded) return -1;
+    HYB_CUDA(cudaSetDevice(c->device));
+    const int64_t N = c->N;
+    if (N == 0) return 0;
+    for (int64_t j = 0; j < nrhs; ++j) {
+        HYB_CUDA(cudaMemcpyAsync(c->vn1, rhs + j * N, sizeof(double) * N, cudaMemcpyHostToDevice, c->st));
+        HYB_CHECK(hyb_potrs(c->st, c->chol, c->vn1));
+        g_misc_launches += 2;
+        HYB_CUDA(cudaMemcpyAsync(x + j * N, c->vn1, sizeof(double) * N, cudaMemcpyDeviceToHost, c->st));
+    }
+    HYB_CUDA(cudaStreamSynchronize(c->st));
+    return 0;
+}
+
+int hyb_G_mul(hyb_ctx* c, char trans, const double* v, double* out) {
+    if (!c || !c->loaded) return -1;
+    HYB_CUDA(cudaSetDevice(c->device));
+    const int64_t q = c->q, N = c->N;
+    if (trans == 'N' || trans == 'n') {
+        if (q == 0) return 0;
+        if (N > 0) HYB_CUDA(cudaMemcpyAsync(c->vn1, v, sizeof(double) * N, cudaMemcpyHostToDevice, c->st));
+        HYB_CHECK(hyb_gemv_n(c->st, q, N, c->GQ2, c->ldq, c->vn1, c->vq1, c->gemv_scratch));
+        g_misc_launches += 2;
+        HYB_CUDA(cudaMemcpyAsync(out, c->vq1, sizeof(double) * q, cudaMemcpyDeviceToHost, c->st));
+    } else {
+        if (N == 0) return 0;
+        if (q > 0) HYB_CUDA(cudaMemcpyAsync(c->vq1, v, sizeof(double) * q, cudaMemcpyHostToDevice, c->st));
+        HYB_CHECK(hyb_gemv_t(c->st, q, N, c->GQ2, c->ldq, c->vq1, c->vn1));
+        g_misc_launches += 1;
+        HYB_CUDA(cudaMemcpyAsync(out, c->vn1, sizeof(double) * N, cudaMemcpyDeviceToHost, c->st));
+    }
+    HYB_CUDA(cudaStreamSynchronize(c->st));
+    return 0;
+}
+
+int hyb_solve_subsystem3(hyb_ctx* c, const double* rhs_x, const double* rhs_z, double* sol_x, double* sol_z) {
+    if (!c || !c->loaded) return -1;
+    HYB_CUDA(cudaSetDevice(c->device));
+    if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(ensure_updated(c, c->loaded_scal));
+    const int64_t q = c->q, N = c->N;
+    cudaStream_t st = c->st;
+    if (q > 0) HYB_CUDA(cudaMemcpyAsync(c->vq1, rhs_z, sizeof(double) * q, cudaMemcpyHostToDevice, st));
+    if (N > 0) {
+        HYB_CUDA(cudaMemcpyAsync(c->vn1, rhs_x, sizeof(double) * N, cudaMemcpyHostToDevice, st));
+        // r = x + G'z
+        HYB_CHECK(hyb_gemv_t(st, q, N, c->GQ2, c->ldq, c->vq1, c->vn2));
+        axpby_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(N, 1.0, c->vn1, 1.0, c->vn2, c->vn1);
+        HYB_CUDA(cudaGetLastError());
+        // x = fact \ r
+        HYB_CHECK(hyb_potrs(st, c->chol, c->vn1));
+        // Gx
+        HYB_CHECK(hyb_gemv_n(st, q, N, c->GQ2, c->ldq, c->vn1, c->vq2, c->gemv_scratch));
+        g_misc_launches += 6;
+        HYB_CUDA(cudaMemcpyAsync(sol_x, c->vn1, sizeof(double) * N, cudaMemcpyDeviceToHost, st));
+    } else if (q > 0) {
+        HYB_CUDA(cudaMemsetAsync(c->vq2, 0, sizeof(double) * q, st));
+    }
+    if (q > 0) {
+        // z = Htilde (Gx) - z
+        HYB_CHECK(hybi_cones_prod(st, c->cones, 4, c->vq2, q, c->vq3, q, 1));
+        axpby_kernel<<<(unsigned)((q + 255) / 256), 256, 0, st>>>(q, 1.0, c->vq3, -1.0, c->vq1, c->vq3);
+        ++g_misc_launches;
+        HYB_CUDA(cudaGetLastError());
+        HYB_CUDA(cudaMemcpyAsync(sol_z, c->vq3, sizeof(double) * q, cudaMemcpyDeviceToHost, st));
+    }
+    HYB_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+// ----------------------------------------------------------------------------- dense helpers
+static int upload_padded(const double* h, int64_t rows, int64_t cols, int64_t ldh, double** d, int64_t* ldd) {
+    *ldd = hyb_round_up(rows > 0 ? rows : 1, 16);
+    HYB_CUDA(cudaMalloc(d, sizeof(double) * (*ldd) * (cols > 0 ? cols : 1)));
+    HYB_CUDA(cudaMemset(*d, 0, sizeof(double) * (*ldd) * (cols > 0 ? cols : 1)));
+    if (rows > 0 && cols > 0)
+        HYB_CUDA(cudaMemcpy2D(*d, sizeof(double) * (*ldd), h, sizeof(double) * ldh, sizeof(double) * rows, cols,
+                              cudaMemcpyHostToDevice));
+    return 0;
+}
+
+int hyb_gemm_tn_host(hyb_ctx* c, int64_t M, int64_t N, int64_t K, double alpha, const double* A, int64_t lda,
+                     const double* B, int64_t ldb, double beta, double* C, int64_t ldc) {
+    if (!c) return -1;
+    HYB_CUDA(cudaSetDevice(c->device));
+    double *dA = nullptr, *dB = nullptr, *dC = nullptr;
+    int64_t lA, lB, lC;
+    HYB_CHECK(upload_padded(A, K, M, lda, &dA, &lA));
+    HYB_CHECK(upload_padded(B, K, N, ldb, &dB, &lB));
+    HYB_CHECK(upload_padded(C, M, N, ldc, &dC, &lC));
+    int rc = hyb_gemm_tn(c->st, M, N, K, alpha, dA, lA, dB, lB, beta, dC, lC, 0);
+    if (rc == 0) {
+        cudaError_t e = cudaStreamSynchronize(c->st);
+        if (e == cudaSuccess)
+            e = cudaMemcpy2D(C, sizeof(double) * ldc, dC, sizeof(double) * lC, sizeof(double) * M, N, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) {
+            hyb_set_error("hyb_gemm_tn_host: %s", cudaGetErrorString(e));
+            rc = -1;
+        }
+    }
+    cudaFree(dA);
+    cudaFree(dB);
+    cudaFree(dC);
+    return rc;
+}
+
+int hyb_outer_prod(hyb_ctx* c, int64_t K, int64_t N, double alpha, const double* A, int64_t lda, double beta, double* C,
+                   int64_t ldc) {
+    if (!c) return -1;
+    HYB_CUDA(cudaSetDevice(c->device));
+    double *dA = nullptr, *dC = nullptr;
+    int64_t lA, lC;
+    HYB_CHECK(upload_padded(A, K, N, lda, &dA, &lA));
+    HYB_CHECK(upload_padded(C, N, N, ldc, &dC, &lC));
+    int rc = hyb_gemm_tn(c->st, N, N, K, alpha, dA, lA, dA, lA, beta, dC, lC, HYB_GEMM_UPPER);
+    if (rc == 0) {
+        cudaError_t e = cudaStreamSynchronize(c->st);
+        if (e == cudaSuccess)
+            e = cudaMemcpy2D(C, sizeof(double) * ldc, dC, sizeof(double) * lC, sizeof(double) * N, N, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) {
+            hyb_set_error("hyb_outer_prod: %s", cudaGetErrorString(e));
+            rc = -1;
+        }
+    }
+    cudaFree(dA);
+    cudaFree(dC);
+    return rc;
+}
+
+int hyb_posdef_solve(hyb_ctx* c, int64_t N, double* A, int64_t lda, double* B, int64_t ldb, int64_t nrhs, int* info) {
+    if (!c) return -1;
+    HYB_CUDA(cudaSetDevice(c->device));
+    HybChol ch;
+    HYB_CHECK(hyb_chol_alloc(ch, N));
+    int rc = 0;
+    cudaError_t e = cudaMemcpy2D(ch.F, sizeof(double) * ch.ld, A, sizeof(double) * lda, sizeof(double) * N, N,
+                                 cudaMemcpyHostToDevice);
+    int inf = 0;
+    if (e == cudaSuccess) rc = hyb_potrf(c->st, ch, &inf);
+    if (e == cudaSuccess && rc == 0) {
+        if (info) *info = inf;
+        e = cudaMemcpy2D(A, sizeof(double) * lda, ch.F, sizeof(double) * ch.ld, sizeof(double) * N, N,
+                         cudaMemcpyDeviceToHost);
+        for (int64_t j = 0; inf == 0 && e == cudaSuccess && rc == 0 && j < nrhs; ++j) {
+            e = cudaMemcpyAsync(ch.work, B + j * ldb, sizeof(double) * N, cudaMemcpyHostToDevice, c->st);
+            if (e == cudaSuccess) rc = hyb_potrs(c->st, ch, ch.work);
+            if (e == cudaSuccess && rc == 0)
+                e = cudaMemcpyAsync(B + j * ldb, ch.work, sizeof(double) * N, cudaMemcpyDeviceToHost, c->st);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(c->st);
+        }
+    }
+    if (e != cudaSuccess) {
+        hyb_set_error("hyb_posdef_solve: %s", cudaGetErrorString(e));
+        rc = -1;
+    }
+    hyb_chol_free(ch);
+    return rc;
+}
+
+}  // extern "C"

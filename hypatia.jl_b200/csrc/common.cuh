@@ -1,0 +1,68 @@
+// Shared declarations for the hypatia_b200 CUDA library (sm_100a only).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#define HYB_EPS 2.220446049250313e-16
+
+// Error plumbing: every internal routine returns cudaError_t-like int (0 = ok) and
+// records a message in a thread-local buffer that hyb_last_error() exposes.
+void hyb_set_error(const char* fmt, ...);
+const char* hyb_get_error();
+
+#define HYB_CUDA(call)                                                                     \
+    do {                                                                                   \
+        cudaError_t _e = (call);                                                           \
+        if (_e != cudaSuccess) {                                                           \
+            hyb_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(_e)); \
+            return -1;                                                                     \
+        }                                                                                  \
+    } while (0)
+
+#define HYB_CHECK(call)                 \
+    do {                                \
+        int _r = (call);                \
+        if (_r != 0) return _r;         \
+    } while (0)
+
+static inline int64_t hyb_round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
+
+// ---- dense engine (gemm_dmma.cu) ------------------------------------------------
+// C(MxN) = alpha * A' * B + beta * C.   A: K x M, B: K x N, all column-major with
+// even leading dimensions and 16-byte aligned bases (TMA requirement).
+// flags: HYB_GEMM_UPPER -> only tiles/entries with col >= row are computed/stored
+// (requires the A and B tile grids to coincide, i.e. SYRK-like use).
+enum { HYB_GEMM_UPPER = 1 };
+int hyb_gemm_tn(cudaStream_t st, int64_t M, int64_t N, int64_t K, double alpha, const double* A, int64_t lda,
+                const double* B, int64_t ldb, double beta, double* C, int64_t ldc, int flags);
+int64_t hyb_gemm_launch_count();
+
+// ---- factorization / solves (potrf.cu) -------------------------------------------
+struct HybChol {
+    int64_t N = 0, ld = 0, nblk = 0;
+    double* F = nullptr;      // N x N (ld), upper factor after hyb_potrf
+    double* Tinv = nullptr;   // nblk blocks of 128x128: inverses of the diagonal blocks of U
+    int* flags = nullptr;     // nblk ready flags for the wavefront solves
+    int* info = nullptr;      // device: index (1-based) of first non-positive pivot, 0 = success
+    int epoch = 0;
+    double* work = nullptr;   // N doubles
+};
+int hyb_chol_alloc(HybChol& ch, int64_t N);
+void hyb_chol_free(HybChol& ch);
+// in-place upper Cholesky of ch.F (upper triangle referenced); returns LAPACK-style info via *info_out
+int hyb_potrf(cudaStream_t st, HybChol& ch, int* info_out);
+// x <- (U'U)^-1 x for one device vector of length N
+int hyb_potrs(cudaStream_t st, HybChol& ch, double* x);
+
+// ---- gemv (gemv.cu) -----------------------------------------------------------------
+// y = G x (q) ; scratch must hold HYB_GEMV_SPLITS * q doubles
+#define HYB_GEMV_SPLITS 8
+int hyb_gemv_n(cudaStream_t st, int64_t q, int64_t N, const double* G, int64_t ld, const double* x, double* y,
+               double* scratch);
+// y = G' z (N)
+int hyb_gemv_t(cudaStream_t st, int64_t q, int64_t N, const double* G, int64_t ld, const double* z, double* y);

@@ -1,0 +1,177 @@
+// FP64 tensor-core contraction engine for sm_100a:  C = alpha * A' * B + beta * C.
+//
+// Replaces the dsyrk / dgemm call sites of the reference's hot path (SURVEY K1, K2,
+// K5 trailing updates, K13-K15): src/linearalgebra/dense.jl:72-79 (outer_prod! ->
+// BLAS.syrk!('U','T')), src/Solvers/systemsolvers/qrchol.jl:242,253.
+//
+// Design (B200): neither tcgen05 nor wgmma has an f64 kind; FP64 tensor work is the
+// warp-level DMMA (mma.sync m8n8k4 f64 -> SASS DMMA.8x8x4).  Both operands are
+// K-major (contraction index contiguous), so one TMA box {16 k, 128 rows} with the
+// 128-byte swizzle feeds fragments with the minimum 2 shared-memory wavefronts per
+// LDS.64.  One CTA = one 128x128 output tile, 8 consumer warps (64x32 each, 64
+// accumulators per thread) + 1 TMA producer warp, 4-stage mbarrier ring of
+// (16 KB A + 16 KB B).  Deterministic: no split-K atomics.
+#include "common.cuh"
+#include "tma.cuh"
+
+namespace {
+
+constexpr int BM = 128, BN = 128, BK = 16, STAGES = 4;
+constexpr int TILE_DOUBLES = BM * BK;           // 2048
+constexpr int TILE_BYTES = TILE_DOUBLES * 8;    // 16 KB
+constexpr int NUM_CONSUMER_WARPS = 8;
+constexpr int THREADS = (NUM_CONSUMER_WARPS + 1) * 32;
+constexpr int SMEM_BYTES = STAGES * 2 * TILE_BYTES + 1024 /*align slack*/ + 128 /*barriers*/;
+
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+}
+
+__global__ void __launch_bounds__(THREADS, 1)
+gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
+               double alpha, double beta, double* __restrict__ C, int64_t ldc, int flags, int tiles_m) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* base = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    double* sA = (double*)base;
+    double* sB = (double*)(base + STAGES * TILE_BYTES);
+    uint64_t* full = (uint64_t*)(base + 2 * STAGES * TILE_BYTES);
+    uint64_t* empty = full + STAGES;
+
+    int ti, tj;
+    if (flags & HYB_GEMM_UPPER) {
+        const int idx = blockIdx.x;
+        tj = (int)((sqrt(8.0 * idx + 1.0) - 1.0) * 0.5);
+        while (tj * (tj + 1) / 2 > idx) --tj;
+        while ((tj + 1) * (tj + 2) / 2 <= idx) ++tj;
+        ti = idx - tj * (tj + 1) / 2;
+    } else {
+        ti = blockIdx.x % tiles_m;
+        tj = blockIdx.x / tiles_m;
+    }
+    const int m0 = ti * BM, n0 = tj * BN;
+    const int nk = (K + BK - 1) / BK;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], NUM_CONSUMER_WARPS);
+        }
+        fence_barrier_init();
+    }
+    __syncthreads();
+
+    if (warp == NUM_CONSUMER_WARPS) {
+        // ---------------- TMA producer ----------------
+        if (lane == 0) {
+            for (int kt = 0; kt < nk; ++kt) {
+                const int s = kt % STAGES;
+                if (kt >= STAGES) mbar_wait(&empty[s], ((kt / STAGES) - 1) & 1);
+                mbar_arrive_expect_tx(&full[s], 2 * TILE_BYTES);
+                tma_load_2d(sA + s * TILE_DOUBLES, &tmA, kt * BK, m0, &full[s]);
+                tma_load_2d(sB + s * TILE_DOUBLES, &tmB, kt * BK, n0, &full[s]);
+            }
+        }
+        return;
+    }
+
+    // ---------------- DMMA consumers ----------------
+    const int wm = warp >> 2, wn = warp & 3;
+    const int g = lane >> 2, t = lane & 3;
+    double acc[8][4][2];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+    const int arow = (wm * 64 + g) * BK;  // + mt*8*BK
+    const int brow = (wn * 32 + g) * BK;  // + nt*8*BK
+
+    for (int kt = 0; kt < nk; ++kt) {
+        const int s = kt % STAGES;
+        mbar_wait(&full[s], (kt / STAGES) & 1);
+        const double* tA = sA + s * TILE_DOUBLES + arow;
+        const double* tB = sB + s * TILE_DOUBLES + brow;
+#pragma unroll
+        for (int kk = 0; kk < BK / 4; ++kk) {
+            // 128B swizzle: 16-byte chunk index (k>>1) is XORed with (row & 7) == g
+            const int off = ((((kk * 2) + (t >> 1)) ^ g) << 1) + (t & 1);
+            double a[8], b[4];
+#pragma unroll
+            for (int mt = 0; mt < 8; ++mt) a[mt] = tA[mt * 8 * BK + off];
+#pragma unroll
+            for (int nt = 0; nt < 4; ++nt) b[nt] = tB[nt * 8 * BK + off];
+#pragma unroll
+            for (int mt = 0; mt < 8; ++mt)
+#pragma unroll
+                for (int nt = 0; nt < 4; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], a[mt], b[nt]);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[s]);
+    }
+
+    // ---------------- epilogue ----------------
+    const bool upper = flags & HYB_GEMM_UPPER;
+#pragma unroll
+    for (int mt = 0; mt < 8; ++mt) {
+        const int row = m0 + wm * 64 + mt * 8 + g;
+        if (row >= M) continue;
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) {
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                const int col = n0 + wn * 32 + nt * 8 + 2 * t + i;
+                if (col >= N || (upper && col < row)) continue;
+                double* p = C + row + (int64_t)col * ldc;
+                double v = alpha * acc[mt][nt][i];
+                if (beta != 0.0) v += beta * (*p);
+                *p = v;
+            }
+        }
+    }
+}
+
+int64_t g_gemm_launches = 0;
+
+}  // namespace
+
+int64_t hyb_gemm_launch_count() { return g_gemm_launches; }
+
+int hyb_gemm_tn(cudaStream_t st, int64_t M, int64_t N, int64_t K, double alpha, const double* A, int64_t lda,
+                const double* B, int64_t ldb, double beta, double* C, int64_t ldc, int flags) {
+    if (M <= 0 || N <= 0) return 0;
+    if (K <= 0) {
+        hyb_set_error("hyb_gemm_tn: K must be positive");
+        return -1;
+    }
+    if ((lda & 1) || (ldb & 1) || ((uintptr_t)A & 15) || ((uintptr_t)B & 15)) {
+        hyb_set_error("hyb_gemm_tn: operands must be 16-byte aligned with even leading dimensions");
+        return -1;
+    }
+    static bool attr_set = false;
+    if (!attr_set) {
+        HYB_CUDA(cudaFuncSetAttribute(gemm_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        attr_set = true;
+    }
+    CUtensorMap tmA, tmB;
+    HYB_CHECK(hyb_make_tmap_2d_f64(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM));
+    HYB_CHECK(hyb_make_tmap_2d_f64(&tmB, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK, BN));
+    const int tiles_m = (int)((M + BM - 1) / BM), tiles_n = (int)((N + BN - 1) / BN);
+    int64_t ntiles;
+    if (flags & HYB_GEMM_UPPER) {
+        if (M != N) {
+            hyb_set_error("hyb_gemm_tn: UPPER needs a square result");
+            return -1;
+        }
+        ntiles = (int64_t)tiles_n * (tiles_n + 1) / 2;
+    } else {
+        ntiles = (int64_t)tiles_m * tiles_n;
+    }
+    gemm_tn_kernel<<<(unsigned)ntiles, THREADS, SMEM_BYTES, st>>>(tmA, tmB, (int)M, (int)N, (int)K, alpha, beta, C, ldc,
+                                                                 flags, tiles_m);
+    ++g_gemm_launches;
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}

@@ -1,0 +1,123 @@
+// HBM-bound matrix-vector products with the resident q x N matrix G (= G*Q2).
+//
+// Replaces the dgemv call sites of the reference's solve path:
+// qrchol.jl:59,80 (G'z, Gx in solve_subsystem3), systemsolvers/common.jl:95,98,151
+// (apply_lhs, solve_system) and Solvers.jl:638,656 (residuals).
+// Algorithmic traffic: 8*q*N bytes per product.  Fixed-order reductions (no atomics).
+#include "common.cuh"
+
+namespace {
+
+// y = G x : thread per row (coalesced down the rows), columns split over blockIdx.y,
+// partial sums to scratch[split][q]; second kernel adds the splits in fixed order.
+__global__ void __launch_bounds__(128)
+gemv_n_partial_kernel(int64_t q, int64_t N, const double* __restrict__ G, int64_t ld, const double* __restrict__ x,
+                      double* __restrict__ scratch) {
+    __shared__ double xs[512];
+    const int64_t row0 = (int64_t)blockIdx.x * 256 + threadIdx.x;  // each thread owns rows row0 and row0 + 128
+    const int split = blockIdx.y, nsplit = gridDim.y;
+    const int64_t cols_per = (N + nsplit - 1) / nsplit;
+    const int64_t c_begin = split * cols_per;
+    const int64_t c_end = (c_begin + cols_per < N) ? c_begin + cols_per : N;
+    double a0 = 0.0, a1 = 0.0;
+    const bool ok0 = row0 < q, ok1 = row0 + 128 < q;
+    for (int64_t cb = c_begin; cb < c_end; cb += 512) {
+        const int nc = (int)((c_end - cb < 512) ? (c_end - cb) : 512);
+        __syncthreads();
+        for (int i = threadIdx.x; i < nc; i += 128) xs[i] = x[cb + i];
+        __syncthreads();
+        const double* p = G + row0 + cb * ld;
+        int c = 0;
+        for (; c + 3 < nc; c += 4) {
+            double v00 = 0, v01 = 0, v02 = 0, v03 = 0, v10 = 0, v11 = 0, v12 = 0, v13 = 0;
+            if (ok0) {
+                v00 = __ldg(p + (int64_t)c * ld);
+                v01 = __ldg(p + (int64_t)(c + 1) * ld);
+                v02 = __ldg(p + (int64_t)(c + 2) * ld);
+                v03 = __ldg(p + (int64_t)(c + 3) * ld);
+            }
+            if (ok1) {
+                v10 = __ldg(p + 128 + (int64_t)c * ld);
+                v11 = __ldg(p + 128 + (int64_t)(c + 1) * ld);
+                v12 = __ldg(p + 128 + (int64_t)(c + 2) * ld);
+                v13 = __ldg(p + 128 + (int64_t)(c + 3) * ld);
+            }
+            a0 += v00 * xs[c] + v01 * xs[c + 1] + v02 * xs[c + 2] + v03 * xs[c + 3];
+            a1 += v10 * xs[c] + v11 * xs[c + 1] + v12 * xs[c + 2] + v13 * xs[c + 3];
+        }
+        for (; c < nc; ++c) {
+            if (ok0) a0 += __ldg(p + (int64_t)c * ld) * xs[c];
+            if (ok1) a1 += __ldg(p + 128 + (int64_t)c * ld) * xs[c];
+        }
+    }
+    if (ok0) scratch[(int64_t)split * q + row0] = a0;
+    if (ok1) scratch[(int64_t)split * q + row0 + 128] = a1;
+}
+
+__global__ void gemv_n_reduce_kernel(int64_t q, int nsplit, const double* __restrict__ scratch, double* __restrict__ y) {
+    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= q) return;
+    double s = 0.0;
+    for (int k = 0; k < nsplit; ++k) s += scratch[(int64_t)k * q + r];
+    y[r] = s;
+}
+
+// y = G' z : one warp per column, lanes stride down the column with double2 loads.
+__global__ void __launch_bounds__(256)
+gemv_t_kernel(int64_t q, int64_t N, const double* __restrict__ G, int64_t ld, const double* __restrict__ z,
+              double* __restrict__ y) {
+    const int lane = threadIdx.x & 31;
+    const int64_t col = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (col >= N) return;
+    const double* p = G + col * ld;
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+    const int64_t q2 = q & ~(int64_t)1;
+    int64_t r = 2 * lane;
+    for (; r + 192 < q2; r += 256) {
+        const double2 g0 = __ldg((const double2*)(p + r)), z0 = __ldg((const double2*)(z + r));
+        const double2 g1 = __ldg((const double2*)(p + r + 64)), z1 = __ldg((const double2*)(z + r + 64));
+        const double2 g2 = __ldg((const double2*)(p + r + 128)), z2 = __ldg((const double2*)(z + r + 128));
+        const double2 g3 = __ldg((const double2*)(p + r + 192)), z3 = __ldg((const double2*)(z + r + 192));
+        a0 += g0.x * z0.x + g0.y * z0.y;
+        a1 += g1.x * z1.x + g1.y * z1.y;
+        a2 += g2.x * z2.x + g2.y * z2.y;
+        a3 += g3.x * z3.x + g3.y * z3.y;
+    }
+    for (; r < q2; r += 64) {
+        const double2 g0 = __ldg((const double2*)(p + r)), z0 = __ldg((const double2*)(z + r));
+        a0 += g0.x * z0.x + g0.y * z0.y;
+    }
+    if (lane == 0 && (q & 1)) a1 += p[q - 1] * z[q - 1];
+    double v = (a0 + a1) + (a2 + a3);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) y[col] = v;
+}
+
+}  // namespace
+
+int hyb_gemv_n(cudaStream_t st, int64_t q, int64_t N, const double* G, int64_t ld, const double* x, double* y,
+               double* scratch) {
+    if (q == 0) return 0;
+    if (N == 0) {
+        HYB_CUDA(cudaMemsetAsync(y, 0, sizeof(double) * q, st));
+        return 0;
+    }
+    dim3 grid((unsigned)((q + 255) / 256), HYB_GEMV_SPLITS);
+    gemv_n_partial_kernel<<<grid, 128, 0, st>>>(q, N, G, ld, x, scratch);
+    HYB_CUDA(cudaGetLastError());
+    gemv_n_reduce_kernel<<<(unsigned)((q + 255) / 256), 256, 0, st>>>(q, HYB_GEMV_SPLITS, scratch, y);
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int hyb_gemv_t(cudaStream_t st, int64_t q, int64_t N, const double* G, int64_t ld, const double* z, double* y) {
+    if (N == 0) return 0;
+    if (q == 0) {
+        HYB_CUDA(cudaMemsetAsync(y, 0, sizeof(double) * N, st));
+        return 0;
+    }
+    gemv_t_kernel<<<(unsigned)((N + 7) / 8), 256, 0, st>>>(q, N, G, ld, z, y);
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}

@@ -1,0 +1,273 @@
+"""Product path: GPU-resident cone batch + B200QRCholSystemSolver, both thin
+wrappers over the C-ABI (include/hypatia_b200.h).  Mirrors, on the host side,
+the Julia types INTEGRATION.md describes:
+
+  B200QRCholSystemSolver{T} <: Solvers.QRCholSystemSolver{T}   (qrchol.jl:21,111-265)
+  B200ConeBatch{T}          <: Cones.Cone{T}                   (Cones.jl:34-304)
+
+No CPU arithmetic for the hot path happens here and there is no fallback: every
+oracle / assembly / factorization / solve is a C-ABI call into CUDA kernels.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import time
+from typing import List
+
+import numpy as np
+
+from . import cones_spec as cs
+from .host.coneset import ConeSet
+from .host.syscommon import QRCholSystemSolver
+from .lib import ConeDesc, Context, HybError, c_double_p, dptr, f64
+
+
+class GpuConeBatch(ConeSet):
+    """All cones of a model as one device-resident batch."""
+
+    def __init__(self, specs: List[cs.ConeSpec], ctx: Context):
+        super().__init__(specs)
+        self.ctx = ctx
+        self.lib = ctx.lib
+        self._grad = None
+        self._point = np.zeros(self.q)
+        self._keep = []  # keeps Ps arrays alive while descs reference them
+        self.descs = self._make_descs()
+        self.model_loaded = False
+
+    def _make_descs(self):
+        arr = (ConeDesc * max(self.K, 1))()
+        for k, s in enumerate(self.specs):
+            d = arr[k]
+            d.type = s.type_code
+            d.use_dual_barrier = int(s.use_dual_barrier)
+            d.offset = int(self.offs[k])
+            d.dim = int(s.dim)
+            d.side_or_R = int(getattr(s, "side", 0) or getattr(s, "R", 0) or 0)
+            d.U = int(getattr(s, "U", 0) or (s.dim if s.type_code == cs.WSOSINTERPNONNEGATIVE else 0))
+            Ps = getattr(s, "Ps", None)
+            if Ps:
+                mats = [f64(P) for P in Ps]
+                ptrs = (c_double_p * len(mats))(*[dptr(P) for P in mats])
+                Ls = (C.c_int64 * len(mats))(*[P.shape[1] for P in mats])
+                self._keep.append((mats, ptrs, Ls))
+                d.nPs = len(mats)
+                d.Ps = C.cast(ptrs, C.POINTER(c_double_p))
+                d.Ls = C.cast(Ls, C.POINTER(C.c_int64))
+            else:
+                d.nPs = 0
+        return arr
+
+    # The device model (G and the cones) is loaded by the system solver's load();
+    # until then the batch loads a cones-only model (N = 0) so the initial-point
+    # oracles of Solvers.jl:749-767 can run.
+    def setup(self):
+        if not self.model_loaded:
+            dummy = np.zeros(1)
+            self.ctx.check(
+                self.lib.hyb_model_load(self.ctx.ptr, self.q, 0, dptr(dummy), self.K, self.descs), "hyb_model_load"
+            )
+            self.model_loaded = True
+        self._pending_primal = None
+        self._pending_dual = np.zeros(self.q)
+        self._pending_scal = 1.0
+
+    def mark_model_loaded(self):
+        self.model_loaded = True
+        self._reload()
+
+    def _reload(self):
+        if self._pending_primal is not None:
+            self._push()
+
+    def _push(self):
+        p = f64(self._pending_primal)
+        d = f64(self._pending_dual)
+        self.ctx.check(self.lib.hyb_cones_load_point(self.ctx.ptr, dptr(p), dptr(d), float(self._pending_scal)), "hyb_cones_load_point")
+        self._grad = None
+        self._dirty = False
+
+    def load_point(self, primal, scal=1.0):
+        self._pending_primal = np.array(primal, dtype=np.float64)
+        self._pending_scal = float(scal)
+        self._point = self._pending_primal * scal if scal != 1.0 else self._pending_primal.copy()
+        self._dirty = True
+
+    def load_dual_point(self, dual):
+        self._pending_dual = np.array(dual, dtype=np.float64)
+        self._dirty = True
+
+    def reset_data(self):
+        self._dirty = True
+
+    def _sync(self):
+        if getattr(self, "_dirty", False):
+            self._push()
+
+    def point(self):
+        return self._point
+
+    def is_feas(self):
+        self._sync()
+        a, b = C.c_int(0), C.c_int(0)
+        self.ctx.check(self.lib.hyb_cones_is_feas(self.ctx.ptr, C.byref(a), C.byref(b)), "hyb_cones_is_feas")
+        return bool(a.value)
+
+    def is_dual_feas(self):
+        self._sync()
+        a, b = C.c_int(0), C.c_int(0)
+        self.ctx.check(self.lib.hyb_cones_is_feas(self.ctx.ptr, C.byref(a), C.byref(b)), "hyb_cones_is_feas")
+        return bool(b.value)
+
+    def grad(self):
+        self._sync()
+        if self._grad is None:
+            g = np.empty(self.q)
+            self.ctx.check(self.lib.hyb_cones_grad(self.ctx.ptr, dptr(g)), "hyb_cones_grad")
+            self._grad = g
+        return self._grad
+
+    def check_neighborhood(self, irtmu, use_max_prox, agg0, proxsqr_bound):
+        self._sync()
+        ok, agg = C.c_int(0), C.c_double(0.0)
+        self.ctx.check(
+            self.lib.hyb_cones_check(self.ctx.ptr, float(irtmu), int(use_max_prox), float(agg0), float(proxsqr_bound), C.byref(ok), C.byref(agg)),
+            "hyb_cones_check",
+        )
+        return bool(ok.value), float(agg.value)
+
+    def _prod(self, which, arr):
+        self._sync()
+        a = f64(arr)
+        m = 1 if a.ndim == 1 else a.shape[1]
+        out = np.empty_like(a, order="F")
+        self.ctx.check(self.lib.hyb_cones_hess_prod(self.ctx.ptr, which, dptr(a), dptr(out), m), "hyb_cones_hess_prod")
+        return out
+
+    def hess_prod(self, arr):
+        return self._prod(0, arr)
+
+    def inv_hess_prod(self, arr):
+        return self._prod(1, arr)
+
+    def sqrt_hess_prod(self, arr):
+        return self._prod(2, arr)
+
+    def inv_sqrt_hess_prod(self, arr):
+        return self._prod(3, arr)
+
+    def block_hess_prod(self, arr):
+        return self._prod(4, arr)
+
+    def hess_prod_slow(self, arr):
+        return self._prod(6, arr)
+
+    def dder3(self, direction):
+        self._sync()
+        d = f64(direction)
+        out = np.empty(self.q)
+        self.ctx.check(self.lib.hyb_cones_dder3(self.ctx.ptr, dptr(d), dptr(out)), "hyb_cones_dder3")
+        return out
+
+
+class B200QRCholSystemSolver(QRCholSystemSolver):
+    """Drop-in for QRCholDenseSystemSolver (qrchol.jl:111-265) on one B200."""
+
+    device_G = True
+
+    def __init__(self, ctx: Context):
+        self.ctx = ctx
+        self.lib = ctx.lib
+        self.time_assemble_ms = 0.0
+        self.time_fact_ms = 0.0
+        self.num_updates = 0
+        self.last_fact_kind = 0
+
+    def cones_factory(self, specs):
+        return GpuConeBatch(specs, self.ctx)
+
+    # ---- load (qrchol.jl:145-187): G*Q2 goes to the device once ------------------
+    def load(self, solver) -> None:
+        model = solver.model
+        assert model.p == 0, "B200QRCholSystemSolver expects the reduced model (p == 0, Ap_Q == I)"
+        cones = solver.cones
+        assert isinstance(cones, GpuConeBatch), "B200QRCholSystemSolver needs the GPU cone batch"
+        G = f64(model.G)
+        self.q, self.N = model.q, model.n
+        self.ctx.check(
+            self.lib.hyb_model_load(self.ctx.ptr, model.q, model.n, dptr(G), cones.K, cones.descs), "hyb_model_load"
+        )
+        cones.mark_model_loaded()
+        self.setup_point_sub(solver)
+
+    # ---- update_lhs (qrchol.jl:189-207) ------------------------------------------
+    def update_lhs(self, solver) -> None:
+        model, cones = solver.model, solver.cones
+        cones._sync()
+        ta, tf, kind = C.c_double(0), C.c_double(0), C.c_int(0)
+        rc = self.ctx.check(
+            self.lib.hyb_schur_update(self.ctx.ptr, C.byref(ta), C.byref(tf), C.byref(kind)), "hyb_schur_update"
+        )
+        self.time_assemble_ms += ta.value
+        self.time_fact_ms += tf.value
+        self.num_updates += 1
+        self.last_fact_kind = kind.value
+        solver.time_upfact += tf.value * 1e-3
+        if rc > 0:
+            print("positive definite linear system factorization failed")
+        self.rhs_const.z[:] = cones.block_hess_prod(model.h)
+        self.solve_subsystem3(solver, self.sol_const, self.rhs_const)
+
+    # ---- setup_rhs3 (qrchol.jl:23-44) --------------------------------------------
+    def setup_rhs3(self, solver, rhs, sol, rhs_sub) -> None:
+        cones = solver.cones
+        if cones.any_dual:
+            dr = cones.dual_rows
+            arr = np.where(dr, -rhs.z - rhs.s, rhs.z)
+            prod = cones.block_hess_prod(arr)
+            rhs_sub.z[:] = np.where(dr, prod, -prod - rhs.s)
+        else:
+            rhs_sub.z[:] = -cones.hess_prod(rhs.z) - rhs.s
+
+    # ---- solve_subsystem3 (qrchol.jl:46-92), p == 0 ------------------------------
+    def solve_subsystem3(self, solver, sol, rhs) -> None:
+        solver.cones._sync()
+        rx, rz = f64(rhs.x), f64(rhs.z)
+        sx = np.empty(self.N)
+        sz = np.empty(self.q)
+        self.ctx.check(
+            self.lib.hyb_solve_subsystem3(self.ctx.ptr, dptr(rx), dptr(rz), dptr(sx), dptr(sz)), "hyb_solve_subsystem3"
+        )
+        sol.x[:] = sx
+        sol.z[:] = sz
+
+    # ---- G products (K7 call sites) ------------------------------------------------
+    def G_mul(self, x):
+        out = np.empty(self.q)
+        xx = f64(x)
+        self.ctx.check(self.lib.hyb_G_mul(self.ctx.ptr, b"N", dptr(xx), dptr(out)), "hyb_G_mul")
+        return out
+
+    def Gt_mul(self, z):
+        out = np.empty(self.N)
+        zz = f64(z)
+        self.ctx.check(self.lib.hyb_G_mul(self.ctx.ptr, b"T", dptr(zz), dptr(out)), "hyb_G_mul")
+        return out
+
+    def schur_matrix(self) -> np.ndarray:
+        out = np.zeros((self.N, self.N), order="F")
+        self.ctx.check(self.lib.hyb_schur_get(self.ctx.ptr, dptr(out)), "hyb_schur_get")
+        return out
+
+    def free_memory(self) -> None:  # Solvers.jl:390 — device memory is owned by the context
+        pass
+
+
+def make_gpu_solver(device: int = 0, **solver_kwargs):
+    """Solver wired to the GPU backends (what `Hypatia.Optimizer(syssolver =
+    B200QRCholSystemSolver{Float64}(), use_dense_model = true)` selects in Julia)."""
+    from .host.solver import Solver
+
+    ctx = Context(device)
+    ss = B200QRCholSystemSolver(ctx)
+    return Solver(ss.cones_factory, ss, **solver_kwargs)

@@ -1,0 +1,168 @@
+"""ctypes binding of the C-ABI declared in include/hypatia_b200.h.
+
+There is NO CPU fallback: if the shared library is missing or no CUDA device
+is present, loading / context creation raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libhypatia_b200.so")
+
+c_double_p = C.POINTER(C.c_double)
+c_int_p = C.POINTER(C.c_int)
+
+
+class ConeDesc(C.Structure):
+    """struct hyb_cone_desc"""
+
+    _fields_ = [
+        ("type", C.c_int32),
+        ("use_dual_barrier", C.c_int32),
+        ("offset", C.c_int64),
+        ("dim", C.c_int64),
+        ("side_or_R", C.c_int64),
+        ("U", C.c_int64),
+        ("nPs", C.c_int32),
+        ("_pad", C.c_int32),
+        ("Ps", C.POINTER(c_double_p)),
+        ("Ls", C.POINTER(C.c_int64)),
+    ]
+
+
+# name -> (restype, argtypes); kept in sync with include/hypatia_b200.h (tests check the header)
+SIGNATURES = {
+    "hyb_ctx_create": (C.c_void_p, [C.c_int]),
+    "hyb_ctx_destroy": (None, [C.c_void_p]),
+    "hyb_last_error": (C.c_char_p, [C.c_void_p]),
+    "hyb_launch_count": (C.c_int64, []),
+    "hyb_model_load": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, c_double_p, C.c_int64, C.POINTER(ConeDesc)]),
+    "hyb_cones_load_point": (C.c_int, [C.c_void_p, c_double_p, c_double_p, C.c_double]),
+    "hyb_cones_is_feas": (C.c_int, [C.c_void_p, c_int_p, c_int_p]),
+    "hyb_cones_check": (C.c_int, [C.c_void_p, C.c_double, C.c_int, C.c_double, C.c_double, c_int_p, c_double_p]),
+    "hyb_cones_grad": (C.c_int, [C.c_void_p, c_double_p]),
+    "hyb_cones_hess_prod": (C.c_int, [C.c_void_p, C.c_int, c_double_p, c_double_p, C.c_int64]),
+    "hyb_cones_dder3": (C.c_int, [C.c_void_p, c_double_p, c_double_p]),
+    "hyb_schur_update": (C.c_int, [C.c_void_p, c_double_p, c_double_p, c_int_p]),
+    "hyb_schur_solve": (C.c_int, [C.c_void_p, c_double_p, c_double_p, C.c_int64]),
+    "hyb_schur_get": (C.c_int, [C.c_void_p, c_double_p]),
+    "hyb_G_mul": (C.c_int, [C.c_void_p, C.c_char, c_double_p, c_double_p]),
+    "hyb_solve_subsystem3": (C.c_int, [C.c_void_p, c_double_p, c_double_p, c_double_p, c_double_p]),
+    "hyb_outer_prod": (
+        C.c_int,
+        [C.c_void_p, C.c_int64, C.c_int64, C.c_double, c_double_p, C.c_int64, C.c_double, c_double_p, C.c_int64],
+    ),
+    "hyb_gemm_tn_host": (
+        C.c_int,
+        [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_double, c_double_p, C.c_int64, c_double_p, C.c_int64,
+         C.c_double, c_double_p, C.c_int64],
+    ),
+    "hyb_posdef_solve": (
+        C.c_int,
+        [C.c_void_p, C.c_int64, c_double_p, C.c_int64, c_double_p, C.c_int64, C.c_int64, c_int_p],
+    ),
+}
+
+_lib: Optional[C.CDLL] = None
+
+
+def load() -> C.CDLL:
+    """dlopen the CUDA library; raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} not found: build it with __graft_entry__.build() (make -C hypatia.jl_b200/csrc). "
+            "hypatia_b200 has no CPU fallback."
+        )
+    lib = C.CDLL(LIB_PATH)
+    for name, (restype, argtypes) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is missing
+        fn.restype = restype
+        fn.argtypes = argtypes
+    _lib = lib
+    return lib
+
+
+class HybError(RuntimeError):
+    pass
+
+
+def dptr(a: np.ndarray):
+    return a.ctypes.data_as(c_double_p)
+
+
+def f64(a, order="F") -> np.ndarray:
+    return np.require(a, dtype=np.float64, requirements=["F_CONTIGUOUS" if order == "F" else "C_CONTIGUOUS", "ALIGNED"])
+
+
+class Context:
+    """Owns one hyb_ctx (one GPU)."""
+
+    def __init__(self, device: int = 0):
+        self.lib = load()
+        self.ptr = self.lib.hyb_ctx_create(int(device))
+        if not self.ptr:
+            msg = self.lib.hyb_last_error(None)
+            raise HybError("hyb_ctx_create failed: " + (msg.decode() if msg else "unknown error"))
+
+    def check(self, rc: int, what: str) -> int:
+        if rc < 0:
+            msg = self.lib.hyb_last_error(self.ptr)
+            raise HybError(f"{what} failed ({rc}): " + (msg.decode() if msg else ""))
+        return rc
+
+    def close(self):
+        if getattr(self, "ptr", None):
+            self.lib.hyb_ctx_destroy(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def launch_count(self) -> int:
+        return int(self.lib.hyb_launch_count())
+
+    # ---- dense helpers -----------------------------------------------------
+    def outer_prod(self, A: np.ndarray, C_: Optional[np.ndarray] = None, alpha=1.0, beta=0.0) -> np.ndarray:
+        A = f64(A)
+        K, N = A.shape
+        out = np.zeros((N, N), order="F") if C_ is None else f64(C_).copy(order="F")
+        self.check(self.lib.hyb_outer_prod(self.ptr, K, N, alpha, dptr(A), max(K, 1), beta, dptr(out), max(N, 1)), "hyb_outer_prod")
+        return out
+
+    def gemm_tn(self, A: np.ndarray, B: np.ndarray, C_: Optional[np.ndarray] = None, alpha=1.0, beta=0.0) -> np.ndarray:
+        A, B = f64(A), f64(B)
+        K, M = A.shape
+        K2, N = B.shape
+        assert K == K2
+        out = np.zeros((M, N), order="F") if C_ is None else f64(C_).copy(order="F")
+        self.check(
+            self.lib.hyb_gemm_tn_host(self.ptr, M, N, K, alpha, dptr(A), max(K, 1), dptr(B), max(K, 1), beta, dptr(out), max(M, 1)),
+            "hyb_gemm_tn_host",
+        )
+        return out
+
+    def posdef_solve(self, A: np.ndarray, B: np.ndarray):
+        """Returns (U, X, info): upper Cholesky factor, solution of A X = B, LAPACK info."""
+        A = f64(A).copy(order="F")
+        B2 = f64(B).copy(order="F")
+        one_d = B2.ndim == 1
+        if one_d:
+            B2 = B2.reshape(-1, 1, order="F")
+        N = A.shape[0]
+        info = C.c_int(0)
+        self.check(
+            self.lib.hyb_posdef_solve(self.ptr, N, dptr(A), max(N, 1), dptr(B2), max(N, 1), B2.shape[1], C.byref(info)),
+            "hyb_posdef_solve",
+        )
+        return np.triu(A), (B2[:, 0] if one_d else B2), info.value

@@ -1,0 +1,120 @@
+/* hypatia_b200 — C ABI of the B200-native interior-point hot path.
+ *
+ * Plain C: pointers and sizes only.  Every entry point is what a Hypatia.jl
+ * `ccall` would bind for this path; the reference interface each one replaces is
+ * cited as file:line into jump-dev/Hypatia.jl v0.9.2.  All host arrays are
+ * column-major Float64 and owned by the caller; the library copies what it needs
+ * to the device and keeps no host pointer after a call returns.  All calls are
+ * synchronous at return.  One context drives one GPU (one process per GPU).
+ *
+ * Return convention: 0 = ok; > 0 = numerical condition reported through the out
+ * parameters (mirrors the reference, where numerical failure is not an
+ * exception, qrchol.jl:260-262); < 0 = CUDA / usage error, message available from
+ * hyb_last_error().
+ */
+#ifndef HYPATIA_B200_H
+#define HYPATIA_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct hyb_ctx hyb_ctx;
+
+/* cone type codes (src/Cones/*.jl) */
+enum hyb_cone_type {
+    HYB_CONE_NONNEGATIVE = 0,             /* nonnegative.jl */
+    HYB_CONE_EPINORMEUCL = 1,             /* epinormeucl.jl */
+    HYB_CONE_EPIPERSQUARE = 2,            /* epipersquare.jl */
+    HYB_CONE_POSSEMIDEFTRI = 3,           /* possemideftri.jl (real svec) */
+    HYB_CONE_WSOSINTERPNONNEGATIVE = 4,   /* wsosinterpnonnegative.jl */
+    HYB_CONE_WSOSINTERPPOSSEMIDEFTRI = 5  /* wsosinterppossemideftri.jl */
+};
+
+/* One entry per cone of model.cones, in order; offsets follow build_cone_idxs
+ * (src/Models/Models.jl:63-73), 0-based. */
+typedef struct hyb_cone_desc {
+    int32_t type;             /* hyb_cone_type */
+    int32_t use_dual_barrier; /* Cones.use_dual_barrier(cone) */
+    int64_t offset;           /* first row of the cone in s / z */
+    int64_t dim;              /* Cones.dimension(cone) */
+    int64_t side_or_R;        /* PSD side, or R for WSOS-PSD; 0 otherwise */
+    int64_t U;                /* WSOS: number of interpolation points; 0 otherwise */
+    int32_t nPs;              /* WSOS: number of P matrices */
+    int32_t _pad;
+    const double* const* Ps;  /* WSOS: nPs column-major U x L[k] matrices */
+    const int64_t* Ls;        /* WSOS: nPs column counts */
+} hyb_cone_desc;
+
+/* ---- context --------------------------------------------------------------- */
+/* Creates a context on CUDA device `device`.  NULL on failure (see hyb_last_error(NULL)). */
+hyb_ctx* hyb_ctx_create(int device);
+/* Solvers.free_memory(syssolver), Solvers.jl:390,796 */
+void hyb_ctx_destroy(hyb_ctx* ctx);
+const char* hyb_last_error(hyb_ctx* ctx);
+/* number of kernels this library has launched so far in this process */
+int64_t hyb_launch_count(void);
+
+/* ---- load: Solvers.load(syssolver, solver), qrchol.jl:145-187 ----------------
+ * GQ2 = (G*Ap_Q)[:, p+1:n] is the q x N matrix of the reduced model (ld = q). */
+int hyb_model_load(hyb_ctx* ctx, int64_t q, int64_t N, const double* GQ2, int64_t ncones, const hyb_cone_desc* descs);
+
+/* ---- cone batch: Cones oracle interface (src/Cones/Cones.jl:34-304) ----------- */
+/* load_point(cone, primal, scal) + load_dual_point + reset_data for every cone
+ * (Cones.jl:164-190; search.jl:144-146).  primal/dual are full q-vectors in
+ * primal-view / dual-view order (point.jl:52-59). */
+int hyb_cones_load_point(hyb_ctx* ctx, const double* primal, const double* dual, double scal);
+/* is_feas / is_dual_feas over all cones (Cones.jl:63,70) */
+int hyb_cones_is_feas(hyb_ctx* ctx, int* is_feas, int* is_dual_feas);
+/* cone loop of check_cone_points (search.jl:141-158): feasibility, dual feasibility,
+ * check_numerics (Cones.jl:267-284) and get_proxsqr (Cones.jl:288-304) aggregated with
+ * max (use_max_prox) or sum starting from agg0.  *ok = 1 iff every cone passes and the
+ * aggregate stays below proxsqr_bound. */
+int hyb_cones_check(hyb_ctx* ctx, double irtmu, int use_max_prox, double agg0, double proxsqr_bound, int* ok,
+                    double* agg);
+/* grad(cone) for every cone (Cones.jl:78) */
+int hyb_cones_grad(hyb_ctx* ctx, double* grad);
+/* hess_prod! / inv_hess_prod! / hess_prod_slow! / block_hess_prod! on a q x m array
+ * (Cones.jl:108-125,229-231; qrchol.jl:94-105).  which: 0 hess, 1 inv_hess,
+ * 2 sqrt_hess, 3 inv_sqrt_hess, 4 block (inv_hess for dual-barrier cones else hess),
+ * 6 hess_prod_slow. */
+int hyb_cones_hess_prod(hyb_ctx* ctx, int which, const double* arr, double* prod, int64_t m);
+/* dder3(cone, dir) for every cone (Cones.jl:139) */
+int hyb_cones_dder3(hyb_ctx* ctx, const double* dir, double* out);
+
+/* ---- Schur complement: update_lhs_fact, qrchol.jl:209-265 -----------------------
+ * Assembles lhs = sum_k (W_k GQ2_k)'(W_k GQ2_k) with the currently loaded cone state
+ * and factorizes it (posdef_fact_copy!, dense.jl:228-249).  fact_kind: 0 Cholesky,
+ * 2 Cholesky after the diagonal shift of increase_diag! (dense.jl:100-107), -1 failed.
+ * Times are CUDA-event milliseconds (time_upsys / time_upfact, Solvers.jl:112-113). */
+int hyb_schur_update(hyb_ctx* ctx, double* t_assemble_ms, double* t_fact_ms, int* fact_kind);
+/* ldiv!(x, fact, rhs), qrchol.jl:75; rhs and x are N x nrhs */
+int hyb_schur_solve(hyb_ctx* ctx, const double* rhs, double* x, int64_t nrhs);
+/* copy of the assembled N x N matrix (upper triangle valid), for tests / fallbacks */
+int hyb_schur_get(hyb_ctx* ctx, double* lhs);
+/* mul!(out, G, v) ('N', out has q entries) or mul!(out, G', v) ('T', N entries):
+ * qrchol.jl:59,80; systemsolvers/common.jl:95,98,151; Solvers.jl:638,656 */
+int hyb_G_mul(hyb_ctx* ctx, char trans, const double* v, double* out);
+/* solve_subsystem3 for the reduced model (p = 0), qrchol.jl:46-92:
+ *   r = rhs_x + G' rhs_z ;  sol_x = fact \ r ;  sol_z = Htilde (G sol_x) - rhs_z */
+int hyb_solve_subsystem3(hyb_ctx* ctx, const double* rhs_x, const double* rhs_z, double* sol_x, double* sol_z);
+
+/* ---- dense helpers: src/linearalgebra/dense.jl ---------------------------------- */
+/* outer_prod!(A, B, alpha, beta) = BLAS.syrk!('U','T'), dense.jl:72-79:
+ * C(N x N, upper) = alpha A'A + beta C with A K x N (lda), C (ldc) */
+int hyb_outer_prod(hyb_ctx* ctx, int64_t K, int64_t N, double alpha, const double* A, int64_t lda, double beta,
+                   double* C, int64_t ldc);
+/* mul!(C, A', B, alpha, beta), qrchol.jl:253: C(M x N) = alpha A'B + beta C */
+int hyb_gemm_tn_host(hyb_ctx* ctx, int64_t M, int64_t N, int64_t K, double alpha, const double* A, int64_t lda,
+                     const double* B, int64_t ldb, double beta, double* C, int64_t ldc);
+/* posdef_fact_copy!(mat2, mat, false) + ldiv!: factor the N x N matrix A (upper triangle
+ * referenced, overwritten by U) and solve for nrhs right-hand sides in B (N x nrhs, ldb).
+ * *info = LAPACK dpotrf info (0 success, j = leading minor j not positive definite). */
+int hyb_posdef_solve(hyb_ctx* ctx, int64_t N, double* A, int64_t lda, double* B, int64_t ldb, int64_t nrhs, int* info);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HYPATIA_B200_H */

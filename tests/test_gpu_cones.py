@@ -1,0 +1,161 @@
+"""Parity of the batched CUDA cone oracles against the CPU oracle cones on the same
+seeded points, through the C-ABI (GpuConeBatch).  Mirrors the identities the
+reference tests (test/cone.jl:31-129) plus direct value comparison."""
+import numpy as np
+import pytest
+
+import hypatia_b200  # noqa: F401
+from hypatia_b200 import cones_spec as cs
+from hypatia_b200.gpu import GpuConeBatch
+from oracle.cones import CpuConeSet
+
+from gpu_util import context, rel_err
+
+pytestmark = pytest.mark.gpu
+TOL = 1e3 * np.finfo(np.float64).eps
+
+
+def interior_point(specs, rng, noise=0.1, scale=1.0):
+    out = []
+    for s in specs:
+        p = s.initial_point()
+        if s.type_code == cs.POSSEMIDEFTRI:
+            B = rng.standard_normal((s.side, s.side)) * noise
+            p = p + cs.smat_to_svec(B @ B.T)
+        else:
+            p = p + noise * (2 * rng.random(s.dim) - 1) * (0.5 if s.type_code != cs.NONNEGATIVE else 1.0) / max(1.0, np.sqrt(s.dim) / 2)
+        out.append(p * scale)
+    return np.concatenate(out)
+
+
+SPEC_SETS = {
+    "nonneg": [cs.Nonnegative(1), cs.Nonnegative(6), cs.Nonnegative(300)],
+    "soc_small": [cs.EpiNormEucl(2)] + [cs.EpiNormEucl(3)] * 5 + [cs.EpiNormEucl(8)] * 40,
+    "rsoc_small": [cs.EpiPerSquare(3)] * 3 + [cs.EpiPerSquare(8)] * 33 + [cs.EpiPerSquare(4)],
+    "soc_large": [cs.EpiNormEucl(33), cs.EpiNormEucl(100), cs.EpiPerSquare(70), cs.EpiPerSquare(257)],
+    "psd": [cs.PosSemidefTri(cs.svec_length(s)) for s in (1, 2, 3, 5, 16, 16, 16, 32)],
+    "mixed": [cs.Nonnegative(10)] + [cs.EpiNormEucl(8)] * 4 + [cs.EpiPerSquare(8)] * 4
+    + [cs.PosSemidefTri(136)] * 3 + [cs.Nonnegative(3), cs.EpiNormEucl(5)],
+}
+
+
+def make_pair(specs):
+    cpu = CpuConeSet(specs)
+    gpu = GpuConeBatch(specs, context())
+    cpu.setup()
+    gpu.setup()
+    return cpu, gpu
+
+
+@pytest.mark.parametrize("name", sorted(SPEC_SETS))
+def test_oracles_match_cpu(name):
+    specs = SPEC_SETS[name]
+    rng = np.random.default_rng(sorted(SPEC_SETS).index(name) + 100)
+    cpu, gpu = make_pair(specs)
+    q = cpu.q
+    primal = interior_point(specs, rng, scale=0.7)
+    dual = interior_point(specs, rng, scale=1.3)
+    irtmu = 1.1
+    for c in (cpu, gpu):
+        c.load_point(primal, irtmu)
+        c.load_dual_point(dual)
+        c.reset_data()
+    assert cpu.is_feas() and gpu.is_feas()
+    assert cpu.is_dual_feas() and gpu.is_dual_feas()
+    assert rel_err(gpu.grad(), cpu.grad()) < TOL
+    assert rel_err(gpu.point(), cpu.point()) == 0.0
+    ok_c, agg_c = cpu.check_neighborhood(irtmu, True, 0.01, 1e6)
+    ok_g, agg_g = gpu.check_neighborhood(irtmu, True, 0.01, 1e6)
+    assert ok_c == ok_g
+    assert abs(agg_c - agg_g) <= 1e-9 * max(1.0, abs(agg_c))
+    ok_c, agg_c = cpu.check_neighborhood(irtmu, False, 0.01, 1e9)
+    ok_g, agg_g = gpu.check_neighborhood(irtmu, False, 0.01, 1e9)
+    assert ok_c == ok_g and abs(agg_c - agg_g) <= 1e-9 * max(1.0, abs(agg_c))
+
+    for m in (1, 7):
+        arr = rng.standard_normal(q) if m == 1 else np.asfortranarray(rng.standard_normal((q, m)))
+        for fn in ("hess_prod", "inv_hess_prod", "block_hess_prod", "hess_prod_slow"):
+            assert rel_err(getattr(gpu, fn)(arr), getattr(cpu, fn)(arr)) < 1e4 * TOL, (fn, m)
+        # sqrt factors against the per-cone CPU oracles
+        want_s = np.empty_like(arr)
+        want_i = np.empty_like(arr)
+        for k, c in enumerate(cpu.cones):
+            sl = slice(int(cpu.offs[k]), int(cpu.offs[k + 1]))
+            want_s[sl] = c.sqrt_hess_prod(arr[sl])
+            want_i[sl] = c.inv_sqrt_hess_prod(arr[sl])
+        assert rel_err(gpu.sqrt_hess_prod(arr), want_s) < 1e4 * TOL
+        assert rel_err(gpu.inv_sqrt_hess_prod(arr), want_i) < 1e4 * TOL
+    d = 0.1 * rng.standard_normal(q)
+    assert rel_err(gpu.dder3(d), cpu.dder3(d)) < 1e4 * TOL
+
+
+def test_oracle_identities_on_gpu():
+    """test/cone.jl:84-126 identities evaluated with the GPU oracles only."""
+    specs = SPEC_SETS["mixed"]
+    rng = np.random.default_rng(5)
+    _, gpu = make_pair(specs)
+    q = gpu.q
+    point = interior_point(specs, rng)
+    dualp = interior_point(specs, rng)
+    gpu.load_point(point)
+    gpu.load_dual_point(dualp)
+    gpu.reset_data()
+    g = gpu.grad()
+    nu_k = gpu.cone_dots(point, g)
+    assert np.allclose(nu_k, -gpu.nus, atol=TOL, rtol=TOL)
+    assert rel_err(gpu.hess_prod(point), -g) < 1e3 * TOL
+    assert rel_err(gpu.inv_hess_prod(g), -point) < 1e3 * TOL
+    E = np.asfortranarray(np.eye(q))
+    H = gpu.hess_prod(E)
+    Hi = gpu.inv_hess_prod(E)
+    assert rel_err(H @ Hi, np.eye(q)) < 1e4 * TOL
+    W = gpu.sqrt_hess_prod(E)
+    assert rel_err(W.T @ W, H) < 1e4 * TOL
+    Wi = gpu.inv_sqrt_hess_prod(E)
+    assert rel_err(Wi.T @ Wi, Hi) < 1e4 * TOL
+    assert rel_err(-gpu.dder3(point), g) < 1e3 * TOL
+    d = 0.1 * rng.standard_normal(q)
+    d3 = gpu.dder3(d)
+    assert np.allclose(gpu.cone_dots(d3, point), gpu.cone_dots(d, H @ d), rtol=1e-9, atol=1e-9)
+
+
+@pytest.mark.parametrize("which", ["primal", "dual"])
+def test_infeasible_points_are_rejected(which):
+    specs = SPEC_SETS["mixed"]
+    rng = np.random.default_rng(11)
+    cpu, gpu = make_pair(specs)
+    for k in range(len(specs)):
+        primal = interior_point(specs, rng)
+        dual = interior_point(specs, rng)
+        bad = primal if which == "primal" else dual
+        lo, hi = int(cpu.offs[k]), int(cpu.offs[k + 1])
+        bad[lo:hi] = -bad[lo:hi]  # push cone k's point out of the cone
+        for c in (cpu, gpu):
+            c.load_point(primal, 1.0)
+            c.load_dual_point(dual)
+            c.reset_data()
+        assert cpu.is_feas() == gpu.is_feas()
+        assert cpu.is_dual_feas() == gpu.is_dual_feas()
+        ok_c, _ = cpu.check_neighborhood(1.0, True, 0.0, 1e9)
+        ok_g, _ = gpu.check_neighborhood(1.0, True, 0.0, 1e9)
+        assert ok_c == ok_g and not ok_g
+
+
+def test_many_small_cones_batch():
+    """cfg4-shaped batch: thousands of EpiNormEucl(4) cones, HBM-bound kernels."""
+    K = 5000
+    specs = [cs.Nonnegative(64)] + [cs.EpiNormEucl(4)] * K
+    rng = np.random.default_rng(2)
+    cpu, gpu = make_pair(specs)
+    primal = interior_point(specs, rng)
+    dual = interior_point(specs, rng)
+    for c in (cpu, gpu):
+        c.load_point(primal, 0.9)
+        c.load_dual_point(dual)
+        c.reset_data()
+    assert rel_err(gpu.grad(), cpu.grad()) < TOL
+    arr = np.asfortranarray(rng.standard_normal((cpu.q, 3)))
+    assert rel_err(gpu.hess_prod(arr), cpu.hess_prod(arr)) < 1e3 * TOL
+    ok_c, agg_c = cpu.check_neighborhood(0.9, True, 0.0, 1e9)
+    ok_g, agg_g = gpu.check_neighborhood(0.9, True, 0.0, 1e9)
+    assert ok_c == ok_g and abs(agg_c - agg_g) <= 1e-10 * max(1, abs(agg_c))
