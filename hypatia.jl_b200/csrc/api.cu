@@ -549,4 +549,101 @@ int hyb_posdef_solve(hyb_ctx* c, int64_t N, double* A, int64_t lda, double* B, i
     return rc;
 }
 
+// ----------------------------------------------------------------------------- measurement
+__global__ void fill_pattern_kernel(int64_t rows, int64_t cols, int64_t ld, double* A, int spd) {
+    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t c = blockIdx.y;
+    if (r >= rows || c >= cols) return;
+    double v;
+    if (spd) {
+        const int64_t d = r > c ? r - c : c - r;
+        v = (d == 0) ? (double)rows : 1.0 / (1.0 + (double)d);
+    } else {
+        const uint64_t h = (uint64_t)(r * 1315423911ull + c * 2654435761ull + 12345ull);
+        v = (double)((h >> 11) & 0xFFFF) / 65536.0 - 0.5;
+    }
+    A[r + c * ld] = v;
+}
+
+int hyb_bench_gemm_tn(hyb_ctx* c, int64_t M, int64_t N, int64_t K, int upper, int reps, double* ms_per_launch) {
+    if (!c) return -1;
+    HYB_CUDA(cudaSetDevice(c->device));
+    const int64_t ldA = hyb_round_up(K, 16), ldC = hyb_round_up(M, 16);
+    double *A = nullptr, *B = nullptr, *C = nullptr;
+    HYB_CUDA(cudaMalloc(&A, sizeof(double) * ldA * M));
+    HYB_CUDA(cudaMalloc(&B, sizeof(double) * ldA * N));
+    HYB_CUDA(cudaMalloc(&C, sizeof(double) * ldC * N));
+    fill_pattern_kernel<<<dim3((unsigned)((K + 255) / 256), (unsigned)M), 256, 0, c->st>>>(K, M, ldA, A, 0);
+    fill_pattern_kernel<<<dim3((unsigned)((K + 255) / 256), (unsigned)N), 256, 0, c->st>>>(K, N, ldA, B, 0);
+    HYB_CUDA(cudaMemsetAsync(C, 0, sizeof(double) * ldC * N, c->st));
+    const int flags = upper ? HYB_GEMM_UPPER : 0;
+    int rc = 0;
+    for (int i = 0; i < 2 && rc == 0; ++i) rc = hyb_gemm_tn(c->st, M, N, K, 1.0, A, ldA, upper ? A : B, ldA, 0.0, C, ldC, flags);
+    if (rc == 0) {
+        cudaEventRecord(c->ev0, c->st);
+        for (int i = 0; i < reps && rc == 0; ++i)
+            rc = hyb_gemm_tn(c->st, M, N, K, 1.0, A, ldA, upper ? A : B, ldA, 0.0, C, ldC, flags);
+        cudaEventRecord(c->ev1, c->st);
+        cudaError_t e = cudaEventSynchronize(c->ev1);
+        float ms = 0;
+        if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+        if (e != cudaSuccess) {
+            hyb_set_error("hyb_bench_gemm_tn: %s", cudaGetErrorString(e));
+            rc = -1;
+        }
+        *ms_per_launch = ms / (reps > 0 ? reps : 1);
+    }
+    cudaFree(A);
+    cudaFree(B);
+    cudaFree(C);
+    return rc;
+}
+
+int hyb_bench_potrf(hyb_ctx* c, int64_t N, int reps, double* ms_factor, double* ms_solve) {
+    if (!c) return -1;
+    HYB_CUDA(cudaSetDevice(c->device));
+    HybChol ch;
+    HYB_CHECK(hyb_chol_alloc(ch, N));
+    double* A0 = nullptr;
+    HYB_CUDA(cudaMalloc(&A0, sizeof(double) * ch.ld * N));
+    fill_pattern_kernel<<<dim3((unsigned)((N + 255) / 256), (unsigned)N), 256, 0, c->st>>>(N, N, ch.ld, A0, 1);
+    int rc = 0, info = 0;
+    float tf = 0, ts = 0;
+    for (int i = 0; i < reps + 1 && rc == 0; ++i) {
+        cudaMemcpyAsync(ch.F, A0, sizeof(double) * ch.ld * N, cudaMemcpyDeviceToDevice, c->st);
+        cudaEventRecord(c->ev0, c->st);
+        rc = hyb_potrf(c->st, ch, nullptr);
+        cudaEventRecord(c->ev1, c->st);
+        cudaEventSynchronize(c->ev1);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+        if (i > 0) tf += ms;
+    }
+    if (rc == 0) {
+        cudaMemcpy(&info, ch.info, sizeof(int), cudaMemcpyDeviceToHost);
+        if (info != 0) {
+            hyb_set_error("hyb_bench_potrf: factorization failed, info %d", info);
+            rc = -1;
+        }
+    }
+    if (rc == 0) {
+        cudaMemsetAsync(ch.work, 0, sizeof(double) * N, c->st);
+        rc = hyb_potrs(c->st, ch, ch.work);
+        cudaEventRecord(c->ev0, c->st);
+        for (int i = 0; i < reps && rc == 0; ++i) rc = hyb_potrs(c->st, ch, ch.work);
+        cudaEventRecord(c->ev1, c->st);
+        cudaError_t e = cudaEventSynchronize(c->ev1);
+        if (e == cudaSuccess) e = cudaEventElapsedTime(&ts, c->ev0, c->ev1);
+        if (e != cudaSuccess) {
+            hyb_set_error("hyb_bench_potrf: %s", cudaGetErrorString(e));
+            rc = -1;
+        }
+    }
+    *ms_factor = tf / (reps > 0 ? reps : 1);
+    *ms_solve = ts / (reps > 0 ? reps : 1);
+    cudaFree(A0);
+    hyb_chol_free(ch);
+    return rc;
+}
+
 }  // extern "C"

@@ -66,6 +66,8 @@ SIGNATURES = {
         C.c_int,
         [C.c_void_p, C.c_int64, c_double_p, C.c_int64, c_double_p, C.c_int64, C.c_int64, c_int_p],
     ),
+    "hyb_bench_gemm_tn": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int, C.c_int, c_double_p]),
+    "hyb_bench_potrf": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, c_double_p, c_double_p]),
 }
 
 _lib: Optional[C.CDLL] = None
@@ -131,6 +133,17 @@ class Context:
 
     def launch_count(self) -> int:
         return int(self.lib.hyb_launch_count())
+
+    # ---- measurement ----------------------------------------------------------
+    def bench_gemm_tn(self, M, N, K, upper=False, reps=5) -> float:
+        ms = C.c_double(0)
+        self.check(self.lib.hyb_bench_gemm_tn(self.ptr, M, N, K, int(upper), reps, C.byref(ms)), "hyb_bench_gemm_tn")
+        return ms.value
+
+    def bench_potrf(self, N, reps=3):
+        mf, ms = C.c_double(0), C.c_double(0)
+        self.check(self.lib.hyb_bench_potrf(self.ptr, N, reps, C.byref(mf), C.byref(ms)), "hyb_bench_potrf")
+        return mf.value, ms.value
 
     # ---- dense helpers -----------------------------------------------------
     def outer_prod(self, A: np.ndarray, C_: Optional[np.ndarray] = None, alpha=1.0, beta=0.0) -> np.ndarray:

@@ -114,6 +114,13 @@ int hyb_gemm_tn_host(hyb_ctx* ctx, int64_t M, int64_t N, int64_t K, double alpha
  * *info = LAPACK dpotrf info (0 success, j = leading minor j not positive definite). */
 int hyb_posdef_solve(hyb_ctx* ctx, int64_t N, double* A, int64_t lda, double* B, int64_t ldb, int64_t nrhs, int* info);
 
+/* ---- measurement helpers (device-resident synthetic operands, CUDA-event timing on the
+ * library's own stream).  They time the same kernels the entry points above launch:
+ * the dsyrk / dgemm replacement (dense.jl:72-79, qrchol.jl:242,253) and the dpotrf /
+ * dpotrs replacement (dense.jl:226, qrchol.jl:75). */
+int hyb_bench_gemm_tn(hyb_ctx* ctx, int64_t M, int64_t N, int64_t K, int upper, int reps, double* ms_per_launch);
+int hyb_bench_potrf(hyb_ctx* ctx, int64_t N, int reps, double* ms_factor, double* ms_solve);
+
 #ifdef __cplusplus
 }
 #endif
