@@ -1,0 +1,351 @@
+#!/usr/bin/env python
+"""Headline benchmark: interior-point iterations per second on the synthetic block
+multi-cone model of BASELINE.json config 5 (Schur dimension N, q = 2N: Nonnegative /
+EpiNormEucl(8) / EpiPerSquare(8) / PosSemidefTri(side 16) quarters), with the
+Schur-assemble + Cholesky milliseconds and the FP64-tensor roofline of the dominant
+kernel (G'HG syrk on DMMA) beside it.
+
+  python bench.py --gpus 1 --steps 5 --warmup 3            # this repo's CUDA path
+  python bench.py --impl reference --steps 3 --warmup 1    # CPU restatement of the reference on host cores
+
+One "step" = one interior-point iteration (update_lhs -> 4 directions with refinement ->
+line search), the unit the reference itself counts (Solvers.jl:371-373, num_iters).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--N", type=int, default=int(os.environ.get("HYB_BENCH_N", 8192)), help="Schur dimension of the cfg5 model")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+
+    FIELDS = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index=0):
+        self.index = index
+        self.samples = []
+        self._stop = threading.Event()
+        self._thread = None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(
+                    ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits"],
+                    capture_output=True, text=True, timeout=5,
+                ).stdout.strip()
+                if out:
+                    self.samples.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def start(self):
+        self._thread = threading.Thread(target=self._run, daemon=True)
+        self._thread.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._thread:
+            self._thread.join(timeout=6)
+        sm, smax, reasons = [], [], set()
+        for s in self.samples:
+            try:
+                sm.append(float(s[0]))
+                smax.append(float(s[1]))
+            except Exception:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), s[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(smax)), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def build_model(N):
+    import hypatia_b200  # noqa: F401
+    from hypatia_b200 import instances
+
+    return instances.block_multicone(N=N, seed=1)
+
+
+def workload_config(N, model, extra=None):
+    cfg = {
+        "workload": f"cfg5 synthetic block multi-cone model: Schur dim N={N}, q={model.q}, "
+                    f"{len(model.cones)} cones (Nonnegative / EpiNormEucl(8) / EpiPerSquare(8) / PosSemidefTri(side 16) quarters), Float64",
+        "step": "one interior-point iteration (CombinedStepper, QRChol system solver, reference defaults)",
+        "N": N, "q": int(model.q), "cones": len(model.cones),
+        "l2": "inputs larger than L2 (G*Q2 is %.2f GB, Schur matrix %.2f GB)" % (model.q * N * 8 / 1e9, N * N * 8 / 1e9),
+    }
+    if extra:
+        cfg.update(extra)
+    return cfg
+
+
+class IterTimer:
+    """Per-iteration wall clock + library statistics, hooked on solver.iter_callback."""
+
+    def __init__(self, ctx=None, sync=None):
+        self.ctx, self.sync = ctx, sync
+        self.rows = []
+        self._t = None
+
+    def start(self):
+        if self.sync:
+            self.sync()
+        if self.ctx:
+            self.ctx.stats(reset=True)
+            self._launch0 = self.ctx.launch_count()
+        self._t = time.perf_counter()
+
+    def __call__(self, solver):
+        if self.sync:
+            self.sync()
+        now = time.perf_counter()
+        row = {"wall_s": now - self._t, "n_cand": solver.stepper.last_num_cand, "n_ref": solver.stepper.last_num_ref}
+        if self.ctx:
+            dev_ms, h2d, d2h = self.ctx.stats(reset=True)
+            tw, ts, tf = self.ctx.last_schur_timings()
+            lc = self.ctx.launch_count()
+            row.update(dev_ms=dev_ms, h2d=h2d, d2h=d2h, t_w=tw, t_syrk=ts, t_fact=tf, launches=lc - self._launch0)
+            self._launch0 = lc
+        self.rows.append(row)
+        self._t = time.perf_counter()
+
+
+def cublas_dgemm_tflops(n=8192, reps=3):
+    """Measuring stick only (never on the hot path): FP64 GEMM rate of cuBLAS on this GPU."""
+    import torch
+
+    a = torch.randn(n, n, dtype=torch.float64, device="cuda")
+    b = torch.randn(n, n, dtype=torch.float64, device="cuda")
+    torch.matmul(a.T, b)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        torch.matmul(a.T, b)
+    e1.record()
+    torch.cuda.synchronize()
+    del a, b
+    torch.cuda.empty_cache()
+    return 2.0 * n**3 * reps / (e0.elapsed_time(e1) * 1e-3) / 1e12
+
+
+def run_cpu_port(model, steps, warmup, preset_fact=None):
+    """CPU restatement of the reference path (oracle/, numpy/scipy -> OpenBLAS) on host cores."""
+    from hypatia_b200.host.solver import Solver
+    from oracle.cones import CpuConeSet
+    from oracle.qrchol import QRCholDenseSystemSolver
+
+    ss = QRCholDenseSystemSolver()
+    cpu = Solver(CpuConeSet, ss, iter_limit=warmup + steps)
+    cpu.preset_AG_fact = preset_fact
+    timer = IterTimer()
+    cpu.iter_callback = timer
+    cpu.load(model)
+    t0 = time.perf_counter()
+    orig_init = cpu._initialize_point
+
+    def init_and_start():
+        orig_init()
+        timer.start()
+
+    cpu._initialize_point = init_and_start
+    cpu.solve()
+    rows = timer.rows[warmup:] if len(timer.rows) > warmup else timer.rows
+    wall = sum(r["wall_s"] for r in rows)
+    return {
+        "iters_per_s": len(rows) / wall if wall > 0 else 0.0,
+        "steps": len(rows),
+        "ms_per_step": 1e3 * wall / max(len(rows), 1),
+        "assemble_ms": 1e3 * ss.time_assemble / max(cpu.num_iters, 1),
+        "factor_ms": 1e3 * cpu.time_upfact / max(cpu.num_iters, 1),
+        "total_s": time.perf_counter() - t0,
+        "status": cpu.status,
+    }
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    cores = os.cpu_count() or 1
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        N = args.N
+        steps, warmup = min(args.steps, 3), min(args.warmup, 1)
+        model = build_model(N)
+        res = run_cpu_port(model, steps, warmup)
+        line = {
+            "impl": "reference", "metric": "ipm_iterations_per_second", "value": res["iters_per_s"], "unit": "iterations/s",
+            "n_gpus": args.gpus, "steps": res["steps"], "warmup": warmup, "ms_per_step": res["ms_per_step"],
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(N, model),
+            "cpu_baseline": {"value": res["iters_per_s"], "unit": "iterations/s", "cores": cores, "kind": "port",
+                             "sample": f"{res['steps']} interior-point iterations of the same model after {warmup} warm-up "
+                                       f"(CPU restatement of the reference, numpy/scipy OpenBLAS; Julia is not available on this box)",
+                             "schur_assemble_ms": res["assemble_ms"], "cholesky_ms": res["factor_ms"]},
+            "e2e": {"value": res["iters_per_s"], "unit": "iterations/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        }
+        print(json.dumps(line))
+        return
+
+    import torch
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the hypatia_b200 hot path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+
+        dist = dist_mod
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    import hypatia_b200  # noqa: F401
+    from hypatia_b200.gpu import make_gpu_solver
+
+    N = args.N
+    model = build_model(N)
+    steps, warmup = args.steps, max(args.warmup, 3)
+    gpu = make_gpu_solver(local_rank, iter_limit=warmup + steps, dist=dist)
+    ctx = gpu.syssolver.ctx
+
+    def sync():
+        torch.cuda.synchronize()
+
+    timer = IterTimer(ctx, sync)
+    sampler = ClockSampler(local_rank)
+    state = {"t_start": None}
+
+    def callback(solver):
+        timer(solver)
+        if len(timer.rows) == warmup + steps:
+            if dist is not None:
+                dist.barrier()
+            sync()
+            state["t_end"] = time.perf_counter()
+        if len(timer.rows) == warmup:  # timed region starts after the warm-up iterations
+            if dist is not None:
+                dist.barrier()
+            sync()
+            sampler.start()
+            state["t_start"] = time.perf_counter()
+            timer._t = time.perf_counter()
+
+    gpu.iter_callback = callback
+    gpu.load(model)
+    orig_init = gpu._initialize_point
+
+    def init_and_start():
+        orig_init()
+        timer.start()
+
+    gpu._initialize_point = init_and_start
+    gpu.solve()
+    sync()
+    if dist is not None:
+        dist.barrier()
+    t_end = state.get("t_end") or time.perf_counter()
+    clocks = sampler.stop()
+    rows = timer.rows[warmup:]
+    if not rows:
+        raise SystemExit(f"bench.py: the solve ended after {len(timer.rows)} iterations, before the timed region")
+    k = len(rows)
+    wall = t_end - state["t_start"]
+    if dist is not None:
+        tw = torch.tensor([wall], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tw, op=dist.ReduceOp.MAX)
+        wall = float(tw.item())
+    dev_s = sum(r["dev_ms"] for r in rows) * 1e-3
+    ms_per_step = 1e3 * wall / k
+    h2d = sum(r["h2d"] for r in rows) / k
+    d2h = sum(r["d2h"] for r in rows) / k
+    t_syrk = float(np.mean([r["t_syrk"] for r in rows]))
+    t_w = float(np.mean([r["t_w"] for r in rows]))
+    t_fact = float(np.mean([r["t_fact"] for r in rows]))
+    launches = int(sum(r["launches"] for r in rows))
+    if rank != 0:
+        return
+
+    q_sqrt = model.q  # every cone of this model takes the sqrt-oracle (syrk) branch, qrchol.jl:228-242
+    syrk_flops = q_sqrt * N * (N + 1)  # algorithmic flops of the G'HG contraction per launch
+    peak_tf = cublas_dgemm_tflops()
+    achieved_tf = syrk_flops / (t_syrk * 1e-3) / 1e12
+    line = {
+        "metric": "ipm_iterations_per_second",
+        "value": k / dev_s if dev_s > 0 else None,
+        "unit": "iterations/s",
+        "n_gpus": world,
+        "steps": k,
+        "warmup": warmup,
+        "ms_per_step": ms_per_step,
+        "higher_is_better": True,
+        "scaling": "strong",
+        "vs_baseline": None,
+        "dtype": "f64",
+        "data": "synthetic",
+        "config": workload_config(N, model, {
+            "value_definition": "iterations / device time: CUDA-event time of every kernel region of the C-ABI calls of the timed iterations (inputs resident in HBM)",
+            "e2e_definition": "iterations / wall time of the same iterations through the C-ABI with host vectors (all H2D/D2H copies and the host-side stepper included)",
+            "status_after_limit": gpu.status, "iterations_run": gpu.num_iters,
+            "line_search_candidates_per_step": float(np.mean([r["n_cand"] for r in rows])),
+            "refinement_solves_per_step": float(np.mean([r["n_ref"] for r in rows])),
+        }),
+        "e2e": {"value": k / wall, "unit": "iterations/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "gpu_launches": launches,
+        "schur_assemble_ms": t_w + t_syrk,
+        "cholesky_ms": t_fact,
+        "clocks": clocks,
+        "roofline": {
+            "kernel": "gemm_tn_kernel (G'HG syrk, FP64 DMMA, TMA-fed)",
+            "bound": "tensor", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
+            "frac": achieved_tf / peak_tf if peak_tf else None,
+            "peak_source": "cuBLAS DGEMM 8192^3 measured in this run (MEASURED_PEAKS.json has no FP64 figure; FP64 tensor work on sm_100a is DMMA, not tcgen05)",
+            "algorithmic_flops_per_launch": syrk_flops, "avg_launch_ms": t_syrk,
+            "traffic": None,
+        },
+    }
+    if not args.no_cpu_baseline and world == 1:
+        steps_cpu = 2
+        res = run_cpu_port(build_model(N), steps_cpu, 1, preset_fact=getattr(gpu, "AG_fact", None))
+        line["cpu_baseline"] = {
+            "value": res["iters_per_s"], "unit": "iterations/s", "cores": cores, "kind": "port",
+            "sample": f"{res['steps']} interior-point iterations of the same model after 1 warm-up iteration "
+                      f"(CPU restatement of the reference, numpy/scipy OpenBLAS, {cores} host cores)",
+            "schur_assemble_ms": res["assemble_ms"], "cholesky_ms": res["factor_ms"],
+        }
+    print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

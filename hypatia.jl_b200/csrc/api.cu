@@ -89,8 +89,30 @@ struct hyb_ctx {
     double updated_irtmu = NAN;
     bool point_loaded = false;
     bool fact_ok = false;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr, evA = nullptr, evB = nullptr;
+    // statistics (hyb_stats): device milliseconds between the last H2D and the first D2H of every
+    // compute call, and the bytes moved across PCIe by the calls
+    double dev_ms = 0.0;
+    int64_t h2d_bytes = 0, d2h_bytes = 0;
+    double last_t[4] = {0, 0, 0, 0};  // apply-W, syrk, factor, (unused)
+    bool in_region = false;
 };
+
+static inline cudaError_t h2d(hyb_ctx* c, void* dst, const void* src, size_t bytes) {
+    c->h2d_bytes += (int64_t)bytes;
+    return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->st);
+}
+static inline cudaError_t d2h(hyb_ctx* c, void* dst, const void* src, size_t bytes) {
+    c->d2h_bytes += (int64_t)bytes;
+    return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c->st);
+}
+// device-time region: KBEGIN after the uploads, KEND before the downloads, KSYNC after the final sync
+#define KBEGIN(c) cudaEventRecord((c)->evA, (c)->st)
+#define KEND(c) cudaEventRecord((c)->evB, (c)->st)
+static inline void ksync(hyb_ctx* c) {
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, c->evA, c->evB) == cudaSuccess) c->dev_ms += ms;
+}
 
 static void free_model(hyb_ctx* c) {
     cudaFree(c->GQ2);
@@ -144,7 +166,9 @@ hyb_ctx* hyb_ctx_create(int device) {
     hyb_ctx* c = new hyb_ctx();
     c->device = device;
     if (cudaStreamCreate(&c->st) != cudaSuccess || cudaEventCreate(&c->ev0) != cudaSuccess ||
-        cudaEventCreate(&c->ev1) != cudaSuccess || cudaEventCreate(&c->ev2) != cudaSuccess) {
+        cudaEventCreate(&c->ev1) != cudaSuccess || cudaEventCreate(&c->ev2) != cudaSuccess ||
+        cudaEventCreate(&c->ev3) != cudaSuccess || cudaEventCreate(&c->evA) != cudaSuccess ||
+        cudaEventCreate(&c->evB) != cudaSuccess) {
         hyb_set_error("stream / event creation failed");
         delete c;
         return nullptr;
@@ -160,13 +184,18 @@ void hyb_ctx_destroy(hyb_ctx* c) {
     cudaEventDestroy(c->ev0);
     cudaEventDestroy(c->ev1);
     cudaEventDestroy(c->ev2);
+    cudaEventDestroy(c->ev3);
+    cudaEventDestroy(c->evA);
+    cudaEventDestroy(c->evB);
     cudaStreamDestroy(c->st);
     delete c;
 }
 
 const char* hyb_last_error(hyb_ctx*) { return hyb_get_error(); }
 
-int64_t hyb_launch_count(void) { return hyb_gemm_launch_count() + hybi_cones_launch_count() + g_misc_launches; }
+int64_t hyb_launch_count(void) {
+    return hyb_gemm_launch_count() + hyb_potrf_launch_count() + hybi_cones_launch_count() + g_misc_launches;
+}
 
 int hyb_model_load(hyb_ctx* c, int64_t q, int64_t N, const double* GQ2, int64_t ncones, const hyb_cone_desc* descs) {
     if (!c) return -1;
@@ -245,15 +274,18 @@ int hyb_cones_load_point(hyb_ctx* c, const double* primal, const double* dual, d
     if (!c || !c->loaded) return -1;
     HYB_CUDA(cudaSetDevice(c->device));
     if (c->q > 0) {
-        HYB_CUDA(cudaMemcpyAsync(c->in_primal, primal, sizeof(double) * c->q, cudaMemcpyHostToDevice, c->st));
-        HYB_CUDA(cudaMemcpyAsync(c->in_dual, dual, sizeof(double) * c->q, cudaMemcpyHostToDevice, c->st));
+        HYB_CUDA(h2d(c, c->in_primal, primal, sizeof(double) * c->q));
+        HYB_CUDA(h2d(c, c->in_dual, dual, sizeof(double) * c->q));
     }
     c->loaded_scal = scal;
     c->point_loaded = true;
     c->updated_irtmu = NAN;
     // in the line search scal == irtmu (search.jl:144), so this is normally the only update
+    KBEGIN(c);
     HYB_CHECK(ensure_updated(c, scal));
+    KEND(c);
     HYB_CUDA(cudaStreamSynchronize(c->st));
+    ksync(c);
     return 0;
 }
 
@@ -287,7 +319,7 @@ int hyb_cones_grad(hyb_ctx* c, double* grad) {
     if (!c || !c->loaded) return -1;
     HYB_CUDA(cudaSetDevice(c->device));
     if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(ensure_updated(c, c->loaded_scal));
-    if (c->q > 0) HYB_CUDA(cudaMemcpyAsync(grad, c->cones.grad, sizeof(double) * c->q, cudaMemcpyDeviceToHost, c->st));
+    if (c->q > 0) HYB_CUDA(d2h(c, grad, c->cones.grad, sizeof(double) * c->q));
     HYB_CUDA(cudaStreamSynchronize(c->st));
     return 0;
 }
@@ -309,11 +341,14 @@ int hyb_cones_hess_prod(hyb_ctx* c, int which, const double* arr, double* prod, 
         HYB_CUDA(cudaMalloc(&din, sizeof(double) * q * m));
         HYB_CUDA(cudaMalloc(&dout, sizeof(double) * q * m));
     }
-    HYB_CUDA(cudaMemcpyAsync(din, arr, sizeof(double) * q * m, cudaMemcpyHostToDevice, c->st));
+    HYB_CUDA(h2d(c, din, arr, sizeof(double) * q * m));
+    KBEGIN(c);
     int rc = hybi_cones_prod(c->st, c->cones, which, din, q, dout, q, m);
+    KEND(c);
     if (rc == 0) {
-        cudaError_t e = cudaMemcpyAsync(prod, dout, sizeof(double) * q * m, cudaMemcpyDeviceToHost, c->st);
+        cudaError_t e = d2h(c, prod, dout, sizeof(double) * q * m);
         if (e == cudaSuccess) e = cudaStreamSynchronize(c->st);
+        ksync(c);
         if (e != cudaSuccess) {
             hyb_set_error("hyb_cones_hess_prod: %s", cudaGetErrorString(e));
             rc = -1;
@@ -331,10 +366,13 @@ int hyb_cones_dder3(hyb_ctx* c, const double* dir, double* out) {
     HYB_CUDA(cudaSetDevice(c->device));
     if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(ensure_updated(c, c->loaded_scal));
     if (c->q == 0) return 0;
-    HYB_CUDA(cudaMemcpyAsync(c->vq1, dir, sizeof(double) * c->q, cudaMemcpyHostToDevice, c->st));
+    HYB_CUDA(h2d(c, c->vq1, dir, sizeof(double) * c->q));
+    KBEGIN(c);
     HYB_CHECK(hybi_cones_dder3(c->st, c->cones, c->vq1, c->vq2));
-    HYB_CUDA(cudaMemcpyAsync(out, c->vq2, sizeof(double) * c->q, cudaMemcpyDeviceToHost, c->st));
+    KEND(c);
+    HYB_CUDA(d2h(c, out, c->vq2, sizeof(double) * c->q));
     HYB_CUDA(cudaStreamSynchronize(c->st));
+    ksync(c);
     return 0;
 }
 
@@ -353,6 +391,7 @@ int hyb_schur_update(hyb_ctx* c, double* t_assemble_ms, double* t_fact_ms, int* 
     HYB_CUDA(cudaEventRecord(c->ev0, c->st));
     // HGQ2 = W * GQ2 with W'W = H (primal barrier) or H^-1 (dual barrier): qrchol.jl:228-241
     HYB_CHECK(hybi_cones_prod(c->st, c->cones, 5, c->GQ2, c->ldq, c->HGQ2, c->ldq, N));
+    HYB_CUDA(cudaEventRecord(c->ev3, c->st));
     // lhs = HGQ2' HGQ2, upper (outer_prod!, qrchol.jl:242)
     HYB_CHECK(hyb_gemm_tn(c->st, N, N, q, 1.0, c->HGQ2, c->ldq, c->HGQ2, c->ldq, 0.0, c->S, c->ldS, HYB_GEMM_UPPER));
     HYB_CUDA(cudaEventRecord(c->ev1, c->st));
@@ -371,9 +410,14 @@ int hyb_schur_update(hyb_ctx* c, double* t_assemble_ms, double* t_fact_ms, int* 
     }
     HYB_CUDA(cudaEventRecord(c->ev2, c->st));
     HYB_CUDA(cudaEventSynchronize(c->ev2));
-    float ta = 0, tf = 0;
+    float ta = 0, tf = 0, tw = 0;
     HYB_CUDA(cudaEventElapsedTime(&ta, c->ev0, c->ev1));
     HYB_CUDA(cudaEventElapsedTime(&tf, c->ev1, c->ev2));
+    HYB_CUDA(cudaEventElapsedTime(&tw, c->ev0, c->ev3));
+    c->last_t[0] = tw;
+    c->last_t[1] = ta - tw;
+    c->last_t[2] = tf;
+    c->dev_ms += ta + tf;
     if (t_assemble_ms) *t_assemble_ms = ta;
     if (t_fact_ms) *t_fact_ms = tf;
     if (fact_kind) *fact_kind = kind;
@@ -396,12 +440,14 @@ int hyb_schur_solve(hyb_ctx* c, const double* rhs, double* x, int64_t nrhs) {
     const int64_t N = c->N;
     if (N == 0) return 0;
     for (int64_t j = 0; j < nrhs; ++j) {
-        HYB_CUDA(cudaMemcpyAsync(c->vn1, rhs + j * N, sizeof(double) * N, cudaMemcpyHostToDevice, c->st));
+        HYB_CUDA(h2d(c, c->vn1, rhs + j * N, sizeof(double) * N));
+        KBEGIN(c);
         HYB_CHECK(hyb_potrs(c->st, c->chol, c->vn1));
-        g_misc_launches += 2;
-        HYB_CUDA(cudaMemcpyAsync(x + j * N, c->vn1, sizeof(double) * N, cudaMemcpyDeviceToHost, c->st));
+        KEND(c);
+        HYB_CUDA(d2h(c, x + j * N, c->vn1, sizeof(double) * N));
+        HYB_CUDA(cudaStreamSynchronize(c->st));
+        ksync(c);
     }
-    HYB_CUDA(cudaStreamSynchronize(c->st));
     return 0;
 }
 
@@ -411,18 +457,23 @@ int hyb_G_mul(hyb_ctx* c, char trans, const double* v, double* out) {
     const int64_t q = c->q, N = c->N;
     if (trans == 'N' || trans == 'n') {
         if (q == 0) return 0;
-        if (N > 0) HYB_CUDA(cudaMemcpyAsync(c->vn1, v, sizeof(double) * N, cudaMemcpyHostToDevice, c->st));
+        if (N > 0) HYB_CUDA(h2d(c, c->vn1, v, sizeof(double) * N));
+        KBEGIN(c);
         HYB_CHECK(hyb_gemv_n(c->st, q, N, c->GQ2, c->ldq, c->vn1, c->vq1, c->gemv_scratch));
+        KEND(c);
         g_misc_launches += 2;
-        HYB_CUDA(cudaMemcpyAsync(out, c->vq1, sizeof(double) * q, cudaMemcpyDeviceToHost, c->st));
+        HYB_CUDA(d2h(c, out, c->vq1, sizeof(double) * q));
     } else {
         if (N == 0) return 0;
-        if (q > 0) HYB_CUDA(cudaMemcpyAsync(c->vq1, v, sizeof(double) * q, cudaMemcpyHostToDevice, c->st));
+        if (q > 0) HYB_CUDA(h2d(c, c->vq1, v, sizeof(double) * q));
+        KBEGIN(c);
         HYB_CHECK(hyb_gemv_t(c->st, q, N, c->GQ2, c->ldq, c->vq1, c->vn1));
+        KEND(c);
         g_misc_launches += 1;
-        HYB_CUDA(cudaMemcpyAsync(out, c->vn1, sizeof(double) * N, cudaMemcpyDeviceToHost, c->st));
+        HYB_CUDA(d2h(c, out, c->vn1, sizeof(double) * N));
     }
     HYB_CUDA(cudaStreamSynchronize(c->st));
+    ksync(c);
     return 0;
 }
 
@@ -432,9 +483,10 @@ int hyb_solve_subsystem3(hyb_ctx* c, const double* rhs_x, const double* rhs_z, d
     if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(ensure_updated(c, c->loaded_scal));
     const int64_t q = c->q, N = c->N;
     cudaStream_t st = c->st;
-    if (q > 0) HYB_CUDA(cudaMemcpyAsync(c->vq1, rhs_z, sizeof(double) * q, cudaMemcpyHostToDevice, st));
+    if (q > 0) HYB_CUDA(h2d(c, c->vq1, rhs_z, sizeof(double) * q));
+    if (N > 0) HYB_CUDA(h2d(c, c->vn1, rhs_x, sizeof(double) * N));
+    KBEGIN(c);
     if (N > 0) {
-        HYB_CUDA(cudaMemcpyAsync(c->vn1, rhs_x, sizeof(double) * N, cudaMemcpyHostToDevice, st));
         // r = x + G'z
         HYB_CHECK(hyb_gemv_t(st, q, N, c->GQ2, c->ldq, c->vq1, c->vn2));
         axpby_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(N, 1.0, c->vn1, 1.0, c->vn2, c->vn1);
@@ -443,8 +495,7 @@ int hyb_solve_subsystem3(hyb_ctx* c, const double* rhs_x, const double* rhs_z, d
         HYB_CHECK(hyb_potrs(st, c->chol, c->vn1));
         // Gx
         HYB_CHECK(hyb_gemv_n(st, q, N, c->GQ2, c->ldq, c->vn1, c->vq2, c->gemv_scratch));
-        g_misc_launches += 6;
-        HYB_CUDA(cudaMemcpyAsync(sol_x, c->vn1, sizeof(double) * N, cudaMemcpyDeviceToHost, st));
+        g_misc_launches += 4;
     } else if (q > 0) {
         HYB_CUDA(cudaMemsetAsync(c->vq2, 0, sizeof(double) * q, st));
     }
@@ -454,9 +505,12 @@ int hyb_solve_subsystem3(hyb_ctx* c, const double* rhs_x, const double* rhs_z, d
         axpby_kernel<<<(unsigned)((q + 255) / 256), 256, 0, st>>>(q, 1.0, c->vq3, -1.0, c->vq1, c->vq3);
         ++g_misc_launches;
         HYB_CUDA(cudaGetLastError());
-        HYB_CUDA(cudaMemcpyAsync(sol_z, c->vq3, sizeof(double) * q, cudaMemcpyDeviceToHost, st));
     }
+    KEND(c);
+    if (N > 0) HYB_CUDA(d2h(c, sol_x, c->vn1, sizeof(double) * N));
+    if (q > 0) HYB_CUDA(d2h(c, sol_z, c->vq3, sizeof(double) * q));
     HYB_CUDA(cudaStreamSynchronize(st));
+    ksync(c);
     return 0;
 }
 
@@ -547,6 +601,26 @@ int hyb_posdef_solve(hyb_ctx* c, int64_t N, double* A, int64_t lda, double* B, i
     }
     hyb_chol_free(ch);
     return rc;
+}
+
+int hyb_stats(hyb_ctx* c, int reset, double* device_ms, int64_t* h2d_bytes, int64_t* d2h_bytes) {
+    if (!c) return -1;
+    if (device_ms) *device_ms = c->dev_ms;
+    if (h2d_bytes) *h2d_bytes = c->h2d_bytes;
+    if (d2h_bytes) *d2h_bytes = c->d2h_bytes;
+    if (reset) {
+        c->dev_ms = 0.0;
+        c->h2d_bytes = c->d2h_bytes = 0;
+    }
+    return 0;
+}
+
+int hyb_last_schur_timings(hyb_ctx* c, double* t_apply_w_ms, double* t_syrk_ms, double* t_factor_ms) {
+    if (!c) return -1;
+    if (t_apply_w_ms) *t_apply_w_ms = c->last_t[0];
+    if (t_syrk_ms) *t_syrk_ms = c->last_t[1];
+    if (t_factor_ms) *t_factor_ms = c->last_t[2];
+    return 0;
 }
 
 // ----------------------------------------------------------------------------- measurement

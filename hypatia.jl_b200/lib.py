@@ -66,6 +66,8 @@ SIGNATURES = {
         C.c_int,
         [C.c_void_p, C.c_int64, c_double_p, C.c_int64, c_double_p, C.c_int64, C.c_int64, c_int_p],
     ),
+    "hyb_stats": (C.c_int, [C.c_void_p, C.c_int, c_double_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "hyb_last_schur_timings": (C.c_int, [C.c_void_p, c_double_p, c_double_p, c_double_p]),
     "hyb_bench_gemm_tn": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int, C.c_int, c_double_p]),
     "hyb_bench_potrf": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, c_double_p, c_double_p]),
 }
@@ -133,6 +135,17 @@ class Context:
 
     def launch_count(self) -> int:
         return int(self.lib.hyb_launch_count())
+
+    def stats(self, reset: bool = False):
+        """(device_ms, h2d_bytes, d2h_bytes) accumulated since the last reset."""
+        ms, a, b = C.c_double(0), C.c_int64(0), C.c_int64(0)
+        self.check(self.lib.hyb_stats(self.ptr, int(reset), C.byref(ms), C.byref(a), C.byref(b)), "hyb_stats")
+        return ms.value, a.value, b.value
+
+    def last_schur_timings(self):
+        a, b, c_ = C.c_double(0), C.c_double(0), C.c_double(0)
+        self.check(self.lib.hyb_last_schur_timings(self.ptr, C.byref(a), C.byref(b), C.byref(c_)), "hyb_last_schur_timings")
+        return a.value, b.value, c_.value
 
     # ---- measurement ----------------------------------------------------------
     def bench_gemm_tn(self, M, N, K, upper=False, reps=5) -> float:

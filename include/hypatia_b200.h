@@ -118,6 +118,12 @@ int hyb_posdef_solve(hyb_ctx* ctx, int64_t N, double* A, int64_t lda, double* B,
  * library's own stream).  They time the same kernels the entry points above launch:
  * the dsyrk / dgemm replacement (dense.jl:72-79, qrchol.jl:242,253) and the dpotrf /
  * dpotrs replacement (dense.jl:226, qrchol.jl:75). */
+/* Accumulated since the last reset: device milliseconds spent between the uploads and the
+ * downloads of every compute call (CUDA events on the library's stream), and the bytes
+ * the calls moved host->device / device->host.  Feeds solver.time_* (Solvers.jl:107-116). */
+int hyb_stats(hyb_ctx* ctx, int reset, double* device_ms, int64_t* h2d_bytes, int64_t* d2h_bytes);
+/* CUDA-event split of the last hyb_schur_update: W*GQ2 products, G'HG syrk, factorization */
+int hyb_last_schur_timings(hyb_ctx* ctx, double* t_apply_w_ms, double* t_syrk_ms, double* t_factor_ms);
 int hyb_bench_gemm_tn(hyb_ctx* ctx, int64_t M, int64_t N, int64_t K, int upper, int reps, double* ms_per_launch);
 int hyb_bench_potrf(hyb_ctx* ctx, int64_t N, int reps, double* ms_factor, double* ms_solve);
 

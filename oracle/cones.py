@@ -518,20 +518,42 @@ class PosSemidefTri(Cone):
         self.inv_hess_mat = _symm_kron(self.mat)
         self.inv_hess_updated = True
 
+    def _idx(self):
+        """svec <-> smat index maps (arrayutilities.jl:183-251), cached."""
+        if not hasattr(self, "_iu"):
+            side = self.side
+            cols = np.repeat(np.arange(side), np.arange(1, side + 1))
+            rows = np.concatenate([np.arange(j + 1) for j in range(side)])
+            self._iu = (rows, cols)
+            self._scale = np.where(rows == cols, 1.0, 1.0 / RT2)
+        return self._iu, self._scale
+
     def _cols(self, arr, fn):
+        """Apply fn to smat of every column (the reference loops over columns through one
+        scratch matrix, possemideftri.jl:138-144; batched here, same arithmetic per column)."""
         a, one_d = _as2d(arr)
-        prod = np.empty_like(a)
-        for i in range(a.shape[1]):
-            M = cs.svec_to_smat(np.ascontiguousarray(a[:, i]))
-            prod[:, i] = cs.smat_to_svec(fn(M))
-        return prod[:, 0] if one_d else prod
+        (rows, cols), scale = self._idx()
+        m = a.shape[1]
+        M = np.zeros((m, self.side, self.side))
+        vals = a.T * scale[None, :]
+        M[:, rows, cols] = vals
+        M[:, cols, rows] = vals
+        R = fn(M)
+        prod = (R[:, rows, cols] / scale[None, :]).T
+        prod = np.ascontiguousarray(prod) if not one_d else prod[:, 0]
+        return prod
 
     def hess_prod(self, arr):  # :135-147   X^-1 A X^-1 (rdiv + ldiv with chol)
         U = self.fact_U
 
         def fn(M):
-            M = sla.cho_solve((U, False), M.T).T  # M / X
-            return sla.cho_solve((U, False), M)  # X \ M
+            m, s_, _ = M.shape
+            # M / X then X \ M with the Cholesky factor, for all columns at once
+            T = sla.cho_solve((U, False), M.transpose(1, 0, 2).reshape(s_, m * s_))  # X^-1 M_k
+            T = T.reshape(s_, m, s_).transpose(1, 0, 2)  # (m, s, s) = X^-1 M_k
+            T = T.transpose(0, 2, 1)  # (X^-1 M_k)' = M_k X^-1
+            T2 = sla.cho_solve((U, False), T.transpose(1, 0, 2).reshape(s_, m * s_))
+            return T2.reshape(s_, m, s_).transpose(1, 0, 2)
 
         return self._cols(arr, fn)
 
@@ -543,8 +565,11 @@ class PosSemidefTri(Cone):
         U = self.fact_U
 
         def fn(M):
-            M = sla.solve_triangular(U, M.T, trans="T", lower=False).T  # M / U
-            return sla.solve_triangular(U, M, trans="T", lower=False)  # U' \ M
+            m, s_, _ = M.shape
+            T = sla.solve_triangular(U, M.transpose(1, 0, 2).reshape(s_, m * s_), trans="T", lower=False)  # U^-T M_k
+            T = T.reshape(s_, m, s_).transpose(1, 0, 2).transpose(0, 2, 1)  # M_k U^-1
+            T2 = sla.solve_triangular(U, T.transpose(1, 0, 2).reshape(s_, m * s_), trans="T", lower=False)
+            return T2.reshape(s_, m, s_).transpose(1, 0, 2)
 
         return self._cols(arr, fn)
 

@@ -153,6 +153,7 @@ def test_many_small_cones_batch():
         c.load_point(primal, 0.9)
         c.load_dual_point(dual)
         c.reset_data()
+    assert cpu.is_feas() and gpu.is_feas()
     assert rel_err(gpu.grad(), cpu.grad()) < TOL
     arr = np.asfortranarray(rng.standard_normal((cpu.q, 3)))
     assert rel_err(gpu.hess_prod(arr), cpu.hess_prod(arr)) < 1e3 * TOL

@@ -60,7 +60,7 @@ def traj_deviation(tg, tc, keys=("x_norm_res", "z_norm_res", "mu", "gap", "tau",
     worst, first_bad = 0.0, None
     for i, (a, b) in enumerate(zip(tg, tc)):
         for k in keys:
-            den = max(abs(b[k]), 1e-12)
+            den = max(abs(b[k]), 1e-9)  # residuals below 1e-9 are rounding noise (tol_feas is 1.5e-8)
             d = abs(a[k] - b[k]) / den
             worst = max(worst, d)
             if d > 1e-8 and first_bad is None:
