@@ -121,3 +121,70 @@ int hyb_gemv_t(cudaStream_t st, int64_t q, int64_t N, const double* G, int64_t l
     HYB_CUDA(cudaGetLastError());
     return 0;
 }
+
+
+// ---------------------------------------------------------------------------------------
+// y = G x without any allocation: the split-sum scratch of the gemv above lives in a
+// fixed, library-owned device array instead of a buffer from cudaMalloc.
+//
+// Who needs this: a host whose device memory is entirely managed by another allocator
+// (for instance a Julia session in which CUDA.jl's memory pool, or a PyTorch process whose
+// caching allocator, has already claimed the GPU, so that a foreign cudaMalloc may fail or
+// fragment the pool), and callers inside a latency-critical section, where cudaMalloc and
+// cudaFree are unwelcome because they synchronise the device.  Such a caller owns G, x and y
+// (device pointers, on the current device) and gets the product with no allocation made by
+// this library, by torch, or by any routine this function calls.
+//
+// The scratch is HYB_GEMV_SPLITS * HYB_NOALLOC_MAX_Q doubles (4 MiB).  Every GPU that loads
+// the library holds that array until the process exits.  All calls on a device share it, so
+// two calls that overlap on the GPU (different streams, or different host threads) race on
+// it: serialise them.  It keeps whatever the previous call left behind; that is harmless
+// here because each call writes every scratch entry it later reads (all HYB_GEMV_SPLITS
+// partial sums of rows 0..q-1), so nothing has to start at zero and nothing is cleared.
+//
+// Set-up: the array's name is only a host-side handle; the device address is looked up with
+// cudaGetSymbolAddress once per device, by the first call made while that device is current.
+// Make that first call outside any stream capture.
+// ---------------------------------------------------------------------------------------
+#define HYB_NOALLOC_MAX_Q 65536
+#define HYB_NOALLOC_MAX_DEVICES 64
+
+static __device__ __align__(256) double g_noalloc_scratch[(size_t)HYB_GEMV_SPLITS * HYB_NOALLOC_MAX_Q];
+static double* g_noalloc_ptr[HYB_NOALLOC_MAX_DEVICES] = {nullptr};
+
+extern "C" int hyb_gemv_n_noalloc(const double* G_dev, int64_t q, int64_t N, int64_t ld, const double* x_dev,
+                                  double* y_dev, void* stream) {
+    if (q > HYB_NOALLOC_MAX_Q) {
+        hyb_set_error("hyb_gemv_n_noalloc: q = %lld exceeds the fixed scratch capacity of %d rows; use hyb_G_mul instead",
+                      (long long)q, HYB_NOALLOC_MAX_Q);
+        return -4;
+    }
+    if (q < 0 || N < 0 || ld < q || (q > 0 && N > 0 && (!G_dev || !x_dev)) || (q > 0 && !y_dev)) {
+        hyb_set_error("hyb_gemv_n_noalloc: bad arguments (q=%lld N=%lld ld=%lld)", (long long)q, (long long)N, (long long)ld);
+        return -3;
+    }
+    if (q == 0) return 0;
+    int dev = -1;
+    HYB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= HYB_NOALLOC_MAX_DEVICES) {
+        hyb_set_error("hyb_gemv_n_noalloc: device index %d out of range", dev);
+        return -3;
+    }
+    if (!g_noalloc_ptr[dev]) {
+        double* ptr = nullptr;
+        HYB_CUDA(cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch));
+        g_noalloc_ptr[dev] = ptr;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    if (N == 0) {
+        HYB_CUDA(cudaMemsetAsync(y_dev, 0, sizeof(double) * q, st));
+        return 0;
+    }
+    double* scratch = g_noalloc_ptr[dev];
+    dim3 grid((unsigned)((q + 255) / 256), HYB_GEMV_SPLITS);
+    gemv_n_partial_kernel<<<grid, 128, 0, st>>>(q, N, G_dev, ld, x_dev, scratch);
+    HYB_CUDA(cudaGetLastError());
+    gemv_n_reduce_kernel<<<(unsigned)((q + 255) / 256), 256, 0, st>>>(q, HYB_GEMV_SPLITS, scratch, y_dev);
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}

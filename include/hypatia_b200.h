@@ -114,6 +114,18 @@ int hyb_gemm_tn_host(hyb_ctx* ctx, int64_t M, int64_t N, int64_t K, double alpha
  * *info = LAPACK dpotrf info (0 success, j = leading minor j not positive definite). */
 int hyb_posdef_solve(hyb_ctx* ctx, int64_t N, double* A, int64_t lda, double* B, int64_t ldb, int64_t nrhs, int* info);
 
+/* ---- allocation-free product (no counterpart in the reference) -----------------------
+ * y = G x on DEVICE pointers owned by the caller (column-major G, q x N, leading dimension
+ * ld >= q; all on the current device), launched on `stream` (a cudaStream_t, NULL for the
+ * default stream) and not synchronised.  For hosts that must not see a cudaMalloc from this
+ * library: another runtime's pool owns the GPU memory, or the call sits in a latency-critical
+ * section.  Its split-sum scratch is a fixed 4 MiB device array inside the library, so
+ * q is limited to 65536 rows (larger q returns -4), every GPU that loads the library keeps
+ * that array until exit, and calls that overlap on one GPU race on it.  The first call on a
+ * device also looks up the array's address; make that call before any stream capture. */
+int hyb_gemv_n_noalloc(const double* G_dev, int64_t q, int64_t N, int64_t ld, const double* x_dev, double* y_dev,
+                       void* stream);
+
 /* ---- measurement helpers (device-resident synthetic operands, CUDA-event timing on the
  * library's own stream).  They time the same kernels the entry points above launch:
  * the dsyrk / dgemm replacement (dense.jl:72-79, qrchol.jl:242,253) and the dpotrf /
