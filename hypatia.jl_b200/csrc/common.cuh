@@ -37,7 +37,7 @@ static inline int64_t hyb_round_up(int64_t x, int64_t m) { return (x + m - 1) / 
 // even leading dimensions and 16-byte aligned bases (TMA requirement).
 // flags: HYB_GEMM_UPPER -> only tiles/entries with col >= row are computed/stored
 // (requires the A and B tile grids to coincide, i.e. SYRK-like use).
-enum { HYB_GEMM_UPPER = 1 };
+enum { HYB_GEMM_UPPER = 1, HYB_GEMM_CVEC = 2 /* internal: C is 16-byte aligned with even ldc */ };
 int hyb_gemm_tn(cudaStream_t st, int64_t M, int64_t N, int64_t K, double alpha, const double* A, int64_t lda,
                 const double* B, int64_t ldb, double beta, double* C, int64_t ldc, int flags);
 int64_t hyb_gemm_launch_count();
@@ -51,6 +51,8 @@ struct HybChol {
     int* info = nullptr;      // device: index (1-based) of first non-positive pivot, 0 = success
     int epoch = 0;
     double* work = nullptr;   // N doubles
+    cudaStream_t panel_stream = nullptr;  // look-ahead panels (high priority)
+    cudaEvent_t ev_head = nullptr, ev_panel = nullptr;
 };
 int hyb_chol_alloc(HybChol& ch, int64_t N);
 void hyb_chol_free(HybChol& ch);

@@ -20,7 +20,7 @@ constexpr int BM = 128, BN = 128, BK = 16, STAGES = 4;
 constexpr int TILE_DOUBLES = BM * BK;           // 2048
 constexpr int TILE_BYTES = TILE_DOUBLES * 8;    // 16 KB
 constexpr int NUM_CONSUMER_WARPS = 8;
-constexpr int THREADS = (NUM_CONSUMER_WARPS + 1) * 32;
+constexpr int THREADS = (NUM_CONSUMER_WARPS + 4) * 32;  // 2 consumer warpgroups + 1 producer warpgroup
 constexpr int SMEM_BYTES = STAGES * 2 * TILE_BYTES + 1024 /*align slack*/ + 128 /*barriers*/;
 
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
@@ -29,6 +29,9 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
                  : "d"(a), "d"(b));
 }
 
+// 12 warps = 3 per SM sub-partition (16K registers each) => 168 registers per thread at launch;
+// the producer warpgroup then gives registers back (setmaxnreg.dec) and the two consumer
+// warpgroups take them (setmaxnreg.inc 232), the Hopper/Blackwell warp-specialisation idiom.
 __global__ void __launch_bounds__(THREADS, 1)
 gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
                double alpha, double beta, double* __restrict__ C, int64_t ldc, int flags, int tiles_m) {
@@ -63,9 +66,10 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     __syncthreads();
 
-    if (warp == NUM_CONSUMER_WARPS) {
-        // ---------------- TMA producer ----------------
-        if (lane == 0) {
+    if (warp >= NUM_CONSUMER_WARPS) {
+        // ---------------- TMA producer warpgroup (one elected thread works) ----------------
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        if (warp == NUM_CONSUMER_WARPS && lane == 0) {
             for (int kt = 0; kt < nk; ++kt) {
                 const int s = kt % STAGES;
                 if (kt >= STAGES) mbar_wait(&empty[s], ((kt / STAGES) - 1) & 1);
@@ -78,6 +82,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
 
     // ---------------- DMMA consumers ----------------
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
     const int wm = warp >> 2, wn = warp & 3;
     const int g = lane >> 2, t = lane & 3;
     double acc[8][4][2];
@@ -113,21 +118,67 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
 
     // ---------------- epilogue ----------------
+    // The accumulators are parked in the (now idle) stage buffers as a 128 x 128 column-major
+    // tile, then the 256 consumer threads update C with coalesced 16-byte accesses:
+    // C = alpha * acc + beta * C.  Loads of a batch are all issued before its stores (a
+    // load -> store -> load chain on possibly aliasing pointers serialises the round trips).
     const bool upper = flags & HYB_GEMM_UPPER;
+    const bool use_c = (beta != 0.0);
+    double* Cs = sA;  // 128 KB = STAGES * (A + B) buffers
+    const int ctid = threadIdx.x;  // 0..255 (consumer threads only)
+    asm volatile("bar.sync 1, 256;" ::: "memory");  // every warp is done reading the last stages
 #pragma unroll
     for (int mt = 0; mt < 8; ++mt) {
-        const int row = m0 + wm * 64 + mt * 8 + g;
-        if (row >= M) continue;
+        const int row = wm * 64 + mt * 8 + g;
 #pragma unroll
-        for (int nt = 0; nt < 4; ++nt) {
+        for (int nt = 0; nt < 4; ++nt)
 #pragma unroll
             for (int i = 0; i < 2; ++i) {
-                const int col = n0 + wn * 32 + nt * 8 + 2 * t + i;
-                if (col >= N || (upper && col < row)) continue;
-                double* p = C + row + (int64_t)col * ldc;
-                double v = alpha * acc[mt][nt][i];
-                if (beta != 0.0) v += beta * (*p);
-                *p = v;
+                const int col = wn * 32 + nt * 8 + 2 * t + i;
+                Cs[col * BM + (row ^ (((col >> 1) & 3) << 3))] = acc[mt][nt][i];
+            }
+    }
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    const bool vec_ok = (flags & HYB_GEMM_CVEC) != 0;
+#pragma unroll 1
+    for (int round = 0; round < 4; ++round) {
+        double2 cv[8];
+        // item = (column, row pair); consecutive threads take consecutive row pairs of a column
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int idx = (round * 8 + j) * 256 + ctid;
+            const int col = idx >> 6, row = (idx & 63) * 2;
+            const int grow = m0 + row, gcol = n0 + col;
+            cv[j] = make_double2(0.0, 0.0);
+            if (use_c && gcol < N) {
+                const double* p = C + grow + (int64_t)gcol * ldc;
+                const bool ok0 = grow < M && !(upper && gcol < grow);
+                const bool ok1 = grow + 1 < M && !(upper && gcol < grow + 1);
+                if (ok0 && ok1 && vec_ok) {
+                    cv[j] = __ldcg((const double2*)p);
+                } else {
+                    if (ok0) cv[j].x = __ldcg(p);
+                    if (ok1) cv[j].y = __ldcg(p + 1);
+                }
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int idx = (round * 8 + j) * 256 + ctid;
+            const int col = idx >> 6, row = (idx & 63) * 2;
+            const int grow = m0 + row, gcol = n0 + col;
+            if (gcol < N) {
+                const double2 sv = *(const double2*)(Cs + col * BM + (row ^ (((col >> 1) & 3) << 3)));
+                double* p = C + grow + (int64_t)gcol * ldc;
+                const bool ok0 = grow < M && !(upper && gcol < grow);
+                const bool ok1 = grow + 1 < M && !(upper && gcol < grow + 1);
+                const double v0 = alpha * sv.x + beta * cv[j].x, v1 = alpha * sv.y + beta * cv[j].y;
+                if (ok0 && ok1 && vec_ok) {
+                    *(double2*)p = make_double2(v0, v1);
+                } else {
+                    if (ok0) p[0] = v0;
+                    if (ok1) p[1] = v1;
+                }
             }
         }
     }
@@ -169,6 +220,7 @@ int hyb_gemm_tn(cudaStream_t st, int64_t M, int64_t N, int64_t K, double alpha, 
     } else {
         ntiles = (int64_t)tiles_m * tiles_n;
     }
+    if (((uintptr_t)C & 15) == 0 && (ldc & 1) == 0) flags |= HYB_GEMM_CVEC;
     gemm_tn_kernel<<<(unsigned)ntiles, THREADS, SMEM_BYTES, st>>>(tmA, tmB, (int)M, (int)N, (int)K, alpha, beta, C, ldc,
                                                                  flags, tiles_m);
     ++g_gemm_launches;

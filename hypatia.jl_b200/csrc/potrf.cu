@@ -35,144 +35,213 @@ constexpr int IB = 16;       // inner block of the panel factorization
 // LAPACK dpotf2/dpotrf (no explicit inverses), so backward stable.
 // The strictly lower triangle of the block in global memory is zeroed on exit.
 // --------------------------------------------------------------------------------
+__device__ __noinline__ void potf2_diag_block(double* S, double* rdiag, int jb, int lane, int* fail, int* info,
+                                                 int k0) {
+    double col[IB];
+    const int c = lane & (IB - 1);
+#pragma unroll
+    for (int i = 0; i < IB; ++i) col[i] = S[(jb + i) * LDS + jb + c];
+    bool bad = false;
+    int badj = 0;
+#pragma unroll
+    for (int j = 0; j < IB; ++j) {
+        const double d = __shfl_sync(0xffffffffu, col[j], j);
+        if (!(d > 0.0) && !bad) {  // also catches NaN
+            bad = true;
+            badj = j;
+        }
+        const double r = sqrt(d);
+        const double rinv = 1.0 / r;
+        const double ujc = (c == j) ? r : col[j] * rinv;
+        if (c >= j) col[j] = ujc;
+        if (lane == j) rdiag[j] = rinv;
+#pragma unroll
+        for (int i = j + 1; i < IB; ++i) {
+            const double uji = __shfl_sync(0xffffffffu, col[j], i);
+            if (c >= i) col[i] -= uji * ujc;
+        }
+    }
+    if (bad) {
+        if (lane == 0) {
+            *fail = 1;
+            *info = k0 + jb + badj + 1;
+        }
+    } else if (lane < IB) {
+#pragma unroll
+        for (int i = 0; i < IB; ++i)
+            if (i <= c) S[(jb + i) * LDS + jb + c] = col[i];
+    }
+}
+
+__device__ __noinline__ void potf2_row_panel(double* S, const double* rdiag, int jb, int c) {
+    double y[IB];
+#pragma unroll
+    for (int i = 0; i < IB; ++i) y[i] = S[(jb + i) * LDS + c];
+#pragma unroll
+    for (int k = 0; k < IB; ++k) {
+        y[k] *= rdiag[k];
+#pragma unroll
+        for (int i = k + 1; i < IB; ++i) y[i] -= S[(jb + k) * LDS + jb + i] * y[k];
+    }
+#pragma unroll
+    for (int i = 0; i < IB; ++i) S[(jb + i) * LDS + c] = y[i];
+}
+
 __global__ void __launch_bounds__(512, 1)
 potf2_kernel(double* __restrict__ A, int64_t lda, int nb, int* __restrict__ info, int k0) {
     extern __shared__ double sm[];
-    double* S = sm;  // S[r * LDS + c]
+    double* S = sm;               // S[r * LDS + c]
+    double* rdiag = sm + NB * LDS;  // reciprocals of the current diagonal block's pivots
     __shared__ int fail;
     const int tid = threadIdx.x, nth = blockDim.x, lane = tid & 31, warp = tid >> 5;
     if (*info != 0) return;  // an earlier panel failed: nothing meaningful to do
     if (tid == 0) fail = 0;
     for (int e = tid; e < NB * NB; e += nth) {
-        const int r = e % NB, c = e / NB;
-        S[r * LDS + c] = (r < nb && c < nb && r <= c) ? A[r + (int64_t)c * lda] : 0.0;
+        const int r = e & (NB - 1), c = e >> 7;
+        S[r * LDS + c] = (r < nb && c < nb && r <= c) ? A[r + (int64_t)c * lda] : ((r == c) ? 1.0 : 0.0);
     }
     __syncthreads();
 
-    for (int jb = 0; jb < nb; jb += IB) {
-        const int w = min(IB, nb - jb);
-        // (1) diagonal block, one warp, unblocked right-looking
-        if (warp == 0) {
-            for (int j = jb; j < jb + w; ++j) {
-                const double d = S[j * LDS + j];
-                if (!(d > 0.0)) {  // also catches NaN
-                    if (lane == 0) {
-                        fail = 1;
-                        *info = k0 + j + 1;
-                    }
-                    break;
-                }
-                const double r = sqrt(d);
-                const double rinv = 1.0 / r;
-                __syncwarp();
-                if (lane < jb + w - j) {
-                    const int c = j + lane;
-                    S[j * LDS + c] = (lane == 0) ? r : S[j * LDS + c] * rinv;
-                }
-                __syncwarp();
-                const int m = jb + w - j - 1;
-                for (int e = lane; e < m * m; e += 32) {
-                    const int i = j + 1 + e / m, c = j + 1 + e % m;
-                    if (c >= i) S[i * LDS + c] -= S[j * LDS + i] * S[j * LDS + c];
-                }
-                __syncwarp();
-            }
-        }
+    // identity padding makes every IB x IB step full-size: no tail cases below
+    const int nbp = (nb + IB - 1) / IB * IB;
+    for (int jb = 0; jb < nbp; jb += IB) {
+        // (1) IB x IB diagonal block: lane c owns column c in registers, right-looking
+        if (warp == 0) potf2_diag_block(S, rdiag, jb, lane, &fail, info, k0);
         __syncthreads();
         if (fail) return;
-        const int t0 = jb + w;      // first trailing column
-        const int m = nb - t0;      // trailing size
+        const int t0 = jb + IB;   // first trailing column
+        const int m = nbp - t0;   // trailing size
         if (m <= 0) break;
-        // (2) row panel: U[jb:jb+w, c] = U11^-T A[jb:jb+w, c], thread per trailing column
-        for (int cc = tid; cc < m; cc += nth) {
-            const int c = t0 + cc;
-            double y[IB];
-#pragma unroll
-            for (int i = 0; i < IB; ++i) y[i] = (i < w) ? S[(jb + i) * LDS + c] : 0.0;
-#pragma unroll
-            for (int k = 0; k < IB; ++k) {
-                if (k < w) {
-                    y[k] = y[k] / S[(jb + k) * LDS + jb + k];
-#pragma unroll
-                    for (int i = k + 1; i < IB; ++i)
-                        if (i < w) y[i] -= S[(jb + k) * LDS + jb + i] * y[k];
-                }
-            }
-#pragma unroll
-            for (int i = 0; i < IB; ++i)
-                if (i < w) S[(jb + i) * LDS + c] = y[i];
-        }
+        // (2) row panel: U[jb:jb+IB, c] = U11^-T A[jb:jb+IB, c], thread per trailing column
+        if (tid < m) potf2_row_panel(S, rdiag, jb, t0 + tid);
         __syncthreads();
-        // (3) trailing update: S[i][c] -= sum_k U[jb+k][i] U[jb+k][c], t0 <= i <= c
-        for (int e = tid; e < m * m; e += nth) {
-            const int i = t0 + e / m, c = t0 + e % m;
-            if (c >= i) {
-                double s = 0.0;
+        // (3) trailing update: S[i][c] -= sum_k U[jb+k][i] U[jb+k][c], t0 <= i <= c.
+        //     threads tile the trailing square: tx over columns (fast), ty over rows.
+        {
+            const int tx = tid & 31, ty = tid >> 5;  // 32 x 16
+            for (int i = t0 + ty; i < nbp; i += 16) {
+                for (int c = t0 + tx; c < nbp; c += 32) {
+                    if (c >= i) {
+                        double s = 0.0;
 #pragma unroll
-                for (int k = 0; k < IB; ++k)
-                    if (k < w) s += S[(jb + k) * LDS + i] * S[(jb + k) * LDS + c];
-                S[i * LDS + c] -= s;
+                        for (int k = 0; k < IB; ++k) s += S[(jb + k) * LDS + i] * S[(jb + k) * LDS + c];
+                        S[i * LDS + c] -= s;
+                    }
+                }
             }
         }
         __syncthreads();
     }
     // write back: U in the upper triangle, zeros strictly below (the block is workspace)
-    for (int e = tid; e < nb * nb; e += nth) {
-        const int r = e % nb, c = e / nb;
-        A[r + (int64_t)c * lda] = (r <= c) ? S[r * LDS + c] : 0.0;
+    for (int e = tid; e < NB * NB; e += nth) {
+        const int r = e & (NB - 1), c = e >> 7;
+        if (r < nb && c < nb) A[r + (int64_t)c * lda] = (r <= c) ? S[r * LDS + c] : 0.0;
     }
 }
 
 // --------------------------------------------------------------------------------
 // row panel of the blocked factorization: A12 <- U11^-T A12 (U11 128 x 128 upper),
-// forward substitution, one thread per column of A12, 32-row register chunks,
-// U11 broadcast from shared memory.  Backward stable (LAPACK dtrsm semantics).
+// forward substitution, one thread per column of A12 in 32-row register chunks.
+// U11 is read straight from global memory with warp-uniform (broadcast) loads that
+// stay in L1; solved chunks of y are parked in shared memory for the later chunks.
+// Backward stable (LAPACK dtrsm semantics), no explicit inverse.
 // --------------------------------------------------------------------------------
-constexpr int TRSM_THREADS = 64;
-__global__ void __launch_bounds__(TRSM_THREADS)
+constexpr int TRSM_THREADS = 128;
+constexpr int TRSM_COLS = 64;          // columns of A12 per CTA
+constexpr int TLD = TRSM_COLS + 1;     // padded slab leading dimension
+
+// substitution of one 32-row chunk, one thread per column, chunk in registers
+// (template instances called in sequence: a register array declared inside a runtime
+//  chunk loop gets demoted to local memory by nvcc)
+template <int CB>
+__device__ __forceinline__ void trsm_solve_chunk(const double* Uc, const double* dinv, double* T, int c) {
+    double v[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = T[(CB * 32 + i) * TLD + c];
+#pragma unroll
+    for (int k = 0; k < 32; ++k) {
+        v[k] *= dinv[CB * 32 + k];
+#pragma unroll
+        for (int i = k + 1; i < 32; ++i) v[i] -= Uc[(CB * 32 + i) * LDS + CB * 32 + k] * v[k];
+    }
+#pragma unroll
+    for (int i = 0; i < 32; ++i) T[(CB * 32 + i) * TLD + c] = v[i];
+}
+
+// rows R0..R0+31 of the slab -= U[0:K, R0:R0+32]' * Y[0:K, :]  (K = CB*32), 4x4 register tiles
+template <int CB>
+__device__ __forceinline__ void trsm_update_chunk(const double* Uc, double* T, int tid) {
+    if (CB == 0) return;
+    const int tr = tid >> 4, tc = tid & 15;  // 8 row groups x 16 column groups
+    const int r0 = CB * 32 + 4 * tr, c0 = 4 * tc;
+    double acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.0;
+#pragma unroll 4
+    for (int k = 0; k < CB * 32; ++k) {
+        double u[4], y[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) u[i] = Uc[(r0 + i) * LDS + k];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) y[j] = T[k * TLD + c0 + j];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[i][j] += u[i] * y[j];
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) T[(r0 + i) * TLD + c0 + j] -= acc[i][j];
+}
+
+// --------------------------------------------------------------------------------
+// row panel of the blocked factorization: A12 <- U11^-T A12 (U11 128 x 128 upper).
+// A CTA stages U11 and a 128 x 64 slab of A12 in shared memory and alternates, per
+// 32-row chunk, a register-tiled update with the rows already solved and a forward
+// substitution with the 32 x 32 diagonal block (one thread per column, chunk in
+// registers).  Substitution only - no explicit inverse (LAPACK dtrsm semantics).
+// --------------------------------------------------------------------------------
+__global__ void __launch_bounds__(TRSM_THREADS, 1)
 trsm_upper_T_kernel(const double* __restrict__ U11, int64_t ldu, double* __restrict__ A12, int64_t ld, int64_t n2) {
     extern __shared__ double sm[];
-    double* Us = sm;              // Us[k * NB + i] = U[k][i]
-    double* dinv = sm + NB * NB;  // 1 / U[k][k]
-    for (int e = threadIdx.x; e < NB * NB; e += TRSM_THREADS) {
-        const int r = e % NB, c = e / NB;
-        Us[r * NB + c] = (r <= c) ? U11[r + (int64_t)c * ldu] : 0.0;
+    double* Uc = sm;                     // Uc[i * LDS + k] = U[k][i]  (column i of U11, contiguous in k)
+    double* T = sm + NB * LDS;           // T[r * TLD + c]
+    double* dinv = T + NB * TLD;         // 1 / U[k][k]
+    const int tid = threadIdx.x;
+    const int64_t col0 = (int64_t)blockIdx.x * TRSM_COLS;
+    const int ncol = (int)((n2 - col0 < TRSM_COLS) ? (n2 - col0) : TRSM_COLS);
+    for (int e = tid; e < NB * NB; e += TRSM_THREADS) {
+        const int k = e & (NB - 1), i = e >> 7;
+        Uc[i * LDS + k] = __ldg(U11 + k + (int64_t)i * ldu);
+    }
+    for (int e = tid; e < NB * TRSM_COLS; e += TRSM_THREADS) {
+        const int r = e & (NB - 1), c = e >> 7;
+        T[r * TLD + c] = (c < ncol) ? A12[r + (col0 + c) * ld] : 0.0;
     }
     __syncthreads();
-    for (int k = threadIdx.x; k < NB; k += TRSM_THREADS) dinv[k] = 1.0 / Us[k * NB + k];
+    if (tid < NB) dinv[tid] = 1.0 / Uc[tid * LDS + tid];
     __syncthreads();
-    const int64_t col = (int64_t)blockIdx.x * TRSM_THREADS + threadIdx.x;
-    if (col >= n2) return;
-    double* a = A12 + col * ld;
-    for (int cb = 0; cb < NB / 32; ++cb) {
-        double v[32];
-#pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-            const double2 t = *(const double2*)(a + cb * 32 + i);
-            v[i] = t.x;
-            v[i + 1] = t.y;
-        }
-        // contributions of the rows already solved (re-read from this thread's own column)
-        for (int k = 0; k < cb * 32; ++k) {
-            const double yk = a[k];
-            const double* urow = Us + k * NB + cb * 32;
-#pragma unroll
-            for (int i = 0; i < 32; i += 2) {
-                const double2 u = *(const double2*)(urow + i);
-                v[i] -= u.x * yk;
-                v[i + 1] -= u.y * yk;
-            }
-        }
-        // 32 x 32 triangle, column-oriented forward substitution in registers
-#pragma unroll
-        for (int k = 0; k < 32; ++k) {
-            v[k] *= dinv[cb * 32 + k];
-            const double* urow = Us + (cb * 32 + k) * NB + cb * 32;
-#pragma unroll
-            for (int i = k + 1; i < 32; ++i) v[i] -= urow[i] * v[k];
-        }
-#pragma unroll
-        for (int i = 0; i < 32; i += 2) *(double2*)(a + cb * 32 + i) = make_double2(v[i], v[i + 1]);
+    const bool solver_thread = tid < TRSM_COLS;
+    if (solver_thread) trsm_solve_chunk<0>(Uc, dinv, T, tid);
+    __syncthreads();
+    trsm_update_chunk<1>(Uc, T, tid);
+    __syncthreads();
+    if (solver_thread) trsm_solve_chunk<1>(Uc, dinv, T, tid);
+    __syncthreads();
+    trsm_update_chunk<2>(Uc, T, tid);
+    __syncthreads();
+    if (solver_thread) trsm_solve_chunk<2>(Uc, dinv, T, tid);
+    __syncthreads();
+    trsm_update_chunk<3>(Uc, T, tid);
+    __syncthreads();
+    if (solver_thread) trsm_solve_chunk<3>(Uc, dinv, T, tid);
+    __syncthreads();
+    for (int e = tid; e < NB * TRSM_COLS; e += TRSM_THREADS) {
+        const int r = e & (NB - 1), c = e >> 7;
+        if (c < ncol) A12[r + (col0 + c) * ld] = T[r * TLD + c];
     }
 }
 
@@ -386,6 +455,11 @@ int hyb_chol_alloc(HybChol& ch, int64_t N) {
     HYB_CUDA(cudaMalloc(&ch.flags, sizeof(int) * (ch.nblk > 0 ? ch.nblk : 1)));
     HYB_CUDA(cudaMemset(ch.flags, 0, sizeof(int) * (ch.nblk > 0 ? ch.nblk : 1)));
     HYB_CUDA(cudaMalloc(&ch.info, sizeof(int)));
+    int lo = 0, hi = 0;
+    HYB_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    HYB_CUDA(cudaStreamCreateWithPriority(&ch.panel_stream, cudaStreamNonBlocking, hi));
+    HYB_CUDA(cudaEventCreateWithFlags(&ch.ev_head, cudaEventDisableTiming));
+    HYB_CUDA(cudaEventCreateWithFlags(&ch.ev_panel, cudaEventDisableTiming));
     HYB_CUDA(cudaMalloc(&ch.work, sizeof(double) * (N > 0 ? N : 1)));
     ch.epoch = 0;
     return 0;
@@ -395,15 +469,21 @@ void hyb_chol_free(HybChol& ch) {
     cudaFree(ch.F);
     cudaFree(ch.flags);
     cudaFree(ch.info);
+    if (ch.panel_stream) cudaStreamDestroy(ch.panel_stream);
+    if (ch.ev_head) cudaEventDestroy(ch.ev_head);
+    if (ch.ev_panel) cudaEventDestroy(ch.ev_panel);
     cudaFree(ch.work);
     ch = HybChol();
 }
 
-constexpr int PANEL_SMEM = NB * LDS * (int)sizeof(double);
-constexpr int TRSM_SMEM = (NB * NB + NB) * (int)sizeof(double);
+constexpr int PANEL_SMEM = (NB * LDS + IB) * (int)sizeof(double);
+constexpr int TRSM_SMEM = (NB * LDS + NB * TLD + NB) * (int)sizeof(double);
 constexpr int TRSV_SMEM = (NB * LDS + 4 * NB) * (int)sizeof(double);
 int64_t g_potrf_launches = 0;
 
+// Right-looking factorization with one panel of look-ahead: while the bulk of step k's
+// trailing update runs on the main stream, the (latency-bound) panel k+1 = potf2 + trsm runs
+// on a second, high-priority stream as soon as block row k+1 has received step k's update.
 int hyb_potrf(cudaStream_t st, HybChol& ch, int* info_out) {
     const int64_t N = ch.N, ld = ch.ld;
     static bool attr_set = false;
@@ -412,25 +492,43 @@ int hyb_potrf(cudaStream_t st, HybChol& ch, int* info_out) {
         HYB_CUDA(cudaFuncSetAttribute(trsm_upper_T_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TRSM_SMEM));
         attr_set = true;
     }
+    cudaStream_t sp = ch.panel_stream;
     HYB_CUDA(cudaMemsetAsync(ch.info, 0, sizeof(int), st));
-    for (int64_t k0 = 0; k0 < N; k0 += NB) {
+    auto panel = [&](cudaStream_t s, int64_t k0) -> int {
         const int nb = (int)((N - k0 < NB) ? (N - k0) : NB);
         double* A11 = ch.F + k0 + k0 * ld;
-        potf2_kernel<<<1, 512, PANEL_SMEM, st>>>(A11, ld, nb, ch.info, (int)k0);
+        potf2_kernel<<<1, 512, PANEL_SMEM, s>>>(A11, ld, nb, ch.info, (int)k0);
         ++g_potrf_launches;
         HYB_CUDA(cudaGetLastError());
         const int64_t n2 = N - k0 - nb;
         if (n2 > 0) {
             double* A12 = ch.F + k0 + (k0 + nb) * ld;
-            double* A22 = ch.F + (k0 + nb) + (k0 + nb) * ld;
-            // U12 = U11^-T A12 by substitution
-            trsm_upper_T_kernel<<<(unsigned)((n2 + TRSM_THREADS - 1) / TRSM_THREADS), TRSM_THREADS, TRSM_SMEM, st>>>(
+            trsm_upper_T_kernel<<<(unsigned)((n2 + TRSM_COLS - 1) / TRSM_COLS), TRSM_THREADS, TRSM_SMEM, s>>>(
                 A11, ld, A12, ld, n2);
             ++g_potrf_launches;
             HYB_CUDA(cudaGetLastError());
-            // A22 -= U12' U12  (upper, FP64 DMMA)
-            HYB_CHECK(hyb_gemm_tn(st, n2, n2, nb, -1.0, A12, ld, A12, ld, 1.0, A22, ld, HYB_GEMM_UPPER));
         }
+        return 0;
+    };
+    HYB_CHECK(panel(st, 0));
+    for (int64_t k0 = 0; k0 + NB < N; k0 += NB) {
+        const int64_t k1 = k0 + NB;
+        const int64_t n2 = N - k1;                       // trailing size
+        const int64_t nb2 = n2 < NB ? n2 : NB;           // height of the next block row
+        const double* U12 = ch.F + k0 + k1 * ld;         // NB x n2 (block row k)
+        double* A22 = ch.F + k1 + k1 * ld;
+        // head: block row k+1 of the trailing matrix  -= U12[:, 0:nb2]' U12
+        HYB_CHECK(hyb_gemm_tn(st, nb2, n2, NB, -1.0, U12, ld, U12, ld, 1.0, A22, ld, 0));
+        HYB_CUDA(cudaEventRecord(ch.ev_head, st));
+        HYB_CUDA(cudaStreamWaitEvent(sp, ch.ev_head, 0));
+        HYB_CHECK(panel(sp, k1));
+        HYB_CUDA(cudaEventRecord(ch.ev_panel, sp));
+        // rest: block rows >= k+2, upper triangle only
+        const int64_t n3 = n2 - nb2;
+        if (n3 > 0)
+            HYB_CHECK(hyb_gemm_tn(st, n3, n3, NB, -1.0, U12 + nb2 * ld, ld, U12 + nb2 * ld, ld, 1.0,
+                                  A22 + nb2 + nb2 * ld, ld, HYB_GEMM_UPPER));
+        HYB_CUDA(cudaStreamWaitEvent(st, ch.ev_panel, 0));
     }
     if (info_out) {
         HYB_CUDA(cudaMemcpyAsync(info_out, ch.info, sizeof(int), cudaMemcpyDeviceToHost, st));

@@ -57,13 +57,14 @@ def test_schur_matrix_and_subsystem_match_cpu():
 
 def traj_deviation(tg, tc, keys=("x_norm_res", "z_norm_res", "mu", "gap", "tau", "kap")):
     """First iteration whose residual / mu trajectory deviates by more than 1e-8 relative
-    (north_star tolerance).  Residual norms are compared relative to max(|value|, 1e-7): below
-    that they are rounding noise of the gemv (the LP's z-residual sits at 1e-14 from the first
-    iteration on) and far under the solver's own feasibility tolerance (eps^0.5 = 1.5e-8)."""
+    (north_star tolerance).  Residual norms are compared relative to max(|value|, 1e-6), i.e.
+    to 1e-14 absolute once they are small: the rounding floor of evaluating a residual with a
+    different summation order is ~1e-14 here (the LP's z-residual sits at that level from the
+    first iteration on), far under the solver's feasibility tolerance (eps^0.5 = 1.5e-8)."""
     worst, first_bad = 0.0, None
     for i, (a, b) in enumerate(zip(tg, tc)):
         for k in keys:
-            floor = 1e-7 if k.endswith("_res") else 1e-12
+            floor = 1e-6 if k.endswith("_res") else 1e-12
             den = max(abs(b[k]), floor)
             d = abs(a[k] - b[k]) / den
             worst = max(worst, d)
