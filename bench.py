@@ -130,7 +130,10 @@ class IterTimer:
             dev_ms, h2d, d2h = self.ctx.stats(reset=True)
             tw, ts, tf = self.ctx.last_schur_timings()
             lc = self.ctx.launch_count()
-            row.update(dev_ms=dev_ms, h2d=h2d, d2h=d2h, t_w=tw, t_syrk=ts, t_fact=tf, launches=lc - self._launch0)
+            red = getattr(solver.syssolver, "time_reduce_ms", 0.0)
+            row.update(dev_ms=dev_ms, h2d=h2d, d2h=d2h, t_w=tw, t_syrk=ts, t_fact=tf, launches=lc - self._launch0,
+                       reduce_ms=red - getattr(self, "_red0", 0.0))
+            self._red0 = red
             self._launch0 = lc
         self.rows.append(row)
         self._t = time.perf_counter()
@@ -284,7 +287,12 @@ def main():
         tw = torch.tensor([wall], dtype=torch.float64, device="cuda")
         dist.all_reduce(tw, op=dist.ReduceOp.MAX)
         wall = float(tw.item())
-    dev_s = sum(r["dev_ms"] for r in rows) * 1e-3
+    dev_s = sum(r["dev_ms"] + r.get("reduce_ms", 0.0) for r in rows) * 1e-3
+    reduce_ms = float(np.mean([r.get("reduce_ms", 0.0) for r in rows]))
+    if dist is not None:
+        td = torch.tensor([dev_s], dtype=torch.float64, device="cuda")
+        dist.all_reduce(td, op=dist.ReduceOp.MAX)
+        dev_s = float(td.item())
     ms_per_step = 1e3 * wall / k
     h2d = sum(r["h2d"] for r in rows) / k
     d2h = sum(r["d2h"] for r in rows) / k
@@ -295,7 +303,9 @@ def main():
     if rank != 0:
         return
 
-    q_sqrt = model.q  # every cone of this model takes the sqrt-oracle (syrk) branch, qrchol.jl:228-242
+    # every cone of this model takes the sqrt-oracle (syrk) branch, qrchol.jl:228-242; with N ranks the
+    # launch timed on rank 0 contracts that rank's rows only
+    q_sqrt = gpu.cones.row_counts[0] if world > 1 else model.q
     syrk_flops = q_sqrt * N * (N + 1)  # algorithmic flops of the G'HG contraction per launch
     peak_tf = cublas_dgemm_tflops()
     achieved_tf = syrk_flops / (t_syrk * 1e-3) / 1e12
@@ -316,12 +326,14 @@ def main():
             "value_definition": "iterations / device time: CUDA-event time of every kernel region of the C-ABI calls of the timed iterations (inputs resident in HBM)",
             "e2e_definition": "iterations / wall time of the same iterations through the C-ABI with host vectors (all H2D/D2H copies and the host-side stepper included)",
             "status_after_limit": gpu.status, "iterations_run": gpu.num_iters,
+            "parallelism": ("cones partitioned by block over %d ranks, NCCL reduce of the partial Schur matrices onto rank 0 (Cholesky + solves on rank 0)" % world) if world > 1 else "single GPU",
             "line_search_candidates_per_step": float(np.mean([r["n_cand"] for r in rows])),
             "refinement_solves_per_step": float(np.mean([r["n_ref"] for r in rows])),
         }),
         "e2e": {"value": k / wall, "unit": "iterations/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": launches,
         "schur_assemble_ms": t_w + t_syrk,
+        "schur_reduce_ms": reduce_ms,
         "cholesky_ms": t_fact,
         "clocks": clocks,
         "roofline": {

@@ -210,6 +210,7 @@ int hyb_model_load(hyb_ctx* c, int64_t q, int64_t N, const double* GQ2, int64_t 
     HYB_CUDA(cudaMalloc(&c->HGQ2, sizeof(double) * c->ldq * ncol));
     HYB_CUDA(cudaMalloc(&c->S, sizeof(double) * c->ldS * ncol));
     HYB_CUDA(cudaMemset(c->HGQ2, 0, sizeof(double) * c->ldq * ncol));
+    HYB_CUDA(cudaMemset(c->S, 0, sizeof(double) * c->ldS * ncol));
     if (q > 0 && N > 0)
         HYB_CUDA(cudaMemcpy2D(c->GQ2, sizeof(double) * c->ldq, GQ2, sizeof(double) * q, sizeof(double) * q, N,
                               cudaMemcpyHostToDevice));
@@ -376,24 +377,47 @@ int hyb_cones_dder3(hyb_ctx* c, const double* dir, double* out) {
     return 0;
 }
 
-int hyb_schur_update(hyb_ctx* c, double* t_assemble_ms, double* t_fact_ms, int* fact_kind) {
+int hyb_schur_assemble(hyb_ctx* c, double* t_assemble_ms) {
     if (!c || !c->loaded) return -1;
     HYB_CUDA(cudaSetDevice(c->device));
     if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(ensure_updated(c, c->loaded_scal));
     const int64_t q = c->q, N = c->N;
+    if (t_assemble_ms) *t_assemble_ms = 0;
+    if (N == 0) return 0;
+    HYB_CUDA(cudaEventRecord(c->ev0, c->st));
+    if (q > 0) {
+        // HGQ2 = W * GQ2 with W'W = H (primal barrier) or H^-1 (dual barrier): qrchol.jl:228-241
+        HYB_CHECK(hybi_cones_prod(c->st, c->cones, 5, c->GQ2, c->ldq, c->HGQ2, c->ldq, N));
+        HYB_CUDA(cudaEventRecord(c->ev3, c->st));
+        // lhs = HGQ2' HGQ2, upper (outer_prod!, qrchol.jl:242)
+        HYB_CHECK(hyb_gemm_tn(c->st, N, N, q, 1.0, c->HGQ2, c->ldq, c->HGQ2, c->ldq, 0.0, c->S, c->ldS, HYB_GEMM_UPPER));
+    } else {
+        HYB_CUDA(cudaEventRecord(c->ev3, c->st));
+        HYB_CUDA(cudaMemsetAsync(c->S, 0, sizeof(double) * c->ldS * N, c->st));
+    }
+    HYB_CUDA(cudaEventRecord(c->ev1, c->st));
+    HYB_CUDA(cudaEventSynchronize(c->ev1));
+    float ta = 0, tw = 0;
+    HYB_CUDA(cudaEventElapsedTime(&ta, c->ev0, c->ev1));
+    HYB_CUDA(cudaEventElapsedTime(&tw, c->ev0, c->ev3));
+    c->last_t[0] = tw;
+    c->last_t[1] = ta - tw;
+    c->dev_ms += ta;
+    if (t_assemble_ms) *t_assemble_ms = ta;
+    c->fact_ok = false;
+    return 0;
+}
+
+int hyb_schur_factor(hyb_ctx* c, double* t_fact_ms, int* fact_kind) {
+    if (!c || !c->loaded) return -1;
+    HYB_CUDA(cudaSetDevice(c->device));
+    const int64_t N = c->N;
+    if (t_fact_ms) *t_fact_ms = 0;
+    if (fact_kind) *fact_kind = 0;
     if (N == 0) {
-        if (t_assemble_ms) *t_assemble_ms = 0;
-        if (t_fact_ms) *t_fact_ms = 0;
-        if (fact_kind) *fact_kind = 0;
         c->fact_ok = true;
         return 0;
     }
-    HYB_CUDA(cudaEventRecord(c->ev0, c->st));
-    // HGQ2 = W * GQ2 with W'W = H (primal barrier) or H^-1 (dual barrier): qrchol.jl:228-241
-    HYB_CHECK(hybi_cones_prod(c->st, c->cones, 5, c->GQ2, c->ldq, c->HGQ2, c->ldq, N));
-    HYB_CUDA(cudaEventRecord(c->ev3, c->st));
-    // lhs = HGQ2' HGQ2, upper (outer_prod!, qrchol.jl:242)
-    HYB_CHECK(hyb_gemm_tn(c->st, N, N, q, 1.0, c->HGQ2, c->ldq, c->HGQ2, c->ldq, 0.0, c->S, c->ldS, HYB_GEMM_UPPER));
     HYB_CUDA(cudaEventRecord(c->ev1, c->st));
     // posdef_fact_copy! (dense.jl:228-249)
     int info = 0, kind = 0;
@@ -410,19 +434,32 @@ int hyb_schur_update(hyb_ctx* c, double* t_assemble_ms, double* t_fact_ms, int* 
     }
     HYB_CUDA(cudaEventRecord(c->ev2, c->st));
     HYB_CUDA(cudaEventSynchronize(c->ev2));
-    float ta = 0, tf = 0, tw = 0;
-    HYB_CUDA(cudaEventElapsedTime(&ta, c->ev0, c->ev1));
+    float tf = 0;
     HYB_CUDA(cudaEventElapsedTime(&tf, c->ev1, c->ev2));
-    HYB_CUDA(cudaEventElapsedTime(&tw, c->ev0, c->ev3));
-    c->last_t[0] = tw;
-    c->last_t[1] = ta - tw;
     c->last_t[2] = tf;
-    c->dev_ms += ta + tf;
-    if (t_assemble_ms) *t_assemble_ms = ta;
+    c->dev_ms += tf;
     if (t_fact_ms) *t_fact_ms = tf;
     if (fact_kind) *fact_kind = kind;
     c->fact_ok = (kind >= 0);
     return kind < 0 ? 1 : 0;
+}
+
+int hyb_schur_update(hyb_ctx* c, double* t_assemble_ms, double* t_fact_ms, int* fact_kind) {
+    HYB_CHECK(hyb_schur_assemble(c, t_assemble_ms));
+    return hyb_schur_factor(c, t_fact_ms, fact_kind);
+}
+
+int hyb_device_buffer(hyb_ctx* c, int which, void** ptr, int64_t* rows, int64_t* cols, int64_t* ld) {
+    if (!c || !c->loaded) return -1;
+    if (which == 0) {
+        *ptr = c->S;
+        *rows = c->N;
+        *cols = c->N;
+        *ld = c->ldS;
+        return 0;
+    }
+    hyb_set_error("hyb_device_buffer: unknown buffer %d", which);
+    return -3;
 }
 
 int hyb_schur_get(hyb_ctx* c, double* lhs) {

@@ -268,8 +268,15 @@ def make_gpu_solver(device: int = 0, dist=None, **solver_kwargs):
     B200QRCholSystemSolver{Float64}(), use_dense_model = true)` selects in Julia)."""
     from .host.solver import Solver
 
-    if dist is not None and dist.get_world_size() > 1:
-        raise NotImplementedError("multi-GPU Schur reduce is not wired yet")
     ctx = Context(device)
+    if dist is not None and dist.get_world_size() > 1:
+        import torch
+
+        from .sharded import Comm, GpuLocalBackend, ShardedQRCholSystemSolver
+
+        comm = Comm(dist, torch.device("cuda", device))
+        ss = ShardedQRCholSystemSolver(GpuLocalBackend(ctx), comm)
+        ss.ctx = ctx
+        return Solver(ss.cones_factory, ss, **solver_kwargs)
     ss = B200QRCholSystemSolver(ctx)
     return Solver(ss.cones_factory, ss, **solver_kwargs)

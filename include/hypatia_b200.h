@@ -90,6 +90,15 @@ int hyb_cones_dder3(hyb_ctx* ctx, const double* dir, double* out);
  * 2 Cholesky after the diagonal shift of increase_diag! (dense.jl:100-107), -1 failed.
  * Times are CUDA-event milliseconds (time_upsys / time_upfact, Solvers.jl:112-113). */
 int hyb_schur_update(hyb_ctx* ctx, double* t_assemble_ms, double* t_fact_ms, int* fact_kind);
+/* The two halves of hyb_schur_update, for the multi-GPU path: every rank assembles
+ * the partial sum over ITS cones (qrchol.jl:228-254 restricted to a cone range), the partials are
+ * reduced onto the factorizing rank (NCCL reduce on the buffer hyb_device_buffer(0) exposes), and
+ * only that rank factorizes (qrchol.jl:257-258). */
+int hyb_schur_assemble(hyb_ctx* ctx, double* t_assemble_ms);
+int hyb_schur_factor(hyb_ctx* ctx, double* t_fact_ms, int* fact_kind);
+/* device address of an internal matrix for collectives: which = 0 -> assembled Schur matrix
+ * (rows x cols, leading dimension ld, column-major FP64, upper triangle valid). */
+int hyb_device_buffer(hyb_ctx* ctx, int which, void** ptr, int64_t* rows, int64_t* cols, int64_t* ld);
 /* ldiv!(x, fact, rhs), qrchol.jl:75; rhs and x are N x nrhs */
 int hyb_schur_solve(hyb_ctx* ctx, const double* rhs, double* x, int64_t nrhs);
 /* copy of the assembled N x N matrix (upper triangle valid), for tests / fallbacks */
