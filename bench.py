@@ -220,8 +220,19 @@ def main():
         print(json.dumps(line))
         return
 
+    os.environ.setdefault("NCCL_DEBUG", "WARN")  # keep NCCL's version banner off stdout (one JSON line only)
+    if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"
     import torch
 
+    if world > 1:
+        # torchrun pins OMP_NUM_THREADS=1; the (untimed) host preprocessing is LAPACK-heavy
+        try:
+            from threadpoolctl import threadpool_limits
+
+            threadpool_limits(max(1, cores // world))
+        except Exception:
+            pass
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the hypatia_b200 hot path has no CPU fallback")
     torch.cuda.set_device(local_rank)

@@ -264,36 +264,54 @@ __device__ __forceinline__ void st_release(int* p, int v) {
     asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
-// stage the diagonal block ib of U into shared memory (Us[r * LDS + c], r <= c), identity padded
-__device__ __forceinline__ void load_diag_block(const double* __restrict__ U, int64_t ld, int ib, int N, double* Us,
-                                                double* dinv, int tid, int nth) {
-    const int nbr = min(NB, N - ib * NB);
-    const double* base = U + (int64_t)ib * NB + (int64_t)ib * NB * ld;
-    for (int e = tid; e < NB * NB; e += nth) {
-        const int r = e % NB, c = e / NB;
-        double v = (r == c) ? 1.0 : 0.0;
-        if (r <= c && c < nbr) v = __ldg(base + r + (int64_t)c * ld);
-        Us[r * LDS + c] = v;
-    }
-}
+// Wavefront solve kernels: 512 threads, one CTA per 128-row block.
+//  * tiles of U that a block needs are double-buffered in registers, so the loads of tile
+//    jb+1 are in flight while the CTA waits for / consumes x-block jb;
+//  * the diagonal block is staged in shared memory pre-scaled by the reciprocal pivots, which
+//    shortens the serial chain of the substitution to one shuffle + one FMA per row.
+constexpr int TRSV_THREADS = 512;
 
 // forward: solve U' y = b in place (x holds b on entry, y on exit)
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(TRSV_THREADS, 1)
 trsv_fwd_kernel(const double* __restrict__ U, int64_t ld, double* x, int N, int nblk, int* flags, int epoch) {
     extern __shared__ double sm[];
-    double* Us = sm;
-    double* dinv = sm + NB * LDS;
+    double* Us = sm;               // Us[k * LDS + i] = U[k][i] / U[i][i]  (k < i)
+    double* dinv = sm + NB * LDS;  // 1 / U[i][i]
     double* ys = dinv + NB;
     double* rs = ys + NB;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     for (int ib = blockIdx.x; ib < nblk; ib += gridDim.x) {
         __syncthreads();  // previous block's substitution is done with Us
-        load_diag_block(U, ld, ib, N, Us, dinv, tid, 256);
-        double acc[16];
+        const int nbr = min(NB, N - ib * NB);
+        const double* dblk = U + (int64_t)ib * NB + (int64_t)ib * NB * ld;
+        if (tid < NB) dinv[tid] = (tid < nbr) ? 1.0 / __ldg(dblk + tid + (int64_t)tid * ld) : 1.0;
+        __syncthreads();
+        for (int e = tid; e < NB * NB; e += TRSV_THREADS) {
+            const int r = e & (NB - 1), c = e >> 7;
+            Us[r * LDS + c] = (r < c && c < nbr) ? __ldg(dblk + r + (int64_t)c * ld) * dinv[c] : 0.0;
+        }
+        // column dots with the tiles above the diagonal: warp w owns columns 8w..8w+7
+        double acc[8];
 #pragma unroll
-        for (int c = 0; c < 16; ++c) acc[c] = 0.0;
-        const int col0 = ib * NB + warp * 16;
+        for (int c = 0; c < 8; ++c) acc[c] = 0.0;
+        const int col0 = ib * NB + warp * 8;
+        double2 nx0[8], nx1[8];
+        auto load_tile = [&](int jb) {
+            const double* base = U + (int64_t)jb * NB + 2 * lane;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const int col = col0 + c;
+                if (col < N) {
+                    nx0[c] = __ldg((const double2*)(base + (int64_t)col * ld));
+                    nx1[c] = __ldg((const double2*)(base + (int64_t)col * ld + 64));
+                } else {
+                    nx0[c] = nx1[c] = make_double2(0.0, 0.0);
+                }
+            }
+        };
+        if (ib > 0) load_tile(0);
         for (int jb = 0; jb < ib; ++jb) {
+            // tile jb is already in registers (its loads were issued before this wait)
             if (tid == 0) {
                 while (ld_acquire(&flags[jb]) != epoch) {
                 }
@@ -302,19 +320,12 @@ trsv_fwd_kernel(const double* __restrict__ U, int64_t ld, double* x, int N, int 
             if (tid < NB) ys[tid] = __ldcg(&x[jb * NB + tid]);
             __syncthreads();
             const double y0 = ys[2 * lane], y1 = ys[2 * lane + 1], y2 = ys[64 + 2 * lane], y3 = ys[65 + 2 * lane];
-            const double* base = U + (int64_t)jb * NB + 2 * lane;
 #pragma unroll
-            for (int c = 0; c < 16; ++c) {
-                const int col = col0 + c;
-                if (col < N) {
-                    const double2 v0 = __ldg((const double2*)(base + (int64_t)col * ld));
-                    const double2 v1 = __ldg((const double2*)(base + (int64_t)col * ld + 64));
-                    acc[c] += (v0.x * y0 + v0.y * y1) + (v1.x * y2 + v1.y * y3);
-                }
-            }
+            for (int c = 0; c < 8; ++c) acc[c] += (nx0[c].x * y0 + nx0[c].y * y1) + (nx1[c].x * y2 + nx1[c].y * y3);
+            if (jb + 1 < ib) load_tile(jb + 1);
         }
 #pragma unroll
-        for (int c = 0; c < 16; ++c) {
+        for (int c = 0; c < 8; ++c) {
             double v = acc[c];
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -323,30 +334,27 @@ trsv_fwd_kernel(const double* __restrict__ U, int64_t ld, double* x, int N, int 
         __syncthreads();  // everyone is done with ys; Us fully staged
         if (lane == 0) {
 #pragma unroll
-            for (int c = 0; c < 16; ++c) {
+            for (int c = 0; c < 8; ++c) {
                 const int col = col0 + c;
-                rs[warp * 16 + c] = (col < N) ? (x[col] - acc[c]) : 0.0;
+                rs[warp * 8 + c] = (col < N) ? (x[col] - acc[c]) * dinv[warp * 8 + c] : 0.0;
             }
         }
-        if (tid < NB) dinv[tid] = 1.0 / Us[tid * LDS + tid];
         __syncthreads();
-        // y_ib = U11^-T r by forward substitution, one warp, 4 rows per lane in registers
+        // y = U11^-T r by forward substitution on the pre-scaled block: with r~_i = r_i / U_ii,
+        // y_k = r~_k and r~_i -= (U[k][i] / U_ii) y_k.  One warp, 4 rows per lane in registers.
         if (warp == 0) {
             double rv[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) rv[j] = rs[lane + 32 * j];
 #pragma unroll
             for (int slot = 0; slot < 4; ++slot) {
+#pragma unroll 8
                 for (int kk = 0; kk < 32; ++kk) {
                     const int k = slot * 32 + kk;
-                    const double yk = __shfl_sync(0xffffffffu, rv[slot] * dinv[k], kk);
-                    if (lane == kk) rv[slot] = yk;
+                    const double yk = __shfl_sync(0xffffffffu, rv[slot], kk);
                     const double* urow = Us + k * LDS + lane;
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const int i = lane + 32 * j;
-                        if (i > k) rv[j] -= urow[32 * j] * yk;
-                    }
+                    for (int j = 0; j < 4; ++j) rv[j] -= urow[32 * j] * yk;  // entries with i <= k are stored as 0
                 }
             }
 #pragma unroll
@@ -356,29 +364,43 @@ trsv_fwd_kernel(const double* __restrict__ U, int64_t ld, double* x, int N, int 
             }
         }
         __syncthreads();
-        if (tid == 0) {
-            __threadfence();
-            st_release(&flags[ib], epoch);
-        }
+        if (tid == 0) st_release(&flags[ib], epoch);
     }
 }
 
 // backward: solve U x = y in place
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(TRSV_THREADS, 1)
 trsv_bwd_kernel(const double* __restrict__ U, int64_t ld, double* x, int N, int nblk, int* flags, int epoch) {
     extern __shared__ double sm[];
-    double* Us = sm;
+    double* Us = sm;               // Us[i * LDS + k] = U[i][k] / U[i][i]  (i < k)
     double* dinv = sm + NB * LDS;
     double* xs = dinv + NB;
-    double* part = xs + NB;  // [2][NB]
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, r = tid & (NB - 1), half = tid >> 7;
+    double* part = xs + NB;  // [4][NB]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, r = tid & (NB - 1), quarter = tid >> 7;
     for (int ib = nblk - 1 - (int)blockIdx.x; ib >= 0; ib -= gridDim.x) {
         __syncthreads();
-        load_diag_block(U, ld, ib, N, Us, dinv, tid, 256);
+        const int nbr = min(NB, N - ib * NB);
+        const double* dblk = U + (int64_t)ib * NB + (int64_t)ib * NB * ld;
+        if (tid < NB) dinv[tid] = (tid < nbr) ? 1.0 / __ldg(dblk + tid + (int64_t)tid * ld) : 1.0;
+        __syncthreads();
+        for (int e = tid; e < NB * NB; e += TRSV_THREADS) {
+            const int rr = e & (NB - 1), c = e >> 7;
+            Us[rr * LDS + c] = (rr < c && c < nbr) ? __ldg(dblk + rr + (int64_t)c * ld) * dinv[rr] : 0.0;
+        }
         const int row = ib * NB + r;
         const bool row_ok = row < N;
         double acc = 0.0;
+        double nx[32];
+        auto load_tile = [&](int jb) {
+            const int ncol = min(NB, N - jb * NB);
+            const double* p = U + row + (int64_t)(jb * NB + quarter * 32) * ld;
+            const int cend = ncol - quarter * 32;
+#pragma unroll
+            for (int c = 0; c < 32; ++c) nx[c] = (row_ok && c < cend) ? __ldg(p + (int64_t)c * ld) : 0.0;
+        };
+        if (ib < nblk - 1) load_tile(nblk - 1);
         for (int jb = nblk - 1; jb > ib; --jb) {
+            // tile jb is already in registers (its loads were issued before this wait)
             if (tid == 0) {
                 while (ld_acquire(&flags[jb]) != epoch) {
                 }
@@ -386,47 +408,39 @@ trsv_bwd_kernel(const double* __restrict__ U, int64_t ld, double* x, int N, int 
             __syncthreads();
             if (tid < NB) xs[tid] = (jb * NB + tid < N) ? __ldcg(&x[jb * NB + tid]) : 0.0;
             __syncthreads();
-            if (row_ok) {
-                const int ncol = min(NB, N - jb * NB);
-                const double* p = U + row + (int64_t)(jb * NB + half * 64) * ld;
-                const int cend = min(64, ncol - half * 64);
-                double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-                int c = 0;
-                for (; c + 3 < cend; c += 4) {
-                    a0 += __ldg(p + (int64_t)c * ld) * xs[half * 64 + c];
-                    a1 += __ldg(p + (int64_t)(c + 1) * ld) * xs[half * 64 + c + 1];
-                    a2 += __ldg(p + (int64_t)(c + 2) * ld) * xs[half * 64 + c + 2];
-                    a3 += __ldg(p + (int64_t)(c + 3) * ld) * xs[half * 64 + c + 3];
-                }
-                for (; c < cend; ++c) a0 += __ldg(p + (int64_t)c * ld) * xs[half * 64 + c];
-                acc += (a0 + a1) + (a2 + a3);
+            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll
+            for (int c = 0; c < 32; c += 4) {
+                a0 += nx[c] * xs[quarter * 32 + c];
+                a1 += nx[c + 1] * xs[quarter * 32 + c + 1];
+                a2 += nx[c + 2] * xs[quarter * 32 + c + 2];
+                a3 += nx[c + 3] * xs[quarter * 32 + c + 3];
             }
+            acc += (a0 + a1) + (a2 + a3);
+            if (jb - 1 > ib) load_tile(jb - 1);
         }
         __syncthreads();
-        part[half * NB + r] = acc;
-        if (tid < NB) dinv[tid] = 1.0 / Us[tid * LDS + tid];
+        part[quarter * NB + r] = acc;
         __syncthreads();
-        // x_ib = U11^-1 (y_ib - acc) by backward substitution, one warp
+        // x = U11^-1 (y - acc) by backward substitution on the row-scaled block, one warp
         if (warp == 0) {
             double rv[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 const int i = lane + 32 * j;
                 const int rw = ib * NB + i;
-                rv[j] = (rw < N) ? (x[rw] - (part[i] + part[NB + i])) : 0.0;
+                const double s = (part[i] + part[NB + i]) + (part[2 * NB + i] + part[3 * NB + i]);
+                rv[j] = (rw < N) ? (x[rw] - s) * dinv[i] : 0.0;
             }
 #pragma unroll
             for (int slot = 3; slot >= 0; --slot) {
+#pragma unroll 8
                 for (int kk = 31; kk >= 0; --kk) {
                     const int k = slot * 32 + kk;
-                    const double xk = __shfl_sync(0xffffffffu, rv[slot] * dinv[k], kk);
-                    if (lane == kk) rv[slot] = xk;
+                    const double xk = __shfl_sync(0xffffffffu, rv[slot], kk);
                     const double* ucol = Us + lane * LDS + k;
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const int i = lane + 32 * j;
-                        if (i < k) rv[j] -= ucol[32 * j * LDS] * xk;
-                    }
+                    for (int j = 0; j < 4; ++j) rv[j] -= ucol[32 * j * LDS] * xk;  // entries with i >= k are 0
                 }
             }
 #pragma unroll
@@ -436,10 +450,7 @@ trsv_bwd_kernel(const double* __restrict__ U, int64_t ld, double* x, int N, int 
             }
         }
         __syncthreads();
-        if (tid == 0) {
-            __threadfence();
-            st_release(&flags[ib], epoch);
-        }
+        if (tid == 0) st_release(&flags[ib], epoch);
     }
 }
 
@@ -478,7 +489,7 @@ void hyb_chol_free(HybChol& ch) {
 
 constexpr int PANEL_SMEM = (NB * LDS + IB) * (int)sizeof(double);
 constexpr int TRSM_SMEM = (NB * LDS + NB * TLD + NB) * (int)sizeof(double);
-constexpr int TRSV_SMEM = (NB * LDS + 4 * NB) * (int)sizeof(double);
+constexpr int TRSV_SMEM = (NB * LDS + 6 * NB) * (int)sizeof(double);
 int64_t g_potrf_launches = 0;
 
 // Right-looking factorization with one panel of look-ahead: while the bulk of step k's
@@ -553,10 +564,10 @@ int hyb_potrs(cudaStream_t st, HybChol& ch, double* x) {
     int* flags = ch.flags;
     int epoch = ++ch.epoch;
     void* args[] = {(void*)&U, (void*)&ld, (void*)&x, (void*)&N, (void*)&nblk, (void*)&flags, (void*)&epoch};
-    HYB_CUDA(cudaLaunchCooperativeKernel((void*)trsv_fwd_kernel, dim3(grid), dim3(256), args, TRSV_SMEM, st));
+    HYB_CUDA(cudaLaunchCooperativeKernel((void*)trsv_fwd_kernel, dim3(grid), dim3(TRSV_THREADS), args, TRSV_SMEM, st));
     int epoch2 = ++ch.epoch;
     void* args2[] = {(void*)&U, (void*)&ld, (void*)&x, (void*)&N, (void*)&nblk, (void*)&flags, (void*)&epoch2};
-    HYB_CUDA(cudaLaunchCooperativeKernel((void*)trsv_bwd_kernel, dim3(grid), dim3(256), args2, TRSV_SMEM, st));
+    HYB_CUDA(cudaLaunchCooperativeKernel((void*)trsv_bwd_kernel, dim3(grid), dim3(TRSV_THREADS), args2, TRSV_SMEM, st));
     g_potrf_launches += 2;
     return 0;
 }
