@@ -158,6 +158,19 @@ def cublas_dgemm_tflops(n=8192, reps=3):
     return 2.0 * n**3 * reps / (e0.elapsed_time(e1) * 1e-3) / 1e12
 
 
+def ncu_traffic(N, K):
+    """DRAM bytes per launch of the syrk kernel from the committed ncu capture (None if the
+    shape was not captured)."""
+    path = os.path.join(ROOT, "profiles", "r01_syrk_N8192_ncu_full.json")
+    try:
+        d = json.load(open(path))
+        if f"N={N}, K={K}," in d["kernel"]:
+            return d["dram_bytes_per_launch"]
+    except Exception:
+        pass
+    return None
+
+
 def run_cpu_port(model, steps, warmup, preset_fact=None):
     """CPU restatement of the reference path (oracle/, numpy/scipy -> OpenBLAS) on host cores."""
     from hypatia_b200.host.solver import Solver
@@ -353,7 +366,8 @@ def main():
             "frac": achieved_tf / peak_tf if peak_tf else None,
             "peak_source": "cuBLAS DGEMM 8192^3 measured in this run (MEASURED_PEAKS.json has no FP64 figure; FP64 tensor work on sm_100a is DMMA, not tcgen05)",
             "algorithmic_flops_per_launch": syrk_flops, "avg_launch_ms": t_syrk,
-            "traffic": None,
+            "traffic": ncu_traffic(N, q_sqrt),
+            "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full capture in profiles/r01_syrk_N8192_ncu_full.json (same N, K)",
         },
     }
     if not args.no_cpu_baseline and world == 1:
