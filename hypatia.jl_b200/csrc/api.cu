@@ -624,12 +624,31 @@ int hyb_posdef_solve(hyb_ctx* c, int64_t N, double* A, int64_t lda, double* B, i
         if (info) *info = inf;
         e = cudaMemcpy2D(A, sizeof(double) * lda, ch.F, sizeof(double) * ch.ld, sizeof(double) * N, N,
                          cudaMemcpyDeviceToHost);
+        if (inf == 0 && e == cudaSuccess && rc == 0 && nrhs >= 4) {
+            // many right-hand sides: blocked triangular solves (dense toolkit of the cone engines)
+            double *dB = nullptr, *Lc = nullptr;
+            int64_t lB = 0;
+            rc = upload_padded(B, N, nrhs, ldb, &dB, &lB);
+            if (rc == 0 && cudaMalloc(&Lc, sizeof(double) * ch.ld * N) != cudaSuccess) rc = -1;
+            if (rc == 0) rc = hyb_transpose(c->st, ch.F, ch.ld, N, N, Lc, ch.ld, 1);
+            if (rc == 0) rc = hyb_trsm_fwd(c->st, ch.F, ch.ld, N, dB, lB, nrhs);
+            if (rc == 0) rc = hyb_trsm_bwd(c->st, ch.F, Lc, ch.ld, N, dB, lB, nrhs);
+            if (rc == 0) {
+                e = cudaStreamSynchronize(c->st);
+                if (e == cudaSuccess)
+                    e = cudaMemcpy2D(B, sizeof(double) * ldb, dB, sizeof(double) * lB, sizeof(double) * N, nrhs,
+                                     cudaMemcpyDeviceToHost);
+            }
+            cudaFree(dB);
+            cudaFree(Lc);
+        } else {
         for (int64_t j = 0; inf == 0 && e == cudaSuccess && rc == 0 && j < nrhs; ++j) {
             e = cudaMemcpyAsync(ch.work, B + j * ldb, sizeof(double) * N, cudaMemcpyHostToDevice, c->st);
             if (e == cudaSuccess) rc = hyb_potrs(c->st, ch, ch.work);
             if (e == cudaSuccess && rc == 0)
                 e = cudaMemcpyAsync(B + j * ldb, ch.work, sizeof(double) * N, cudaMemcpyDeviceToHost, c->st);
             if (e == cudaSuccess) e = cudaStreamSynchronize(c->st);
+        }
         }
     }
     if (e != cudaSuccess) {

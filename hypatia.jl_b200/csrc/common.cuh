@@ -47,6 +47,7 @@ int64_t hyb_potrf_launch_count();
 struct HybChol {
     int64_t N = 0, ld = 0, nblk = 0;
     double* F = nullptr;      // N x N (ld), upper factor after hyb_potrf
+    bool owns_F = true;
     int* flags = nullptr;     // nblk ready flags for the wavefront solves
     int* info = nullptr;      // device: index (1-based) of first non-positive pivot, 0 = success
     int epoch = 0;
@@ -58,6 +59,14 @@ int hyb_chol_alloc(HybChol& ch, int64_t N);
 void hyb_chol_free(HybChol& ch);
 // in-place upper Cholesky of ch.F (upper triangle referenced); returns LAPACK-style info via *info_out
 int hyb_potrf(cudaStream_t st, HybChol& ch, int* info_out);
+int hyb_chol_attach(HybChol& ch, double* F, int64_t ld, int64_t N);
+// multi-RHS triangular solves with the upper factor U (ld): B <- U^-T B ; B <- U^-1 B (needs Lc = U')
+int hyb_trsm_fwd(cudaStream_t st, const double* U, int64_t ld, int64_t N, double* B, int64_t ldb, int64_t nrhs);
+int hyb_trsm_bwd(cudaStream_t st, const double* U, const double* Lc, int64_t ld, int64_t N, double* B, int64_t ldb,
+                 int64_t nrhs);
+// dst (cols x rows) = src' ; upper_only != 0 reads only src's upper triangle (zeros elsewhere)
+int hyb_transpose(cudaStream_t st, const double* src, int64_t lds_, int64_t rows, int64_t cols, double* dst,
+                  int64_t ldd, int upper_only);
 // x <- (U'U)^-1 x for one device vector of length N
 int hyb_potrs(cudaStream_t st, HybChol& ch, double* x);
 

@@ -204,8 +204,28 @@ __device__ __forceinline__ void trsm_update_chunk(const double* Uc, double* T, i
 // substitution with the 32 x 32 diagonal block (one thread per column, chunk in
 // registers).  Substitution only - no explicit inverse (LAPACK dtrsm semantics).
 // --------------------------------------------------------------------------------
+// stage U11 (nb x nb upper, identity padded to 128) and a 128 x 64 slab of the right-hand sides
+__device__ __forceinline__ void trsm_stage(const double* __restrict__ U11, int64_t ldu, int nb,
+                                           const double* __restrict__ B, int64_t ld, int64_t col0, int ncol, double* Uc,
+                                           double* T, double* dinv, int tid) {
+    for (int e = tid; e < NB * NB; e += TRSM_THREADS) {
+        const int k = e & (NB - 1), i = e >> 7;
+        double v = (k == i) ? 1.0 : 0.0;
+        if (k <= i && i < nb) v = __ldg(U11 + k + (int64_t)i * ldu);
+        Uc[i * LDS + k] = v;
+    }
+    for (int e = tid; e < NB * TRSM_COLS; e += TRSM_THREADS) {
+        const int r = e & (NB - 1), c = e >> 7;
+        T[r * TLD + c] = (c < ncol && r < nb) ? B[r + (col0 + c) * ld] : 0.0;
+    }
+    __syncthreads();
+    if (tid < NB) dinv[tid] = 1.0 / Uc[tid * LDS + tid];
+    __syncthreads();
+}
+
 __global__ void __launch_bounds__(TRSM_THREADS, 1)
-trsm_upper_T_kernel(const double* __restrict__ U11, int64_t ldu, double* __restrict__ A12, int64_t ld, int64_t n2) {
+trsm_upper_T_kernel(const double* __restrict__ U11, int64_t ldu, int nb, double* __restrict__ A12, int64_t ld,
+                    int64_t n2) {
     extern __shared__ double sm[];
     double* Uc = sm;                     // Uc[i * LDS + k] = U[k][i]  (column i of U11, contiguous in k)
     double* T = sm + NB * LDS;           // T[r * TLD + c]
@@ -213,17 +233,7 @@ trsm_upper_T_kernel(const double* __restrict__ U11, int64_t ldu, double* __restr
     const int tid = threadIdx.x;
     const int64_t col0 = (int64_t)blockIdx.x * TRSM_COLS;
     const int ncol = (int)((n2 - col0 < TRSM_COLS) ? (n2 - col0) : TRSM_COLS);
-    for (int e = tid; e < NB * NB; e += TRSM_THREADS) {
-        const int k = e & (NB - 1), i = e >> 7;
-        Uc[i * LDS + k] = __ldg(U11 + k + (int64_t)i * ldu);
-    }
-    for (int e = tid; e < NB * TRSM_COLS; e += TRSM_THREADS) {
-        const int r = e & (NB - 1), c = e >> 7;
-        T[r * TLD + c] = (c < ncol) ? A12[r + (col0 + c) * ld] : 0.0;
-    }
-    __syncthreads();
-    if (tid < NB) dinv[tid] = 1.0 / Uc[tid * LDS + tid];
-    __syncthreads();
+    trsm_stage(U11, ldu, nb, A12, ld, col0, ncol, Uc, T, dinv, tid);
     const bool solver_thread = tid < TRSM_COLS;
     if (solver_thread) trsm_solve_chunk<0>(Uc, dinv, T, tid);
     __syncthreads();
@@ -241,7 +251,102 @@ trsm_upper_T_kernel(const double* __restrict__ U11, int64_t ldu, double* __restr
     __syncthreads();
     for (int e = tid; e < NB * TRSM_COLS; e += TRSM_THREADS) {
         const int r = e & (NB - 1), c = e >> 7;
-        if (c < ncol) A12[r + (col0 + c) * ld] = T[r * TLD + c];
+        if (c < ncol && r < nb) A12[r + (col0 + c) * ld] = T[r * TLD + c];
+    }
+}
+
+// ---- backward variant: slab <- U11^-1 slab (U11 upper, back substitution) ----------------
+template <int CB>
+__device__ __forceinline__ void trsm_bsolve_chunk(const double* Uc, const double* dinv, double* T, int c) {
+    double v[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = T[(CB * 32 + i) * TLD + c];
+#pragma unroll
+    for (int k = 31; k >= 0; --k) {
+        v[k] *= dinv[CB * 32 + k];
+#pragma unroll
+        for (int i = 0; i < k; ++i) v[i] -= Uc[(CB * 32 + k) * LDS + CB * 32 + i] * v[k];  // U[i][k]
+    }
+#pragma unroll
+    for (int i = 0; i < 32; ++i) T[(CB * 32 + i) * TLD + c] = v[i];
+}
+
+// rows of chunk CB -= U[chunk rows, later rows] * X[later rows, :]   (later = (CB+1)*32 .. 127)
+template <int CB>
+__device__ __forceinline__ void trsm_bupdate_chunk(const double* Uc, double* T, int tid) {
+    if (CB == 3) return;
+    const int tr = tid >> 4, tc = tid & 15;
+    const int r0 = CB * 32 + 4 * tr, c0 = 4 * tc;
+    double acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.0;
+#pragma unroll 4
+    for (int k = (CB + 1) * 32; k < NB; ++k) {
+        double u[4], y[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) u[i] = Uc[k * LDS + r0 + i];  // U[r0+i][k]
+#pragma unroll
+        for (int j = 0; j < 4; ++j) y[j] = T[k * TLD + c0 + j];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[i][j] += u[i] * y[j];
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) T[(r0 + i) * TLD + c0 + j] -= acc[i][j];
+}
+
+__global__ void __launch_bounds__(TRSM_THREADS, 1)
+trsm_upper_N_kernel(const double* __restrict__ U11, int64_t ldu, int nb, double* __restrict__ B, int64_t ld,
+                    int64_t n2) {
+    extern __shared__ double sm[];
+    double* Uc = sm;
+    double* T = sm + NB * LDS;
+    double* dinv = T + NB * TLD;
+    const int tid = threadIdx.x;
+    const int64_t col0 = (int64_t)blockIdx.x * TRSM_COLS;
+    const int ncol = (int)((n2 - col0 < TRSM_COLS) ? (n2 - col0) : TRSM_COLS);
+    trsm_stage(U11, ldu, nb, B, ld, col0, ncol, Uc, T, dinv, tid);
+    const bool solver_thread = tid < TRSM_COLS;
+    if (solver_thread) trsm_bsolve_chunk<3>(Uc, dinv, T, tid);
+    __syncthreads();
+    trsm_bupdate_chunk<2>(Uc, T, tid);
+    __syncthreads();
+    if (solver_thread) trsm_bsolve_chunk<2>(Uc, dinv, T, tid);
+    __syncthreads();
+    trsm_bupdate_chunk<1>(Uc, T, tid);
+    __syncthreads();
+    if (solver_thread) trsm_bsolve_chunk<1>(Uc, dinv, T, tid);
+    __syncthreads();
+    trsm_bupdate_chunk<0>(Uc, T, tid);
+    __syncthreads();
+    if (solver_thread) trsm_bsolve_chunk<0>(Uc, dinv, T, tid);
+    __syncthreads();
+    for (int e = tid; e < NB * TRSM_COLS; e += TRSM_THREADS) {
+        const int r = e & (NB - 1), c = e >> 7;
+        if (c < ncol && r < nb) B[r + (col0 + c) * ld] = T[r * TLD + c];
+    }
+}
+
+// dst (cols x rows) = src' ; upper_only: read src's upper triangle only (zeros elsewhere)
+__global__ void transpose_kernel(const double* __restrict__ src, int64_t lds_, int64_t rows, int64_t cols,
+                                 double* __restrict__ dst, int64_t ldd, int upper_only) {
+    __shared__ double tile[32][33];
+    const int64_t r0 = (int64_t)blockIdx.x * 32, c0 = (int64_t)blockIdx.y * 32;
+    for (int j = threadIdx.y; j < 32; j += 8) {
+        const int64_t r = r0 + threadIdx.x, c = c0 + j;
+        double v = 0.0;
+        if (r < rows && c < cols && (!upper_only || r <= c)) v = src[r + c * lds_];
+        tile[j][threadIdx.x] = v;
+    }
+    __syncthreads();
+    for (int j = threadIdx.y; j < 32; j += 8) {
+        const int64_t c = c0 + threadIdx.x, r = r0 + j;  // dst(c, r) = src(r, c)
+        if (r < rows && c < cols) dst[c + r * ldd] = tile[threadIdx.x][j];
     }
 }
 
@@ -477,7 +582,7 @@ int hyb_chol_alloc(HybChol& ch, int64_t N) {
 }
 
 void hyb_chol_free(HybChol& ch) {
-    cudaFree(ch.F);
+    if (ch.owns_F) cudaFree(ch.F);
     cudaFree(ch.flags);
     cudaFree(ch.info);
     if (ch.panel_stream) cudaStreamDestroy(ch.panel_stream);
@@ -501,6 +606,7 @@ int hyb_potrf(cudaStream_t st, HybChol& ch, int* info_out) {
     if (!attr_set) {
         HYB_CUDA(cudaFuncSetAttribute(potf2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PANEL_SMEM));
         HYB_CUDA(cudaFuncSetAttribute(trsm_upper_T_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TRSM_SMEM));
+        HYB_CUDA(cudaFuncSetAttribute(trsm_upper_N_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TRSM_SMEM));
         attr_set = true;
     }
     cudaStream_t sp = ch.panel_stream;
@@ -515,7 +621,7 @@ int hyb_potrf(cudaStream_t st, HybChol& ch, int* info_out) {
         if (n2 > 0) {
             double* A12 = ch.F + k0 + (k0 + nb) * ld;
             trsm_upper_T_kernel<<<(unsigned)((n2 + TRSM_COLS - 1) / TRSM_COLS), TRSM_THREADS, TRSM_SMEM, s>>>(
-                A11, ld, A12, ld, n2);
+                A11, ld, nb, A12, ld, n2);
             ++g_potrf_launches;
             HYB_CUDA(cudaGetLastError());
         }
@@ -580,5 +686,81 @@ int hyb_copy_upper(cudaStream_t st, const double* src, int64_t lds_, double* dst
     dim3 grid((unsigned)((N + 255) / 256), (unsigned)N);
     copy_upper_kernel<<<grid, 256, 0, st>>>(src, lds_, dst, ldd, N);
     HYB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// dense toolkit used by the large-PSD and WSOS cone engines
+// ---------------------------------------------------------------------------------------
+static int ensure_trsm_attrs() {
+    static bool done = false;
+    if (!done) {
+        HYB_CUDA(cudaFuncSetAttribute(potf2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PANEL_SMEM));
+        HYB_CUDA(cudaFuncSetAttribute(trsm_upper_T_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TRSM_SMEM));
+        HYB_CUDA(cudaFuncSetAttribute(trsm_upper_N_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TRSM_SMEM));
+        done = true;
+    }
+    return 0;
+}
+
+// B (N x nrhs) <- U^-T B : blocked forward substitution, DMMA updates (LAPACK dtrsm 'L','U','T')
+int hyb_trsm_fwd(cudaStream_t st, const double* U, int64_t ld, int64_t N, double* B, int64_t ldb, int64_t nrhs) {
+    if (N <= 0 || nrhs <= 0) return 0;
+    HYB_CHECK(ensure_trsm_attrs());
+    const unsigned grid = (unsigned)((nrhs + TRSM_COLS - 1) / TRSM_COLS);
+    for (int64_t k0 = 0; k0 < N; k0 += NB) {
+        const int nb = (int)((N - k0 < NB) ? (N - k0) : NB);
+        trsm_upper_T_kernel<<<grid, TRSM_THREADS, TRSM_SMEM, st>>>(U + k0 + k0 * ld, ld, nb, B + k0, ldb, nrhs);
+        ++g_potrf_launches;
+        HYB_CUDA(cudaGetLastError());
+        const int64_t rest = N - k0 - nb;
+        if (rest > 0)
+            HYB_CHECK(hyb_gemm_tn(st, rest, nrhs, nb, -1.0, U + k0 + (k0 + nb) * ld, ld, B + k0, ldb, 1.0, B + k0 + nb, ldb, 0));
+    }
+    return 0;
+}
+
+// B (N x nrhs) <- U^-1 B : blocked back substitution; Lc = U' (lower, explicit zeros above the diagonal)
+int hyb_trsm_bwd(cudaStream_t st, const double* U, const double* Lc, int64_t ld, int64_t N, double* B, int64_t ldb,
+                 int64_t nrhs) {
+    if (N <= 0 || nrhs <= 0) return 0;
+    HYB_CHECK(ensure_trsm_attrs());
+    const unsigned grid = (unsigned)((nrhs + TRSM_COLS - 1) / TRSM_COLS);
+    const int64_t last = ((N - 1) / NB) * NB;
+    for (int64_t k0 = last; k0 >= 0; k0 -= NB) {
+        const int nb = (int)((N - k0 < NB) ? (N - k0) : NB);
+        trsm_upper_N_kernel<<<grid, TRSM_THREADS, TRSM_SMEM, st>>>(U + k0 + k0 * ld, ld, nb, B + k0, ldb, nrhs);
+        ++g_potrf_launches;
+        HYB_CUDA(cudaGetLastError());
+        if (k0 > 0)  // B[0:k0] -= U[0:k0, k0:k0+nb] X_k = (Lc[k0:k0+nb, 0:k0])' X_k
+            HYB_CHECK(hyb_gemm_tn(st, k0, nrhs, nb, -1.0, Lc + k0, ld, B + k0, ldb, 1.0, B, ldb, 0));
+    }
+    return 0;
+}
+
+int hyb_transpose(cudaStream_t st, const double* src, int64_t lds_, int64_t rows, int64_t cols, double* dst,
+                  int64_t ldd, int upper_only) {
+    if (rows <= 0 || cols <= 0) return 0;
+    dim3 grid((unsigned)((rows + 31) / 32), (unsigned)((cols + 31) / 32));
+    transpose_kernel<<<grid, dim3(32, 8), 0, st>>>(src, lds_, rows, cols, dst, ldd, upper_only);
+    ++g_potrf_launches;
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// Cholesky workspace around caller-owned storage (F is not freed by hyb_chol_free)
+int hyb_chol_attach(HybChol& ch, double* F, int64_t ld, int64_t N) {
+    HYB_CHECK(hyb_chol_alloc(ch, 0));
+    cudaFree(ch.F);
+    ch.F = F;
+    ch.owns_F = false;
+    ch.N = N;
+    ch.ld = ld;
+    ch.nblk = (N + NB - 1) / NB;
+    cudaFree(ch.flags);
+    HYB_CUDA(cudaMalloc(&ch.flags, sizeof(int) * (ch.nblk > 0 ? ch.nblk : 1)));
+    HYB_CUDA(cudaMemset(ch.flags, 0, sizeof(int) * (ch.nblk > 0 ? ch.nblk : 1)));
+    cudaFree(ch.work);
+    HYB_CUDA(cudaMalloc(&ch.work, sizeof(double) * (N > 0 ? N : 1)));
     return 0;
 }

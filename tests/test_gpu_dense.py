@@ -67,3 +67,18 @@ def test_posdef_detects_indefinite():
     A2[200, 200] = -1.0
     _, _, info2 = context().posdef_solve(A2, np.ones(N))
     assert info2 == 201
+
+
+@pytest.mark.parametrize("N,nrhs", [(5, 4), (128, 65), (129, 64), (300, 200), (700, 130)])
+def test_posdef_solve_many_rhs(N, nrhs):
+    """Blocked multi-RHS triangular solves (forward with U', backward with U)."""
+    rng = np.random.default_rng(N + nrhs)
+    B = rng.standard_normal((N + 5, N))
+    A = B.T @ B + N * 1e-3 * np.eye(N)
+    rhs = rng.standard_normal((N, nrhs))
+    _, X, info = context().posdef_solve(np.triu(A), rhs)
+    assert info == 0
+    resid = np.linalg.norm(A @ X - rhs) / (np.linalg.norm(A) * np.linalg.norm(X))
+    assert resid < 100 * N * EPS
+    Xref = sla.cho_solve(sla.cho_factor(A), rhs)
+    assert rel_err(X, Xref) < 1e-8 * np.linalg.cond(A) ** 0.5 + 1e-9
