@@ -238,7 +238,8 @@ int hyb_model_load(hyb_ctx* c, int64_t q, int64_t N, const double* GQ2, int64_t 
             return -3;
         }
         expect += d.dim;
-        const bool mergeable = d.type != HYB_CONE_WSOSINTERPNONNEGATIVE && d.type != HYB_CONE_WSOSINTERPPOSSEMIDEFTRI;
+        const bool mergeable = d.type != HYB_CONE_WSOSINTERPNONNEGATIVE && d.type != HYB_CONE_WSOSINTERPPOSSEMIDEFTRI &&
+                               !(d.type == HYB_CONE_POSSEMIDEFTRI && d.side_or_R > 32);  // large PSD: one dense engine each
         if (!cs.blocks.empty() && mergeable) {
             HybConeBlock& b = cs.blocks.back();
             if (b.type == d.type && b.dim == d.dim && b.use_dual == d.use_dual_barrier) {

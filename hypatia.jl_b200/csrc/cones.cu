@@ -12,6 +12,8 @@
 // with lanes striding down the rows.  All reductions are fixed-order.
 #include "cones.cuh"
 
+#include "cones_dense.cuh"
+
 namespace {
 
 int64_t g_cone_launches = 0;
@@ -657,7 +659,7 @@ inline unsigned nblocks(int64_t n, int per) { return (unsigned)((n + per - 1) / 
 
 }  // namespace
 
-int64_t hybi_cones_launch_count() { return g_cone_launches; }
+int64_t hybi_cones_launch_count() { return g_cone_launches + hybd_launch_count(); }
 
 int hybi_cones_alloc(HybCones& cs) {
     const int64_t q = cs.q > 0 ? cs.q : 1, K = cs.K > 0 ? cs.K : 1;
@@ -677,9 +679,11 @@ int hybi_cones_alloc(HybCones& cs) {
     int64_t mat_total = 0;
     for (auto& b : cs.blocks) {
         if (b.type == HYB_POSSEMIDEFTRI) {
-            if (b.side > PSD_MAX_SIDE) {
-                hyb_set_error("PosSemidefTri side %d > %d is not supported by the batched GPU path yet", b.side, PSD_MAX_SIDE);
-                return -2;
+            if (b.side > PSD_MAX_SIDE) {  // large cone: dense engine (one object per cone)
+                HybDensePsd* d = nullptr;
+                HYB_CHECK(hybd_psd_create(&d, b.side));
+                b.dense = d;
+                continue;
             }
             b.mat_off = mat_total;
             mat_total += b.count * 4 * b.side * b.side;
@@ -706,6 +710,11 @@ int hybi_cones_alloc(HybCones& cs) {
 }
 
 void hybi_cones_free(HybCones& cs) {
+    for (auto& b : cs.blocks)
+        if (b.dense) {
+            hybd_psd_destroy((HybDensePsd*)b.dense);
+            b.dense = nullptr;
+        }
     cudaFree(cs.point);
     cudaFree(cs.dual);
     cudaFree(cs.grad);
@@ -748,6 +757,12 @@ int hybi_cones_update(cudaStream_t st, HybCones& cs, const double* primal, const
                 break;
             }
             case HYB_POSSEMIDEFTRI:
+                if (b.dense) {
+                    HYB_CHECK(hybd_psd_update(st, (HybDensePsd*)b.dense, primal + b.offset, dual_in + b.offset, scal, irtmu,
+                                              cs.point + b.offset, cs.dual + b.offset, cs.grad + b.offset,
+                                              cs.item_flag + b.offset, cs.item_prox + b.offset));
+                    break;
+                }
                 psd_update_kernel<<<nblocks(b.count, PSD_WARPS), PSD_WARPS * 32,
                                     PSD_WARPS * 4 * PSD_MAT * sizeof(double), st>>>(
                     b.count, b.side, b.offset, b.mat_off, primal, dual_in, scal, irtmu, cs.point, cs.dual, cs.grad,
@@ -805,6 +820,10 @@ int hybi_cones_prod(cudaStream_t st, HybCones& cs, int which, const double* arr,
                 break;
             }
             case HYB_POSSEMIDEFTRI:
+                if (b.dense) {
+                    HYB_CHECK(hybd_psd_prod(st, (HybDensePsd*)b.dense, op, arr + b.offset, lda, prod + b.offset, ldp, m));
+                    break;
+                }
                 psd_prod_kernel<<<nblocks(b.count * m, PSD_WARPS), PSD_WARPS * 32,
                                   PSD_WARPS * 3 * PSD_MAT * sizeof(double), st>>>(b.count, b.side, b.offset, b.mat_off, m,
                                                                                  op, cs.mats, arr, lda, prod, ldp);
@@ -843,6 +862,10 @@ int hybi_cones_dder3(cudaStream_t st, HybCones& cs, const double* dir, double* o
                 break;
             }
             case HYB_POSSEMIDEFTRI:
+                if (b.dense) {
+                    HYB_CHECK(hybd_psd_dder3(st, (HybDensePsd*)b.dense, dir + b.offset, out + b.offset));
+                    break;
+                }
                 psd_dder3_kernel<<<nblocks(b.count, PSD_WARPS), PSD_WARPS * 32, PSD_WARPS * 3 * PSD_MAT * sizeof(double),
                                    st>>>(b.count, b.side, b.offset, b.mat_off, cs.mats, dir, out);
                 break;

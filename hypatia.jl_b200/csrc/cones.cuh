@@ -26,6 +26,7 @@ struct HybConeBlock {
     int64_t offset = 0;    // first row
     int64_t cone0 = 0;     // index of the first cone (into aux)
     int64_t mat_off = 0;   // PSD: offset (doubles) of this block's matrices in `mats`
+    void* dense = nullptr; // dense engine object (PosSemidefTri with side > 32)
 };
 
 struct HybCones {

@@ -1,0 +1,17 @@
+// Dense cone engines: cones whose oracles are sequences of large dense operations
+// (Cholesky, multi-RHS triangular solves, FP64 DMMA contractions) rather than one kernel.
+#pragma once
+#include "common.cuh"
+
+struct HybDensePsd;   // PosSemidefTri with side > 32 (possemideftri.jl)
+int hybd_psd_create(HybDensePsd** out, int side);
+void hybd_psd_destroy(HybDensePsd* c);
+// loads point = scal * primal, dual; feasibility, dual feasibility, grad, check_numerics, proxsqr.
+// primal/dual/point/dual_out/grad are this cone's dim-vectors; flag/prox its item slots.
+int hybd_psd_update(cudaStream_t st, HybDensePsd* c, const double* primal, const double* dual_in, double scal, double irtmu,
+                    double* point, double* dual_out, double* grad, int* flag, double* prox);
+// prod columns = op(H) arr columns; arr/prod point at this cone's first row, column strides lda/ldp
+int hybd_psd_prod(cudaStream_t st, HybDensePsd* c, int op, const double* arr, int64_t lda, double* prod, int64_t ldp,
+                  int64_t m);
+int hybd_psd_dder3(cudaStream_t st, HybDensePsd* c, const double* dir, double* out);
+int64_t hybd_launch_count();

@@ -34,6 +34,7 @@ SPEC_SETS = {
     "rsoc_small": [cs.EpiPerSquare(3)] * 3 + [cs.EpiPerSquare(8)] * 33 + [cs.EpiPerSquare(4)],
     "soc_large": [cs.EpiNormEucl(33), cs.EpiNormEucl(100), cs.EpiPerSquare(70), cs.EpiPerSquare(257)],
     "psd": [cs.PosSemidefTri(cs.svec_length(s)) for s in (1, 2, 3, 5, 16, 16, 16, 32)],
+    "psd_large": [cs.PosSemidefTri(cs.svec_length(s)) for s in (33, 64, 100, 150)] + [cs.EpiNormEucl(5)],
     "mixed": [cs.Nonnegative(10)] + [cs.EpiNormEucl(8)] * 4 + [cs.EpiPerSquare(8)] * 4
     + [cs.PosSemidefTri(136)] * 3 + [cs.Nonnegative(3), cs.EpiNormEucl(5)],
 }

@@ -144,6 +144,18 @@ def test_portfolio_socs_small():
     assert abs(gpu.primal_obj - cpu.primal_obj) <= 1e-7 * (1 + abs(cpu.primal_obj))
 
 
+def test_nearestpsd_large_psd_cone():
+    """cfg2-shaped (variant A): one dense PosSemidefTri cone with side > 32 (dense engine:
+    Cholesky + multi-RHS triangular solves + DMMA contractions) and one equality."""
+    gpu, cpu = solve_both(lambda: instances.nearestpsd(side=40, seed=2))
+    assert gpu.status == cpu.status == "Optimal"
+    assert abs(gpu.num_iters - cpu.num_iters) <= 1
+    assert abs(gpu.primal_obj - cpu.primal_obj) <= 1e-7 * (1 + abs(cpu.primal_obj))
+    n_early = max(3, len(cpu.trace) // 2)
+    _, bad_early = traj_deviation(gpu.trace[:n_early], cpu.trace[:n_early])
+    assert bad_early is None, bad_early
+
+
 def test_modify_and_resolve_on_gpu():
     """modify1 (test/nativeinstances.jl:2866-2949) through the CUDA path."""
     model = Model([1, 0], [[1, 1]], [-2], -np.eye(2), [0, 0], [cs.Nonnegative(2)])
