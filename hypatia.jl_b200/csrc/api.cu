@@ -6,6 +6,7 @@
 #include "../../include/hypatia_b200.h"
 #include "common.cuh"
 #include "cones.cuh"
+#include "cones_dense.cuh"
 #include "tma.cuh"
 
 int hyb_copy_upper(cudaStream_t st, const double* src, int64_t lds_, double* dst, int64_t ldd, int64_t N);
@@ -254,6 +255,10 @@ int hyb_model_load(hyb_ctx* c, int64_t q, int64_t N, const double* GQ2, int64_t 
         b.dim = (int)d.dim;
         b.side = (int)d.side_or_R;
         b.use_dual = d.use_dual_barrier;
+        b.U = d.U;
+        b.nPs = d.nPs;
+        b.Ps = d.Ps;
+        b.Ls = d.Ls;
         b.count = 1;
         b.offset = d.offset;
         b.cone0 = k;
@@ -330,8 +335,7 @@ int hyb_cones_hess_prod(hyb_ctx* c, int which, const double* arr, double* prod, 
     if (!c || !c->loaded) return -1;
     HYB_CUDA(cudaSetDevice(c->device));
     if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(ensure_updated(c, c->loaded_scal));
-    if (which == 6) which = 0;  // hess_prod_slow! == hess_prod! for the cones batched here (Cones.jl:229-231)
-    if (which < 0 || which > 5) {
+    if (which < 0 || which > 6) {
         hyb_set_error("hyb_cones_hess_prod: bad selector %d", which);
         return -3;
     }
@@ -387,11 +391,67 @@ int hyb_schur_assemble(hyb_ctx* c, double* t_assemble_ms) {
     if (N == 0) return 0;
     HYB_CUDA(cudaEventRecord(c->ev0, c->st));
     if (q > 0) {
+        // use_sqrt_hess_oracles per cone (qrchol.jl:222-225, Cones.jl:193-199): closed-form cones
+        // always; a generic-Hessian cone only if its Hessian Cholesky exists
+        HybCones& cs = c->cones;
+        std::vector<char> sqrt_mask(cs.blocks.size(), 1);
+        bool all_sqrt = true;
+        for (size_t bi = 0; bi < cs.blocks.size(); ++bi) {
+            if (cs.blocks[bi].type == HYB_WSOSINTERPNONNEGATIVE) {
+                int ok = 0;
+                HYB_CHECK(hybd_wsos_sqrt_ok(c->st, (HybDenseWsos*)cs.blocks[bi].dense, &ok));
+                sqrt_mask[bi] = (char)ok;
+                all_sqrt = all_sqrt && ok;
+            }
+        }
         // HGQ2 = W * GQ2 with W'W = H (primal barrier) or H^-1 (dual barrier): qrchol.jl:228-241
-        HYB_CHECK(hybi_cones_prod(c->st, c->cones, 5, c->GQ2, c->ldq, c->HGQ2, c->ldq, N));
+        if (!all_sqrt) {
+            cs.block_mask = sqrt_mask;
+            for (size_t bi = 0; bi < cs.blocks.size(); ++bi)
+                if (!sqrt_mask[bi]) {
+                    const HybConeBlock& b = cs.blocks[bi];
+                    HYB_CUDA(cudaMemset2DAsync(c->HGQ2 + b.offset, sizeof(double) * c->ldq, 0,
+                                               sizeof(double) * b.count * b.dim, N, c->st));
+                }
+        }
+        int rcp = hybi_cones_prod(c->st, cs, 5, c->GQ2, c->ldq, c->HGQ2, c->ldq, N);
+        cs.block_mask.clear();
+        HYB_CHECK(rcp);
         HYB_CUDA(cudaEventRecord(c->ev3, c->st));
         // lhs = HGQ2' HGQ2, upper (outer_prod!, qrchol.jl:242)
         HYB_CHECK(hyb_gemm_tn(c->st, N, N, q, 1.0, c->HGQ2, c->ldq, c->HGQ2, c->ldq, 0.0, c->S, c->ldS, HYB_GEMM_UPPER));
+        // remaining cones: lhs += GQ2_k' (H~_k GQ2_k)  (block_hess_prod! + mul!, qrchol.jl:248-254)
+        for (size_t bi = 0; bi < cs.blocks.size() && !all_sqrt; ++bi) {
+            if (sqrt_mask[bi]) continue;
+            const HybConeBlock& b = cs.blocks[bi];
+            const int64_t rows = b.count * b.dim;
+            std::vector<char> one(cs.blocks.size(), 0);
+            one[bi] = 1;
+            cs.block_mask = one;
+            rcp = hybi_cones_prod(c->st, cs, 4, c->GQ2, c->ldq, c->HGQ2, c->ldq, N);
+            cs.block_mask.clear();
+            HYB_CHECK(rcp);
+            const double *Ak = c->GQ2 + b.offset, *Bk = c->HGQ2 + b.offset;
+            int64_t ldk = c->ldq;
+            double* bounce = nullptr;
+            if (b.offset & 1) {  // TMA needs 16-byte aligned operands: stage the cone's rows
+                const int64_t ldb = hyb_round_up(rows, 16);
+                HYB_CUDA(cudaMalloc(&bounce, sizeof(double) * ldb * N * 2));
+                HYB_CUDA(cudaMemcpy2DAsync(bounce, sizeof(double) * ldb, Ak, sizeof(double) * c->ldq, sizeof(double) * rows, N,
+                                           cudaMemcpyDeviceToDevice, c->st));
+                HYB_CUDA(cudaMemcpy2DAsync(bounce + ldb * N, sizeof(double) * ldb, Bk, sizeof(double) * c->ldq,
+                                           sizeof(double) * rows, N, cudaMemcpyDeviceToDevice, c->st));
+                Ak = bounce;
+                Bk = bounce + ldb * N;
+                ldk = ldb;
+            }
+            int rcg = hyb_gemm_tn(c->st, N, N, rows, 1.0, Ak, ldk, Bk, ldk, 1.0, c->S, c->ldS, HYB_GEMM_UPPER);
+            if (bounce) {
+                cudaStreamSynchronize(c->st);
+                cudaFree(bounce);
+            }
+            HYB_CHECK(rcg);
+        }
     } else {
         HYB_CUDA(cudaEventRecord(c->ev3, c->st));
         HYB_CUDA(cudaMemsetAsync(c->S, 0, sizeof(double) * c->ldS * N, c->st));

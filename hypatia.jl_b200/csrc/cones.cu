@@ -687,6 +687,10 @@ int hybi_cones_alloc(HybCones& cs) {
             }
             b.mat_off = mat_total;
             mat_total += b.count * 4 * b.side * b.side;
+        } else if (b.type == HYB_WSOSINTERPNONNEGATIVE) {
+            HybDenseWsos* d = nullptr;
+            HYB_CHECK(hybd_wsos_create(&d, b.U, b.nPs, b.Ps, b.Ls));
+            b.dense = d;
         } else if (b.type != HYB_NONNEGATIVE && b.type != HYB_EPINORMEUCL && b.type != HYB_EPIPERSQUARE) {
             hyb_set_error("cone type %d is not supported by the GPU path yet", b.type);
             return -2;
@@ -712,7 +716,8 @@ int hybi_cones_alloc(HybCones& cs) {
 void hybi_cones_free(HybCones& cs) {
     for (auto& b : cs.blocks)
         if (b.dense) {
-            hybd_psd_destroy((HybDensePsd*)b.dense);
+            if (b.type == HYB_WSOSINTERPNONNEGATIVE) hybd_wsos_destroy((HybDenseWsos*)b.dense);
+            else hybd_psd_destroy((HybDensePsd*)b.dense);
             b.dense = nullptr;
         }
     cudaFree(cs.point);
@@ -768,6 +773,11 @@ int hybi_cones_update(cudaStream_t st, HybCones& cs, const double* primal, const
                     b.count, b.side, b.offset, b.mat_off, primal, dual_in, scal, irtmu, cs.point, cs.dual, cs.grad,
                     cs.mats, cs.item_flag, cs.item_prox);
                 break;
+            case HYB_WSOSINTERPNONNEGATIVE:
+                HYB_CHECK(hybd_wsos_update(st, (HybDenseWsos*)b.dense, primal + b.offset, dual_in + b.offset, scal, irtmu,
+                                           cs.point + b.offset, cs.dual + b.offset, cs.grad + b.offset,
+                                           cs.item_flag + b.offset, cs.item_prox + b.offset));
+                break;
             default:
                 hyb_set_error("cone type %d unsupported", b.type);
                 return -2;
@@ -791,10 +801,13 @@ int hybi_cones_reduce(cudaStream_t st, HybCones& cs, int use_max_prox, int* all_
 int hybi_cones_prod(cudaStream_t st, HybCones& cs, int which, const double* arr, int64_t lda, double* prod, int64_t ldp,
                    int64_t m) {
     if (m <= 0) return 0;
-    for (const auto& b : cs.blocks) {
+    for (size_t bi = 0; bi < cs.blocks.size(); ++bi) {
+        const auto& b = cs.blocks[bi];
+        if (!cs.block_mask.empty() && !cs.block_mask[bi]) continue;
         int op;
         if (which == 4) op = b.use_dual ? HYB_OP_INV_HESS : HYB_OP_HESS;
         else if (which == 5) op = b.use_dual ? HYB_OP_INV_SQRT_HESS : HYB_OP_SQRT_HESS;
+        else if (which == 6) op = (b.type == HYB_WSOSINTERPNONNEGATIVE) ? 6 : HYB_OP_HESS;  // Cones.jl:229-231
         else op = which;
         const int64_t rows = b.count * b.dim;
         switch (b.type) {
@@ -827,6 +840,9 @@ int hybi_cones_prod(cudaStream_t st, HybCones& cs, int which, const double* arr,
                 psd_prod_kernel<<<nblocks(b.count * m, PSD_WARPS), PSD_WARPS * 32,
                                   PSD_WARPS * 3 * PSD_MAT * sizeof(double), st>>>(b.count, b.side, b.offset, b.mat_off, m,
                                                                                  op, cs.mats, arr, lda, prod, ldp);
+                break;
+            case HYB_WSOSINTERPNONNEGATIVE:
+                HYB_CHECK(hybd_wsos_prod(st, (HybDenseWsos*)b.dense, op, arr + b.offset, lda, prod + b.offset, ldp, m));
                 break;
             default:
                 hyb_set_error("cone type %d unsupported", b.type);
@@ -868,6 +884,9 @@ int hybi_cones_dder3(cudaStream_t st, HybCones& cs, const double* dir, double* o
                 }
                 psd_dder3_kernel<<<nblocks(b.count, PSD_WARPS), PSD_WARPS * 32, PSD_WARPS * 3 * PSD_MAT * sizeof(double),
                                    st>>>(b.count, b.side, b.offset, b.mat_off, cs.mats, dir, out);
+                break;
+            case HYB_WSOSINTERPNONNEGATIVE:
+                HYB_CHECK(hybd_wsos_dder3(st, (HybDenseWsos*)b.dense, dir + b.offset, out + b.offset));
                 break;
             default:
                 hyb_set_error("cone type %d unsupported", b.type);

@@ -26,7 +26,12 @@ struct HybConeBlock {
     int64_t offset = 0;    // first row
     int64_t cone0 = 0;     // index of the first cone (into aux)
     int64_t mat_off = 0;   // PSD: offset (doubles) of this block's matrices in `mats`
-    void* dense = nullptr; // dense engine object (PosSemidefTri with side > 32)
+    void* dense = nullptr; // dense engine object (PosSemidefTri with side > 32, WSOS cones)
+    // WSOS parameters (host pointers, valid during hyb_model_load only)
+    int64_t U = 0;
+    int nPs = 0;
+    const double* const* Ps = nullptr;
+    const int64_t* Ls = nullptr;
 };
 
 struct HybCones {
@@ -42,6 +47,7 @@ struct HybCones {
     int* red_flag = nullptr;      // 1 : AND over items
     double* red_prox = nullptr;   // 1 : max / sum over items
     double* tmp = nullptr;        // q scratch vector
+    std::vector<char> block_mask; // if non-empty: hybi_cones_prod touches only blocks with mask != 0
 };
 
 int hybi_cones_alloc(HybCones& cs);
@@ -55,7 +61,7 @@ int hybi_cones_update(cudaStream_t st, HybCones& cs, const double* primal, const
 int hybi_cones_reduce(cudaStream_t st, HybCones& cs, int use_max_prox, int* all_flags, double* agg);
 // prod = op(H) * arr for every cone; arr/prod are q x m column-major device arrays (ld >= q).
 // which: 0 hess, 1 inv_hess, 2 sqrt_hess, 3 inv_sqrt_hess, 4 block (inv_hess for dual-barrier cones, else hess),
-//        5 block sqrt (inv_sqrt for dual-barrier cones, else sqrt)
+//        5 block sqrt (inv_sqrt for dual-barrier cones, else sqrt), 6 hess_prod_slow
 int hybi_cones_prod(cudaStream_t st, HybCones& cs, int which, const double* arr, int64_t lda, double* prod, int64_t ldp,
                    int64_t m);
 int hybi_cones_dder3(cudaStream_t st, HybCones& cs, const double* dir, double* out);

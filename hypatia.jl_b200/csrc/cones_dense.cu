@@ -324,3 +324,372 @@ int hybd_psd_dder3(cudaStream_t st, HybDensePsd* c, const double* dir, double* o
     HYB_CUDA(cudaGetLastError());
     return 0;
 }
+
+// =======================================================================================
+// WSOSInterpNonnegative (real): src/Cones/wsosinterpnonnegative.jl
+//   update_feas :99-128   Lambda_k = P_k' diag(s) P_k, Cholesky each
+//   is_dual_feas :130-133 all(z > eps) (necessary condition only)
+//   update_grad :135-149  F_k = R_k^-T P_k'  (Lambda_k = R_k' R_k),  g_j = -sum_k |F_k[:,j]|^2
+//   update_hess :151-166  H = sum_k (F_k' F_k) .^ 2
+//   generic products with H / chol(H): Cones.jl:108-125,202-214; update_hess_fact :233-245
+//   hess_prod_slow! :168-191, dder3 :193-204, partial_lambda! :206-211
+//   update_use_hess_prod_slow: Cones.jl:218-227
+// Everything is evaluated eagerly at load time (the reference fills the same caches lazily
+// during check_cone_points); if chol(H) fails the candidate is reported as failing
+// check_numerics (the reference would continue with a Bunch-Kaufman factorization).
+// =======================================================================================
+namespace {
+
+__global__ void rowscale_kernel(const double* __restrict__ in, const double* __restrict__ d, int64_t rows, int64_t cols,
+                                int64_t ld, double* __restrict__ out) {
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= rows * cols) return;
+    const int64_t r = e % rows, c = e / rows;
+    out[r + c * ld] = d[r] * in[r + c * ld];
+}
+// out[j] = beta * out[j] + alpha * sum_r A[r,j] * B[r,j]   (one warp per column)
+__global__ void coldot_kernel(const double* __restrict__ A, const double* __restrict__ B, int64_t rows, int64_t cols,
+                              int64_t ld, double alpha, double beta, double* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int64_t j = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (j >= cols) return;
+    double s = 0.0;
+    for (int64_t r = lane; r < rows; r += 32) s += A[r + j * ld] * B[r + j * ld];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) out[j] = (beta == 0.0 ? 0.0 : beta * out[j]) + alpha * s;
+}
+// H_upper (+)= UU_upper .^ 2
+__global__ void sq_accum_kernel(const double* __restrict__ UU, double* __restrict__ H, int64_t n, int64_t ld, int first) {
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n * n) return;
+    const int64_t r = e % n, c = e / n;
+    if (r > c) return;
+    const double u = UU[r + c * ld];
+    H[r + c * ld] = (first ? 0.0 : H[r + c * ld]) + u * u;
+}
+__global__ void symmetrize_kernel(double* __restrict__ H, int64_t n, int64_t ld) {
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n * n) return;
+    const int64_t r = e % n, c = e / n;
+    if (r > c) H[r + c * ld] = H[c + r * ld];
+}
+__global__ void copy_upper_dense_kernel(const double* __restrict__ src, double* __restrict__ dst, int64_t n, int64_t ld) {
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n * n) return;
+    const int64_t r = e % n, c = e / n;
+    dst[r + c * ld] = (r <= c) ? src[r + c * ld] : 0.0;
+}
+__global__ void __launch_bounds__(1024) all_gt_eps_kernel(int64_t n, const double* __restrict__ v, int* out) {
+    __shared__ int ok;
+    if (threadIdx.x == 0) ok = 1;
+    __syncthreads();
+    int mine = 1;
+    for (int64_t i = threadIdx.x; i < n; i += 1024)
+        if (!(v[i] > HYB_EPS)) mine = 0;
+    if (!mine) ok = 0;
+    __syncthreads();
+    if (threadIdx.x == 0) *out = ok;
+}
+__global__ void copy_mat_kernel(const double* __restrict__ src, int64_t lds_, double* __restrict__ dst, int64_t ldd,
+                                int64_t rows, int64_t cols) {
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= rows * cols) return;
+    const int64_t r = e % rows, c = e / rows;
+    dst[r + c * ldd] = src[r + c * lds_];
+}
+// scal: [0] <g,p>  [1] <Hinv g, g>  [2] psi' Hinv psi  [3] p' H p ; infos: K Lambda infos then H info
+__global__ void wsos_finalize_kernel(const int* const* lam_infos, int nPs, const int* info_h, const int* dual_ok,
+                                     const double* scal, double nu, int64_t dim, int* flag, double* prox, int* slow,
+                                     int* sqrt_ok) {
+    int f = 0;
+    double p = 0.0;
+    bool feas = true;
+    for (int k = 0; k < nPs; ++k)
+        if (*lam_infos[k] != 0) feas = false;
+    if (*dual_ok) f |= HYB_ST_DUAL_FEAS;
+    *sqrt_ok = (feas && *info_h == 0) ? 1 : 0;
+    *slow = 0;
+    if (feas) {
+        f |= HYB_ST_FEAS;
+        bool ok = (*info_h == 0);
+        if (fabs(1.0 + scal[0] / nu) > 1.220703125e-4 * (double)dim) ok = false;
+        if (fabs(1.0 - scal[1] / nu) > 1.104854345603981e-1 * (double)dim) ok = false;
+        if (ok) f |= HYB_ST_NUMERICS;
+        p = (scal[2] < -1.4901161193847656e-08 * (double)dim) ? INFINITY : fabs(scal[2]);
+        // update_use_hess_prod_slow (Cones.jl:218-227)
+        if (fabs(1.0 - scal[3] / nu) > (double)dim * 1.4901161193847656e-08) *slow = 1;
+    }
+    *flag = f;
+    *prox = p;
+}
+
+}  // namespace
+
+struct HybDenseWsos {
+    int64_t U = 0, ldU = 0;
+    int nPs = 0;
+    double nu = 0.0;
+    std::vector<int64_t> L, ldL;
+    std::vector<double*> P, Pt, F, Ft, Lam, M1, LU;  // per k
+    std::vector<HybChol> chLam;
+    double *PD = nullptr;                             // U x Lmax scratch
+    double *H = nullptr, *Hf = nullptr, *Lh = nullptr, *UU = nullptr;
+    HybChol chH;
+    double *v1 = nullptr, *v2 = nullptr, *v3 = nullptr, *scal = nullptr;
+    int *dual_ok = nullptr, *slow = nullptr, *sqrt_ok = nullptr;
+    const int** lam_infos_dev = nullptr;
+    double *big1 = nullptr, *big2 = nullptr;
+    int64_t big_cols = 0;
+    double* gemv_scratch = nullptr;
+};
+
+static int wsos_ensure_big(HybDenseWsos* c, int64_t m) {
+    if (m <= c->big_cols) return 0;
+    cudaFree(c->big1);
+    cudaFree(c->big2);
+    c->big1 = c->big2 = nullptr;
+    HYB_CUDA(cudaMalloc(&c->big1, sizeof(double) * c->ldU * m));
+    HYB_CUDA(cudaMalloc(&c->big2, sizeof(double) * c->ldU * m));
+    c->big_cols = m;
+    return 0;
+}
+
+int hybd_wsos_create(HybDenseWsos** out, int64_t U, int nPs, const double* const* Ps_host, const int64_t* Ls) {
+    HybDenseWsos* c = new HybDenseWsos();
+    c->U = U;
+    c->ldU = hyb_round_up(U, 16);
+    c->nPs = nPs;
+    int64_t Lmax = 1;
+    c->chLam.resize(nPs);
+    for (int k = 0; k < nPs; ++k) {
+        const int64_t L = Ls[k], ldL = hyb_round_up(L, 16);
+        c->L.push_back(L);
+        c->ldL.push_back(ldL);
+        c->nu += (double)L;
+        Lmax = L > Lmax ? L : Lmax;
+        double *P = nullptr, *Pt = nullptr, *F = nullptr, *Ft = nullptr, *Lam = nullptr, *M1 = nullptr, *LU = nullptr;
+        HYB_CUDA(cudaMalloc(&P, sizeof(double) * c->ldU * L));
+        HYB_CUDA(cudaMemset(P, 0, sizeof(double) * c->ldU * L));
+        HYB_CUDA(cudaMemcpy2D(P, sizeof(double) * c->ldU, Ps_host[k], sizeof(double) * U, sizeof(double) * U, L,
+                              cudaMemcpyHostToDevice));
+        HYB_CUDA(cudaMalloc(&Pt, sizeof(double) * ldL * U));
+        HYB_CUDA(cudaMemset(Pt, 0, sizeof(double) * ldL * U));
+        HYB_CHECK(hyb_transpose(nullptr, P, c->ldU, U, L, Pt, ldL, 0));
+        HYB_CUDA(cudaMalloc(&F, sizeof(double) * ldL * U));
+        HYB_CUDA(cudaMemset(F, 0, sizeof(double) * ldL * U));
+        HYB_CUDA(cudaMalloc(&LU, sizeof(double) * ldL * U));
+        HYB_CUDA(cudaMalloc(&Ft, sizeof(double) * c->ldU * L));
+        HYB_CUDA(cudaMemset(Ft, 0, sizeof(double) * c->ldU * L));
+        HYB_CUDA(cudaMalloc(&Lam, sizeof(double) * ldL * L));
+        HYB_CUDA(cudaMemset(Lam, 0, sizeof(double) * ldL * L));
+        HYB_CUDA(cudaMalloc(&M1, sizeof(double) * ldL * L));
+        c->P.push_back(P);
+        c->Pt.push_back(Pt);
+        c->F.push_back(F);
+        c->Ft.push_back(Ft);
+        c->Lam.push_back(Lam);
+        c->M1.push_back(M1);
+        c->LU.push_back(LU);
+        HYB_CHECK(hyb_chol_attach(c->chLam[k], Lam, ldL, L));
+    }
+    HYB_CUDA(cudaMalloc(&c->PD, sizeof(double) * c->ldU * Lmax));
+    const size_t ub = sizeof(double) * c->ldU * U;
+    double** mats[] = {&c->H, &c->Hf, &c->Lh, &c->UU};
+    for (double** m : mats) {
+        HYB_CUDA(cudaMalloc(m, ub));
+        HYB_CUDA(cudaMemset(*m, 0, ub));
+    }
+    HYB_CHECK(hyb_chol_attach(c->chH, c->Hf, c->ldU, U));
+    HYB_CUDA(cudaMalloc(&c->v1, sizeof(double) * c->ldU));
+    HYB_CUDA(cudaMalloc(&c->v2, sizeof(double) * c->ldU));
+    HYB_CUDA(cudaMalloc(&c->v3, sizeof(double) * c->ldU));
+    HYB_CUDA(cudaMalloc(&c->scal, sizeof(double) * 8));
+    HYB_CUDA(cudaMemset(c->scal, 0, sizeof(double) * 8));
+    HYB_CUDA(cudaMalloc(&c->dual_ok, sizeof(int)));
+    HYB_CUDA(cudaMalloc(&c->slow, sizeof(int)));
+    HYB_CUDA(cudaMalloc(&c->sqrt_ok, sizeof(int)));
+    HYB_CUDA(cudaMemset(c->slow, 0, sizeof(int)));
+    HYB_CUDA(cudaMemset(c->sqrt_ok, 0, sizeof(int)));
+    std::vector<const int*> infos;
+    for (int k = 0; k < nPs; ++k) infos.push_back(c->chLam[k].info);
+    HYB_CUDA(cudaMalloc((void**)&c->lam_infos_dev, sizeof(int*) * (nPs > 0 ? nPs : 1)));
+    HYB_CUDA(cudaMemcpy((void*)c->lam_infos_dev, infos.data(), sizeof(int*) * nPs, cudaMemcpyHostToDevice));
+    HYB_CUDA(cudaMalloc(&c->gemv_scratch, sizeof(double) * U * HYB_GEMV_SPLITS));
+    HYB_CUDA(cudaDeviceSynchronize());
+    *out = c;
+    return 0;
+}
+
+void hybd_wsos_destroy(HybDenseWsos* c) {
+    if (!c) return;
+    for (int k = 0; k < c->nPs; ++k) {
+        hyb_chol_free(c->chLam[k]);
+        cudaFree(c->P[k]);
+        cudaFree(c->Pt[k]);
+        cudaFree(c->F[k]);
+        cudaFree(c->Ft[k]);
+        cudaFree(c->Lam[k]);
+        cudaFree(c->M1[k]);
+        cudaFree(c->LU[k]);
+    }
+    hyb_chol_free(c->chH);
+    cudaFree(c->PD);
+    cudaFree(c->H);
+    cudaFree(c->Hf);
+    cudaFree(c->Lh);
+    cudaFree(c->UU);
+    cudaFree(c->v1);
+    cudaFree(c->v2);
+    cudaFree(c->v3);
+    cudaFree(c->scal);
+    cudaFree(c->dual_ok);
+    cudaFree(c->slow);
+    cudaFree(c->sqrt_ok);
+    cudaFree((void*)c->lam_infos_dev);
+    cudaFree(c->big1);
+    cudaFree(c->big2);
+    cudaFree(c->gemv_scratch);
+    delete c;
+}
+
+// LU_k = (F_k diag(d) F_k') F_k   (partial_lambda!, wsosinterpnonnegative.jl:206-211), d a device U-vector
+static int wsos_partial_lambda(cudaStream_t st, HybDenseWsos* c, int k, const double* d) {
+    const int64_t U = c->U, L = c->L[k], ldU = c->ldU, ldL = c->ldL[k];
+    rowscale_kernel<<<nb1(U * L), 256, 0, st>>>(c->Ft[k], d, U, L, ldU, c->PD);
+    DLAUNCHED();
+    HYB_CUDA(cudaGetLastError());
+    HYB_CHECK(hyb_gemm_tn(st, L, L, U, 1.0, c->Ft[k], ldU, c->PD, ldU, 0.0, c->M1[k], ldL, 0));
+    HYB_CHECK(hyb_gemm_tn(st, L, U, L, 1.0, c->M1[k], ldL, c->F[k], ldL, 0.0, c->LU[k], ldL, 0));
+    return 0;
+}
+
+int hybd_wsos_update(cudaStream_t st, HybDenseWsos* c, const double* primal, const double* dual_in, double scal,
+                     double irtmu, double* point, double* dual_out, double* grad, int* flag, double* prox) {
+    const int64_t U = c->U, ldU = c->ldU;
+    lincomb_kernel<<<nb1(U), 256, 0, st>>>(U, scal, primal, 0.0, nullptr, point);
+    lincomb_kernel<<<nb1(U), 256, 0, st>>>(U, 1.0, dual_in, 0.0, nullptr, dual_out);
+    lincomb_kernel<<<nb1(U), 256, 0, st>>>(U, 1.0, point, 0.0, nullptr, c->v3);  // aligned copy of the point
+    all_gt_eps_kernel<<<1, 1024, 0, st>>>(U, dual_out, c->dual_ok);
+    g_dense_launches += 4;
+    HYB_CUDA(cudaGetLastError());
+    for (int k = 0; k < c->nPs; ++k) {
+        const int64_t L = c->L[k], ldL = c->ldL[k];
+        // Lambda_k = P_k' diag(s) P_k, upper, Cholesky
+        rowscale_kernel<<<nb1(U * L), 256, 0, st>>>(c->P[k], c->v3, U, L, ldU, c->PD);
+        DLAUNCHED();
+        HYB_CHECK(hyb_gemm_tn(st, L, L, U, 1.0, c->P[k], ldU, c->PD, ldU, 0.0, c->Lam[k], ldL, HYB_GEMM_UPPER));
+        HYB_CHECK(hyb_potrf(st, c->chLam[k], nullptr));
+        // F_k = R_k^-T P_k'
+        copy_mat_kernel<<<nb1(L * U), 256, 0, st>>>(c->Pt[k], ldL, c->F[k], ldL, L, U);
+        DLAUNCHED();
+        HYB_CHECK(hyb_trsm_fwd(st, c->Lam[k], ldL, L, c->F[k], ldL, U));
+        HYB_CHECK(hyb_transpose(st, c->F[k], ldL, L, U, c->Ft[k], ldU, 0));
+        // grad_j -= |F_k[:, j]|^2
+        coldot_kernel<<<nb1(U, 8), 256, 0, st>>>(c->F[k], c->F[k], L, U, ldL, -1.0, k == 0 ? 0.0 : 1.0, grad);
+        DLAUNCHED();
+        // H (+)= (F_k' F_k) .^ 2
+        HYB_CHECK(hyb_gemm_tn(st, U, U, L, 1.0, c->F[k], ldL, c->F[k], ldL, 0.0, c->UU, ldU, HYB_GEMM_UPPER));
+        sq_accum_kernel<<<nb1(U * U), 256, 0, st>>>(c->UU, c->H, U, ldU, k == 0);
+        DLAUNCHED();
+        HYB_CUDA(cudaGetLastError());
+    }
+    symmetrize_kernel<<<nb1(U * U), 256, 0, st>>>(c->H, U, ldU);
+    copy_upper_dense_kernel<<<nb1(U * U), 256, 0, st>>>(c->H, c->Hf, U, ldU);
+    g_dense_launches += 2;
+    HYB_CHECK(hyb_potrf(st, c->chH, nullptr));
+    HYB_CHECK(hyb_transpose(st, c->Hf, ldU, U, U, c->Lh, ldU, 1));
+    // scalars for check_numerics / proxsqr / hess_prod_slow switch
+    lincomb_kernel<<<nb1(U), 256, 0, st>>>(U, 1.0, grad, 0.0, nullptr, c->v1);
+    dot_kernel<<<1, 1024, 0, st>>>(U, c->v1, c->v3, c->scal + 0);
+    HYB_CHECK(hyb_potrs(st, c->chH, c->v1));  // Hinv g
+    lincomb_kernel<<<nb1(U), 256, 0, st>>>(U, 1.0, grad, 0.0, nullptr, c->v2);
+    dot_kernel<<<1, 1024, 0, st>>>(U, c->v1, c->v2, c->scal + 1);
+    lincomb_kernel<<<nb1(U), 256, 0, st>>>(U, irtmu, dual_out, 1.0, grad, c->v2);  // psi
+    lincomb_kernel<<<nb1(U), 256, 0, st>>>(U, 1.0, c->v2, 0.0, nullptr, c->v1);
+    HYB_CHECK(hyb_potrs(st, c->chH, c->v1));
+    dot_kernel<<<1, 1024, 0, st>>>(U, c->v1, c->v2, c->scal + 2);
+    HYB_CHECK(hyb_gemv_t(st, U, U, c->H, ldU, c->v3, c->v1));  // H p (H symmetric)
+    dot_kernel<<<1, 1024, 0, st>>>(U, c->v1, c->v3, c->scal + 3);
+    wsos_finalize_kernel<<<1, 1, 0, st>>>(c->lam_infos_dev, c->nPs, c->chH.info, c->dual_ok, c->scal, c->nu, U, flag, prox,
+                                          c->slow, c->sqrt_ok);
+    g_dense_launches += 10;
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int hybd_wsos_sqrt_ok(cudaStream_t st, HybDenseWsos* c, int* ok) {
+    HYB_CUDA(cudaMemcpyAsync(ok, c->sqrt_ok, sizeof(int), cudaMemcpyDeviceToHost, st));
+    HYB_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int hybd_wsos_prod(cudaStream_t st, HybDenseWsos* c, int op, const double* arr, int64_t lda, double* prod, int64_t ldp,
+                   int64_t m) {
+    if (m <= 0) return 0;
+    const int64_t U = c->U, ldU = c->ldU;
+    HYB_CHECK(wsos_ensure_big(c, m));
+    double *A = c->big1, *B = c->big2;
+    // aligned working copy of the input block (the cone's rows may start at an odd offset)
+    copy_mat_kernel<<<nb1(U * m), 256, 0, st>>>(arr, lda, A, ldU, U, m);
+    DLAUNCHED();
+    HYB_CUDA(cudaGetLastError());
+    const double* result = nullptr;
+    if (op == 6) {
+        int slow = 0;
+        HYB_CUDA(cudaMemcpyAsync(&slow, c->slow, sizeof(int), cudaMemcpyDeviceToHost, st));
+        HYB_CUDA(cudaStreamSynchronize(st));
+        if (!slow) op = HYB_OP_HESS;
+    }
+    if (op == HYB_OP_HESS) {
+        if (m == 1) HYB_CHECK(hyb_gemv_t(st, U, U, c->H, ldU, A, B));
+        else HYB_CHECK(hyb_gemm_tn(st, U, m, U, 1.0, c->H, ldU, A, ldU, 0.0, B, ldU, 0));
+        result = B;
+    } else if (op == HYB_OP_INV_HESS) {
+        if (m == 1) {
+            HYB_CHECK(hyb_potrs(st, c->chH, A));
+        } else {
+            HYB_CHECK(hyb_trsm_fwd(st, c->Hf, ldU, U, A, ldU, m));
+            HYB_CHECK(hyb_trsm_bwd(st, c->Hf, c->Lh, ldU, U, A, ldU, m));
+        }
+        result = A;
+    } else if (op == HYB_OP_SQRT_HESS) {  // chol(H).U * arr = Lh' arr
+        if (m == 1) HYB_CHECK(hyb_gemv_t(st, U, U, c->Lh, ldU, A, B));
+        else HYB_CHECK(hyb_gemm_tn(st, U, m, U, 1.0, c->Lh, ldU, A, ldU, 0.0, B, ldU, 0));
+        result = B;
+    } else if (op == HYB_OP_INV_SQRT_HESS) {  // chol(H).U' \ arr
+        HYB_CHECK(hyb_trsm_fwd(st, c->Hf, ldU, U, A, ldU, m));
+        result = A;
+    } else {  // hess_prod_slow!, factor-based (wsosinterpnonnegative.jl:168-191), column by column
+        for (int64_t j = 0; j < m; ++j) {
+            for (int k = 0; k < c->nPs; ++k) {
+                HYB_CHECK(wsos_partial_lambda(st, c, k, A + j * ldU));
+                coldot_kernel<<<nb1(U, 8), 256, 0, st>>>(c->F[k], c->LU[k], c->L[k], U, c->ldL[k], 1.0, k == 0 ? 0.0 : 1.0,
+                                                        B + j * ldU);
+                DLAUNCHED();
+                HYB_CUDA(cudaGetLastError());
+            }
+        }
+        result = B;
+    }
+    copy_mat_kernel<<<nb1(U * m), 256, 0, st>>>(result, ldU, prod, ldp, U, m);
+    DLAUNCHED();
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int hybd_wsos_dder3(cudaStream_t st, HybDenseWsos* c, const double* dir, double* out) {
+    const int64_t U = c->U;
+    lincomb_kernel<<<nb1(U), 256, 0, st>>>(U, 1.0, dir, 0.0, nullptr, c->v1);
+    DLAUNCHED();
+    for (int k = 0; k < c->nPs; ++k) {
+        HYB_CHECK(wsos_partial_lambda(st, c, k, c->v1));
+        coldot_kernel<<<nb1(U, 8), 256, 0, st>>>(c->LU[k], c->LU[k], c->L[k], U, c->ldL[k], 1.0, k == 0 ? 0.0 : 1.0, c->v2);
+        DLAUNCHED();
+        HYB_CUDA(cudaGetLastError());
+    }
+    lincomb_kernel<<<nb1(U), 256, 0, st>>>(U, 1.0, c->v2, 0.0, nullptr, out);
+    DLAUNCHED();
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}

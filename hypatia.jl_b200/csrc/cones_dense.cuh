@@ -15,3 +15,15 @@ int hybd_psd_prod(cudaStream_t st, HybDensePsd* c, int op, const double* arr, in
                   int64_t m);
 int hybd_psd_dder3(cudaStream_t st, HybDensePsd* c, const double* dir, double* out);
 int64_t hybd_launch_count();
+
+struct HybDenseWsos;  // WSOSInterpNonnegative (wsosinterpnonnegative.jl), real case
+int hybd_wsos_create(HybDenseWsos** out, int64_t U, int nPs, const double* const* Ps_host, const int64_t* Ls);
+void hybd_wsos_destroy(HybDenseWsos* c);
+int hybd_wsos_update(cudaStream_t st, HybDenseWsos* c, const double* primal, const double* dual_in, double scal,
+                     double irtmu, double* point, double* dual_out, double* grad, int* flag, double* prox);
+// op: HYB_OP_* or 6 = hess_prod_slow
+int hybd_wsos_prod(cudaStream_t st, HybDenseWsos* c, int op, const double* arr, int64_t lda, double* prod, int64_t ldp,
+                   int64_t m);
+int hybd_wsos_dder3(cudaStream_t st, HybDenseWsos* c, const double* dir, double* out);
+// 1 if chol(H) of the loaded point succeeded (sqrt oracles usable, Cones.jl:193-199); synchronizes
+int hybd_wsos_sqrt_ok(cudaStream_t st, HybDenseWsos* c, int* ok);

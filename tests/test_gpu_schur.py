@@ -85,7 +85,8 @@ def solve_both(model_fn, **kw):
 
 GPU_KNOWN = ["dimension1", "primalinfeas1", "primalinfeas2", "dualinfeas2", "dualinfeas3", "nonnegative4",
              "possemideftri1", "possemideftri2", "possemideftri8", "possemideftri9", "epinormeucl1", "epinormeucl2",
-             "epinormeucl3", "epipersquare1", "epipersquare2", "epipersquare3", "epipersquare4"]
+             "epinormeucl3", "epipersquare1", "epipersquare2", "epipersquare3", "epipersquare4",
+             "wsosinterpnonnegative1", "wsosinterpnonnegative2", "wsosinterpnonnegative3"]
 
 
 @pytest.mark.parametrize("name", GPU_KNOWN)
@@ -154,6 +155,14 @@ def test_nearestpsd_large_psd_cone():
     n_early = max(3, len(cpu.trace) // 2)
     _, bad_early = traj_deviation(gpu.trace[:n_early], cpu.trace[:n_early])
     assert bad_early is None, bad_early
+
+
+def test_polymin_wsos_small():
+    """cfg3-shaped: polymin dual form, WSOSInterpNonnegative cone (n = 2, halfdeg = 4)."""
+    gpu, cpu = solve_both(lambda: instances.polymin(n=2, halfdeg=4, seed=1))
+    assert gpu.status == cpu.status == "Optimal"
+    assert abs(gpu.num_iters - cpu.num_iters) <= 1
+    assert abs(gpu.primal_obj - cpu.primal_obj) <= 1e-7 * (1 + abs(cpu.primal_obj))
 
 
 def test_modify_and_resolve_on_gpu():
