@@ -397,9 +397,12 @@ int hyb_schur_assemble(hyb_ctx* c, double* t_assemble_ms) {
         std::vector<char> sqrt_mask(cs.blocks.size(), 1);
         bool all_sqrt = true;
         for (size_t bi = 0; bi < cs.blocks.size(); ++bi) {
-            if (cs.blocks[bi].type == HYB_WSOSINTERPNONNEGATIVE) {
+            if (cs.blocks[bi].type == HYB_WSOSINTERPNONNEGATIVE || cs.blocks[bi].type == HYB_WSOSINTERPPOSSEMIDEFTRI) {
                 int ok = 0;
-                HYB_CHECK(hybd_wsos_sqrt_ok(c->st, (HybDenseWsos*)cs.blocks[bi].dense, &ok));
+                if (cs.blocks[bi].type == HYB_WSOSINTERPNONNEGATIVE)
+                    HYB_CHECK(hybd_wsos_sqrt_ok(c->st, (HybDenseWsos*)cs.blocks[bi].dense, &ok));
+                else
+                    HYB_CHECK(hybd_wsospsd_sqrt_ok(c->st, (HybDenseWsosPsd*)cs.blocks[bi].dense, &ok));
                 sqrt_mask[bi] = (char)ok;
                 all_sqrt = all_sqrt && ok;
             }

@@ -691,6 +691,10 @@ int hybi_cones_alloc(HybCones& cs) {
             HybDenseWsos* d = nullptr;
             HYB_CHECK(hybd_wsos_create(&d, b.U, b.nPs, b.Ps, b.Ls));
             b.dense = d;
+        } else if (b.type == HYB_WSOSINTERPPOSSEMIDEFTRI) {
+            HybDenseWsosPsd* d = nullptr;
+            HYB_CHECK(hybd_wsospsd_create(&d, b.side, b.U, b.nPs, b.Ps, b.Ls));
+            b.dense = d;
         } else if (b.type != HYB_NONNEGATIVE && b.type != HYB_EPINORMEUCL && b.type != HYB_EPIPERSQUARE) {
             hyb_set_error("cone type %d is not supported by the GPU path yet", b.type);
             return -2;
@@ -717,6 +721,7 @@ void hybi_cones_free(HybCones& cs) {
     for (auto& b : cs.blocks)
         if (b.dense) {
             if (b.type == HYB_WSOSINTERPNONNEGATIVE) hybd_wsos_destroy((HybDenseWsos*)b.dense);
+            else if (b.type == HYB_WSOSINTERPPOSSEMIDEFTRI) hybd_wsospsd_destroy((HybDenseWsosPsd*)b.dense);
             else hybd_psd_destroy((HybDensePsd*)b.dense);
             b.dense = nullptr;
         }
@@ -778,6 +783,11 @@ int hybi_cones_update(cudaStream_t st, HybCones& cs, const double* primal, const
                                            cs.point + b.offset, cs.dual + b.offset, cs.grad + b.offset,
                                            cs.item_flag + b.offset, cs.item_prox + b.offset));
                 break;
+            case HYB_WSOSINTERPPOSSEMIDEFTRI:
+                HYB_CHECK(hybd_wsospsd_update(st, (HybDenseWsosPsd*)b.dense, primal + b.offset, dual_in + b.offset, scal,
+                                              irtmu, cs.point + b.offset, cs.dual + b.offset, cs.grad + b.offset,
+                                              cs.item_flag + b.offset, cs.item_prox + b.offset));
+                break;
             default:
                 hyb_set_error("cone type %d unsupported", b.type);
                 return -2;
@@ -807,7 +817,8 @@ int hybi_cones_prod(cudaStream_t st, HybCones& cs, int which, const double* arr,
         int op;
         if (which == 4) op = b.use_dual ? HYB_OP_INV_HESS : HYB_OP_HESS;
         else if (which == 5) op = b.use_dual ? HYB_OP_INV_SQRT_HESS : HYB_OP_SQRT_HESS;
-        else if (which == 6) op = (b.type == HYB_WSOSINTERPNONNEGATIVE) ? 6 : HYB_OP_HESS;  // Cones.jl:229-231
+        else if (which == 6)  // hess_prod_slow! is hess_prod! except for the WSOS cones (Cones.jl:229-231)
+            op = (b.type == HYB_WSOSINTERPNONNEGATIVE || b.type == HYB_WSOSINTERPPOSSEMIDEFTRI) ? 6 : HYB_OP_HESS;
         else op = which;
         const int64_t rows = b.count * b.dim;
         switch (b.type) {
@@ -843,6 +854,9 @@ int hybi_cones_prod(cudaStream_t st, HybCones& cs, int which, const double* arr,
                 break;
             case HYB_WSOSINTERPNONNEGATIVE:
                 HYB_CHECK(hybd_wsos_prod(st, (HybDenseWsos*)b.dense, op, arr + b.offset, lda, prod + b.offset, ldp, m));
+                break;
+            case HYB_WSOSINTERPPOSSEMIDEFTRI:
+                HYB_CHECK(hybd_wsospsd_prod(st, (HybDenseWsosPsd*)b.dense, op, arr + b.offset, lda, prod + b.offset, ldp, m));
                 break;
             default:
                 hyb_set_error("cone type %d unsupported", b.type);
@@ -887,6 +901,9 @@ int hybi_cones_dder3(cudaStream_t st, HybCones& cs, const double* dir, double* o
                 break;
             case HYB_WSOSINTERPNONNEGATIVE:
                 HYB_CHECK(hybd_wsos_dder3(st, (HybDenseWsos*)b.dense, dir + b.offset, out + b.offset));
+                break;
+            case HYB_WSOSINTERPPOSSEMIDEFTRI:
+                HYB_CHECK(hybd_wsospsd_dder3(st, (HybDenseWsosPsd*)b.dense, dir + b.offset, out + b.offset));
                 break;
             default:
                 hyb_set_error("cone type %d unsupported", b.type);

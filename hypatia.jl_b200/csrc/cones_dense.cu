@@ -693,3 +693,381 @@ int hybd_wsos_dder3(cudaStream_t st, HybDenseWsos* c, const double* dir, double*
     HYB_CUDA(cudaGetLastError());
     return 0;
 }
+
+// =======================================================================================
+// WSOSInterpPosSemidefTri: src/Cones/wsosinterppossemideftri.jl
+//   point = R(R+1)/2 blocks of length U in svec order of (p, q), p >= q (off-diagonal blocks
+//   carry the sqrt2 scaling)                                                 :63-123
+//   update_feas :125-158   Lambda_k (RL x RL) block (p,q) = P_k' diag(s_pq) P_k, Cholesky
+//   is_dual_feas :160-169  diagonal blocks of the dual point > eps
+//   update_grad :171-220   F_k = C_k^-T kron(I_R, P_k')  (Lambda_k = C_k' C_k), block_diag_prod!
+//   update_hess :222-270   block Hadamard products of PLiP = F_k' F_k
+//   hess_prod_slow! / dder3 = partial_prod! :272-358 ; block_diag_prod! :289-312
+//   generic Hessian-based products and the slow switch as for WSOSInterpNonnegative
+// =======================================================================================
+namespace {
+
+__device__ __forceinline__ void blk_pq(int b, int& p, int& q) {
+    int pp = (int)((sqrt(8.0 * b + 1.0) - 1.0) * 0.5);
+    while (pp * (pp + 1) / 2 > b) --pp;
+    while ((pp + 1) * (pp + 2) / 2 <= b) ++pp;
+    p = pp;
+    q = b - pp * (pp + 1) / 2;
+}
+
+// out[r, c] = fac * d[r] * in[r, c]
+__global__ void rowscale_fac_kernel(const double* __restrict__ in, const double* __restrict__ d, double fac, int64_t rows,
+                                    int64_t cols, int64_t ld, double* __restrict__ out) {
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= rows * cols) return;
+    const int64_t r = e % rows, c = e / rows;
+    out[r + c * ld] = fac * d[r] * in[r + c * ld];
+}
+
+// block_diag_prod! (wsosinterppossemideftri.jl:289-312): one warp per (block (j,i), u):
+// out[blk(j,i) * U + u] = beta * out + alpha * scale_ij * <M1[:, i*U+u], M2[:, j*U+u]>
+__global__ void blockdiag_dot_kernel(const double* __restrict__ M1, const double* __restrict__ M2, int64_t rows, int64_t U,
+                                     int R, int64_t ld, double alpha, double beta, double* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int64_t item = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int nblk = R * (R + 1) / 2;
+    if (item >= (int64_t)nblk * U) return;
+    const int b = (int)(item / U);
+    const int64_t u = item % U;
+    int j, i;
+    blk_pq(b, j, i);  // j >= i
+    const double* a = M1 + ((int64_t)i * U + u) * ld;
+    const double* bb = M2 + ((int64_t)j * U + u) * ld;
+    double s = 0.0;
+    for (int64_t r = lane; r < rows; r += 32) s += a[r] * bb[r];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) {
+        const double v = alpha * ((i != j) ? RT2 : 1.0) * s;
+        out[(int64_t)b * U + u] = (beta == 0.0 ? 0.0 : beta * out[(int64_t)b * U + u]) + v;
+    }
+}
+
+// update_hess (wsosinterppossemideftri.jl:245-266): H[block, block2] (+)= PLP[p,p2] .* PLP[q,q2] * scal
+//   (+ PLP[p,q2] .* PLP[q,p2] when both blocks are off-diagonal), for block2 >= block
+__global__ void wsospsd_hess_kernel(const double* __restrict__ PLP, int64_t ldP, int64_t U, int R, double* __restrict__ H,
+                                    int64_t ldH, int first) {
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int block = blockIdx.y, block2 = blockIdx.z;
+    if (e >= U * U || block2 < block) return;
+    const int64_t i = e % U, j = e / U;
+    int p, q, p2, q2;
+    blk_pq(block, p, q);
+    blk_pq(block2, p2, q2);
+    const double scal = ((p == q) != (p2 == q2)) ? RT2 : 1.0;
+    auto el = [&](int a, int b) { return PLP[(int64_t)a * U + i + ((int64_t)b * U + j) * ldP]; };
+    double v = el(p, p2) * el(q, q2) * scal;
+    if (p != q && p2 != q2) v += el(p, q2) * el(q, p2);
+    double* h = H + (int64_t)block * U + i + ((int64_t)block2 * U + j) * ldH;
+    *h = (first ? 0.0 : *h) + v;
+}
+
+// dual feasibility: the diagonal blocks of the dual point are positive
+__global__ void __launch_bounds__(1024) wsospsd_dualfeas_kernel(const double* __restrict__ z, int64_t U, int R, int* out) {
+    __shared__ int ok;
+    if (threadIdx.x == 0) ok = 1;
+    __syncthreads();
+    int mine = 1;
+    for (int p = 0; p < R; ++p) {
+        const int64_t base = (int64_t)(p * (p + 1) / 2 + p) * U;
+        for (int64_t i = threadIdx.x; i < U; i += 1024)
+            if (!(z[base + i] > HYB_EPS)) mine = 0;
+    }
+    if (!mine) ok = 0;
+    __syncthreads();
+    if (threadIdx.x == 0) *out = ok;
+}
+
+}  // namespace
+
+struct HybDenseWsosPsd {
+    int R = 1;
+    int64_t U = 0, dim = 0, ldD = 0, ldU = 0, RU = 0, ldRU = 0;
+    int nPs = 0;
+    double nu = 0.0;
+    std::vector<int64_t> L, RL, ldRL;
+    std::vector<double*> P, Pt, F, Lam, M, Mt, LRUR;  // per k
+    std::vector<HybChol> chLam;
+    double *PD = nullptr, *PLP = nullptr;
+    double *H = nullptr, *Hf = nullptr, *Lh = nullptr;
+    HybChol chH;
+    double *v1 = nullptr, *v2 = nullptr, *v3 = nullptr, *scal = nullptr;
+    int *dual_ok = nullptr, *slow = nullptr, *sqrt_ok = nullptr;
+    const int** lam_infos_dev = nullptr;
+    double *big1 = nullptr, *big2 = nullptr;
+    int64_t big_cols = 0;
+};
+
+int hybd_wsospsd_create(HybDenseWsosPsd** out, int R, int64_t U, int nPs, const double* const* Ps_host,
+                        const int64_t* Ls) {
+    HybDenseWsosPsd* c = new HybDenseWsosPsd();
+    c->R = R;
+    c->U = U;
+    c->ldU = hyb_round_up(U, 16);
+    c->dim = U * (R * (R + 1) / 2);
+    c->ldD = hyb_round_up(c->dim, 16);
+    c->RU = (int64_t)R * U;
+    c->ldRU = hyb_round_up(c->RU, 16);
+    c->nPs = nPs;
+    c->chLam.resize(nPs);
+    int64_t Lmax = 1;
+    for (int k = 0; k < nPs; ++k) {
+        const int64_t L = Ls[k], RL = (int64_t)R * L, ldRL = hyb_round_up(RL, 16), ldL = hyb_round_up(L, 16);
+        c->L.push_back(L);
+        c->RL.push_back(RL);
+        c->ldRL.push_back(ldRL);
+        c->nu += (double)RL;
+        Lmax = L > Lmax ? L : Lmax;
+        double *P = nullptr, *Pt = nullptr, *F = nullptr, *Lam = nullptr, *M = nullptr, *Mt = nullptr, *LRUR = nullptr;
+        HYB_CUDA(cudaMalloc(&P, sizeof(double) * c->ldU * L));
+        HYB_CUDA(cudaMemset(P, 0, sizeof(double) * c->ldU * L));
+        HYB_CUDA(cudaMemcpy2D(P, sizeof(double) * c->ldU, Ps_host[k], sizeof(double) * U, sizeof(double) * U, L,
+                              cudaMemcpyHostToDevice));
+        HYB_CUDA(cudaMalloc(&Pt, sizeof(double) * ldL * U));
+        HYB_CUDA(cudaMemset(Pt, 0, sizeof(double) * ldL * U));
+        HYB_CHECK(hyb_transpose(nullptr, P, c->ldU, U, L, Pt, ldL, 0));
+        HYB_CUDA(cudaMalloc(&F, sizeof(double) * ldRL * c->RU));
+        HYB_CUDA(cudaMalloc(&LRUR, sizeof(double) * ldRL * c->RU));
+        HYB_CUDA(cudaMalloc(&Lam, sizeof(double) * ldRL * RL));
+        HYB_CUDA(cudaMemset(Lam, 0, sizeof(double) * ldRL * RL));
+        HYB_CUDA(cudaMalloc(&M, sizeof(double) * ldRL * RL));
+        HYB_CUDA(cudaMalloc(&Mt, sizeof(double) * ldRL * RL));
+        HYB_CUDA(cudaMemset(M, 0, sizeof(double) * ldRL * RL));
+        c->P.push_back(P);
+        c->Pt.push_back(Pt);
+        c->F.push_back(F);
+        c->Lam.push_back(Lam);
+        c->M.push_back(M);
+        c->Mt.push_back(Mt);
+        c->LRUR.push_back(LRUR);
+        HYB_CHECK(hyb_chol_attach(c->chLam[k], Lam, ldRL, RL));
+    }
+    HYB_CUDA(cudaMalloc(&c->PD, sizeof(double) * c->ldU * Lmax));
+    HYB_CUDA(cudaMalloc(&c->PLP, sizeof(double) * c->ldRU * c->RU));
+    const size_t hb = sizeof(double) * c->ldD * c->dim;
+    double** mats[] = {&c->H, &c->Hf, &c->Lh};
+    for (double** m : mats) {
+        HYB_CUDA(cudaMalloc(m, hb));
+        HYB_CUDA(cudaMemset(*m, 0, hb));
+    }
+    HYB_CHECK(hyb_chol_attach(c->chH, c->Hf, c->ldD, c->dim));
+    HYB_CUDA(cudaMalloc(&c->v1, sizeof(double) * c->ldD));
+    HYB_CUDA(cudaMalloc(&c->v2, sizeof(double) * c->ldD));
+    HYB_CUDA(cudaMalloc(&c->v3, sizeof(double) * c->ldD));
+    HYB_CUDA(cudaMalloc(&c->scal, sizeof(double) * 8));
+    HYB_CUDA(cudaMemset(c->scal, 0, sizeof(double) * 8));
+    HYB_CUDA(cudaMalloc(&c->dual_ok, sizeof(int)));
+    HYB_CUDA(cudaMalloc(&c->slow, sizeof(int)));
+    HYB_CUDA(cudaMalloc(&c->sqrt_ok, sizeof(int)));
+    HYB_CUDA(cudaMemset(c->slow, 0, sizeof(int)));
+    HYB_CUDA(cudaMemset(c->sqrt_ok, 0, sizeof(int)));
+    std::vector<const int*> infos;
+    for (int k = 0; k < nPs; ++k) infos.push_back(c->chLam[k].info);
+    HYB_CUDA(cudaMalloc((void**)&c->lam_infos_dev, sizeof(int*) * (nPs > 0 ? nPs : 1)));
+    HYB_CUDA(cudaMemcpy((void*)c->lam_infos_dev, infos.data(), sizeof(int*) * nPs, cudaMemcpyHostToDevice));
+    HYB_CUDA(cudaDeviceSynchronize());
+    *out = c;
+    return 0;
+}
+
+void hybd_wsospsd_destroy(HybDenseWsosPsd* c) {
+    if (!c) return;
+    for (int k = 0; k < c->nPs; ++k) {
+        hyb_chol_free(c->chLam[k]);
+        cudaFree(c->P[k]);
+        cudaFree(c->Pt[k]);
+        cudaFree(c->F[k]);
+        cudaFree(c->Lam[k]);
+        cudaFree(c->M[k]);
+        cudaFree(c->Mt[k]);
+        cudaFree(c->LRUR[k]);
+    }
+    hyb_chol_free(c->chH);
+    cudaFree(c->PD);
+    cudaFree(c->PLP);
+    cudaFree(c->H);
+    cudaFree(c->Hf);
+    cudaFree(c->Lh);
+    cudaFree(c->v1);
+    cudaFree(c->v2);
+    cudaFree(c->v3);
+    cudaFree(c->scal);
+    cudaFree(c->dual_ok);
+    cudaFree(c->slow);
+    cudaFree(c->sqrt_ok);
+    cudaFree((void*)c->lam_infos_dev);
+    cudaFree(c->big1);
+    cudaFree(c->big2);
+    delete c;
+}
+
+// dst (RL x RL, upper blocks then symmetrized if asked) : block (q,p), q <= p, = P_k' diag(vec_pq') P_k
+static int wsospsd_build_lambda(cudaStream_t st, HybDenseWsosPsd* c, int k, const double* vec, double* dst, bool full) {
+    const int64_t U = c->U, L = c->L[k], ldU = c->ldU, ldRL = c->ldRL[k];
+    for (int p = 0; p < c->R; ++p)
+        for (int q = 0; q <= p; ++q) {
+            const double* d = vec + (int64_t)(p * (p + 1) / 2 + q) * U;
+            rowscale_fac_kernel<<<nb1(U * L), 256, 0, st>>>(c->P[k], d, (p != q) ? 1.0 / RT2 : 1.0, U, L, ldU, c->PD);
+            DLAUNCHED();
+            HYB_CUDA(cudaGetLastError());
+            HYB_CHECK(hyb_gemm_tn(st, L, L, U, 1.0, c->P[k], ldU, c->PD, ldU, 0.0, dst + (int64_t)q * L + (int64_t)p * L * ldRL,
+                                  ldRL, 0));
+        }
+    if (full) {
+        symmetrize_kernel<<<nb1(c->RL[k] * c->RL[k]), 256, 0, st>>>(dst, c->RL[k], ldRL);
+        DLAUNCHED();
+        HYB_CUDA(cudaGetLastError());
+    }
+    return 0;
+}
+
+int hybd_wsospsd_update(cudaStream_t st, HybDenseWsosPsd* c, const double* primal, const double* dual_in, double scal,
+                        double irtmu, double* point, double* dual_out, double* grad, int* flag, double* prox) {
+    const int64_t U = c->U, dim = c->dim, RU = c->RU, ldRU = c->ldRU, ldD = c->ldD;
+    const int R = c->R;
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, scal, primal, 0.0, nullptr, point);
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, dual_in, 0.0, nullptr, dual_out);
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, point, 0.0, nullptr, c->v3);
+    wsospsd_dualfeas_kernel<<<1, 1024, 0, st>>>(dual_out, U, R, c->dual_ok);
+    g_dense_launches += 4;
+    HYB_CUDA(cudaGetLastError());
+    for (int k = 0; k < c->nPs; ++k) {
+        const int64_t L = c->L[k], RL = c->RL[k], ldRL = c->ldRL[k], ldL = hyb_round_up(L, 16);
+        HYB_CHECK(wsospsd_build_lambda(st, c, k, c->v3, c->Lam[k], false));
+        HYB_CHECK(hyb_potrf(st, c->chLam[k], nullptr));
+        // F_k = C_k^-T kron(I_R, P_k')
+        HYB_CUDA(cudaMemsetAsync(c->F[k], 0, sizeof(double) * ldRL * RU, st));
+        for (int p = 0; p < R; ++p) {
+            copy_mat_kernel<<<nb1(L * U), 256, 0, st>>>(c->Pt[k], ldL, c->F[k] + (int64_t)p * L + (int64_t)p * U * ldRL, ldRL, L, U);
+            DLAUNCHED();
+        }
+        HYB_CUDA(cudaGetLastError());
+        HYB_CHECK(hyb_trsm_fwd(st, c->Lam[k], ldRL, RL, c->F[k], ldRL, RU));
+        // grad -= block_diag_prod(F, F)
+        blockdiag_dot_kernel<<<nb1((int64_t)(R * (R + 1) / 2) * U, 8), 256, 0, st>>>(c->F[k], c->F[k], RL, U, R, ldRL, -1.0,
+                                                                                     k == 0 ? 0.0 : 1.0, grad);
+        DLAUNCHED();
+        // PLiP = F' F (full symmetric), then the block Hadamard update of H
+        HYB_CHECK(hyb_gemm_tn(st, RU, RU, RL, 1.0, c->F[k], ldRL, c->F[k], ldRL, 0.0, c->PLP, ldRU, HYB_GEMM_UPPER));
+        symmetrize_kernel<<<nb1(RU * RU), 256, 0, st>>>(c->PLP, RU, ldRU);
+        const int nblk = R * (R + 1) / 2;
+        wsospsd_hess_kernel<<<dim3(nb1(U * U), nblk, nblk), 256, 0, st>>>(c->PLP, ldRU, U, R, c->H, ldD, k == 0);
+        g_dense_launches += 2;
+        HYB_CUDA(cudaGetLastError());
+    }
+    symmetrize_kernel<<<nb1(dim * dim), 256, 0, st>>>(c->H, dim, ldD);
+    copy_upper_dense_kernel<<<nb1(dim * dim), 256, 0, st>>>(c->H, c->Hf, dim, ldD);
+    g_dense_launches += 2;
+    HYB_CHECK(hyb_potrf(st, c->chH, nullptr));
+    HYB_CHECK(hyb_transpose(st, c->Hf, ldD, dim, dim, c->Lh, ldD, 1));
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, grad, 0.0, nullptr, c->v1);
+    dot_kernel<<<1, 1024, 0, st>>>(dim, c->v1, c->v3, c->scal + 0);
+    HYB_CHECK(hyb_potrs(st, c->chH, c->v1));
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, grad, 0.0, nullptr, c->v2);
+    dot_kernel<<<1, 1024, 0, st>>>(dim, c->v1, c->v2, c->scal + 1);
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, irtmu, dual_out, 1.0, grad, c->v2);
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, c->v2, 0.0, nullptr, c->v1);
+    HYB_CHECK(hyb_potrs(st, c->chH, c->v1));
+    dot_kernel<<<1, 1024, 0, st>>>(dim, c->v1, c->v2, c->scal + 2);
+    HYB_CHECK(hyb_gemv_t(st, dim, dim, c->H, ldD, c->v3, c->v1));
+    dot_kernel<<<1, 1024, 0, st>>>(dim, c->v1, c->v3, c->scal + 3);
+    wsos_finalize_kernel<<<1, 1, 0, st>>>(c->lam_infos_dev, c->nPs, c->chH.info, c->dual_ok, c->scal, c->nu, dim, flag, prox,
+                                          c->slow, c->sqrt_ok);
+    g_dense_launches += 10;
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int hybd_wsospsd_sqrt_ok(cudaStream_t st, HybDenseWsosPsd* c, int* ok) {
+    HYB_CUDA(cudaMemcpyAsync(ok, c->sqrt_ok, sizeof(int), cudaMemcpyDeviceToHost, st));
+    HYB_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+// partial_prod! (wsosinterppossemideftri.jl:314-358) for one direction d (aligned device dim-vector):
+// out (+)= block_diag_prod(left, LRUR) with LRUR = (C^-T Lambda(d) C^-1) F, left = LRUR (dder3) or F (slow product)
+static int wsospsd_partial_prod(cudaStream_t st, HybDenseWsosPsd* c, const double* d, bool symm, double* out) {
+    const int R = c->R;
+    const int64_t U = c->U, RU = c->RU;
+    for (int k = 0; k < c->nPs; ++k) {
+        const int64_t RL = c->RL[k], ldRL = c->ldRL[k];
+        HYB_CHECK(wsospsd_build_lambda(st, c, k, d, c->M[k], true));
+        HYB_CHECK(hyb_trsm_fwd(st, c->Lam[k], ldRL, RL, c->M[k], ldRL, RL));
+        HYB_CHECK(hyb_transpose(st, c->M[k], ldRL, RL, RL, c->Mt[k], ldRL, 0));
+        HYB_CHECK(hyb_trsm_fwd(st, c->Lam[k], ldRL, RL, c->Mt[k], ldRL, RL));
+        HYB_CHECK(hyb_gemm_tn(st, RL, RU, RL, 1.0, c->Mt[k], ldRL, c->F[k], ldRL, 0.0, c->LRUR[k], ldRL, 0));
+        blockdiag_dot_kernel<<<nb1((int64_t)(R * (R + 1) / 2) * U, 8), 256, 0, st>>>(
+            symm ? c->LRUR[k] : c->F[k], c->LRUR[k], RL, U, R, ldRL, 1.0, k == 0 ? 0.0 : 1.0, out);
+        DLAUNCHED();
+        HYB_CUDA(cudaGetLastError());
+    }
+    return 0;
+}
+
+int hybd_wsospsd_prod(cudaStream_t st, HybDenseWsosPsd* c, int op, const double* arr, int64_t lda, double* prod,
+                      int64_t ldp, int64_t m) {
+    if (m <= 0) return 0;
+    const int64_t dim = c->dim, ldD = c->ldD;
+    if (m > c->big_cols) {
+        cudaFree(c->big1);
+        cudaFree(c->big2);
+        c->big1 = c->big2 = nullptr;
+        HYB_CUDA(cudaMalloc(&c->big1, sizeof(double) * ldD * m));
+        HYB_CUDA(cudaMalloc(&c->big2, sizeof(double) * ldD * m));
+        c->big_cols = m;
+    }
+    double *A = c->big1, *B = c->big2;
+    copy_mat_kernel<<<nb1(dim * m), 256, 0, st>>>(arr, lda, A, ldD, dim, m);
+    DLAUNCHED();
+    HYB_CUDA(cudaGetLastError());
+    const double* result = nullptr;
+    if (op == 6) {
+        int slow = 0;
+        HYB_CUDA(cudaMemcpyAsync(&slow, c->slow, sizeof(int), cudaMemcpyDeviceToHost, st));
+        HYB_CUDA(cudaStreamSynchronize(st));
+        if (!slow) op = HYB_OP_HESS;
+    }
+    if (op == HYB_OP_HESS) {
+        if (m == 1) HYB_CHECK(hyb_gemv_t(st, dim, dim, c->H, ldD, A, B));
+        else HYB_CHECK(hyb_gemm_tn(st, dim, m, dim, 1.0, c->H, ldD, A, ldD, 0.0, B, ldD, 0));
+        result = B;
+    } else if (op == HYB_OP_INV_HESS) {
+        if (m == 1) {
+            HYB_CHECK(hyb_potrs(st, c->chH, A));
+        } else {
+            HYB_CHECK(hyb_trsm_fwd(st, c->Hf, ldD, dim, A, ldD, m));
+            HYB_CHECK(hyb_trsm_bwd(st, c->Hf, c->Lh, ldD, dim, A, ldD, m));
+        }
+        result = A;
+    } else if (op == HYB_OP_SQRT_HESS) {
+        if (m == 1) HYB_CHECK(hyb_gemv_t(st, dim, dim, c->Lh, ldD, A, B));
+        else HYB_CHECK(hyb_gemm_tn(st, dim, m, dim, 1.0, c->Lh, ldD, A, ldD, 0.0, B, ldD, 0));
+        result = B;
+    } else if (op == HYB_OP_INV_SQRT_HESS) {
+        HYB_CHECK(hyb_trsm_fwd(st, c->Hf, ldD, dim, A, ldD, m));
+        result = A;
+    } else {
+        for (int64_t j = 0; j < m; ++j) HYB_CHECK(wsospsd_partial_prod(st, c, A + j * ldD, false, B + j * ldD));
+        result = B;
+    }
+    copy_mat_kernel<<<nb1(dim * m), 256, 0, st>>>(result, ldD, prod, ldp, dim, m);
+    DLAUNCHED();
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int hybd_wsospsd_dder3(cudaStream_t st, HybDenseWsosPsd* c, const double* dir, double* out) {
+    const int64_t dim = c->dim;
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, dir, 0.0, nullptr, c->v1);
+    DLAUNCHED();
+    HYB_CHECK(wsospsd_partial_prod(st, c, c->v1, true, c->v2));
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, c->v2, 0.0, nullptr, out);
+    DLAUNCHED();
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}

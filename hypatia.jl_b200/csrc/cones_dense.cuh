@@ -27,3 +27,13 @@ int hybd_wsos_prod(cudaStream_t st, HybDenseWsos* c, int op, const double* arr, 
 int hybd_wsos_dder3(cudaStream_t st, HybDenseWsos* c, const double* dir, double* out);
 // 1 if chol(H) of the loaded point succeeded (sqrt oracles usable, Cones.jl:193-199); synchronizes
 int hybd_wsos_sqrt_ok(cudaStream_t st, HybDenseWsos* c, int* ok);
+
+struct HybDenseWsosPsd;  // WSOSInterpPosSemidefTri (wsosinterppossemideftri.jl)
+int hybd_wsospsd_create(HybDenseWsosPsd** out, int R, int64_t U, int nPs, const double* const* Ps_host, const int64_t* Ls);
+void hybd_wsospsd_destroy(HybDenseWsosPsd* c);
+int hybd_wsospsd_update(cudaStream_t st, HybDenseWsosPsd* c, const double* primal, const double* dual_in, double scal,
+                        double irtmu, double* point, double* dual_out, double* grad, int* flag, double* prox);
+int hybd_wsospsd_prod(cudaStream_t st, HybDenseWsosPsd* c, int op, const double* arr, int64_t lda, double* prod,
+                      int64_t ldp, int64_t m);
+int hybd_wsospsd_dder3(cudaStream_t st, HybDenseWsosPsd* c, const double* dir, double* out);
+int hybd_wsospsd_sqrt_ok(cudaStream_t st, HybDenseWsosPsd* c, int* ok);

@@ -35,7 +35,15 @@ def _wsos(n, halfdeg, use_dual=False):
     return cs.WSOSInterpNonnegative(U, Ps, use_dual=use_dual)
 
 
+def _wsospsd(n, halfdeg, R):
+    from hypatia_b200 import polyutils as pu
+
+    U, _, Ps = pu.interpolate(pu.BoxDomain(-np.ones(n), np.ones(n)), halfdeg, sample=False)
+    return cs.wsos_psd(R, U, Ps)
+
+
 SPEC_SETS = {
+    "wsospsd": [_wsospsd(1, 1, 1), _wsospsd(1, 2, 2), cs.EpiNormEucl(4), _wsospsd(2, 2, 3), _wsospsd(1, 1, 4)],
     "wsos": [_wsos(1, 3), cs.Nonnegative(3), _wsos(2, 2, use_dual=True), _wsos(2, 4)],
     "nonneg": [cs.Nonnegative(1), cs.Nonnegative(6), cs.Nonnegative(300)],
     "soc_small": [cs.EpiNormEucl(2)] + [cs.EpiNormEucl(3)] * 5 + [cs.EpiNormEucl(8)] * 40,
@@ -61,7 +69,7 @@ def test_oracles_match_cpu(name):
     specs = SPEC_SETS[name]
     rng = np.random.default_rng(sorted(SPEC_SETS).index(name) + 100)
     cpu, gpu = make_pair(specs)
-    tol_scale = 1e5 if name == "wsos" else 1.0  # products with the (ill-conditioned) WSOS Hessian
+    tol_scale = 1e5 if name.startswith("wsos") else 1.0  # products with the (ill-conditioned) WSOS Hessian
     q = cpu.q
     primal = interior_point(specs, rng, scale=0.7)
     dual = interior_point(specs, rng, scale=1.3)

@@ -86,7 +86,8 @@ def solve_both(model_fn, **kw):
 GPU_KNOWN = ["dimension1", "primalinfeas1", "primalinfeas2", "dualinfeas2", "dualinfeas3", "nonnegative4",
              "possemideftri1", "possemideftri2", "possemideftri8", "possemideftri9", "epinormeucl1", "epinormeucl2",
              "epinormeucl3", "epipersquare1", "epipersquare2", "epipersquare3", "epipersquare4",
-             "wsosinterpnonnegative1", "wsosinterpnonnegative2", "wsosinterpnonnegative3"]
+             "wsosinterpnonnegative1", "wsosinterpnonnegative2", "wsosinterpnonnegative3",
+             "wsosinterppossemideftri1", "wsosinterppossemideftri2", "wsosinterppossemideftri3"]
 
 
 @pytest.mark.parametrize("name", GPU_KNOWN)
