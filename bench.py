@@ -243,7 +243,8 @@ def main():
         try:
             from threadpoolctl import threadpool_limits
 
-            threadpool_limits(max(1, cores // world))
+            # rank 0 does the one pivoted QR of the preprocessing and broadcasts its outcome
+            threadpool_limits(cores if rank == 0 else max(1, cores // world))
         except Exception:
             pass
     if not torch.cuda.is_available():

@@ -277,6 +277,8 @@ def make_gpu_solver(device: int = 0, dist=None, **solver_kwargs):
         comm = Comm(dist, torch.device("cuda", device))
         ss = ShardedQRCholSystemSolver(GpuLocalBackend(ctx), comm)
         ss.ctx = ctx
-        return Solver(ss.cones_factory, ss, **solver_kwargs)
+        solver = Solver(ss.cones_factory, ss, **solver_kwargs)
+        solver.setup_comm = comm  # rank 0 does the preprocessing QR and broadcasts its outcome
+        return solver
     ss = B200QRCholSystemSolver(ctx)
     return Solver(ss.cones_factory, ss, **solver_kwargs)

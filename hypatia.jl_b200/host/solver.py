@@ -327,17 +327,50 @@ class Solver:
             return
         init_y = self._update_primal_eq(init_z)
         t0 = time.time()
-        self._handle_dual_eq()
+        init_x = self._dual_eq_and_init_x(init_s)
         self.time_initx = time.time() - t0
         if self.status == "DualInconsistent":
             return
-        init_x = self._update_dual_eq(init_s)
         model = self.model
         point = self.point = Point(model.n, model.p, model.q)
         point.x[:] = init_x
         point.y[:] = init_y
         point.z[:] = init_z
         point.s[:] = init_s
+
+    def _dual_eq_and_init_x(self, init_s: np.ndarray) -> np.ndarray:
+        """handle_dual_eq + update_dual_eq (process.jl:68-200).  With several ranks running the
+        same (replicated, deterministic) host driver, only rank 0 does the pivoted QR of [A; G] and
+        broadcasts its outcome (status, kept columns, initial x): identical results everywhere
+        without every rank repeating the same LAPACK factorization on a share of the cores."""
+        comm = getattr(self, "setup_comm", None)
+        if comm is None or comm.world == 1:
+            self._handle_dual_eq()
+            if self.status == "DualInconsistent":
+                return np.zeros(0)
+            return self._update_dual_eq(init_s)
+        model = self.model
+        payload = None
+        if comm.rank == 0:
+            self._handle_dual_eq()
+            if self.status == "DualInconsistent":
+                payload = ("DualInconsistent", None, None)
+            else:
+                init_x = self._update_dual_eq(init_s)
+                payload = (self.status, np.asarray(self.x_keep_idxs), init_x)
+        status, keep, init_x = comm.bcast_object(payload)
+        if comm.rank != 0:
+            self.AG_fact = None
+            if status == "DualInconsistent":
+                self.status = status
+                return np.zeros(0)
+            self.x_keep_idxs = keep
+            if keep.size != model.n:
+                model.A = np.asfortranarray(model.A[:, keep])
+                model.G = np.asfortranarray(model.G[:, keep])
+                model.n = keep.size
+            model.c = model.c[keep]
+        return init_x
 
     def _update_initial_point(self) -> None:  # Solvers.jl:484-497
         init_z, init_s = self._initialize_cone_point()

@@ -122,6 +122,11 @@ class Comm:
             return
         self.dist.reduce(t, dst=0, op=self.dist.ReduceOp.SUM)
 
+    def bcast_object(self, obj, src: int = 0):
+        box = [obj]
+        self.dist.broadcast_object_list(box, src=src)
+        return box[0]
+
     def barrier(self):
         self.dist.barrier()
 

@@ -75,6 +75,7 @@ def _worker(rank, world, port, which, out):
         model = getattr(instances, which[0])(**which[1])
         ss = ShardedQRCholSystemSolver(NumpyLocalBackend(), comm)
         solver = Solver(ss.cones_factory, ss, trace=True)
+        solver.setup_comm = comm
         solver.load(model)
         solver.solve()
         if rank == 0:
