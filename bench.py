@@ -238,15 +238,17 @@ def main():
         os.environ["NCCL_DEBUG"] = "WARN"
     import torch
 
-    if world > 1:
-        # torchrun pins OMP_NUM_THREADS=1; the (untimed) host preprocessing is LAPACK-heavy
-        try:
-            from threadpoolctl import threadpool_limits
+    # Host BLAS threads: the (untimed) preprocessing is LAPACK-heavy and runs on rank 0 only (it
+    # broadcasts its outcome), so rank 0 gets all cores for the set-up; the iteration loop does
+    # only O(n+q) vector work on the host, where a large BLAS pool just adds wake-up latency
+    # (and oversubscribes the cores when several ranks share the box).
+    try:
+        from threadpoolctl import threadpool_limits
 
-            # rank 0 does the one pivoted QR of the preprocessing and broadcasts its outcome
-            threadpool_limits(cores if rank == 0 else max(1, cores // world))
-        except Exception:
-            pass
+        threadpool_limits(cores if rank == 0 else 1)
+        loop_threads = max(1, min(4, cores // max(world, 1)))
+    except Exception:
+        threadpool_limits, loop_threads = None, None
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the hypatia_b200 hot path has no CPU fallback")
     torch.cuda.set_device(local_rank)
@@ -263,7 +265,7 @@ def main():
     N = args.N
     model = build_model(N)
     steps, warmup = args.steps, max(args.warmup, 3)
-    gpu = make_gpu_solver(local_rank, iter_limit=warmup + steps, dist=dist)
+    gpu = make_gpu_solver(local_rank, iter_limit=warmup + steps, dist=dist, use_peer=not os.environ.get("HYB_NO_PEER"))
     ctx = gpu.syssolver.ctx
 
     def sync():
@@ -294,6 +296,8 @@ def main():
 
     def init_and_start():
         orig_init()
+        if threadpool_limits is not None:
+            threadpool_limits(loop_threads)
         timer.start()
 
     gpu._initialize_point = init_and_start
@@ -351,7 +355,8 @@ def main():
             "value_definition": "iterations / device time: CUDA-event time of every kernel region of the C-ABI calls of the timed iterations (inputs resident in HBM)",
             "e2e_definition": "iterations / wall time of the same iterations through the C-ABI with host vectors (all H2D/D2H copies and the host-side stepper included)",
             "status_after_limit": gpu.status, "iterations_run": gpu.num_iters,
-            "parallelism": ("cones partitioned by block over %d ranks, NCCL reduce of the partial Schur matrices onto rank 0 (Cholesky + solves on rank 0)" % world) if world > 1 else "single GPU",
+            "parallelism": ("cones partitioned by block over %d ranks; partial Schur matrices reach rank 0 by %s; Cholesky + solves on rank 0"
+                            % (world, "peer stores from the syrk epilogue over NVLink + fixed-order sum" if getattr(gpu.syssolver.backend, "peer", False) else "NCCL reduce")) if world > 1 else "single GPU",
             "line_search_candidates_per_step": float(np.mean([r["n_cand"] for r in rows])),
             "refinement_solves_per_step": float(np.mean([r["n_ref"] for r in rows])),
         }),

@@ -97,6 +97,12 @@ struct hyb_ctx {
     int64_t h2d_bytes = 0, d2h_bytes = 0;
     double last_t[4] = {0, 0, 0, 0};  // apply-W, syrk, factor, (unused)
     bool in_region = false;
+    // peer-memory Schur reduce (multi-GPU): root owns `peer_world` slots of ldS x N doubles; a rank's
+    // syrk epilogue stores into `peer_slot` (its slot in the ROOT's memory, mapped through CUDA IPC)
+    double* peer_slots = nullptr;   // root only: base of all slots
+    double* peer_slot = nullptr;    // this rank's slot (local pointer on root, IPC-mapped elsewhere)
+    void* peer_ipc_base = nullptr;  // non-root: pointer returned by cudaIpcOpenMemHandle
+    int peer_world = 0, peer_rank = 0;
 };
 
 static inline cudaError_t h2d(hyb_ctx* c, void* dst, const void* src, size_t bytes) {
@@ -133,6 +139,11 @@ static void free_model(hyb_ctx* c) {
         hyb_chol_free(c->chol);
         hybi_cones_free(c->cones);
     }
+    if (c->peer_ipc_base) cudaIpcCloseMemHandle(c->peer_ipc_base);
+    if (c->peer_slots) cudaFree(c->peer_slots);
+    c->peer_ipc_base = nullptr;
+    c->peer_slots = c->peer_slot = nullptr;
+    c->peer_world = 0;
     c->loaded = false;
 }
 
@@ -382,8 +393,14 @@ int hyb_cones_dder3(hyb_ctx* c, const double* dir, double* out) {
     return 0;
 }
 
+static int schur_assemble_into(hyb_ctx* c, double* Sdst, double* t_assemble_ms);
+
 int hyb_schur_assemble(hyb_ctx* c, double* t_assemble_ms) {
     if (!c || !c->loaded) return -1;
+    return schur_assemble_into(c, c->S, t_assemble_ms);
+}
+
+static int schur_assemble_into(hyb_ctx* c, double* Sdst, double* t_assemble_ms) {
     HYB_CUDA(cudaSetDevice(c->device));
     if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(ensure_updated(c, c->loaded_scal));
     const int64_t q = c->q, N = c->N;
@@ -422,7 +439,7 @@ int hyb_schur_assemble(hyb_ctx* c, double* t_assemble_ms) {
         HYB_CHECK(rcp);
         HYB_CUDA(cudaEventRecord(c->ev3, c->st));
         // lhs = HGQ2' HGQ2, upper (outer_prod!, qrchol.jl:242)
-        HYB_CHECK(hyb_gemm_tn(c->st, N, N, q, 1.0, c->HGQ2, c->ldq, c->HGQ2, c->ldq, 0.0, c->S, c->ldS, HYB_GEMM_UPPER));
+        HYB_CHECK(hyb_gemm_tn(c->st, N, N, q, 1.0, c->HGQ2, c->ldq, c->HGQ2, c->ldq, 0.0, Sdst, c->ldS, HYB_GEMM_UPPER));
         // remaining cones: lhs += GQ2_k' (H~_k GQ2_k)  (block_hess_prod! + mul!, qrchol.jl:248-254)
         for (size_t bi = 0; bi < cs.blocks.size() && !all_sqrt; ++bi) {
             if (sqrt_mask[bi]) continue;
@@ -448,7 +465,7 @@ int hyb_schur_assemble(hyb_ctx* c, double* t_assemble_ms) {
                 Bk = bounce + ldb * N;
                 ldk = ldb;
             }
-            int rcg = hyb_gemm_tn(c->st, N, N, rows, 1.0, Ak, ldk, Bk, ldk, 1.0, c->S, c->ldS, HYB_GEMM_UPPER);
+            int rcg = hyb_gemm_tn(c->st, N, N, rows, 1.0, Ak, ldk, Bk, ldk, 1.0, Sdst, c->ldS, HYB_GEMM_UPPER);
             if (bounce) {
                 cudaStreamSynchronize(c->st);
                 cudaFree(bounce);
@@ -457,7 +474,7 @@ int hyb_schur_assemble(hyb_ctx* c, double* t_assemble_ms) {
         }
     } else {
         HYB_CUDA(cudaEventRecord(c->ev3, c->st));
-        HYB_CUDA(cudaMemsetAsync(c->S, 0, sizeof(double) * c->ldS * N, c->st));
+        HYB_CUDA(cudaMemsetAsync(Sdst, 0, sizeof(double) * c->ldS * N, c->st));
     }
     HYB_CUDA(cudaEventRecord(c->ev1, c->st));
     HYB_CUDA(cudaEventSynchronize(c->ev1));
@@ -511,6 +528,80 @@ int hyb_schur_factor(hyb_ctx* c, double* t_fact_ms, int* fact_kind) {
 int hyb_schur_update(hyb_ctx* c, double* t_assemble_ms, double* t_fact_ms, int* fact_kind) {
     HYB_CHECK(hyb_schur_assemble(c, t_assemble_ms));
     return hyb_schur_factor(c, t_fact_ms, fact_kind);
+}
+
+// S(upper) = sum over ranks of their slots, in rank order (deterministic)
+__global__ void sum_slots_kernel(const double* __restrict__ slots, int world, int64_t slot_stride, int64_t N, int64_t ld,
+                                 double* __restrict__ S) {
+    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t col = blockIdx.y;
+    if (r >= N || r > col) return;
+    const int64_t off = r + col * ld;
+    double acc = 0.0;
+    for (int k = 0; k < world; ++k) acc += slots[k * slot_stride + off];
+    S[off] = acc;
+}
+
+int hyb_peer_root_create(hyb_ctx* c, int world, unsigned char* handle_out) {
+    if (!c || !c->loaded) return -1;
+    HYB_CUDA(cudaSetDevice(c->device));
+    const int64_t slot = c->ldS * (c->N > 0 ? c->N : 1);
+    if (c->peer_slots) cudaFree(c->peer_slots);
+    HYB_CUDA(cudaMalloc(&c->peer_slots, sizeof(double) * slot * world));
+    HYB_CUDA(cudaMemset(c->peer_slots, 0, sizeof(double) * slot * world));
+    cudaIpcMemHandle_t h;
+    HYB_CUDA(cudaIpcGetMemHandle(&h, c->peer_slots));
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    memcpy(handle_out, &h, 64);
+    c->peer_world = world;
+    c->peer_rank = 0;
+    c->peer_slot = c->peer_slots;  // slot 0
+    return 0;
+}
+
+int hyb_peer_attach(hyb_ctx* c, const unsigned char* handle, int rank, int world) {
+    if (!c || !c->loaded) return -1;
+    if (rank == 0) return 0;  // the root uses its local slot
+    HYB_CUDA(cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    void* base = nullptr;
+    HYB_CUDA(cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
+    c->peer_ipc_base = base;
+    const int64_t slot = c->ldS * (c->N > 0 ? c->N : 1);
+    c->peer_slot = (double*)base + (int64_t)rank * slot;
+    c->peer_world = world;
+    c->peer_rank = rank;
+    return 0;
+}
+
+int hyb_schur_assemble_peer(hyb_ctx* c, double* t_assemble_ms) {
+    if (!c || !c->loaded) return -1;
+    if (!c->peer_slot) {
+        hyb_set_error("hyb_schur_assemble_peer: no peer slot attached");
+        return -3;
+    }
+    return schur_assemble_into(c, c->peer_slot, t_assemble_ms);
+}
+
+int hyb_peer_root_sum(hyb_ctx* c, double* t_ms) {
+    if (!c || !c->loaded || !c->peer_slots) return -1;
+    HYB_CUDA(cudaSetDevice(c->device));
+    const int64_t N = c->N;
+    if (t_ms) *t_ms = 0;
+    if (N == 0) return 0;
+    HYB_CUDA(cudaEventRecord(c->ev0, c->st));
+    dim3 grid((unsigned)((N + 255) / 256), (unsigned)N);
+    sum_slots_kernel<<<grid, 256, 0, c->st>>>(c->peer_slots, c->peer_world, c->ldS * N, N, c->ldS, c->S);
+    ++g_misc_launches;
+    HYB_CUDA(cudaGetLastError());
+    HYB_CUDA(cudaEventRecord(c->ev1, c->st));
+    HYB_CUDA(cudaEventSynchronize(c->ev1));
+    float ms = 0;
+    HYB_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    c->dev_ms += ms;
+    if (t_ms) *t_ms = ms;
+    return 0;
 }
 
 int hyb_device_buffer(hyb_ctx* c, int which, void** ptr, int64_t* rows, int64_t* cols, int64_t* ld) {

@@ -263,7 +263,7 @@ class B200QRCholSystemSolver(QRCholSystemSolver):
         pass
 
 
-def make_gpu_solver(device: int = 0, dist=None, **solver_kwargs):
+def make_gpu_solver(device: int = 0, dist=None, use_peer: bool = True, **solver_kwargs):
     """Solver wired to the GPU backends (what `Hypatia.Optimizer(syssolver =
     B200QRCholSystemSolver{Float64}(), use_dense_model = true)` selects in Julia)."""
     from .host.solver import Solver
@@ -275,7 +275,7 @@ def make_gpu_solver(device: int = 0, dist=None, **solver_kwargs):
         from .sharded import Comm, GpuLocalBackend, ShardedQRCholSystemSolver
 
         comm = Comm(dist, torch.device("cuda", device))
-        ss = ShardedQRCholSystemSolver(GpuLocalBackend(ctx), comm)
+        ss = ShardedQRCholSystemSolver(GpuLocalBackend(ctx, comm, use_peer=use_peer), comm)
         ss.ctx = ctx
         solver = Solver(ss.cones_factory, ss, **solver_kwargs)
         solver.setup_comm = comm  # rank 0 does the preprocessing QR and broadcasts its outcome

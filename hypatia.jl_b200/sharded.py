@@ -313,13 +313,17 @@ class ShardedQRCholSystemSolver(QRCholSystemSolver):
 class GpuLocalBackend:
     """The rank's shard on its B200, through the C-ABI."""
 
-    def __init__(self, ctx):
+    def __init__(self, ctx, comm=None, use_peer=True):
         from .gpu import GpuConeBatch
 
         self.ctx = ctx
         self.lib = ctx.lib
         self._GpuConeBatch = GpuConeBatch
         self.S_tensor = None
+        self.comm = comm
+        self.want_peer = use_peer
+        self.peer = False
+        self.time_peer_sum_ms = 0.0
 
     def local_cones_factory(self, specs):
         return self._GpuConeBatch(specs, self.ctx)
@@ -346,14 +350,53 @@ class GpuLocalBackend:
 
         self._iface = _Iface()
         self.S_tensor = torch.as_tensor(self._iface, device=torch.device("cuda", torch.cuda.current_device())) if self.N else None
+        self._setup_peer()
+
+    def _setup_peer(self) -> None:
+        """Peer-memory reduce: every rank's syrk epilogue stores into its slot in the root's
+        memory (CUDA IPC + NVLink P2P).  Needs one GPU per rank on one node and the NCCL
+        backend's device topology; otherwise the NCCL / gloo reduce stays in use."""
+        self.peer = False
+        comm = self.comm
+        if not (self.want_peer and comm is not None and comm.world > 1 and self.N and comm.dist.get_backend() == "nccl"):
+            return
+        import ctypes as C
+
+        handle = C.create_string_buffer(64)
+        ok = 1
+        if comm.rank == 0:
+            rc = self.lib.hyb_peer_root_create(self.ctx.ptr, comm.world, handle)
+            ok = 1 if rc == 0 else 0
+        payload = comm.bcast_object((ok, bytes(handle.raw)) if comm.rank == 0 else None)
+        ok, raw = payload
+        if ok and comm.rank != 0:
+            rc = self.lib.hyb_peer_attach(self.ctx.ptr, raw, comm.rank, comm.world)
+            ok = 1 if rc == 0 else 0
+        all_ok = comm.allreduce_min(np.array([float(ok)]))[0] > 0.5
+        self.peer = bool(all_ok)
+        if not self.peer and comm.rank == 0:
+            print("hypatia_b200: peer-memory Schur reduce unavailable (%s); using the NCCL reduce"
+                  % self.lib.hyb_last_error(self.ctx.ptr).decode())
 
     def assemble(self) -> float:
         self.cones._sync()
         ta = C.c_double(0)
-        self.ctx.check(self.lib.hyb_schur_assemble(self.ctx.ptr, C.byref(ta)), "hyb_schur_assemble")
+        if self.peer:
+            self.ctx.check(self.lib.hyb_schur_assemble_peer(self.ctx.ptr, C.byref(ta)), "hyb_schur_assemble_peer")
+        else:
+            self.ctx.check(self.lib.hyb_schur_assemble(self.ctx.ptr, C.byref(ta)), "hyb_schur_assemble")
         return ta.value
 
     def reduce_to_root(self, comm: Comm) -> None:
+        if self.peer:
+            # every rank's tiles are already in the root's memory (the assemble call returned after
+            # its kernels completed); one host barrier, then the root adds the slots in rank order
+            comm.barrier()
+            if comm.rank == 0:
+                t = C.c_double(0)
+                self.ctx.check(self.lib.hyb_peer_root_sum(self.ctx.ptr, C.byref(t)), "hyb_peer_root_sum")
+                self.time_peer_sum_ms += t.value
+            return
         if self.S_tensor is not None and comm.world > 1:
             comm.reduce_tensor_to_root(self.S_tensor)
             comm.torch.cuda.synchronize()

@@ -99,6 +99,17 @@ int hyb_schur_factor(hyb_ctx* ctx, double* t_fact_ms, int* fact_kind);
 /* device address of an internal matrix for collectives: which = 0 -> assembled Schur matrix
  * (rows x cols, leading dimension ld, column-major FP64, upper triangle valid). */
 int hyb_device_buffer(hyb_ctx* ctx, int which, void** ptr, int64_t* rows, int64_t* cols, int64_t* ld);
+/* Fused assembly + NVLink transfer for the multi-GPU reduce (no counterpart in the reference,
+ * which is single-process): the factorizing rank owns one N x N slot per rank
+ * (hyb_peer_root_create exports a 64-byte CUDA IPC handle); the other ranks map it
+ * (hyb_peer_attach) and hyb_schur_assemble_peer makes the syrk epilogue store each finished
+ * tile directly into the rank's slot in the ROOT's memory (peer stores over NVLink, overlapped
+ * with the remaining tiles' math).  After a host barrier the root adds the slots in rank order
+ * (hyb_peer_root_sum) - bitwise deterministic, unlike atomics. */
+int hyb_peer_root_create(hyb_ctx* ctx, int world, unsigned char* handle64_out);
+int hyb_peer_attach(hyb_ctx* ctx, const unsigned char* handle64, int rank, int world);
+int hyb_schur_assemble_peer(hyb_ctx* ctx, double* t_assemble_ms);
+int hyb_peer_root_sum(hyb_ctx* ctx, double* t_ms);
 /* ldiv!(x, fact, rhs), qrchol.jl:75; rhs and x are N x nrhs */
 int hyb_schur_solve(hyb_ctx* ctx, const double* rhs, double* x, int64_t nrhs);
 /* copy of the assembled N x N matrix (upper triangle valid), for tests / fallbacks */
