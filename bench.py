@@ -129,6 +129,11 @@ class IterTimer:
         if self.ctx:
             dev_ms, h2d, d2h = self.ctx.stats(reset=True)
             tw, ts, tf = self.ctx.last_schur_timings()
+            if getattr(self, "shard_ctx", None):  # root/worker form: rank 0 assembles its share in a second context
+                sc = self.shard_ctx()
+                d2, a2, b2 = sc.stats(reset=True)
+                tw, ts, _ = sc.last_schur_timings()
+                dev_ms, h2d, d2h = dev_ms + d2, h2d + a2, d2h + b2
             lc = self.ctx.launch_count()
             red = getattr(solver.syssolver, "time_reduce_ms", 0.0)
             row.update(dev_ms=dev_ms, h2d=h2d, d2h=d2h, t_w=tw, t_syrk=ts, t_fact=tf, launches=lc - self._launch0,
@@ -265,7 +270,20 @@ def main():
     N = args.N
     model = build_model(N)
     steps, warmup = args.steps, max(args.warmup, 3)
-    gpu = make_gpu_solver(local_rank, iter_limit=warmup + steps, dist=dist, use_peer=not os.environ.get("HYB_NO_PEER"))
+    mode = os.environ.get("HYB_MULTI_MODE", "rootworker")  # or "replicated" (sharded.py)
+    gpu = make_gpu_solver(local_rank, iter_limit=warmup + steps, dist=dist, use_peer=not os.environ.get("HYB_NO_PEER"), mode=mode)
+    rootworker = world > 1 and mode == "rootworker"
+    if rootworker and rank != 0:
+        # assembly worker: it has no iteration loop of its own; it serves the root until the root stops it
+        gpu.load(model)
+        gpu.solve()
+        torch.cuda.synchronize()
+        dist.barrier()
+        for _ in range(2):  # the root's max-over-ranks reductions of wall and device time
+            z = torch.zeros(1, dtype=torch.float64, device="cuda")
+            dist.all_reduce(z, op=dist.ReduceOp.MAX)
+        dist.destroy_process_group()
+        return
     ctx = gpu.syssolver.ctx
 
     def sync():
@@ -277,13 +295,15 @@ def main():
 
     def callback(solver):
         timer(solver)
+        # (root/worker form: the workers are inside every iteration's barrier already, and only the
+        # root has an iteration loop to bracket)
         if len(timer.rows) == warmup + steps:
-            if dist is not None:
+            if dist is not None and not rootworker:
                 dist.barrier()
             sync()
             state["t_end"] = time.perf_counter()
         if len(timer.rows) == warmup:  # timed region starts after the warm-up iterations
-            if dist is not None:
+            if dist is not None and not rootworker:
                 dist.barrier()
             sync()
             sampler.start()
@@ -301,6 +321,8 @@ def main():
         timer.start()
 
     gpu._initialize_point = init_and_start
+    if rootworker:
+        timer.shard_ctx = lambda: gpu.syssolver.shard.ctx
     gpu.solve()
     sync()
     if dist is not None:
@@ -334,7 +356,10 @@ def main():
 
     # every cone of this model takes the sqrt-oracle (syrk) branch, qrchol.jl:228-242; with N ranks the
     # launch timed on rank 0 contracts that rank's rows only
-    q_sqrt = gpu.cones.row_counts[0] if world > 1 else model.q
+    if rootworker:
+        q_sqrt = gpu.syssolver.row_counts[0]
+    else:
+        q_sqrt = gpu.cones.row_counts[0] if world > 1 else model.q
     syrk_flops = q_sqrt * N * (N + 1)  # algorithmic flops of the G'HG contraction per launch
     peak_tf = cublas_dgemm_tflops()
     achieved_tf = syrk_flops / (t_syrk * 1e-3) / 1e12
@@ -356,7 +381,8 @@ def main():
             "e2e_definition": "iterations / wall time of the same iterations through the C-ABI with host vectors (all H2D/D2H copies and the host-side stepper included)",
             "status_after_limit": gpu.status, "iterations_run": gpu.num_iters,
             "parallelism": ("cones partitioned by block over %d ranks; partial Schur matrices reach rank 0 by %s; Cholesky + solves on rank 0"
-                            % (world, "peer stores from the syrk epilogue over NVLink + fixed-order sum" if getattr(gpu.syssolver.backend, "peer", False) else "NCCL reduce")) if world > 1 else "single GPU",
+                            % (world, "peer stores from the syrk epilogue over NVLink + fixed-order sum" if (rootworker or getattr(gpu.syssolver.backend, "peer", False)) else "NCCL reduce")) if world > 1 else "single GPU",
+            "multi_gpu_form": ("root/worker: rank 0 runs the algorithm, 1 point broadcast + 1 barrier per iteration" if rootworker else "replicated host driver, sharded oracles") if world > 1 else None,
             "line_search_candidates_per_step": float(np.mean([r["n_cand"] for r in rows])),
             "refinement_solves_per_step": float(np.mean([r["n_ref"] for r in rows])),
         }),

@@ -575,6 +575,14 @@ int hyb_peer_attach(hyb_ctx* c, const unsigned char* handle, int rank, int world
     return 0;
 }
 
+// same-process variant of hyb_peer_attach: the slot is a plain device pointer (the root's own shard
+// context writes into slot 0 of the slots its full-model context owns)
+int hyb_peer_set_slot(hyb_ctx* c, void* slot_ptr) {
+    if (!c || !c->loaded) return -1;
+    c->peer_slot = (double*)slot_ptr;
+    return 0;
+}
+
 int hyb_schur_assemble_peer(hyb_ctx* c, double* t_assemble_ms) {
     if (!c || !c->loaded) return -1;
     if (!c->peer_slot) {
@@ -612,6 +620,13 @@ int hyb_device_buffer(hyb_ctx* c, int which, void** ptr, int64_t* rows, int64_t*
         *cols = c->N;
         *ld = c->ldS;
         return 0;
+    }
+    if (which == 1) {  // base of the peer slots (root only): peer_world slots of ld x cols doubles
+        *ptr = c->peer_slots;
+        *rows = c->N;
+        *cols = c->N;
+        *ld = c->ldS;
+        return c->peer_slots ? 0 : -3;
     }
     hyb_set_error("hyb_device_buffer: unknown buffer %d", which);
     return -3;

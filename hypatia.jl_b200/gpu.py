@@ -263,11 +263,19 @@ class B200QRCholSystemSolver(QRCholSystemSolver):
         pass
 
 
-def make_gpu_solver(device: int = 0, dist=None, use_peer: bool = True, **solver_kwargs):
+def make_gpu_solver(device: int = 0, dist=None, use_peer: bool = True, mode: str = "rootworker", **solver_kwargs):
     """Solver wired to the GPU backends (what `Hypatia.Optimizer(syssolver =
-    B200QRCholSystemSolver{Float64}(), use_dense_model = true)` selects in Julia)."""
+    B200QRCholSystemSolver{Float64}(), use_dense_model = true)` selects in Julia).
+
+    With several ranks, `mode="rootworker"` (default) runs the algorithm on rank 0 and uses the
+    other GPUs as Schur-assembly workers over peer memory (rootworker.py); `mode="replicated"`
+    runs the same host driver on every rank with sharded cone oracles (sharded.py)."""
     from .host.solver import Solver
 
+    if dist is not None and dist.get_world_size() > 1 and mode == "rootworker":
+        from .rootworker import make_rootworker_solver
+
+        return make_rootworker_solver(device, dist, **solver_kwargs)
     ctx = Context(device)
     if dist is not None and dist.get_world_size() > 1:
         import torch

@@ -204,6 +204,13 @@ class Solver:
         if init_status not in ("Loaded", "Modified"):
             raise RuntimeError(f"solve called when solver status is {init_status}")
         self._setup_solver()
+        if getattr(self.syssolver, "is_worker", False):
+            # multi-GPU root/worker form (rootworker.py): this rank only assembles partial Schur
+            # matrices for the rank that runs the algorithm
+            self.syssolver.serve(self)
+            self.status = "Worker"
+            self.solve_time = time.time() - self.solve_time
+            return
         if init_status == "Modified":
             self._setup_modified()
         else:
@@ -218,6 +225,8 @@ class Solver:
             if self.status in CHECK_NEAR_STATUSES:
                 self._check_converged(True)
             self._postprocess()
+        elif hasattr(self.syssolver, "abort_workers"):
+            self.syssolver.abort_workers()
         self.solve_time = time.time() - self.solve_time
         if self.verbose:
             print(f"\nstatus is {self.status} after {self.num_iters} iterations and {self.solve_time:.3f} seconds\n")

@@ -54,6 +54,7 @@ SIGNATURES = {
     "hyb_device_buffer": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "hyb_peer_root_create": (C.c_int, [C.c_void_p, C.c_int, C.c_char_p]),
     "hyb_peer_attach": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int, C.c_int]),
+    "hyb_peer_set_slot": (C.c_int, [C.c_void_p, C.c_void_p]),
     "hyb_schur_assemble_peer": (C.c_int, [C.c_void_p, c_double_p]),
     "hyb_peer_root_sum": (C.c_int, [C.c_void_p, c_double_p]),
     "hyb_schur_solve": (C.c_int, [C.c_void_p, c_double_p, c_double_p, C.c_int64]),

@@ -97,7 +97,8 @@ int hyb_schur_update(hyb_ctx* ctx, double* t_assemble_ms, double* t_fact_ms, int
 int hyb_schur_assemble(hyb_ctx* ctx, double* t_assemble_ms);
 int hyb_schur_factor(hyb_ctx* ctx, double* t_fact_ms, int* fact_kind);
 /* device address of an internal matrix for collectives: which = 0 -> assembled Schur matrix
- * (rows x cols, leading dimension ld, column-major FP64, upper triangle valid). */
+ * (rows x cols, leading dimension ld, column-major FP64, upper triangle valid); which = 1 -> base of
+ * the peer slots created by hyb_peer_root_create. */
 int hyb_device_buffer(hyb_ctx* ctx, int which, void** ptr, int64_t* rows, int64_t* cols, int64_t* ld);
 /* Fused assembly + NVLink transfer for the multi-GPU reduce (no counterpart in the reference,
  * which is single-process): the factorizing rank owns one N x N slot per rank
@@ -108,6 +109,7 @@ int hyb_device_buffer(hyb_ctx* ctx, int which, void** ptr, int64_t* rows, int64_
  * (hyb_peer_root_sum) - bitwise deterministic, unlike atomics. */
 int hyb_peer_root_create(hyb_ctx* ctx, int world, unsigned char* handle64_out);
 int hyb_peer_attach(hyb_ctx* ctx, const unsigned char* handle64, int rank, int world);
+int hyb_peer_set_slot(hyb_ctx* ctx, void* slot_device_ptr); /* same-process attach (root's own shard context) */
 int hyb_schur_assemble_peer(hyb_ctx* ctx, double* t_assemble_ms);
 int hyb_peer_root_sum(hyb_ctx* ctx, double* t_ms);
 /* ldiv!(x, fact, rhs), qrchol.jl:75; rhs and x are N x nrhs */

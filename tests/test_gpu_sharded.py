@@ -1,6 +1,8 @@
 """GPU test of the multi-GPU layer with the real CUDA backend: two ranks (processes) share
 cuda:0, each owning half of the cones / rows of G*Q2, collectives through gloo (host side, so
-nothing on the device waits on the other rank).  Result must match the single-process oracle."""
+nothing on the device waits on the other rank).  Both forms are covered: root/worker
+(rootworker.py: rank 1 stores its partial Schur matrix into rank 0's memory through a CUDA-IPC
+mapping) and the replicated driver (sharded.py).  Result must match the single-process oracle."""
 import os
 import socket
 import sys
@@ -18,7 +20,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, which, out):
+def _worker(rank, world, port, which, mode, out):
     sys.path.insert(0, ROOT)
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
@@ -32,13 +34,16 @@ def _worker(rank, world, port, which, out):
         from hypatia_b200 import instances
         from hypatia_b200.gpu import make_gpu_solver
 
-        solver = make_gpu_solver(0, dist=dist, trace=True)
+        solver = make_gpu_solver(0, dist=dist, trace=True, mode=mode)
         solver.syssolver.comm.device = torch.device("cpu")  # gloo: vectors travel through the host
         solver.load(getattr(instances, which[0])(**which[1]))
         solver.solve()
         if rank == 0:
+            rows = solver.syssolver.row_counts if mode == "rootworker" else solver.cones.row_counts
             out.put((solver.status, solver.num_iters, solver.primal_obj, [r["mu"] for r in solver.trace],
-                     solver.cones.row_counts, solver.syssolver.ctx.launch_count()))
+                     rows, solver.syssolver.ctx.launch_count()))
+        else:
+            assert mode != "rootworker" or (solver.status == "Worker" and solver.syssolver.num_updates > 0)
     finally:
         dist.destroy_process_group()
 
@@ -48,7 +53,8 @@ def _worker(rank, world, port, which, out):
     [("block_multicone", dict(N=160, seed=5, psd_side=8)), ("linearopt", dict(m=60, n=200, seed=3))],
     ids=["block_multicone", "linearopt_split_nonnegative"],
 )
-def test_two_rank_gpu_solve_matches_oracle(which):
+@pytest.mark.parametrize("mode", ["rootworker", "replicated"])
+def test_two_rank_gpu_solve_matches_oracle(which, mode):
     import torch.multiprocessing as mp
 
     import hypatia_b200  # noqa: F401
@@ -60,7 +66,7 @@ def test_two_rank_gpu_solve_matches_oracle(which):
     ctx = mp.get_context("spawn")
     out = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, which, out)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, which, mode, out)) for r in range(2)]
     for p in procs:
         p.start()
     status, iters, obj, mus, row_counts, launches = out.get(timeout=600)
