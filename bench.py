@@ -112,6 +112,7 @@ class IterTimer:
         self.ctx, self.sync = ctx, sync
         self.rows = []
         self._t = None
+        self._ph = {}
 
     def start(self):
         if self.sync:
@@ -126,6 +127,10 @@ class IterTimer:
             self.sync()
         now = time.perf_counter()
         row = {"wall_s": now - self._t, "n_cand": solver.stepper.last_num_cand, "n_ref": solver.stepper.last_num_ref}
+        for name in ("upsys", "uprhs", "getdir", "search"):  # the driver's own phase clocks (Solvers.jl:529-564)
+            tot = getattr(solver, "time_" + name, 0.0)
+            row["ph_" + name] = 1e3 * (tot - self._ph.get(name, 0.0))
+            self._ph[name] = tot
         if self.ctx:
             dev_ms, h2d, d2h = self.ctx.stats(reset=True)
             tw, ts, tf = self.ctx.last_schur_timings()
@@ -388,6 +393,7 @@ def main():
         }),
         "e2e": {"value": k / wall, "unit": "iterations/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": launches,
+        "phase_ms": {name: float(np.mean([r["ph_" + name] for r in rows])) for name in ("upsys", "uprhs", "getdir", "search")},
         "schur_assemble_ms": t_w + t_syrk,
         "schur_reduce_ms": reduce_ms,
         "cholesky_ms": t_fact,

@@ -8,6 +8,7 @@
 #include "cones.cuh"
 #include "cones_dense.cuh"
 #include "tma.cuh"
+#include "ctx.cuh"
 
 int hyb_copy_upper(cudaStream_t st, const double* src, int64_t lds_, double* dst, int64_t ldd, int64_t N);
 
@@ -55,7 +56,7 @@ int hyb_make_tmap_2d_f64(CUtensorMap* tm, const double* base, uint64_t inner, ui
 }
 
 // ----------------------------------------------------------------------------- small kernels
-static int64_t g_misc_launches = 0;
+int64_t g_misc_launches = 0;
 
 __global__ void axpby_kernel(int64_t n, double a, const double* __restrict__ x, double b, const double* __restrict__ y,
                              double* __restrict__ out) {
@@ -69,56 +70,6 @@ __global__ void increase_diag_kernel(int64_t n, double* A, int64_t ld) {
         const double d = A[i + i * ld];
         A[i + i * ld] = (1.0 + 1e-5) * fmax(d, 1000.0 * HYB_EPS);
     }
-}
-
-// ----------------------------------------------------------------------------- context
-struct hyb_ctx {
-    int device = 0;
-    cudaStream_t st = nullptr;
-    bool loaded = false;
-    int64_t q = 0, N = 0, ldq = 0, ldS = 0;
-    double* GQ2 = nullptr;
-    double* HGQ2 = nullptr;
-    double* S = nullptr;
-    HybChol chol;
-    HybCones cones;
-    double* in_primal = nullptr;
-    double* in_dual = nullptr;
-    double *vq1 = nullptr, *vq2 = nullptr, *vq3 = nullptr, *vn1 = nullptr, *vn2 = nullptr;
-    double* gemv_scratch = nullptr;
-    double loaded_scal = 1.0;
-    double updated_irtmu = NAN;
-    bool point_loaded = false;
-    bool fact_ok = false;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr, evA = nullptr, evB = nullptr;
-    // statistics (hyb_stats): device milliseconds between the last H2D and the first D2H of every
-    // compute call, and the bytes moved across PCIe by the calls
-    double dev_ms = 0.0;
-    int64_t h2d_bytes = 0, d2h_bytes = 0;
-    double last_t[4] = {0, 0, 0, 0};  // apply-W, syrk, factor, (unused)
-    bool in_region = false;
-    // peer-memory Schur reduce (multi-GPU): root owns `peer_world` slots of ldS x N doubles; a rank's
-    // syrk epilogue stores into `peer_slot` (its slot in the ROOT's memory, mapped through CUDA IPC)
-    double* peer_slots = nullptr;   // root only: base of all slots
-    double* peer_slot = nullptr;    // this rank's slot (local pointer on root, IPC-mapped elsewhere)
-    void* peer_ipc_base = nullptr;  // non-root: pointer returned by cudaIpcOpenMemHandle
-    int peer_world = 0, peer_rank = 0;
-};
-
-static inline cudaError_t h2d(hyb_ctx* c, void* dst, const void* src, size_t bytes) {
-    c->h2d_bytes += (int64_t)bytes;
-    return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->st);
-}
-static inline cudaError_t d2h(hyb_ctx* c, void* dst, const void* src, size_t bytes) {
-    c->d2h_bytes += (int64_t)bytes;
-    return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c->st);
-}
-// device-time region: KBEGIN after the uploads, KEND before the downloads, KSYNC after the final sync
-#define KBEGIN(c) cudaEventRecord((c)->evA, (c)->st)
-#define KEND(c) cudaEventRecord((c)->evB, (c)->st)
-static inline void ksync(hyb_ctx* c) {
-    float ms = 0;
-    if (cudaEventElapsedTime(&ms, c->evA, c->evB) == cudaSuccess) c->dev_ms += ms;
 }
 
 static void free_model(hyb_ctx* c) {
@@ -139,6 +90,7 @@ static void free_model(hyb_ctx* c) {
         hyb_chol_free(c->chol);
         hybi_cones_free(c->cones);
     }
+    hyb_dirs_free(c);
     if (c->peer_ipc_base) cudaIpcCloseMemHandle(c->peer_ipc_base);
     if (c->peer_slots) cudaFree(c->peer_slots);
     c->peer_ipc_base = nullptr;
@@ -147,7 +99,7 @@ static void free_model(hyb_ctx* c) {
     c->loaded = false;
 }
 
-static int ensure_updated(hyb_ctx* c, double irtmu) {
+int hyb_ensure_updated(hyb_ctx* c, double irtmu) {
     if (!c->point_loaded) {
         hyb_set_error("no point loaded: call hyb_cones_load_point first");
         return -3;
@@ -300,7 +252,7 @@ int hyb_cones_load_point(hyb_ctx* c, const double* primal, const double* dual, d
     c->updated_irtmu = NAN;
     // in the line search scal == irtmu (search.jl:144), so this is normally the only update
     KBEGIN(c);
-    HYB_CHECK(ensure_updated(c, scal));
+    HYB_CHECK(hyb_ensure_updated(c, scal));
     KEND(c);
     HYB_CUDA(cudaStreamSynchronize(c->st));
     ksync(c);
@@ -310,7 +262,7 @@ int hyb_cones_load_point(hyb_ctx* c, const double* primal, const double* dual, d
 int hyb_cones_is_feas(hyb_ctx* c, int* is_feas, int* is_dual_feas) {
     if (!c || !c->loaded) return -1;
     HYB_CUDA(cudaSetDevice(c->device));
-    if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(ensure_updated(c, c->loaded_scal));
+    if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(hyb_ensure_updated(c, c->loaded_scal));
     int flags = 0;
     double agg = 0.0;
     HYB_CHECK(hybi_cones_reduce(c->st, c->cones, 1, &flags, &agg));
@@ -323,7 +275,7 @@ int hyb_cones_check(hyb_ctx* c, double irtmu, int use_max_prox, double agg0, dou
                     double* agg) {
     if (!c || !c->loaded) return -1;
     HYB_CUDA(cudaSetDevice(c->device));
-    HYB_CHECK(ensure_updated(c, irtmu));
+    HYB_CHECK(hyb_ensure_updated(c, irtmu));
     int flags = 0;
     double a = 0.0;
     HYB_CHECK(hybi_cones_reduce(c->st, c->cones, use_max_prox, &flags, &a));
@@ -336,7 +288,7 @@ int hyb_cones_check(hyb_ctx* c, double irtmu, int use_max_prox, double agg0, dou
 int hyb_cones_grad(hyb_ctx* c, double* grad) {
     if (!c || !c->loaded) return -1;
     HYB_CUDA(cudaSetDevice(c->device));
-    if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(ensure_updated(c, c->loaded_scal));
+    if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(hyb_ensure_updated(c, c->loaded_scal));
     if (c->q > 0) HYB_CUDA(d2h(c, grad, c->cones.grad, sizeof(double) * c->q));
     HYB_CUDA(cudaStreamSynchronize(c->st));
     return 0;
@@ -345,7 +297,7 @@ int hyb_cones_grad(hyb_ctx* c, double* grad) {
 int hyb_cones_hess_prod(hyb_ctx* c, int which, const double* arr, double* prod, int64_t m) {
     if (!c || !c->loaded) return -1;
     HYB_CUDA(cudaSetDevice(c->device));
-    if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(ensure_updated(c, c->loaded_scal));
+    if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(hyb_ensure_updated(c, c->loaded_scal));
     if (which < 0 || which > 6) {
         hyb_set_error("hyb_cones_hess_prod: bad selector %d", which);
         return -3;
@@ -381,7 +333,7 @@ int hyb_cones_hess_prod(hyb_ctx* c, int which, const double* arr, double* prod, 
 int hyb_cones_dder3(hyb_ctx* c, const double* dir, double* out) {
     if (!c || !c->loaded) return -1;
     HYB_CUDA(cudaSetDevice(c->device));
-    if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(ensure_updated(c, c->loaded_scal));
+    if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(hyb_ensure_updated(c, c->loaded_scal));
     if (c->q == 0) return 0;
     HYB_CUDA(h2d(c, c->vq1, dir, sizeof(double) * c->q));
     KBEGIN(c);
@@ -402,7 +354,7 @@ int hyb_schur_assemble(hyb_ctx* c, double* t_assemble_ms) {
 
 static int schur_assemble_into(hyb_ctx* c, double* Sdst, double* t_assemble_ms) {
     HYB_CUDA(cudaSetDevice(c->device));
-    if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(ensure_updated(c, c->loaded_scal));
+    if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(hyb_ensure_updated(c, c->loaded_scal));
     const int64_t q = c->q, N = c->N;
     if (t_assemble_ms) *t_assemble_ms = 0;
     if (N == 0) return 0;
@@ -687,7 +639,7 @@ int hyb_G_mul(hyb_ctx* c, char trans, const double* v, double* out) {
 int hyb_solve_subsystem3(hyb_ctx* c, const double* rhs_x, const double* rhs_z, double* sol_x, double* sol_z) {
     if (!c || !c->loaded) return -1;
     HYB_CUDA(cudaSetDevice(c->device));
-    if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(ensure_updated(c, c->loaded_scal));
+    if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(hyb_ensure_updated(c, c->loaded_scal));
     const int64_t q = c->q, N = c->N;
     cudaStream_t st = c->st;
     if (q > 0) HYB_CUDA(h2d(c, c->vq1, rhs_z, sizeof(double) * q));
@@ -794,7 +746,20 @@ int hyb_posdef_solve(hyb_ctx* c, int64_t N, double* A, int64_t lda, double* B, i
         if (info) *info = inf;
         e = cudaMemcpy2D(A, sizeof(double) * lda, ch.F, sizeof(double) * ch.ld, sizeof(double) * N, N,
                          cudaMemcpyDeviceToHost);
-        if (inf == 0 && e == cudaSuccess && rc == 0 && nrhs >= 4) {
+        if (inf == 0 && e == cudaSuccess && rc == 0 && nrhs >= 2 && nrhs <= HYB_MAX_RHS) {
+            // a few right-hand sides: one pair of wavefront kernels solves them together
+            double* dB = nullptr;
+            int64_t lB = 0;
+            rc = upload_padded(B, N, nrhs, ldb, &dB, &lB);
+            if (rc == 0) rc = hyb_potrs_multi(c->st, ch, dB, lB, (int)nrhs);
+            if (rc == 0) {
+                e = cudaStreamSynchronize(c->st);
+                if (e == cudaSuccess)
+                    e = cudaMemcpy2D(B, sizeof(double) * ldb, dB, sizeof(double) * lB, sizeof(double) * N, nrhs,
+                                     cudaMemcpyDeviceToHost);
+            }
+            cudaFree(dB);
+        } else if (inf == 0 && e == cudaSuccess && rc == 0 && nrhs > HYB_MAX_RHS) {
             // many right-hand sides: blocked triangular solves (dense toolkit of the cone engines)
             double *dB = nullptr, *Lc = nullptr;
             int64_t lB = 0;

@@ -75,5 +75,13 @@ int hyb_potrs(cudaStream_t st, HybChol& ch, double* x);
 #define HYB_GEMV_SPLITS 8
 int hyb_gemv_n(cudaStream_t st, int64_t q, int64_t N, const double* G, int64_t ld, const double* x, double* y,
                double* scratch);
+// the same products for M <= HYB_MAX_RHS vectors in one pass over G
+#define HYB_MAX_RHS 4
+int hyb_gemm_n_small(cudaStream_t st, int64_t q, int64_t N, const double* G, int64_t ld, const double* X, int64_t ldx,
+                     int M, double* Y, int64_t ldy, double* scratch);
+int hyb_gemm_t_small(cudaStream_t st, int64_t q, int64_t N, const double* G, int64_t ld, const double* Z, int64_t ldz,
+                     int M, double* Y, int64_t ldy);
+// x <- (U'U)^-1 x for R <= HYB_MAX_RHS device vectors (columns of X, leading dimension ldx)
+int hyb_potrs_multi(cudaStream_t st, HybChol& ch, double* X, int64_t ldx, int R);
 // y = G' z (N)
 int hyb_gemv_t(cudaStream_t st, int64_t q, int64_t N, const double* G, int64_t ld, const double* z, double* y);

@@ -1,0 +1,64 @@
+// The library context (one per GPU) shared by api.cu and dirs.cu.
+#pragma once
+#include <cmath>
+#include "../../include/hypatia_b200.h"
+#include "common.cuh"
+#include "cones.cuh"
+
+extern int64_t g_misc_launches;
+struct HybDirs;  // device-resident direction engine (dirs.cu)
+
+// ----------------------------------------------------------------------------- context
+struct hyb_ctx {
+    int device = 0;
+    cudaStream_t st = nullptr;
+    bool loaded = false;
+    int64_t q = 0, N = 0, ldq = 0, ldS = 0;
+    double* GQ2 = nullptr;
+    double* HGQ2 = nullptr;
+    double* S = nullptr;
+    HybChol chol;
+    HybCones cones;
+    double* in_primal = nullptr;
+    double* in_dual = nullptr;
+    double *vq1 = nullptr, *vq2 = nullptr, *vq3 = nullptr, *vn1 = nullptr, *vn2 = nullptr;
+    double* gemv_scratch = nullptr;
+    double loaded_scal = 1.0;
+    double updated_irtmu = NAN;
+    bool point_loaded = false;
+    bool fact_ok = false;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr, evA = nullptr, evB = nullptr;
+    // statistics (hyb_stats): device milliseconds between the last H2D and the first D2H of every
+    // compute call, and the bytes moved across PCIe by the calls
+    double dev_ms = 0.0;
+    int64_t h2d_bytes = 0, d2h_bytes = 0;
+    double last_t[4] = {0, 0, 0, 0};  // apply-W, syrk, factor, (unused)
+    bool in_region = false;
+    // peer-memory Schur reduce (multi-GPU): root owns `peer_world` slots of ldS x N doubles; a rank's
+    // syrk epilogue stores into `peer_slot` (its slot in the ROOT's memory, mapped through CUDA IPC)
+    double* peer_slots = nullptr;   // root only: base of all slots
+    double* peer_slot = nullptr;    // this rank's slot (local pointer on root, IPC-mapped elsewhere)
+    void* peer_ipc_base = nullptr;  // non-root: pointer returned by cudaIpcOpenMemHandle
+    int peer_world = 0, peer_rank = 0;
+    HybDirs* dirs = nullptr;  // direction engine state (allocated by hyb_dirs_setup)
+};
+
+static inline cudaError_t h2d(hyb_ctx* c, void* dst, const void* src, size_t bytes) {
+    c->h2d_bytes += (int64_t)bytes;
+    return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->st);
+}
+static inline cudaError_t d2h(hyb_ctx* c, void* dst, const void* src, size_t bytes) {
+    c->d2h_bytes += (int64_t)bytes;
+    return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c->st);
+}
+// device-time region: KBEGIN after the uploads, KEND before the downloads, KSYNC after the final sync
+#define KBEGIN(c) cudaEventRecord((c)->evA, (c)->st)
+#define KEND(c) cudaEventRecord((c)->evB, (c)->st)
+static inline void ksync(hyb_ctx* c) {
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, c->evA, c->evB) == cudaSuccess) c->dev_ms += ms;
+}
+
+
+int hyb_ensure_updated(hyb_ctx* c, double irtmu);
+void hyb_dirs_free(hyb_ctx* c);

@@ -1,0 +1,541 @@
+// Device-resident direction solves: get_directions with iterative refinement
+// (systemsolvers/common.jl:22-83), apply_lhs (:86-125), solve_system (:133-158),
+// solve_subsystem4 (:161-189) and the QRChol setup_rhs3 / solve_subsystem3 (qrchol.jl:23-92,
+// reduced model: p == 0) for up to HYB_MAX_RHS - 1 right-hand sides at once.
+//
+// Why batched: the four directions of a CombinedStepper iteration (combined.jl:60-125) come in two
+// independent pairs -- (cent, pred), then (centadj, predadj), each adjustment needing only its own
+// unadjusted direction -- and the constant solve of update_lhs (qrchol.jl:199-206) is independent
+// of the first pair.  Every solve is bound by one pass over G for G'z, one for Gx (8 q N bytes
+// each) and the latency of the two wavefront triangular solves; solving a pair together reads G and
+// the Cholesky factor once for both and runs the two substitutions side by side.
+//
+// Vector layout at the boundary (point.jl:31-62 with p == 0): [x(N); z(q); tau; s(q); kap].
+#include "ctx.cuh"
+
+struct HybVecs {  // one set of m <= HYB_MAX_RHS "points" on the device
+    double *x = nullptr, *z = nullptr, *s = nullptr, *tk = nullptr;  // x: ldn x M, z/s: ldq x M, tk: 2 x M (tau, kap)
+};
+
+struct HybDirs {
+    int64_t N = 0, q = 0, ldn = 0, ldq = 0;
+    double *c = nullptr, *h = nullptr;
+    unsigned char* dual_row = nullptr;  // 1 where the row belongs to a dual-barrier cone
+    HybVecs rhs, dir, res, tmp, rrhs, rdir;  // rrhs / rdir: single-column scratch of the refinement rounds
+    double *A = nullptr, *B = nullptr, *Vx = nullptr, *Vz = nullptr, *Gx = nullptr, *T = nullptr;  // work, M columns
+    double *xc = nullptr, *zc = nullptr, *Gxc = nullptr;  // sol_const (common.jl:191-209) and G * sol_const.x
+    double* scal = nullptr;     // device scalars: [0] = dot_obj(sol_const), [1 + j] = dot_obj(sol_sub_j), [8 + j] = norms
+    double* gemm_scratch = nullptr;
+    bool have_const = false;
+};
+
+namespace {
+
+constexpr int RED_THREADS = 512;
+
+// deterministic block reduction (fixed tree)
+__device__ __forceinline__ double block_sum(double v, double* sh) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    __syncthreads();
+    if (lane == 0) sh[w] = v;
+    __syncthreads();
+    double t = (threadIdx.x < (blockDim.x >> 5)) ? sh[threadIdx.x] : 0.0;
+    if (w == 0) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    }
+    return t;  // valid in warp 0
+}
+__device__ __forceinline__ double block_max(double v, double* sh) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    __syncthreads();
+    if (lane == 0) sh[w] = v;
+    __syncthreads();
+    double t = (threadIdx.x < (blockDim.x >> 5)) ? sh[threadIdx.x] : 0.0;
+    if (w == 0) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t = fmax(t, __shfl_xor_sync(0xffffffffu, t, o));
+    }
+    return t;
+}
+
+// setup_rhs3 part 1 (qrchol.jl:23-44): the argument of the block Hessian product.
+// Column `const_col` (if >= 0) is the constant system: argument h (qrchol.jl:199-203).
+__global__ void rhs3_pre_kernel(int64_t q, int64_t ldq, int m, int const_col, const double* __restrict__ Rz,
+                                const double* __restrict__ Rs, const double* __restrict__ h,
+                                const unsigned char* __restrict__ dual_row, double* __restrict__ A) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y;
+    if (i >= q || j >= m) return;
+    const int64_t o = i + (int64_t)j * ldq;
+    if (j == const_col)
+        A[o] = h[i];
+    else
+        A[o] = dual_row[i] ? (-Rz[o] - Rs[o]) : Rz[o];
+}
+// part 2: rhs_sub.z from the product B = Htilde * A
+__global__ void rhs3_post_kernel(int64_t q, int64_t ldq, int m, int const_col, const double* __restrict__ B,
+                                 const double* __restrict__ Rs, const unsigned char* __restrict__ dual_row,
+                                 double* __restrict__ Vz) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y;
+    if (i >= q || j >= m) return;
+    const int64_t o = i + (int64_t)j * ldq;
+    if (j == const_col)
+        Vz[o] = B[o];
+    else
+        Vz[o] = dual_row[i] ? B[o] : (-B[o] - Rs[o]);
+}
+// r = rhs_sub.x + G' rhs_sub.z (qrchol.jl:59-60); rhs_sub.x = rhs.x, or -c for the constant system
+__global__ void subx_kernel(int64_t N, int64_t ldn, int m, int const_col, const double* __restrict__ Rx,
+                            const double* __restrict__ c, const double* __restrict__ T, double* __restrict__ Vx) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y;
+    if (i >= N || j >= m) return;
+    const int64_t o = i + (int64_t)j * ldn;
+    Vx[o] = ((j == const_col) ? -c[i] : Rx[o]) + T[o];
+}
+// sol_sub.z = Htilde (G x) - rhs_sub.z (qrchol.jl:84-91)
+__global__ void subz_kernel(int64_t q, int64_t ldq, int m, const double* __restrict__ B, double* __restrict__ Vz) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y;
+    if (i >= q || j >= m) return;
+    const int64_t o = i + (int64_t)j * ldq;
+    Vz[o] = B[o] - Vz[o];
+}
+// dot_obj (common.jl:222-224) of column j: c'x + h'z ; one block per column
+__global__ void __launch_bounds__(RED_THREADS)
+dot_obj_kernel(int64_t N, int64_t q, int64_t ldn, int64_t ldq, const double* __restrict__ c, const double* __restrict__ h,
+               const double* __restrict__ X, const double* __restrict__ Z, double* __restrict__ out) {
+    __shared__ double sh[32];
+    const int j = blockIdx.x;
+    double a = 0.0, b = 0.0;
+    for (int64_t i = threadIdx.x; i < N; i += RED_THREADS) a += c[i] * X[i + (int64_t)j * ldn];
+    for (int64_t i = threadIdx.x; i < q; i += RED_THREADS) b += h[i] * Z[i + (int64_t)j * ldq];
+    const double sa = block_sum(a, sh);
+    const double sb = block_sum(b, sh);
+    if (threadIdx.x == 0) out[j] = sa + sb;
+}
+// solve_subsystem4's tau elimination and the lift of solve_system (common.jl:133-189):
+//   tau = (rhs.tau + rhs.kap + dot_obj(sol_sub)) / (mu / taubar^2 - dot_obj(sol_const))
+//   x = sol_sub.x + tau xc ; z = sol_sub.z + tau zc ; s = h tau - rhs.z - G x ; kap = -mu/taubar^2 tau + rhs.kap
+__global__ void lift_kernel(int64_t N, int64_t q, int64_t ldn, int64_t ldq, int m, double mu_tt,
+                            const double* __restrict__ scal, const double* __restrict__ Rz, const double* __restrict__ Rtk,
+                            const double* __restrict__ h, const double* __restrict__ Vx, const double* __restrict__ Vz,
+                            const double* __restrict__ Gx, const double* __restrict__ xc, const double* __restrict__ zc,
+                            const double* __restrict__ Gxc, double* __restrict__ Dx, double* __restrict__ Dz,
+                            double* __restrict__ Ds, double* __restrict__ Dtk) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y;
+    if (j >= m) return;
+    const double rtau = Rtk[2 * j], rkap = Rtk[2 * j + 1];
+    const double tau = (rtau + rkap + scal[1 + j]) / (mu_tt - scal[0]);
+    if (i < N) Dx[i + (int64_t)j * ldn] = Vx[i + (int64_t)j * ldn] + tau * xc[i];
+    if (i < q) {
+        const int64_t o = i + (int64_t)j * ldq;
+        Dz[o] = Vz[o] + tau * zc[i];
+        Ds[o] = h[i] * tau - Rz[o] - (Gx[o] + tau * Gxc[i]);
+    }
+    if (i == 0) {
+        Dtk[2 * j] = tau;
+        Dtk[2 * j + 1] = -mu_tt * tau + rkap;
+    }
+}
+// apply_lhs (common.jl:86-125) minus the right-hand side, elementwise parts:
+//   res.x = G'z + tau c - rhs.x ; res.z = h tau - s - G x - rhs.z ; primal / dual direction split
+__global__ void reslin_kernel(int64_t N, int64_t q, int64_t ldn, int64_t ldq, int m, const double* __restrict__ c,
+                              const double* __restrict__ h, const unsigned char* __restrict__ dual_row,
+                              const double* __restrict__ Dz, const double* __restrict__ Ds, const double* __restrict__ Dtk,
+                              const double* __restrict__ T, const double* __restrict__ Gx, const double* __restrict__ Rx,
+                              const double* __restrict__ Rz, double* __restrict__ Ex, double* __restrict__ Ez,
+                              double* __restrict__ A) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y;
+    if (j >= m) return;
+    const double tau = Dtk[2 * j];
+    if (i < N) {
+        const int64_t o = i + (int64_t)j * ldn;
+        Ex[o] = T[o] + tau * c[i] - Rx[o];
+    }
+    if (i < q) {
+        const int64_t o = i + (int64_t)j * ldq;
+        Ez[o] = h[i] * tau - Ds[o] - Gx[o] - Rz[o];
+        A[o] = dual_row[i] ? Dz[o] : Ds[o];  // primal direction of the cone
+    }
+}
+//   res.s = H_slow(prim_dir) + dual_dir - rhs.s
+__global__ void ress_kernel(int64_t q, int64_t ldq, int m, const unsigned char* __restrict__ dual_row,
+                            const double* __restrict__ B, const double* __restrict__ Dz, const double* __restrict__ Ds,
+                            const double* __restrict__ Rs, double* __restrict__ Es) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y;
+    if (i >= q || j >= m) return;
+    const int64_t o = i + (int64_t)j * ldq;
+    Es[o] = B[o] + (dual_row[i] ? Ds[o] : Dz[o]) - Rs[o];
+}
+//   res.tau = -c'x - h'z - kap - rhs.tau ; res.kap = mu/taubar^2 tau + kap - rhs.kap ; inf-norm of the column
+__global__ void __launch_bounds__(RED_THREADS)
+resnorm_kernel(int64_t N, int64_t q, int64_t ldn, int64_t ldq, double mu_tt, const double* __restrict__ c,
+               const double* __restrict__ h, const double* __restrict__ Dx, const double* __restrict__ Dz,
+               const double* __restrict__ Dtk, const double* __restrict__ Rtk, const double* __restrict__ Ex,
+               const double* __restrict__ Ez, const double* __restrict__ Es, double* __restrict__ Etk,
+               double* __restrict__ norms) {
+    __shared__ double sh[32];
+    const int j = blockIdx.x;
+    double a = 0.0, b = 0.0, mx = 0.0;
+    bool bad = false;
+    for (int64_t i = threadIdx.x; i < N; i += RED_THREADS) {
+        a += c[i] * Dx[i + (int64_t)j * ldn];
+        const double e = fabs(Ex[i + (int64_t)j * ldn]);
+        bad |= !(e == e);
+        mx = fmax(mx, e);
+    }
+    for (int64_t i = threadIdx.x; i < q; i += RED_THREADS) {
+        const int64_t o = i + (int64_t)j * ldq;
+        b += h[i] * Dz[o];
+        const double e1 = fabs(Ez[o]), e2 = fabs(Es[o]);
+        bad |= !(e1 == e1) || !(e2 == e2);
+        mx = fmax(mx, fmax(e1, e2));
+    }
+    const double sa = block_sum(a, sh);
+    const double sb = block_sum(b, sh);
+    double m2 = block_max(bad ? INFINITY : mx, sh);
+    if (threadIdx.x == 0) {
+        const double tau = Dtk[2 * j], kap = Dtk[2 * j + 1];
+        const double et = -(sa + sb) - kap - Rtk[2 * j];
+        const double ek = mu_tt * tau + kap - Rtk[2 * j + 1];
+        Etk[2 * j] = et;
+        Etk[2 * j + 1] = ek;
+        m2 = fmax(m2, fmax(fabs(et), fabs(ek)));
+        if (!(et == et) || !(ek == ek) || m2 == INFINITY) m2 = NAN;  // a NaN residual is reported as NaN
+        norms[j] = m2;
+    }
+}
+// dir = dir_temp - dir (common.jl:52-53), all pieces of one column
+__global__ void refine_combine_kernel(int64_t N, int64_t q, const double* __restrict__ Tx, const double* __restrict__ Tz,
+                                      const double* __restrict__ Ts, const double* __restrict__ Ttk, double* __restrict__ Dx,
+                                      double* __restrict__ Dz, double* __restrict__ Ds, double* __restrict__ Dtk) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < N) Dx[i] = Tx[i] - Dx[i];
+    if (i < q) {
+        Dz[i] = Tz[i] - Dz[i];
+        Ds[i] = Ts[i] - Ds[i];
+    }
+    if (i < 2) Dtk[i] = Ttk[i] - Dtk[i];
+}
+
+}  // namespace
+
+// ----------------------------------------------------------------------------- host side
+static void free_vecs(HybVecs& v) {
+    cudaFree(v.x);
+    cudaFree(v.z);
+    cudaFree(v.s);
+    cudaFree(v.tk);
+    v = HybVecs();
+}
+static int alloc_vecs(HybVecs& v, const HybDirs& d, int m) {
+    HYB_CUDA(cudaMalloc(&v.x, sizeof(double) * d.ldn * m));
+    HYB_CUDA(cudaMalloc(&v.z, sizeof(double) * d.ldq * m));
+    HYB_CUDA(cudaMalloc(&v.s, sizeof(double) * d.ldq * m));
+    HYB_CUDA(cudaMalloc(&v.tk, sizeof(double) * 2 * m));
+    HYB_CUDA(cudaMemset(v.x, 0, sizeof(double) * d.ldn * m));
+    HYB_CUDA(cudaMemset(v.z, 0, sizeof(double) * d.ldq * m));
+    HYB_CUDA(cudaMemset(v.s, 0, sizeof(double) * d.ldq * m));
+    HYB_CUDA(cudaMemset(v.tk, 0, sizeof(double) * 2 * m));
+    return 0;
+}
+static HybVecs column(const HybVecs& v, const HybDirs& d, int j) {
+    HybVecs o;
+    o.x = v.x + (int64_t)j * d.ldn;
+    o.z = v.z + (int64_t)j * d.ldq;
+    o.s = v.s + (int64_t)j * d.ldq;
+    o.tk = v.tk + 2 * j;
+    return o;
+}
+
+void hyb_dirs_free(hyb_ctx* c) {
+    HybDirs* d = c->dirs;
+    if (!d) return;
+    cudaFree(d->c);
+    cudaFree(d->h);
+    cudaFree(d->dual_row);
+    free_vecs(d->rhs);
+    free_vecs(d->dir);
+    free_vecs(d->res);
+    free_vecs(d->tmp);
+    free_vecs(d->rrhs);
+    free_vecs(d->rdir);
+    cudaFree(d->A);
+    cudaFree(d->B);
+    cudaFree(d->Vx);
+    cudaFree(d->Vz);
+    cudaFree(d->Gx);
+    cudaFree(d->T);
+    cudaFree(d->xc);
+    cudaFree(d->zc);
+    cudaFree(d->Gxc);
+    cudaFree(d->scal);
+    cudaFree(d->gemm_scratch);
+    delete d;
+    c->dirs = nullptr;
+}
+
+static inline dim3 grid2(int64_t n, int m) { return dim3((unsigned)((n + 255) / 256), (unsigned)m); }
+
+// solve_system (common.jl:133-158) for m columns of `rhs` into `out`; with_const appends the
+// constant system of update_lhs (qrchol.jl:199-206) as column m and refreshes sol_const from it
+static int solve_system_dev(hyb_ctx* c, HybDirs& d, int m, bool with_const, const HybVecs& rhs, const HybVecs& out,
+                            double mu_tt) {
+    cudaStream_t st = c->st;
+    const int64_t N = d.N, q = d.q, ldn = d.ldn, ldq = d.ldq;
+    const int mm = m + (with_const ? 1 : 0), cc = with_const ? m : -1;
+    const int64_t nq = N > q ? N : q;
+    if (q > 0) {
+        rhs3_pre_kernel<<<grid2(q, mm), 256, 0, st>>>(q, ldq, mm, cc, rhs.z, rhs.s, d.h, d.dual_row, d.A);
+        HYB_CUDA(cudaGetLastError());
+        HYB_CHECK(hybi_cones_prod(st, c->cones, 4, d.A, ldq, d.B, ldq, mm));
+        rhs3_post_kernel<<<grid2(q, mm), 256, 0, st>>>(q, ldq, mm, cc, d.B, rhs.s, d.dual_row, d.Vz);
+        HYB_CUDA(cudaGetLastError());
+        g_misc_launches += 2;
+    }
+    if (N > 0) {
+        HYB_CHECK(hyb_gemm_t_small(st, q, N, c->GQ2, c->ldq, d.Vz, ldq, mm, d.T, ldn));
+        subx_kernel<<<grid2(N, mm), 256, 0, st>>>(N, ldn, mm, cc, rhs.x, d.c, d.T, d.Vx);
+        HYB_CUDA(cudaGetLastError());
+        HYB_CHECK(hyb_potrs_multi(st, c->chol, d.Vx, ldn, mm));
+        HYB_CHECK(hyb_gemm_n_small(st, q, N, c->GQ2, c->ldq, d.Vx, ldn, mm, d.Gx, ldq, d.gemm_scratch));
+        g_misc_launches += 4;
+    } else if (q > 0) {
+        HYB_CUDA(cudaMemsetAsync(d.Gx, 0, sizeof(double) * ldq * mm, st));
+    }
+    if (q > 0) {
+        HYB_CHECK(hybi_cones_prod(st, c->cones, 4, d.Gx, ldq, d.B, ldq, mm));
+        subz_kernel<<<grid2(q, mm), 256, 0, st>>>(q, ldq, mm, d.B, d.Vz);
+        HYB_CUDA(cudaGetLastError());
+        ++g_misc_launches;
+    }
+    if (with_const) {
+        if (N > 0) HYB_CUDA(cudaMemcpyAsync(d.xc, d.Vx + (int64_t)m * ldn, sizeof(double) * N, cudaMemcpyDeviceToDevice, st));
+        if (q > 0) {
+            HYB_CUDA(cudaMemcpyAsync(d.zc, d.Vz + (int64_t)m * ldq, sizeof(double) * q, cudaMemcpyDeviceToDevice, st));
+            HYB_CUDA(cudaMemcpyAsync(d.Gxc, d.Gx + (int64_t)m * ldq, sizeof(double) * q, cudaMemcpyDeviceToDevice, st));
+        }
+        dot_obj_kernel<<<1, RED_THREADS, 0, st>>>(N, q, ldn, ldq, d.c, d.h, d.xc, d.zc, d.scal);
+        HYB_CUDA(cudaGetLastError());
+        ++g_misc_launches;
+        d.have_const = true;
+    }
+    if (m > 0) {
+        if (!d.have_const) {
+            hyb_set_error("hyb_get_directions: no constant solution yet (call with refresh_const after each hyb_schur_factor)");
+            return -3;
+        }
+        dot_obj_kernel<<<m, RED_THREADS, 0, st>>>(N, q, ldn, ldq, d.c, d.h, d.Vx, d.Vz, d.scal + 1);
+        HYB_CUDA(cudaGetLastError());
+        lift_kernel<<<grid2(nq > 0 ? nq : 1, m), 256, 0, st>>>(N, q, ldn, ldq, m, mu_tt, d.scal, rhs.z, rhs.tk, d.h, d.Vx, d.Vz,
+                                                             d.Gx, d.xc, d.zc, d.Gxc, out.x, out.z, out.s, out.tk);
+        HYB_CUDA(cudaGetLastError());
+        g_misc_launches += 2;
+    }
+    return 0;
+}
+
+// res = LHS * dir - rhs (apply_lhs, common.jl:86-125, then common.jl:42) and the inf-norms into d.scal[8..]
+static int residual_dev(hyb_ctx* c, HybDirs& d, int m, const HybVecs& dir, const HybVecs& rhs, const HybVecs& res,
+                        double mu_tt, double* norms_dev) {
+    cudaStream_t st = c->st;
+    const int64_t N = d.N, q = d.q, ldn = d.ldn, ldq = d.ldq;
+    const int64_t nq = N > q ? N : q;
+    if (N > 0) {
+        HYB_CHECK(hyb_gemm_t_small(st, q, N, c->GQ2, c->ldq, dir.z, ldq, m, d.T, ldn));
+        HYB_CHECK(hyb_gemm_n_small(st, q, N, c->GQ2, c->ldq, dir.x, ldn, m, d.Gx, ldq, d.gemm_scratch));
+        g_misc_launches += 3;
+    } else if (q > 0) {
+        HYB_CUDA(cudaMemsetAsync(d.Gx, 0, sizeof(double) * ldq * m, st));
+    }
+    reslin_kernel<<<grid2(nq > 0 ? nq : 1, m), 256, 0, st>>>(N, q, ldn, ldq, m, d.c, d.h, d.dual_row, dir.z, dir.s, dir.tk, d.T,
+                                                           d.Gx, rhs.x, rhs.z, res.x, res.z, d.A);
+    HYB_CUDA(cudaGetLastError());
+    if (q > 0) {
+        HYB_CHECK(hybi_cones_prod(st, c->cones, 6, d.A, ldq, d.B, ldq, m));
+        ress_kernel<<<grid2(q, m), 256, 0, st>>>(q, ldq, m, d.dual_row, d.B, dir.z, dir.s, rhs.s, res.s);
+        HYB_CUDA(cudaGetLastError());
+    }
+    resnorm_kernel<<<m, RED_THREADS, 0, st>>>(N, q, ldn, ldq, mu_tt, d.c, d.h, dir.x, dir.z, dir.tk, rhs.tk, res.x, res.z,
+                                              res.s, res.tk, norms_dev);
+    HYB_CUDA(cudaGetLastError());
+    g_misc_launches += 3;
+    return 0;
+}
+
+static int copy_vecs(hyb_ctx* c, const HybDirs& d, const HybVecs& dst, const HybVecs& src) {
+    cudaStream_t st = c->st;
+    if (d.N > 0) HYB_CUDA(cudaMemcpyAsync(dst.x, src.x, sizeof(double) * d.N, cudaMemcpyDeviceToDevice, st));
+    if (d.q > 0) {
+        HYB_CUDA(cudaMemcpyAsync(dst.z, src.z, sizeof(double) * d.q, cudaMemcpyDeviceToDevice, st));
+        HYB_CUDA(cudaMemcpyAsync(dst.s, src.s, sizeof(double) * d.q, cudaMemcpyDeviceToDevice, st));
+    }
+    HYB_CUDA(cudaMemcpyAsync(dst.tk, src.tk, sizeof(double) * 2, cudaMemcpyDeviceToDevice, st));
+    return 0;
+}
+
+extern "C" {
+
+int hyb_dirs_setup(hyb_ctx* c, const double* cvec, const double* hvec) {
+    if (!c || !c->loaded) return -1;
+    HYB_CUDA(cudaSetDevice(c->device));
+    hyb_dirs_free(c);
+    HybDirs* d = new HybDirs();
+    c->dirs = d;
+    const int64_t N = d->N = c->N, q = d->q = c->q;
+    d->ldn = hyb_round_up(N > 0 ? N : 1, 16);
+    d->ldq = c->ldq;
+    const int M = HYB_MAX_RHS;
+    HYB_CUDA(cudaMalloc(&d->c, sizeof(double) * d->ldn));
+    HYB_CUDA(cudaMalloc(&d->h, sizeof(double) * d->ldq));
+    HYB_CUDA(cudaMalloc(&d->dual_row, (size_t)d->ldq));
+    if (N > 0) HYB_CUDA(cudaMemcpy(d->c, cvec, sizeof(double) * N, cudaMemcpyHostToDevice));
+    if (q > 0) HYB_CUDA(cudaMemcpy(d->h, hvec, sizeof(double) * q, cudaMemcpyHostToDevice));
+    std::vector<unsigned char> mask((size_t)d->ldq, 0);
+    for (const HybConeBlock& b : c->cones.blocks) {
+        if (!b.use_dual) continue;
+        const int64_t rows = (int64_t)b.dim * b.count;
+        for (int64_t i = 0; i < rows; ++i) mask[(size_t)(b.offset + i)] = 1;
+    }
+    HYB_CUDA(cudaMemcpy(d->dual_row, mask.data(), mask.size(), cudaMemcpyHostToDevice));
+    HYB_CHECK(alloc_vecs(d->rhs, *d, M));
+    HYB_CHECK(alloc_vecs(d->dir, *d, M));
+    HYB_CHECK(alloc_vecs(d->res, *d, M));
+    HYB_CHECK(alloc_vecs(d->tmp, *d, 1));
+    HYB_CHECK(alloc_vecs(d->rrhs, *d, 1));
+    HYB_CHECK(alloc_vecs(d->rdir, *d, 1));
+    HYB_CUDA(cudaMalloc(&d->A, sizeof(double) * d->ldq * M));
+    HYB_CUDA(cudaMalloc(&d->B, sizeof(double) * d->ldq * M));
+    HYB_CUDA(cudaMalloc(&d->Vz, sizeof(double) * d->ldq * M));
+    HYB_CUDA(cudaMalloc(&d->Gx, sizeof(double) * d->ldq * M));
+    HYB_CUDA(cudaMalloc(&d->Vx, sizeof(double) * d->ldn * M));
+    HYB_CUDA(cudaMalloc(&d->T, sizeof(double) * d->ldn * M));
+    HYB_CUDA(cudaMalloc(&d->xc, sizeof(double) * d->ldn));
+    HYB_CUDA(cudaMalloc(&d->zc, sizeof(double) * d->ldq));
+    HYB_CUDA(cudaMalloc(&d->Gxc, sizeof(double) * d->ldq));
+    HYB_CUDA(cudaMalloc(&d->scal, sizeof(double) * 16));
+    HYB_CUDA(cudaMalloc(&d->gemm_scratch, sizeof(double) * (q > 0 ? q : 1) * HYB_GEMV_SPLITS * M));
+    HYB_CUDA(cudaMemset(d->Vx, 0, sizeof(double) * d->ldn * M));
+    HYB_CUDA(cudaMemset(d->T, 0, sizeof(double) * d->ldn * M));
+    HYB_CUDA(cudaMemset(d->scal, 0, sizeof(double) * 16));
+    return 0;
+}
+
+int hyb_get_directions(hyb_ctx* c, int nrhs, const double* rhs, double* dir, int64_t ldv, int refresh_const,
+                       double tau_bar, double mu, double res_norm_cutoff, int max_ref_steps, double min_impr_tol,
+                       int* num_ref, double* res_norm, double* sol_const) {
+    if (!c || !c->loaded) return -1;
+    HybDirs* dp = c->dirs;
+    if (!dp) {
+        hyb_set_error("hyb_get_directions: call hyb_dirs_setup first");
+        return -3;
+    }
+    HybDirs& d = *dp;
+    const int m = nrhs;
+    if (m < 0 || m + (refresh_const ? 1 : 0) > HYB_MAX_RHS) {
+        hyb_set_error("hyb_get_directions: %d right-hand sides (+%d) exceed the batch limit %d", m, refresh_const ? 1 : 0,
+                      HYB_MAX_RHS);
+        return -3;
+    }
+    HYB_CUDA(cudaSetDevice(c->device));
+    if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(hyb_ensure_updated(c, c->loaded_scal));
+    cudaStream_t st = c->st;
+    const int64_t N = d.N, q = d.q, L = N + 2 * q + 2;
+    if (m > 0 && ldv < L) {
+        hyb_set_error("hyb_get_directions: ldv %lld < N + 2q + 2 = %lld", (long long)ldv, (long long)L);
+        return -3;
+    }
+    const size_t hp = sizeof(double) * (size_t)ldv;
+    auto up = [&](double* dst, int64_t ldd, int64_t off, int64_t len) -> cudaError_t {
+        if (len == 0 || m == 0) return cudaSuccess;
+        c->h2d_bytes += (int64_t)sizeof(double) * len * m;
+        return cudaMemcpy2DAsync(dst, sizeof(double) * ldd, rhs + off, hp, sizeof(double) * len, m, cudaMemcpyHostToDevice, st);
+    };
+    auto down = [&](double* src, int64_t lds_, int64_t off, int64_t len) -> cudaError_t {
+        if (len == 0 || m == 0) return cudaSuccess;
+        c->d2h_bytes += (int64_t)sizeof(double) * len * m;
+        return cudaMemcpy2DAsync(dir + off, hp, src, sizeof(double) * lds_, sizeof(double) * len, m, cudaMemcpyDeviceToHost, st);
+    };
+    HYB_CUDA(up(d.rhs.x, d.ldn, 0, N));
+    HYB_CUDA(up(d.rhs.z, d.ldq, N, q));
+    HYB_CUDA(up(d.rhs.tk, 2, N + q, 1));
+    HYB_CUDA(up(d.rhs.s, d.ldq, N + q + 1, q));
+    HYB_CUDA(up(d.rhs.tk + 1, 2, N + 2 * q + 1, 1));
+    const double mu_tt = mu / tau_bar / tau_bar;
+    KBEGIN(c);
+    HYB_CHECK(solve_system_dev(c, d, m, refresh_const != 0, d.rhs, d.dir, mu_tt));
+    double norms[HYB_MAX_RHS] = {0, 0, 0, 0};
+    for (int j = 0; j < m; ++j) {
+        if (num_ref) num_ref[j] = 0;
+        if (res_norm) res_norm[j] = 0.0;
+    }
+    if (max_ref_steps > 0 && m > 0) {
+        HYB_CHECK(residual_dev(c, d, m, d.dir, d.rhs, d.res, mu_tt, d.scal + 8));
+        HYB_CUDA(cudaMemcpyAsync(norms, d.scal + 8, sizeof(double) * m, cudaMemcpyDeviceToHost, st));
+        HYB_CUDA(cudaStreamSynchronize(st));
+        for (int j = 0; j < m; ++j) {
+            double rn = norms[j];
+            int nref = 0;
+            if (rn > res_norm_cutoff) {  // iterative refinement of column j (common.jl:46-79)
+                const HybVecs dj = column(d.dir, d, j), rj = column(d.rhs, d, j), ej = column(d.res, d, j);
+                HYB_CHECK(copy_vecs(c, d, d.tmp, dj));
+                bool prev_slow = false;
+                double prev = rn;
+                for (int it = 0; it < max_ref_steps; ++it) {
+                    ++nref;
+                    HYB_CHECK(copy_vecs(c, d, d.rrhs, ej));
+                    HYB_CHECK(solve_system_dev(c, d, 1, false, d.rrhs, d.rdir, mu_tt));
+                    const int64_t nq = N > q ? N : q;
+                    refine_combine_kernel<<<(unsigned)(((nq > 2 ? nq : 2) + 255) / 256), 256, 0, st>>>(
+                        N, q, d.tmp.x, d.tmp.z, d.tmp.s, d.tmp.tk, d.rdir.x, d.rdir.z, d.rdir.s, d.rdir.tk);
+                    HYB_CUDA(cudaGetLastError());
+                    ++g_misc_launches;
+                    HYB_CHECK(residual_dev(c, d, 1, d.rdir, rj, ej, mu_tt, d.scal + 12));
+                    double rn_new = 0.0;
+                    HYB_CUDA(cudaMemcpyAsync(&rn_new, d.scal + 12, sizeof(double), cudaMemcpyDeviceToHost, st));
+                    HYB_CUDA(cudaStreamSynchronize(st));
+                    if (rn_new != rn_new) {  // NaN: reported, the caller asserts like common.jl:81
+                        rn = rn_new;
+                        break;
+                    }
+                    if (rn_new >= rn) break;  // worse: keep the previous direction (still in column j)
+                    HYB_CHECK(copy_vecs(c, d, dj, d.rdir));
+                    HYB_CHECK(copy_vecs(c, d, d.tmp, d.rdir));
+                    rn = rn_new;
+                    if (rn < res_norm_cutoff) break;
+                    const bool curr_slow = rn > min_impr_tol * prev;
+                    if (prev_slow && curr_slow) break;
+                    prev = rn;
+                    prev_slow = curr_slow;
+                }
+            }
+            if (num_ref) num_ref[j] = nref;
+            if (res_norm) res_norm[j] = rn;
+        }
+    }
+    KEND(c);
+    HYB_CUDA(down(d.dir.x, d.ldn, 0, N));
+    HYB_CUDA(down(d.dir.z, d.ldq, N, q));
+    HYB_CUDA(down(d.dir.tk, 2, N + q, 1));
+    HYB_CUDA(down(d.dir.s, d.ldq, N + q + 1, q));
+    HYB_CUDA(down(d.dir.tk + 1, 2, N + 2 * q + 1, 1));
+    if (sol_const && d.have_const) {
+        if (N > 0) HYB_CUDA(d2h(c, sol_const, d.xc, sizeof(double) * N));
+        if (q > 0) HYB_CUDA(d2h(c, sol_const + N, d.zc, sizeof(double) * q));
+    }
+    HYB_CUDA(cudaStreamSynchronize(st));
+    ksync(c);
+    return 0;
+}
+
+}  // extern "C"

@@ -94,6 +94,117 @@ gemv_t_kernel(int64_t q, int64_t N, const double* __restrict__ G, int64_t ld, co
     if (lane == 0) y[col] = v;
 }
 
+// ---- the same two products for a few right-hand sides at once (the batched direction solves of
+// dirs.cu): G is read ONCE for all M columns, which is the whole point -- the products are bound by
+// the 8*q*N bytes of G, not by the M vectors.
+template <int M>
+__global__ void __launch_bounds__(128)
+gemm_n_partial_kernel(int64_t q, int64_t N, const double* __restrict__ G, int64_t ld, const double* __restrict__ X,
+                      int64_t ldx, double* __restrict__ scratch) {
+    __shared__ double xs[M][256];
+    const int64_t row0 = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    const int split = blockIdx.y, nsplit = gridDim.y;
+    const int64_t cols_per = (N + nsplit - 1) / nsplit;
+    const int64_t c_begin = split * cols_per;
+    const int64_t c_end = (c_begin + cols_per < N) ? c_begin + cols_per : N;
+    double a0[M], a1[M];
+#pragma unroll
+    for (int m = 0; m < M; ++m) a0[m] = a1[m] = 0.0;
+    const bool ok0 = row0 < q, ok1 = row0 + 128 < q;
+    for (int64_t cb = c_begin; cb < c_end; cb += 256) {
+        const int nc = (int)((c_end - cb < 256) ? (c_end - cb) : 256);
+        __syncthreads();
+#pragma unroll
+        for (int m = 0; m < M; ++m)
+            for (int i = threadIdx.x; i < nc; i += 128) xs[m][i] = X[cb + i + (int64_t)m * ldx];
+        __syncthreads();
+        const double* p = G + row0 + cb * ld;
+        int c = 0;
+        for (; c + 3 < nc; c += 4) {
+            double v0[4], v1[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                v0[u] = ok0 ? __ldg(p + (int64_t)(c + u) * ld) : 0.0;
+                v1[u] = ok1 ? __ldg(p + 128 + (int64_t)(c + u) * ld) : 0.0;
+            }
+#pragma unroll
+            for (int m = 0; m < M; ++m) {
+                a0[m] += v0[0] * xs[m][c] + v0[1] * xs[m][c + 1] + v0[2] * xs[m][c + 2] + v0[3] * xs[m][c + 3];
+                a1[m] += v1[0] * xs[m][c] + v1[1] * xs[m][c + 1] + v1[2] * xs[m][c + 2] + v1[3] * xs[m][c + 3];
+            }
+        }
+        for (; c < nc; ++c) {
+            const double v0 = ok0 ? __ldg(p + (int64_t)c * ld) : 0.0;
+            const double v1 = ok1 ? __ldg(p + 128 + (int64_t)c * ld) : 0.0;
+#pragma unroll
+            for (int m = 0; m < M; ++m) {
+                a0[m] += v0 * xs[m][c];
+                a1[m] += v1 * xs[m][c];
+            }
+        }
+    }
+#pragma unroll
+    for (int m = 0; m < M; ++m) {
+        double* sc = scratch + ((int64_t)m * nsplit + split) * q;
+        if (ok0) sc[row0] = a0[m];
+        if (ok1) sc[row0 + 128] = a1[m];
+    }
+}
+
+__global__ void gemm_n_reduce_kernel(int64_t q, int nsplit, const double* __restrict__ scratch, double* __restrict__ Y,
+                                     int64_t ldy) {
+    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int m = blockIdx.y;
+    if (r >= q) return;
+    double s = 0.0;
+    for (int k = 0; k < nsplit; ++k) s += scratch[((int64_t)m * nsplit + k) * q + r];
+    Y[r + (int64_t)m * ldy] = s;
+}
+
+template <int M>
+__global__ void __launch_bounds__(256)
+gemm_t_kernel(int64_t q, int64_t N, const double* __restrict__ G, int64_t ld, const double* __restrict__ Z, int64_t ldz,
+              double* __restrict__ Y, int64_t ldy) {
+    const int lane = threadIdx.x & 31;
+    const int64_t col = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (col >= N) return;
+    const double* p = G + col * ld;
+    double a0[M], a1[M];
+#pragma unroll
+    for (int m = 0; m < M; ++m) a0[m] = a1[m] = 0.0;
+    const int64_t q2 = q & ~(int64_t)1;
+    int64_t r = 2 * lane;
+    for (; r + 64 < q2; r += 128) {
+        const double2 g0 = __ldg((const double2*)(p + r)), g1 = __ldg((const double2*)(p + r + 64));
+#pragma unroll
+        for (int m = 0; m < M; ++m) {
+            const double2 z0 = __ldg((const double2*)(Z + r + (int64_t)m * ldz));
+            const double2 z1 = __ldg((const double2*)(Z + r + 64 + (int64_t)m * ldz));
+            a0[m] += g0.x * z0.x + g0.y * z0.y;
+            a1[m] += g1.x * z1.x + g1.y * z1.y;
+        }
+    }
+    for (; r < q2; r += 64) {
+        const double2 g0 = __ldg((const double2*)(p + r));
+#pragma unroll
+        for (int m = 0; m < M; ++m) {
+            const double2 z0 = __ldg((const double2*)(Z + r + (int64_t)m * ldz));
+            a0[m] += g0.x * z0.x + g0.y * z0.y;
+        }
+    }
+    if (lane == 0 && (q & 1)) {
+#pragma unroll
+        for (int m = 0; m < M; ++m) a1[m] += p[q - 1] * Z[q - 1 + (int64_t)m * ldz];
+    }
+#pragma unroll
+    for (int m = 0; m < M; ++m) {
+        double v = a0[m] + a1[m];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) Y[col + (int64_t)m * ldy] = v;
+    }
+}
+
 }  // namespace
 
 int hyb_gemv_n(cudaStream_t st, int64_t q, int64_t N, const double* G, int64_t ld, const double* x, double* y,
@@ -122,6 +233,48 @@ int hyb_gemv_t(cudaStream_t st, int64_t q, int64_t N, const double* G, int64_t l
     return 0;
 }
 
+
+// Y (q x M) = G X (N x M), M <= HYB_MAX_RHS ; scratch must hold M * HYB_GEMV_SPLITS * q doubles
+int hyb_gemm_n_small(cudaStream_t st, int64_t q, int64_t N, const double* G, int64_t ld, const double* X, int64_t ldx,
+                     int M, double* Y, int64_t ldy, double* scratch) {
+    if (q == 0 || M <= 0) return 0;
+    if (N == 0) {
+        HYB_CUDA(cudaMemset2DAsync(Y, sizeof(double) * ldy, 0, sizeof(double) * q, M, st));
+        return 0;
+    }
+    dim3 grid((unsigned)((q + 255) / 256), HYB_GEMV_SPLITS);
+    switch (M) {
+        case 1: gemm_n_partial_kernel<1><<<grid, 128, 0, st>>>(q, N, G, ld, X, ldx, scratch); break;
+        case 2: gemm_n_partial_kernel<2><<<grid, 128, 0, st>>>(q, N, G, ld, X, ldx, scratch); break;
+        case 3: gemm_n_partial_kernel<3><<<grid, 128, 0, st>>>(q, N, G, ld, X, ldx, scratch); break;
+        case 4: gemm_n_partial_kernel<4><<<grid, 128, 0, st>>>(q, N, G, ld, X, ldx, scratch); break;
+        default: hyb_set_error("hyb_gemm_n_small: M = %d out of range", M); return -3;
+    }
+    HYB_CUDA(cudaGetLastError());
+    gemm_n_reduce_kernel<<<dim3((unsigned)((q + 255) / 256), M), 256, 0, st>>>(q, HYB_GEMV_SPLITS, scratch, Y, ldy);
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// Y (N x M) = G' Z (q x M) ; Z columns 16-byte aligned (even ldz)
+int hyb_gemm_t_small(cudaStream_t st, int64_t q, int64_t N, const double* G, int64_t ld, const double* Z, int64_t ldz,
+                     int M, double* Y, int64_t ldy) {
+    if (N == 0 || M <= 0) return 0;
+    if (q == 0) {
+        HYB_CUDA(cudaMemset2DAsync(Y, sizeof(double) * ldy, 0, sizeof(double) * N, M, st));
+        return 0;
+    }
+    const unsigned grid = (unsigned)((N + 7) / 8);
+    switch (M) {
+        case 1: gemm_t_kernel<1><<<grid, 256, 0, st>>>(q, N, G, ld, Z, ldz, Y, ldy); break;
+        case 2: gemm_t_kernel<2><<<grid, 256, 0, st>>>(q, N, G, ld, Z, ldz, Y, ldy); break;
+        case 3: gemm_t_kernel<3><<<grid, 256, 0, st>>>(q, N, G, ld, Z, ldz, Y, ldy); break;
+        case 4: gemm_t_kernel<4><<<grid, 256, 0, st>>>(q, N, G, ld, Z, ldz, Y, ldy); break;
+        default: hyb_set_error("hyb_gemm_t_small: M = %d out of range", M); return -3;
+    }
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}
 
 // ---------------------------------------------------------------------------------------
 // y = G x without any allocation: the split-sum scratch of the gemv above lives in a

@@ -376,14 +376,20 @@ __device__ __forceinline__ void st_release(int* p, int v) {
 //    shortens the serial chain of the substitution to one shuffle + one FMA per row.
 constexpr int TRSV_THREADS = 512;
 
+// Both kernels are templates on R, the number of right-hand sides solved together (columns of x,
+// leading dimension ldx): the tiles of U -- all of the traffic -- are loaded once for the R
+// vectors, and the R serial substitutions of a block run on R different warps at the same time,
+// so R systems cost about the latency of one.
+
 // forward: solve U' y = b in place (x holds b on entry, y on exit)
+template <int R>
 __global__ void __launch_bounds__(TRSV_THREADS, 1)
-trsv_fwd_kernel(const double* __restrict__ U, int64_t ld, double* x, int N, int nblk, int* flags, int epoch) {
+trsv_fwd_kernel(const double* __restrict__ U, int64_t ld, double* x, int64_t ldx, int N, int nblk, int* flags, int epoch) {
     extern __shared__ double sm[];
     double* Us = sm;               // Us[k * LDS + i] = U[k][i] / U[i][i]  (k < i)
     double* dinv = sm + NB * LDS;  // 1 / U[i][i]
-    double* ys = dinv + NB;
-    double* rs = ys + NB;
+    double* ys = dinv + NB;        // [R][NB]
+    double* rs = ys + R * NB;      // [R][NB]
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     for (int ib = blockIdx.x; ib < nblk; ib += gridDim.x) {
         __syncthreads();  // previous block's substitution is done with Us
@@ -396,9 +402,11 @@ trsv_fwd_kernel(const double* __restrict__ U, int64_t ld, double* x, int N, int 
             Us[r * LDS + c] = (r < c && c < nbr) ? __ldg(dblk + r + (int64_t)c * ld) * dinv[c] : 0.0;
         }
         // column dots with the tiles above the diagonal: warp w owns columns 8w..8w+7
-        double acc[8];
+        double acc[R][8];
 #pragma unroll
-        for (int c = 0; c < 8; ++c) acc[c] = 0.0;
+        for (int rr = 0; rr < R; ++rr)
+#pragma unroll
+            for (int c = 0; c < 8; ++c) acc[rr][c] = 0.0;
         const int col0 = ib * NB + warp * 8;
         double2 nx0[8], nx1[8];
         auto load_tile = [&](int jb) {
@@ -422,35 +430,45 @@ trsv_fwd_kernel(const double* __restrict__ U, int64_t ld, double* x, int N, int 
                 }
             }
             __syncthreads();
-            if (tid < NB) ys[tid] = __ldcg(&x[jb * NB + tid]);
+            if (tid < R * NB) ys[tid] = __ldcg(&x[jb * NB + (tid & (NB - 1)) + (int64_t)(tid >> 7) * ldx]);
             __syncthreads();
-            const double y0 = ys[2 * lane], y1 = ys[2 * lane + 1], y2 = ys[64 + 2 * lane], y3 = ys[65 + 2 * lane];
 #pragma unroll
-            for (int c = 0; c < 8; ++c) acc[c] += (nx0[c].x * y0 + nx0[c].y * y1) + (nx1[c].x * y2 + nx1[c].y * y3);
+            for (int rr = 0; rr < R; ++rr) {
+                const double* yr = ys + rr * NB;
+                const double y0 = yr[2 * lane], y1 = yr[2 * lane + 1], y2 = yr[64 + 2 * lane], y3 = yr[65 + 2 * lane];
+#pragma unroll
+                for (int c = 0; c < 8; ++c)
+                    acc[rr][c] += (nx0[c].x * y0 + nx0[c].y * y1) + (nx1[c].x * y2 + nx1[c].y * y3);
+            }
             if (jb + 1 < ib) load_tile(jb + 1);
         }
 #pragma unroll
-        for (int c = 0; c < 8; ++c) {
-            double v = acc[c];
+        for (int rr = 0; rr < R; ++rr)
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-            acc[c] = v;
-        }
+            for (int c = 0; c < 8; ++c) {
+                double v = acc[rr][c];
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                acc[rr][c] = v;
+            }
         __syncthreads();  // everyone is done with ys; Us fully staged
         if (lane == 0) {
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                const int col = col0 + c;
-                rs[warp * 8 + c] = (col < N) ? (x[col] - acc[c]) * dinv[warp * 8 + c] : 0.0;
-            }
+            for (int rr = 0; rr < R; ++rr)
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    const int col = col0 + c;
+                    rs[rr * NB + warp * 8 + c] = (col < N) ? (x[col + (int64_t)rr * ldx] - acc[rr][c]) * dinv[warp * 8 + c] : 0.0;
+                }
         }
         __syncthreads();
         // y = U11^-T r by forward substitution on the pre-scaled block: with r~_i = r_i / U_ii,
-        // y_k = r~_k and r~_i -= (U[k][i] / U_ii) y_k.  One warp, 4 rows per lane in registers.
-        if (warp == 0) {
+        // y_k = r~_k and r~_i -= (U[k][i] / U_ii) y_k.  One warp per right-hand side, 4 rows per
+        // lane in registers.
+        if (warp < R) {
             double rv[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) rv[j] = rs[lane + 32 * j];
+            for (int j = 0; j < 4; ++j) rv[j] = rs[warp * NB + lane + 32 * j];
 #pragma unroll
             for (int slot = 0; slot < 4; ++slot) {
 #pragma unroll 8
@@ -465,7 +483,7 @@ trsv_fwd_kernel(const double* __restrict__ U, int64_t ld, double* x, int N, int 
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 const int row = ib * NB + lane + 32 * j;
-                if (row < N) x[row] = rv[j];
+                if (row < N) x[row + (int64_t)warp * ldx] = rv[j];
             }
         }
         __syncthreads();
@@ -474,13 +492,14 @@ trsv_fwd_kernel(const double* __restrict__ U, int64_t ld, double* x, int N, int 
 }
 
 // backward: solve U x = y in place
+template <int R>
 __global__ void __launch_bounds__(TRSV_THREADS, 1)
-trsv_bwd_kernel(const double* __restrict__ U, int64_t ld, double* x, int N, int nblk, int* flags, int epoch) {
+trsv_bwd_kernel(const double* __restrict__ U, int64_t ld, double* x, int64_t ldx, int N, int nblk, int* flags, int epoch) {
     extern __shared__ double sm[];
     double* Us = sm;               // Us[i * LDS + k] = U[i][k] / U[i][i]  (i < k)
     double* dinv = sm + NB * LDS;
-    double* xs = dinv + NB;
-    double* part = xs + NB;  // [4][NB]
+    double* xs = dinv + NB;        // [R][NB]
+    double* part = xs + R * NB;    // [R][4][NB]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, r = tid & (NB - 1), quarter = tid >> 7;
     for (int ib = nblk - 1 - (int)blockIdx.x; ib >= 0; ib -= gridDim.x) {
         __syncthreads();
@@ -494,7 +513,9 @@ trsv_bwd_kernel(const double* __restrict__ U, int64_t ld, double* x, int N, int 
         }
         const int row = ib * NB + r;
         const bool row_ok = row < N;
-        double acc = 0.0;
+        double acc[R];
+#pragma unroll
+        for (int v = 0; v < R; ++v) acc[v] = 0.0;
         double nx[32];
         auto load_tile = [&](int jb) {
             const int ncol = min(NB, N - jb * NB);
@@ -511,31 +532,41 @@ trsv_bwd_kernel(const double* __restrict__ U, int64_t ld, double* x, int N, int 
                 }
             }
             __syncthreads();
-            if (tid < NB) xs[tid] = (jb * NB + tid < N) ? __ldcg(&x[jb * NB + tid]) : 0.0;
-            __syncthreads();
-            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-#pragma unroll
-            for (int c = 0; c < 32; c += 4) {
-                a0 += nx[c] * xs[quarter * 32 + c];
-                a1 += nx[c + 1] * xs[quarter * 32 + c + 1];
-                a2 += nx[c + 2] * xs[quarter * 32 + c + 2];
-                a3 += nx[c + 3] * xs[quarter * 32 + c + 3];
+            if (tid < R * NB) {
+                const int i = tid & (NB - 1);
+                xs[tid] = (jb * NB + i < N) ? __ldcg(&x[jb * NB + i + (int64_t)(tid >> 7) * ldx]) : 0.0;
             }
-            acc += (a0 + a1) + (a2 + a3);
+            __syncthreads();
+#pragma unroll
+            for (int v = 0; v < R; ++v) {
+                const double* xv = xs + v * NB + quarter * 32;
+                double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll
+                for (int c = 0; c < 32; c += 4) {
+                    a0 += nx[c] * xv[c];
+                    a1 += nx[c + 1] * xv[c + 1];
+                    a2 += nx[c + 2] * xv[c + 2];
+                    a3 += nx[c + 3] * xv[c + 3];
+                }
+                acc[v] += (a0 + a1) + (a2 + a3);
+            }
             if (jb - 1 > ib) load_tile(jb - 1);
         }
         __syncthreads();
-        part[quarter * NB + r] = acc;
+#pragma unroll
+        for (int v = 0; v < R; ++v) part[(v * 4 + quarter) * NB + r] = acc[v];
         __syncthreads();
-        // x = U11^-1 (y - acc) by backward substitution on the row-scaled block, one warp
-        if (warp == 0) {
+        // x = U11^-1 (y - acc) by backward substitution on the row-scaled block, one warp per
+        // right-hand side
+        if (warp < R) {
+            const double* pv = part + warp * 4 * NB;
             double rv[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 const int i = lane + 32 * j;
                 const int rw = ib * NB + i;
-                const double s = (part[i] + part[NB + i]) + (part[2 * NB + i] + part[3 * NB + i]);
-                rv[j] = (rw < N) ? (x[rw] - s) * dinv[i] : 0.0;
+                const double s = (pv[i] + pv[NB + i]) + (pv[2 * NB + i] + pv[3 * NB + i]);
+                rv[j] = (rw < N) ? (x[rw + (int64_t)warp * ldx] - s) * dinv[i] : 0.0;
             }
 #pragma unroll
             for (int slot = 3; slot >= 0; --slot) {
@@ -551,7 +582,7 @@ trsv_bwd_kernel(const double* __restrict__ U, int64_t ld, double* x, int N, int 
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 const int rw = ib * NB + lane + 32 * j;
-                if (rw < N) x[rw] = rv[j];
+                if (rw < N) x[rw + (int64_t)warp * ldx] = rv[j];
             }
         }
         __syncthreads();
@@ -594,7 +625,7 @@ void hyb_chol_free(HybChol& ch) {
 
 constexpr int PANEL_SMEM = (NB * LDS + IB) * (int)sizeof(double);
 constexpr int TRSM_SMEM = (NB * LDS + NB * TLD + NB) * (int)sizeof(double);
-constexpr int TRSV_SMEM = (NB * LDS + 6 * NB) * (int)sizeof(double);
+constexpr int TRSV_SMEM = (NB * LDS + NB + 5 * HYB_MAX_RHS * NB) * (int)sizeof(double);
 int64_t g_potrf_launches = 0;
 
 // Right-looking factorization with one panel of look-ahead: while the bulk of step k's
@@ -654,14 +685,13 @@ int hyb_potrf(cudaStream_t st, HybChol& ch, int* info_out) {
     return 0;
 }
 
-int hyb_potrs(cudaStream_t st, HybChol& ch, double* x) {
-    if (ch.N == 0) return 0;
-    if (g_num_sms == 0) {
-        int dev = 0;
-        HYB_CUDA(cudaGetDevice(&dev));
-        HYB_CUDA(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
-        HYB_CUDA(cudaFuncSetAttribute(trsv_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TRSV_SMEM));
-        HYB_CUDA(cudaFuncSetAttribute(trsv_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TRSV_SMEM));
+template <int R>
+static int potrs_launch(cudaStream_t st, HybChol& ch, double* x, int64_t ldx) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        HYB_CUDA(cudaFuncSetAttribute(trsv_fwd_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, TRSV_SMEM));
+        HYB_CUDA(cudaFuncSetAttribute(trsv_bwd_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, TRSV_SMEM));
+        attr_set = true;
     }
     int N = (int)ch.N, nblk = (int)ch.nblk;
     int grid = nblk < g_num_sms ? nblk : g_num_sms;
@@ -669,14 +699,33 @@ int hyb_potrs(cudaStream_t st, HybChol& ch, double* x) {
     int64_t ld = ch.ld;
     int* flags = ch.flags;
     int epoch = ++ch.epoch;
-    void* args[] = {(void*)&U, (void*)&ld, (void*)&x, (void*)&N, (void*)&nblk, (void*)&flags, (void*)&epoch};
-    HYB_CUDA(cudaLaunchCooperativeKernel((void*)trsv_fwd_kernel, dim3(grid), dim3(TRSV_THREADS), args, TRSV_SMEM, st));
+    void* args[] = {(void*)&U, (void*)&ld, (void*)&x, (void*)&ldx, (void*)&N, (void*)&nblk, (void*)&flags, (void*)&epoch};
+    HYB_CUDA(cudaLaunchCooperativeKernel((void*)trsv_fwd_kernel<R>, dim3(grid), dim3(TRSV_THREADS), args, TRSV_SMEM, st));
     int epoch2 = ++ch.epoch;
-    void* args2[] = {(void*)&U, (void*)&ld, (void*)&x, (void*)&N, (void*)&nblk, (void*)&flags, (void*)&epoch2};
-    HYB_CUDA(cudaLaunchCooperativeKernel((void*)trsv_bwd_kernel, dim3(grid), dim3(TRSV_THREADS), args2, TRSV_SMEM, st));
+    void* args2[] = {(void*)&U, (void*)&ld, (void*)&x, (void*)&ldx, (void*)&N, (void*)&nblk, (void*)&flags, (void*)&epoch2};
+    HYB_CUDA(cudaLaunchCooperativeKernel((void*)trsv_bwd_kernel<R>, dim3(grid), dim3(TRSV_THREADS), args2, TRSV_SMEM, st));
     g_potrf_launches += 2;
     return 0;
 }
+
+int hyb_potrs_multi(cudaStream_t st, HybChol& ch, double* X, int64_t ldx, int R) {
+    if (ch.N == 0 || R <= 0) return 0;
+    if (g_num_sms == 0) {
+        int dev = 0;
+        HYB_CUDA(cudaGetDevice(&dev));
+        HYB_CUDA(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
+    }
+    switch (R) {
+        case 1: return potrs_launch<1>(st, ch, X, ldx);
+        case 2: return potrs_launch<2>(st, ch, X, ldx);
+        case 3: return potrs_launch<3>(st, ch, X, ldx);
+        case 4: return potrs_launch<4>(st, ch, X, ldx);
+    }
+    hyb_set_error("hyb_potrs_multi: %d right-hand sides (max %d)", R, HYB_MAX_RHS);
+    return -3;
+}
+
+int hyb_potrs(cudaStream_t st, HybChol& ch, double* x) { return hyb_potrs_multi(st, ch, x, ch.N, 1); }
 
 int64_t hyb_potrf_launch_count() { return g_potrf_launches; }
 

@@ -175,9 +175,14 @@ class B200QRCholSystemSolver(QRCholSystemSolver):
 
     device_G = True
 
-    def __init__(self, ctx: Context):
+    def __init__(self, ctx: Context, batched_dirs: bool = True):
         self.ctx = ctx
         self.lib = ctx.lib
+        # device-resident get_directions in batched pairs (hyb_get_directions); False keeps the
+        # reference's one-direction-at-a-time call pattern through the generic host code
+        self.batched_dirs = batched_dirs
+        self._dev_const_stale = True
+        self._host_const_stale = True
         self.time_assemble_ms = 0.0
         self.time_fact_ms = 0.0
         self.num_updates = 0
@@ -200,9 +205,16 @@ class B200QRCholSystemSolver(QRCholSystemSolver):
         cones.mark_model_loaded()
         self.setup_point_sub(solver)
 
+    def set_point_sub_rhs(self, solver) -> None:  # common.jl:211-220 (also on modify)
+        super().set_point_sub_rhs(solver)
+        m = solver.model
+        cv, hv = f64(m.c), f64(m.h)
+        self.ctx.check(self.lib.hyb_dirs_setup(self.ctx.ptr, dptr(cv), dptr(hv)), "hyb_dirs_setup")
+        self._dev_const_stale = self._host_const_stale = True
+
     # ---- update_lhs (qrchol.jl:189-207) ------------------------------------------
     def update_lhs(self, solver) -> None:
-        model, cones = solver.model, solver.cones
+        cones = solver.cones
         cones._sync()
         ta, tf, kind = C.c_double(0), C.c_double(0), C.c_int(0)
         rc = self.ctx.check(
@@ -210,13 +222,60 @@ class B200QRCholSystemSolver(QRCholSystemSolver):
         )
         self.time_assemble_ms += ta.value
         self.time_fact_ms += tf.value
+        self._after_factor(solver, tf.value, kind.value, rc)
+
+    def _after_factor(self, solver, tf_ms, kind, rc) -> None:
         self.num_updates += 1
-        self.last_fact_kind = kind.value
-        solver.time_upfact += tf.value * 1e-3
+        self.last_fact_kind = kind
+        solver.time_upfact += tf_ms * 1e-3
         if rc > 0:
             print("positive definite linear system factorization failed")
-        self.rhs_const.z[:] = cones.block_hess_prod(model.h)
-        self.solve_subsystem3(solver, self.sol_const, self.rhs_const)
+        # the constant system (qrchol.jl:199-206) is solved with the first batch of directions
+        # (hyb_get_directions, refresh_const) or, for the host call pattern, right here
+        self._dev_const_stale = self._host_const_stale = True
+        if not self.batched_dirs:
+            self._ensure_host_const(solver)
+
+    def _ensure_host_const(self, solver) -> None:
+        if self._host_const_stale:
+            self.rhs_const.z[:] = solver.cones.block_hess_prod(solver.model.h)
+            self.solve_subsystem3(solver, self.sol_const, self.rhs_const)
+            self._host_const_stale = False
+
+    def solve_subsystem4(self, solver, sol, rhs) -> None:
+        self._ensure_host_const(solver)
+        super().solve_subsystem4(solver, sol, rhs)
+
+    # ---- get_directions (common.jl:22-83), device-resident and batched --------------
+    def get_directions_batch(self, stepper, solver, rhs_points, dir_points) -> None:
+        import math
+
+        solver.cones._sync()
+        m = len(rhs_points)
+        L = rhs_points[0].vec.size
+        rhs = np.empty((L, m), order="F")
+        for j, r in enumerate(rhs_points):
+            rhs[:, j] = r.vec
+        out = np.empty((L, m), order="F")
+        nref = (C.c_int * m)()
+        rn = (C.c_double * m)()
+        sc = np.empty(self.N + self.q) if self._dev_const_stale else None
+        self.ctx.check(
+            self.lib.hyb_get_directions(
+                self.ctx.ptr, m, dptr(rhs), dptr(out), L, int(self._dev_const_stale), float(solver.point.tau), float(solver.mu),
+                float(solver.res_norm_cutoff), int(solver.max_ref_steps), 0.5, nref, rn, dptr(sc) if sc is not None else None,
+            ),
+            "hyb_get_directions",
+        )
+        if sc is not None:
+            self.sol_const.x[:] = sc[: self.N]
+            self.sol_const.z[:] = sc[self.N :]
+            self._dev_const_stale = self._host_const_stale = False
+        for j, d in enumerate(dir_points):
+            d.vec[:] = out[:, j]
+            stepper.last_num_ref += int(nref[j])
+            assert not math.isnan(rn[j]), "NaN residual in direction solve"
+            solver.worst_dir_res = max(solver.worst_dir_res, float(rn[j]))
 
     # ---- setup_rhs3 (qrchol.jl:23-44) --------------------------------------------
     def setup_rhs3(self, solver, rhs, sol, rhs_sub) -> None:
@@ -263,7 +322,8 @@ class B200QRCholSystemSolver(QRCholSystemSolver):
         pass
 
 
-def make_gpu_solver(device: int = 0, dist=None, use_peer: bool = True, mode: str = "rootworker", **solver_kwargs):
+def make_gpu_solver(device: int = 0, dist=None, use_peer: bool = True, mode: str = "rootworker", batched_dirs: bool = True,
+                    **solver_kwargs):
     """Solver wired to the GPU backends (what `Hypatia.Optimizer(syssolver =
     B200QRCholSystemSolver{Float64}(), use_dense_model = true)` selects in Julia).
 
@@ -288,5 +348,5 @@ def make_gpu_solver(device: int = 0, dist=None, use_peer: bool = True, mode: str
         solver = Solver(ss.cones_factory, ss, **solver_kwargs)
         solver.setup_comm = comm  # rank 0 does the preprocessing QR and broadcasts its outcome
         return solver
-    ss = B200QRCholSystemSolver(ctx)
+    ss = B200QRCholSystemSolver(ctx, batched_dirs=batched_dirs)
     return Solver(ss.cones_factory, ss, **solver_kwargs)

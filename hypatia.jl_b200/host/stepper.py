@@ -47,6 +47,7 @@ class CombinedStepper:
         m = solver.model
         self.prev_alpha = 1.0
         self.rhs = Point(m.n, m.p, m.q)
+        self.rhs2 = Point(m.n, m.p, m.q)  # second right-hand side of a batched pair
         self.dir = Point(m.n, m.p, m.q)
         self.temp = Point(m.n, m.p, m.q)
         self.dir_cent = Point(m.n, m.p, m.q)
@@ -71,12 +72,35 @@ class CombinedStepper:
         solver.syssolver.update_lhs(solver)
         solver.time_upsys += time.time() - t0
 
-        for builder, store, needs_dir in (
-            (update_rhs_cent, self.dir_cent, False),
-            (update_rhs_centadj, self.dir_centadj, True),
-            (update_rhs_pred, self.dir_pred, False),
-            (update_rhs_predadj, self.dir_predadj, True),
-        ):
+        if getattr(solver.syssolver, "batched_dirs", False):
+            # Device-resident direction solves: the two unadjusted directions are independent of
+            # each other, and each adjustment needs only its own unadjusted direction
+            # (combined.jl:74-95), so the four solves run as two batched pairs.
+            ss = solver.syssolver
+            for (b1, d1), (b2, d2), needs_dir in (
+                ((update_rhs_cent, self.dir_cent), (update_rhs_pred, self.dir_pred), False),
+                ((update_rhs_centadj, self.dir_centadj), (update_rhs_predadj, self.dir_predadj), True),
+            ):
+                t0 = time.time()
+                if needs_dir:
+                    b1(solver, self.rhs, self.dir_cent)
+                    b2(solver, self.rhs2, self.dir_pred)
+                else:
+                    b1(solver, self.rhs)
+                    b2(solver, self.rhs2)
+                solver.time_uprhs += time.time() - t0
+                t0 = time.time()
+                ss.get_directions_batch(self, solver, (self.rhs, self.rhs2), (d1, d2))
+                solver.time_getdir += time.time() - t0
+            builders = ()
+        else:
+            builders = (
+                (update_rhs_cent, self.dir_cent, False),
+                (update_rhs_centadj, self.dir_centadj, True),
+                (update_rhs_pred, self.dir_pred, False),
+                (update_rhs_predadj, self.dir_predadj, True),
+            )
+        for builder, store, needs_dir in builders:
             t0 = time.time()
             if needs_dir:
                 builder(solver, rhs, dir_)

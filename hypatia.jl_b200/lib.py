@@ -61,6 +61,12 @@ SIGNATURES = {
     "hyb_schur_get": (C.c_int, [C.c_void_p, c_double_p]),
     "hyb_G_mul": (C.c_int, [C.c_void_p, C.c_char, c_double_p, c_double_p]),
     "hyb_solve_subsystem3": (C.c_int, [C.c_void_p, c_double_p, c_double_p, c_double_p, c_double_p]),
+    "hyb_dirs_setup": (C.c_int, [C.c_void_p, c_double_p, c_double_p]),
+    "hyb_get_directions": (
+        C.c_int,
+        [C.c_void_p, C.c_int, c_double_p, c_double_p, C.c_int64, C.c_int, C.c_double, C.c_double, C.c_double, C.c_int,
+         C.c_double, c_int_p, c_double_p, c_double_p],
+    ),
     "hyb_outer_prod": (
         C.c_int,
         [C.c_void_p, C.c_int64, C.c_int64, C.c_double, c_double_p, C.c_int64, C.c_double, c_double_p, C.c_int64],

@@ -187,13 +187,7 @@ class RootQRCholSystemSolver(RootAssembly, B200QRCholSystemSolver):
         tf, kind = C.c_double(0), C.c_int(0)
         rc = self.ctx.check(self.lib.hyb_schur_factor(self.ctx.ptr, C.byref(tf), C.byref(kind)), "hyb_schur_factor")
         self.time_fact_ms += tf.value
-        self.num_updates += 1
-        self.last_fact_kind = kind.value
-        solver.time_upfact += tf.value * 1e-3
-        if rc > 0:
-            print("positive definite linear system factorization failed")
-        self.rhs_const.z[:] = cones.block_hess_prod(model.h)
-        self.solve_subsystem3(solver, self.sol_const, self.rhs_const)
+        self._after_factor(solver, tf.value, kind.value, rc)
 
 
 class WorkerQRCholSystemSolver:

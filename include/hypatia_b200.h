@@ -123,6 +123,28 @@ int hyb_G_mul(hyb_ctx* ctx, char trans, const double* v, double* out);
  *   r = rhs_x + G' rhs_z ;  sol_x = fact \ r ;  sol_z = Htilde (G sol_x) - rhs_z */
 int hyb_solve_subsystem3(hyb_ctx* ctx, const double* rhs_x, const double* rhs_z, double* sol_x, double* sol_z);
 
+/* ---- device-resident direction solves: src/Solvers/systemsolvers/common.jl -------- */
+/* set_point_sub_rhs (common.jl:211-220): the model vectors c (N) and h (q) the direction solves
+ * need (rhs_const = (-c, h), dot_obj, apply_lhs).  Call after hyb_model_load and again whenever
+ * c or h change (modify, Solvers.jl:431-452). */
+int hyb_dirs_setup(hyb_ctx* ctx, const double* c, const double* h);
+/* get_directions (common.jl:22-83) for `nrhs` right-hand sides at once: solve_system
+ * (common.jl:133-158: setup_rhs3 qrchol.jl:23-44, solve_subsystem3 qrchol.jl:46-92,
+ * solve_subsystem4 common.jl:161-189), the residual apply_lhs(dir) - rhs (common.jl:86-125) and
+ * the refinement rounds (accepted while the inf-norm residual decreases; stops below
+ * res_norm_cutoff, after two slow rounds (> min_impr_tol x previous) or max_ref_steps), all on the
+ * device.  rhs / dir: nrhs columns of [x(N); z(q); tau; s(q); kap] (point.jl:31-62, p = 0) with
+ * leading dimension ldv.  The columns must be independent of each other (the stepper pairs
+ * (cent, pred) and (centadj, predadj), combined.jl:74-95).  refresh_const != 0 also solves the
+ * constant system of update_lhs (qrchol.jl:199-206: rhs_const.z = Htilde h, sol_const =
+ * solve_subsystem3(rhs_const)) in the same batch; it must be set on the first call after every
+ * hyb_schur_factor.  nrhs + (refresh_const ? 1 : 0) <= 4.  tau_bar = point.tau, mu = solver.mu.
+ * Out: num_ref[j] refinement solves used, res_norm[j] final residual inf-norm (NaN if the
+ * residual is NaN; the caller asserts like common.jl:81), sol_const [x(N); z(q)] if not NULL. */
+int hyb_get_directions(hyb_ctx* ctx, int nrhs, const double* rhs, double* dir, int64_t ldv, int refresh_const,
+                       double tau_bar, double mu, double res_norm_cutoff, int max_ref_steps, double min_impr_tol,
+                       int* num_ref, double* res_norm, double* sol_const);
+
 /* ---- dense helpers: src/linearalgebra/dense.jl ---------------------------------- */
 /* outer_prod!(A, B, alpha, beta) = BLAS.syrk!('U','T'), dense.jl:72-79:
  * C(N x N, upper) = alpha A'A + beta C with A K x N (lda), C (ldc) */

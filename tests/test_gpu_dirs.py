@@ -1,0 +1,110 @@
+"""Device-resident, batched get_directions (hyb_get_directions, csrc/dirs.cu) against the
+reference's one-direction-at-a-time pattern (systemsolvers/common.jl:22-189) driven from the
+host through the per-call C-ABI, and against the CPU oracle."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import hypatia_b200  # noqa: F401
+from hypatia_b200 import instances
+from hypatia_b200.gpu import make_gpu_solver
+from hypatia_b200.host.models import Point
+from hypatia_b200.host.syscommon import get_directions
+from hypatia_b200.host import stepper as st
+
+pytestmark = pytest.mark.gpu
+
+
+def _capture_state(model_fn, n_iters, **kw):
+    """Run n_iters iterations on the GPU path and return the solver frozen at the next
+    iteration's state (point accepted, cones loaded, residuals computed)."""
+    s = make_gpu_solver(0, iter_limit=n_iters, **kw)
+    s.load(model_fn())
+    s.solve()
+    return s
+
+
+MODELS = {
+    "block_multicone": lambda: instances.block_multicone(N=96, seed=3, psd_side=8),
+    "linearopt": lambda: instances.linearopt(m=30, n=80, seed=1),
+    "polymin_wsos_dual_barrier": lambda: instances.polymin(n=1, halfdeg=4, use_primal=True, seed=2),
+}
+
+
+@pytest.mark.parametrize("name", list(MODELS))
+@pytest.mark.parametrize("n_iters", [1, 6])
+def test_batched_directions_match_host_pattern(name, n_iters):
+    s = _capture_state(MODELS[name], n_iters)
+    ss, stepper, m = s.syssolver, s.stepper, s.model
+    assert ss.batched_dirs
+    # a fresh factorization at the frozen point, like the top of CombinedStepper.step
+    ss.update_lhs(s)
+    rhs1, rhs2 = Point(m.n, m.p, m.q), Point(m.n, m.p, m.q)
+    d1, d2 = Point(m.n, m.p, m.q), Point(m.n, m.p, m.q)
+    st.update_rhs_cent(s, rhs1)
+    st.update_rhs_pred(s, rhs2)
+    s.max_ref_steps = 5
+    for cutoff in (s.res_norm_cutoff, 0.0):  # 0.0 forces the refinement rounds
+        s.res_norm_cutoff = cutoff
+        stepper.last_num_ref = 0
+        ss._dev_const_stale = True
+        ss.get_directions_batch(stepper, s, (rhs1, rhs2), (d1, d2))
+        nref_dev = stepper.last_num_ref
+        # host pattern: one direction at a time through solve_system / apply_lhs
+        ss._host_const_stale = True
+        got = []
+        nref_host = 0
+        for rhs in (rhs1, rhs2):
+            stepper.rhs.vec[:] = rhs.vec
+            stepper.last_num_ref = 0
+            get_directions(stepper, s)
+            nref_host += stepper.last_num_ref
+            got.append(stepper.dir.vec.copy())
+        for dev, host in zip((d1, d2), got):
+            scale = np.max(np.abs(host)) + 1e-300
+            assert np.max(np.abs(dev.vec - host)) <= 1e-9 * scale
+        if cutoff > 0.0:
+            assert nref_dev == nref_host
+        else:
+            assert nref_dev >= 2  # both columns went through at least one refinement round
+    # adjustment pair
+    st.update_rhs_centadj(s, rhs1, d1)
+    st.update_rhs_predadj(s, rhs2, d2)
+    a1, a2 = Point(m.n, m.p, m.q), Point(m.n, m.p, m.q)
+    ss.get_directions_batch(stepper, s, (rhs1, rhs2), (a1, a2))
+    for rhs, dev in ((rhs1, a1), (rhs2, a2)):
+        stepper.rhs.vec[:] = rhs.vec
+        get_directions(stepper, s)
+        scale = np.max(np.abs(stepper.dir.vec)) + 1e-300
+        assert np.max(np.abs(dev.vec - stepper.dir.vec)) <= 1e-9 * scale
+
+
+@pytest.mark.parametrize("name", ["block_multicone", "linearopt"])
+def test_batched_and_unbatched_solves_agree(name):
+    a = make_gpu_solver(0, trace=True, batched_dirs=True)
+    b = make_gpu_solver(0, trace=True, batched_dirs=False)
+    for s in (a, b):
+        s.load(MODELS[name]())
+        s.solve()
+    assert a.status == b.status == "Optimal"
+    assert a.num_iters == b.num_iters
+    assert abs(a.primal_obj - b.primal_obj) <= 1e-9 * (1 + abs(b.primal_obj))
+    n = len(b.trace) // 2
+    assert np.allclose([r["mu"] for r in a.trace[:n]], [r["mu"] for r in b.trace[:n]], rtol=1e-8)
+
+
+@pytest.mark.parametrize("N,R", [(100, 2), (300, 3), (1000, 4), (129, 1)])
+def test_multi_rhs_wavefront_solves(N, R):
+    """potrs with R right-hand sides in one pair of wavefront kernels == R single solves."""
+    from hypatia_b200.lib import Context, dptr, f64
+
+    rng = np.random.default_rng(N + R)
+    A = rng.standard_normal((N, N))
+    A = A @ A.T + N * np.eye(N)
+    B = rng.standard_normal((N, R))
+    ctx = Context(0)
+    _, X, info = ctx.posdef_solve(A, B)
+    assert info == 0
+    ref = np.linalg.solve(A, B)
+    assert np.max(np.abs(X - ref)) <= 1e-10 * np.max(np.abs(ref))
