@@ -23,7 +23,7 @@ struct HybDirs {
     unsigned char* dual_row = nullptr;  // 1 where the row belongs to a dual-barrier cone
     HybVecs rhs, dir, res, tmp, rrhs, rdir;  // rrhs / rdir: single-column scratch of the refinement rounds
     double *A = nullptr, *B = nullptr, *Vx = nullptr, *Vz = nullptr, *Gx = nullptr, *T = nullptr;  // work, M columns
-    double *xc = nullptr, *zc = nullptr, *Gxc = nullptr;  // sol_const (common.jl:191-209) and G * sol_const.x
+    double *xc = nullptr, *zc = nullptr;  // sol_const (common.jl:191-209)
     double* scal = nullptr;     // device scalars: [0] = dot_obj(sol_const), [1 + j] = dot_obj(sol_sub_j), [8 + j] = norms
     double* gemm_scratch = nullptr;
     bool have_const = false;
@@ -122,13 +122,14 @@ dot_obj_kernel(int64_t N, int64_t q, int64_t ldn, int64_t ldq, const double* __r
 }
 // solve_subsystem4's tau elimination and the lift of solve_system (common.jl:133-189):
 //   tau = (rhs.tau + rhs.kap + dot_obj(sol_sub)) / (mu / taubar^2 - dot_obj(sol_const))
-//   x = sol_sub.x + tau xc ; z = sol_sub.z + tau zc ; s = h tau - rhs.z - G x ; kap = -mu/taubar^2 tau + rhs.kap
+//   x = sol_sub.x + tau xc ; z = sol_sub.z + tau zc ; kap = -mu/taubar^2 tau + rhs.kap
+// (s follows in lift_s_kernel from a fresh product G x, as common.jl:151-153 computes it: forming it
+// from G sol_sub.x + tau G xc instead loses digits when the two terms cancel near convergence)
 __global__ void lift_kernel(int64_t N, int64_t q, int64_t ldn, int64_t ldq, int m, double mu_tt,
-                            const double* __restrict__ scal, const double* __restrict__ Rz, const double* __restrict__ Rtk,
-                            const double* __restrict__ h, const double* __restrict__ Vx, const double* __restrict__ Vz,
-                            const double* __restrict__ Gx, const double* __restrict__ xc, const double* __restrict__ zc,
-                            const double* __restrict__ Gxc, double* __restrict__ Dx, double* __restrict__ Dz,
-                            double* __restrict__ Ds, double* __restrict__ Dtk) {
+                            const double* __restrict__ scal, const double* __restrict__ Rtk,
+                            const double* __restrict__ Vx, const double* __restrict__ Vz,
+                            const double* __restrict__ xc, const double* __restrict__ zc,
+                            double* __restrict__ Dx, double* __restrict__ Dz, double* __restrict__ Dtk) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int j = blockIdx.y;
     if (j >= m) return;
@@ -138,12 +139,20 @@ __global__ void lift_kernel(int64_t N, int64_t q, int64_t ldn, int64_t ldq, int 
     if (i < q) {
         const int64_t o = i + (int64_t)j * ldq;
         Dz[o] = Vz[o] + tau * zc[i];
-        Ds[o] = h[i] * tau - Rz[o] - (Gx[o] + tau * Gxc[i]);
     }
     if (i == 0) {
         Dtk[2 * j] = tau;
         Dtk[2 * j + 1] = -mu_tt * tau + rkap;
     }
+}
+//   s = h tau - rhs.z - G x (common.jl:151-153)
+__global__ void lift_s_kernel(int64_t q, int64_t ldq, int m, const double* __restrict__ h, const double* __restrict__ Rz,
+                              const double* __restrict__ Dtk, const double* __restrict__ Gx, double* __restrict__ Ds) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y;
+    if (i >= q || j >= m) return;
+    const int64_t o = i + (int64_t)j * ldq;
+    Ds[o] = h[i] * Dtk[2 * j] - Rz[o] - Gx[o];
 }
 // apply_lhs (common.jl:86-125) minus the right-hand side, elementwise parts:
 //   res.x = G'z + tau c - rhs.x ; res.z = h tau - s - G x - rhs.z ; primal / dual direction split
@@ -278,7 +287,6 @@ void hyb_dirs_free(hyb_ctx* c) {
     cudaFree(d->T);
     cudaFree(d->xc);
     cudaFree(d->zc);
-    cudaFree(d->Gxc);
     cudaFree(d->scal);
     cudaFree(d->gemm_scratch);
     delete d;
@@ -323,7 +331,6 @@ static int solve_system_dev(hyb_ctx* c, HybDirs& d, int m, bool with_const, cons
         if (N > 0) HYB_CUDA(cudaMemcpyAsync(d.xc, d.Vx + (int64_t)m * ldn, sizeof(double) * N, cudaMemcpyDeviceToDevice, st));
         if (q > 0) {
             HYB_CUDA(cudaMemcpyAsync(d.zc, d.Vz + (int64_t)m * ldq, sizeof(double) * q, cudaMemcpyDeviceToDevice, st));
-            HYB_CUDA(cudaMemcpyAsync(d.Gxc, d.Gx + (int64_t)m * ldq, sizeof(double) * q, cudaMemcpyDeviceToDevice, st));
         }
         dot_obj_kernel<<<1, RED_THREADS, 0, st>>>(N, q, ldn, ldq, d.c, d.h, d.xc, d.zc, d.scal);
         HYB_CUDA(cudaGetLastError());
@@ -337,24 +344,35 @@ static int solve_system_dev(hyb_ctx* c, HybDirs& d, int m, bool with_const, cons
         }
         dot_obj_kernel<<<m, RED_THREADS, 0, st>>>(N, q, ldn, ldq, d.c, d.h, d.Vx, d.Vz, d.scal + 1);
         HYB_CUDA(cudaGetLastError());
-        lift_kernel<<<grid2(nq > 0 ? nq : 1, m), 256, 0, st>>>(N, q, ldn, ldq, m, mu_tt, d.scal, rhs.z, rhs.tk, d.h, d.Vx, d.Vz,
-                                                             d.Gx, d.xc, d.zc, d.Gxc, out.x, out.z, out.s, out.tk);
+        lift_kernel<<<grid2(nq > 0 ? nq : 1, m), 256, 0, st>>>(N, q, ldn, ldq, m, mu_tt, d.scal, rhs.tk, d.Vx, d.Vz, d.xc, d.zc,
+                                                             out.x, out.z, out.tk);
         HYB_CUDA(cudaGetLastError());
         g_misc_launches += 2;
+        if (q > 0) {
+            // d.Gx <- G x for the lifted x; residual_dev reuses it (gx_ready) for the same direction
+            if (N > 0) {
+                HYB_CHECK(hyb_gemm_n_small(st, q, N, c->GQ2, c->ldq, out.x, ldn, m, d.Gx, ldq, d.gemm_scratch));
+                g_misc_launches += 2;
+            }
+            lift_s_kernel<<<grid2(q, m), 256, 0, st>>>(q, ldq, m, d.h, rhs.z, out.tk, d.Gx, out.s);
+            HYB_CUDA(cudaGetLastError());
+            ++g_misc_launches;
+        }
     }
     return 0;
 }
 
 // res = LHS * dir - rhs (apply_lhs, common.jl:86-125, then common.jl:42) and the inf-norms into d.scal[8..]
+// gx_ready: d.Gx already holds G * dir.x (left there by solve_system_dev for this very direction)
 static int residual_dev(hyb_ctx* c, HybDirs& d, int m, const HybVecs& dir, const HybVecs& rhs, const HybVecs& res,
-                        double mu_tt, double* norms_dev) {
+                        double mu_tt, double* norms_dev, bool gx_ready) {
     cudaStream_t st = c->st;
     const int64_t N = d.N, q = d.q, ldn = d.ldn, ldq = d.ldq;
     const int64_t nq = N > q ? N : q;
     if (N > 0) {
         HYB_CHECK(hyb_gemm_t_small(st, q, N, c->GQ2, c->ldq, dir.z, ldq, m, d.T, ldn));
-        HYB_CHECK(hyb_gemm_n_small(st, q, N, c->GQ2, c->ldq, dir.x, ldn, m, d.Gx, ldq, d.gemm_scratch));
-        g_misc_launches += 3;
+        if (!gx_ready) HYB_CHECK(hyb_gemm_n_small(st, q, N, c->GQ2, c->ldq, dir.x, ldn, m, d.Gx, ldq, d.gemm_scratch));
+        g_misc_launches += gx_ready ? 1 : 3;
     } else if (q > 0) {
         HYB_CUDA(cudaMemsetAsync(d.Gx, 0, sizeof(double) * ldq * m, st));
     }
@@ -422,7 +440,6 @@ int hyb_dirs_setup(hyb_ctx* c, const double* cvec, const double* hvec) {
     HYB_CUDA(cudaMalloc(&d->T, sizeof(double) * d->ldn * M));
     HYB_CUDA(cudaMalloc(&d->xc, sizeof(double) * d->ldn));
     HYB_CUDA(cudaMalloc(&d->zc, sizeof(double) * d->ldq));
-    HYB_CUDA(cudaMalloc(&d->Gxc, sizeof(double) * d->ldq));
     HYB_CUDA(cudaMalloc(&d->scal, sizeof(double) * 16));
     HYB_CUDA(cudaMalloc(&d->gemm_scratch, sizeof(double) * (q > 0 ? q : 1) * HYB_GEMV_SPLITS * M));
     HYB_CUDA(cudaMemset(d->Vx, 0, sizeof(double) * d->ldn * M));
@@ -480,7 +497,7 @@ int hyb_get_directions(hyb_ctx* c, int nrhs, const double* rhs, double* dir, int
         if (res_norm) res_norm[j] = 0.0;
     }
     if (max_ref_steps > 0 && m > 0) {
-        HYB_CHECK(residual_dev(c, d, m, d.dir, d.rhs, d.res, mu_tt, d.scal + 8));
+        HYB_CHECK(residual_dev(c, d, m, d.dir, d.rhs, d.res, mu_tt, d.scal + 8, true));
         HYB_CUDA(cudaMemcpyAsync(norms, d.scal + 8, sizeof(double) * m, cudaMemcpyDeviceToHost, st));
         HYB_CUDA(cudaStreamSynchronize(st));
         for (int j = 0; j < m; ++j) {
@@ -500,7 +517,7 @@ int hyb_get_directions(hyb_ctx* c, int nrhs, const double* rhs, double* dir, int
                         N, q, d.tmp.x, d.tmp.z, d.tmp.s, d.tmp.tk, d.rdir.x, d.rdir.z, d.rdir.s, d.rdir.tk);
                     HYB_CUDA(cudaGetLastError());
                     ++g_misc_launches;
-                    HYB_CHECK(residual_dev(c, d, 1, d.rdir, rj, ej, mu_tt, d.scal + 12));
+                    HYB_CHECK(residual_dev(c, d, 1, d.rdir, rj, ej, mu_tt, d.scal + 12, false));
                     double rn_new = 0.0;
                     HYB_CUDA(cudaMemcpyAsync(&rn_new, d.scal + 12, sizeof(double), cudaMemcpyDeviceToHost, st));
                     HYB_CUDA(cudaStreamSynchronize(st));

@@ -335,7 +335,7 @@ def make_gpu_solver(device: int = 0, dist=None, use_peer: bool = True, mode: str
     if dist is not None and dist.get_world_size() > 1 and mode == "rootworker":
         from .rootworker import make_rootworker_solver
 
-        return make_rootworker_solver(device, dist, **solver_kwargs)
+        return make_rootworker_solver(device, dist, batched_dirs=batched_dirs, **solver_kwargs)
     ctx = Context(device)
     if dist is not None and dist.get_world_size() > 1:
         import torch

@@ -150,8 +150,8 @@ class RootAssembly:
 class RootQRCholSystemSolver(RootAssembly, B200QRCholSystemSolver):
     """Rank 0: the single-GPU system solver plus the distributed Schur assembly."""
 
-    def __init__(self, ctx: Context, comm: Comm, device: int):
-        B200QRCholSystemSolver.__init__(self, ctx)
+    def __init__(self, ctx: Context, comm: Comm, device: int, batched_dirs: bool = True):
+        B200QRCholSystemSolver.__init__(self, ctx, batched_dirs=batched_dirs)
         self._rw_init(comm)
         self.device = device
 
@@ -244,7 +244,7 @@ class WorkerQRCholSystemSolver:
         pass
 
 
-def make_rootworker_solver(device: int, dist, **solver_kwargs):
+def make_rootworker_solver(device: int, dist, batched_dirs: bool = True, **solver_kwargs):
     import torch
 
     from .host.solver import Solver
@@ -253,7 +253,7 @@ def make_rootworker_solver(device: int, dist, **solver_kwargs):
     comm = Comm(dist, torch.device("cuda", device) if backend == "nccl" else torch.device("cpu"))
     if comm.rank == 0:
         ctx = Context(device)
-        ss = RootQRCholSystemSolver(ctx, comm, device)
+        ss = RootQRCholSystemSolver(ctx, comm, device, batched_dirs=batched_dirs)
         solver = Solver(ss.cones_factory, ss, **solver_kwargs)
     else:
         ss = WorkerQRCholSystemSolver(comm, device)

@@ -10,10 +10,28 @@ import hypatia_b200  # noqa: F401
 from hypatia_b200 import instances
 from hypatia_b200.gpu import make_gpu_solver
 from hypatia_b200.host.models import Point
-from hypatia_b200.host.syscommon import get_directions
+from hypatia_b200.host.syscommon import apply_lhs, get_directions
 from hypatia_b200.host import stepper as st
 
 pytestmark = pytest.mark.gpu
+
+
+def _host_residual(stepper, s, dir_vec, rhs_vec):
+    """inf-norm of LHS * dir - rhs evaluated by the host code (apply_lhs, common.jl:86-125)."""
+    stepper.dir.vec[:] = dir_vec
+    res = apply_lhs(stepper, s)
+    return float(np.max(np.abs(res.vec - rhs_vec)))
+
+
+def _same_solution(stepper, s, dev_vec, host_vec, rhs_vec):
+    """Two solves of the same (possibly ill-conditioned) system agree when they have the same
+    residual quality; their difference is then bounded by cond * eps, checked loosely."""
+    scale = np.max(np.abs(host_vec)) + 1e-300
+    assert np.max(np.abs(dev_vec - host_vec)) <= 1e-6 * scale
+    r_dev = _host_residual(stepper, s, dev_vec, rhs_vec)
+    r_host = _host_residual(stepper, s, host_vec, rhs_vec)
+    floor = 1e-13 * max(1.0, np.max(np.abs(rhs_vec)), scale)
+    assert r_dev <= 10.0 * r_host + floor, (r_dev, r_host)
 
 
 def _capture_state(model_fn, n_iters, **kw):
@@ -28,7 +46,10 @@ def _capture_state(model_fn, n_iters, **kw):
 MODELS = {
     "block_multicone": lambda: instances.block_multicone(N=96, seed=3, psd_side=8),
     "linearopt": lambda: instances.linearopt(m=30, n=80, seed=1),
-    "polymin_wsos_dual_barrier": lambda: instances.polymin(n=1, halfdeg=4, use_primal=True, seed=2),
+    "polymin_wsos": lambda: instances.polymin(n=1, halfdeg=4, seed=2),
+    # primal-form WSOS instance: the cone uses the dual barrier (z/s roles swapped, inverse products)
+    "wsos_dual_barrier": lambda: instances.KNOWN_ANSWER["wsosinterpnonnegative1"]()[0],
+    "epipersquare4": lambda: instances.KNOWN_ANSWER["epipersquare4"]()[0],
 }
 
 
@@ -61,9 +82,8 @@ def test_batched_directions_match_host_pattern(name, n_iters):
             get_directions(stepper, s)
             nref_host += stepper.last_num_ref
             got.append(stepper.dir.vec.copy())
-        for dev, host in zip((d1, d2), got):
-            scale = np.max(np.abs(host)) + 1e-300
-            assert np.max(np.abs(dev.vec - host)) <= 1e-9 * scale
+        for dev, host, rhs in zip((d1, d2), got, (rhs1, rhs2)):
+            _same_solution(stepper, s, dev.vec.copy(), host, rhs.vec)
         if cutoff > 0.0:
             assert nref_dev == nref_host
         else:
@@ -76,8 +96,7 @@ def test_batched_directions_match_host_pattern(name, n_iters):
     for rhs, dev in ((rhs1, a1), (rhs2, a2)):
         stepper.rhs.vec[:] = rhs.vec
         get_directions(stepper, s)
-        scale = np.max(np.abs(stepper.dir.vec)) + 1e-300
-        assert np.max(np.abs(dev.vec - stepper.dir.vec)) <= 1e-9 * scale
+        _same_solution(stepper, s, dev.vec.copy(), stepper.dir.vec.copy(), rhs.vec)
 
 
 @pytest.mark.parametrize("name", ["block_multicone", "linearopt"])
@@ -89,7 +108,7 @@ def test_batched_and_unbatched_solves_agree(name):
         s.solve()
     assert a.status == b.status == "Optimal"
     assert a.num_iters == b.num_iters
-    assert abs(a.primal_obj - b.primal_obj) <= 1e-9 * (1 + abs(b.primal_obj))
+    assert abs(a.primal_obj - b.primal_obj) <= 1e-7 * (1 + abs(b.primal_obj))  # north_star objective tolerance
     n = len(b.trace) // 2
     assert np.allclose([r["mu"] for r in a.trace[:n]], [r["mu"] for r in b.trace[:n]], rtol=1e-8)
 

@@ -52,6 +52,7 @@ def test_schur_matrix_and_subsystem_match_cpu():
     S_cpu = np.triu(cpu.syssolver.lhs)
     assert rel_err(S_gpu, S_cpu) < 1e-12
     assert gpu.syssolver.last_fact_kind == 0
+    gpu.syssolver._ensure_host_const(gpu)  # the constant solve is deferred to the first direction batch
     assert rel_err(gpu.syssolver.sol_const.vec, cpu.syssolver.sol_const.vec) < 1e-9
 
 
