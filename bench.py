@@ -215,8 +215,25 @@ def run_cpu_port(model, steps, warmup, preset_fact=None):
     }
 
 
+_JSON_FD = None
+
+
+def _claim_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries (NCCL's version banner, torchrun notes)
+    write to fd 1 behind Python's back, so everything but the result line is sent to stderr."""
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    os.write(_JSON_FD if _JSON_FD is not None else 1, (json.dumps(line) + "\n").encode())
+
+
 def main():
     args = parse_args()
+    _claim_stdout()
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
@@ -240,7 +257,7 @@ def main():
                              "schur_assemble_ms": res["assemble_ms"], "cholesky_ms": res["factor_ms"]},
             "e2e": {"value": res["iters_per_s"], "unit": "iterations/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         }
-        print(json.dumps(line))
+        emit(line)
         return
 
     os.environ.setdefault("NCCL_DEBUG", "WARN")  # keep NCCL's version banner off stdout (one JSON line only)
@@ -417,7 +434,7 @@ def main():
                       f"(CPU restatement of the reference, numpy/scipy OpenBLAS, {cores} host cores)",
             "schur_assemble_ms": res["assemble_ms"], "cholesky_ms": res["factor_ms"],
         }
-    print(json.dumps(line))
+    emit(line)
     if dist is not None:
         dist.destroy_process_group()
 
