@@ -40,6 +40,9 @@ static inline int64_t hyb_round_up(int64_t x, int64_t m) { return (x + m - 1) / 
 enum { HYB_GEMM_UPPER = 1, HYB_GEMM_CVEC = 2 /* internal: C is 16-byte aligned with even ldc */ };
 int hyb_gemm_tn(cudaStream_t st, int64_t M, int64_t N, int64_t K, double alpha, const double* A, int64_t lda,
                 const double* B, int64_t ldb, double beta, double* C, int64_t ldc, int flags);
+int hyb_gemm_tn_blockdiag(cudaStream_t st, int64_t M, int64_t N, int64_t K, int64_t step, int64_t batch, double alpha,
+                          const double* A, int64_t lda, const double* B, int64_t ldb, double beta, double* C,
+                          int64_t ldc);
 int64_t hyb_gemm_launch_count();
 int64_t hyb_potrf_launch_count();
 

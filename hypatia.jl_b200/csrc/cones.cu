@@ -587,6 +587,40 @@ psd_prod_kernel(int64_t count, int side, int64_t offset, int64_t mat_off, int64_
     smem_to_svec(A, side, prod + offset + c * dim + j * ldp, lane, 1.0);
 }
 
+// Wide products (many columns, e.g. the q x N matrix G*Q2 in the Schur assembly): the map
+// a -> svec(M smat(a) M') is linear, so per cone it is one dim x dim matrix, the symmetric Kronecker
+// product of M with itself (the reference builds the same matrix for its explicit Hessian,
+// arrayutilities.jl:287-324 symm_kron!), and the product for all columns is a block-diagonal GEMM
+// on the DMMA engine instead of count * m little 16 x 16 products.  With s_ij = 1 (i == j) or sqrt 2:
+//   H[(i,j),(k,l)] = s_ij / s_kl * (k == l ? M_ik M_jk : M_ik M_jl + M_il M_jk)
+// Stored K-major for hyb_gemm_tn_blockdiag: out[(c * dim + row) * ldh + col], row = (i,j), col = (k,l).
+__global__ void psd_skron_kernel(int64_t count, int side, int64_t mat_off, int op, const double* __restrict__ mats,
+                                 double* __restrict__ out, int ldh) {
+    const int dim = side * (side + 1) / 2;
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= count * dim * dim) return;
+    const int64_t c = e / ((int64_t)dim * dim);
+    const int rem = (int)(e - c * dim * dim);
+    const int row = rem / dim, col = rem - row * dim;
+    auto unpack = [](int k, int& r, int& cc) {
+        cc = (int)((sqrt(8.0 * k + 1.0) - 1.0) * 0.5);
+        while (cc * (cc + 1) / 2 > k) --cc;
+        while ((cc + 1) * (cc + 2) / 2 <= k) ++cc;
+        r = k - cc * (cc + 1) / 2;
+    };
+    int i, j, k, l;
+    unpack(row, i, j);
+    unpack(col, k, l);
+    const int which = (op == HYB_OP_HESS) ? 3 : (op == HYB_OP_INV_HESS) ? 0 : (op == HYB_OP_SQRT_HESS) ? 2 : 1;
+    const double* G = mats + mat_off + c * 4 * side * side + which * side * side;
+    const bool tr = (op == HYB_OP_SQRT_HESS);  // M = Uinv'
+    auto Mel = [&](int r, int cc) { return tr ? G[cc + r * side] : G[r + cc * side]; };
+    double v = (k == l) ? Mel(i, k) * Mel(j, k) : Mel(i, k) * Mel(j, l) + Mel(i, l) * Mel(j, k);
+    if (i != j) v *= RT2;
+    if (k != l) v *= (1.0 / RT2);
+    out[(c * dim + row) * ldh + col] = v;
+}
+
 // dder3 = svec(S S'), S = Xinv D Uinv  (possemideftri.jl:194-204)
 __global__ void __launch_bounds__(PSD_WARPS * 32)
 psd_dder3_kernel(int64_t count, int side, int64_t offset, int64_t mat_off, const double* __restrict__ mats,
@@ -731,6 +765,7 @@ void hybi_cones_free(HybCones& cs) {
     cudaFree(cs.tmp);
     cudaFree(cs.aux);
     cudaFree(cs.mats);
+    cudaFree(cs.skron);
     cudaFree(cs.item_flag);
     cudaFree(cs.item_prox);
     cudaFree(cs.red_flag);
@@ -847,6 +882,30 @@ int hybi_cones_prod(cudaStream_t st, HybCones& cs, int which, const double* arr,
                 if (b.dense) {
                     HYB_CHECK(hybd_psd_prod(st, (HybDensePsd*)b.dense, op, arr + b.offset, lda, prod + b.offset, ldp, m));
                     break;
+                }
+                {
+                    // many columns: block-diagonal DMMA GEMM with the symmetric-Kronecker matrices
+                    const int64_t ldh = (b.dim + 1) & ~(int64_t)1;
+                    const int64_t need = b.count * b.dim * ldh;
+                    const bool aligned = !(b.offset & 1) && !(b.dim & 1) && !(lda & 1) && !((uintptr_t)arr & 15);
+                    if (m >= 64 && b.dim >= 28 && aligned && b.count <= 65535 && need <= ((int64_t)1 << 28)) {
+                        if (cs.skron_cap < need) {
+                            HYB_CUDA(cudaStreamSynchronize(st));
+                            cudaFree(cs.skron);
+                            cs.skron = nullptr;
+                            cs.skron_cap = 0;
+                            HYB_CUDA(cudaMalloc(&cs.skron, sizeof(double) * need));
+                            cs.skron_cap = need;
+                        }
+                        if (ldh != b.dim) HYB_CUDA(cudaMemsetAsync(cs.skron, 0, sizeof(double) * need, st));
+                        psd_skron_kernel<<<nblocks(b.count * b.dim * b.dim, 256), 256, 0, st>>>(b.count, b.side, b.mat_off, op,
+                                                                                              cs.mats, cs.skron, (int)ldh);
+                        LAUNCHED();
+                        HYB_CUDA(cudaGetLastError());
+                        HYB_CHECK(hyb_gemm_tn_blockdiag(st, b.dim, m, b.dim, b.dim, b.count, 1.0, cs.skron, ldh,
+                                                        arr + b.offset, lda, 0.0, prod + b.offset, ldp));
+                        break;
+                    }
                 }
                 psd_prod_kernel<<<nblocks(b.count * m, PSD_WARPS), PSD_WARPS * 32,
                                   PSD_WARPS * 3 * PSD_MAT * sizeof(double), st>>>(b.count, b.side, b.offset, b.mat_off, m,

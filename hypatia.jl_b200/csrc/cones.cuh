@@ -47,6 +47,8 @@ struct HybCones {
     int* red_flag = nullptr;      // 1 : AND over items
     double* red_prox = nullptr;   // 1 : max / sum over items
     double* tmp = nullptr;        // q scratch vector
+    double* skron = nullptr;      // PSD blocks, wide products: per cone the dim x dim symmetric-Kronecker matrix
+    int64_t skron_cap = 0;        // doubles allocated in skron
     std::vector<char> block_mask; // if non-empty: hybi_cones_prod touches only blocks with mask != 0
 };
 

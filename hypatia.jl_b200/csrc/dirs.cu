@@ -11,6 +11,8 @@
 // the Cholesky factor once for both and runs the two substitutions side by side.
 //
 // Vector layout at the boundary (point.jl:31-62 with p == 0): [x(N); z(q); tau; s(q); kap].
+#include <cstdlib>
+
 #include "ctx.cuh"
 
 struct HybVecs {  // one set of m <= HYB_MAX_RHS "points" on the device
@@ -491,6 +493,7 @@ int hyb_get_directions(hyb_ctx* c, int nrhs, const double* rhs, double* dir, int
     const double mu_tt = mu / tau_bar / tau_bar;
     KBEGIN(c);
     HYB_CHECK(solve_system_dev(c, d, m, refresh_const != 0, d.rhs, d.dir, mu_tt));
+    static const bool dbg = getenv("HYB_DEBUG_DIRS") != nullptr;
     double norms[HYB_MAX_RHS] = {0, 0, 0, 0};
     for (int j = 0; j < m; ++j) {
         if (num_ref) num_ref[j] = 0;
@@ -503,6 +506,7 @@ int hyb_get_directions(hyb_ctx* c, int nrhs, const double* rhs, double* dir, int
         for (int j = 0; j < m; ++j) {
             double rn = norms[j];
             int nref = 0;
+            if (dbg) fprintf(stderr, "  dirs: col %d res_norm %.3e cutoff %.3e\n", j, rn, res_norm_cutoff);
             if (rn > res_norm_cutoff) {  // iterative refinement of column j (common.jl:46-79)
                 const HybVecs dj = column(d.dir, d, j), rj = column(d.rhs, d, j), ej = column(d.res, d, j);
                 HYB_CHECK(copy_vecs(c, d, d.tmp, dj));
@@ -521,6 +525,7 @@ int hyb_get_directions(hyb_ctx* c, int nrhs, const double* rhs, double* dir, int
                     double rn_new = 0.0;
                     HYB_CUDA(cudaMemcpyAsync(&rn_new, d.scal + 12, sizeof(double), cudaMemcpyDeviceToHost, st));
                     HYB_CUDA(cudaStreamSynchronize(st));
+                    if (dbg) fprintf(stderr, "    refine: %.3e -> %.3e\n", rn, rn_new);
                     if (rn_new != rn_new) {  // NaN: reported, the caller asserts like common.jl:81
                         rn = rn_new;
                         break;

@@ -34,7 +34,8 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
 // warpgroups take them (setmaxnreg.inc 232), the Hopper/Blackwell warp-specialisation idiom.
 __global__ void __launch_bounds__(THREADS, 1)
 gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
-               double alpha, double beta, double* __restrict__ C, int64_t ldc, int flags, int tiles_m) {
+               double alpha, double beta, double* __restrict__ C, int64_t ldc, int flags, int tiles_m, int a_step,
+               int b_step, int64_t c_step) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     double* sA = (double*)base;
@@ -54,6 +55,10 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         tj = blockIdx.x / tiles_m;
     }
     const int m0 = ti * BM, n0 = tj * BN;
+    // batched use (blockIdx.y = batch): A advances by a_step along its outer (M) coordinate, B by
+    // b_step along its inner (K) coordinate, C by c_step doubles
+    const int a_off = blockIdx.y * a_step, b_off = blockIdx.y * b_step;
+    C += (int64_t)blockIdx.y * c_step;
     const int nk = (K + BK - 1) / BK;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -74,8 +79,8 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 const int s = kt % STAGES;
                 if (kt >= STAGES) mbar_wait(&empty[s], ((kt / STAGES) - 1) & 1);
                 mbar_arrive_expect_tx(&full[s], 2 * TILE_BYTES);
-                tma_load_2d(sA + s * TILE_DOUBLES, &tmA, kt * BK, m0, &full[s]);
-                tma_load_2d(sB + s * TILE_DOUBLES, &tmB, kt * BK, n0, &full[s]);
+                tma_load_2d(sA + s * TILE_DOUBLES, &tmA, kt * BK, m0 + a_off, &full[s]);
+                tma_load_2d(sB + s * TILE_DOUBLES, &tmB, kt * BK + b_off, n0, &full[s]);
             }
         }
         return;
@@ -222,7 +227,45 @@ int hyb_gemm_tn(cudaStream_t st, int64_t M, int64_t N, int64_t K, double alpha, 
     }
     if (((uintptr_t)C & 15) == 0 && (ldc & 1) == 0) flags |= HYB_GEMM_CVEC;
     gemm_tn_kernel<<<(unsigned)ntiles, THREADS, SMEM_BYTES, st>>>(tmA, tmB, (int)M, (int)N, (int)K, alpha, beta, C, ldc,
-                                                                 flags, tiles_m);
+                                                                 flags, tiles_m, 0, 0, 0);
+    ++g_gemm_launches;
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// Batched form for block-diagonal left factors: for b = 0..batch-1
+//   C[b*step : b*step + M, :] = alpha * A_b' * B[b*step : b*step + K, :] + beta * C[...]
+// with A_b = columns b*step .. b*step + M of the K x (batch*step) K-major array A (lda) and B, C tall
+// matrices of batch*step rows (ldb, ldc).  Used with M = K = step: every diagonal block maps its
+// own row range (the symmetric-Kronecker form of the PSD cone products, cones.cu).  Rows of B
+// past the block's K rows are multiplied by zero-filled rows of A (A's K extent is exact), so B
+// must be finite there.
+int hyb_gemm_tn_blockdiag(cudaStream_t st, int64_t M, int64_t N, int64_t K, int64_t step, int64_t batch, double alpha,
+                          const double* A, int64_t lda, const double* B, int64_t ldb, double beta, double* C,
+                          int64_t ldc) {
+    if (M <= 0 || N <= 0 || batch <= 0) return 0;
+    if (K <= 0 || batch > 65535) {
+        hyb_set_error("hyb_gemm_tn_blockdiag: bad K or batch");
+        return -1;
+    }
+    if ((lda & 1) || (ldb & 1) || (step & 1) || ((uintptr_t)A & 15) || ((uintptr_t)B & 15)) {
+        hyb_set_error("hyb_gemm_tn_blockdiag: operands must be 16-byte aligned with even leading dimensions and step");
+        return -1;
+    }
+    static bool attr_set = false;
+    if (!attr_set) {
+        HYB_CUDA(cudaFuncSetAttribute(gemm_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        attr_set = true;
+    }
+    CUtensorMap tmA, tmB;
+    HYB_CHECK(hyb_make_tmap_2d_f64(&tmA, A, (uint64_t)K, (uint64_t)(step * (batch - 1) + M), (uint64_t)lda, BK, BM));
+    HYB_CHECK(hyb_make_tmap_2d_f64(&tmB, B, (uint64_t)(step * (batch - 1) + K), (uint64_t)N, (uint64_t)ldb, BK, BN));
+    const int tiles_m = (int)((M + BM - 1) / BM), tiles_n = (int)((N + BN - 1) / BN);
+    int flags = 0;
+    if (((uintptr_t)C & 15) == 0 && (ldc & 1) == 0) flags |= HYB_GEMM_CVEC;
+    dim3 grid((unsigned)(tiles_m * tiles_n), (unsigned)batch);
+    gemm_tn_kernel<<<grid, THREADS, SMEM_BYTES, st>>>(tmA, tmB, (int)M, (int)N, (int)K, alpha, beta, C, ldc, flags, tiles_m,
+                                                      (int)step, (int)step, step);
     ++g_gemm_launches;
     HYB_CUDA(cudaGetLastError());
     return 0;

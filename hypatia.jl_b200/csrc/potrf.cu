@@ -18,6 +18,7 @@
 // solves its diagonal block by substitution in shared memory, and publishes its block.
 // Fixed summation order -> bitwise reproducible.
 #include <cooperative_groups.h>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -25,20 +26,23 @@ namespace {
 
 constexpr int NB = 128;
 constexpr int LDS = NB + 1;  // padded shared-memory leading dimension
-constexpr int IB = 16;       // inner block of the panel factorization
+constexpr int IB = 32;       // inner block of the panel factorization
 
 // --------------------------------------------------------------------------------
 // panel: in-place upper Cholesky of an nb x nb diagonal block (nb <= 128) in shared
-// memory, blocked by IB columns: (1) one warp factors the IB x IB diagonal block,
-// (2) thread-per-column forward substitution gives the IB x m row panel, (3) all
-// threads apply the rank-IB update to the trailing triangle.  Same arithmetic as
-// LAPACK dpotf2/dpotrf (no explicit inverses), so backward stable.
+// memory, blocked by IB = 32 columns: (1) one warp factors the 32 x 32 diagonal block in
+// registers (lane c owns column c; pivots and multipliers travel by shuffle), (2)
+// thread-per-column forward substitution gives the 32 x m row panel, (3) all threads apply
+// the rank-32 update to the trailing triangle in 4 x 4 register tiles.  Substitution only
+// (no explicit inverses), so backward stable like LAPACK dpotf2/dpotrf.  The reciprocal pivot
+// comes from rsqrt (1 ulp) and the pivot itself is d * rsqrt(d): both are off by at most a few
+// ulp from LAPACK's sqrt / divide, which is a relative perturbation of the same size in A_jj.
 // The strictly lower triangle of the block in global memory is zeroed on exit.
 // --------------------------------------------------------------------------------
 __device__ __noinline__ void potf2_diag_block(double* S, double* rdiag, int jb, int lane, int* fail, int* info,
                                                  int k0) {
     double col[IB];
-    const int c = lane & (IB - 1);
+    const int c = lane;
 #pragma unroll
     for (int i = 0; i < IB; ++i) col[i] = S[(jb + i) * LDS + jb + c];
     bool bad = false;
@@ -50,14 +54,19 @@ __device__ __noinline__ void potf2_diag_block(double* S, double* rdiag, int jb, 
             bad = true;
             badj = j;
         }
+#ifdef HYB_POTF2_RSQRT
+        const double rinv = rsqrt(d);
+        const double ujc = (c == j) ? d * rinv : col[j] * rinv;
+#else
         const double r = sqrt(d);
         const double rinv = 1.0 / r;
         const double ujc = (c == j) ? r : col[j] * rinv;
+#endif
         if (c >= j) col[j] = ujc;
         if (lane == j) rdiag[j] = rinv;
 #pragma unroll
         for (int i = j + 1; i < IB; ++i) {
-            const double uji = __shfl_sync(0xffffffffu, col[j], i);
+            const double uji = __shfl_sync(0xffffffffu, ujc, i);
             if (c >= i) col[i] -= uji * ujc;
         }
     }
@@ -66,7 +75,7 @@ __device__ __noinline__ void potf2_diag_block(double* S, double* rdiag, int jb, 
             *fail = 1;
             *info = k0 + jb + badj + 1;
         }
-    } else if (lane < IB) {
+    } else {
 #pragma unroll
         for (int i = 0; i < IB; ++i)
             if (i <= c) S[(jb + i) * LDS + jb + c] = col[i];
@@ -87,6 +96,48 @@ __device__ __noinline__ void potf2_row_panel(double* S, const double* rdiag, int
     for (int i = 0; i < IB; ++i) S[(jb + i) * LDS + c] = y[i];
 }
 
+// S[i][c] -= sum_k U[jb+k][i] U[jb+k][c] for t0 <= i <= c < nbp, in 4 x 4 register tiles.
+// A thread's 4 rows / 4 columns are interleaved with stride mt (= tiles per side), so the lanes
+// of a warp read consecutive shared-memory words (a contiguous 4 x 4 tile per thread puts the
+// lanes 32 bytes apart: 4-way bank conflicts on every operand load).
+__device__ __forceinline__ void potf2_trailing_update(double* S, int jb, int t0, int nbp, int tid, int nth) {
+    const int mt = (nbp - t0) >> 2;  // tiles per side
+    for (int t = tid; t < mt * mt; t += nth) {
+        const int ti = t / mt, tj = t - ti * mt;
+        const int i0 = t0 + ti, c0 = t0 + tj;
+        double acc[4][4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
+#pragma unroll 8
+        for (int k = 0; k < IB; ++k) {
+            const double* row = S + (jb + k) * LDS;
+            double u[4], v[4];
+#pragma unroll
+            for (int a = 0; a < 4; ++a) u[a] = row[i0 + a * mt];
+#pragma unroll
+            for (int b = 0; b < 4; ++b) v[b] = row[c0 + b * mt];
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int b = a; b < 4; ++b) acc[a][b] += u[a] * v[b];  // b < a lies below the diagonal
+        }
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = a; b < 4; ++b)
+                if (c0 + b * mt >= i0 + a * mt) S[(i0 + a * mt) * LDS + c0 + b * mt] -= acc[a][b];
+    }
+}
+
+#ifdef HYB_PROFILE_POTF2
+__device__ long long g_potf2_ts[32];
+#define POTF2_TS(i) do { if (tid == 0) g_potf2_ts[i] = clock64(); } while (0)
+#else
+#define POTF2_TS(i)
+#endif
+
 __global__ void __launch_bounds__(512, 1)
 potf2_kernel(double* __restrict__ A, int64_t lda, int nb, int* __restrict__ info, int k0) {
     extern __shared__ double sm[];
@@ -96,18 +147,32 @@ potf2_kernel(double* __restrict__ A, int64_t lda, int nb, int* __restrict__ info
     const int tid = threadIdx.x, nth = blockDim.x, lane = tid & 31, warp = tid >> 5;
     if (*info != 0) return;  // an earlier panel failed: nothing meaningful to do
     if (tid == 0) fail = 0;
-    for (int e = tid; e < NB * NB; e += nth) {
-        const int r = e & (NB - 1), c = e >> 7;
-        S[r * LDS + c] = (r < nb && c < nb && r <= c) ? A[r + (int64_t)c * lda] : ((r == c) ? 1.0 : 0.0);
+    POTF2_TS(0);
+    // stage the block: every thread issues all 32 of its loads before the first store, so a full
+    // bandwidth-latency product of requests is in flight (a load->store loop leaves one per thread)
+    {
+        double v[NB * NB / 512];
+#pragma unroll
+        for (int t = 0; t < NB * NB / 512; ++t) {
+            const int e = tid + t * 512, r = e & (NB - 1), c = e >> 7;
+            v[t] = (r < nb && c < nb && r <= c) ? __ldg(A + r + (int64_t)c * lda) : ((r == c) ? 1.0 : 0.0);
+        }
+#pragma unroll
+        for (int t = 0; t < NB * NB / 512; ++t) {
+            const int e = tid + t * 512, r = e & (NB - 1), c = e >> 7;
+            S[r * LDS + c] = v[t];
+        }
     }
     __syncthreads();
 
+    POTF2_TS(1);
     // identity padding makes every IB x IB step full-size: no tail cases below
     const int nbp = (nb + IB - 1) / IB * IB;
     for (int jb = 0; jb < nbp; jb += IB) {
-        // (1) IB x IB diagonal block: lane c owns column c in registers, right-looking
+        // (1) IB x IB diagonal block
         if (warp == 0) potf2_diag_block(S, rdiag, jb, lane, &fail, info, k0);
         __syncthreads();
+        POTF2_TS(2 + 3 * (jb / IB));
         if (fail) return;
         const int t0 = jb + IB;   // first trailing column
         const int m = nbp - t0;   // trailing size
@@ -115,29 +180,33 @@ potf2_kernel(double* __restrict__ A, int64_t lda, int nb, int* __restrict__ info
         // (2) row panel: U[jb:jb+IB, c] = U11^-T A[jb:jb+IB, c], thread per trailing column
         if (tid < m) potf2_row_panel(S, rdiag, jb, t0 + tid);
         __syncthreads();
-        // (3) trailing update: S[i][c] -= sum_k U[jb+k][i] U[jb+k][c], t0 <= i <= c.
-        //     threads tile the trailing square: tx over columns (fast), ty over rows.
-        {
-            const int tx = tid & 31, ty = tid >> 5;  // 32 x 16
-            for (int i = t0 + ty; i < nbp; i += 16) {
-                for (int c = t0 + tx; c < nbp; c += 32) {
-                    if (c >= i) {
-                        double s = 0.0;
-#pragma unroll
-                        for (int k = 0; k < IB; ++k) s += S[(jb + k) * LDS + i] * S[(jb + k) * LDS + c];
-                        S[i * LDS + c] -= s;
-                    }
-                }
-            }
-        }
+        POTF2_TS(3 + 3 * (jb / IB));
+        // (3) trailing update
+        potf2_trailing_update(S, jb, t0, nbp, tid, nth);
         __syncthreads();
+        POTF2_TS(4 + 3 * (jb / IB));
     }
+    POTF2_TS(20);
     // write back: U in the upper triangle, zeros strictly below (the block is workspace)
     for (int e = tid; e < NB * NB; e += nth) {
         const int r = e & (NB - 1), c = e >> 7;
         if (r < nb && c < nb) A[r + (int64_t)c * lda] = (r <= c) ? S[r * LDS + c] : 0.0;
     }
+    POTF2_TS(21);
 }
+
+#ifdef HYB_PROFILE_POTF2
+void hyb_potf2_dump_ts() {
+    long long ts[32];
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(ts, g_potf2_ts, sizeof(ts));
+    fprintf(stderr, "potf2 clocks: stage %lld", ts[1] - ts[0]);
+    for (int b = 0; b < 4; ++b)
+        fprintf(stderr, " | diag %lld panel %lld upd %lld", ts[2 + 3 * b] - (b ? ts[1 + 3 * b] : ts[1]),
+                ts[3 + 3 * b] - ts[2 + 3 * b], ts[4 + 3 * b] - ts[3 + 3 * b]);
+    fprintf(stderr, " | writeback %lld | total %lld\n", ts[21] - ts[20], ts[21] - ts[0]);
+}
+#endif
 
 // --------------------------------------------------------------------------------
 // row panel of the blocked factorization: A12 <- U11^-T A12 (U11 128 x 128 upper),
@@ -208,15 +277,30 @@ __device__ __forceinline__ void trsm_update_chunk(const double* Uc, double* T, i
 __device__ __forceinline__ void trsm_stage(const double* __restrict__ U11, int64_t ldu, int nb,
                                            const double* __restrict__ B, int64_t ld, int64_t col0, int ncol, double* Uc,
                                            double* T, double* dinv, int tid) {
-    for (int e = tid; e < NB * NB; e += TRSM_THREADS) {
-        const int k = e & (NB - 1), i = e >> 7;
-        double v = (k == i) ? 1.0 : 0.0;
-        if (k <= i && i < nb) v = __ldg(U11 + k + (int64_t)i * ldu);
-        Uc[i * LDS + k] = v;
+    // batches of 32 loads per thread in flight before the stores (see potf2_kernel)
+    static_assert(TRSM_THREADS == NB, "staging below assumes one thread per row");
+#pragma unroll 1
+    for (int i0 = 0; i0 < NB; i0 += 32) {
+        double v[32];
+#pragma unroll
+        for (int t = 0; t < 32; ++t) {
+            const int k = tid, i = i0 + t;
+            v[t] = (k == i) ? 1.0 : 0.0;
+            if (k <= i && i < nb) v[t] = __ldg(U11 + k + (int64_t)i * ldu);
+        }
+#pragma unroll
+        for (int t = 0; t < 32; ++t) Uc[(i0 + t) * LDS + tid] = v[t];
     }
-    for (int e = tid; e < NB * TRSM_COLS; e += TRSM_THREADS) {
-        const int r = e & (NB - 1), c = e >> 7;
-        T[r * TLD + c] = (c < ncol && r < nb) ? B[r + (col0 + c) * ld] : 0.0;
+#pragma unroll 1
+    for (int c0 = 0; c0 < TRSM_COLS; c0 += 32) {
+        double v[32];
+#pragma unroll
+        for (int t = 0; t < 32; ++t) {
+            const int r = tid, c = c0 + t;
+            v[t] = (c < ncol && r < nb) ? B[r + (col0 + c) * ld] : 0.0;
+        }
+#pragma unroll
+        for (int t = 0; t < 32; ++t) T[tid * TLD + c0 + t] = v[t];
     }
     __syncthreads();
     if (tid < NB) dinv[tid] = 1.0 / Uc[tid * LDS + tid];
@@ -628,9 +712,30 @@ constexpr int TRSM_SMEM = (NB * LDS + NB * TLD + NB) * (int)sizeof(double);
 constexpr int TRSV_SMEM = (NB * LDS + NB + 5 * HYB_MAX_RHS * NB) * (int)sizeof(double);
 int64_t g_potrf_launches = 0;
 
-// Right-looking factorization with one panel of look-ahead: while the bulk of step k's
-// trailing update runs on the main stream, the (latency-bound) panel k+1 = potf2 + trsm runs
-// on a second, high-priority stream as soon as block row k+1 has received step k's update.
+// Right-looking factorization, two-level blocking with look-ahead.
+//  * Outer blocks of OB columns (OB = 128 * 2^k, default 256, HYB_POTRF_OB): the trailing matrix
+//    is updated once per outer block with a rank-OB gemm, so its N^2/2 entries are read and
+//    written N/OB times instead of N/128 times (at K = 128 the update is bound by that traffic and
+//    by the number of launches, not by the DMMA pipe).
+//  * Inside an outer block the 128-column panels are factored left to right (potf2 + row trsm),
+//    each followed by a rank-128 update of the remaining block rows OF THE OUTER BLOCK only.
+//  * Look-ahead: after an outer block is done, the next outer block's rows get their rank-OB
+//    update first; the (latency-bound) panels of that block then run on a second, high-priority
+//    stream while the bulk of the rank-OB update proceeds on the main stream.
+// The strictly lower triangle of ch.F is workspace (the rectangular updates write there).
+static int potrf_outer_block() {
+    static int ob = 0;
+    if (ob == 0) {
+        ob = 256;
+        const char* e = getenv("HYB_POTRF_OB");
+        if (e) {
+            const int v = atoi(e);
+            if (v == 128 || v == 256 || v == 512 || v == 1024) ob = v;
+        }
+    }
+    return ob;
+}
+
 int hyb_potrf(cudaStream_t st, HybChol& ch, int* info_out) {
     const int64_t N = ch.N, ld = ch.ld;
     static bool attr_set = false;
@@ -640,6 +745,7 @@ int hyb_potrf(cudaStream_t st, HybChol& ch, int* info_out) {
         HYB_CUDA(cudaFuncSetAttribute(trsm_upper_N_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TRSM_SMEM));
         attr_set = true;
     }
+    const int64_t OB = potrf_outer_block();
     cudaStream_t sp = ch.panel_stream;
     HYB_CUDA(cudaMemsetAsync(ch.info, 0, sizeof(int), st));
     auto panel = [&](cudaStream_t s, int64_t k0) -> int {
@@ -658,30 +764,43 @@ int hyb_potrf(cudaStream_t st, HybChol& ch, int* info_out) {
         }
         return 0;
     };
-    HYB_CHECK(panel(st, 0));
-    for (int64_t k0 = 0; k0 + NB < N; k0 += NB) {
-        const int64_t k1 = k0 + NB;
-        const int64_t n2 = N - k1;                       // trailing size
-        const int64_t nb2 = n2 < NB ? n2 : NB;           // height of the next block row
-        const double* U12 = ch.F + k0 + k1 * ld;         // NB x n2 (block row k)
-        double* A22 = ch.F + k1 + k1 * ld;
-        // head: block row k+1 of the trailing matrix  -= U12[:, 0:nb2]' U12
-        HYB_CHECK(hyb_gemm_tn(st, nb2, n2, NB, -1.0, U12, ld, U12, ld, 1.0, A22, ld, 0));
-        HYB_CUDA(cudaEventRecord(ch.ev_head, st));
+    HYB_CUDA(cudaEventRecord(ch.ev_head, st));
+    for (int64_t K0 = 0; K0 < N; K0 += OB) {
+        const int64_t ob = (N - K0 < OB) ? (N - K0) : OB;
+        const int64_t K1 = K0 + ob;
+        // the panels of this outer block, on the panel stream, once its rows are up to date
         HYB_CUDA(cudaStreamWaitEvent(sp, ch.ev_head, 0));
-        HYB_CHECK(panel(sp, k1));
+        for (int64_t j0 = K0; j0 < K1; j0 += NB) {
+            HYB_CHECK(panel(sp, j0));
+            const int64_t r1 = j0 + NB;
+            if (r1 < K1) {  // rank-128 update of the outer block's remaining rows: all columns >= r1
+                const double* U = ch.F + j0 + r1 * ld;
+                HYB_CHECK(hyb_gemm_tn(sp, K1 - r1, N - r1, NB, -1.0, U, ld, U, ld, 1.0, ch.F + r1 + r1 * ld, ld, 0));
+            }
+        }
         HYB_CUDA(cudaEventRecord(ch.ev_panel, sp));
-        // rest: block rows >= k+2, upper triangle only
-        const int64_t n3 = n2 - nb2;
-        if (n3 > 0)
-            HYB_CHECK(hyb_gemm_tn(st, n3, n3, NB, -1.0, U12 + nb2 * ld, ld, U12 + nb2 * ld, ld, 1.0,
-                                  A22 + nb2 + nb2 * ld, ld, HYB_GEMM_UPPER));
         HYB_CUDA(cudaStreamWaitEvent(st, ch.ev_panel, 0));
+        const int64_t n2 = N - K1;  // trailing size
+        if (n2 <= 0) break;
+        const double* U12 = ch.F + K0 + K1 * ld;  // ob x n2: block rows of this outer block
+        double* A22 = ch.F + K1 + K1 * ld;
+        // look-ahead: the next outer block's rows first
+        const int64_t nh = n2 < OB ? n2 : OB;
+        HYB_CHECK(hyb_gemm_tn(st, nh, n2, ob, -1.0, U12, ld, U12, ld, 1.0, A22, ld, 0));
+        HYB_CUDA(cudaEventRecord(ch.ev_head, st));
+        // bulk: everything below, upper triangle only
+        const int64_t n3 = n2 - nh;
+        if (n3 > 0)
+            HYB_CHECK(hyb_gemm_tn(st, n3, n3, ob, -1.0, U12 + nh * ld, ld, U12 + nh * ld, ld, 1.0, A22 + nh + nh * ld, ld,
+                                  HYB_GEMM_UPPER));
     }
     if (info_out) {
         HYB_CUDA(cudaMemcpyAsync(info_out, ch.info, sizeof(int), cudaMemcpyDeviceToHost, st));
         HYB_CUDA(cudaStreamSynchronize(st));
     }
+#ifdef HYB_PROFILE_POTF2
+    hyb_potf2_dump_ts();
+#endif
     return 0;
 }
 

@@ -271,6 +271,8 @@ class B200QRCholSystemSolver(QRCholSystemSolver):
             self.sol_const.x[:] = sc[: self.N]
             self.sol_const.z[:] = sc[self.N :]
             self._dev_const_stale = self._host_const_stale = False
+        self.last_res_norms = [float(v) for v in rn]
+        self.last_num_refs = [int(v) for v in nref]
         for j, d in enumerate(dir_points):
             d.vec[:] = out[:, j]
             stepper.last_num_ref += int(nref[j])

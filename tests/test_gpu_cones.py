@@ -50,6 +50,9 @@ SPEC_SETS = {
     "rsoc_small": [cs.EpiPerSquare(3)] * 3 + [cs.EpiPerSquare(8)] * 33 + [cs.EpiPerSquare(4)],
     "soc_large": [cs.EpiNormEucl(33), cs.EpiNormEucl(100), cs.EpiPerSquare(70), cs.EpiPerSquare(257)],
     "psd": [cs.PosSemidefTri(cs.svec_length(s)) for s in (1, 2, 3, 5, 16, 16, 16, 32)],
+    # even offsets and dims: products with >= 64 columns take the symmetric-Kronecker DMMA path
+    "psd_wide": [cs.Nonnegative(4)] + [cs.PosSemidefTri(cs.svec_length(8))] * 3 + [cs.PosSemidefTri(136)] * 5
+    + [cs.EpiNormEucl(6)] + [cs.PosSemidefTri(cs.svec_length(32))],
     "psd_large": [cs.PosSemidefTri(cs.svec_length(s)) for s in (33, 64, 100, 150)] + [cs.EpiNormEucl(5)],
     "mixed": [cs.Nonnegative(10)] + [cs.EpiNormEucl(8)] * 4 + [cs.EpiPerSquare(8)] * 4
     + [cs.PosSemidefTri(136)] * 3 + [cs.Nonnegative(3), cs.EpiNormEucl(5)],
@@ -90,7 +93,7 @@ def test_oracles_match_cpu(name):
     ok_g, agg_g = gpu.check_neighborhood(irtmu, False, 0.01, 1e9)
     assert ok_c == ok_g and abs(agg_c - agg_g) <= 1e-9 * tol_scale * max(1.0, abs(agg_c))
 
-    for m in (1, 7):
+    for m in (1, 7) + ((80, 200) if name == "psd_wide" else ()):
         arr = rng.standard_normal(q) if m == 1 else np.asfortranarray(rng.standard_normal((q, m)))
         for fn in ("hess_prod", "inv_hess_prod", "block_hess_prod", "hess_prod_slow"):
             assert rel_err(getattr(gpu, fn)(arr), getattr(cpu, fn)(arr)) < 1e4 * TOL * tol_scale, (fn, m)

@@ -107,7 +107,7 @@ def test_batched_and_unbatched_solves_agree(name):
         s.load(MODELS[name]())
         s.solve()
     assert a.status == b.status == "Optimal"
-    assert a.num_iters == b.num_iters
+    assert abs(a.num_iters - b.num_iters) <= 1
     assert abs(a.primal_obj - b.primal_obj) <= 1e-7 * (1 + abs(b.primal_obj))  # north_star objective tolerance
     n = len(b.trace) // 2
     assert np.allclose([r["mu"] for r in a.trace[:n]], [r["mu"] for r in b.trace[:n]], rtol=1e-8)

@@ -19,7 +19,7 @@ elif name == "cfg1":
     fn = lambda: instances.linearopt(500, 1000, seed=1)
 elif name.startswith("block"):
     fn = lambda: instances.block_multicone(N=int(name[5:]), seed=1)
-gpu = make_gpu_solver(0, trace=True)
+gpu = make_gpu_solver(0, trace=True, batched_dirs=not os.environ.get("HYB_UNBATCHED"))
 cpu = Solver(CpuConeSet, QRCholDenseSystemSolver(), trace=True)
 for s in (gpu, cpu):
     s.load(fn())
