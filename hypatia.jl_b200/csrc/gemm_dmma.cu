@@ -11,6 +11,8 @@
 // LDS.64.  One CTA = one 128x128 output tile, 8 consumer warps (64x32 each, 64
 // accumulators per thread) + 1 TMA producer warp, 4-stage mbarrier ring of
 // (16 KB A + 16 KB B).  Deterministic: no split-K atomics.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "tma.cuh"
 
@@ -35,7 +37,7 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
 __global__ void __launch_bounds__(THREADS, 1)
 gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
                double alpha, double beta, double* __restrict__ C, int64_t ldc, int flags, int tiles_m, int a_step,
-               int b_step, int64_t c_step) {
+               int b_step, int64_t c_step, int n_main, int nsplit, double* __restrict__ ws) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     double* sA = (double*)base;
@@ -43,23 +45,41 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     uint64_t* full = (uint64_t*)(base + 2 * STAGES * TILE_BYTES);
     uint64_t* empty = full + STAGES;
 
+    // Tail splitting: tiles [n_main, ...) -- the last, partial wave of CTAs -- are cut along K into
+    // nsplit CTAs each, which park raw partial tiles in `ws`; gemm_tail_reduce_kernel then adds the
+    // partials of a tile in a fixed order (deterministic) and applies alpha / beta.  Without it a
+    // result of 14 waves + 8 tiles costs 15 waves.
+    int tile_idx = blockIdx.x, split = 0;
+    const bool partial = (int)blockIdx.x >= n_main;
+    if (partial) {
+        const int t = blockIdx.x - n_main;
+        tile_idx = n_main + t / nsplit;
+        split = t - (t / nsplit) * nsplit;
+    }
     int ti, tj;
     if (flags & HYB_GEMM_UPPER) {
-        const int idx = blockIdx.x;
+        const int idx = tile_idx;
         tj = (int)((sqrt(8.0 * idx + 1.0) - 1.0) * 0.5);
         while (tj * (tj + 1) / 2 > idx) --tj;
         while ((tj + 1) * (tj + 2) / 2 <= idx) ++tj;
         ti = idx - tj * (tj + 1) / 2;
     } else {
-        ti = blockIdx.x % tiles_m;
-        tj = blockIdx.x / tiles_m;
+        ti = tile_idx % tiles_m;
+        tj = tile_idx / tiles_m;
     }
     const int m0 = ti * BM, n0 = tj * BN;
     // batched use (blockIdx.y = batch): A advances by a_step along its outer (M) coordinate, B by
     // b_step along its inner (K) coordinate, C by c_step doubles
     const int a_off = blockIdx.y * a_step, b_off = blockIdx.y * b_step;
     C += (int64_t)blockIdx.y * c_step;
-    const int nk = (K + BK - 1) / BK;
+    const int nk_all = (K + BK - 1) / BK;
+    int kt0 = 0, nk = nk_all;  // this CTA's k-steps: [kt0, kt0 + nk)
+    if (partial) {
+        const int per = (nk_all + nsplit - 1) / nsplit;
+        kt0 = split * per;
+        nk = nk_all - kt0 < per ? nk_all - kt0 : per;
+        if (nk < 0) nk = 0;
+    }
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
@@ -79,8 +99,8 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 const int s = kt % STAGES;
                 if (kt >= STAGES) mbar_wait(&empty[s], ((kt / STAGES) - 1) & 1);
                 mbar_arrive_expect_tx(&full[s], 2 * TILE_BYTES);
-                tma_load_2d(sA + s * TILE_DOUBLES, &tmA, kt * BK, m0 + a_off, &full[s]);
-                tma_load_2d(sB + s * TILE_DOUBLES, &tmB, kt * BK + b_off, n0, &full[s]);
+                tma_load_2d(sA + s * TILE_DOUBLES, &tmA, (kt0 + kt) * BK, m0 + a_off, &full[s]);
+                tma_load_2d(sB + s * TILE_DOUBLES, &tmB, (kt0 + kt) * BK + b_off, n0, &full[s]);
             }
         }
         return;
@@ -144,6 +164,16 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
     }
     asm volatile("bar.sync 1, 256;" ::: "memory");
+    if (partial) {  // raw partial tile, column-major 128 x 128, to this CTA's workspace slot
+        double* wt = ws + (int64_t)(blockIdx.x - n_main) * (BM * BN);
+#pragma unroll 4
+        for (int it = 0; it < 32; ++it) {
+            const int idx = it * 256 + ctid;
+            const int col = idx >> 6, row = (idx & 63) * 2;
+            *(double2*)(wt + col * BM + row) = *(const double2*)(Cs + col * BM + (row ^ (((col >> 1) & 3) << 3)));
+        }
+        return;
+    }
     const bool vec_ok = (flags & HYB_GEMM_CVEC) != 0;
 #pragma unroll 1
     for (int round = 0; round < 4; ++round) {
@@ -189,7 +219,39 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
 }
 
+// C tile = alpha * (sum of the nsplit partial tiles, in split order) + beta * C for the split tail tiles
+__global__ void __launch_bounds__(256)
+gemm_tail_reduce_kernel(int M, int N, double alpha, double beta, double* __restrict__ C, int64_t ldc, int flags,
+                        int tiles_m, int n_main, int nsplit, const double* __restrict__ ws) {
+    const int tile_idx = n_main + blockIdx.x;
+    int ti, tj;
+    if (flags & HYB_GEMM_UPPER) {
+        tj = (int)((sqrt(8.0 * tile_idx + 1.0) - 1.0) * 0.5);
+        while (tj * (tj + 1) / 2 > tile_idx) --tj;
+        while ((tj + 1) * (tj + 2) / 2 <= tile_idx) ++tj;
+        ti = tile_idx - tj * (tj + 1) / 2;
+    } else {
+        ti = tile_idx % tiles_m;
+        tj = tile_idx / tiles_m;
+    }
+    const int m0 = ti * BM, n0 = tj * BN;
+    const bool upper = flags & HYB_GEMM_UPPER;
+    const double* w0 = ws + (int64_t)blockIdx.x * nsplit * (BM * BN);
+    for (int e = threadIdx.x; e < BM * BN; e += 256) {
+        const int row = e & (BM - 1), col = e >> 7;
+        const int grow = m0 + row, gcol = n0 + col;
+        if (grow >= M || gcol >= N || (upper && gcol < grow)) continue;
+        double s = 0.0;
+        for (int k = 0; k < nsplit; ++k) s += w0[(int64_t)k * (BM * BN) + e];
+        double* p = C + grow + (int64_t)gcol * ldc;
+        *p = (beta != 0.0) ? alpha * s + beta * *p : alpha * s;
+    }
+}
+
 int64_t g_gemm_launches = 0;
+int g_gemm_num_sms = 0;
+struct TailWs { cudaStream_t st; double* p; };
+std::vector<TailWs> g_tail_ws;  // one workspace per stream that ever needed one (never shrinks)
 
 }  // namespace
 
@@ -226,10 +288,45 @@ int hyb_gemm_tn(cudaStream_t st, int64_t M, int64_t N, int64_t K, double alpha, 
         ntiles = (int64_t)tiles_m * tiles_n;
     }
     if (((uintptr_t)C & 15) == 0 && (ldc & 1) == 0) flags |= HYB_GEMM_CVEC;
-    gemm_tn_kernel<<<(unsigned)ntiles, THREADS, SMEM_BYTES, st>>>(tmA, tmB, (int)M, (int)N, (int)K, alpha, beta, C, ldc,
-                                                                 flags, tiles_m, 0, 0, 0);
+    // split the tiles of a small last wave along K (long contractions only: the Schur syrk)
+    if (g_gemm_num_sms == 0) {
+        int dev = 0;
+        HYB_CUDA(cudaGetDevice(&dev));
+        HYB_CUDA(cudaDeviceGetAttribute(&g_gemm_num_sms, cudaDevAttrMultiProcessorCount, dev));
+    }
+    const int P = g_gemm_num_sms;
+    int64_t n_main = ntiles;
+    int nsplit = 1;
+    double* ws = nullptr;
+    const int64_t nk_all = (K + BK - 1) / BK;
+    const int64_t r = ntiles % P;
+    static const bool no_split = getenv("HYB_GEMM_NO_SPLIT") != nullptr;
+    if (!no_split && ntiles > P && r > 0 && 2 * r <= P && nk_all >= 128) {
+        nsplit = (int)(P / r);
+        if (nsplit > nk_all / 32) nsplit = (int)(nk_all / 32);
+        if (nsplit >= 2) {
+            n_main = ntiles - r;
+            for (auto& w : g_tail_ws)
+                if (w.st == st) ws = w.p;
+            if (!ws) {
+                HYB_CUDA(cudaMalloc(&ws, sizeof(double) * BM * BN * (size_t)P));
+                g_tail_ws.push_back({st, ws});
+            }
+        } else {
+            nsplit = 1;
+        }
+    }
+    const int64_t grid = n_main + (ntiles - n_main) * nsplit;
+    gemm_tn_kernel<<<(unsigned)grid, THREADS, SMEM_BYTES, st>>>(tmA, tmB, (int)M, (int)N, (int)K, alpha, beta, C, ldc, flags,
+                                                              tiles_m, 0, 0, 0, (int)n_main, nsplit, ws);
     ++g_gemm_launches;
     HYB_CUDA(cudaGetLastError());
+    if (n_main < ntiles) {
+        gemm_tail_reduce_kernel<<<(unsigned)(ntiles - n_main), 256, 0, st>>>((int)M, (int)N, alpha, beta, C, ldc, flags, tiles_m,
+                                                                            (int)n_main, nsplit, ws);
+        ++g_gemm_launches;
+        HYB_CUDA(cudaGetLastError());
+    }
     return 0;
 }
 
@@ -265,7 +362,7 @@ int hyb_gemm_tn_blockdiag(cudaStream_t st, int64_t M, int64_t N, int64_t K, int6
     if (((uintptr_t)C & 15) == 0 && (ldc & 1) == 0) flags |= HYB_GEMM_CVEC;
     dim3 grid((unsigned)(tiles_m * tiles_n), (unsigned)batch);
     gemm_tn_kernel<<<grid, THREADS, SMEM_BYTES, st>>>(tmA, tmB, (int)M, (int)N, (int)K, alpha, beta, C, ldc, flags, tiles_m,
-                                                      (int)step, (int)step, step);
+                                                      (int)step, (int)step, step, (int)(tiles_m * tiles_n), 1, nullptr);
     ++g_gemm_launches;
     HYB_CUDA(cudaGetLastError());
     return 0;

@@ -11,7 +11,10 @@ pytestmark = pytest.mark.gpu
 EPS = np.finfo(np.float64).eps
 
 
-@pytest.mark.parametrize("M,N,K", [(1, 1, 1), (3, 5, 7), (128, 128, 16), (129, 127, 33), (200, 300, 1000), (64, 513, 257), (500, 500, 1001)])
+# the last two shapes have 150 tiles and a long K: on a 148-SM part the 2 tiles of the last wave are
+# split along K (gemm_dmma.cu tail splitting) and summed by the fixed-order reduce kernel
+@pytest.mark.parametrize("M,N,K", [(1, 1, 1), (3, 5, 7), (128, 128, 16), (129, 127, 33), (200, 300, 1000), (64, 513, 257), (500, 500, 1001),
+                                   (1280, 1920, 2100), (1275, 1900, 4096)])
 def test_gemm_tn(M, N, K):
     rng = np.random.default_rng(M * 7 + N * 3 + K)
     A = rng.standard_normal((K, M))
@@ -22,7 +25,8 @@ def test_gemm_tn(M, N, K):
     assert rel_err(got, want) < 50 * K * EPS
 
 
-@pytest.mark.parametrize("K,N", [(1, 1), (5, 3), (1000, 500), (777, 257), (4096, 384), (130, 1025)])
+# N = 2176 / 2170: 153 upper tiles = one wave + 5 split tiles
+@pytest.mark.parametrize("K,N", [(1, 1), (5, 3), (1000, 500), (777, 257), (4096, 384), (130, 1025), (2048, 2176), (3001, 2170)])
 def test_outer_prod_upper(K, N):
     rng = np.random.default_rng(K + N)
     A = rng.standard_normal((K, N))
