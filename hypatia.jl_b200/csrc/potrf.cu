@@ -133,6 +133,7 @@ __device__ __forceinline__ void potf2_trailing_update(double* S, int jb, int t0,
 
 #ifdef HYB_PROFILE_POTF2
 __device__ long long g_potf2_ts[32];
+__device__ long long g_trsm_ts[16];
 #define POTF2_TS(i) do { if (tid == 0) g_potf2_ts[i] = clock64(); } while (0)
 #else
 #define POTF2_TS(i)
@@ -205,6 +206,11 @@ void hyb_potf2_dump_ts() {
         fprintf(stderr, " | diag %lld panel %lld upd %lld", ts[2 + 3 * b] - (b ? ts[1 + 3 * b] : ts[1]),
                 ts[3 + 3 * b] - ts[2 + 3 * b], ts[4 + 3 * b] - ts[3 + 3 * b]);
     fprintf(stderr, " | writeback %lld | total %lld\n", ts[21] - ts[20], ts[21] - ts[0]);
+    long long tt[16];
+    cudaMemcpyFromSymbol(tt, g_trsm_ts, sizeof(tt));
+    fprintf(stderr, "trsm clocks: stage %lld | s0 %lld u1 %lld s1 %lld u2 %lld s2 %lld u3 %lld s3 %lld | writeback %lld | total %lld\n",
+            tt[1] - tt[0], tt[2] - tt[1], tt[3] - tt[2], tt[4] - tt[3], tt[5] - tt[4], tt[6] - tt[5], tt[7] - tt[6],
+            tt[8] - tt[7], tt[9] - tt[8], tt[9] - tt[0]);
 }
 #endif
 
@@ -241,8 +247,10 @@ __device__ __forceinline__ void trsm_solve_chunk(const double* Uc, const double*
 template <int CB>
 __device__ __forceinline__ void trsm_update_chunk(const double* Uc, double* T, int tid) {
     if (CB == 0) return;
+    // a thread's 4 rows are 8 apart and its 4 columns 16 apart, so the lanes of a warp read
+    // consecutive words of the slab (contiguous 4 x 4 tiles put them 32 bytes apart: 4-way conflicts)
     const int tr = tid >> 4, tc = tid & 15;  // 8 row groups x 16 column groups
-    const int r0 = CB * 32 + 4 * tr, c0 = 4 * tc;
+    const int r0 = CB * 32 + tr, c0 = tc;
     double acc[4][4];
 #pragma unroll
     for (int i = 0; i < 4; ++i)
@@ -252,9 +260,9 @@ __device__ __forceinline__ void trsm_update_chunk(const double* Uc, double* T, i
     for (int k = 0; k < CB * 32; ++k) {
         double u[4], y[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) u[i] = Uc[(r0 + i) * LDS + k];
+        for (int i = 0; i < 4; ++i) u[i] = Uc[(r0 + 8 * i) * LDS + k];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) y[j] = T[k * TLD + c0 + j];
+        for (int j = 0; j < 4; ++j) y[j] = T[k * TLD + c0 + 16 * j];
 #pragma unroll
         for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -263,7 +271,7 @@ __device__ __forceinline__ void trsm_update_chunk(const double* Uc, double* T, i
 #pragma unroll
     for (int i = 0; i < 4; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) T[(r0 + i) * TLD + c0 + j] -= acc[i][j];
+        for (int j = 0; j < 4; ++j) T[(r0 + 8 * i) * TLD + c0 + 16 * j] -= acc[i][j];
 }
 
 // --------------------------------------------------------------------------------
@@ -307,6 +315,12 @@ __device__ __forceinline__ void trsm_stage(const double* __restrict__ U11, int64
     __syncthreads();
 }
 
+#ifdef HYB_PROFILE_POTF2
+#define TRSM_TS(i) do { if (tid == 0 && blockIdx.x == 0) g_trsm_ts[i] = clock64(); } while (0)
+#else
+#define TRSM_TS(i)
+#endif
+
 __global__ void __launch_bounds__(TRSM_THREADS, 1)
 trsm_upper_T_kernel(const double* __restrict__ U11, int64_t ldu, int nb, double* __restrict__ A12, int64_t ld,
                     int64_t n2) {
@@ -317,26 +331,36 @@ trsm_upper_T_kernel(const double* __restrict__ U11, int64_t ldu, int nb, double*
     const int tid = threadIdx.x;
     const int64_t col0 = (int64_t)blockIdx.x * TRSM_COLS;
     const int ncol = (int)((n2 - col0 < TRSM_COLS) ? (n2 - col0) : TRSM_COLS);
+    TRSM_TS(0);
     trsm_stage(U11, ldu, nb, A12, ld, col0, ncol, Uc, T, dinv, tid);
+    TRSM_TS(1);
     const bool solver_thread = tid < TRSM_COLS;
     if (solver_thread) trsm_solve_chunk<0>(Uc, dinv, T, tid);
     __syncthreads();
+    TRSM_TS(2);
     trsm_update_chunk<1>(Uc, T, tid);
     __syncthreads();
+    TRSM_TS(3);
     if (solver_thread) trsm_solve_chunk<1>(Uc, dinv, T, tid);
     __syncthreads();
+    TRSM_TS(4);
     trsm_update_chunk<2>(Uc, T, tid);
     __syncthreads();
+    TRSM_TS(5);
     if (solver_thread) trsm_solve_chunk<2>(Uc, dinv, T, tid);
     __syncthreads();
+    TRSM_TS(6);
     trsm_update_chunk<3>(Uc, T, tid);
     __syncthreads();
+    TRSM_TS(7);
     if (solver_thread) trsm_solve_chunk<3>(Uc, dinv, T, tid);
     __syncthreads();
+    TRSM_TS(8);
     for (int e = tid; e < NB * TRSM_COLS; e += TRSM_THREADS) {
         const int r = e & (NB - 1), c = e >> 7;
         if (c < ncol && r < nb) A12[r + (col0 + c) * ld] = T[r * TLD + c];
     }
+    TRSM_TS(9);
 }
 
 // ---- backward variant: slab <- U11^-1 slab (U11 upper, back substitution) ----------------
@@ -360,7 +384,7 @@ template <int CB>
 __device__ __forceinline__ void trsm_bupdate_chunk(const double* Uc, double* T, int tid) {
     if (CB == 3) return;
     const int tr = tid >> 4, tc = tid & 15;
-    const int r0 = CB * 32 + 4 * tr, c0 = 4 * tc;
+    const int r0 = CB * 32 + tr, c0 = tc;  // interleaved like trsm_update_chunk
     double acc[4][4];
 #pragma unroll
     for (int i = 0; i < 4; ++i)
@@ -370,9 +394,9 @@ __device__ __forceinline__ void trsm_bupdate_chunk(const double* Uc, double* T, 
     for (int k = (CB + 1) * 32; k < NB; ++k) {
         double u[4], y[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) u[i] = Uc[k * LDS + r0 + i];  // U[r0+i][k]
+        for (int i = 0; i < 4; ++i) u[i] = Uc[k * LDS + r0 + 8 * i];  // U[r][k]
 #pragma unroll
-        for (int j = 0; j < 4; ++j) y[j] = T[k * TLD + c0 + j];
+        for (int j = 0; j < 4; ++j) y[j] = T[k * TLD + c0 + 16 * j];
 #pragma unroll
         for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -381,7 +405,7 @@ __device__ __forceinline__ void trsm_bupdate_chunk(const double* Uc, double* T, 
 #pragma unroll
     for (int i = 0; i < 4; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) T[(r0 + i) * TLD + c0 + j] -= acc[i][j];
+        for (int j = 0; j < 4; ++j) T[(r0 + 8 * i) * TLD + c0 + 16 * j] -= acc[i][j];
 }
 
 __global__ void __launch_bounds__(TRSM_THREADS, 1)
