@@ -351,4 +351,15 @@ def make_gpu_solver(device: int = 0, dist=None, use_peer: bool = True, mode: str
         solver.setup_comm = comm  # rank 0 does the preprocessing QR and broadcasts its outcome
         return solver
     ss = B200QRCholSystemSolver(ctx, batched_dirs=batched_dirs)
-    return Solver(ss.cones_factory, ss, **solver_kwargs)
+    solver = Solver(ss.cones_factory, ss, **solver_kwargs)
+    attach_gpu_qr(solver, ctx)
+    return solver
+
+
+def attach_gpu_qr(solver, ctx: Context) -> None:
+    """Preprocessing QRs (process.jl:109,233) of matrices with >= HYB_GPU_QR_MIN (default 256) rows and
+    columns run on the GPU (hyb_geqp3); smaller ones stay with LAPACK, where they take microseconds."""
+    import os
+
+    solver.qr_backend = ctx.geqp3
+    solver.qr_backend_min_cols = int(os.environ.get("HYB_GPU_QR_MIN", "256"))

@@ -46,7 +46,9 @@ class _PivotedQR:
     """Column-pivoted Householder QR (LAPACK dgeqp3), the ``qr!(M, ColumnNorm())``
     of process.jl:109,233.  Q is kept in factored form and applied with dormqr."""
 
-    def __init__(self, M: np.ndarray):
+    def __init__(self, M: np.ndarray, backend=None):
+        """``backend(M) -> (qr, tau, piv)`` replaces LAPACK's dgeqp3 with the same output
+        conventions (the GPU path passes ``Context.geqp3``); Q is still applied on the host."""
         M = np.array(M, dtype=np.float64, order="F")
         self.m, self.ncols = M.shape
         if M.size == 0:
@@ -54,7 +56,10 @@ class _PivotedQR:
             self.tau = np.zeros(0)
             self.piv = np.arange(self.ncols)
             return
-        (qr, tau), _, piv = sla.qr(M, mode="raw", pivoting=True, overwrite_a=True)
+        if backend is not None:
+            qr, tau, piv = backend(M)
+        else:
+            (qr, tau), _, piv = sla.qr(M, mode="raw", pivoting=True, overwrite_a=True)
         self.qr, self.tau, self.piv = np.asfortranarray(qr), tau, piv
         self.refl = np.asfortranarray(self.qr[:, : tau.size])  # Householder vectors for dormqr
 
@@ -282,6 +287,14 @@ class Solver:
         self.syssolver.set_point_sub_rhs(self)
 
     # ------------------------------------------------------------------ preprocessing
+    def _qr_backend_for(self, shape):
+        """The pivoted-QR implementation for a matrix of this shape: ``self.qr_backend`` (set by
+        the GPU path) when the matrix has at least ``qr_backend_min_cols`` columns, else LAPACK."""
+        be = getattr(self, "qr_backend", None)
+        if be is not None and min(shape) >= getattr(self, "qr_backend_min_cols", 0):
+            return be
+        return None
+
     def _rescale_data(self) -> bool:  # process.jl:15-66
         if not self.rescale:
             return False
@@ -396,7 +409,7 @@ class Solver:
         if p == 0:
             self.y_keep_idxs = np.zeros(0, dtype=np.int64)
             return
-        fact = self.Ap_fact = _PivotedQR(model.A.T)
+        fact = self.Ap_fact = _PivotedQR(model.A.T, self._qr_backend_for(model.A.T.shape))
         rank = self.Ap_rank = fact.rank_est(self.init_tol_qr)
         Ap_R = fact.R(rank)
         y_keep = fact.piv[:rank].copy()
@@ -449,7 +462,7 @@ class Solver:
         if preset is not None and (preset.m, preset.ncols) == AG.shape:
             fact = self.AG_fact = preset
         else:
-            fact = self.AG_fact = _PivotedQR(AG)
+            fact = self.AG_fact = _PivotedQR(AG, self._qr_backend_for(AG.shape))
         rank = self.AG_rank = fact.rank_est(self.init_tol_qr)
         if rank == n:
             return

@@ -67,6 +67,7 @@ SIGNATURES = {
         [C.c_void_p, C.c_int, c_double_p, c_double_p, C.c_int64, C.c_int, C.c_double, C.c_double, C.c_double, C.c_int,
          C.c_double, c_int_p, c_double_p, c_double_p],
     ),
+    "hyb_geqp3": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, c_double_p, C.c_int64, c_int_p, c_double_p]),
     "hyb_outer_prod": (
         C.c_int,
         [C.c_void_p, C.c_int64, C.c_int64, C.c_double, c_double_p, C.c_int64, C.c_double, c_double_p, C.c_int64],
@@ -172,6 +173,21 @@ class Context:
         mf, ms = C.c_double(0), C.c_double(0)
         self.check(self.lib.hyb_bench_potrf(self.ptr, N, reps, C.byref(mf), C.byref(ms)), "hyb_bench_potrf")
         return mf.value, ms.value
+
+    # ---- preprocessing -------------------------------------------------------
+    def geqp3(self, M: np.ndarray):
+        """Column-pivoted QR on the GPU; returns (qr, tau, piv) like
+        scipy.linalg.qr(M, mode="raw", pivoting=True)."""
+        A = np.array(M, dtype=np.float64, order="F")
+        m, n = A.shape
+        k = min(m, n)
+        tau = np.zeros(k)
+        piv = np.zeros(max(n, 1), dtype=np.int32)
+        self.check(
+            self.lib.hyb_geqp3(self.ptr, m, n, dptr(A), max(m, 1), piv.ctypes.data_as(c_int_p), dptr(tau) if k else None),
+            "hyb_geqp3",
+        )
+        return A, tau, piv[:n].astype(np.int64)
 
     # ---- dense helpers -----------------------------------------------------
     def outer_prod(self, A: np.ndarray, C_: Optional[np.ndarray] = None, alpha=1.0, beta=0.0) -> np.ndarray:

@@ -255,6 +255,9 @@ def make_rootworker_solver(device: int, dist, batched_dirs: bool = True, **solve
         ctx = Context(device)
         ss = RootQRCholSystemSolver(ctx, comm, device, batched_dirs=batched_dirs)
         solver = Solver(ss.cones_factory, ss, **solver_kwargs)
+        from .gpu import attach_gpu_qr
+
+        attach_gpu_qr(solver, ctx)
     else:
         ss = WorkerQRCholSystemSolver(comm, device)
         solver = Solver(ss.cones_factory, ss, **solver_kwargs)

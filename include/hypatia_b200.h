@@ -145,6 +145,14 @@ int hyb_get_directions(hyb_ctx* ctx, int nrhs, const double* rhs, double* dir, i
                        double tau_bar, double mu, double res_norm_cutoff, int max_ref_steps, double min_impr_tol,
                        int* num_ref, double* res_norm, double* sol_const);
 
+/* ---- preprocessing: src/Solvers/process.jl ------------------------------------------ */
+/* qr!(M, ColumnNorm()) = LAPACK.geqp3!, process.jl:109 ([A; G], handle_dual_eq) and :233 (A',
+ * handle_primal_eq): column-pivoted Householder QR of the m x n host matrix A (lda), in place, with
+ * LAPACK's output conventions -- R on and above the diagonal, Householder vectors below it (unit
+ * first entry implicit), tau (min(m,n)), jpvt (n, 0-based: column j of A*P is column jpvt[j] of A)
+ * -- so dormqr / triangular solves on the host consume it unchanged.  Needs no loaded model. */
+int hyb_geqp3(hyb_ctx* ctx, int64_t m, int64_t n, double* A, int64_t lda, int* jpvt, double* tau);
+
 /* ---- dense helpers: src/linearalgebra/dense.jl ---------------------------------- */
 /* outer_prod!(A, B, alpha, beta) = BLAS.syrk!('U','T'), dense.jl:72-79:
  * C(N x N, upper) = alpha A'A + beta C with A K x N (lda), C (ldc) */
