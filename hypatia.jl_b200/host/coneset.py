@@ -30,6 +30,15 @@ class ConeSet:
         # row-level mask: True where the cone's "primal" slice is z (dual barrier), point.jl:52-59
         self.dual_rows = np.repeat(self.dual_mask, self.dims) if self.K else np.zeros(0, bool)
         self.any_dual = bool(self.dual_mask.any())
+        # runs of consecutive cones of equal dimension: (first cone, number of cones, dim, first row)
+        self._runs = []
+        k = 0
+        while k < self.K:
+            k2 = k
+            while k2 + 1 < self.K and self.dims[k2 + 1] == self.dims[k]:
+                k2 += 1
+            self._runs.append((k, k2 - k + 1, int(self.dims[k]), int(self.offs[k])))
+            k = k2 + 1
 
     # ---- view helpers (point.jl:50-59) ---------------------------------
     def primal_of(self, z: np.ndarray, s: np.ndarray) -> np.ndarray:
@@ -42,6 +51,21 @@ class ConeSet:
         """K per-cone inner products <a_k, b_k> (fixed left-to-right order)."""
         if self.K == 0:
             return np.zeros(0)
+        if 4 * len(self._runs) <= self.K:
+            # many small cones of equal size (cfg4: 10^5 second-order cones): one reshaped row sum per
+            # run instead of a reduceat over 10^5 tiny segments (several times faster)
+            out = np.empty(self.K)
+            for k0, cnt, dim, r0 in self._runs:
+                sl = slice(r0, r0 + cnt * dim)
+                prod = (a[sl] * b[sl]).reshape(cnt, dim)
+                if dim <= 16:
+                    acc = prod[:, 0].copy()
+                    for j in range(1, dim):
+                        acc += prod[:, j]
+                    out[k0 : k0 + cnt] = acc
+                else:
+                    out[k0 : k0 + cnt] = prod.sum(axis=1)
+            return out
         return np.add.reduceat(a * b, self.starts)
 
     def expand(self, per_cone: np.ndarray) -> np.ndarray:
