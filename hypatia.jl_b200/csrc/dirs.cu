@@ -29,6 +29,18 @@ struct HybDirs {
     double* scal = nullptr;     // device scalars: [0] = dot_obj(sol_const), [1 + j] = dot_obj(sol_sub_j), [8 + j] = norms
     double* gemm_scratch = nullptr;
     bool have_const = false;
+    // device-resident line search (search.jl:72-162): the current point, the four directions of the
+    // iteration (slots: 0 cent, 1 centadj, 2 pred, 3 predadj), per-cone data
+    double *pz = nullptr, *ps = nullptr;       // point.z, point.s
+    double *kz = nullptr, *ks = nullptr;       // kept directions: ldq x 4 each
+    double* szk = nullptr;                     // K : <s_k, z_k> of the candidate
+    double* nus = nullptr;                     // K : barrier parameters
+    int64_t *cone_off = nullptr;               // K : first row of every cone
+    int* cone_dim = nullptr;                   // K
+    double* sred = nullptr;                    // [0] min szk, [1] sum szk ; int flag in sflag
+    int* sflag = nullptr;
+    int64_t K = 0;
+    bool search_ready = false;
 };
 
 namespace {
@@ -291,6 +303,16 @@ void hyb_dirs_free(hyb_ctx* c) {
     cudaFree(d->zc);
     cudaFree(d->scal);
     cudaFree(d->gemm_scratch);
+    cudaFree(d->pz);
+    cudaFree(d->ps);
+    cudaFree(d->kz);
+    cudaFree(d->ks);
+    cudaFree(d->szk);
+    cudaFree(d->nus);
+    cudaFree(d->cone_off);
+    cudaFree(d->cone_dim);
+    cudaFree(d->sred);
+    cudaFree(d->sflag);
     delete d;
     c->dirs = nullptr;
 }
@@ -447,6 +469,31 @@ int hyb_dirs_setup(hyb_ctx* c, const double* cvec, const double* hvec) {
     HYB_CUDA(cudaMemset(d->Vx, 0, sizeof(double) * d->ldn * M));
     HYB_CUDA(cudaMemset(d->T, 0, sizeof(double) * d->ldn * M));
     HYB_CUDA(cudaMemset(d->scal, 0, sizeof(double) * 16));
+    // line-search state
+    const int64_t K = d->K = c->cones.K;
+    const int64_t Ka = K > 0 ? K : 1;
+    HYB_CUDA(cudaMalloc(&d->pz, sizeof(double) * d->ldq));
+    HYB_CUDA(cudaMalloc(&d->ps, sizeof(double) * d->ldq));
+    HYB_CUDA(cudaMalloc(&d->kz, sizeof(double) * d->ldq * 4));
+    HYB_CUDA(cudaMalloc(&d->ks, sizeof(double) * d->ldq * 4));
+    HYB_CUDA(cudaMemset(d->kz, 0, sizeof(double) * d->ldq * 4));
+    HYB_CUDA(cudaMemset(d->ks, 0, sizeof(double) * d->ldq * 4));
+    HYB_CUDA(cudaMalloc(&d->szk, sizeof(double) * Ka));
+    HYB_CUDA(cudaMalloc(&d->nus, sizeof(double) * Ka));
+    HYB_CUDA(cudaMalloc(&d->cone_off, sizeof(int64_t) * Ka));
+    HYB_CUDA(cudaMalloc(&d->cone_dim, sizeof(int) * Ka));
+    HYB_CUDA(cudaMalloc(&d->sred, sizeof(double) * 2));
+    HYB_CUDA(cudaMalloc(&d->sflag, sizeof(int)));
+    std::vector<int64_t> off((size_t)Ka, 0);
+    std::vector<int> dm((size_t)Ka, 0);
+    for (const HybConeBlock& b : c->cones.blocks)
+        for (int64_t i = 0; i < b.count; ++i) {
+            off[(size_t)(b.cone0 + i)] = b.offset + i * b.dim;
+            dm[(size_t)(b.cone0 + i)] = b.dim;
+        }
+    HYB_CUDA(cudaMemcpy(d->cone_off, off.data(), sizeof(int64_t) * Ka, cudaMemcpyHostToDevice));
+    HYB_CUDA(cudaMemcpy(d->cone_dim, dm.data(), sizeof(int) * Ka, cudaMemcpyHostToDevice));
+    d->search_ready = false;
     return 0;
 }
 
@@ -557,6 +604,235 @@ int hyb_get_directions(hyb_ctx* c, int nrhs, const double* rhs, double* dir, int
     }
     HYB_CUDA(cudaStreamSynchronize(st));
     ksync(c);
+    return 0;
+}
+
+}  // extern "C"
+
+// =============================================================================================
+// Device-resident line search: check_cone_points (search.jl:100-162) on a candidate
+//   cand.ztsk = point.ztsk + sum_k coef_k dir_k.ztsk            (update_stepper_points, combined.jl:129-177)
+// formed on the device from the point and the four directions kept after hyb_get_directions, so a
+// candidate costs a few small kernels and two or three scalars over PCIe instead of two q-vectors
+// and O(q) host arithmetic.  tau / kap (scalars) stay with the host.
+// =============================================================================================
+namespace {
+
+// candidate primal / dual slices of every cone (point.jl:50-59: dual-barrier cones take z as primal)
+__global__ void cand_kernel(int64_t q, int64_t ldq, double c0, double c1, double c2, double c3,
+                            const double* __restrict__ pz, const double* __restrict__ ps, const double* __restrict__ kz,
+                            const double* __restrict__ ks, const unsigned char* __restrict__ dual_row,
+                            double* __restrict__ primal, double* __restrict__ dual) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= q) return;
+    double z = pz[i], s = ps[i];
+    // same order of additions as the host's `cand += a*d1 + b*d2 + ...` (left to right)
+    double dz = 0.0, ds = 0.0;
+    bool first = true;
+    const double cf[4] = {c0, c1, c2, c3};
+    // order used by update_stepper_points: pred, predadj, cent, centadj  (slots 2, 3, 0, 1)
+    const int order[4] = {2, 3, 0, 1};
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+        const int k = order[t];
+        if (cf[k] != 0.0) {
+            const double az = cf[k] * kz[i + (int64_t)k * ldq], as = cf[k] * ks[i + (int64_t)k * ldq];
+            dz = first ? az : dz + az;
+            ds = first ? as : ds + as;
+            first = false;
+        }
+    }
+    z += dz;
+    s += ds;
+    const bool dr = dual_row[i] != 0;
+    primal[i] = dr ? z : s;
+    dual[i] = dr ? s : z;
+}
+// <primal_k, dual_k> per cone, one warp per cone
+__global__ void __launch_bounds__(256)
+cone_dots_kernel(int64_t K, const int64_t* __restrict__ off, const int* __restrict__ dim, const double* __restrict__ a,
+                 const double* __restrict__ b, double* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int64_t k = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (k >= K) return;
+    const int64_t o = off[k];
+    const int n = dim[k];
+    double s = 0.0;
+    for (int r = lane; r < n; r += 32) s += a[o + r] * b[o + r];
+#pragma unroll
+    for (int w = 16; w > 0; w >>= 1) s += __shfl_xor_sync(0xffffffffu, s, w);
+    if (lane == 0) out[k] = s;
+}
+// min and sum of szk (one CTA, fixed order)
+__global__ void __launch_bounds__(1024)
+szk_reduce_kernel(int64_t K, const double* __restrict__ szk, double* __restrict__ out) {
+    __shared__ double smin[32], ssum[32];
+    double mn = INFINITY, sm = 0.0;
+    bool nan = false;
+    for (int64_t k = threadIdx.x; k < K; k += 1024) {
+        const double v = szk[k];
+        nan |= (v != v);
+        mn = fmin(mn, v);
+        sm += v;
+    }
+    if (nan) mn = NAN;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const double om = __shfl_xor_sync(0xffffffffu, mn, o);
+        mn = (mn != mn || om != om) ? NAN : fmin(mn, om);
+        sm += __shfl_xor_sync(0xffffffffu, sm, o);
+    }
+    if (lane == 0) {
+        smin[w] = mn;
+        ssum[w] = sm;
+    }
+    __syncthreads();
+    if (w == 0) {
+        mn = smin[lane];
+        sm = ssum[lane];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const double om = __shfl_xor_sync(0xffffffffu, mn, o);
+            mn = (mn != mn || om != om) ? NAN : fmin(mn, om);
+            sm += __shfl_xor_sync(0xffffffffu, sm, o);
+        }
+        if (lane == 0) {
+            out[0] = mn;
+            out[1] = sm;
+        }
+    }
+}
+// per-cone gates of search.jl:124-130: sz_rel < min_prox or nu (sz_rel - 1)^2 > bound
+__global__ void __launch_bounds__(1024)
+szk_gate_kernel(int64_t K, const double* __restrict__ szk, const double* __restrict__ nus, double mu, double min_prox,
+                double bound, int* __restrict__ flag) {
+    __shared__ int any;
+    if (threadIdx.x == 0) any = 0;
+    __syncthreads();
+    int bad = 0;
+    for (int64_t k = threadIdx.x; k < K; k += 1024) {
+        const double nu = nus[k];
+        const double rel = szk[k] / (mu * nu);
+        const double dv = rel - 1.0;
+        if (rel < min_prox || nu * (dv * dv) > bound) bad = 1;
+    }
+    if (bad) atomicOr(&any, 1);
+    __syncthreads();
+    if (threadIdx.x == 0) *flag = any;
+}
+
+}  // namespace
+
+extern "C" {
+
+int hyb_search_setup(hyb_ctx* c, const double* nus) {
+    if (!c || !c->loaded || !c->dirs) {
+        hyb_set_error("hyb_search_setup: call hyb_dirs_setup first");
+        return -3;
+    }
+    HybDirs& d = *c->dirs;
+    HYB_CUDA(cudaSetDevice(c->device));
+    if (d.K > 0) HYB_CUDA(cudaMemcpy(d.nus, nus, sizeof(double) * d.K, cudaMemcpyHostToDevice));
+    d.search_ready = true;
+    return 0;
+}
+
+int hyb_dirs_keep(hyb_ctx* c, int col, int slot) {
+    if (!c || !c->loaded || !c->dirs) return -1;
+    HybDirs& d = *c->dirs;
+    if (col < 0 || col >= HYB_MAX_RHS || slot < 0 || slot > 3) {
+        hyb_set_error("hyb_dirs_keep: column %d / slot %d out of range", col, slot);
+        return -3;
+    }
+    HYB_CUDA(cudaSetDevice(c->device));
+    if (d.q > 0) {
+        HYB_CUDA(cudaMemcpyAsync(d.kz + (int64_t)slot * d.ldq, d.dir.z + (int64_t)col * d.ldq, sizeof(double) * d.q,
+                                 cudaMemcpyDeviceToDevice, c->st));
+        HYB_CUDA(cudaMemcpyAsync(d.ks + (int64_t)slot * d.ldq, d.dir.s + (int64_t)col * d.ldq, sizeof(double) * d.q,
+                                 cudaMemcpyDeviceToDevice, c->st));
+    }
+    return 0;
+}
+
+int hyb_search_load_point(hyb_ctx* c, const double* z, const double* s) {
+    if (!c || !c->loaded || !c->dirs) return -1;
+    HybDirs& d = *c->dirs;
+    HYB_CUDA(cudaSetDevice(c->device));
+    if (d.q > 0) {
+        HYB_CUDA(h2d(c, d.pz, z, sizeof(double) * d.q));
+        HYB_CUDA(h2d(c, d.ps, s, sizeof(double) * d.q));
+    }
+    return 0;
+}
+
+int hyb_search_gates(hyb_ctx* c, const double* coef, double* min_szk, double* sum_szk) {
+    if (!c || !c->loaded || !c->dirs || !c->dirs->search_ready) {
+        hyb_set_error("hyb_search_gates: call hyb_search_setup first");
+        return -3;
+    }
+    HybDirs& d = *c->dirs;
+    HYB_CUDA(cudaSetDevice(c->device));
+    cudaStream_t st = c->st;
+    const int64_t q = d.q, K = d.K;
+    *min_szk = INFINITY;
+    *sum_szk = 0.0;
+    if (q == 0 || K == 0) return 0;
+    KBEGIN(c);
+    cand_kernel<<<(unsigned)((q + 255) / 256), 256, 0, st>>>(q, d.ldq, coef[0], coef[1], coef[2], coef[3], d.pz, d.ps, d.kz, d.ks,
+                                                           d.dual_row, c->in_primal, c->in_dual);
+    cone_dots_kernel<<<(unsigned)((K + 7) / 8), 256, 0, st>>>(K, d.cone_off, d.cone_dim, c->in_primal, c->in_dual, d.szk);
+    szk_reduce_kernel<<<1, 1024, 0, st>>>(K, d.szk, d.sred);
+    HYB_CUDA(cudaGetLastError());
+    g_misc_launches += 3;
+    KEND(c);
+    // the loaded cone state no longer matches in_primal / in_dual until hyb_search_check runs
+    c->point_loaded = false;
+    c->updated_irtmu = NAN;
+    double out[2];
+    HYB_CUDA(d2h(c, out, d.sred, sizeof(double) * 2));
+    HYB_CUDA(cudaStreamSynchronize(st));
+    ksync(c);
+    *min_szk = out[0];
+    *sum_szk = out[1];
+    return 0;
+}
+
+int hyb_search_check(hyb_ctx* c, double mu, double min_prox, double proxsqr_bound, int use_max_prox, double agg0, int* ok,
+                     double* agg) {
+    if (!c || !c->loaded || !c->dirs || !c->dirs->search_ready) return -1;
+    HybDirs& d = *c->dirs;
+    HYB_CUDA(cudaSetDevice(c->device));
+    cudaStream_t st = c->st;
+    *ok = 0;
+    *agg = agg0;
+    const double irtmu = 1.0 / sqrt(mu);
+    if (d.K > 0) {
+        KBEGIN(c);
+        szk_gate_kernel<<<1, 1024, 0, st>>>(d.K, d.szk, d.nus, mu, min_prox, proxsqr_bound, d.sflag);
+        HYB_CUDA(cudaGetLastError());
+        ++g_misc_launches;
+        KEND(c);
+        int viol = 0;
+        HYB_CUDA(d2h(c, &viol, d.sflag, sizeof(int)));
+        HYB_CUDA(cudaStreamSynchronize(st));
+        ksync(c);
+        if (viol) return 0;
+    }
+    // load_point(cone, primal, irtmu), load_dual_point, reset_data, then the oracle checks (search.jl:141-158)
+    c->loaded_scal = irtmu;
+    c->point_loaded = true;
+    c->updated_irtmu = NAN;
+    KBEGIN(c);
+    HYB_CHECK(hyb_ensure_updated(c, irtmu));
+    KEND(c);
+    int flags = 0;
+    double a = 0.0;
+    HYB_CHECK(hybi_cones_reduce(st, c->cones, use_max_prox, &flags, &a));
+    ksync(c);
+    const double total = use_max_prox ? fmax(agg0, a) : agg0 + a;
+    *agg = total;
+    *ok = (flags == HYB_ST_ALL) && (total < proxsqr_bound) ? 1 : 0;
     return 0;
 }
 

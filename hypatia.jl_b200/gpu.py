@@ -100,6 +100,16 @@ class GpuConeBatch(ConeSet):
     def reset_data(self):
         self._dirty = True
 
+    def note_device_point(self, primal, dual, scal):
+        """The device already holds this point (loaded by hyb_search_check from a candidate it formed
+        itself): bring the host mirror up to date without pushing anything."""
+        self._pending_primal = np.array(primal, dtype=np.float64)
+        self._pending_dual = np.array(dual, dtype=np.float64)
+        self._pending_scal = float(scal)
+        self._point = self._pending_primal * scal if scal != 1.0 else self._pending_primal.copy()
+        self._grad = None
+        self._dirty = False
+
     def _sync(self):
         if getattr(self, "_dirty", False):
             self._push()
@@ -181,6 +191,11 @@ class B200QRCholSystemSolver(QRCholSystemSolver):
         # device-resident get_directions in batched pairs (hyb_get_directions); False keeps the
         # reference's one-direction-at-a-time call pattern through the generic host code
         self.batched_dirs = batched_dirs
+        # line-search candidates formed and gated on the device (hyb_search_*); needs the directions
+        # the batched solves leave there.  HYB_HOST_SEARCH=1 keeps the host loop of search.jl
+        import os
+
+        self.device_search = bool(batched_dirs) and not os.environ.get("HYB_HOST_SEARCH")
         self._dev_const_stale = True
         self._host_const_stale = True
         self.time_assemble_ms = 0.0
@@ -210,6 +225,8 @@ class B200QRCholSystemSolver(QRCholSystemSolver):
         m = solver.model
         cv, hv = f64(m.c), f64(m.h)
         self.ctx.check(self.lib.hyb_dirs_setup(self.ctx.ptr, dptr(cv), dptr(hv)), "hyb_dirs_setup")
+        nus = f64(solver.cones.nus)
+        self.ctx.check(self.lib.hyb_search_setup(self.ctx.ptr, dptr(nus) if nus.size else None), "hyb_search_setup")
         self._dev_const_stale = self._host_const_stale = True
 
     # ---- update_lhs (qrchol.jl:189-207) ------------------------------------------
@@ -247,7 +264,27 @@ class B200QRCholSystemSolver(QRCholSystemSolver):
         super().solve_subsystem4(solver, sol, rhs)
 
     # ---- get_directions (common.jl:22-83), device-resident and batched --------------
-    def get_directions_batch(self, stepper, solver, rhs_points, dir_points) -> None:
+    # ---- check_cone_points (search.jl:100-162) on the device ---------------------------
+    def search_load_point(self, point) -> None:
+        z, s_ = f64(point.z), f64(point.s)
+        self.ctx.check(self.lib.hyb_search_load_point(self.ctx.ptr, dptr(z), dptr(s_)), "hyb_search_load_point")
+
+    def search_gates(self, coefs):
+        cf = (C.c_double * 4)(*coefs)
+        mn, sm = C.c_double(0), C.c_double(0)
+        self.ctx.check(self.lib.hyb_search_gates(self.ctx.ptr, cf, C.byref(mn), C.byref(sm)), "hyb_search_gates")
+        return mn.value, sm.value
+
+    def search_check(self, mu, min_prox, proxsqr_bound, use_max_prox, agg0):
+        ok, agg = C.c_int(0), C.c_double(0)
+        self.ctx.check(
+            self.lib.hyb_search_check(self.ctx.ptr, float(mu), float(min_prox), float(proxsqr_bound), int(use_max_prox),
+                                      float(agg0), C.byref(ok), C.byref(agg)),
+            "hyb_search_check",
+        )
+        return bool(ok.value), float(agg.value)
+
+    def get_directions_batch(self, stepper, solver, rhs_points, dir_points, slots=None) -> None:
         import math
 
         solver.cones._sync()
@@ -271,6 +308,9 @@ class B200QRCholSystemSolver(QRCholSystemSolver):
             self.sol_const.x[:] = sc[: self.N]
             self.sol_const.z[:] = sc[self.N :]
             self._dev_const_stale = self._host_const_stale = False
+        if slots is not None and self.device_search:
+            for j, slot in enumerate(slots):
+                self.ctx.check(self.lib.hyb_dirs_keep(self.ctx.ptr, j, int(slot)), "hyb_dirs_keep")
         self.last_res_norms = [float(v) for v in rn]
         self.last_num_refs = [int(v) for v in nref]
         for j, d in enumerate(dir_points):

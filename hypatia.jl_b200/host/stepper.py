@@ -77,9 +77,10 @@ class CombinedStepper:
             # each other, and each adjustment needs only its own unadjusted direction
             # (combined.jl:74-95), so the four solves run as two batched pairs.
             ss = solver.syssolver
-            for (b1, d1), (b2, d2), needs_dir in (
-                ((update_rhs_cent, self.dir_cent), (update_rhs_pred, self.dir_pred), False),
-                ((update_rhs_centadj, self.dir_centadj), (update_rhs_predadj, self.dir_predadj), True),
+            # direction slots on the device for the line search: 0 cent, 1 centadj, 2 pred, 3 predadj
+            for (b1, d1), (b2, d2), needs_dir, slots in (
+                ((update_rhs_cent, self.dir_cent), (update_rhs_pred, self.dir_pred), False, (0, 2)),
+                ((update_rhs_centadj, self.dir_centadj), (update_rhs_predadj, self.dir_predadj), True, (1, 3)),
             ):
                 t0 = time.time()
                 if needs_dir:
@@ -90,7 +91,7 @@ class CombinedStepper:
                     b2(solver, self.rhs2)
                 solver.time_uprhs += time.time() - t0
                 t0 = time.time()
-                ss.get_directions_batch(self, solver, (self.rhs, self.rhs2), (d1, d2))
+                ss.get_directions_batch(self, solver, (self.rhs, self.rhs2), (d1, d2), slots)
                 solver.time_getdir += time.time() - t0
             builders = ()
         else:
@@ -114,6 +115,9 @@ class CombinedStepper:
 
         self.unadj_only = self.cent_only = False
         t0 = time.time()
+        self._device_search = bool(getattr(solver.syssolver, "device_search", False)) and solver.cones.K > 0
+        if self._device_search:
+            solver.syssolver.search_load_point(point)
         alpha = self.search_alpha(point, solver)
         if alpha == 0.0:
             self.unadj_only = True  # combined without adjustment
@@ -172,14 +176,68 @@ class CombinedStepper:
         sched = self.start_sched()
         while sched <= len(searcher.alpha_sched):
             alpha = searcher.alpha_sched[sched - 1]
-            self.update_stepper_points(alpha, point, True)
             self.last_num_cand += 1
-            if self.check_cone_points(solver):
+            if getattr(self, "_device_search", False):
+                accepted = self.check_cone_points_device(solver, point, alpha)
+            else:
+                self.update_stepper_points(alpha, point, True)
+                accepted = self.check_cone_points(solver)
+            if accepted:
                 searcher.prev_sched = sched
                 return alpha
             sched += 1
         searcher.prev_sched = sched
+        if getattr(self, "_device_search", False):
+            solver.cones.reset_data()  # the device holds a rejected candidate: reload on next use
         return 0.0
+
+    def _coefs(self, alpha: float):
+        """Coefficients of (cent, centadj, pred, predadj) in update_stepper_points (combined.jl:146-173)."""
+        if self.unadj_only:
+            return (alpha, 0.0, 0.0, 0.0) if self.cent_only else (1 - alpha, 0.0, alpha, 0.0)
+        if self.cent_only:
+            return (alpha, alpha * alpha, 0.0, 0.0)
+        am1 = 1 - alpha
+        return (am1, am1 * am1, alpha, alpha * alpha)
+
+    # ---- search.jl:100-162 with the O(q) work on the device (hyb_search_gates / hyb_search_check) ----
+    def check_cone_points_device(self, solver, point: Point, alpha: float) -> bool:
+        searcher, ss, cones = self.searcher, solver.syssolver, solver.cones
+        min_prox = searcher.min_prox
+        proxsqr_bound = searcher.prox_bound**2
+        cf = self._coefs(alpha)
+        dirs = (self.dir_cent, self.dir_centadj, self.dir_pred, self.dir_predadj)
+        # tau, kap of the candidate: same left-to-right sum as update_stepper_points
+        dtau = dkap = None
+        for k in (2, 3, 0, 1):
+            if cf[k] != 0.0:
+                dtau = cf[k] * dirs[k].tau if dtau is None else dtau + cf[k] * dirs[k].tau
+                dkap = cf[k] * dirs[k].kap if dkap is None else dkap + cf[k] * dirs[k].kap
+        tau, kap = point.tau + (dtau or 0.0), point.kap + (dkap or 0.0)
+        taukap = tau * kap
+        if min(tau, kap, taukap) < EPS:
+            return False
+        min_szk, sum_szk = ss.search_gates(cf)
+        if min_szk < EPS:
+            return False
+        mu = (sum_szk + taukap) / searcher.nup1
+        if mu < EPS:
+            return False
+        taukap_rel = taukap / mu
+        if taukap_rel < min_prox:
+            return False
+        taukap_proxsqr = (taukap_rel - 1.0) ** 2
+        if taukap_proxsqr > proxsqr_bound:
+            return False
+        ok, agg = ss.search_check(mu, min_prox, proxsqr_bound, searcher.use_max_prox, taukap_proxsqr)
+        if not ok:
+            return False
+        searcher.prox = math.sqrt(agg)
+        # accepted: the device holds the candidate; refresh the host mirror of the cone batch once
+        self.update_stepper_points(alpha, point, True)
+        cand = self.temp
+        cones.note_device_point(cones.primal_of(cand.z, cand.s), cones.dual_of(cand.z, cand.s), 1.0 / math.sqrt(mu))
+        return True
 
     # ---- search.jl:100-162 -------------------------------------------------
     def check_cone_points(self, solver) -> bool:

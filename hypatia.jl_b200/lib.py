@@ -67,6 +67,11 @@ SIGNATURES = {
         [C.c_void_p, C.c_int, c_double_p, c_double_p, C.c_int64, C.c_int, C.c_double, C.c_double, C.c_double, C.c_int,
          C.c_double, c_int_p, c_double_p, c_double_p],
     ),
+    "hyb_search_setup": (C.c_int, [C.c_void_p, c_double_p]),
+    "hyb_dirs_keep": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
+    "hyb_search_load_point": (C.c_int, [C.c_void_p, c_double_p, c_double_p]),
+    "hyb_search_gates": (C.c_int, [C.c_void_p, c_double_p, c_double_p, c_double_p]),
+    "hyb_search_check": (C.c_int, [C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_int, C.c_double, c_int_p, c_double_p]),
     "hyb_geqp3": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, c_double_p, C.c_int64, c_int_p, c_double_p]),
     "hyb_outer_prod": (
         C.c_int,

@@ -145,6 +145,28 @@ int hyb_get_directions(hyb_ctx* ctx, int nrhs, const double* rhs, double* dir, i
                        double tau_bar, double mu, double res_norm_cutoff, int max_ref_steps, double min_impr_tol,
                        int* num_ref, double* res_norm, double* sol_const);
 
+/* ---- device-resident line search: src/Solvers/search.jl, steppers/combined.jl ------------ */
+/* Barrier parameters nu_k of the K cones (Cones.get_nu, used by the gates of search.jl:124-130).
+ * Call once after hyb_dirs_setup. */
+int hyb_search_setup(hyb_ctx* ctx, const double* nus);
+/* Keep column `col` of the last hyb_get_directions result on the device as direction `slot`
+ * (0 cent, 1 centadj, 2 pred, 3 predadj: the four directions of combined.jl:74-95). */
+int hyb_dirs_keep(hyb_ctx* ctx, int col, int slot);
+/* point.z, point.s of the current iterate (q each). */
+int hyb_search_load_point(hyb_ctx* ctx, const double* z, const double* s);
+/* First half of check_cone_points (search.jl:100-122) for the candidate
+ *   cand = point + coef[0] cent + coef[1] centadj + coef[2] pred + coef[3] predadj
+ * (update_stepper_points, combined.jl:129-177; tau and kap stay with the caller): forms the
+ * candidate's primal / dual cone slices on the device and returns min_k <s_k, z_k> and sum_k <s_k, z_k>. */
+int hyb_search_gates(hyb_ctx* ctx, const double* coef, double* min_szk, double* sum_szk);
+/* Second half (search.jl:124-158) for the same candidate, given its mu: the per-cone gates
+ * sz_rel >= min_prox and nu (sz_rel - 1)^2 <= proxsqr_bound, then load_point(1/sqrt(mu)) /
+ * load_dual_point / reset_data and the batched oracle checks of hyb_cones_check with the
+ * aggregate started at agg0.  *ok = 1 iff the candidate is accepted; the cone batch is then
+ * loaded at the candidate like after hyb_cones_load_point. */
+int hyb_search_check(hyb_ctx* ctx, double mu, double min_prox, double proxsqr_bound, int use_max_prox, double agg0,
+                     int* ok, double* agg);
+
 /* ---- preprocessing: src/Solvers/process.jl ------------------------------------------ */
 /* qr!(M, ColumnNorm()) = LAPACK.geqp3!, process.jl:109 ([A; G], handle_dual_eq) and :233 (A',
  * handle_primal_eq): column-pivoted Householder QR of the m x n host matrix A (lda), in place, with

@@ -127,3 +127,27 @@ def test_multi_rhs_wavefront_solves(N, R):
     assert info == 0
     ref = np.linalg.solve(A, B)
     assert np.max(np.abs(X - ref)) <= 1e-10 * np.max(np.abs(ref))
+
+
+@pytest.mark.parametrize("name", list(MODELS))
+def test_device_line_search_matches_host_loop(name, monkeypatch):
+    """check_cone_points on the device (hyb_search_gates / hyb_search_check) takes the same
+    accept / reject decisions as the host loop of search.jl:72-162."""
+    dev = make_gpu_solver(0, trace=True)
+    assert dev.syssolver.device_search
+    monkeypatch.setenv("HYB_HOST_SEARCH", "1")
+    host = make_gpu_solver(0, trace=True)
+    assert not host.syssolver.device_search
+    for s in (dev, host):
+        s.load(MODELS[name]())
+        s.solve()
+    assert dev.status == host.status
+    assert abs(dev.num_iters - host.num_iters) <= 1
+    if host.status == "Optimal":
+        assert abs(dev.primal_obj - host.primal_obj) <= 1e-7 * (1 + abs(host.primal_obj))
+    # same step lengths and candidate counts while the iterates are away from the rounding floor
+    n = max(3, min(len(dev.trace), len(host.trace)) // 2)
+    assert [r["alpha"] for r in dev.trace[:n]] == [r["alpha"] for r in host.trace[:n]]
+    assert [r["n_cand"] for r in dev.trace[:n]] == [r["n_cand"] for r in host.trace[:n]]
+    assert np.allclose([r["mu"] for r in dev.trace[:n]], [r["mu"] for r in host.trace[:n]], rtol=1e-9)
+    assert np.allclose([r["prox"] for r in dev.trace[:n]], [r["prox"] for r in host.trace[:n]], rtol=1e-6, atol=1e-12)
