@@ -239,7 +239,14 @@ int hybd_psd_update(cudaStream_t st, HybDensePsd* c, const double* primal, const
     copy_block_kernel<<<nb1((int64_t)s * s), 256, 0, st>>>(c->X, c->Ux, ld, s, s);
     g_dense_launches += 5;
     HYB_CUDA(cudaGetLastError());
-    HYB_CHECK(hyb_potrf(st, c->chX, nullptr));
+    int inf_x = 0;
+    HYB_CHECK(hyb_potrf(st, c->chX, &inf_x));
+    if (inf_x != 0) {  // infeasible candidate: rejected before grad / Hessian are needed (search.jl:146-150)
+        psd_finalize_kernel<<<1, 1, 0, st>>>(c->chX.info, c->chW.info, c->scal, s, dim, flag, prox);
+        DLAUNCHED();
+        HYB_CUDA(cudaGetLastError());
+        return 0;
+    }
     HYB_CHECK(hyb_transpose(st, c->Ux, ld, s, s, c->Lx, ld, 1));
     // Xinv = X^-1 by two triangular solves on the identity (update_grad, possemideftri.jl:106-116)
     set_identity_kernel<<<nb1((int64_t)s * s), 256, 0, st>>>(c->Xinv, ld, s);
@@ -579,7 +586,21 @@ int hybd_wsos_update(cudaStream_t st, HybDenseWsos* c, const double* primal, con
         rowscale_kernel<<<nb1(U * L), 256, 0, st>>>(c->P[k], c->v3, U, L, ldU, c->PD);
         DLAUNCHED();
         HYB_CHECK(hyb_gemm_tn(st, L, L, U, 1.0, c->P[k], ldU, c->PD, ldU, 0.0, c->Lam[k], ldL, HYB_GEMM_UPPER));
-        HYB_CHECK(hyb_potrf(st, c->chLam[k], nullptr));
+        int inf = 0;
+        HYB_CHECK(hyb_potrf(st, c->chLam[k], &inf));
+        if (inf != 0) {
+            // not in the cone: update_feas stops at the first Lambda_k that is not positive definite
+            // (wsosinterpnonnegative.jl:99-128) and the line search rejects the candidate before any
+            // gradient / Hessian oracle is asked for (search.jl:146-150) -- skip that work (3/4 of it)
+            wsos_finalize_kernel<<<1, 1, 0, st>>>(c->lam_infos_dev, c->nPs, c->chH.info, c->dual_ok, c->scal, c->nu, U, flag,
+                                                  prox, c->slow, c->sqrt_ok);
+            DLAUNCHED();
+            HYB_CUDA(cudaGetLastError());
+            return 0;
+        }
+    }
+    for (int k = 0; k < c->nPs; ++k) {
+        const int64_t L = c->L[k], ldL = c->ldL[k];
         // F_k = R_k^-T P_k'
         copy_mat_kernel<<<nb1(L * U), 256, 0, st>>>(c->Pt[k], ldL, c->F[k], ldL, L, U);
         DLAUNCHED();
