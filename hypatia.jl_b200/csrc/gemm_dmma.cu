@@ -250,8 +250,8 @@ gemm_tail_reduce_kernel(int M, int N, double alpha, double beta, double* __restr
 
 int64_t g_gemm_launches = 0;
 int g_gemm_num_sms = 0;
-struct TailWs { cudaStream_t st; double* p; };
-std::vector<TailWs> g_tail_ws;  // one workspace per stream that ever needed one (never shrinks)
+struct TailWs { int dev; cudaStream_t st; double* p; };
+std::vector<TailWs> g_tail_ws;  // one workspace per (device, stream) that ever needed one (never shrinks)
 
 }  // namespace
 
@@ -289,11 +289,9 @@ int hyb_gemm_tn(cudaStream_t st, int64_t M, int64_t N, int64_t K, double alpha, 
     }
     if (((uintptr_t)C & 15) == 0 && (ldc & 1) == 0) flags |= HYB_GEMM_CVEC;
     // split the tiles of a small last wave along K (long contractions only: the Schur syrk)
-    if (g_gemm_num_sms == 0) {
-        int dev = 0;
-        HYB_CUDA(cudaGetDevice(&dev));
-        HYB_CUDA(cudaDeviceGetAttribute(&g_gemm_num_sms, cudaDevAttrMultiProcessorCount, dev));
-    }
+    int dev = 0;
+    HYB_CUDA(cudaGetDevice(&dev));
+    if (g_gemm_num_sms == 0) HYB_CUDA(cudaDeviceGetAttribute(&g_gemm_num_sms, cudaDevAttrMultiProcessorCount, dev));
     const int P = g_gemm_num_sms;
     int64_t n_main = ntiles;
     int nsplit = 1;
@@ -307,10 +305,10 @@ int hyb_gemm_tn(cudaStream_t st, int64_t M, int64_t N, int64_t K, double alpha, 
         if (nsplit >= 2) {
             n_main = ntiles - r;
             for (auto& w : g_tail_ws)
-                if (w.st == st) ws = w.p;
+                if (w.dev == dev && w.st == st) ws = w.p;
             if (!ws) {
                 HYB_CUDA(cudaMalloc(&ws, sizeof(double) * BM * BN * (size_t)P));
-                g_tail_ws.push_back({st, ws});
+                g_tail_ws.push_back({dev, st, ws});
             }
         } else {
             nsplit = 1;
