@@ -410,6 +410,9 @@ def main():
         }),
         "e2e": {"value": k / wall, "unit": "iterations/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": launches,
+        # untimed set-up of the solve (Solvers.jl:395-429), seconds: rescale, primal-equality QR + reduce,
+        # dual-equality pivoted QR (hyb_geqp3 on the GPU) + initial point, upload of G*Q2
+        "setup_s": {name: float(getattr(gpu, "time_" + name, 0.0)) for name in ("rescale", "inity", "initx", "loadsys")},
         "phase_ms": {name: float(np.mean([r["ph_" + name] for r in rows])) for name in ("upsys", "uprhs", "getdir", "search")},
         "schur_assemble_ms": t_w + t_syrk,
         "schur_reduce_ms": reduce_ms,
