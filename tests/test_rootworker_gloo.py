@@ -30,6 +30,8 @@ def _build(which):
 
         G = -np.array([[1.0, 1.0], [1.0, 1.0], [2.0, 2.0]])
         return Model(np.array([1.0, -1.0]), np.zeros((0, 2)), np.zeros(0), G, np.zeros(3), [Nonnegative(3)])
+    if which[0] == "known":
+        return instances.KNOWN_ANSWER[which[1]]()[0]
     return getattr(instances, which[0])(**which[1])
 
 
@@ -196,6 +198,25 @@ def test_rootworker_solve_matches_single_process(which):
     assert min(row_counts) > 0
     # every Schur update of the root was served by the worker, which then got the stop message
     assert workers == [("worker", "Worker", collects)] and collects >= iters
+
+
+def test_rootworker_with_an_empty_shard():
+    """Fewer cone atoms than ranks: a worker owns no rows, serves every update with a zero slot."""
+    import hypatia_b200  # noqa: F401
+    from hypatia_b200.host.solver import Solver
+    from oracle.cones import CpuConeSet
+    from oracle.qrchol import QRCholDenseSystemSolver
+
+    which = ("known", "epinormeucl1")
+    root, workers = _run(which, world=3)
+    _, status, iters, obj, mus, row_counts, collects = root
+    ref = Solver(CpuConeSet, QRCholDenseSystemSolver(), trace=True)
+    ref.load(_build(which))
+    ref.solve()
+    assert min(row_counts) == 0 and sum(row_counts) == ref.model.q
+    assert status == ref.status == "Optimal" and iters == ref.num_iters
+    assert abs(obj - ref.primal_obj) <= 1e-9 * (1 + abs(ref.primal_obj))
+    assert sorted(workers) == [("worker", "Worker", collects)] * 2
 
 
 def test_rootworker_abort_releases_workers():
