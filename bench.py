@@ -24,7 +24,48 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+
+def _host_cores():
+    """(physical cores, logical cpus) of this box."""
+    logical = os.cpu_count() or 1
+    try:
+        import psutil
+
+        return int(psutil.cpu_count(logical=False) or logical), logical
+    except Exception:
+        return logical, logical
+
+
+# torchrun exports OMP_NUM_THREADS=1 to every rank; OpenBLAS reads it when numpy is imported, which
+# would time the CPU arms on ONE thread.  Rank 0 (the only rank that does host LAPACK / runs the CPU
+# arm) gets the physical cores, stated in the JSON line; the protocol of the reference's own
+# benchmarks states its BLAS thread count the same way (benchmarks/natvsext/run.jl:38-60).
+PHYS_CORES, LOGICAL_CPUS = _host_cores()
+if int(os.environ.get("RANK", "0")) == 0:
+    for _v in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ[_v] = str(PHYS_CORES)
+
 import numpy as np  # noqa: E402
+
+
+def blas_threads():
+    """BLAS threads actually in use (threadpoolctl), as reported in cpu_baseline.cores."""
+    try:
+        from threadpoolctl import threadpool_info
+
+        n = [int(i.get("num_threads", 0)) for i in threadpool_info() if i.get("user_api") == "blas"]
+        return max(n) if n else 1
+    except Exception:
+        return 1
+
+
+def set_blas_threads(n):
+    try:
+        from threadpoolctl import threadpool_limits
+
+        threadpool_limits(int(n), user_api="blas")
+    except Exception:
+        pass
 
 
 def parse_args():
@@ -85,6 +126,13 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(smax)), "reasons": sorted(reasons), "samples": len(sm)}
 
 
+# Solver options of the reference's own benchmark protocol (benchmarks/natvsext/run.jl:44-60), used by both
+# arms.  At the default tolerances (eps^0.5 = 1.5e-8) this model stalls a hair short of the feasibility
+# tolerance in the CPU restatement and on the GPU alike (SlowProgress -> NearOptimal after 23 iterations,
+# tests/golden/trajectories_big.json); under the benchmark tolerances both end Optimal after 15.
+BENCH_TOL = dict(tol_rel_opt=1e-7, tol_feas=1e-7, tol_abs_opt=1e-10, tol_infeas=1e-10)
+
+
 def build_model(N):
     import hypatia_b200  # noqa: F401
     from hypatia_b200 import instances
@@ -97,6 +145,8 @@ def workload_config(N, model, extra=None):
         "workload": f"cfg5 synthetic block multi-cone model: Schur dim N={N}, q={model.q}, "
                     f"{len(model.cones)} cones (Nonnegative / EpiNormEucl(8) / EpiPerSquare(8) / PosSemidefTri(side 16) quarters), Float64",
         "step": "one interior-point iteration (CombinedStepper, QRChol system solver, reference defaults)",
+        "solver_options": "tolerances of the reference's benchmark protocol (benchmarks/natvsext/run.jl:44-60): "
+                          "tol_rel_opt = tol_feas = 1e-7, tol_abs_opt = tol_infeas = 1e-10; everything else default",
         "N": N, "q": int(model.q), "cones": len(model.cones),
         "l2": "inputs larger than L2 (G*Q2 is %.2f GB, Schur matrix %.2f GB)" % (model.q * N * 8 / 1e9, N * N * 8 / 1e9),
     }
@@ -181,17 +231,29 @@ def ncu_traffic(N, K):
     return None
 
 
-def run_cpu_port(model, steps, warmup, preset_fact=None):
-    """CPU restatement of the reference path (oracle/, numpy/scipy -> OpenBLAS) on host cores."""
+def run_cpu_port(model, steps, warmup, preset_fact=None, budget_s=150.0):
+    """CPU restatement of the reference path (oracle/, numpy/scipy -> OpenBLAS) on host cores:
+    `warmup` untimed + up to `steps` timed interior-point iterations, cut short (never below one
+    timed iteration) once the iteration loop has used `budget_s` seconds."""
     from hypatia_b200.host.solver import Solver
     from oracle.cones import CpuConeSet
     from oracle.qrchol import QRCholDenseSystemSolver
 
+    set_blas_threads(PHYS_CORES)
     ss = QRCholDenseSystemSolver()
-    cpu = Solver(CpuConeSet, ss, iter_limit=warmup + steps)
+    cpu = Solver(CpuConeSet, ss, iter_limit=warmup + steps, **BENCH_TOL)
     cpu.preset_AG_fact = preset_fact
     timer = IterTimer()
-    cpu.iter_callback = timer
+    loop_t0 = [None]
+
+    def cb(solver):
+        timer(solver)
+        if loop_t0[0] is None:
+            loop_t0[0] = time.perf_counter() - timer.rows[-1]["wall_s"]
+        if time.perf_counter() - loop_t0[0] > budget_s and len(timer.rows) > warmup:
+            solver.iter_limit = solver.num_iters  # bounded sample: stop after this iteration
+
+    cpu.iter_callback = cb
     cpu.load(model)
     t0 = time.perf_counter()
     orig_init = cpu._initialize_point
@@ -212,6 +274,7 @@ def run_cpu_port(model, steps, warmup, preset_fact=None):
         "factor_ms": 1e3 * cpu.time_upfact / max(cpu.num_iters, 1),
         "total_s": time.perf_counter() - t0,
         "status": cpu.status,
+        "threads": blas_threads(),
     }
 
 
@@ -237,23 +300,25 @@ def main():
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
-    cores = os.cpu_count() or 1
+    cores = PHYS_CORES
 
     if args.impl == "reference":
         if rank != 0:
             return
         N = args.N
-        steps, warmup = min(args.steps, 3), min(args.warmup, 1)
+        steps, warmup = args.steps, args.warmup
         model = build_model(N)
-        res = run_cpu_port(model, steps, warmup)
+        res = run_cpu_port(model, steps, warmup, budget_s=float(os.environ.get("HYB_REF_BUDGET_S", 150)))
         line = {
             "impl": "reference", "metric": "ipm_iterations_per_second", "value": res["iters_per_s"], "unit": "iterations/s",
             "n_gpus": args.gpus, "steps": res["steps"], "warmup": warmup, "ms_per_step": res["ms_per_step"],
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": workload_config(N, model),
-            "cpu_baseline": {"value": res["iters_per_s"], "unit": "iterations/s", "cores": cores, "kind": "port",
+            "cpu_baseline": {"value": res["iters_per_s"], "unit": "iterations/s", "cores": res["threads"], "kind": "port",
+                             "physical_cores": PHYS_CORES, "logical_cpus": LOGICAL_CPUS, "blas_threads": res["threads"],
                              "sample": f"{res['steps']} interior-point iterations of the same model after {warmup} warm-up "
-                                       f"(CPU restatement of the reference, numpy/scipy OpenBLAS; Julia is not available on this box)",
+                                       f"(CPU restatement of the reference, numpy/scipy OpenBLAS with {res['threads']} threads, bounded "
+                                       f"to ~150 s of iterations; Julia is not available on this box)",
                              "schur_assemble_ms": res["assemble_ms"], "cholesky_ms": res["factor_ms"]},
             "e2e": {"value": res["iters_per_s"], "unit": "iterations/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         }
@@ -293,12 +358,18 @@ def main():
     model = build_model(N)
     steps, warmup = args.steps, max(args.warmup, 3)
     mode = os.environ.get("HYB_MULTI_MODE", "rootworker")  # or "replicated" (sharded.py)
-    gpu = make_gpu_solver(local_rank, iter_limit=warmup + steps, dist=dist, use_peer=not os.environ.get("HYB_NO_PEER"), mode=mode)
+    gpu = make_gpu_solver(local_rank, iter_limit=warmup + steps, **BENCH_TOL, dist=dist, use_peer=not os.environ.get("HYB_NO_PEER"), mode=mode)
     rootworker = world > 1 and mode == "rootworker"
     if rootworker and rank != 0:
-        # assembly worker: it has no iteration loop of its own; it serves the root until the root stops it
-        gpu.load(model)
-        gpu.solve()
+        # assembly worker: it has no iteration loop of its own; it serves the root until the root stops it,
+        # once per solve of the root (the root says after each solve whether another one follows)
+        while True:
+            gpu.load(model)
+            gpu.solve()
+            again = torch.zeros(1, dtype=torch.float64, device="cuda")
+            dist.broadcast(again, src=0)
+            if again.item() < 0.5:
+                break
         torch.cuda.synchronize()
         dist.barrier()
         for _ in range(2):  # the root's max-over-ranks reductions of wall and device time
@@ -313,27 +384,21 @@ def main():
 
     timer = IterTimer(ctx, sync)
     sampler = ClockSampler(local_rank)
-    state = {"t_start": None}
+    state = {"sampling": False}
 
     def callback(solver):
+        if dist is not None and not rootworker:
+            dist.barrier()  # replicated form: every rank brackets its own iteration (root/worker: the
+            # workers are inside every iteration's barrier already, only the root has an iteration loop)
         timer(solver)
-        # (root/worker form: the workers are inside every iteration's barrier already, and only the
-        # root has an iteration loop to bracket)
-        if len(timer.rows) == warmup + steps:
-            if dist is not None and not rootworker:
-                dist.barrier()
-            sync()
-            state["t_end"] = time.perf_counter()
-        if len(timer.rows) == warmup:  # timed region starts after the warm-up iterations
-            if dist is not None and not rootworker:
-                dist.barrier()
-            sync()
+        if len(timer.rows) >= warmup and not state["sampling"]:  # timed region starts after the warm-up iterations
+            state["sampling"] = True
             sampler.start()
-            state["t_start"] = time.perf_counter()
             timer._t = time.perf_counter()
+        if len(timer.rows) >= warmup + steps:
+            solver.iter_limit = solver.num_iters  # exactly `steps` timed iterations
 
     gpu.iter_callback = callback
-    gpu.load(model)
     orig_init = gpu._initialize_point
 
     def init_and_start():
@@ -345,17 +410,34 @@ def main():
     gpu._initialize_point = init_and_start
     if rootworker:
         timer.shard_ctx = lambda: gpu.syssolver.shard.ctx
-    gpu.solve()
-    sync()
+    # The model converges in fewer iterations than warm-up + steps may ask for: the timed iterations
+    # then continue into a fresh solve of the same model (its set-up is outside the timed iterations,
+    # like the first solve's), until exactly `steps` iterations have been timed.
+    solves = []
+    setup_s = {}
+    while True:
+        if threadpool_limits is not None:
+            threadpool_limits(cores if rank == 0 else 1)
+        gpu.iter_limit = max(1, warmup + steps - len(timer.rows))
+        gpu.load(model)
+        gpu.solve()
+        sync()
+        solves.append({"status": gpu.status, "iterations": int(gpu.num_iters)})
+        if not setup_s:
+            setup_s = {name: float(getattr(gpu, "time_" + name, 0.0)) for name in ("rescale", "inity", "initx", "loadsys")}
+        more = len(timer.rows) < warmup + steps and len(solves) < 8
+        if rootworker:
+            dist.broadcast(torch.tensor([1.0 if more else 0.0], dtype=torch.float64, device="cuda"), src=0)
+        if not more:
+            break
     if dist is not None:
         dist.barrier()
-    t_end = state.get("t_end") or time.perf_counter()
     clocks = sampler.stop()
-    rows = timer.rows[warmup:]
+    rows = timer.rows[warmup:warmup + steps]
     if not rows:
-        raise SystemExit(f"bench.py: the solve ended after {len(timer.rows)} iterations, before the timed region")
+        raise SystemExit(f"bench.py: the solves ended after {len(timer.rows)} iterations, before the timed region")
     k = len(rows)
-    wall = t_end - state["t_start"]
+    wall = sum(r["wall_s"] for r in rows)  # every iteration is bracketed by a device synchronize
     if dist is not None:
         tw = torch.tensor([wall], dtype=torch.float64, device="cuda")
         dist.all_reduce(tw, op=dist.ReduceOp.MAX)
@@ -401,7 +483,7 @@ def main():
         "config": workload_config(N, model, {
             "value_definition": "iterations / device time: CUDA-event time of every kernel region of the C-ABI calls of the timed iterations (inputs resident in HBM)",
             "e2e_definition": "iterations / wall time of the same iterations through the C-ABI with host vectors (all H2D/D2H copies and the host-side stepper included)",
-            "status_after_limit": gpu.status, "iterations_run": gpu.num_iters,
+            "solves": solves,
             "parallelism": ("cones partitioned by block over %d ranks; partial Schur matrices reach rank 0 by %s; Cholesky + solves on rank 0"
                             % (world, "peer stores from the syrk epilogue over NVLink + fixed-order sum" if (rootworker or getattr(gpu.syssolver.backend, "peer", False)) else "NCCL reduce")) if world > 1 else "single GPU",
             "multi_gpu_form": ("root/worker: rank 0 runs the algorithm, 1 point broadcast + 1 barrier per iteration" if rootworker else "replicated host driver, sharded oracles") if world > 1 else None,
@@ -412,7 +494,7 @@ def main():
         "gpu_launches": launches,
         # untimed set-up of the solve (Solvers.jl:395-429), seconds: rescale, primal-equality QR + reduce,
         # dual-equality pivoted QR (hyb_geqp3 on the GPU) + initial point, upload of G*Q2
-        "setup_s": {name: float(getattr(gpu, "time_" + name, 0.0)) for name in ("rescale", "inity", "initx", "loadsys")},
+        "setup_s": setup_s,
         "phase_ms": {name: float(np.mean([r["ph_" + name] for r in rows])) for name in ("upsys", "uprhs", "getdir", "search")},
         "schur_assemble_ms": t_w + t_syrk,
         "schur_reduce_ms": reduce_ms,
@@ -429,12 +511,14 @@ def main():
         },
     }
     if not args.no_cpu_baseline and world == 1:
-        steps_cpu = 2
-        res = run_cpu_port(build_model(N), steps_cpu, 1, preset_fact=getattr(gpu, "AG_fact", None))
+        steps_cpu = 3
+        res = run_cpu_port(build_model(N), steps_cpu, 1, preset_fact=getattr(gpu, "AG_fact", None), budget_s=30.0)
         line["cpu_baseline"] = {
-            "value": res["iters_per_s"], "unit": "iterations/s", "cores": cores, "kind": "port",
+            "value": res["iters_per_s"], "unit": "iterations/s", "cores": res["threads"], "kind": "port",
+            "physical_cores": PHYS_CORES, "logical_cpus": LOGICAL_CPUS, "blas_threads": res["threads"],
             "sample": f"{res['steps']} interior-point iterations of the same model after 1 warm-up iteration "
-                      f"(CPU restatement of the reference, numpy/scipy OpenBLAS, {cores} host cores)",
+                      f"(CPU restatement of the reference, numpy/scipy OpenBLAS, {res['threads']} BLAS threads on "
+                      f"{PHYS_CORES} physical cores)",
             "schur_assemble_ms": res["assemble_ms"], "cholesky_ms": res["factor_ms"],
         }
     emit(line)

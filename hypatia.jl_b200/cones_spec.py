@@ -164,6 +164,28 @@ class EpiNormEucl(ConeSpec):
 
 
 @dataclass
+class EpiNormInf(ConeSpec):
+    """src/Cones/epinorminf.jl:16-98 (real case): epigraph of the infinity norm; with ``use_dual`` the
+    dual barrier is used, i.e. the cone is the epigraph of the 1-norm."""
+
+    use_dual: bool = False
+
+    def __post_init__(self):
+        assert self.dim >= 2
+        self.type_code = EPINORMINF
+        self.use_dual_barrier = bool(self.use_dual)
+
+    @property
+    def nu(self):
+        return float(self.dim)  # 1 + d with d = dim - 1 (epinorminf.jl:90)
+
+    def initial_point(self):
+        arr = np.zeros(self.dim)
+        arr[0] = math.sqrt(self.nu)
+        return arr
+
+
+@dataclass
 class EpiPerSquare(ConeSpec):
     """src/Cones/epipersquare.jl:17-70"""
 

@@ -2,6 +2,7 @@
 // cone batch, Schur assembly + factorization, solves.
 #include <cstdarg>
 #include <cmath>
+#include <cstdlib>
 
 #include "../../include/hypatia_b200.h"
 #include "common.cuh"
@@ -91,6 +92,8 @@ static void free_model(hyb_ctx* c) {
         hybi_cones_free(c->cones);
     }
     hyb_dirs_free(c);
+    for (auto& r : c->stage) cudaFree(r.buf);
+    c->stage.clear();
     if (c->peer_ipc_base) cudaIpcCloseMemHandle(c->peer_ipc_base);
     if (c->peer_slots) cudaFree(c->peer_slots);
     c->peer_ipc_base = nullptr;
@@ -158,7 +161,8 @@ void hyb_ctx_destroy(hyb_ctx* c) {
 const char* hyb_last_error(hyb_ctx*) { return hyb_get_error(); }
 
 int64_t hyb_launch_count(void) {
-    return hyb_gemm_launch_count() + hyb_potrf_launch_count() + hybi_cones_launch_count() + g_misc_launches;
+    return hyb_gemm_launch_count() + hyb_potrf_launch_count() + hyb_sytrf_launch_count() + hybi_cones_launch_count() +
+           g_misc_launches;
 }
 
 int hyb_model_load(hyb_ctx* c, int64_t q, int64_t N, const double* GQ2, int64_t ncones, const hyb_cone_desc* descs) {
@@ -352,6 +356,41 @@ int hyb_schur_assemble(hyb_ctx* c, double* t_assemble_ms) {
     return schur_assemble_into(c, c->S, t_assemble_ms);
 }
 
+// Operand of one run of rows in the assembly GEMMs.  TMA needs 16-byte aligned operands, i.e. an even
+// first row: a run that starts on an odd row is contracted from an aligned staging copy -- G*Q2's rows are
+// constant over the solve, so that copy is made once and kept; only the product rows are copied per
+// iteration (device to device, no allocation and no synchronisation after the first iteration).
+static int staged_rows(hyb_ctx* c, const double* src, int64_t off, int64_t rows, bool constant, const double** out,
+                       int64_t* ld) {
+    const int64_t N = c->N;
+    if (!(off & 1)) {
+        *out = src + off;
+        *ld = c->ldq;
+        return 0;
+    }
+    for (auto& r : c->stage)
+        if (r.off == off && r.rows == rows && r.constant == constant) {
+            if (!constant)
+                HYB_CUDA(cudaMemcpy2DAsync(r.buf, sizeof(double) * r.ld, src + off, sizeof(double) * c->ldq, sizeof(double) * rows, N,
+                                           cudaMemcpyDeviceToDevice, c->st));
+            *out = r.buf;
+            *ld = r.ld;
+            return 0;
+        }
+    HybStageRun r;
+    r.off = off;
+    r.rows = rows;
+    r.constant = constant;
+    r.ld = hyb_round_up(rows, 16);
+    HYB_CUDA(cudaMalloc(&r.buf, sizeof(double) * r.ld * N));
+    HYB_CUDA(cudaMemcpy2DAsync(r.buf, sizeof(double) * r.ld, src + off, sizeof(double) * c->ldq, sizeof(double) * rows, N,
+                               cudaMemcpyDeviceToDevice, c->st));
+    c->stage.push_back(r);
+    *out = r.buf;
+    *ld = r.ld;
+    return 0;
+}
+
 static int schur_assemble_into(hyb_ctx* c, double* Sdst, double* t_assemble_ms) {
     HYB_CUDA(cudaSetDevice(c->device));
     if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(hyb_ensure_updated(c, c->loaded_scal));
@@ -360,69 +399,56 @@ static int schur_assemble_into(hyb_ctx* c, double* Sdst, double* t_assemble_ms) 
     if (N == 0) return 0;
     HYB_CUDA(cudaEventRecord(c->ev0, c->st));
     if (q > 0) {
-        // use_sqrt_hess_oracles per cone (qrchol.jl:222-225, Cones.jl:193-199): closed-form cones
-        // always; a generic-Hessian cone only if its Hessian Cholesky exists
+        // use_sqrt_hess_oracles per cone (qrchol.jl:222-225): the closed-form cones with sqrt oracles always;
+        // a generic-Hessian cone (WSOS) only if its Hessian Cholesky exists (Cones.jl:193-199); EpiNormInf
+        // never (epinorminf.jl:73)
         HybCones& cs = c->cones;
-        std::vector<char> sqrt_mask(cs.blocks.size(), 1);
-        bool all_sqrt = true;
-        for (size_t bi = 0; bi < cs.blocks.size(); ++bi) {
-            if (cs.blocks[bi].type == HYB_WSOSINTERPNONNEGATIVE || cs.blocks[bi].type == HYB_WSOSINTERPPOSSEMIDEFTRI) {
+        const size_t nb = cs.blocks.size();
+        std::vector<char> sqrt_mask(nb, 1);
+        for (size_t bi = 0; bi < nb; ++bi) {
+            const int ty = cs.blocks[bi].type;
+            if (ty == HYB_WSOSINTERPNONNEGATIVE || ty == HYB_WSOSINTERPPOSSEMIDEFTRI) {
                 int ok = 0;
-                if (cs.blocks[bi].type == HYB_WSOSINTERPNONNEGATIVE)
+                if (ty == HYB_WSOSINTERPNONNEGATIVE)
                     HYB_CHECK(hybd_wsos_sqrt_ok(c->st, (HybDenseWsos*)cs.blocks[bi].dense, &ok));
                 else
                     HYB_CHECK(hybd_wsospsd_sqrt_ok(c->st, (HybDenseWsosPsd*)cs.blocks[bi].dense, &ok));
                 sqrt_mask[bi] = (char)ok;
-                all_sqrt = all_sqrt && ok;
+            } else if (ty == HYB_EPINORMINF) {
+                sqrt_mask[bi] = 0;
             }
         }
-        // HGQ2 = W * GQ2 with W'W = H (primal barrier) or H^-1 (dual barrier): qrchol.jl:228-241
-        if (!all_sqrt) {
-            cs.block_mask = sqrt_mask;
-            for (size_t bi = 0; bi < cs.blocks.size(); ++bi)
-                if (!sqrt_mask[bi]) {
-                    const HybConeBlock& b = cs.blocks[bi];
-                    HYB_CUDA(cudaMemset2DAsync(c->HGQ2 + b.offset, sizeof(double) * c->ldq, 0,
-                                               sizeof(double) * b.count * b.dim, N, c->st));
-                }
-        }
-        int rcp = hybi_cones_prod(c->st, cs, 5, c->GQ2, c->ldq, c->HGQ2, c->ldq, N);
-        cs.block_mask.clear();
+        // one pass of product kernels: rows of sqrt cones get W_k GQ2_k with W'W = H~ (qrchol.jl:228-241),
+        // rows of the other cones H~_k GQ2_k (block_hess_prod!, qrchol.jl:248-252); H~ = H or H^-1 by barrier side
+        cs.block_sqrt = sqrt_mask;
+        int rcp = hybi_cones_prod(c->st, cs, 7, c->GQ2, c->ldq, c->HGQ2, c->ldq, N);
+        cs.block_sqrt.clear();
         HYB_CHECK(rcp);
         HYB_CUDA(cudaEventRecord(c->ev3, c->st));
-        // lhs = HGQ2' HGQ2, upper (outer_prod!, qrchol.jl:242)
-        HYB_CHECK(hyb_gemm_tn(c->st, N, N, q, 1.0, c->HGQ2, c->ldq, c->HGQ2, c->ldq, 0.0, Sdst, c->ldS, HYB_GEMM_UPPER));
-        // remaining cones: lhs += GQ2_k' (H~_k GQ2_k)  (block_hess_prod! + mul!, qrchol.jl:248-254)
-        for (size_t bi = 0; bi < cs.blocks.size() && !all_sqrt; ++bi) {
-            if (sqrt_mask[bi]) continue;
-            const HybConeBlock& b = cs.blocks[bi];
-            const int64_t rows = b.count * b.dim;
-            std::vector<char> one(cs.blocks.size(), 0);
-            one[bi] = 1;
-            cs.block_mask = one;
-            rcp = hybi_cones_prod(c->st, cs, 4, c->GQ2, c->ldq, c->HGQ2, c->ldq, N);
-            cs.block_mask.clear();
-            HYB_CHECK(rcp);
-            const double *Ak = c->GQ2 + b.offset, *Bk = c->HGQ2 + b.offset;
-            int64_t ldk = c->ldq;
-            double* bounce = nullptr;
-            if (b.offset & 1) {  // TMA needs 16-byte aligned operands: stage the cone's rows
-                const int64_t ldb = hyb_round_up(rows, 16);
-                HYB_CUDA(cudaMalloc(&bounce, sizeof(double) * ldb * N * 2));
-                HYB_CUDA(cudaMemcpy2DAsync(bounce, sizeof(double) * ldb, Ak, sizeof(double) * c->ldq, sizeof(double) * rows, N,
-                                           cudaMemcpyDeviceToDevice, c->st));
-                HYB_CUDA(cudaMemcpy2DAsync(bounce + ldb * N, sizeof(double) * ldb, Bk, sizeof(double) * c->ldq,
-                                           sizeof(double) * rows, N, cudaMemcpyDeviceToDevice, c->st));
-                Ak = bounce;
-                Bk = bounce + ldb * N;
-                ldk = ldb;
+        // lhs = sum over runs of consecutive cones of the same kind: (W GQ2)'(W GQ2) (outer_prod!, qrchol.jl:242)
+        // or GQ2' (H~ GQ2) (mul!, qrchol.jl:253); the reference packs the sqrt rows first, which only reorders
+        // the sum
+        bool first = true;
+        for (size_t b0 = 0; b0 < nb;) {
+            size_t b1 = b0;
+            int64_t rows = 0;
+            while (b1 < nb && sqrt_mask[b1] == sqrt_mask[b0]) {
+                rows += cs.blocks[b1].count * cs.blocks[b1].dim;
+                ++b1;
             }
-            int rcg = hyb_gemm_tn(c->st, N, N, rows, 1.0, Ak, ldk, Bk, ldk, 1.0, Sdst, c->ldS, HYB_GEMM_UPPER);
-            if (bounce) {
-                cudaStreamSynchronize(c->st);
-                cudaFree(bounce);
+            const int64_t off = cs.blocks[b0].offset;
+            const double *Bk = nullptr, *Ak = nullptr;
+            int64_t ldb = 0, lda = 0;
+            HYB_CHECK(staged_rows(c, c->HGQ2, off, rows, false, &Bk, &ldb));
+            if (sqrt_mask[b0]) {
+                Ak = Bk;
+                lda = ldb;
+            } else {
+                HYB_CHECK(staged_rows(c, c->GQ2, off, rows, true, &Ak, &lda));
             }
-            HYB_CHECK(rcg);
+            HYB_CHECK(hyb_gemm_tn(c->st, N, N, rows, 1.0, Ak, lda, Bk, ldb, first ? 0.0 : 1.0, Sdst, c->ldS, HYB_GEMM_UPPER));
+            first = false;
+            b0 = b1;
         }
     } else {
         HYB_CUDA(cudaEventRecord(c->ev3, c->st));
@@ -457,13 +483,23 @@ int hyb_schur_factor(hyb_ctx* c, double* t_fact_ms, int* fact_kind) {
     HYB_CHECK(hyb_copy_upper(c->st, c->S, c->ldS, c->chol.F, c->chol.ld, N));
     ++g_misc_launches;
     HYB_CHECK(hyb_potrf(c->st, c->chol, &info));
-    if (info != 0) {
+    static const bool force_bk = getenv("HYB_FORCE_BK") != nullptr;  // test hook: take the fallback on a good matrix
+    if (info != 0 || force_bk) {
+        // Cholesky failed: Bunch-Kaufman (rook) of the SAME matrix first (symm_fact!, dense.jl:199-203,237-239)
         HYB_CHECK(hyb_copy_upper(c->st, c->S, c->ldS, c->chol.F, c->chol.ld, N));
-        increase_diag_kernel<<<(unsigned)((N + 255) / 256), 256, 0, c->st>>>(N, c->chol.F, c->chol.ld);
-        g_misc_launches += 2;
-        HYB_CUDA(cudaGetLastError());
-        HYB_CHECK(hyb_potrf(c->st, c->chol, &info));
-        kind = (info == 0) ? 2 : -1;
+        ++g_misc_launches;
+        HYB_CHECK(hyb_sytrf_rook(c->st, c->chol, &info));
+        kind = 1;
+        if (info != 0) {
+            // that failed too (an exactly singular pivot block): shift the diagonal and retry
+            // (increase_diag! + symm_fact!, dense.jl:240-246)
+            HYB_CHECK(hyb_copy_upper(c->st, c->S, c->ldS, c->chol.F, c->chol.ld, N));
+            increase_diag_kernel<<<(unsigned)((N + 255) / 256), 256, 0, c->st>>>(N, c->chol.F, c->chol.ld);
+            g_misc_launches += 2;
+            HYB_CUDA(cudaGetLastError());
+            HYB_CHECK(hyb_sytrf_rook(c->st, c->chol, &info));
+            kind = (info == 0) ? 2 : -1;
+        }
     }
     HYB_CUDA(cudaEventRecord(c->ev2, c->st));
     HYB_CUDA(cudaEventSynchronize(c->ev2));
@@ -792,6 +828,57 @@ int hyb_posdef_solve(hyb_ctx* c, int64_t N, double* A, int64_t lda, double* B, i
     }
     hyb_chol_free(ch);
     return rc;
+}
+
+int hyb_symm_solve(hyb_ctx* c, int64_t N, double* A, int64_t lda, int* ipiv, double* B, int64_t ldb, int64_t nrhs,
+                   int* info) {
+    if (!c) return -1;
+    if (nrhs < 0 || nrhs > HYB_MAX_RHS) {
+        hyb_set_error("hyb_symm_solve: %lld right-hand sides (max %d)", (long long)nrhs, HYB_MAX_RHS);
+        return -3;
+    }
+    HYB_CUDA(cudaSetDevice(c->device));
+    HybChol ch;
+    HYB_CHECK(hyb_chol_alloc(ch, N));
+    int rc = 0, inf = 0;
+    cudaError_t e = cudaSuccess;
+    if (N > 0)
+        e = cudaMemcpy2D(ch.F, sizeof(double) * ch.ld, A, sizeof(double) * lda, sizeof(double) * N, N, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) rc = hyb_sytrf_rook(c->st, ch, &inf);
+    if (e == cudaSuccess && rc == 0 && N > 0) {
+        if (info) *info = inf;
+        e = cudaMemcpy2D(A, sizeof(double) * lda, ch.F, sizeof(double) * ch.ld, sizeof(double) * N, N, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess && ipiv) e = cudaMemcpy(ipiv, ch.ipiv, sizeof(int) * N, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess && inf == 0 && nrhs > 0) {
+            double* dB = nullptr;
+            int64_t lB = 0;
+            rc = upload_padded(B, N, nrhs, ldb, &dB, &lB);
+            if (rc == 0) rc = hyb_sytrs_rook(c->st, ch, dB, lB, (int)nrhs);
+            if (rc == 0) {
+                e = cudaStreamSynchronize(c->st);
+                if (e == cudaSuccess)
+                    e = cudaMemcpy2D(B, sizeof(double) * ldb, dB, sizeof(double) * lB, sizeof(double) * N, nrhs,
+                                     cudaMemcpyDeviceToHost);
+            }
+            cudaFree(dB);
+        }
+    }
+    if (e != cudaSuccess) {
+        hyb_set_error("hyb_symm_solve: %s", cudaGetErrorString(e));
+        rc = -1;
+    }
+    hyb_chol_free(ch);
+    return rc;
+}
+
+int hyb_schur_set(hyb_ctx* c, const double* lhs) {
+    if (!c || !c->loaded) return -1;
+    HYB_CUDA(cudaSetDevice(c->device));
+    if (c->N == 0) return 0;
+    HYB_CUDA(cudaMemcpy2D(c->S, sizeof(double) * c->ldS, lhs, sizeof(double) * c->N, sizeof(double) * c->N, c->N,
+                          cudaMemcpyHostToDevice));
+    c->fact_ok = false;
+    return 0;
 }
 
 int hyb_stats(hyb_ctx* c, int reset, double* device_ms, int64_t* h2d_bytes, int64_t* d2h_bytes) {

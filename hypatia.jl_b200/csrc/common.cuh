@@ -32,6 +32,29 @@ const char* hyb_get_error();
 
 static inline int64_t hyb_round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
 
+// Per-device one-time set-up.  cudaFuncSetAttribute and the SM count are properties of the CURRENT
+// device, so a process that opens contexts on several GPUs must repeat them on each one:
+//   static HybDevOnce once;  if (once.first()) { cudaFuncSetAttribute(...); }
+#define HYB_MAX_DEVICES 64
+struct HybDevOnce {
+    bool done[HYB_MAX_DEVICES] = {};
+    bool first() {
+        int d = 0;
+        if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= HYB_MAX_DEVICES) return true;
+        if (done[d]) return false;
+        done[d] = true;
+        return true;
+    }
+};
+// multiprocessor count of the current device (cached per device)
+static inline int hyb_num_sms() {
+    static int sms[HYB_MAX_DEVICES] = {};
+    int d = 0;
+    if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= HYB_MAX_DEVICES) return 148;
+    if (sms[d] == 0) cudaDeviceGetAttribute(&sms[d], cudaDevAttrMultiProcessorCount, d);
+    return sms[d] > 0 ? sms[d] : 148;
+}
+
 // ---- dense engine (gemm_dmma.cu) ------------------------------------------------
 // C(MxN) = alpha * A' * B + beta * C.   A: K x M, B: K x N, all column-major with
 // even leading dimensions and 16-byte aligned bases (TMA requirement).
@@ -57,6 +80,12 @@ struct HybChol {
     double* work = nullptr;   // N doubles
     cudaStream_t panel_stream = nullptr;  // look-ahead panels (high priority)
     cudaEvent_t ev_head = nullptr, ev_panel = nullptr;
+    // symmetric-indefinite fallback (sytrf.cu): kind 0 = F holds the Cholesky factor, 1 = F holds the
+    // rook-pivoted Bunch-Kaufman factorization U D U' with pivot vector ipiv (LAPACK dsytrf_rook layout)
+    int kind = 0;
+    int* ipiv = nullptr;       // device, N
+    double* bk_ws = nullptr;   // device, 4 N
+    void* bk_state = nullptr;  // device step state
 };
 int hyb_chol_alloc(HybChol& ch, int64_t N);
 void hyb_chol_free(HybChol& ch);
@@ -72,6 +101,12 @@ int hyb_transpose(cudaStream_t st, const double* src, int64_t lds_, int64_t rows
                   int64_t ldd, int upper_only);
 // x <- (U'U)^-1 x for one device vector of length N
 int hyb_potrs(cudaStream_t st, HybChol& ch, double* x);
+// symmetric-indefinite fallback of posdef_fact_copy! (dense.jl:199-203,228-249): in-place rook-pivoted
+// Bunch-Kaufman of ch.F (LAPACK dsytrf_rook semantics) and the matching solves (dsytrs_rook);
+// hyb_potrs / hyb_potrs_multi dispatch on ch.kind, so callers of the solves need not care
+int hyb_sytrf_rook(cudaStream_t st, HybChol& ch, int* info_out);
+int hyb_sytrs_rook(cudaStream_t st, HybChol& ch, double* X, int64_t ldx, int R);
+int64_t hyb_sytrf_launch_count();
 
 // ---- gemv (gemv.cu) -----------------------------------------------------------------
 // y = G x (q) ; scratch must hold HYB_GEMV_SPLITS * q doubles

@@ -363,6 +363,186 @@ __global__ void soc_dder3_kernel(int64_t count, int d, int64_t offset, int64_t c
     }
 }
 
+// ------------------------------------------------------------------ EpiNormInf (real)
+// src/Cones/epinorminf.jl:100-392.  point = (u, w), d = dim - 1, nu = 1 + d.  Per coordinate
+//   mu_i = w_i / u, zeta_i = (u - mu_i w_i) / 2, cu = (d - 1) / u
+// are recomputed from the point (two flops) instead of stored; the one scalar worth keeping per cone is
+//   Zu = -cu + sum_i 1 / (u - zeta_i)                 (update_inv_hess_aux, :257-273)
+// in aux[cone].  No sqrt oracles (use_sqrt_hess_oracles = false, :73): the cone takes the gemm branch of
+// the Schur assembly (qrchol.jl:248-254).  Same thread mapping as the second-order cones above.
+template <bool WARP>
+__device__ __forceinline__ double red_max(double v) {
+    if (WARP) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    }
+    return v;
+}
+
+// H^-1 a . b for the loaded point (inv_hess_prod!, :314-335): c1 = u (a_0 + wumzi . a_w) / Zu,
+// (H^-1 a)_0 = c1, (H^-1 a)_i = c1 wumzi_i + zeta_i zti_i a_i, wumzi = w / (u - zeta), zti = u - wumzi w
+template <bool WARP, class FA, class FB>
+__device__ __forceinline__ double ninf_hinv_dot(const double* p, int d, int i0, int stride, double Zu, FA a, FB b) {
+    const double u = p[0];
+    double s = 0.0;
+    for (int i = 1 + i0; i < d; i += stride) {
+        const double w = p[i], zeta = 0.5 * (u - (w / u) * w);
+        s += (w / (u - zeta)) * a(i);
+    }
+    s = red_sum<WARP>(s);
+    const double c1 = u * (a(0) + s) / Zu;
+    double acc = (i0 == 0) ? c1 * b(0) : 0.0;
+    for (int i = 1 + i0; i < d; i += stride) {
+        const double w = p[i], zeta = 0.5 * (u - (w / u) * w);
+        const double wumzi = w / (u - zeta), zti = u - wumzi * w;
+        acc += (c1 * wumzi + zeta * a(i) * zti) * b(i);
+    }
+    return red_sum<WARP>(acc);
+}
+
+template <bool WARP>
+__global__ void ninf_update_kernel(int64_t count, int d, int64_t offset, int64_t cone0, const double* __restrict__ primal,
+                                   const double* __restrict__ dual_in, double scal, double irtmu,
+                                   double* __restrict__ point, double* __restrict__ dual, double* __restrict__ grad,
+                                   double* __restrict__ aux, int* __restrict__ flag, double* __restrict__ prox) {
+    const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t c = WARP ? (gt >> 5) : gt;
+    const int i0 = WARP ? (int)(gt & 31) : 0;
+    const int stride = WARP ? 32 : 1;
+    if (c >= count) return;
+    const int64_t base = offset + c * d;
+    double* p = point + base;
+    double* z = dual + base;
+    double* g = grad + base;
+    for (int i = i0; i < d; i += stride) {
+        p[i] = scal * primal[base + i];
+        z[i] = dual_in[base + i];
+    }
+    if (WARP) __syncwarp();
+    int f = 0;
+    const double u = p[0];
+    {  // update_feas (:100-113): u > eps and u - max|w| > eps
+        double m = 0.0;
+        for (int i = 1 + i0; i < d; i += stride) m = fmax(m, fabs(p[i]));
+        m = red_max<WARP>(m);
+        if (u > HYB_EPS && (u - m) > HYB_EPS) f |= HYB_ST_FEAS;
+    }
+    {  // is_dual_feas (:115-128): u > eps and u - sum|w| > eps
+        double s1 = 0.0;
+        for (int i = 1 + i0; i < d; i += stride) s1 += fabs(z[i]);
+        s1 = red_sum<WARP>(s1);
+        if (z[0] > HYB_EPS && (z[0] - s1) > HYB_EPS) f |= HYB_ST_DUAL_FEAS;
+    }
+    double proxsqr = 0.0, Zu = 0.0;
+    if (f & HYB_ST_FEAS) {
+        const int dw = d - 1;
+        const double nu = (double)d, cu = (double)(dw - 1) / u;
+        // update_grad (:136-162)
+        double sz = 0.0, su = 0.0;
+        for (int i = 1 + i0; i < d; i += stride) {
+            const double w = p[i], mu = w / u, zeta = 0.5 * (u - mu * w);
+            sz += 1.0 / zeta;
+            su += 1.0 / (u - zeta);
+            g[i] = mu / zeta;
+        }
+        sz = red_sum<WARP>(sz);
+        su = red_sum<WARP>(su);
+        Zu = -cu + su;
+        if (i0 == 0) g[0] = cu - sz;
+        if (WARP) __syncwarp();
+        // check_numerics (Cones.jl:267-284)
+        double gp = 0.0;
+        for (int i = i0; i < d; i += stride) gp += g[i] * p[i];
+        gp = red_sum<WARP>(gp);
+        bool ok = !(fabs(1.0 + gp / nu) > 1.220703125e-4 * d);
+        auto gv = [&](int i) { return g[i]; };
+        const double hgg = ninf_hinv_dot<WARP>(p, d, i0, stride, Zu, gv, gv);
+        if (fabs(1.0 - hgg / nu) > 1.104854345603981e-1 * d) ok = false;
+        if (ok) f |= HYB_ST_NUMERICS;
+        // get_proxsqr (Cones.jl:288-304): psi = irtmu z + g ; psi' H^-1 psi
+        auto psi = [&](int i) { return irtmu * z[i] + g[i]; };
+        const double acc = ninf_hinv_dot<WARP>(p, d, i0, stride, Zu, psi, psi);
+        proxsqr = (acc < -1.4901161193847656e-08 * d) ? INFINITY : fabs(acc);
+    }
+    if (i0 == 0) {
+        aux[cone0 + c] = Zu;
+        flag[base] = f;
+        prox[base] = proxsqr;
+    }
+}
+
+// hess_prod! (:205-229) / inv_hess_prod! (:314-335) on a q_block x m array; item = (cone, column)
+template <bool WARP>
+__global__ void ninf_prod_kernel(int64_t count, int d, int64_t offset, int64_t cone0, int64_t m, int op,
+                                 const double* __restrict__ point, const double* __restrict__ aux,
+                                 const double* __restrict__ arr, int64_t lda, double* __restrict__ prod, int64_t ldp) {
+    const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t item = WARP ? (gt >> 5) : gt;
+    const int i0 = WARP ? (int)(gt & 31) : 0;
+    const int stride = WARP ? 32 : 1;
+    if (item >= count * m) return;
+    const int64_t c = item % count, j = item / count;
+    const double* p = point + offset + c * d;
+    const double* a = arr + offset + c * d + j * lda;
+    double* r = prod + offset + c * d + j * ldp;
+    const double u = p[0], a0 = a[0];
+    if (op == HYB_OP_HESS) {
+        const double pui = a0 / u, cu = (double)(d - 2) / u;
+        double s = 0.0;
+        for (int i = 1 + i0; i < d; i += stride) {
+            const double w = p[i], mu = w / u, zeta = 0.5 * (u - mu * w);
+            const double ai = a[i];
+            const double s1 = (a0 - mu * ai) / zeta;
+            s += (s1 - pui) / zeta;
+            r[i] = (ai / u - s1 * mu) / zeta;
+        }
+        s = red_sum<WARP>(s);
+        if (i0 == 0) r[0] = s - cu * pui;
+    } else {
+        const double Zu = aux[cone0 + c];
+        double s = 0.0;
+        for (int i = 1 + i0; i < d; i += stride) {
+            const double w = p[i], zeta = 0.5 * (u - (w / u) * w);
+            s += (w / (u - zeta)) * a[i];
+        }
+        s = red_sum<WARP>(s);
+        const double c1 = u * (a0 + s) / Zu;
+        if (WARP) __syncwarp();
+        for (int i = 1 + i0; i < d; i += stride) {
+            const double w = p[i], zeta = 0.5 * (u - (w / u) * w);
+            const double wumzi = w / (u - zeta), zti = u - wumzi * w;
+            r[i] = c1 * wumzi + zeta * a[i] * zti;
+        }
+        if (i0 == 0) r[0] = c1;
+    }
+}
+
+// dder3 (:366-392)
+template <bool WARP>
+__global__ void ninf_dder3_kernel(int64_t count, int d, int64_t offset, const double* __restrict__ point,
+                                  const double* __restrict__ dir, double* __restrict__ out) {
+    const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t c = WARP ? (gt >> 5) : gt;
+    const int i0 = WARP ? (int)(gt & 31) : 0;
+    const int stride = WARP ? 32 : 1;
+    if (c >= count) return;
+    const double* p = point + offset + c * d;
+    const double* dr = dir + offset + c * d;
+    double* o = out + offset + c * d;
+    const double u = p[0], pp = dr[0], pui = pp / u, cu = (double)(d - 2) / u;
+    double c1 = 0.0;
+    for (int i = 1 + i0; i < d; i += stride) {
+        const double w = p[i], mu = w / u, zeta = 0.5 * (u - mu * w);
+        const double ri = dr[i], rui = ri / u;
+        const double s1 = (pp - mu * ri) / zeta;
+        const double s2 = 0.5 * (pp * pui - rui * ri) / zeta - s1 * s1;
+        c1 += (s1 * pui + s2) / zeta;
+        o[i] = (s1 * rui + s2 * mu) / zeta;
+    }
+    c1 = red_sum<WARP>(c1);
+    if (i0 == 0) o[0] = -c1 - cu * pui * pui;
+}
+
 // ------------------------------------------------------------------ PosSemidefTri, side <= 32
 // Per-cone matrices in global memory: [X | U | Uinv | Xinv], each side*side column-major.
 constexpr int PSD_MAX_SIDE = 32;
@@ -729,7 +909,8 @@ int hybi_cones_alloc(HybCones& cs) {
             HybDenseWsosPsd* d = nullptr;
             HYB_CHECK(hybd_wsospsd_create(&d, b.side, b.U, b.nPs, b.Ps, b.Ls));
             b.dense = d;
-        } else if (b.type != HYB_NONNEGATIVE && b.type != HYB_EPINORMEUCL && b.type != HYB_EPIPERSQUARE) {
+        } else if (b.type != HYB_NONNEGATIVE && b.type != HYB_EPINORMEUCL && b.type != HYB_EPIPERSQUARE &&
+                   b.type != HYB_EPINORMINF) {
             hyb_set_error("cone type %d is not supported by the GPU path yet", b.type);
             return -2;
         }
@@ -738,15 +919,14 @@ int hybi_cones_alloc(HybCones& cs) {
     fill_items_kernel<<<nblocks(q, 256), 256>>>(cs.q, cs.item_flag, cs.item_prox);
     HYB_CUDA(cudaGetLastError());
     HYB_CUDA(cudaDeviceSynchronize());
-    static bool attr_set = false;
-    if (!attr_set) {
+    static HybDevOnce attr_once;
+    if (attr_once.first()) {
         HYB_CUDA(cudaFuncSetAttribute(psd_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       PSD_WARPS * 4 * PSD_MAT * (int)sizeof(double)));
         HYB_CUDA(cudaFuncSetAttribute(psd_prod_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       PSD_WARPS * 3 * PSD_MAT * (int)sizeof(double)));
         HYB_CUDA(cudaFuncSetAttribute(psd_dder3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       PSD_WARPS * 3 * PSD_MAT * (int)sizeof(double)));
-        attr_set = true;
     }
     return 0;
 }
@@ -801,6 +981,19 @@ int hybi_cones_update(cudaStream_t st, HybCones& cs, const double* primal, const
 #undef SOC_UPD
                 break;
             }
+            case HYB_EPINORMINF: {
+                const bool warp = b.dim > 32;
+                const int64_t threads = warp ? b.count * 32 : b.count;
+                if (warp)
+                    ninf_update_kernel<true><<<nblocks(threads, 128), 128, 0, st>>>(b.count, b.dim, b.offset, b.cone0, primal,
+                                                                                  dual_in, scal, irtmu, cs.point, cs.dual,
+                                                                                  cs.grad, cs.aux, cs.item_flag, cs.item_prox);
+                else
+                    ninf_update_kernel<false><<<nblocks(threads, 128), 128, 0, st>>>(b.count, b.dim, b.offset, b.cone0, primal,
+                                                                                   dual_in, scal, irtmu, cs.point, cs.dual,
+                                                                                   cs.grad, cs.aux, cs.item_flag, cs.item_prox);
+                break;
+            }
             case HYB_POSSEMIDEFTRI:
                 if (b.dense) {
                     HYB_CHECK(hybd_psd_update(st, (HybDensePsd*)b.dense, primal + b.offset, dual_in + b.offset, scal, irtmu,
@@ -851,7 +1044,8 @@ int hybi_cones_prod(cudaStream_t st, HybCones& cs, int which, const double* arr,
         if (!cs.block_mask.empty() && !cs.block_mask[bi]) continue;
         int op;
         if (which == 4) op = b.use_dual ? HYB_OP_INV_HESS : HYB_OP_HESS;
-        else if (which == 5) op = b.use_dual ? HYB_OP_INV_SQRT_HESS : HYB_OP_SQRT_HESS;
+        else if (which == 5 || (which == 7 && cs.block_sqrt[bi])) op = b.use_dual ? HYB_OP_INV_SQRT_HESS : HYB_OP_SQRT_HESS;
+        else if (which == 7) op = b.use_dual ? HYB_OP_INV_HESS : HYB_OP_HESS;
         else if (which == 6)  // hess_prod_slow! is hess_prod! except for the WSOS cones (Cones.jl:229-231)
             op = (b.type == HYB_WSOSINTERPNONNEGATIVE || b.type == HYB_WSOSINTERPPOSSEMIDEFTRI) ? 6 : HYB_OP_HESS;
         else op = which;
@@ -876,6 +1070,21 @@ int hybi_cones_prod(cudaStream_t st, HybCones& cs, int which, const double* arr,
                     if (warp) SOC_PROD(2, true); else SOC_PROD(2, false);
                 }
 #undef SOC_PROD
+                break;
+            }
+            case HYB_EPINORMINF: {
+                if (op != HYB_OP_HESS && op != HYB_OP_INV_HESS) {
+                    hyb_set_error("EpiNormInf has no sqrt Hessian oracles (epinorminf.jl:73)");
+                    return -3;
+                }
+                const bool warp = b.dim > 32;
+                const int64_t threads = (warp ? 32 : 1) * b.count * m;
+                if (warp)
+                    ninf_prod_kernel<true><<<nblocks(threads, 128), 128, 0, st>>>(b.count, b.dim, b.offset, b.cone0, m, op,
+                                                                                cs.point, cs.aux, arr, lda, prod, ldp);
+                else
+                    ninf_prod_kernel<false><<<nblocks(threads, 128), 128, 0, st>>>(b.count, b.dim, b.offset, b.cone0, m, op,
+                                                                                 cs.point, cs.aux, arr, lda, prod, ldp);
                 break;
             }
             case HYB_POSSEMIDEFTRI:
@@ -948,6 +1157,15 @@ int hybi_cones_dder3(cudaStream_t st, HybCones& cs, const double* dir, double* o
                     if (warp) SOC_D3(2, true); else SOC_D3(2, false);
                 }
 #undef SOC_D3
+                break;
+            }
+            case HYB_EPINORMINF: {
+                const bool warp = b.dim > 32;
+                const int64_t threads = warp ? b.count * 32 : b.count;
+                if (warp)
+                    ninf_dder3_kernel<true><<<nblocks(threads, 128), 128, 0, st>>>(b.count, b.dim, b.offset, cs.point, dir, out);
+                else
+                    ninf_dder3_kernel<false><<<nblocks(threads, 128), 128, 0, st>>>(b.count, b.dim, b.offset, cs.point, dir, out);
                 break;
             }
             case HYB_POSSEMIDEFTRI:

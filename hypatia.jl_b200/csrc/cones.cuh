@@ -9,6 +9,7 @@ enum HybConeType {
     HYB_POSSEMIDEFTRI = 3,
     HYB_WSOSINTERPNONNEGATIVE = 4,
     HYB_WSOSINTERPPOSSEMIDEFTRI = 5,
+    HYB_EPINORMINF = 6,
 };
 
 enum HybProdOp { HYB_OP_HESS = 0, HYB_OP_INV_HESS = 1, HYB_OP_SQRT_HESS = 2, HYB_OP_INV_SQRT_HESS = 3 };
@@ -50,6 +51,7 @@ struct HybCones {
     double* skron = nullptr;      // PSD blocks, wide products: per cone the dim x dim symmetric-Kronecker matrix
     int64_t skron_cap = 0;        // doubles allocated in skron
     std::vector<char> block_mask; // if non-empty: hybi_cones_prod touches only blocks with mask != 0
+    std::vector<char> block_sqrt; // selector 7: per block 1 = (inv_)sqrt product, 0 = block Hessian product
 };
 
 int hybi_cones_alloc(HybCones& cs);
@@ -63,7 +65,8 @@ int hybi_cones_update(cudaStream_t st, HybCones& cs, const double* primal, const
 int hybi_cones_reduce(cudaStream_t st, HybCones& cs, int use_max_prox, int* all_flags, double* agg);
 // prod = op(H) * arr for every cone; arr/prod are q x m column-major device arrays (ld >= q).
 // which: 0 hess, 1 inv_hess, 2 sqrt_hess, 3 inv_sqrt_hess, 4 block (inv_hess for dual-barrier cones, else hess),
-//        5 block sqrt (inv_sqrt for dual-barrier cones, else sqrt), 6 hess_prod_slow
+//        5 block sqrt (inv_sqrt for dual-barrier cones, else sqrt), 6 hess_prod_slow,
+//        7 Schur assembly: per block 5 or 4 as cs.block_sqrt says (qrchol.jl:228-252)
 int hybi_cones_prod(cudaStream_t st, HybCones& cs, int which, const double* arr, int64_t lda, double* prod, int64_t ldp,
                    int64_t m);
 int hybi_cones_dder3(cudaStream_t st, HybCones& cs, const double* dir, double* out);

@@ -8,6 +8,13 @@
 extern int64_t g_misc_launches;
 struct HybDirs;  // device-resident direction engine (dirs.cu)
 
+// aligned staging copy of a run of rows of GQ2 / HGQ2 that starts on an odd row (api.cu: staged_rows)
+struct HybStageRun {
+    int64_t off = 0, rows = 0, ld = 0;
+    bool constant = false;
+    double* buf = nullptr;
+};
+
 // ----------------------------------------------------------------------------- context
 struct hyb_ctx {
     int device = 0;
@@ -41,6 +48,7 @@ struct hyb_ctx {
     void* peer_ipc_base = nullptr;  // non-root: pointer returned by cudaIpcOpenMemHandle
     int peer_world = 0, peer_rank = 0;
     HybDirs* dirs = nullptr;  // direction engine state (allocated by hyb_dirs_setup)
+    std::vector<HybStageRun> stage;
 };
 
 static inline cudaError_t h2d(hyb_ctx* c, void* dst, const void* src, size_t bytes) {

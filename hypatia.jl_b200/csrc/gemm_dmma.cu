@@ -249,7 +249,6 @@ gemm_tail_reduce_kernel(int M, int N, double alpha, double beta, double* __restr
 }
 
 int64_t g_gemm_launches = 0;
-int g_gemm_num_sms = 0;
 struct TailWs { int dev; cudaStream_t st; double* p; };
 std::vector<TailWs> g_tail_ws;  // one workspace per (device, stream) that ever needed one (never shrinks)
 
@@ -268,10 +267,9 @@ int hyb_gemm_tn(cudaStream_t st, int64_t M, int64_t N, int64_t K, double alpha, 
         hyb_set_error("hyb_gemm_tn: operands must be 16-byte aligned with even leading dimensions");
         return -1;
     }
-    static bool attr_set = false;
-    if (!attr_set) {
+    static HybDevOnce attr_once;
+    if (attr_once.first()) {
         HYB_CUDA(cudaFuncSetAttribute(gemm_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-        attr_set = true;
     }
     CUtensorMap tmA, tmB;
     HYB_CHECK(hyb_make_tmap_2d_f64(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM));
@@ -291,8 +289,7 @@ int hyb_gemm_tn(cudaStream_t st, int64_t M, int64_t N, int64_t K, double alpha, 
     // split the tiles of a small last wave along K (long contractions only: the Schur syrk)
     int dev = 0;
     HYB_CUDA(cudaGetDevice(&dev));
-    if (g_gemm_num_sms == 0) HYB_CUDA(cudaDeviceGetAttribute(&g_gemm_num_sms, cudaDevAttrMultiProcessorCount, dev));
-    const int P = g_gemm_num_sms;
+    const int P = hyb_num_sms();
     int64_t n_main = ntiles;
     int nsplit = 1;
     double* ws = nullptr;
@@ -347,10 +344,9 @@ int hyb_gemm_tn_blockdiag(cudaStream_t st, int64_t M, int64_t N, int64_t K, int6
         hyb_set_error("hyb_gemm_tn_blockdiag: operands must be 16-byte aligned with even leading dimensions and step");
         return -1;
     }
-    static bool attr_set = false;
-    if (!attr_set) {
+    static HybDevOnce attr_once;
+    if (attr_once.first()) {
         HYB_CUDA(cudaFuncSetAttribute(gemm_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-        attr_set = true;
     }
     CUtensorMap tmA, tmB;
     HYB_CHECK(hyb_make_tmap_2d_f64(&tmA, A, (uint64_t)K, (uint64_t)(step * (batch - 1) + M), (uint64_t)lda, BK, BM));

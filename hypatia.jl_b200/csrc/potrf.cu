@@ -26,25 +26,33 @@ namespace {
 
 constexpr int NB = 128;
 constexpr int LDS = NB + 1;  // padded shared-memory leading dimension
-constexpr int IB = 32;       // inner block of the panel factorization
+constexpr int IB = 16;       // inner block of the panel factorization
+constexpr int PLD = NB + 4;  // row stride of the panel kernel's block (conflict-free DMMA fragment loads)
 
 // --------------------------------------------------------------------------------
 // panel: in-place upper Cholesky of an nb x nb diagonal block (nb <= 128) in shared
-// memory, blocked by IB = 32 columns: (1) one warp factors the 32 x 32 diagonal block in
-// registers (lane c owns column c; pivots and multipliers travel by shuffle), (2)
-// thread-per-column forward substitution gives the 32 x m row panel, (3) all threads apply
-// the rank-32 update to the trailing triangle in 4 x 4 register tiles.  Substitution only
-// (no explicit inverses), so backward stable like LAPACK dpotf2/dpotrf.  The reciprocal pivot
-// comes from rsqrt (1 ulp) and the pivot itself is d * rsqrt(d): both are off by at most a few
-// ulp from LAPACK's sqrt / divide, which is a relative perturbation of the same size in A_jj.
+// memory, blocked by IB = 16 columns: (1) one warp factors the 16 x 16 diagonal block in
+// registers (lane c & 15 owns column c; pivots and multipliers travel by shuffle), (2)
+// thread-per-column forward substitution gives the 16 x m row panel, (3) all threads apply
+// the rank-16 update to the trailing triangle in 4 x 4 register tiles.  Substitution only
+// (no explicit inverses), so backward stable like LAPACK dpotf2/dpotrf.
+//
+// The serial chain of the whole panel is 128 x (pivot -> reciprocal square root -> scale ->
+// rank-1 update of the next pivot).  IB = 16 keeps the per-pivot shuffle/FMA work of the one
+// warp on that chain short (15 instead of 31 steps).  Pivot arithmetic, two variants:
+//   EXACT (default): r = sqrt(d) (IEEE), rinv = 1 / r (IEEE) -- what LAPACK's dpotf2 computes;
+//   FAST : rinv = rsqrt(d) polished by one Newton step (<= 0.5 ulp + 2^-70 from 1/sqrt(d)),
+//          r = d * rinv corrected by one Newton step off the chain (the IEEE sqrt in all but
+//          near-tie cases): no divide and no sqrt->divide dependency on the chain.
 // The strictly lower triangle of the block in global memory is zeroed on exit.
 // --------------------------------------------------------------------------------
+template <bool FAST>
 __device__ __noinline__ void potf2_diag_block(double* S, double* rdiag, int jb, int lane, int* fail, int* info,
                                                  int k0) {
     double col[IB];
-    const int c = lane;
+    const int c = lane & (IB - 1);  // lanes 16..31 mirror lanes 0..15
 #pragma unroll
-    for (int i = 0; i < IB; ++i) col[i] = S[(jb + i) * LDS + jb + c];
+    for (int i = 0; i < IB; ++i) col[i] = S[(jb + i) * PLD + jb + c];
     bool bad = false;
     int badj = 0;
 #pragma unroll
@@ -54,14 +62,18 @@ __device__ __noinline__ void potf2_diag_block(double* S, double* rdiag, int jb, 
             bad = true;
             badj = j;
         }
-#ifdef HYB_POTF2_RSQRT
-        const double rinv = rsqrt(d);
-        const double ujc = (c == j) ? d * rinv : col[j] * rinv;
-#else
-        const double r = sqrt(d);
-        const double rinv = 1.0 / r;
+        double r, rinv;
+        if (FAST) {
+            double y = rsqrt(d);
+            const double e = fma(-d * y, y, 1.0);
+            rinv = fma(0.5 * y, e, y);
+            r = d * rinv;
+            r = fma(fma(-r, r, d), 0.5 * rinv, r);
+        } else {
+            r = sqrt(d);
+            rinv = 1.0 / r;
+        }
         const double ujc = (c == j) ? r : col[j] * rinv;
-#endif
         if (c >= j) col[j] = ujc;
         if (lane == j) rdiag[j] = rinv;
 #pragma unroll
@@ -75,75 +87,87 @@ __device__ __noinline__ void potf2_diag_block(double* S, double* rdiag, int jb, 
             *fail = 1;
             *info = k0 + jb + badj + 1;
         }
-    } else {
+    } else if (lane < IB) {
 #pragma unroll
         for (int i = 0; i < IB; ++i)
-            if (i <= c) S[(jb + i) * LDS + jb + c] = col[i];
+            if (i <= c) S[(jb + i) * PLD + jb + c] = col[i];
     }
 }
 
 __device__ __noinline__ void potf2_row_panel(double* S, const double* rdiag, int jb, int c) {
     double y[IB];
 #pragma unroll
-    for (int i = 0; i < IB; ++i) y[i] = S[(jb + i) * LDS + c];
+    for (int i = 0; i < IB; ++i) y[i] = S[(jb + i) * PLD + c];
 #pragma unroll
     for (int k = 0; k < IB; ++k) {
         y[k] *= rdiag[k];
 #pragma unroll
-        for (int i = k + 1; i < IB; ++i) y[i] -= S[(jb + k) * LDS + jb + i] * y[k];
+        for (int i = k + 1; i < IB; ++i) y[i] -= S[(jb + k) * PLD + jb + i] * y[k];
     }
 #pragma unroll
-    for (int i = 0; i < IB; ++i) S[(jb + i) * LDS + c] = y[i];
+    for (int i = 0; i < IB; ++i) S[(jb + i) * PLD + c] = y[i];
 }
 
-// S[i][c] -= sum_k U[jb+k][i] U[jb+k][c] for t0 <= i <= c < nbp, in 4 x 4 register tiles.
-// A thread's 4 rows / 4 columns are interleaved with stride mt (= tiles per side), so the lanes
-// of a warp read consecutive shared-memory words (a contiguous 4 x 4 tile per thread puts the
-// lanes 32 bytes apart: 4-way bank conflicts on every operand load).
-__device__ __forceinline__ void potf2_trailing_update(double* S, int jb, int t0, int nbp, int tid, int nth) {
-    const int mt = (nbp - t0) >> 2;  // tiles per side
-    for (int t = tid; t < mt * mt; t += nth) {
-        const int ti = t / mt, tj = t - ti * mt;
-        const int i0 = t0 + ti, c0 = t0 + tj;
-        double acc[4][4];
+// S[i][c] -= sum_k U[jb+k][i] U[jb+k][c] for t0 <= i, c < nbp (block upper triangle) on the FP64 tensor
+// pipe: every warp takes 16 x 16 blocks of the trailing matrix (2 x 2 m8n8k4 tiles, K = IB = 16 in four
+// k-steps).  Per 1024 FMAs a warp issues 4 shared-memory loads instead of the 16 a 4 x 4 register tile
+// of scalar FMAs needs -- the scalar form was bound by shared-memory bandwidth (8.3k cycles for the first
+// update of a panel against 1.8k here).  With the row stride PLD = 132 the fragment loads
+// (word = 4 t + g mod 16 per half-warp) are conflict-free.  Entries below the diagonal inside the
+// diagonal blocks are updated too; nothing ever reads them.
+__device__ __forceinline__ void dmma884_sub(double& c0, double& c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+}
+__device__ __forceinline__ void potf2_trailing_update(double* S, int jb, int t0, int nbp, int warp, int lane, int nwarps) {
+    const int nt = (nbp - t0) >> 4;  // 16-wide blocks per side
+    const int cnt = nt * (nt + 1) / 2;
+    const int g = lane >> 2, t = lane & 3;
+    for (int idx = warp; idx < cnt; idx += nwarps) {
+        int bj = (int)((sqrtf(8.0f * idx + 1.0f) - 1.0f) * 0.5f);
+        while (bj * (bj + 1) / 2 > idx) --bj;
+        while ((bj + 1) * (bj + 2) / 2 <= idx) ++bj;
+        const int bi = idx - bj * (bj + 1) / 2;
+        const int i0 = t0 + 16 * bi, c0 = t0 + 16 * bj;
+        double acc[2][2][2] = {{{0.0, 0.0}, {0.0, 0.0}}, {{0.0, 0.0}, {0.0, 0.0}}};
 #pragma unroll
-        for (int a = 0; a < 4; ++a)
-#pragma unroll
-            for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
-#pragma unroll 8
-        for (int k = 0; k < IB; ++k) {
-            const double* row = S + (jb + k) * LDS;
-            double u[4], v[4];
-#pragma unroll
-            for (int a = 0; a < 4; ++a) u[a] = row[i0 + a * mt];
-#pragma unroll
-            for (int b = 0; b < 4; ++b) v[b] = row[c0 + b * mt];
-#pragma unroll
-            for (int a = 0; a < 4; ++a)
-#pragma unroll
-                for (int b = a; b < 4; ++b) acc[a][b] += u[a] * v[b];  // b < a lies below the diagonal
+        for (int kk = 0; kk < IB / 4; ++kk) {
+            const double* row = S + (jb + 4 * kk + t) * PLD;
+            const double a0 = row[i0 + g], a1 = row[i0 + 8 + g];
+            const double b0 = row[c0 + g], b1 = row[c0 + 8 + g];
+            dmma884_sub(acc[0][0][0], acc[0][0][1], a0, b0);
+            dmma884_sub(acc[0][1][0], acc[0][1][1], a0, b1);
+            dmma884_sub(acc[1][0][0], acc[1][0][1], a1, b0);
+            dmma884_sub(acc[1][1][0], acc[1][1][1], a1, b1);
         }
 #pragma unroll
-        for (int a = 0; a < 4; ++a)
+        for (int mi = 0; mi < 2; ++mi)
 #pragma unroll
-            for (int b = a; b < 4; ++b)
-                if (c0 + b * mt >= i0 + a * mt) S[(i0 + a * mt) * LDS + c0 + b * mt] -= acc[a][b];
+            for (int ni = 0; ni < 2; ++ni) {
+                double2* pc = (double2*)(S + (i0 + 8 * mi + g) * PLD + c0 + 8 * ni + 2 * t);
+                double2 v = *pc;
+                v.x -= acc[mi][ni][0];
+                v.y -= acc[mi][ni][1];
+                *pc = v;
+            }
     }
 }
 
 #ifdef HYB_PROFILE_POTF2
-__device__ long long g_potf2_ts[32];
+__device__ long long g_potf2_ts[64];
 __device__ long long g_trsm_ts[16];
 #define POTF2_TS(i) do { if (tid == 0) g_potf2_ts[i] = clock64(); } while (0)
 #else
 #define POTF2_TS(i)
 #endif
 
+template <bool FAST>
 __global__ void __launch_bounds__(512, 1)
 potf2_kernel(double* __restrict__ A, int64_t lda, int nb, int* __restrict__ info, int k0) {
     extern __shared__ double sm[];
-    double* S = sm;               // S[r * LDS + c]
-    double* rdiag = sm + NB * LDS;  // reciprocals of the current diagonal block's pivots
+    double* S = sm;               // S[r * PLD + c]
+    double* rdiag = sm + NB * PLD;  // reciprocals of the current diagonal block's pivots
     __shared__ int fail;
     const int tid = threadIdx.x, nth = blockDim.x, lane = tid & 31, warp = tid >> 5;
     if (*info != 0) return;  // an earlier panel failed: nothing meaningful to do
@@ -161,7 +185,7 @@ potf2_kernel(double* __restrict__ A, int64_t lda, int nb, int* __restrict__ info
 #pragma unroll
         for (int t = 0; t < NB * NB / 512; ++t) {
             const int e = tid + t * 512, r = e & (NB - 1), c = e >> 7;
-            S[r * LDS + c] = v[t];
+            S[r * PLD + c] = v[t];
         }
     }
     __syncthreads();
@@ -171,7 +195,7 @@ potf2_kernel(double* __restrict__ A, int64_t lda, int nb, int* __restrict__ info
     const int nbp = (nb + IB - 1) / IB * IB;
     for (int jb = 0; jb < nbp; jb += IB) {
         // (1) IB x IB diagonal block
-        if (warp == 0) potf2_diag_block(S, rdiag, jb, lane, &fail, info, k0);
+        if (warp == 0) potf2_diag_block<FAST>(S, rdiag, jb, lane, &fail, info, k0);
         __syncthreads();
         POTF2_TS(2 + 3 * (jb / IB));
         if (fail) return;
@@ -183,29 +207,29 @@ potf2_kernel(double* __restrict__ A, int64_t lda, int nb, int* __restrict__ info
         __syncthreads();
         POTF2_TS(3 + 3 * (jb / IB));
         // (3) trailing update
-        potf2_trailing_update(S, jb, t0, nbp, tid, nth);
+        potf2_trailing_update(S, jb, t0, nbp, warp, lane, nth >> 5);
         __syncthreads();
         POTF2_TS(4 + 3 * (jb / IB));
     }
-    POTF2_TS(20);
+    POTF2_TS(40);
     // write back: U in the upper triangle, zeros strictly below (the block is workspace)
     for (int e = tid; e < NB * NB; e += nth) {
         const int r = e & (NB - 1), c = e >> 7;
-        if (r < nb && c < nb) A[r + (int64_t)c * lda] = (r <= c) ? S[r * LDS + c] : 0.0;
+        if (r < nb && c < nb) A[r + (int64_t)c * lda] = (r <= c) ? S[r * PLD + c] : 0.0;
     }
-    POTF2_TS(21);
+    POTF2_TS(41);
 }
 
 #ifdef HYB_PROFILE_POTF2
 void hyb_potf2_dump_ts() {
-    long long ts[32];
+    long long ts[64];
     cudaDeviceSynchronize();
     cudaMemcpyFromSymbol(ts, g_potf2_ts, sizeof(ts));
     fprintf(stderr, "potf2 clocks: stage %lld", ts[1] - ts[0]);
-    for (int b = 0; b < 4; ++b)
+    for (int b = 0; b < NB / IB; ++b)
         fprintf(stderr, " | diag %lld panel %lld upd %lld", ts[2 + 3 * b] - (b ? ts[1 + 3 * b] : ts[1]),
                 ts[3 + 3 * b] - ts[2 + 3 * b], ts[4 + 3 * b] - ts[3 + 3 * b]);
-    fprintf(stderr, " | writeback %lld | total %lld\n", ts[21] - ts[20], ts[21] - ts[0]);
+    fprintf(stderr, " | writeback %lld | total %lld\n", ts[41] - ts[40], ts[41] - ts[0]);
     long long tt[16];
     cudaMemcpyFromSymbol(tt, g_trsm_ts, sizeof(tt));
     fprintf(stderr, "trsm clocks: stage %lld | s0 %lld u1 %lld s1 %lld u2 %lld s2 %lld u3 %lld s3 %lld | writeback %lld | total %lld\n",
@@ -222,14 +246,23 @@ void hyb_potf2_dump_ts() {
 // Backward stable (LAPACK dtrsm semantics), no explicit inverse.
 // --------------------------------------------------------------------------------
 constexpr int TRSM_THREADS = 128;
-constexpr int TRSM_COLS = 64;          // columns of A12 per CTA
-constexpr int TLD = TRSM_COLS + 1;     // padded slab leading dimension
+constexpr int TRSM_COLS = 64;          // columns of the right-hand side per CTA (widest instance)
+// The slab kernels are templates on COLS (64, 32 or 16 columns per CTA): the work of a CTA is
+// 128 x 128 / 2 x COLS FP64 FMAs on one SM's FP64 pipe, so narrower slabs on more SMs shorten the
+// kernel whenever the launch still fits one wave -- which is what matters for the row panel of the
+// Cholesky factorization, where this kernel sits on the serial chain.
+template <int COLS> struct TrsmCfg {
+    static constexpr int TLD = COLS + 1;      // padded slab leading dimension
+    static constexpr int CPT = COLS / 16;     // columns per thread in the register-tiled updates
+    static constexpr int SMEM = (NB * LDS + NB * (COLS + 1) + NB) * (int)sizeof(double);
+};
 
 // substitution of one 32-row chunk, one thread per column, chunk in registers
 // (template instances called in sequence: a register array declared inside a runtime
 //  chunk loop gets demoted to local memory by nvcc)
-template <int CB>
+template <int CB, int COLS>
 __device__ __forceinline__ void trsm_solve_chunk(const double* Uc, const double* dinv, double* T, int c) {
+    constexpr int TLD = TrsmCfg<COLS>::TLD;
     double v[32];
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = T[(CB * 32 + i) * TLD + c];
@@ -243,48 +276,52 @@ __device__ __forceinline__ void trsm_solve_chunk(const double* Uc, const double*
     for (int i = 0; i < 32; ++i) T[(CB * 32 + i) * TLD + c] = v[i];
 }
 
-// rows R0..R0+31 of the slab -= U[0:K, R0:R0+32]' * Y[0:K, :]  (K = CB*32), 4x4 register tiles
-template <int CB>
+// rows R0..R0+31 of the slab -= U[0:K, R0:R0+32]' * Y[0:K, :]  (K = CB*32), 4 x CPT register tiles
+template <int CB, int COLS>
 __device__ __forceinline__ void trsm_update_chunk(const double* Uc, double* T, int tid) {
     if (CB == 0) return;
-    // a thread's 4 rows are 8 apart and its 4 columns 16 apart, so the lanes of a warp read
-    // consecutive words of the slab (contiguous 4 x 4 tiles put them 32 bytes apart: 4-way conflicts)
+    constexpr int TLD = TrsmCfg<COLS>::TLD, CPT = TrsmCfg<COLS>::CPT;
+    // a thread's 4 rows are 8 apart and its columns 16 apart, so the lanes of a warp read
+    // consecutive words of the slab (contiguous tiles put them 32 bytes apart: 4-way conflicts)
     const int tr = tid >> 4, tc = tid & 15;  // 8 row groups x 16 column groups
     const int r0 = CB * 32 + tr, c0 = tc;
-    double acc[4][4];
+    double acc[4][CPT];
 #pragma unroll
     for (int i = 0; i < 4; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = 0.0;
+        for (int j = 0; j < CPT; ++j) acc[i][j] = 0.0;
 #pragma unroll 4
     for (int k = 0; k < CB * 32; ++k) {
-        double u[4], y[4];
+        double u[4], y[CPT];
 #pragma unroll
         for (int i = 0; i < 4; ++i) u[i] = Uc[(r0 + 8 * i) * LDS + k];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) y[j] = T[k * TLD + c0 + 16 * j];
+        for (int j = 0; j < CPT; ++j) y[j] = T[k * TLD + c0 + 16 * j];
 #pragma unroll
         for (int i = 0; i < 4; ++i)
 #pragma unroll
-            for (int j = 0; j < 4; ++j) acc[i][j] += u[i] * y[j];
+            for (int j = 0; j < CPT; ++j) acc[i][j] += u[i] * y[j];
     }
 #pragma unroll
     for (int i = 0; i < 4; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) T[(r0 + 8 * i) * TLD + c0 + 16 * j] -= acc[i][j];
+        for (int j = 0; j < CPT; ++j) T[(r0 + 8 * i) * TLD + c0 + 16 * j] -= acc[i][j];
 }
 
 // --------------------------------------------------------------------------------
 // row panel of the blocked factorization: A12 <- U11^-T A12 (U11 128 x 128 upper).
-// A CTA stages U11 and a 128 x 64 slab of A12 in shared memory and alternates, per
+// A CTA stages U11 and a 128 x COLS slab of A12 in shared memory and alternates, per
 // 32-row chunk, a register-tiled update with the rows already solved and a forward
 // substitution with the 32 x 32 diagonal block (one thread per column, chunk in
 // registers).  Substitution only - no explicit inverse (LAPACK dtrsm semantics).
 // --------------------------------------------------------------------------------
-// stage U11 (nb x nb upper, identity padded to 128) and a 128 x 64 slab of the right-hand sides
+// stage U11 (nb x nb upper, identity padded to 128) and a 128 x COLS slab of the right-hand sides
+template <int COLS>
 __device__ __forceinline__ void trsm_stage(const double* __restrict__ U11, int64_t ldu, int nb,
                                            const double* __restrict__ B, int64_t ld, int64_t col0, int ncol, double* Uc,
                                            double* T, double* dinv, int tid) {
+    constexpr int TLD = TrsmCfg<COLS>::TLD;
+    constexpr int CW = COLS < 32 ? COLS : 32;
     // batches of 32 loads per thread in flight before the stores (see potf2_kernel)
     static_assert(TRSM_THREADS == NB, "staging below assumes one thread per row");
 #pragma unroll 1
@@ -300,15 +337,15 @@ __device__ __forceinline__ void trsm_stage(const double* __restrict__ U11, int64
         for (int t = 0; t < 32; ++t) Uc[(i0 + t) * LDS + tid] = v[t];
     }
 #pragma unroll 1
-    for (int c0 = 0; c0 < TRSM_COLS; c0 += 32) {
-        double v[32];
+    for (int c0 = 0; c0 < COLS; c0 += CW) {
+        double v[CW];
 #pragma unroll
-        for (int t = 0; t < 32; ++t) {
+        for (int t = 0; t < CW; ++t) {
             const int r = tid, c = c0 + t;
             v[t] = (c < ncol && r < nb) ? B[r + (col0 + c) * ld] : 0.0;
         }
 #pragma unroll
-        for (int t = 0; t < 32; ++t) T[tid * TLD + c0 + t] = v[t];
+        for (int t = 0; t < CW; ++t) T[tid * TLD + c0 + t] = v[t];
     }
     __syncthreads();
     if (tid < NB) dinv[tid] = 1.0 / Uc[tid * LDS + tid];
@@ -321,42 +358,44 @@ __device__ __forceinline__ void trsm_stage(const double* __restrict__ U11, int64
 #define TRSM_TS(i)
 #endif
 
+template <int COLS>
 __global__ void __launch_bounds__(TRSM_THREADS, 1)
 trsm_upper_T_kernel(const double* __restrict__ U11, int64_t ldu, int nb, double* __restrict__ A12, int64_t ld,
                     int64_t n2) {
+    constexpr int TLD = TrsmCfg<COLS>::TLD;
     extern __shared__ double sm[];
     double* Uc = sm;                     // Uc[i * LDS + k] = U[k][i]  (column i of U11, contiguous in k)
     double* T = sm + NB * LDS;           // T[r * TLD + c]
     double* dinv = T + NB * TLD;         // 1 / U[k][k]
     const int tid = threadIdx.x;
-    const int64_t col0 = (int64_t)blockIdx.x * TRSM_COLS;
-    const int ncol = (int)((n2 - col0 < TRSM_COLS) ? (n2 - col0) : TRSM_COLS);
+    const int64_t col0 = (int64_t)blockIdx.x * COLS;
+    const int ncol = (int)((n2 - col0 < COLS) ? (n2 - col0) : COLS);
     TRSM_TS(0);
-    trsm_stage(U11, ldu, nb, A12, ld, col0, ncol, Uc, T, dinv, tid);
+    trsm_stage<COLS>(U11, ldu, nb, A12, ld, col0, ncol, Uc, T, dinv, tid);
     TRSM_TS(1);
-    const bool solver_thread = tid < TRSM_COLS;
-    if (solver_thread) trsm_solve_chunk<0>(Uc, dinv, T, tid);
+    const bool solver_thread = tid < COLS;
+    if (solver_thread) trsm_solve_chunk<0, COLS>(Uc, dinv, T, tid);
     __syncthreads();
     TRSM_TS(2);
-    trsm_update_chunk<1>(Uc, T, tid);
+    trsm_update_chunk<1, COLS>(Uc, T, tid);
     __syncthreads();
     TRSM_TS(3);
-    if (solver_thread) trsm_solve_chunk<1>(Uc, dinv, T, tid);
+    if (solver_thread) trsm_solve_chunk<1, COLS>(Uc, dinv, T, tid);
     __syncthreads();
     TRSM_TS(4);
-    trsm_update_chunk<2>(Uc, T, tid);
+    trsm_update_chunk<2, COLS>(Uc, T, tid);
     __syncthreads();
     TRSM_TS(5);
-    if (solver_thread) trsm_solve_chunk<2>(Uc, dinv, T, tid);
+    if (solver_thread) trsm_solve_chunk<2, COLS>(Uc, dinv, T, tid);
     __syncthreads();
     TRSM_TS(6);
-    trsm_update_chunk<3>(Uc, T, tid);
+    trsm_update_chunk<3, COLS>(Uc, T, tid);
     __syncthreads();
     TRSM_TS(7);
-    if (solver_thread) trsm_solve_chunk<3>(Uc, dinv, T, tid);
+    if (solver_thread) trsm_solve_chunk<3, COLS>(Uc, dinv, T, tid);
     __syncthreads();
     TRSM_TS(8);
-    for (int e = tid; e < NB * TRSM_COLS; e += TRSM_THREADS) {
+    for (int e = tid; e < NB * COLS; e += TRSM_THREADS) {
         const int r = e & (NB - 1), c = e >> 7;
         if (c < ncol && r < nb) A12[r + (col0 + c) * ld] = T[r * TLD + c];
     }
@@ -364,6 +403,7 @@ trsm_upper_T_kernel(const double* __restrict__ U11, int64_t ldu, int nb, double*
 }
 
 // ---- backward variant: slab <- U11^-1 slab (U11 upper, back substitution) ----------------
+constexpr int TLD = TrsmCfg<TRSM_COLS>::TLD;
 template <int CB>
 __device__ __forceinline__ void trsm_bsolve_chunk(const double* Uc, const double* dinv, double* T, int c) {
     double v[32];
@@ -418,7 +458,7 @@ trsm_upper_N_kernel(const double* __restrict__ U11, int64_t ldu, int nb, double*
     const int tid = threadIdx.x;
     const int64_t col0 = (int64_t)blockIdx.x * TRSM_COLS;
     const int ncol = (int)((n2 - col0 < TRSM_COLS) ? (n2 - col0) : TRSM_COLS);
-    trsm_stage(U11, ldu, nb, B, ld, col0, ncol, Uc, T, dinv, tid);
+    trsm_stage<TRSM_COLS>(U11, ldu, nb, B, ld, col0, ncol, Uc, T, dinv, tid);
     const bool solver_thread = tid < TRSM_COLS;
     if (solver_thread) trsm_bsolve_chunk<3>(Uc, dinv, T, tid);
     __syncthreads();
@@ -698,8 +738,6 @@ trsv_bwd_kernel(const double* __restrict__ U, int64_t ld, double* x, int64_t ldx
     }
 }
 
-int g_num_sms = 0;
-
 }  // namespace
 
 int hyb_chol_alloc(HybChol& ch, int64_t N) {
@@ -728,11 +766,14 @@ void hyb_chol_free(HybChol& ch) {
     if (ch.ev_head) cudaEventDestroy(ch.ev_head);
     if (ch.ev_panel) cudaEventDestroy(ch.ev_panel);
     cudaFree(ch.work);
+    cudaFree(ch.ipiv);
+    cudaFree(ch.bk_ws);
+    cudaFree(ch.bk_state);
     ch = HybChol();
 }
 
-constexpr int PANEL_SMEM = (NB * LDS + IB) * (int)sizeof(double);
-constexpr int TRSM_SMEM = (NB * LDS + NB * TLD + NB) * (int)sizeof(double);
+constexpr int PANEL_SMEM = (NB * PLD + IB) * (int)sizeof(double);
+constexpr int TRSM_SMEM = TrsmCfg<TRSM_COLS>::SMEM;
 constexpr int TRSV_SMEM = (NB * LDS + NB + 5 * HYB_MAX_RHS * NB) * (int)sizeof(double);
 int64_t g_potrf_launches = 0;
 
@@ -760,40 +801,85 @@ static int potrf_outer_block() {
     return ob;
 }
 
+// per-device attributes of the panel / slab kernels (dynamic shared memory above 48 KB)
+static int ensure_panel_attrs() {
+    static HybDevOnce once;
+    if (once.first()) {
+        HYB_CUDA(cudaFuncSetAttribute(potf2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, PANEL_SMEM));
+        HYB_CUDA(cudaFuncSetAttribute(potf2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, PANEL_SMEM));
+        HYB_CUDA(cudaFuncSetAttribute(trsm_upper_T_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, TrsmCfg<64>::SMEM));
+        HYB_CUDA(cudaFuncSetAttribute(trsm_upper_T_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, TrsmCfg<32>::SMEM));
+        HYB_CUDA(cudaFuncSetAttribute(trsm_upper_T_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, TrsmCfg<16>::SMEM));
+        HYB_CUDA(cudaFuncSetAttribute(trsm_upper_N_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TRSM_SMEM));
+    }
+    return 0;
+}
+
+// pivot arithmetic of the panel kernel: IEEE sqrt + divide (default) or the polished rsqrt form
+// (HYB_POTF2_FAST=1), see potf2_diag_block
+static bool potf2_fast() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("HYB_POTF2_FAST");
+        v = (e && atoi(e) != 0) ? 1 : 0;
+    }
+    return v == 1;
+}
+
+// A12 (nb x n2) <- U11^-T A12 with the narrowest slabs that still fit one wave of CTAs
+static int launch_row_trsm(cudaStream_t s, const double* U11, int64_t ldu, int nb, double* A12, int64_t ld, int64_t n2) {
+    const int sms = hyb_num_sms();
+    if (n2 <= (int64_t)16 * sms)
+        trsm_upper_T_kernel<16><<<(unsigned)((n2 + 15) / 16), TRSM_THREADS, TrsmCfg<16>::SMEM, s>>>(U11, ldu, nb, A12, ld, n2);
+    else if (n2 <= (int64_t)32 * sms)
+        trsm_upper_T_kernel<32><<<(unsigned)((n2 + 31) / 32), TRSM_THREADS, TrsmCfg<32>::SMEM, s>>>(U11, ldu, nb, A12, ld, n2);
+    else
+        trsm_upper_T_kernel<64><<<(unsigned)((n2 + 63) / 64), TRSM_THREADS, TrsmCfg<64>::SMEM, s>>>(U11, ldu, nb, A12, ld, n2);
+    ++g_potrf_launches;
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}
+
 int hyb_potrf(cudaStream_t st, HybChol& ch, int* info_out) {
     const int64_t N = ch.N, ld = ch.ld;
-    static bool attr_set = false;
-    if (!attr_set) {
-        HYB_CUDA(cudaFuncSetAttribute(potf2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PANEL_SMEM));
-        HYB_CUDA(cudaFuncSetAttribute(trsm_upper_T_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TRSM_SMEM));
-        HYB_CUDA(cudaFuncSetAttribute(trsm_upper_N_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TRSM_SMEM));
-        attr_set = true;
-    }
+    HYB_CHECK(ensure_panel_attrs());
     const int64_t OB = potrf_outer_block();
+    const bool fast = potf2_fast();
+    ch.kind = 0;
     cudaStream_t sp = ch.panel_stream;
     HYB_CUDA(cudaMemsetAsync(ch.info, 0, sizeof(int), st));
     auto panel = [&](cudaStream_t s, int64_t k0) -> int {
         const int nb = (int)((N - k0 < NB) ? (N - k0) : NB);
         double* A11 = ch.F + k0 + k0 * ld;
-        potf2_kernel<<<1, 512, PANEL_SMEM, s>>>(A11, ld, nb, ch.info, (int)k0);
+        if (fast)
+            potf2_kernel<true><<<1, 512, PANEL_SMEM, s>>>(A11, ld, nb, ch.info, (int)k0);
+        else
+            potf2_kernel<false><<<1, 512, PANEL_SMEM, s>>>(A11, ld, nb, ch.info, (int)k0);
         ++g_potrf_launches;
         HYB_CUDA(cudaGetLastError());
         const int64_t n2 = N - k0 - nb;
-        if (n2 > 0) {
-            double* A12 = ch.F + k0 + (k0 + nb) * ld;
-            trsm_upper_T_kernel<<<(unsigned)((n2 + TRSM_COLS - 1) / TRSM_COLS), TRSM_THREADS, TRSM_SMEM, s>>>(
-                A11, ld, nb, A12, ld, n2);
-            ++g_potrf_launches;
-            HYB_CUDA(cudaGetLastError());
-        }
+        if (n2 > 0) HYB_CHECK(launch_row_trsm(s, A11, ld, nb, ch.F + k0 + (k0 + nb) * ld, ld, n2));
         return 0;
     };
+    // HYB_POTRF_TRACE=1: time stamps (CUDA events) of every outer block's phases on both streams, printed
+    // as a table at the end (a measurement aid; adds event records only)
+    static const bool trace = getenv("HYB_POTRF_TRACE") != nullptr;
+    std::vector<cudaEvent_t> tev;
+    auto stamp = [&](cudaStream_t s) {
+        if (!trace) return;
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        cudaEventRecord(e, s);
+        tev.push_back(e);
+    };
+    stamp(st);
     HYB_CUDA(cudaEventRecord(ch.ev_head, st));
     for (int64_t K0 = 0; K0 < N; K0 += OB) {
         const int64_t ob = (N - K0 < OB) ? (N - K0) : OB;
         const int64_t K1 = K0 + ob;
         // the panels of this outer block, on the panel stream, once its rows are up to date
         HYB_CUDA(cudaStreamWaitEvent(sp, ch.ev_head, 0));
+        stamp(sp);  // [1 + 5b] panels start
         for (int64_t j0 = K0; j0 < K1; j0 += NB) {
             HYB_CHECK(panel(sp, j0));
             const int64_t r1 = j0 + NB;
@@ -802,8 +888,10 @@ int hyb_potrf(cudaStream_t st, HybChol& ch, int* info_out) {
                 HYB_CHECK(hyb_gemm_tn(sp, K1 - r1, N - r1, NB, -1.0, U, ld, U, ld, 1.0, ch.F + r1 + r1 * ld, ld, 0));
             }
         }
+        stamp(sp);  // [2 + 5b] panels end
         HYB_CUDA(cudaEventRecord(ch.ev_panel, sp));
         HYB_CUDA(cudaStreamWaitEvent(st, ch.ev_panel, 0));
+        stamp(st);  // [3 + 5b] main stream has the panels (and its own previous bulk update)
         const int64_t n2 = N - K1;  // trailing size
         if (n2 <= 0) break;
         const double* U12 = ch.F + K0 + K1 * ld;  // ob x n2: block rows of this outer block
@@ -811,12 +899,29 @@ int hyb_potrf(cudaStream_t st, HybChol& ch, int* info_out) {
         // look-ahead: the next outer block's rows first
         const int64_t nh = n2 < OB ? n2 : OB;
         HYB_CHECK(hyb_gemm_tn(st, nh, n2, ob, -1.0, U12, ld, U12, ld, 1.0, A22, ld, 0));
+        stamp(st);  // [4 + 5b] head update done
         HYB_CUDA(cudaEventRecord(ch.ev_head, st));
         // bulk: everything below, upper triangle only
         const int64_t n3 = n2 - nh;
         if (n3 > 0)
             HYB_CHECK(hyb_gemm_tn(st, n3, n3, ob, -1.0, U12 + nh * ld, ld, U12 + nh * ld, ld, 1.0, A22 + nh + nh * ld, ld,
                                   HYB_GEMM_UPPER));
+        stamp(st);  // [5 + 5b] bulk update done
+    }
+    if (trace) {
+        cudaStreamSynchronize(sp);
+        cudaStreamSynchronize(st);
+        auto at = [&](size_t i) {
+            float ms = 0;
+            if (i < tev.size()) cudaEventElapsedTime(&ms, tev[0], tev[i]);
+            return ms * 1e3f;
+        };
+        fprintf(stderr, "potrf trace N=%lld OB=%lld (us since start): block | panels start..end | main gets panels | head done | bulk done\n",
+                (long long)N, (long long)OB);
+        for (size_t b = 0; 1 + 5 * b + 2 < tev.size(); ++b)
+            fprintf(stderr, "  %3zu | %8.0f .. %8.0f | %8.0f | %8.0f | %8.0f\n", b, at(1 + 5 * b), at(2 + 5 * b), at(3 + 5 * b),
+                    at(4 + 5 * b), at(5 + 5 * b));
+        for (cudaEvent_t e : tev) cudaEventDestroy(e);
     }
     if (info_out) {
         HYB_CUDA(cudaMemcpyAsync(info_out, ch.info, sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -830,14 +935,14 @@ int hyb_potrf(cudaStream_t st, HybChol& ch, int* info_out) {
 
 template <int R>
 static int potrs_launch(cudaStream_t st, HybChol& ch, double* x, int64_t ldx) {
-    static bool attr_set = false;
-    if (!attr_set) {
+    static HybDevOnce attr_once;
+    if (attr_once.first()) {
         HYB_CUDA(cudaFuncSetAttribute(trsv_fwd_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, TRSV_SMEM));
         HYB_CUDA(cudaFuncSetAttribute(trsv_bwd_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, TRSV_SMEM));
-        attr_set = true;
     }
     int N = (int)ch.N, nblk = (int)ch.nblk;
-    int grid = nblk < g_num_sms ? nblk : g_num_sms;
+    const int num_sms = hyb_num_sms();
+    int grid = nblk < num_sms ? nblk : num_sms;
     const double* U = ch.F;
     int64_t ld = ch.ld;
     int* flags = ch.flags;
@@ -853,11 +958,7 @@ static int potrs_launch(cudaStream_t st, HybChol& ch, double* x, int64_t ldx) {
 
 int hyb_potrs_multi(cudaStream_t st, HybChol& ch, double* X, int64_t ldx, int R) {
     if (ch.N == 0 || R <= 0) return 0;
-    if (g_num_sms == 0) {
-        int dev = 0;
-        HYB_CUDA(cudaGetDevice(&dev));
-        HYB_CUDA(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
-    }
+    if (ch.kind == 1) return hyb_sytrs_rook(st, ch, X, ldx, R);
     switch (R) {
         case 1: return potrs_launch<1>(st, ch, X, ldx);
         case 2: return potrs_launch<2>(st, ch, X, ldx);
@@ -884,25 +985,14 @@ int hyb_copy_upper(cudaStream_t st, const double* src, int64_t lds_, double* dst
 // ---------------------------------------------------------------------------------------
 // dense toolkit used by the large-PSD and WSOS cone engines
 // ---------------------------------------------------------------------------------------
-static int ensure_trsm_attrs() {
-    static bool done = false;
-    if (!done) {
-        HYB_CUDA(cudaFuncSetAttribute(potf2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PANEL_SMEM));
-        HYB_CUDA(cudaFuncSetAttribute(trsm_upper_T_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TRSM_SMEM));
-        HYB_CUDA(cudaFuncSetAttribute(trsm_upper_N_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TRSM_SMEM));
-        done = true;
-    }
-    return 0;
-}
-
 // B (N x nrhs) <- U^-T B : blocked forward substitution, DMMA updates (LAPACK dtrsm 'L','U','T')
 int hyb_trsm_fwd(cudaStream_t st, const double* U, int64_t ld, int64_t N, double* B, int64_t ldb, int64_t nrhs) {
     if (N <= 0 || nrhs <= 0) return 0;
-    HYB_CHECK(ensure_trsm_attrs());
+    HYB_CHECK(ensure_panel_attrs());
     const unsigned grid = (unsigned)((nrhs + TRSM_COLS - 1) / TRSM_COLS);
     for (int64_t k0 = 0; k0 < N; k0 += NB) {
         const int nb = (int)((N - k0 < NB) ? (N - k0) : NB);
-        trsm_upper_T_kernel<<<grid, TRSM_THREADS, TRSM_SMEM, st>>>(U + k0 + k0 * ld, ld, nb, B + k0, ldb, nrhs);
+        trsm_upper_T_kernel<64><<<grid, TRSM_THREADS, TRSM_SMEM, st>>>(U + k0 + k0 * ld, ld, nb, B + k0, ldb, nrhs);
         ++g_potrf_launches;
         HYB_CUDA(cudaGetLastError());
         const int64_t rest = N - k0 - nb;
@@ -916,7 +1006,7 @@ int hyb_trsm_fwd(cudaStream_t st, const double* U, int64_t ld, int64_t N, double
 int hyb_trsm_bwd(cudaStream_t st, const double* U, const double* Lc, int64_t ld, int64_t N, double* B, int64_t ldb,
                  int64_t nrhs) {
     if (N <= 0 || nrhs <= 0) return 0;
-    HYB_CHECK(ensure_trsm_attrs());
+    HYB_CHECK(ensure_panel_attrs());
     const unsigned grid = (unsigned)((nrhs + TRSM_COLS - 1) / TRSM_COLS);
     const int64_t last = ((N - 1) / NB) * NB;
     for (int64_t k0 = last; k0 >= 0; k0 -= NB) {

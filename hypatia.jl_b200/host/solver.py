@@ -228,6 +228,7 @@ class Solver:
                 if self._step_and_check():
                     break
             if self.status in CHECK_NEAR_STATUSES:
+                self.exit_reason = self.status  # which exit led to the near-convergence recheck (Solvers.jl:375-377)
                 self._check_converged(True)
             self._postprocess()
         elif hasattr(self.syssolver, "abort_workers"):
@@ -251,6 +252,7 @@ class Solver:
         self.primal_obj_t = self.dual_obj_t = self.primal_obj = self.dual_obj = nan
         self.gap = self.x_feas = self.y_feas = self.z_feas = self.tau_feas = nan
         self.trace = []
+        self.exit_reason = None
 
     def _setup_loaded(self) -> None:  # Solvers.jl:395-429
         orig = self.orig_model
@@ -545,6 +547,7 @@ class Solver:
         if self.stepper.expect_improvement():
             if improv < self.tol_slow:
                 if self.prev_is_slow and self.prev2_is_slow:
+                    self.exit_reason = "SlowProgress"
                     self.status = "SlowProgress"
                     return True
                 self.prev2_is_slow = self.prev_is_slow

@@ -105,6 +105,42 @@ def possemideftri9():  # :498-556
     return m, dict(status="Optimal", primal_obj=RT2 + RT3, s=s, z=z)
 
 
+def epinorminf1():  # :882-897
+    m = Model([0, -1, -1], [[1, 0, 0], [0, 1, 0]], [1, 1 / RT2], -_I(3), np.zeros(3), [cs.EpiNormInf(3)])
+    return m, dict(status="Optimal", primal_obj=-1 - 1 / RT2, x=[1, 1 / RT2, 1], y=[1, 1])
+
+
+def epinorminf2():  # :899-928  (l = 3; a dual-barrier and a primal-barrier cone)
+    l = 3
+    L = 2 * l + 1
+    c = np.arange(-l, l + 1, dtype=np.float64)
+    A = np.zeros((2, L))
+    A[0, 0] = A[0, L - 1] = A[1, 0] = 1
+    A[1, L - 1] = -1
+    G = np.vstack([np.zeros((1, L)), _I(L), np.zeros((1, L)), 2 * _I(L)])
+    h = np.zeros(2 * L + 2)
+    h[0] = 1
+    h[L + 1] = 1
+    cones = [cs.EpiNormInf(L + 1, use_dual=True), cs.EpiNormInf(L + 1, use_dual=False)]
+    m = Model(c, A, [0, 0], G, h, cones, obj_offset=1.0)
+    return m, dict(status="Optimal", primal_obj=-l + 2.0, x_at={1: 0.5, L - 2: -0.5}, x_abs_sum=1.0, tol_factor=10.0)
+
+
+def epinorminf3():  # :930-946 (primal-barrier case of the loop)
+    m = Model([1, 0, 0, 0, 0, 0], np.zeros((0, 6)), [], -_I(6), np.zeros(6), [cs.EpiNormInf(6)])
+    return m, dict(status="Optimal", primal_obj=0.0, x_norm=0.0)
+
+
+def epinorminf3_dual():  # :930-946 (use_dual = true case of the loop)
+    m = Model([1, 0, 0, 0, 0, 0], np.zeros((0, 6)), [], -_I(6), np.zeros(6), [cs.EpiNormInf(6, use_dual=True)])
+    return m, dict(status="Optimal", primal_obj=0.0, x_norm=0.0)
+
+
+def epinorminf4():  # :948-962
+    m = Model([0, 1, -1], [[1, 0, 0], [0, 1, 0]], [1, -0.4], -_I(3), np.zeros(3), [cs.EpiNormInf(3, use_dual=True)])
+    return m, dict(status="Optimal", primal_obj=-1.0, x=[1, -0.4, 0.6], y=[1, 0])
+
+
 def epinormeucl1():  # :1014-1030
     m = Model([0, -1, -1], [[10, 0, 0], [0, 10, 0]], [10, 10 / RT2], -_I(3), np.zeros(3), [cs.EpiNormEucl(3)])
     return m, dict(status="Optimal", primal_obj=-RT2, x=[1, 1 / RT2, 1 / RT2], y=[RT2 / 10, 0])
@@ -224,6 +260,7 @@ KNOWN_ANSWER = {
     for f in (
         dimension1, primalinfeas1, primalinfeas2, dualinfeas2, dualinfeas3, nonnegative4,
         possemideftri1, possemideftri2, possemideftri8, possemideftri9,
+        epinorminf1, epinorminf2, epinorminf3, epinorminf3_dual, epinorminf4,
         epinormeucl1, epinormeucl2, epinormeucl3,
         epipersquare1, epipersquare2, epipersquare3, epipersquare4,
         wsosinterpnonnegative1, wsosinterpnonnegative2, wsosinterpnonnegative3,
@@ -300,6 +337,29 @@ def portfolio_socs(K: int = 100_000, d: int = 4, n: int = 2048, seed: int = 1) -
         h[r0] = gammas[j]
         G[r0 + 1 : r0 + d, :] = -S[j]
         cones.append(cs.EpiNormEucl(d))
+    return Model(-returns, np.ones((1, n)), [1.0], G, h, cones)
+
+
+def portfolio_norminf(K: int = 100_000, d: int = 4, n: int = 2048, seed: int = 1) -> Model:
+    """cfg4, EpiNormInf variant (BASELINE config 4 names "EpiNormEucl/EpiNormInf"): K scenario risk
+    constraints ||S_j x||_inf <= gamma_j (EpiNormInf(d), the cone without sqrt oracles: every iteration
+    takes the gemm branch of the Schur assembly, qrchol.jl:248-254), 1'x = 1, x >= 0."""
+    rng = np.random.default_rng(seed)
+    returns = rng.random(n)
+    x0 = rng.random(n)
+    x0 /= x0.sum()
+    S = rng.standard_normal((K, d - 1, n))
+    gammas = np.max(np.abs(S @ x0), axis=1) * 1.5 + 1e-3
+    q = n + K * d
+    G = np.zeros((q, n))
+    h = np.zeros(q)
+    G[:n, :] = -_I(n)
+    cones = [cs.Nonnegative(n)]
+    for j in range(K):
+        r0 = n + j * d
+        h[r0] = gammas[j]
+        G[r0 + 1 : r0 + d, :] = -S[j]
+        cones.append(cs.EpiNormInf(d))
     return Model(-returns, np.ones((1, n)), [1.0], G, h, cones)
 
 

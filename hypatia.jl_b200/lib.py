@@ -12,7 +12,8 @@ from typing import Optional
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libhypatia_b200.so")
+# HYB_LIB: an alternative build of the same library (profiling builds of tools/); never a different backend
+LIB_PATH = os.environ.get("HYB_LIB") or os.path.join(_HERE, "libhypatia_b200.so")
 
 c_double_p = C.POINTER(C.c_double)
 c_int_p = C.POINTER(C.c_int)
@@ -86,6 +87,11 @@ SIGNATURES = {
         C.c_int,
         [C.c_void_p, C.c_int64, c_double_p, C.c_int64, c_double_p, C.c_int64, C.c_int64, c_int_p],
     ),
+    "hyb_symm_solve": (
+        C.c_int,
+        [C.c_void_p, C.c_int64, c_double_p, C.c_int64, c_int_p, c_double_p, C.c_int64, C.c_int64, c_int_p],
+    ),
+    "hyb_schur_set": (C.c_int, [C.c_void_p, c_double_p]),
     "hyb_gemv_n_noalloc": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
     "hyb_stats": (C.c_int, [C.c_void_p, C.c_int, c_double_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "hyb_last_schur_timings": (C.c_int, [C.c_void_p, c_double_p, c_double_p, c_double_p]),
@@ -213,6 +219,28 @@ class Context:
             "hyb_gemm_tn_host",
         )
         return out
+
+    def symm_solve(self, A: np.ndarray, B: Optional[np.ndarray] = None):
+        """Rook-pivoted Bunch-Kaufman on the GPU: returns (ldu, ipiv, X, info) in LAPACK dsytrf_rook's layout."""
+        A = f64(A).copy(order="F")
+        N = A.shape[0]
+        ipiv = np.zeros(max(N, 1), dtype=np.int32)
+        info = C.c_int(0)
+        if B is None:
+            B2, nrhs, one_d = np.zeros((max(N, 1), 1), order="F"), 0, False
+        else:
+            B2 = f64(B).copy(order="F")
+            one_d = B2.ndim == 1
+            if one_d:
+                B2 = B2.reshape(-1, 1, order="F")
+            nrhs = B2.shape[1]
+        self.check(
+            self.lib.hyb_symm_solve(self.ptr, N, dptr(A), max(N, 1), ipiv.ctypes.data_as(c_int_p), dptr(B2), max(N, 1), nrhs,
+                                    C.byref(info)),
+            "hyb_symm_solve",
+        )
+        X = None if B is None else (B2[:, 0] if one_d else B2)
+        return A, ipiv[:N], X, info.value
 
     def posdef_solve(self, A: np.ndarray, B: np.ndarray):
         """Returns (U, X, info): upper Cholesky factor, solution of A X = B, LAPACK info."""

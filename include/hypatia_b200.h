@@ -30,7 +30,8 @@ enum hyb_cone_type {
     HYB_CONE_EPIPERSQUARE = 2,            /* epipersquare.jl */
     HYB_CONE_POSSEMIDEFTRI = 3,           /* possemideftri.jl (real svec) */
     HYB_CONE_WSOSINTERPNONNEGATIVE = 4,   /* wsosinterpnonnegative.jl */
-    HYB_CONE_WSOSINTERPPOSSEMIDEFTRI = 5  /* wsosinterppossemideftri.jl */
+    HYB_CONE_WSOSINTERPPOSSEMIDEFTRI = 5, /* wsosinterppossemideftri.jl */
+    HYB_CONE_EPINORMINF = 6               /* epinorminf.jl (real; use_dual_barrier: epigraph of the 1-norm) */
 };
 
 /* One entry per cone of model.cones, in order; offsets follow build_cone_idxs
@@ -187,6 +188,16 @@ int hyb_gemm_tn_host(hyb_ctx* ctx, int64_t M, int64_t N, int64_t K, double alpha
  * referenced, overwritten by U) and solve for nrhs right-hand sides in B (N x nrhs, ldb).
  * *info = LAPACK dpotrf info (0 success, j = leading minor j not positive definite). */
 int hyb_posdef_solve(hyb_ctx* ctx, int64_t N, double* A, int64_t lda, double* B, int64_t ldb, int64_t nrhs, int* info);
+/* symm_fact!(A) = bunchkaufman!(A, true) + ldiv!, dense.jl:199-203 (LAPACK dsytrf_rook / dsytrs_rook): factor
+ * the symmetric N x N matrix A (upper triangle referenced) as U D U' with rook pivoting, in LAPACK's storage
+ * (A overwritten by the multipliers and D, ipiv[N] 1-based with negative entries for 2 x 2 pivots), and solve
+ * for nrhs <= 4 right-hand sides in B.  *info = LAPACK info (0, or the 1-based column of an exactly zero pivot). */
+int hyb_symm_solve(hyb_ctx* ctx, int64_t N, double* A, int64_t lda, int* ipiv, double* B, int64_t ldb, int64_t nrhs,
+                   int* info);
+/* Replace the assembled Schur matrix by a host matrix (N x N, upper triangle referenced) before
+ * hyb_schur_factor: the `lhs` field of QRCholDenseSystemSolver (qrchol.jl:111-143) is plain data a caller may
+ * overwrite, and the tests use it to drive posdef_fact_copy!'s fallback chain with an indefinite matrix. */
+int hyb_schur_set(hyb_ctx* ctx, const double* lhs);
 
 /* ---- allocation-free product (no counterpart in the reference) -----------------------
  * y = G x on DEVICE pointers owned by the caller (column-major G, q x N, leading dimension
@@ -195,8 +206,11 @@ int hyb_posdef_solve(hyb_ctx* ctx, int64_t N, double* A, int64_t lda, double* B,
  * library: another runtime's pool owns the GPU memory, or the call sits in a latency-critical
  * section.  Its split-sum scratch is a fixed 4 MiB device array inside the library, so
  * q is limited to 65536 rows (larger q returns -4), every GPU that loads the library keeps
- * that array until exit, and calls that overlap on one GPU race on it.  The first call on a
- * device also looks up the array's address; make that call before any stream capture. */
+ * that array until exit, and calls that overlap on one GPU race on it.  The FIRST call on a
+ * device is a warm-up: it makes the CUDA runtime load this library's code on that device (which
+ * is when the 4 MiB array itself comes into being -- an implicit device allocation that may
+ * synchronise) and looks up the array's address.  Make that call at initialisation, outside any
+ * latency-critical section and before any stream capture; every later call allocates nothing. */
 int hyb_gemv_n_noalloc(const double* G_dev, int64_t q, int64_t N, int64_t ld, const double* x_dev, double* y_dev,
                        void* stream);
 

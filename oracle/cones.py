@@ -330,6 +330,127 @@ class EpiNormEucl(Cone):
 
 
 # ---------------------------------------------------------------------------
+class EpiNormInf(Cone):
+    """src/Cones/epinorminf.jl (real case, R == T): all oracles are O(d) closed forms; no sqrt oracles
+    (use_sqrt_hess_oracles = false, :73), so this cone takes the gemm branch of the Schur assembly."""
+
+    def use_sqrt_hess_oracles(self, arr_dim):  # :73
+        return False
+
+    def reset_data(self):  # :63-71
+        super().reset_data()
+        self.inv_hess_aux_updated = False
+
+    def update_feas(self):  # :100-113
+        u = self.point[0]
+        if u > EPS:
+            self.w = self.point[1:].copy()
+            self.is_feas_flag = (u - float(np.max(np.abs(self.w)))) > EPS
+        else:
+            self.is_feas_flag = False
+        self.feas_updated = True
+        return self.is_feas_flag
+
+    def is_dual_feas(self):  # :115-128
+        u = self.dual_point[0]
+        if u > EPS:
+            return (u - float(np.sum(np.abs(self.dual_point[1:])))) > EPS
+        return False
+
+    def update_grad(self):  # :136-162
+        u, w = self.point[0], self.w
+        d = self.dim - 1
+        self.mu = w / u
+        self.zeta = 0.5 * (u - self.mu * w)
+        self.cu = (d - 1) / u
+        g = np.empty(self.dim)
+        g[0] = self.cu - float(np.sum(1.0 / self.zeta))
+        g[1:] = self.mu / self.zeta
+        self.grad_vec = g
+        self.grad_updated = True
+        return g
+
+    def update_hess(self):  # :164-203 (dense restatement of the arrow-shaped sparse Hessian)
+        g = self.grad()
+        u, zeta = self.point[0], self.zeta
+        ui = 1.0 / u
+        tzi2 = (1.0 / zeta - ui) / zeta
+        H = np.zeros((self.dim, self.dim))
+        H[0, 0] = float(np.sum(tzi2)) - self.cu / u
+        off = -g[1:] / zeta
+        H[0, 1:] = off
+        H[1:, 0] = off
+        H[np.arange(1, self.dim), np.arange(1, self.dim)] = tzi2
+        self.hess_mat = H
+        self.hess_updated = True
+
+    def hess_prod(self, arr):  # :205-229
+        self.grad()
+        a, one_d = _as2d(arr)
+        u, mu, zeta = self.point[0], self.mu[:, None], self.zeta[:, None]
+        p, r = a[0], a[1:]
+        pui = p / u
+        s1 = (p[None, :] - mu * r) / zeta
+        prod = np.empty_like(a)
+        prod[0] = np.sum((s1 - pui[None, :]) / zeta, axis=0) - self.cu * pui
+        prod[1:] = (r / u - s1 * mu) / zeta
+        return prod[:, 0] if one_d else prod
+
+    def _update_inv_hess_aux(self):  # :257-273
+        self.grad()
+        u, w = self.point[0], self.w
+        umz = u - self.zeta
+        self.Zu = -self.cu + float(np.sum(1.0 / umz))
+        self.wumzi = w / umz
+        self.zti = u - self.wumzi * w
+        self.inv_hess_aux_updated = True
+
+    def update_inv_hess(self):  # :275-312
+        if not self.inv_hess_aux_updated:
+            self._update_inv_hess_aux()
+        u = self.point[0]
+        Hi = np.empty((self.dim, self.dim))
+        hiuu = Hi[0, 0] = u / self.Zu
+        Hi[1:, 0] = self.wumzi * hiuu
+        Hi[0, 1:] = Hi[1:, 0]
+        Hi[1:, 1:] = np.outer(self.wumzi, self.wumzi * hiuu)
+        Hi[np.arange(1, self.dim), np.arange(1, self.dim)] += self.zeta * self.zti
+        self.inv_hess_mat = Hi
+        self.inv_hess_updated = True
+
+    def inv_hess_prod(self, arr):  # :314-335
+        if not self.inv_hess_aux_updated:
+            self._update_inv_hess_aux()
+        a, one_d = _as2d(arr)
+        u = self.point[0]
+        p, r = a[0], a[1:]
+        c1 = u * (p + self.wumzi @ r) / self.Zu
+        prod = np.empty_like(a)
+        prod[0] = c1
+        prod[1:] = c1[None, :] * self.wumzi[:, None] + (self.zeta * self.zti)[:, None] * r
+        return prod[:, 0] if one_d else prod
+
+    def sqrt_hess_prod(self, arr):
+        raise NotImplementedError("EpiNormInf has no sqrt Hessian oracles (epinorminf.jl:73)")
+
+    inv_sqrt_hess_prod = sqrt_hess_prod
+
+    def dder3(self, direction):  # :366-392
+        self.grad()
+        u, mu, zeta = self.point[0], self.mu, self.zeta
+        p, r = direction[0], direction[1:]
+        pui = p / u
+        rui = r / u
+        s1 = (p - mu * r) / zeta
+        s2 = 0.5 * (p * pui - rui * r) / zeta - s1 * s1
+        c1 = float(np.sum((s1 * pui + s2) / zeta))
+        out = np.empty(self.dim)
+        out[0] = -c1 - self.cu * pui * pui
+        out[1:] = (s1 * rui + s2 * mu) / zeta
+        return out
+
+
+# ---------------------------------------------------------------------------
 class EpiPerSquare(Cone):
     def use_sqrt_hess_oracles(self, arr_dim):
         return True
@@ -803,6 +924,7 @@ _CLASSES = {
     cs.POSSEMIDEFTRI: PosSemidefTri,
     cs.WSOSINTERPNONNEGATIVE: WSOSInterpNonnegative,
     cs.WSOSINTERPPOSSEMIDEFTRI: WSOSInterpPosSemidefTri,
+    cs.EPINORMINF: EpiNormInf,
 }
 
 

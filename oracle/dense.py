@@ -6,14 +6,15 @@ Dense factorization helpers, restating src/linearalgebra/dense.jl:
   inv_fact!          :20-24    (potri)
   outer_prod!        :72-79    (syrk, upper)
 
-Deviation (rare fallback path only): the reference's symmetric-indefinite
-fallback is rook-pivoted Bunch-Kaufman (dsytrf_rook, dense.jl:199-201); scipy
-ships no wrapper for it, so plain partial-pivoting dsytrf is used here.
+The symmetric-indefinite fallback is rook-pivoted Bunch-Kaufman like the reference's
+(`bunchkaufman!(A, true)` -> dsytrf_rook, dense.jl:199-201), through oracle/lapack_rook.py.
 """
 from __future__ import annotations
 
 import numpy as np
 from scipy.linalg import lapack
+
+from .lapack_rook import dsytrf_rook, dsytri_rook, dsytrs_rook
 
 EPS = float(np.finfo(np.float64).eps)
 
@@ -27,30 +28,37 @@ def increase_diag(A: np.ndarray) -> np.ndarray:
 
 
 class Fact:
-    """kind: 'chol' (upper factor in .factor) or 'bk' (dsytrf output)."""
+    """kind: 'chol' (upper factor in .factor) or 'bk' (dsytrf_rook output)."""
 
     def __init__(self, kind, factor, ipiv, success):
         self.kind, self.factor, self.ipiv, self.success = kind, factor, ipiv, success
+        self.shifted = False
+
+    @property
+    def kind_code(self) -> int:
+        """0 Cholesky, 1 Bunch-Kaufman, 2 diagonal shift + Bunch-Kaufman, -1 failed (the C-ABI's fact_kind)."""
+        if not self.success:
+            return -1
+        return 0 if self.kind == "chol" else (2 if self.shifted else 1)
 
     def solve(self, arr: np.ndarray) -> np.ndarray:
         b = np.asfortranarray(arr, dtype=np.float64)
         if self.kind == "chol":
             x, info = lapack.dpotrs(self.factor, b, lower=0)
         else:
-            x, info = lapack.dsytrs(self.factor, self.ipiv, b, lower=0)
+            x = dsytrs_rook(self.factor, self.ipiv, b)
         return x
 
     def inverse(self) -> np.ndarray:
         if self.kind == "chol":
             inv, info = lapack.dpotri(self.factor, lower=0)
         else:
-            inv, info = lapack.dsytri(self.factor, self.ipiv, lower=0)
+            return dsytri_rook(self.factor, self.ipiv)
         return np.triu(inv) + np.triu(inv, 1).T
 
 
 def _bk(mat: np.ndarray) -> Fact:
-    lw = lapack.dsytrf_lwork(mat.shape[0], lower=0)[0]
-    ldu, ipiv, info = lapack.dsytrf(mat, lower=0, lwork=int(lw))
+    ldu, ipiv, info = dsytrf_rook(mat)
     return Fact("bk", ldu, ipiv, info == 0)
 
 
@@ -62,6 +70,7 @@ def posdef_fact_copy(mat: np.ndarray, try_shift: bool = True) -> Fact:
     fact = _bk(np.array(mat, order="F"))
     if try_shift and not fact.success:
         fact = _bk(increase_diag(np.array(mat, order="F")))
+        fact.shifted = True
     return fact
 
 

@@ -32,6 +32,7 @@ class QRCholDenseSystemSolver(QRCholSystemSolver):
         self.lhs = np.zeros((n, n), order="F")
         self.fact = None
         self.time_assemble = 0.0
+        self.fact_kinds = []  # per update_lhs: 0 Cholesky, 1 Bunch-Kaufman, 2 shifted + BK, -1 failed (dense.jl:228-249)
         self.setup_point_sub(solver)
 
     def update_lhs(self, solver) -> None:
@@ -74,6 +75,7 @@ class QRCholDenseSystemSolver(QRCholSystemSolver):
         t1 = time.time()
         self.fact = posdef_fact_copy(lhs)
         t2 = time.time()
+        self.fact_kinds.append(self.fact.kind_code)
         self.time_assemble += t1 - t0
         solver.time_upfact += t2 - t1
         if not self.fact.success:

@@ -54,6 +54,12 @@ SPEC_SETS = {
     "psd_wide": [cs.Nonnegative(4)] + [cs.PosSemidefTri(cs.svec_length(8))] * 3 + [cs.PosSemidefTri(136)] * 5
     + [cs.EpiNormEucl(6)] + [cs.PosSemidefTri(cs.svec_length(32))],
     "psd_large": [cs.PosSemidefTri(cs.svec_length(s)) for s in (33, 64, 100, 150)] + [cs.EpiNormEucl(5)],
+    # EpiNormInf (no sqrt oracles; use_dual = epigraph of the 1-norm), thread-per-cone and warp-per-cone sizes,
+    # odd row offsets
+    "norminf_small": [cs.EpiNormInf(2)] + [cs.EpiNormInf(4)] * 40 + [cs.EpiNormInf(7, use_dual=True)] * 5 + [cs.EpiNormInf(3)],
+    "norminf_large": [cs.EpiNormInf(40), cs.EpiNormInf(129, use_dual=True), cs.EpiNormInf(33)],
+    "norminf_mixed": [cs.Nonnegative(3)] + [cs.EpiNormInf(4)] * 5 + [cs.EpiNormEucl(5), cs.EpiNormInf(6, use_dual=True),
+                                                                     cs.PosSemidefTri(6), cs.EpiNormInf(9)],
     "mixed": [cs.Nonnegative(10)] + [cs.EpiNormEucl(8)] * 4 + [cs.EpiPerSquare(8)] * 4
     + [cs.PosSemidefTri(136)] * 3 + [cs.Nonnegative(3), cs.EpiNormEucl(5)],
 }
@@ -97,6 +103,13 @@ def test_oracles_match_cpu(name):
         arr = rng.standard_normal(q) if m == 1 else np.asfortranarray(rng.standard_normal((q, m)))
         for fn in ("hess_prod", "inv_hess_prod", "block_hess_prod", "hess_prod_slow"):
             assert rel_err(getattr(gpu, fn)(arr), getattr(cpu, fn)(arr)) < 1e4 * TOL * tol_scale, (fn, m)
+        if any(sp.type_code == cs.EPINORMINF for sp in specs):
+            # EpiNormInf has no sqrt oracles (epinorminf.jl:73): the batch refuses instead of inventing one
+            from hypatia_b200.lib import HybError
+
+            with pytest.raises(HybError):
+                gpu.sqrt_hess_prod(arr)
+            continue
         # sqrt factors against the per-cone CPU oracles
         want_s = np.empty_like(arr)
         want_i = np.empty_like(arr)

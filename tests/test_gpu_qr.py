@@ -77,11 +77,15 @@ def _oracle(model, **kw):
 )
 def test_solves_with_gpu_preprocessing_qr(build, monkeypatch):
     monkeypatch.setenv("HYB_GPU_QR_MIN", "0")
-    gpu = make_gpu_solver(0)
+    # the reference's benchmark tolerances (benchmarks/natvsext/run.jl:44-60): this test is about the
+    # preprocessing, and at the default eps^0.5 the block model reaches x_feas = 2.0e-8 against 1.5e-8 at
+    # iteration 10, after which the count of remaining iterations is decided by rounding (12 +- 2)
+    kw = dict(tol_rel_opt=1e-7, tol_feas=1e-7, tol_abs_opt=1e-10, tol_infeas=1e-10)
+    gpu = make_gpu_solver(0, **kw)
     assert gpu.qr_backend_min_cols == 0
     gpu.load(build())
     gpu.solve()
-    ref = _oracle(build())
+    ref = _oracle(build(), **kw)
     assert gpu.status == ref.status
     assert abs(gpu.num_iters - ref.num_iters) <= 1
     if ref.status == "Optimal":

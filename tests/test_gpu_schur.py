@@ -85,7 +85,8 @@ def solve_both(model_fn, **kw):
 
 
 GPU_KNOWN = ["dimension1", "primalinfeas1", "primalinfeas2", "dualinfeas2", "dualinfeas3", "nonnegative4",
-             "possemideftri1", "possemideftri2", "possemideftri8", "possemideftri9", "epinormeucl1", "epinormeucl2",
+             "possemideftri1", "possemideftri2", "possemideftri8", "possemideftri9", "epinorminf1", "epinorminf2",
+             "epinorminf3", "epinorminf3_dual", "epinorminf4", "epinormeucl1", "epinormeucl2",
              "epinormeucl3", "epipersquare1", "epipersquare2", "epipersquare3", "epipersquare4",
              "wsosinterpnonnegative1", "wsosinterpnonnegative2", "wsosinterpnonnegative3",
              "wsosinterppossemideftri1", "wsosinterppossemideftri2", "wsosinterppossemideftri3"]
@@ -150,6 +151,49 @@ def test_portfolio_socs_small():
     # at the default eps^0.5 this instance stalls near the optimum on both backends
     kw = dict(tol_rel_opt=1e-6, tol_feas=1e-6, tol_abs_opt=1e-8)
     gpu, cpu = solve_both(lambda: instances.portfolio_socs(K=400, d=4, n=48, seed=1), **kw)
+    assert gpu.status == cpu.status == "Optimal"
+    assert abs(gpu.num_iters - cpu.num_iters) <= 1
+    assert abs(gpu.primal_obj - cpu.primal_obj) <= 1e-7 * (1 + abs(cpu.primal_obj))
+
+
+def test_portfolio_norminf_small():
+    """cfg4-shaped, EpiNormInf variant: every iteration takes the gemm branch of the Schur assembly
+    (use_sqrt_hess_oracles = false) for the norm cones and the syrk branch for the orthant."""
+    kw = dict(tol_rel_opt=1e-7, tol_feas=1e-7, tol_abs_opt=1e-10, tol_infeas=1e-10)  # benchmarks/natvsext/run.jl:44-60
+    gpu, cpu = solve_both(lambda: instances.portfolio_norminf(K=300, d=4, n=40, seed=1), **kw)
+    assert gpu.status == cpu.status == "Optimal"
+    assert abs(gpu.num_iters - cpu.num_iters) <= 1
+    assert abs(gpu.primal_obj - cpu.primal_obj) <= 1e-7 * (1 + abs(cpu.primal_obj))
+    n_early = max(3, len(cpu.trace) // 2)
+    _, bad_early = traj_deviation(gpu.trace[:n_early], cpu.trace[:n_early])
+    assert bad_early is None, bad_early
+
+
+def test_schur_matrix_with_gemm_branch_cones():
+    """Schur matrix of a model mixing sqrt cones and EpiNormInf cones (odd row offsets included) against the oracle."""
+    def model():
+        rng = np.random.default_rng(7)
+        cones = [cs.Nonnegative(5)] + [cs.EpiNormInf(4)] * 6 + [cs.EpiNormEucl(5)] * 3 + [cs.EpiNormInf(7, use_dual=True)] * 2
+        q = sum(c.dim for c in cones)
+        N = 24
+        G = rng.standard_normal((q, N)) / np.sqrt(N)
+        s0 = np.concatenate([c.initial_point() for c in cones])
+        h = G @ rng.standard_normal(N) + s0
+        c = -G.T @ s0
+        return Model(c, np.zeros((0, N)), [], G, h, cones)
+
+    gpu = make_gpu_solver(0)
+    cpu = cpu_solver()
+    for s in (gpu, cpu):
+        s.load(model())
+        s._setup_solver()
+        s._setup_loaded()
+        s._initialize_point()
+        s._setup_stepping()
+        s._calc_convergence_params()
+        s.syssolver.update_lhs(s)
+    assert rel_err(np.triu(gpu.syssolver.schur_matrix()), np.triu(cpu.syssolver.lhs)) < 1e-12
+    gpu, cpu = solve_both(model)
     assert gpu.status == cpu.status == "Optimal"
     assert abs(gpu.num_iters - cpu.num_iters) <= 1
     assert abs(gpu.primal_obj - cpu.primal_obj) <= 1e-7 * (1 + abs(cpu.primal_obj))

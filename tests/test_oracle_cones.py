@@ -103,6 +103,53 @@ def test_epinormeucl(dw):  # :485-489
 
 
 @pytest.mark.parametrize("dw", [1, 2, 5])
+def test_epinorminf(dw):  # :465-470
+    run_oracle_identities(cs.EpiNormInf(1 + dw))
+
+
+def test_epinorminf_barrier_derivatives():
+    """test/cone.jl:472-480 gives the barrier -sum log(u^2 - w_i^2) + (d - 1) log u: the oracle's grad,
+    Hessian product and dder3 are checked against finite differences of it."""
+    dw = 3
+    spec = cs.EpiNormInf(1 + dw)
+    cone = make_cone(spec)
+    cone.setup_data()
+    rng = np.random.default_rng(4)
+    s = np.concatenate([[2.0], rng.uniform(-1, 1, dw)])
+
+    def barrier(v):
+        return -np.sum(np.log(v[0] ** 2 - v[1:] ** 2)) + (dw - 1) * np.log(v[0])
+
+    def grad_at(v):
+        c = make_cone(spec)
+        c.setup_data()
+        c.load_point(v)
+        assert c.is_feas()
+        return c.grad().copy()
+
+    cone.load_point(s)
+    assert cone.is_feas()
+    g = cone.grad()
+    h = 1e-6
+    fd_g = np.array([(barrier(s + h * e) - barrier(s - h * e)) / (2 * h) for e in np.eye(1 + dw)])
+    assert np.allclose(g, fd_g, rtol=1e-7, atol=1e-7)
+    d = rng.standard_normal(1 + dw)
+    fd_H = (grad_at(s + h * d) - grad_at(s - h * d)) / (2 * h)
+    assert np.allclose(cone.hess_prod(d), fd_H, rtol=1e-6, atol=1e-6)
+    # dder3(d) = -1/2 * third directional derivative: d/dt [H(s + t d) d] = -2 dder3(d)
+    def Hd_at(v):
+        c = make_cone(spec)
+        c.setup_data()
+        c.load_point(v)
+        assert c.is_feas()
+        return c.hess_prod(d)
+
+    h3 = 1e-5
+    fd_T = (Hd_at(s + h3 * d) - Hd_at(s - h3 * d)) / (2 * h3)
+    assert np.allclose(cone.dder3(d), -0.5 * fd_T, rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize("dw", [1, 2, 5])
 def test_epipersquare(dw):  # :502-506
     run_oracle_identities(cs.EpiPerSquare(2 + dw))
 
