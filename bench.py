@@ -165,6 +165,7 @@ class IterTimer:
         self._ph = {}
 
     def start(self):
+        self._ph = {}  # the driver zeroes its phase clocks at the start of every solve
         if self.sync:
             self.sync()
         if self.ctx:
@@ -189,6 +190,8 @@ class IterTimer:
                 d2, a2, b2 = sc.stats(reset=True)
                 tw, ts, _ = sc.last_schur_timings()
                 dev_ms, h2d, d2h = dev_ms + d2, h2d + a2, d2h + b2
+            if hasattr(solver.syssolver, "last_assemble_ms"):  # single-process multi-GPU: slowest device's assembly
+                tw, ts = 0.0, solver.syssolver.last_assemble_ms
             lc = self.ctx.launch_count()
             red = getattr(solver.syssolver, "time_reduce_ms", 0.0)
             row.update(dev_ms=dev_ms, h2d=h2d, d2h=d2h, t_w=tw, t_syrk=ts, t_fact=tf, launches=lc - self._launch0,
@@ -357,8 +360,24 @@ def main():
     N = args.N
     model = build_model(N)
     steps, warmup = args.steps, max(args.warmup, 3)
-    mode = os.environ.get("HYB_MULTI_MODE", "rootworker")  # or "replicated" (sharded.py)
-    gpu = make_gpu_solver(local_rank, iter_limit=warmup + steps, **BENCH_TOL, dist=dist, use_peer=not os.environ.get("HYB_NO_PEER"), mode=mode)
+    # multi-GPU form: "rootworker" (default; one process per GPU, rootworker.py), "replicated" (sharded.py) or
+    # "single_process" (rank 0 drives every GPU through hyb_multi_* alone -- the form a Julia host would use;
+    # the other ranks only keep the launch contract: they join the final barrier and reductions)
+    mode = os.environ.get("HYB_MULTI_MODE", "rootworker")
+    single = world > 1 and mode == "single_process"
+    if single and rank != 0:
+        torch.cuda.synchronize()
+        dist.barrier()
+        for _ in range(2):
+            z = torch.zeros(1, dtype=torch.float64, device="cuda")
+            dist.all_reduce(z, op=dist.ReduceOp.MAX)
+        dist.destroy_process_group()
+        return
+    if single:
+        gpu = make_gpu_solver(0, iter_limit=warmup + steps, **BENCH_TOL, devices=list(range(world)))
+    else:
+        gpu = make_gpu_solver(local_rank, iter_limit=warmup + steps, **BENCH_TOL, dist=dist,
+                              use_peer=not os.environ.get("HYB_NO_PEER"), mode=mode)
     rootworker = world > 1 and mode == "rootworker"
     if rootworker and rank != 0:
         # assembly worker: it has no iteration loop of its own; it serves the root until the root stops it,
@@ -387,7 +406,7 @@ def main():
     state = {"sampling": False}
 
     def callback(solver):
-        if dist is not None and not rootworker:
+        if dist is not None and not rootworker and not single:
             dist.barrier()  # replicated form: every rank brackets its own iteration (root/worker: the
             # workers are inside every iteration's barrier already, only the root has an iteration loop)
         timer(solver)
@@ -462,6 +481,8 @@ def main():
     # launch timed on rank 0 contracts that rank's rows only
     if rootworker:
         q_sqrt = gpu.syssolver.row_counts[0]
+    elif single:
+        q_sqrt = max(hi - lo for lo, hi in gpu.syssolver.row_ranges)
     else:
         q_sqrt = gpu.cones.row_counts[0] if world > 1 else model.q
     syrk_flops = q_sqrt * N * (N + 1)  # algorithmic flops of the G'HG contraction per launch
@@ -485,8 +506,10 @@ def main():
             "e2e_definition": "iterations / wall time of the same iterations through the C-ABI with host vectors (all H2D/D2H copies and the host-side stepper included)",
             "solves": solves,
             "parallelism": ("cones partitioned by block over %d ranks; partial Schur matrices reach rank 0 by %s; Cholesky + solves on rank 0"
-                            % (world, "peer stores from the syrk epilogue over NVLink + fixed-order sum" if (rootworker or getattr(gpu.syssolver.backend, "peer", False)) else "NCCL reduce")) if world > 1 else "single GPU",
-            "multi_gpu_form": ("root/worker: rank 0 runs the algorithm, 1 point broadcast + 1 barrier per iteration" if rootworker else "replicated host driver, sharded oracles") if world > 1 else None,
+                            % (world, "peer stores from the syrk epilogue over NVLink + fixed-order sum" if (rootworker or single or getattr(gpu.syssolver.backend, "peer", False)) else "NCCL reduce")) if world > 1 else "single GPU",
+            "multi_gpu_form": ("root/worker: rank 0 runs the algorithm, 1 point broadcast + 1 barrier per iteration" if rootworker else
+                               ("single host process driving all GPUs through hyb_multi_* (peer access, no collective library)" if single
+                                else "replicated host driver, sharded oracles")) if world > 1 else None,
             "line_search_candidates_per_step": float(np.mean([r["n_cand"] for r in rows])),
             "refinement_solves_per_step": float(np.mean([r["n_ref"] for r in rows])),
         }),

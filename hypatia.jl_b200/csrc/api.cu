@@ -57,7 +57,7 @@ int hyb_make_tmap_2d_f64(CUtensorMap* tm, const double* base, uint64_t inner, ui
 }
 
 // ----------------------------------------------------------------------------- small kernels
-int64_t g_misc_launches = 0;
+hyb_counter g_misc_launches{0};
 
 __global__ void axpby_kernel(int64_t n, double a, const double* __restrict__ x, double b, const double* __restrict__ y,
                              double* __restrict__ out) {
@@ -74,8 +74,11 @@ __global__ void increase_diag_kernel(int64_t n, double* A, int64_t ld) {
 }
 
 static void free_model(hyb_ctx* c) {
-    cudaFree(c->GQ2);
-    cudaFree(c->HGQ2);
+    if (!c->borrowed) {
+        cudaFree(c->GQ2);
+        cudaFree(c->HGQ2);
+    }
+    c->borrowed = false;
     cudaFree(c->S);
     cudaFree(c->in_primal);
     cudaFree(c->in_dual);
@@ -160,12 +163,29 @@ void hyb_ctx_destroy(hyb_ctx* c) {
 
 const char* hyb_last_error(hyb_ctx*) { return hyb_get_error(); }
 
+int hyb_ctx_set_assemble_only(hyb_ctx* c, int flag) {
+    if (!c) return -1;
+    c->want_assemble_only = flag != 0;
+    return 0;
+}
+
 int64_t hyb_launch_count(void) {
     return hyb_gemm_launch_count() + hyb_potrf_launch_count() + hyb_sytrf_launch_count() + hybi_cones_launch_count() +
            g_misc_launches;
 }
 
 int hyb_model_load(hyb_ctx* c, int64_t q, int64_t N, const double* GQ2, int64_t ncones, const hyb_cone_desc* descs) {
+    return hyb_model_load_impl(c, q, N, GQ2, q, ncones, descs, nullptr, 0);
+}
+
+}  // extern "C"
+
+// hyb_model_load with the rows of G*Q2 taken from a host array of leading dimension ldg (a row range of the
+// full matrix) and, for a context that only ever assembles partial Schur matrices into another context's
+// memory (multi.cu), without the Schur matrix and the Cholesky workspace of its own.  `borrow` (same device
+// only): use that context's G*Q2 / product rows starting at row `borrow_row` instead of uploading a copy.
+int hyb_model_load_impl(hyb_ctx* c, int64_t q, int64_t N, const double* GQ2, int64_t ldg, int64_t ncones,
+                        const hyb_cone_desc* descs, hyb_ctx* borrow, int64_t borrow_row) {
     if (!c) return -1;
     HYB_CUDA(cudaSetDevice(c->device));
     free_model(c);
@@ -174,14 +194,24 @@ int hyb_model_load(hyb_ctx* c, int64_t q, int64_t N, const double* GQ2, int64_t 
     c->ldq = hyb_round_up(q > 0 ? q : 1, 16);
     c->ldS = hyb_round_up(N > 0 ? N : 1, 16);
     const int64_t ncol = N > 0 ? N : 1;
-    HYB_CUDA(cudaMalloc(&c->GQ2, sizeof(double) * c->ldq * ncol));
-    HYB_CUDA(cudaMalloc(&c->HGQ2, sizeof(double) * c->ldq * ncol));
-    HYB_CUDA(cudaMalloc(&c->S, sizeof(double) * c->ldS * ncol));
-    HYB_CUDA(cudaMemset(c->HGQ2, 0, sizeof(double) * c->ldq * ncol));
-    HYB_CUDA(cudaMemset(c->S, 0, sizeof(double) * c->ldS * ncol));
-    if (q > 0 && N > 0)
-        HYB_CUDA(cudaMemcpy2D(c->GQ2, sizeof(double) * c->ldq, GQ2, sizeof(double) * q, sizeof(double) * q, N,
-                              cudaMemcpyHostToDevice));
+    if (borrow) {
+        c->GQ2 = borrow->GQ2 + borrow_row;
+        c->HGQ2 = borrow->HGQ2 + borrow_row;
+        c->ldq = borrow->ldq;
+        c->borrowed = true;
+    } else {
+        HYB_CUDA(cudaMalloc(&c->GQ2, sizeof(double) * c->ldq * ncol));
+        HYB_CUDA(cudaMalloc(&c->HGQ2, sizeof(double) * c->ldq * ncol));
+        HYB_CUDA(cudaMemset(c->HGQ2, 0, sizeof(double) * c->ldq * ncol));
+        if (q > 0 && N > 0 && GQ2)
+            HYB_CUDA(cudaMemcpy2D(c->GQ2, sizeof(double) * c->ldq, GQ2, sizeof(double) * ldg, sizeof(double) * q, N,
+                                  cudaMemcpyHostToDevice));
+    }
+    c->assemble_only = c->want_assemble_only || borrow != nullptr;
+    if (!c->assemble_only) {
+        HYB_CUDA(cudaMalloc(&c->S, sizeof(double) * c->ldS * ncol));
+        HYB_CUDA(cudaMemset(c->S, 0, sizeof(double) * c->ldS * ncol));
+    }
     const int64_t qa = q > 0 ? q : 1, Na = N > 0 ? N : 1;
     HYB_CUDA(cudaMalloc(&c->in_primal, sizeof(double) * qa));
     HYB_CUDA(cudaMalloc(&c->in_dual, sizeof(double) * qa));
@@ -236,13 +266,15 @@ int hyb_model_load(hyb_ctx* c, int64_t q, int64_t N, const double* GQ2, int64_t 
         return -3;
     }
     HYB_CHECK(hybi_cones_alloc(cs));
-    HYB_CHECK(hyb_chol_alloc(c->chol, N));
+    if (!c->assemble_only) HYB_CHECK(hyb_chol_alloc(c->chol, N));
     c->loaded = true;
     c->point_loaded = false;
     c->fact_ok = false;
     c->updated_irtmu = NAN;
     return 0;
 }
+
+extern "C" {
 
 int hyb_cones_load_point(hyb_ctx* c, const double* primal, const double* dual, double scal) {
     if (!c || !c->loaded) return -1;
@@ -349,12 +381,16 @@ int hyb_cones_dder3(hyb_ctx* c, const double* dir, double* out) {
     return 0;
 }
 
-static int schur_assemble_into(hyb_ctx* c, double* Sdst, double* t_assemble_ms);
-
 int hyb_schur_assemble(hyb_ctx* c, double* t_assemble_ms) {
     if (!c || !c->loaded) return -1;
-    return schur_assemble_into(c, c->S, t_assemble_ms);
+    if (!c->S) {
+        hyb_set_error("hyb_schur_assemble: this context was loaded assemble-only (no Schur matrix of its own)");
+        return -3;
+    }
+    return hyb_schur_assemble_into(c, c->S, t_assemble_ms);
 }
+
+}  // extern "C"
 
 // Operand of one run of rows in the assembly GEMMs.  TMA needs 16-byte aligned operands, i.e. an even
 // first row: a run that starts on an odd row is contracted from an aligned staging copy -- G*Q2's rows are
@@ -391,7 +427,7 @@ static int staged_rows(hyb_ctx* c, const double* src, int64_t off, int64_t rows,
     return 0;
 }
 
-static int schur_assemble_into(hyb_ctx* c, double* Sdst, double* t_assemble_ms) {
+int hyb_schur_assemble_into(hyb_ctx* c, double* Sdst, double* t_assemble_ms) {
     HYB_CUDA(cudaSetDevice(c->device));
     if (c->updated_irtmu != c->updated_irtmu) HYB_CHECK(hyb_ensure_updated(c, c->loaded_scal));
     const int64_t q = c->q, N = c->N;
@@ -467,8 +503,14 @@ static int schur_assemble_into(hyb_ctx* c, double* Sdst, double* t_assemble_ms) 
     return 0;
 }
 
+extern "C" {
+
 int hyb_schur_factor(hyb_ctx* c, double* t_fact_ms, int* fact_kind) {
     if (!c || !c->loaded) return -1;
+    if (c->assemble_only) {
+        hyb_set_error("hyb_schur_factor: this context was loaded assemble-only");
+        return -3;
+    }
     HYB_CUDA(cudaSetDevice(c->device));
     const int64_t N = c->N;
     if (t_fact_ms) *t_fact_ms = 0;
@@ -577,7 +619,7 @@ int hyb_schur_assemble_peer(hyb_ctx* c, double* t_assemble_ms) {
         hyb_set_error("hyb_schur_assemble_peer: no peer slot attached");
         return -3;
     }
-    return schur_assemble_into(c, c->peer_slot, t_assemble_ms);
+    return hyb_schur_assemble_into(c, c->peer_slot, t_assemble_ms);
 }
 
 int hyb_peer_root_sum(hyb_ctx* c, double* t_ms) {

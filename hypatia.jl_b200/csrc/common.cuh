@@ -4,9 +4,14 @@
 #include <cuda_runtime.h>
 #include <cstdint>
 #include <cstdio>
+#include <atomic>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
+
+// launch counters are bumped from several host threads when one process drives several GPUs (multi.cu)
+typedef std::atomic<int64_t> hyb_counter;
 
 #define HYB_EPS 2.220446049250313e-16
 
@@ -34,17 +39,24 @@ static inline int64_t hyb_round_up(int64_t x, int64_t m) { return (x + m - 1) / 
 
 // Per-device one-time set-up.  cudaFuncSetAttribute and the SM count are properties of the CURRENT
 // device, so a process that opens contexts on several GPUs must repeat them on each one:
-//   static HybDevOnce once;  if (once.first()) { cudaFuncSetAttribute(...); }
+//   static HybDevOnce once;  if (HybDevOnce::Guard g(once); g.first) { cudaFuncSetAttribute(...); }
 #define HYB_MAX_DEVICES 64
 struct HybDevOnce {
+    std::mutex mu;
     bool done[HYB_MAX_DEVICES] = {};
-    bool first() {
-        int d = 0;
-        if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= HYB_MAX_DEVICES) return true;
-        if (done[d]) return false;
-        done[d] = true;
-        return true;
-    }
+    // `if (HybDevOnce::Guard g(once); g.first) { ... }`: the lock is held until the body has run, so a second
+    // host thread (multi.cu issues per-device work from several) cannot launch before the attributes are set
+    struct Guard {
+        std::unique_lock<std::mutex> lock;
+        bool first = true;
+        explicit Guard(HybDevOnce& o) : lock(o.mu) {
+            int d = 0;
+            if (cudaGetDevice(&d) == cudaSuccess && d >= 0 && d < HYB_MAX_DEVICES) {
+                first = !o.done[d];
+                o.done[d] = true;
+            }
+        }
+    };
 };
 // multiprocessor count of the current device (cached per device)
 static inline int hyb_num_sms() {

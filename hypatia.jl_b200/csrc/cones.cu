@@ -16,7 +16,7 @@
 
 namespace {
 
-int64_t g_cone_launches = 0;
+hyb_counter g_cone_launches{0};
 #define LAUNCHED() (++g_cone_launches)
 
 constexpr double RT2 = 1.4142135623730951;
@@ -920,7 +920,7 @@ int hybi_cones_alloc(HybCones& cs) {
     HYB_CUDA(cudaGetLastError());
     HYB_CUDA(cudaDeviceSynchronize());
     static HybDevOnce attr_once;
-    if (attr_once.first()) {
+    if (HybDevOnce::Guard g_(attr_once); g_.first) {
         HYB_CUDA(cudaFuncSetAttribute(psd_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       PSD_WARPS * 4 * PSD_MAT * (int)sizeof(double)));
         HYB_CUDA(cudaFuncSetAttribute(psd_prod_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,

@@ -16,7 +16,7 @@
 
 namespace {
 
-int64_t g_dense_launches = 0;
+hyb_counter g_dense_launches{0};
 #define DLAUNCHED() (++g_dense_launches)
 constexpr double RT2 = 1.4142135623730951;
 

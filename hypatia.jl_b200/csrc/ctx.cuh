@@ -5,7 +5,7 @@
 #include "common.cuh"
 #include "cones.cuh"
 
-extern int64_t g_misc_launches;
+extern hyb_counter g_misc_launches;
 struct HybDirs;  // device-resident direction engine (dirs.cu)
 
 // aligned staging copy of a run of rows of GQ2 / HGQ2 that starts on an odd row (api.cu: staged_rows)
@@ -49,6 +49,10 @@ struct hyb_ctx {
     int peer_world = 0, peer_rank = 0;
     HybDirs* dirs = nullptr;  // direction engine state (allocated by hyb_dirs_setup)
     std::vector<HybStageRun> stage;
+    // contexts that only assemble partial Schur matrices into another context's memory (multi.cu, rootworker.py)
+    bool want_assemble_only = false;  // request: skip the Schur matrix and the Cholesky workspace at load
+    bool assemble_only = false;
+    bool borrowed = false;            // GQ2 / HGQ2 point into another context's arrays (not freed here)
 };
 
 static inline cudaError_t h2d(hyb_ctx* c, void* dst, const void* src, size_t bytes) {
@@ -69,4 +73,7 @@ static inline void ksync(hyb_ctx* c) {
 
 
 int hyb_ensure_updated(hyb_ctx* c, double irtmu);
+int hyb_model_load_impl(hyb_ctx* c, int64_t q, int64_t N, const double* GQ2, int64_t ldg, int64_t ncones,
+                        const hyb_cone_desc* descs, hyb_ctx* borrow, int64_t borrow_row);
+int hyb_schur_assemble_into(hyb_ctx* c, double* Sdst, double* t_assemble_ms);
 void hyb_dirs_free(hyb_ctx* c);

@@ -248,9 +248,10 @@ gemm_tail_reduce_kernel(int M, int N, double alpha, double beta, double* __restr
     }
 }
 
-int64_t g_gemm_launches = 0;
+hyb_counter g_gemm_launches{0};
 struct TailWs { int dev; cudaStream_t st; double* p; };
-std::vector<TailWs> g_tail_ws;  // one workspace per (device, stream) that ever needed one (never shrinks)
+std::vector<TailWs> g_tail_ws;
+std::mutex g_tail_mutex;  // one workspace per (device, stream) that ever needed one (never shrinks)
 
 }  // namespace
 
@@ -268,7 +269,7 @@ int hyb_gemm_tn(cudaStream_t st, int64_t M, int64_t N, int64_t K, double alpha, 
         return -1;
     }
     static HybDevOnce attr_once;
-    if (attr_once.first()) {
+    if (HybDevOnce::Guard g_(attr_once); g_.first) {
         HYB_CUDA(cudaFuncSetAttribute(gemm_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     }
     CUtensorMap tmA, tmB;
@@ -301,6 +302,7 @@ int hyb_gemm_tn(cudaStream_t st, int64_t M, int64_t N, int64_t K, double alpha, 
         if (nsplit > nk_all / 32) nsplit = (int)(nk_all / 32);
         if (nsplit >= 2) {
             n_main = ntiles - r;
+            std::lock_guard<std::mutex> lock(g_tail_mutex);
             for (auto& w : g_tail_ws)
                 if (w.dev == dev && w.st == st) ws = w.p;
             if (!ws) {
@@ -345,7 +347,7 @@ int hyb_gemm_tn_blockdiag(cudaStream_t st, int64_t M, int64_t N, int64_t K, int6
         return -1;
     }
     static HybDevOnce attr_once;
-    if (attr_once.first()) {
+    if (HybDevOnce::Guard g_(attr_once); g_.first) {
         HYB_CUDA(cudaFuncSetAttribute(gemm_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     }
     CUtensorMap tmA, tmB;

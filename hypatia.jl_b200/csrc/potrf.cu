@@ -775,7 +775,7 @@ void hyb_chol_free(HybChol& ch) {
 constexpr int PANEL_SMEM = (NB * PLD + IB) * (int)sizeof(double);
 constexpr int TRSM_SMEM = TrsmCfg<TRSM_COLS>::SMEM;
 constexpr int TRSV_SMEM = (NB * LDS + NB + 5 * HYB_MAX_RHS * NB) * (int)sizeof(double);
-int64_t g_potrf_launches = 0;
+hyb_counter g_potrf_launches{0};
 
 // Right-looking factorization, two-level blocking with look-ahead.
 //  * Outer blocks of OB columns (OB = 128 * 2^k, default 256, HYB_POTRF_OB): the trailing matrix
@@ -804,7 +804,7 @@ static int potrf_outer_block() {
 // per-device attributes of the panel / slab kernels (dynamic shared memory above 48 KB)
 static int ensure_panel_attrs() {
     static HybDevOnce once;
-    if (once.first()) {
+    if (HybDevOnce::Guard g_(once); g_.first) {
         HYB_CUDA(cudaFuncSetAttribute(potf2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, PANEL_SMEM));
         HYB_CUDA(cudaFuncSetAttribute(potf2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, PANEL_SMEM));
         HYB_CUDA(cudaFuncSetAttribute(trsm_upper_T_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, TrsmCfg<64>::SMEM));
@@ -936,7 +936,7 @@ int hyb_potrf(cudaStream_t st, HybChol& ch, int* info_out) {
 template <int R>
 static int potrs_launch(cudaStream_t st, HybChol& ch, double* x, int64_t ldx) {
     static HybDevOnce attr_once;
-    if (attr_once.first()) {
+    if (HybDevOnce::Guard g_(attr_once); g_.first) {
         HYB_CUDA(cudaFuncSetAttribute(trsv_fwd_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, TRSV_SMEM));
         HYB_CUDA(cudaFuncSetAttribute(trsv_bwd_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, TRSV_SMEM));
     }

@@ -348,7 +348,7 @@ __global__ void sy_init_kernel(SyState* st, int n) {
     st->a = 0.0;
 }
 
-int64_t g_sytrf_launches = 0;
+hyb_counter g_sytrf_launches{0};
 
 }  // namespace
 

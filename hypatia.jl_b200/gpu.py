@@ -364,20 +364,67 @@ class B200QRCholSystemSolver(QRCholSystemSolver):
         pass
 
 
+class B200MultiQRCholSystemSolver(B200QRCholSystemSolver):
+    """`B200QRCholSystemSolver{Float64}(devices = 0:7)` of INTEGRATION.md: one host process, several GPUs, through
+    hyb_multi_* alone (no torch.distributed).  Only `load` and `update_lhs` differ from the single-GPU solver:
+    the cones are partitioned by block over the devices for the Schur assembly; everything else runs in the
+    root device's context."""
+
+    def __init__(self, mctx, batched_dirs: bool = True):
+        super().__init__(mctx.root, batched_dirs=batched_dirs)
+        self.mctx = mctx
+        self.time_reduce_ms = 0.0
+
+    def load(self, solver) -> None:
+        model = solver.model
+        assert model.p == 0, "B200QRCholSystemSolver expects the reduced model (p == 0, Ap_Q == I)"
+        cones = solver.cones
+        G = f64(model.G)
+        self.q, self.N = model.q, model.n
+        self.ctx.check(
+            self.lib.hyb_multi_model_load(self.mctx.ptr, model.q, model.n, dptr(G), cones.K, cones.descs), "hyb_multi_model_load"
+        )
+        cones.mark_model_loaded()
+        self.row_ranges = self.mctx.shard_rows()
+        self.setup_point_sub(solver)
+
+    def update_lhs(self, solver) -> None:
+        solver.cones._sync()
+        ta, tr, tf, kind = C.c_double(0), C.c_double(0), C.c_double(0), C.c_int(0)
+        rc = self.ctx.check(
+            self.lib.hyb_multi_schur_update(self.mctx.ptr, C.byref(ta), C.byref(tr), C.byref(tf), C.byref(kind)),
+            "hyb_multi_schur_update",
+        )
+        self.time_assemble_ms += ta.value
+        self.time_reduce_ms += tr.value
+        self.time_fact_ms += tf.value
+        self.last_assemble_ms = ta.value
+        self._after_factor(solver, tf.value, kind.value, rc)
+
+
 def make_gpu_solver(device: int = 0, dist=None, use_peer: bool = True, mode: str = "rootworker", batched_dirs: bool = True,
-                    **solver_kwargs):
+                    devices=None, **solver_kwargs):
     """Solver wired to the GPU backends (what `Hypatia.Optimizer(syssolver =
     B200QRCholSystemSolver{Float64}(), use_dense_model = true)` selects in Julia).
 
     With several ranks, `mode="rootworker"` (default) runs the algorithm on rank 0 and uses the
     other GPUs as Schur-assembly workers over peer memory (rootworker.py); `mode="replicated"`
-    runs the same host driver on every rank with sharded cone oracles (sharded.py)."""
+    runs the same host driver on every rank with sharded cone oracles (sharded.py).  ``devices=[0, 1, ...]``
+    instead drives several GPUs from THIS process through hyb_multi_* (no torch.distributed at all)."""
     from .host.solver import Solver
 
     if dist is not None and dist.get_world_size() > 1 and mode == "rootworker":
         from .rootworker import make_rootworker_solver
 
         return make_rootworker_solver(device, dist, batched_dirs=batched_dirs, **solver_kwargs)
+    if devices is not None and len(devices) > 1 or (devices is not None and mode == "single_process"):
+        from .lib import MultiContext
+
+        mctx = MultiContext(devices)
+        ss = B200MultiQRCholSystemSolver(mctx, batched_dirs=batched_dirs)
+        solver = Solver(ss.cones_factory, ss, **solver_kwargs)
+        attach_gpu_qr(solver, mctx.root)
+        return solver
     ctx = Context(device)
     if dist is not None and dist.get_world_size() > 1:
         import torch

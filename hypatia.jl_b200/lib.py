@@ -87,6 +87,13 @@ SIGNATURES = {
         C.c_int,
         [C.c_void_p, C.c_int64, c_double_p, C.c_int64, c_double_p, C.c_int64, C.c_int64, c_int_p],
     ),
+    "hyb_multi_create": (C.c_void_p, [C.c_int, c_int_p]),
+    "hyb_multi_destroy": (None, [C.c_void_p]),
+    "hyb_multi_root": (C.c_void_p, [C.c_void_p]),
+    "hyb_multi_model_load": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, c_double_p, C.c_int64, C.POINTER(ConeDesc)]),
+    "hyb_multi_shard_rows": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "hyb_multi_schur_update": (C.c_int, [C.c_void_p, c_double_p, c_double_p, c_double_p, c_int_p]),
+    "hyb_ctx_set_assemble_only": (C.c_int, [C.c_void_p, C.c_int]),
     "hyb_symm_solve": (
         C.c_int,
         [C.c_void_p, C.c_int64, c_double_p, C.c_int64, c_int_p, c_double_p, C.c_int64, C.c_int64, c_int_p],
@@ -151,7 +158,8 @@ class Context:
 
     def close(self):
         if getattr(self, "ptr", None):
-            self.lib.hyb_ctx_destroy(self.ptr)
+            if not getattr(self, "_borrowed", False):  # a MultiContext's root belongs to the hyb_multi
+                self.lib.hyb_ctx_destroy(self.ptr)
             self.ptr = None
 
     def __del__(self):
@@ -256,3 +264,42 @@ class Context:
             "hyb_posdef_solve",
         )
         return np.triu(A), (B2[:, 0] if one_d else B2), info.value
+
+
+class MultiContext:
+    """Owns one hyb_multi: several GPUs driven from this process through the C-ABI alone.  ``root`` is the
+    ordinary Context of devices[0] (the factorizing GPU)."""
+
+    def __init__(self, devices):
+        self.lib = load()
+        self.devices = [int(d) for d in devices]
+        arr = (C.c_int * len(self.devices))(*self.devices)
+        self.ptr = self.lib.hyb_multi_create(len(self.devices), arr)
+        if not self.ptr:
+            msg = self.lib.hyb_last_error(None)
+            raise HybError("hyb_multi_create failed: " + (msg.decode() if msg else "unknown error"))
+        self.root = Context.__new__(Context)
+        self.root.lib = self.lib
+        self.root.ptr = self.lib.hyb_multi_root(self.ptr)
+        self.root._borrowed = True
+
+    def check(self, rc: int, what: str) -> int:
+        return self.root.check(rc, what)
+
+    def shard_rows(self):
+        n = len(self.devices)
+        lo, hi = (C.c_int64 * n)(), (C.c_int64 * n)()
+        self.check(self.lib.hyb_multi_shard_rows(self.ptr, lo, hi), "hyb_multi_shard_rows")
+        return [(int(a), int(b)) for a, b in zip(lo, hi)]
+
+    def close(self):
+        if getattr(self, "ptr", None):
+            self.root.ptr = None
+            self.lib.hyb_multi_destroy(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -39,6 +39,8 @@ class ShardEngine:
     def __init__(self, device: int, atoms):
         self.ctx = Context(device)
         self.lib = self.ctx.lib
+        # a shard only assembles into the root's memory: no Schur matrix / Cholesky workspace of its own
+        self.ctx.check(self.lib.hyb_ctx_set_assemble_only(self.ctx.ptr, 1), "hyb_ctx_set_assemble_only")
         self.cones = GpuConeBatch(atoms, self.ctx)
         self.q = self.cones.q
 

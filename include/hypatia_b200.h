@@ -199,6 +199,30 @@ int hyb_symm_solve(hyb_ctx* ctx, int64_t N, double* A, int64_t lda, int* ipiv, d
  * overwrite, and the tests use it to drive posdef_fact_copy!'s fallback chain with an indefinite matrix. */
 int hyb_schur_set(hyb_ctx* ctx, const double* lhs);
 
+/* ---- several GPUs from one host process ----------------------------------------------
+ * a Julia host uses a whole node with ccalls alone.  The cones are partitioned by block over the
+ * devices; each device assembles the partial Schur matrix of its cones (update_lhs_fact, qrchol.jl:209-254, is
+ * a sum over cones) and its syrk epilogue stores the tiles into the FIRST device's memory over NVLink (peer
+ * access); that device adds the partials in device order, factorizes (posdef_fact_copy!, qrchol.jl:257-258) and
+ * serves everything else.  devices[0] is the factorizing GPU.  hyb_multi_root() is its ordinary context: load
+ * points, run oracles, directions and the line search through it exactly as on one GPU, and call
+ * hyb_multi_schur_update where a single GPU calls hyb_schur_update. */
+typedef struct hyb_multi hyb_multi;
+hyb_multi* hyb_multi_create(int ndev, const int* devices);
+void hyb_multi_destroy(hyb_multi* m);
+hyb_ctx* hyb_multi_root(hyb_multi* m);
+/* Solvers.load(syssolver, solver), qrchol.jl:145-187: the full model on the root plus every device's row range
+ * (Nonnegative cones are cut at the range boundaries so that LPs shard too) */
+int hyb_multi_model_load(hyb_multi* m, int64_t q, int64_t N, const double* GQ2, int64_t ncones, const hyb_cone_desc* descs);
+/* rows [row_lo[d], row_hi[d]) of s / z owned by device d (arrays of ndev entries) */
+int hyb_multi_shard_rows(hyb_multi* m, int64_t* row_lo, int64_t* row_hi);
+/* update_lhs_fact (qrchol.jl:209-265) for the point loaded in the root context: t_assemble_ms = slowest device's
+ * assembly, t_reduce_ms = the fixed-order sum of the partials, then as hyb_schur_factor */
+int hyb_multi_schur_update(hyb_multi* m, double* t_assemble_ms, double* t_reduce_ms, double* t_fact_ms, int* fact_kind);
+/* A context that will only ever assemble partial Schur matrices into another context's memory
+ * (hyb_schur_assemble_peer) can skip its own Schur matrix and Cholesky workspace: set before hyb_model_load. */
+int hyb_ctx_set_assemble_only(hyb_ctx* ctx, int flag);
+
 /* ---- allocation-free product (no counterpart in the reference) -----------------------
  * y = G x on DEVICE pointers owned by the caller (column-major G, q x N, leading dimension
  * ld >= q; all on the current device), launched on `stream` (a cudaStream_t, NULL for the

@@ -17,8 +17,11 @@ builders = {
     "cfg3s": lambda: instances.polymin(n=2, halfdeg=12, seed=1),
     "cfg4": lambda: instances.portfolio_socs(K=100_000, d=4, n=2048, seed=1),
     "cfg4s": lambda: instances.portfolio_socs(K=20_000, d=4, n=512, seed=1),
+    "cfg4n": lambda: instances.portfolio_norminf(K=100_000, d=4, n=2048, seed=1),
+    "cfg4ns": lambda: instances.portfolio_norminf(K=20_000, d=4, n=512, seed=1),
 }
-kw = dict(tol_rel_opt=1e-6, tol_feas=1e-6, tol_abs_opt=1e-8) if name.startswith("cfg4") else {}
+# cfg4: the reference's benchmark tolerances (benchmarks/natvsext/run.jl:44-60)
+kw = dict(tol_rel_opt=1e-7, tol_feas=1e-7, tol_abs_opt=1e-10, tol_infeas=1e-10) if name.startswith("cfg4") else {}
 t0 = time.time(); model = builders[name](); tb = time.time() - t0
 gpu = make_gpu_solver(0, trace=True, **kw)
 gpu.load(model)
