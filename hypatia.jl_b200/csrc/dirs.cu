@@ -13,35 +13,7 @@
 // Vector layout at the boundary (point.jl:31-62 with p == 0): [x(N); z(q); tau; s(q); kap].
 #include <cstdlib>
 
-#include "ctx.cuh"
-
-struct HybVecs {  // one set of m <= HYB_MAX_RHS "points" on the device
-    double *x = nullptr, *z = nullptr, *s = nullptr, *tk = nullptr;  // x: ldn x M, z/s: ldq x M, tk: 2 x M (tau, kap)
-};
-
-struct HybDirs {
-    int64_t N = 0, q = 0, ldn = 0, ldq = 0;
-    double *c = nullptr, *h = nullptr;
-    unsigned char* dual_row = nullptr;  // 1 where the row belongs to a dual-barrier cone
-    HybVecs rhs, dir, res, tmp, rrhs, rdir;  // rrhs / rdir: single-column scratch of the refinement rounds
-    double *A = nullptr, *B = nullptr, *Vx = nullptr, *Vz = nullptr, *Gx = nullptr, *T = nullptr;  // work, M columns
-    double *xc = nullptr, *zc = nullptr;  // sol_const (common.jl:191-209)
-    double* scal = nullptr;     // device scalars: [0] = dot_obj(sol_const), [1 + j] = dot_obj(sol_sub_j), [8 + j] = norms
-    double* gemm_scratch = nullptr;
-    bool have_const = false;
-    // device-resident line search (search.jl:72-162): the current point, the four directions of the
-    // iteration (slots: 0 cent, 1 centadj, 2 pred, 3 predadj), per-cone data
-    double *pz = nullptr, *ps = nullptr;       // point.z, point.s
-    double *kz = nullptr, *ks = nullptr;       // kept directions: ldq x 4 each
-    double* szk = nullptr;                     // K : <s_k, z_k> of the candidate
-    double* nus = nullptr;                     // K : barrier parameters
-    int64_t *cone_off = nullptr;               // K : first row of every cone
-    int* cone_dim = nullptr;                   // K
-    double* sred = nullptr;                    // [0] min szk, [1] sum szk ; int flag in sflag
-    int* sflag = nullptr;
-    int64_t K = 0;
-    bool search_ready = false;
-};
+#include "dirs.cuh"
 
 namespace {
 
@@ -304,6 +276,11 @@ void hyb_dirs_free(hyb_ctx* c) {
     cudaFree(d->scal);
     cudaFree(d->gemm_scratch);
     cudaFree(d->pz);
+    cudaFree(d->px);
+    cudaFree(d->kx);
+    cudaFree(d->resx);
+    cudaFree(d->resz);
+    cudaFree(d->sout);
     cudaFree(d->ps);
     cudaFree(d->kz);
     cudaFree(d->ks);
@@ -426,6 +403,68 @@ static int copy_vecs(hyb_ctx* c, const HybDirs& d, const HybVecs& dst, const Hyb
     return 0;
 }
 
+// get_directions (common.jl:22-83) on the m right-hand sides in d.rhs; the directions end up in d.dir
+int hyb_directions_core(hyb_ctx* c, int m, bool refresh_const, double mu_tt, double res_norm_cutoff, int max_ref_steps,
+                        double min_impr_tol, int* num_ref, double* res_norm) {
+    HybDirs& d = *c->dirs;
+    cudaStream_t st = c->st;
+    const int64_t N = d.N, q = d.q;
+    HYB_CHECK(solve_system_dev(c, d, m, refresh_const, d.rhs, d.dir, mu_tt));
+    static const bool dbg = getenv("HYB_DEBUG_DIRS") != nullptr;
+    double norms[HYB_MAX_RHS] = {0, 0, 0, 0};
+    for (int j = 0; j < m; ++j) {
+        if (num_ref) num_ref[j] = 0;
+        if (res_norm) res_norm[j] = 0.0;
+    }
+    if (max_ref_steps > 0 && m > 0) {
+        HYB_CHECK(residual_dev(c, d, m, d.dir, d.rhs, d.res, mu_tt, d.scal + 8, true));
+        HYB_CUDA(cudaMemcpyAsync(norms, d.scal + 8, sizeof(double) * m, cudaMemcpyDeviceToHost, st));
+        HYB_CUDA(cudaStreamSynchronize(st));
+        for (int j = 0; j < m; ++j) {
+            double rn = norms[j];
+            int nref = 0;
+            if (dbg) fprintf(stderr, "  dirs: col %d res_norm %.3e cutoff %.3e\n", j, rn, res_norm_cutoff);
+            if (rn > res_norm_cutoff) {  // iterative refinement of column j (common.jl:46-79)
+                const HybVecs dj = column(d.dir, d, j), rj = column(d.rhs, d, j), ej = column(d.res, d, j);
+                HYB_CHECK(copy_vecs(c, d, d.tmp, dj));
+                bool prev_slow = false;
+                double prev = rn;
+                for (int it = 0; it < max_ref_steps; ++it) {
+                    ++nref;
+                    HYB_CHECK(copy_vecs(c, d, d.rrhs, ej));
+                    HYB_CHECK(solve_system_dev(c, d, 1, false, d.rrhs, d.rdir, mu_tt));
+                    const int64_t nq = N > q ? N : q;
+                    refine_combine_kernel<<<(unsigned)(((nq > 2 ? nq : 2) + 255) / 256), 256, 0, st>>>(
+                        N, q, d.tmp.x, d.tmp.z, d.tmp.s, d.tmp.tk, d.rdir.x, d.rdir.z, d.rdir.s, d.rdir.tk);
+                    HYB_CUDA(cudaGetLastError());
+                    ++g_misc_launches;
+                    HYB_CHECK(residual_dev(c, d, 1, d.rdir, rj, ej, mu_tt, d.scal + 12, false));
+                    double rn_new = 0.0;
+                    HYB_CUDA(cudaMemcpyAsync(&rn_new, d.scal + 12, sizeof(double), cudaMemcpyDeviceToHost, st));
+                    HYB_CUDA(cudaStreamSynchronize(st));
+                    if (dbg) fprintf(stderr, "    refine: %.3e -> %.3e\n", rn, rn_new);
+                    if (rn_new != rn_new) {  // NaN: reported, the caller asserts like common.jl:81
+                        rn = rn_new;
+                        break;
+                    }
+                    if (rn_new >= rn) break;  // worse: keep the previous direction (still in column j)
+                    HYB_CHECK(copy_vecs(c, d, dj, d.rdir));
+                    HYB_CHECK(copy_vecs(c, d, d.tmp, d.rdir));
+                    rn = rn_new;
+                    if (rn < res_norm_cutoff) break;
+                    const bool curr_slow = rn > min_impr_tol * prev;
+                    if (prev_slow && curr_slow) break;
+                    prev = rn;
+                    prev_slow = curr_slow;
+                }
+            }
+            if (num_ref) num_ref[j] = nref;
+            if (res_norm) res_norm[j] = rn;
+        }
+    }
+    return 0;
+}
+
 extern "C" {
 
 int hyb_dirs_setup(hyb_ctx* c, const double* cvec, const double* hvec) {
@@ -474,6 +513,13 @@ int hyb_dirs_setup(hyb_ctx* c, const double* cvec, const double* hvec) {
     const int64_t Ka = K > 0 ? K : 1;
     HYB_CUDA(cudaMalloc(&d->pz, sizeof(double) * d->ldq));
     HYB_CUDA(cudaMalloc(&d->ps, sizeof(double) * d->ldq));
+    HYB_CUDA(cudaMalloc(&d->px, sizeof(double) * d->ldn));
+    HYB_CUDA(cudaMalloc(&d->kx, sizeof(double) * d->ldn * 4));
+    HYB_CUDA(cudaMalloc(&d->resx, sizeof(double) * d->ldn));
+    HYB_CUDA(cudaMalloc(&d->resz, sizeof(double) * d->ldq));
+    HYB_CUDA(cudaMalloc(&d->sout, sizeof(double) * 8));
+    HYB_CUDA(cudaMemset(d->px, 0, sizeof(double) * d->ldn));
+    HYB_CUDA(cudaMemset(d->kx, 0, sizeof(double) * d->ldn * 4));
     HYB_CUDA(cudaMalloc(&d->kz, sizeof(double) * d->ldq * 4));
     HYB_CUDA(cudaMalloc(&d->ks, sizeof(double) * d->ldq * 4));
     HYB_CUDA(cudaMemset(d->kz, 0, sizeof(double) * d->ldq * 4));
@@ -539,59 +585,7 @@ int hyb_get_directions(hyb_ctx* c, int nrhs, const double* rhs, double* dir, int
     HYB_CUDA(up(d.rhs.tk + 1, 2, N + 2 * q + 1, 1));
     const double mu_tt = mu / tau_bar / tau_bar;
     KBEGIN(c);
-    HYB_CHECK(solve_system_dev(c, d, m, refresh_const != 0, d.rhs, d.dir, mu_tt));
-    static const bool dbg = getenv("HYB_DEBUG_DIRS") != nullptr;
-    double norms[HYB_MAX_RHS] = {0, 0, 0, 0};
-    for (int j = 0; j < m; ++j) {
-        if (num_ref) num_ref[j] = 0;
-        if (res_norm) res_norm[j] = 0.0;
-    }
-    if (max_ref_steps > 0 && m > 0) {
-        HYB_CHECK(residual_dev(c, d, m, d.dir, d.rhs, d.res, mu_tt, d.scal + 8, true));
-        HYB_CUDA(cudaMemcpyAsync(norms, d.scal + 8, sizeof(double) * m, cudaMemcpyDeviceToHost, st));
-        HYB_CUDA(cudaStreamSynchronize(st));
-        for (int j = 0; j < m; ++j) {
-            double rn = norms[j];
-            int nref = 0;
-            if (dbg) fprintf(stderr, "  dirs: col %d res_norm %.3e cutoff %.3e\n", j, rn, res_norm_cutoff);
-            if (rn > res_norm_cutoff) {  // iterative refinement of column j (common.jl:46-79)
-                const HybVecs dj = column(d.dir, d, j), rj = column(d.rhs, d, j), ej = column(d.res, d, j);
-                HYB_CHECK(copy_vecs(c, d, d.tmp, dj));
-                bool prev_slow = false;
-                double prev = rn;
-                for (int it = 0; it < max_ref_steps; ++it) {
-                    ++nref;
-                    HYB_CHECK(copy_vecs(c, d, d.rrhs, ej));
-                    HYB_CHECK(solve_system_dev(c, d, 1, false, d.rrhs, d.rdir, mu_tt));
-                    const int64_t nq = N > q ? N : q;
-                    refine_combine_kernel<<<(unsigned)(((nq > 2 ? nq : 2) + 255) / 256), 256, 0, st>>>(
-                        N, q, d.tmp.x, d.tmp.z, d.tmp.s, d.tmp.tk, d.rdir.x, d.rdir.z, d.rdir.s, d.rdir.tk);
-                    HYB_CUDA(cudaGetLastError());
-                    ++g_misc_launches;
-                    HYB_CHECK(residual_dev(c, d, 1, d.rdir, rj, ej, mu_tt, d.scal + 12, false));
-                    double rn_new = 0.0;
-                    HYB_CUDA(cudaMemcpyAsync(&rn_new, d.scal + 12, sizeof(double), cudaMemcpyDeviceToHost, st));
-                    HYB_CUDA(cudaStreamSynchronize(st));
-                    if (dbg) fprintf(stderr, "    refine: %.3e -> %.3e\n", rn, rn_new);
-                    if (rn_new != rn_new) {  // NaN: reported, the caller asserts like common.jl:81
-                        rn = rn_new;
-                        break;
-                    }
-                    if (rn_new >= rn) break;  // worse: keep the previous direction (still in column j)
-                    HYB_CHECK(copy_vecs(c, d, dj, d.rdir));
-                    HYB_CHECK(copy_vecs(c, d, d.tmp, d.rdir));
-                    rn = rn_new;
-                    if (rn < res_norm_cutoff) break;
-                    const bool curr_slow = rn > min_impr_tol * prev;
-                    if (prev_slow && curr_slow) break;
-                    prev = rn;
-                    prev_slow = curr_slow;
-                }
-            }
-            if (num_ref) num_ref[j] = nref;
-            if (res_norm) res_norm[j] = rn;
-        }
-    }
+    HYB_CHECK(hyb_directions_core(c, m, refresh_const != 0, mu_tt, res_norm_cutoff, max_ref_steps, min_impr_tol, num_ref, res_norm));
     KEND(c);
     HYB_CUDA(down(d.dir.x, d.ldn, 0, N));
     HYB_CUDA(down(d.dir.z, d.ldq, N, q));
@@ -746,6 +740,9 @@ int hyb_dirs_keep(hyb_ctx* c, int col, int slot) {
         return -3;
     }
     HYB_CUDA(cudaSetDevice(c->device));
+    if (d.N > 0)
+        HYB_CUDA(cudaMemcpyAsync(d.kx + (int64_t)slot * d.ldn, d.dir.x + (int64_t)col * d.ldn, sizeof(double) * d.N,
+                                 cudaMemcpyDeviceToDevice, c->st));
     if (d.q > 0) {
         HYB_CUDA(cudaMemcpyAsync(d.kz + (int64_t)slot * d.ldq, d.dir.z + (int64_t)col * d.ldq, sizeof(double) * d.q,
                                  cudaMemcpyDeviceToDevice, c->st));

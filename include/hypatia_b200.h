@@ -168,6 +168,32 @@ int hyb_search_gates(hyb_ctx* ctx, const double* coef, double* min_szk, double* 
 int hyb_search_check(hyb_ctx* ctx, double mu, double min_prox, double proxsqr_bound, int use_max_prox, double agg0,
                      int* ok, double* agg);
 
+/* ---- device-resident stepper: src/Solvers/Solvers.jl, steppers/common.jl, steppers/combined.jl ----
+ * The iterate's x (N), z (q), s (q) stay on the device for the whole solve; tau, kap, mu stay with the caller.
+ * With these and the line search above an iteration moves only scalars across PCIe.  Needs hyb_dirs_setup. */
+/* the iterate after initialize_point (Solvers.jl:499-516) / for postprocess (process.jl:415-469; NULL = skip) */
+int hyb_step_point_set(hyb_ctx* ctx, const double* x, const double* z, const double* s);
+int hyb_step_point_get(hyb_ctx* ctx, double* x, double* z, double* s);
+/* calc_convergence_params (Solvers.jl:631-693, reduced model p = 0) at the device iterate and the caller's tau.
+ * Keeps x_residual = -(G'z + c tau) and z_residual = G x + s - h tau on the device (update_rhs_pred uses them).
+ * out7 = { |G'z|_inf, |G'z + c tau|_inf, |G x + s|_inf, |G x + s - h tau|_inf, c'x, h'z, z's }. */
+int hyb_step_convergence(hyb_ctx* ctx, double tau, double* out7);
+/* Right-hand side builders of steppers/common.jl into column `col` (0..3) of the direction engine:
+ * kind 0 update_rhs_cent (:66-83), 1 update_rhs_centadj (:86-119), 2 update_rhs_pred (:14-28),
+ * 3 update_rhs_predadj (:30-63).  mu, tau, kap: solver.mu, point.tau, point.kap; tau_residual (pred only):
+ * solver.tau_residual; dir_tau (adjustments only): the tau entry of the kept unadjusted direction (slot 0 for
+ * centadj, slot 2 for predadj, see hyb_dirs_keep), whose z / s parts are read on the device.  The adjustments
+ * apply the reference's per-cone identity gate |<dder3, s> - <d, H d>| / (sqrt(eps) + |.|) < 1e-4. */
+int hyb_step_rhs(hyb_ctx* ctx, int kind, int col, double mu, double tau, double kap, double tau_residual, double dir_tau);
+/* hyb_get_directions on the right-hand sides built by hyb_step_rhs in columns 0..nrhs-1; the directions stay on
+ * the device (keep them with hyb_dirs_keep); dir_taukap receives their (tau, kap) entries, 2 per column. */
+int hyb_step_directions(hyb_ctx* ctx, int nrhs, int refresh_const, double tau_bar, double mu, double res_norm_cutoff,
+                        int max_ref_steps, double min_impr_tol, int* num_ref, double* res_norm, double* dir_taukap);
+/* update_stepper_points(alpha, point, false) (combined.jl:129-177) on x, z, s:
+ * point += coef[0] cent + coef[1] centadj + coef[2] pred + coef[3] predadj (the kept directions);
+ * *zs = <z, s> of the new iterate (calc_mu, Solvers.jl:625-629). */
+int hyb_step_point_update(hyb_ctx* ctx, const double* coef, double* zs);
+
 /* ---- preprocessing: src/Solvers/process.jl ------------------------------------------ */
 /* qr!(M, ColumnNorm()) = LAPACK.geqp3!, process.jl:109 ([A; G], handle_dual_eq) and :233 (A',
  * handle_primal_eq): column-pivoted Householder QR of the m x n host matrix A (lda), in place, with
