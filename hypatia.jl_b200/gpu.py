@@ -100,6 +100,14 @@ class GpuConeBatch(ConeSet):
     def reset_data(self):
         self._dirty = True
 
+    def note_device_resident(self, scal):
+        """Device-resident stepper: the device holds the accepted candidate and the host keeps no copy."""
+        self._pending_primal = None
+        self._pending_scal = float(scal)
+        self._point = None
+        self._grad = None
+        self._dirty = False
+
     def note_device_point(self, primal, dual, scal):
         """The device already holds this point (loaded by hyb_search_check from a candidate it formed
         itself): bring the host mirror up to date without pushing anything."""
@@ -196,6 +204,9 @@ class B200QRCholSystemSolver(QRCholSystemSolver):
         import os
 
         self.device_search = bool(batched_dirs) and not os.environ.get("HYB_HOST_SEARCH")
+        # the whole stepper inner loop on the device (hyb_step_*): the iterate never leaves the GPU between
+        # initialize_point and postprocess.  HYB_HOST_STEPPER=1 keeps the host-vector protocol above.
+        self.device_stepper = self.device_search and not os.environ.get("HYB_HOST_STEPPER")
         self._dev_const_stale = True
         self._host_const_stale = True
         self.time_assemble_ms = 0.0
@@ -283,6 +294,64 @@ class B200QRCholSystemSolver(QRCholSystemSolver):
             "hyb_search_check",
         )
         return bool(ok.value), float(agg.value)
+
+    # ---- device-resident stepper (hyb_step_*): steppers/common.jl, combined.jl, Solvers.jl:631-693 ------
+    def step_point_set(self, point) -> None:
+        x, z, s_ = f64(point.x), f64(point.z), f64(point.s)
+        self.ctx.check(self.lib.hyb_step_point_set(self.ctx.ptr, dptr(x), dptr(z), dptr(s_)), "hyb_step_point_set")
+
+    def step_point_get(self, point) -> None:
+        x, z, s_ = np.empty(self.N), np.empty(self.q), np.empty(self.q)
+        self.ctx.check(self.lib.hyb_step_point_get(self.ctx.ptr, dptr(x), dptr(z), dptr(s_)), "hyb_step_point_get")
+        point.x[:] = x
+        point.z[:] = z
+        point.s[:] = s_
+
+    def step_convergence(self, tau: float):
+        out = (C.c_double * 7)()
+        self.ctx.check(self.lib.hyb_step_convergence(self.ctx.ptr, float(tau), out), "hyb_step_convergence")
+        return [float(v) for v in out]
+
+    def step_rhs(self, kind: int, col: int, solver, dir_tau: float = 0.0) -> None:
+        pt = solver.point
+        self.ctx.check(
+            self.lib.hyb_step_rhs(self.ctx.ptr, int(kind), int(col), float(solver.mu), float(pt.tau), float(pt.kap),
+                                  float(solver.tau_residual), float(dir_tau)),
+            "hyb_step_rhs",
+        )
+
+    def step_directions(self, stepper, solver, m: int):
+        """get_directions on the m right-hand sides built by step_rhs; returns [(tau, kap)] of the directions."""
+        import math
+
+        solver.cones._sync()
+        nref = (C.c_int * m)()
+        rn = (C.c_double * m)()
+        tk = (C.c_double * (2 * m))()
+        self.ctx.check(
+            self.lib.hyb_step_directions(
+                self.ctx.ptr, m, int(self._dev_const_stale), float(solver.point.tau), float(solver.mu),
+                float(solver.res_norm_cutoff), int(solver.max_ref_steps), 0.5, nref, rn, tk,
+            ),
+            "hyb_step_directions",
+        )
+        self._dev_const_stale = False
+        self.last_res_norms = [float(v) for v in rn]
+        self.last_num_refs = [int(v) for v in nref]
+        for j in range(m):
+            stepper.last_num_ref += int(nref[j])
+            assert not math.isnan(rn[j]), "NaN residual in direction solve"
+            solver.worst_dir_res = max(solver.worst_dir_res, float(rn[j]))
+        return [(float(tk[2 * j]), float(tk[2 * j + 1])) for j in range(m)]
+
+    def dirs_keep(self, col: int, slot: int) -> None:
+        self.ctx.check(self.lib.hyb_dirs_keep(self.ctx.ptr, int(col), int(slot)), "hyb_dirs_keep")
+
+    def step_point_update(self, coefs) -> float:
+        cf = (C.c_double * 4)(*coefs)
+        zs = C.c_double(0)
+        self.ctx.check(self.lib.hyb_step_point_update(self.ctx.ptr, cf, C.byref(zs)), "hyb_step_point_update")
+        return zs.value
 
     def get_directions_batch(self, stepper, solver, rhs_points, dir_points, slots=None) -> None:
         import math

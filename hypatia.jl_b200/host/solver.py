@@ -515,6 +515,13 @@ class Solver:
         cones = self.cones
         cones.load_point(cones.primal_of(point.z, point.s))
         cones.load_dual_point(cones.dual_of(point.z, point.s))
+        # device-resident stepper (gpu.py, hyb_step_*): from here to postprocess the iterate's x, z, s live on
+        # the device; the host keeps tau, kap, mu
+        self.device_stepper = bool(getattr(self.syssolver, "device_stepper", False)) and cones.K > 0
+        if self.device_stepper:
+            cones._sync()
+            self.syssolver.step_point_set(point)
+            self._zs_dev = float(point.z @ point.s)
 
     def _setup_stepping(self) -> None:  # Solvers.jl:518-527
         model = self.model
@@ -527,7 +534,8 @@ class Solver:
 
     def calc_mu(self) -> float:  # Solvers.jl:625-629
         point = self.point
-        self.mu = (float(point.z @ point.s) + point.tau * point.kap) / (self.model.nu + 1.0)
+        zs = self._zs_dev if getattr(self, "device_stepper", False) else float(point.z @ point.s)
+        self.mu = (zs + point.tau * point.kap) / (self.model.nu + 1.0)
         return self.mu
 
     def _step_and_check(self) -> bool:  # Solvers.jl:566-623
@@ -572,6 +580,8 @@ class Solver:
     def _calc_convergence_params(self) -> float:  # Solvers.jl:631-693
         model, point = self.model, self.point
         tau = point.tau
+        if getattr(self, "device_stepper", False):
+            return self._calc_convergence_params_device()
         xr = self.Gt_mul(point.z)
         if model.p:
             xr = xr + model.A.T @ point.y
@@ -611,6 +621,36 @@ class Solver:
         self.gap = float(point.z @ point.s)
         return improv
 
+    def _calc_convergence_params_device(self) -> float:
+        """Solvers.jl:631-693 with the O(qN) and O(q) work on the device (hyb_step_convergence); the residual
+        vectors stay there as the prediction right-hand side.  Reduced model: p = 0."""
+        model, point = self.model, self.point
+        tau = point.tau
+        o = self.syssolver.step_convergence(tau)
+        self.x_norm_res_t = o[0]
+        self.x_norm_res = o[1] / tau
+        x_feas = self.x_norm_res * self.x_conv_tol
+        self.y_norm_res_t = self.y_norm_res = 0.0
+        y_feas = 0.0
+        self.z_norm_res_t = o[2]
+        self.z_norm_res = o[3] / tau
+        z_feas = self.z_norm_res * self.z_conv_tol
+        self.primal_obj_t = o[4]
+        self.dual_obj_t = -o[5]
+        self.tau_residual = self.primal_obj_t - self.dual_obj_t + point.kap
+        tau_feas = abs(self.tau_residual)
+        improv = 0.0
+        for curr, prev in ((x_feas, self.x_feas), (y_feas, self.y_feas), (z_feas, self.z_feas), (tau_feas, self.tau_feas)):
+            if math.isnan(prev) or math.isnan(curr):
+                continue
+            improv = max(improv, (prev - curr) / (abs(prev) + EPS))
+        self.x_feas, self.y_feas, self.z_feas, self.tau_feas = x_feas, y_feas, z_feas, tau_feas
+        self.primal_obj = self.primal_obj_t / tau + model.obj_offset
+        self.dual_obj = self.dual_obj_t / tau + model.obj_offset
+        self.gap = o[6]
+        self._zs_dev = o[6]
+        return improv
+
     def _check_converged(self, check_near: bool = False) -> bool:  # Solvers.jl:696-747
         nf = self.near_factor if check_near else 1.0
         tau = self.point.tau
@@ -643,6 +683,9 @@ class Solver:
     # ------------------------------------------------------------------ postprocess
     def _postprocess(self) -> None:  # process.jl:415-505
         point, result = self.point, self.result
+        if getattr(self, "device_stepper", False):
+            self.syssolver.step_point_get(point)  # the iterate comes back from the device once
+            self.device_stepper = False
         tau = point.tau
         if tau <= 0 or np.any(np.isnan(point.vec)):
             result.vec[:] = math.nan

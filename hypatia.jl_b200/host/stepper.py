@@ -72,7 +72,32 @@ class CombinedStepper:
         solver.syssolver.update_lhs(solver)
         solver.time_upsys += time.time() - t0
 
-        if getattr(solver.syssolver, "batched_dirs", False):
+        dev = bool(getattr(solver, "device_stepper", False))
+        if dev:
+            # Device-resident stepper (hyb_step_*): right-hand sides are built on the device from the device
+            # iterate, the directions stay there; the host sees their (tau, kap) entries only.
+            ss = solver.syssolver
+            t0 = time.time()
+            ss.step_rhs(0, 0, solver)  # cent
+            ss.step_rhs(2, 1, solver)  # pred
+            solver.time_uprhs += time.time() - t0
+            t0 = time.time()
+            (self.dir_cent.tau, self.dir_cent.kap), (self.dir_pred.tau, self.dir_pred.kap) = ss.step_directions(self, solver, 2)
+            ss.dirs_keep(0, 0)
+            ss.dirs_keep(1, 2)
+            solver.time_getdir += time.time() - t0
+            t0 = time.time()
+            ss.step_rhs(1, 0, solver, self.dir_cent.tau)  # centadj
+            ss.step_rhs(3, 1, solver, self.dir_pred.tau)  # predadj
+            solver.time_uprhs += time.time() - t0
+            t0 = time.time()
+            (self.dir_centadj.tau, self.dir_centadj.kap), (self.dir_predadj.tau, self.dir_predadj.kap) = ss.step_directions(
+                self, solver, 2)
+            ss.dirs_keep(0, 1)
+            ss.dirs_keep(1, 3)
+            solver.time_getdir += time.time() - t0
+            builders = ()
+        elif getattr(solver.syssolver, "batched_dirs", False):
             # Device-resident direction solves: the two unadjusted directions are independent of
             # each other, and each adjustment needs only its own unadjusted direction
             # (combined.jl:74-95), so the four solves run as two batched pairs.
@@ -116,7 +141,8 @@ class CombinedStepper:
         self.unadj_only = self.cent_only = False
         t0 = time.time()
         self._device_search = bool(getattr(solver.syssolver, "device_search", False)) and solver.cones.K > 0
-        if self._device_search:
+        self._device_stepper = dev
+        if self._device_search and not dev:
             solver.syssolver.search_load_point(point)
         alpha = self.search_alpha(point, solver)
         if alpha == 0.0:
@@ -136,7 +162,14 @@ class CombinedStepper:
                         solver.time_search += time.time() - t0
                         return False
         solver.time_search += time.time() - t0
-        self.update_stepper_points(alpha, point, False)
+        if dev:
+            cf = self._coefs(alpha)
+            dtau, dkap = self._combine_taukap(cf)
+            solver._zs_dev = solver.syssolver.step_point_update(cf)
+            point.tau += dtau
+            point.kap += dkap
+        else:
+            self.update_stepper_points(alpha, point, False)
         self.prev_alpha = alpha
         return True
 
@@ -187,7 +220,7 @@ class CombinedStepper:
                 return alpha
             sched += 1
         searcher.prev_sched = sched
-        if getattr(self, "_device_search", False):
+        if getattr(self, "_device_search", False) and not getattr(self, "_device_stepper", False):
             solver.cones.reset_data()  # the device holds a rejected candidate: reload on next use
         return 0.0
 
@@ -199,6 +232,16 @@ class CombinedStepper:
             return (alpha, alpha * alpha, 0.0, 0.0)
         am1 = 1 - alpha
         return (am1, am1 * am1, alpha, alpha * alpha)
+
+    def _combine_taukap(self, cf):
+        """(d tau, d kap) of update_stepper_points for coefficients cf, same left-to-right sum (combined.jl:146-173)."""
+        dirs = (self.dir_cent, self.dir_centadj, self.dir_pred, self.dir_predadj)
+        dtau = dkap = None
+        for k in (2, 3, 0, 1):
+            if cf[k] != 0.0:
+                dtau = cf[k] * dirs[k].tau if dtau is None else dtau + cf[k] * dirs[k].tau
+                dkap = cf[k] * dirs[k].kap if dkap is None else dkap + cf[k] * dirs[k].kap
+        return (dtau or 0.0), (dkap or 0.0)
 
     # ---- search.jl:100-162 with the O(q) work on the device (hyb_search_gates / hyb_search_check) ----
     def check_cone_points_device(self, solver, point: Point, alpha: float) -> bool:
@@ -233,6 +276,9 @@ class CombinedStepper:
         if not ok:
             return False
         searcher.prox = math.sqrt(agg)
+        if getattr(self, "_device_stepper", False):
+            cones.note_device_resident(1.0 / math.sqrt(mu))
+            return True
         # accepted: the device holds the candidate; refresh the host mirror of the cone batch once
         self.update_stepper_points(alpha, point, True)
         cand = self.temp

@@ -154,6 +154,7 @@ class RootQRCholSystemSolver(RootAssembly, B200QRCholSystemSolver):
 
     def __init__(self, ctx: Context, comm: Comm, device: int, batched_dirs: bool = True):
         B200QRCholSystemSolver.__init__(self, ctx, batched_dirs=batched_dirs)
+        self.device_stepper = False  # the accepted point is broadcast to the workers from host memory
         self._rw_init(comm)
         self.device = device
 

@@ -151,3 +151,28 @@ def test_device_line_search_matches_host_loop(name, monkeypatch):
     assert [r["n_cand"] for r in dev.trace[:n]] == [r["n_cand"] for r in host.trace[:n]]
     assert np.allclose([r["mu"] for r in dev.trace[:n]], [r["mu"] for r in host.trace[:n]], rtol=1e-9)
     assert np.allclose([r["prox"] for r in dev.trace[:n]], [r["prox"] for r in host.trace[:n]], rtol=1e-6, atol=1e-12)
+
+
+@pytest.mark.parametrize("name", list(MODELS))
+def test_device_resident_stepper_matches_host_vector_protocol(name, monkeypatch):
+    """hyb_step_* (iterate, right-hand-side builders, point update on the device) against the same solve with
+    the host building the right-hand sides and holding the iterate (steppers/common.jl:14-119, combined.jl:129-177)."""
+    dev = make_gpu_solver(0, trace=True)
+    assert dev.syssolver.device_stepper
+    monkeypatch.setenv("HYB_HOST_STEPPER", "1")
+    host = make_gpu_solver(0, trace=True)
+    assert not host.syssolver.device_stepper and host.syssolver.device_search
+    for s in (dev, host):
+        s.load(MODELS[name]())
+        s.solve()
+    assert dev.status == host.status
+    assert abs(dev.num_iters - host.num_iters) <= 1
+    if host.status == "Optimal":
+        assert abs(dev.primal_obj - host.primal_obj) <= 1e-7 * (1 + abs(host.primal_obj))
+        assert np.abs(dev.get_x() - host.get_x()).max() <= 1e-6 * (1 + np.abs(host.get_x()).max())
+    n = max(3, min(len(dev.trace), len(host.trace)) // 2)
+    assert [r["alpha"] for r in dev.trace[:n]] == [r["alpha"] for r in host.trace[:n]]
+    for key in ("mu", "x_norm_res", "z_norm_res", "gap", "tau", "kap"):
+        a = np.array([r[key] for r in dev.trace[:n]])
+        b = np.array([r[key] for r in host.trace[:n]])
+        assert np.all(np.abs(a - b) <= 1e-8 * np.maximum(np.abs(b), 1e-5)), key
