@@ -874,8 +874,17 @@ int hyb_potrf(cudaStream_t st, HybChol& ch, int* info_out) {
     };
     stamp(st);
     HYB_CUDA(cudaEventRecord(ch.ev_head, st));
-    for (int64_t K0 = 0; K0 < N; K0 += OB) {
-        const int64_t ob = (N - K0 < OB) ? (N - K0) : OB;
+    // Once the trailing matrix is small the bulk update no longer hides the (latency-bound) panel chain, and the
+    // in-block rank-128 update plus the rank-OB head update are two serial launches where one rank-128 head
+    // update would do: the last `late` columns use outer blocks of 128 (HYB_POTRF_LATE, default 3072; 0 = off).
+    static const int64_t late = [] {
+        const char* e = getenv("HYB_POTRF_LATE");
+        return (int64_t)(e ? atoi(e) : 3072);
+    }();
+    int64_t obc = OB;
+    for (int64_t K0 = 0; K0 < N; K0 += obc) {
+        obc = (N - K0 <= late) ? NB : OB;
+        const int64_t ob = (N - K0 < obc) ? (N - K0) : obc;
         const int64_t K1 = K0 + ob;
         // the panels of this outer block, on the panel stream, once its rows are up to date
         HYB_CUDA(cudaStreamWaitEvent(sp, ch.ev_head, 0));
@@ -897,7 +906,8 @@ int hyb_potrf(cudaStream_t st, HybChol& ch, int* info_out) {
         const double* U12 = ch.F + K0 + K1 * ld;  // ob x n2: block rows of this outer block
         double* A22 = ch.F + K1 + K1 * ld;
         // look-ahead: the next outer block's rows first
-        const int64_t nh = n2 < OB ? n2 : OB;
+        const int64_t obn = (n2 <= late) ? NB : OB;  // width of the next outer block
+        const int64_t nh = n2 < obn ? n2 : obn;
         HYB_CHECK(hyb_gemm_tn(st, nh, n2, ob, -1.0, U12, ld, U12, ld, 1.0, A22, ld, 0));
         stamp(st);  // [4 + 5b] head update done
         HYB_CUDA(cudaEventRecord(ch.ev_head, st));
