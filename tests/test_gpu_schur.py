@@ -115,7 +115,9 @@ def test_known_answer_instances_on_gpu(name):
 # search flip on rounding differences (the GPU path itself gives 13 or 15 iterations depending on
 # whether the four directions are solved one by one or as batched pairs; the oracle gives 13; status
 # and objective are identical and the trajectories agree to 1e-5 until iteration 12).
-ITER_SLACK = {"wsosinterppossemideftri3": 2}
+# nonnegative4 with the device-resident stepper: see DEVICE_STEPPER_ITER_SLACK in tests/test_golden.py (the
+# host-vector protocol is held to +-1 there).
+ITER_SLACK = {"wsosinterppossemideftri3": 2, "nonnegative4": 3}
 
 
 @pytest.mark.parametrize("N,seed", [(64, 0), (96, 1), (256, 2)])

@@ -12,6 +12,9 @@ cap() {  # name regex skip count cmd...
   local name=$1 rx=$2 skip=$3 cnt=$4; shift 4
   ncu --set full --clock-control none --import-source on -k regex:$rx -s $skip -c $cnt -f -o gpurun_out/${TAG}_ncu_$name "$@" > gpurun_out/${TAG}_ncu_$name.log 2>&1
   echo "$name rc=$?"
+  # gpurun_out/ may carry 64 MiB at most: keep the raw-counter page as CSV, drop the report (two are kept whole)
+  ncu -i gpurun_out/${TAG}_ncu_$name.ncu-rep --page raw --csv > gpurun_out/${TAG}_ncu_${name}_raw.csv 2>/dev/null
+  case $name in gemm_t|potf2) ;; *) rm -f gpurun_out/${TAG}_ncu_$name.ncu-rep ;; esac
 }
 cap gemm_t        'gemm_t_kernel'         6 2 $BENCH
 cap gemm_n        'gemm_n_partial_kernel' 6 2 $BENCH
@@ -28,4 +31,4 @@ cap soc_prod4     'soc_prod_kernel'      10 3 $CFG4
 cap ninf_update4  'ninf_update_kernel'   10 2 $CFG4N
 cap ninf_prod4    'ninf_prod_kernel'     10 3 $CFG4N
 cap nonneg_prod4  'nonneg_prod_kernel'   10 2 $CFG4
-ls -la gpurun_out/${TAG}_ncu_*.ncu-rep | wc -l
+ls gpurun_out/${TAG}_ncu_*_raw.csv | wc -l; du -sh gpurun_out
