@@ -37,7 +37,19 @@ def _same_solution(stepper, s, dev_vec, host_vec, rhs_vec):
 def _capture_state(model_fn, n_iters, **kw):
     """Run n_iters iterations on the GPU path and return the solver frozen at the next
     iteration's state (point accepted, cones loaded, residuals computed)."""
-    s = make_gpu_solver(0, iter_limit=n_iters, **kw)
+    import os
+
+    # these tests drive the host-vector protocol (right-hand sides built by host/stepper.py): the host must
+    # hold the iterate and the cone batch's mirror, which the device-resident stepper does not keep
+    old = os.environ.get("HYB_HOST_STEPPER")
+    os.environ["HYB_HOST_STEPPER"] = "1"
+    try:
+        s = make_gpu_solver(0, iter_limit=n_iters, **kw)
+    finally:
+        if old is None:
+            del os.environ["HYB_HOST_STEPPER"]
+        else:
+            os.environ["HYB_HOST_STEPPER"] = old
     s.load(model_fn())
     s.solve()
     return s
