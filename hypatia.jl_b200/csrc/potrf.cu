@@ -881,9 +881,20 @@ int hyb_potrf(cudaStream_t st, HybChol& ch, int* info_out) {
         const char* e = getenv("HYB_POTRF_LATE");
         return (int64_t)(e ? atoi(e) : 3072);
     }();
+    // ... and while the trailing matrix is large the step is bound by the bulk update, which runs closer to the
+    // DMMA peak the longer its contraction: outer blocks of 2 OB there (HYB_POTRF_EARLY, default 5120; 0 = off).
+    static const int64_t early = [] {
+        const char* e = getenv("HYB_POTRF_EARLY");
+        return (int64_t)(e ? atoi(e) : 5120);
+    }();
+    auto block_width = [&](int64_t remaining) -> int64_t {
+        if (remaining <= late) return NB;
+        if (early > 0 && remaining > early) return 2 * OB;
+        return OB;
+    };
     int64_t obc = OB;
     for (int64_t K0 = 0; K0 < N; K0 += obc) {
-        obc = (N - K0 <= late) ? NB : OB;
+        obc = block_width(N - K0);
         const int64_t ob = (N - K0 < obc) ? (N - K0) : obc;
         const int64_t K1 = K0 + ob;
         // the panels of this outer block, on the panel stream, once its rows are up to date
@@ -906,7 +917,7 @@ int hyb_potrf(cudaStream_t st, HybChol& ch, int* info_out) {
         const double* U12 = ch.F + K0 + K1 * ld;  // ob x n2: block rows of this outer block
         double* A22 = ch.F + K1 + K1 * ld;
         // look-ahead: the next outer block's rows first
-        const int64_t obn = (n2 <= late) ? NB : OB;  // width of the next outer block
+        const int64_t obn = block_width(n2);  // width of the next outer block
         const int64_t nh = n2 < obn ? n2 : obn;
         HYB_CHECK(hyb_gemm_tn(st, nh, n2, ob, -1.0, U12, ld, U12, ld, 1.0, A22, ld, 0));
         stamp(st);  // [4 + 5b] head update done
