@@ -363,7 +363,7 @@ def main():
     # multi-GPU form: "rootworker" (default; one process per GPU, rootworker.py), "replicated" (sharded.py) or
     # "single_process" (rank 0 drives every GPU through hyb_multi_* alone -- the form a Julia host would use;
     # the other ranks only keep the launch contract: they join the final barrier and reductions)
-    mode = os.environ.get("HYB_MULTI_MODE", "rootworker")
+    mode = os.environ.get("HYB_MULTI_MODE", "single_process")
     single = world > 1 and mode == "single_process"
     if single and rank != 0:
         torch.cuda.synchronize()

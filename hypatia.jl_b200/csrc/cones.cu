@@ -206,20 +206,11 @@ __global__ void soc_update_kernel(int64_t count, int d, int64_t offset, int64_t 
 
 // products on a q_block x m array.  Item = (cone c, column j); thread mapping puts adjacent
 // threads on adjacent cones of the same column.
+// one (cone, column) item: r = op(H) a for the cone with point p and dist; r may alias a (every entry of a
+// that is needed after the first store has been read into a register by then)
 template <int TYPE, bool WARP>
-__global__ void soc_prod_kernel(int64_t count, int d, int64_t offset, int64_t cone0, int64_t m, int op,
-                                const double* __restrict__ point, const double* __restrict__ aux,
-                                const double* __restrict__ arr, int64_t lda, double* __restrict__ prod, int64_t ldp) {
-    const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int64_t item = WARP ? (gt >> 5) : gt;
-    const int i0 = WARP ? (int)(gt & 31) : 0;
-    const int stride = WARP ? 32 : 1;
-    if (item >= count * m) return;
-    const int64_t c = item % count, j = item / count;
-    const double* p = point + offset + c * d;
-    const double* a = arr + offset + c * d + j * lda;
-    double* r = prod + offset + c * d + j * ldp;
-    const double dist = aux[cone0 + c];
+__device__ __forceinline__ void soc_prod_item(const double* p, const double* a, double* r, double dist, int d, int op,
+                                              int i0, int stride) {
     if (op == HYB_OP_HESS) {
         // epinormeucl.jl:129-144, epipersquare.jl:145-162
         const double wwa = dot_strided<WARP>(p, a, TYPE, d, i0, stride);
@@ -299,6 +290,57 @@ __global__ void soc_prod_kernel(int64_t count, int d, int64_t offset, int64_t co
                 r[1] = dotj * v1 - a0 * rtdist;
             }
         }
+    }
+}
+
+template <int TYPE, bool WARP>
+__global__ void soc_prod_kernel(int64_t count, int d, int64_t offset, int64_t cone0, int64_t m, int op,
+                                const double* __restrict__ point, const double* __restrict__ aux,
+                                const double* __restrict__ arr, int64_t lda, double* __restrict__ prod, int64_t ldp) {
+    const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t item = WARP ? (gt >> 5) : gt;
+    const int i0 = WARP ? (int)(gt & 31) : 0;
+    const int stride = WARP ? 32 : 1;
+    if (item >= count * m) return;
+    const int64_t c = item % count, j = item / count;
+    soc_prod_item<TYPE, WARP>(point + offset + c * d, arr + offset + c * d + j * lda, prod + offset + c * d + j * ldp,
+                              aux[cone0 + c], d, op, i0, stride);
+}
+
+// Wide products (m >= 32 columns, the W * GQ2 product of the Schur assembly) of small cones: a thread that walks
+// its cone's d consecutive rows makes the warp touch 32 segments d * 8 bytes apart per load instruction (measured:
+// 25 % of the HBM copy rate at d = 8).  Here a CTA moves a tile of 256 cones x 1 column (256 d consecutive
+// doubles) between global and shared memory with fully coalesced accesses, and the per-cone arithmetic runs
+// out of shared memory (row stride d + 1: conflict-free).  The cones' points are staged once per CTA and
+// reused for CPB columns.
+constexpr int SOC_TILE = 256, SOC_CPB = 8;
+template <int TYPE>
+__global__ void __launch_bounds__(SOC_TILE)
+soc_prod_tile_kernel(int64_t count, int d, int64_t offset, int64_t cone0, int64_t m, int op,
+                     const double* __restrict__ point, const double* __restrict__ aux, const double* __restrict__ arr,
+                     int64_t lda, double* __restrict__ prod, int64_t ldp) {
+    extern __shared__ double sm[];
+    const int ds = d + 1;
+    double* P = sm;
+    double* A = sm + SOC_TILE * ds;
+    const int tid = threadIdx.x;
+    const int64_t c0 = (int64_t)blockIdx.x * SOC_TILE;
+    const int nc = (int)((count - c0 < SOC_TILE) ? (count - c0) : SOC_TILE);
+    const int ne = nc * d;
+    const int64_t base = offset + c0 * d;
+    for (int e = tid; e < ne; e += SOC_TILE) P[(e / d) * ds + (e % d)] = point[base + e];
+    const double dist = (tid < nc) ? aux[cone0 + c0 + tid] : 1.0;
+    const int64_t j0 = (int64_t)blockIdx.y * SOC_CPB;
+    const int64_t j1 = (j0 + SOC_CPB < m) ? (j0 + SOC_CPB) : m;
+    for (int64_t j = j0; j < j1; ++j) {
+        const double* src = arr + base + j * lda;
+        for (int e = tid; e < ne; e += SOC_TILE) A[(e / d) * ds + (e % d)] = src[e];
+        __syncthreads();
+        if (tid < nc) soc_prod_item<TYPE, false>(P + tid * ds, A + tid * ds, A + tid * ds, dist, d, op, 0, 1);
+        __syncthreads();
+        double* dst = prod + base + j * ldp;
+        for (int e = tid; e < ne; e += SOC_TILE) dst[e] = A[(e / d) * ds + (e % d)];
+        __syncthreads();
     }
 }
 
@@ -473,18 +515,8 @@ __global__ void ninf_update_kernel(int64_t count, int d, int64_t offset, int64_t
 
 // hess_prod! (:205-229) / inv_hess_prod! (:314-335) on a q_block x m array; item = (cone, column)
 template <bool WARP>
-__global__ void ninf_prod_kernel(int64_t count, int d, int64_t offset, int64_t cone0, int64_t m, int op,
-                                 const double* __restrict__ point, const double* __restrict__ aux,
-                                 const double* __restrict__ arr, int64_t lda, double* __restrict__ prod, int64_t ldp) {
-    const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int64_t item = WARP ? (gt >> 5) : gt;
-    const int i0 = WARP ? (int)(gt & 31) : 0;
-    const int stride = WARP ? 32 : 1;
-    if (item >= count * m) return;
-    const int64_t c = item % count, j = item / count;
-    const double* p = point + offset + c * d;
-    const double* a = arr + offset + c * d + j * lda;
-    double* r = prod + offset + c * d + j * ldp;
+__device__ __forceinline__ void ninf_prod_item(const double* p, const double* a, double* r, double Zu, int d, int op, int i0,
+                                               int stride) {
     const double u = p[0], a0 = a[0];
     if (op == HYB_OP_HESS) {
         const double pui = a0 / u, cu = (double)(d - 2) / u;
@@ -499,7 +531,6 @@ __global__ void ninf_prod_kernel(int64_t count, int d, int64_t offset, int64_t c
         s = red_sum<WARP>(s);
         if (i0 == 0) r[0] = s - cu * pui;
     } else {
-        const double Zu = aux[cone0 + c];
         double s = 0.0;
         for (int i = 1 + i0; i < d; i += stride) {
             const double w = p[i], zeta = 0.5 * (u - (w / u) * w);
@@ -514,6 +545,50 @@ __global__ void ninf_prod_kernel(int64_t count, int d, int64_t offset, int64_t c
             r[i] = c1 * wumzi + zeta * a[i] * zti;
         }
         if (i0 == 0) r[0] = c1;
+    }
+}
+
+template <bool WARP>
+__global__ void ninf_prod_kernel(int64_t count, int d, int64_t offset, int64_t cone0, int64_t m, int op,
+                                 const double* __restrict__ point, const double* __restrict__ aux,
+                                 const double* __restrict__ arr, int64_t lda, double* __restrict__ prod, int64_t ldp) {
+    const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t item = WARP ? (gt >> 5) : gt;
+    const int i0 = WARP ? (int)(gt & 31) : 0;
+    const int stride = WARP ? 32 : 1;
+    if (item >= count * m) return;
+    const int64_t c = item % count, j = item / count;
+    ninf_prod_item<WARP>(point + offset + c * d, arr + offset + c * d + j * lda, prod + offset + c * d + j * ldp, aux[cone0 + c],
+                         d, op, i0, stride);
+}
+
+// coalesced-tile form for wide products, as soc_prod_tile_kernel
+__global__ void __launch_bounds__(SOC_TILE)
+ninf_prod_tile_kernel(int64_t count, int d, int64_t offset, int64_t cone0, int64_t m, int op, const double* __restrict__ point,
+                      const double* __restrict__ aux, const double* __restrict__ arr, int64_t lda, double* __restrict__ prod,
+                      int64_t ldp) {
+    extern __shared__ double sm[];
+    const int ds = d + 1;
+    double* P = sm;
+    double* A = sm + SOC_TILE * ds;
+    const int tid = threadIdx.x;
+    const int64_t c0 = (int64_t)blockIdx.x * SOC_TILE;
+    const int nc = (int)((count - c0 < SOC_TILE) ? (count - c0) : SOC_TILE);
+    const int ne = nc * d;
+    const int64_t base = offset + c0 * d;
+    for (int e = tid; e < ne; e += SOC_TILE) P[(e / d) * ds + (e % d)] = point[base + e];
+    const double Zu = (tid < nc) ? aux[cone0 + c0 + tid] : 1.0;
+    const int64_t j0 = (int64_t)blockIdx.y * SOC_CPB;
+    const int64_t j1 = (j0 + SOC_CPB < m) ? (j0 + SOC_CPB) : m;
+    for (int64_t j = j0; j < j1; ++j) {
+        const double* src = arr + base + j * lda;
+        for (int e = tid; e < ne; e += SOC_TILE) A[(e / d) * ds + (e % d)] = src[e];
+        __syncthreads();
+        if (tid < nc) ninf_prod_item<false>(P + tid * ds, A + tid * ds, A + tid * ds, Zu, d, op, 0, 1);
+        __syncthreads();
+        double* dst = prod + base + j * ldp;
+        for (int e = tid; e < ne; e += SOC_TILE) dst[e] = A[(e / d) * ds + (e % d)];
+        __syncthreads();
     }
 }
 
@@ -927,6 +1002,12 @@ int hybi_cones_alloc(HybCones& cs) {
                                       PSD_WARPS * 3 * PSD_MAT * (int)sizeof(double)));
         HYB_CUDA(cudaFuncSetAttribute(psd_dder3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       PSD_WARPS * 3 * PSD_MAT * (int)sizeof(double)));
+        HYB_CUDA(cudaFuncSetAttribute(soc_prod_tile_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      2 * SOC_TILE * 33 * (int)sizeof(double)));
+        HYB_CUDA(cudaFuncSetAttribute(soc_prod_tile_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      2 * SOC_TILE * 33 * (int)sizeof(double)));
+        HYB_CUDA(cudaFuncSetAttribute(ninf_prod_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      2 * SOC_TILE * 33 * (int)sizeof(double)));
     }
     return 0;
 }
@@ -1064,6 +1145,17 @@ int hybi_cones_prod(cudaStream_t st, HybCones& cs, int which, const double* arr,
 #define SOC_PROD(T, W)                                                                                               \
     soc_prod_kernel<T, W><<<nblocks(threads, 128), 128, 0, st>>>(b.count, b.dim, b.offset, b.cone0, m, op, cs.point, \
                                                                  cs.aux, arr, lda, prod, ldp)
+                if (!warp && m >= 32 && b.count >= 32) {  // wide product of many small cones: coalesced tiles
+                    dim3 grid(nblocks(b.count, SOC_TILE), (unsigned)((m + SOC_CPB - 1) / SOC_CPB));
+                    const size_t smem = sizeof(double) * 2 * SOC_TILE * (b.dim + 1);
+                    if (b.type == HYB_EPINORMEUCL)
+                        soc_prod_tile_kernel<1><<<grid, SOC_TILE, smem, st>>>(b.count, b.dim, b.offset, b.cone0, m, op, cs.point,
+                                                                             cs.aux, arr, lda, prod, ldp);
+                    else
+                        soc_prod_tile_kernel<2><<<grid, SOC_TILE, smem, st>>>(b.count, b.dim, b.offset, b.cone0, m, op, cs.point,
+                                                                             cs.aux, arr, lda, prod, ldp);
+                    break;
+                }
                 if (b.type == HYB_EPINORMEUCL) {
                     if (warp) SOC_PROD(1, true); else SOC_PROD(1, false);
                 } else {
@@ -1079,6 +1171,12 @@ int hybi_cones_prod(cudaStream_t st, HybCones& cs, int which, const double* arr,
                 }
                 const bool warp = b.dim > 32;
                 const int64_t threads = (warp ? 32 : 1) * b.count * m;
+                if (!warp && m >= 32 && b.count >= 32) {
+                    dim3 grid(nblocks(b.count, SOC_TILE), (unsigned)((m + SOC_CPB - 1) / SOC_CPB));
+                    ninf_prod_tile_kernel<<<grid, SOC_TILE, sizeof(double) * 2 * SOC_TILE * (b.dim + 1), st>>>(
+                        b.count, b.dim, b.offset, b.cone0, m, op, cs.point, cs.aux, arr, lda, prod, ldp);
+                    break;
+                }
                 if (warp)
                     ninf_prod_kernel<true><<<nblocks(threads, 128), 128, 0, st>>>(b.count, b.dim, b.offset, b.cone0, m, op,
                                                                                 cs.point, cs.aux, arr, lda, prod, ldp);

@@ -297,11 +297,15 @@ int hyb_gemm_tn(cudaStream_t st, int64_t M, int64_t N, int64_t K, double alpha, 
     const int64_t nk_all = (K + BK - 1) / BK;
     const int64_t r = ntiles % P;
     static const bool no_split = getenv("HYB_GEMM_NO_SPLIT") != nullptr;
-    if (!no_split && ntiles > P && r > 0 && 2 * r <= P && nk_all >= 128) {
-        nsplit = (int)(P / r);
+    // ... and when the whole result has fewer tiles than half the SMs but the contraction is long (a small Schur
+    // matrix under very many cone rows: cfg4-like models), every tile is split the same way
+    const bool few_tiles = 2 * ntiles <= P && nk_all >= 64;
+    if (!no_split && ((ntiles > P && r > 0 && 2 * r <= P && nk_all >= 128) || few_tiles)) {
+        const int64_t rr = few_tiles ? ntiles : r;
+        nsplit = (int)(P / rr);
         if (nsplit > nk_all / 32) nsplit = (int)(nk_all / 32);
         if (nsplit >= 2) {
-            n_main = ntiles - r;
+            n_main = ntiles - rr;
             std::lock_guard<std::mutex> lock(g_tail_mutex);
             for (auto& w : g_tail_ws)
                 if (w.dev == dev && w.st == st) ws = w.p;

@@ -48,6 +48,9 @@ SPEC_SETS = {
     "nonneg": [cs.Nonnegative(1), cs.Nonnegative(6), cs.Nonnegative(300)],
     "soc_small": [cs.EpiNormEucl(2)] + [cs.EpiNormEucl(3)] * 5 + [cs.EpiNormEucl(8)] * 40,
     "rsoc_small": [cs.EpiPerSquare(3)] * 3 + [cs.EpiPerSquare(8)] * 33 + [cs.EpiPerSquare(4)],
+    # many small cones and >= 32 columns: the coalesced tile kernel (ragged last tile, odd offsets, d up to 32)
+    "soc_wide": [cs.Nonnegative(3)] + [cs.EpiNormEucl(8)] * 300 + [cs.EpiPerSquare(5)] * 70 + [cs.EpiNormEucl(32)] * 40
+    + [cs.EpiPerSquare(3)] * 33,
     "soc_large": [cs.EpiNormEucl(33), cs.EpiNormEucl(100), cs.EpiPerSquare(70), cs.EpiPerSquare(257)],
     "psd": [cs.PosSemidefTri(cs.svec_length(s)) for s in (1, 2, 3, 5, 16, 16, 16, 32)],
     # even offsets and dims: products with >= 64 columns take the symmetric-Kronecker DMMA path
@@ -56,6 +59,7 @@ SPEC_SETS = {
     "psd_large": [cs.PosSemidefTri(cs.svec_length(s)) for s in (33, 64, 100, 150)] + [cs.EpiNormEucl(5)],
     # EpiNormInf (no sqrt oracles; use_dual = epigraph of the 1-norm), thread-per-cone and warp-per-cone sizes,
     # odd row offsets
+    "norminf_wide": [cs.Nonnegative(1)] + [cs.EpiNormInf(4)] * 300 + [cs.EpiNormInf(7, use_dual=True)] * 50,
     "norminf_small": [cs.EpiNormInf(2)] + [cs.EpiNormInf(4)] * 40 + [cs.EpiNormInf(7, use_dual=True)] * 5 + [cs.EpiNormInf(3)],
     "norminf_large": [cs.EpiNormInf(40), cs.EpiNormInf(129, use_dual=True), cs.EpiNormInf(33)],
     "norminf_mixed": [cs.Nonnegative(3)] + [cs.EpiNormInf(4)] * 5 + [cs.EpiNormEucl(5), cs.EpiNormInf(6, use_dual=True),
@@ -99,7 +103,7 @@ def test_oracles_match_cpu(name):
     ok_g, agg_g = gpu.check_neighborhood(irtmu, False, 0.01, 1e9)
     assert ok_c == ok_g and abs(agg_c - agg_g) <= 1e-9 * tol_scale * max(1.0, abs(agg_c))
 
-    for m in (1, 7) + ((80, 200) if name == "psd_wide" else ()):
+    for m in (1, 7) + ((80, 200) if name in ("psd_wide", "soc_wide", "norminf_wide") else ()):
         arr = rng.standard_normal(q) if m == 1 else np.asfortranarray(rng.standard_normal((q, m)))
         for fn in ("hess_prod", "inv_hess_prod", "block_hess_prod", "hess_prod_slow"):
             assert rel_err(getattr(gpu, fn)(arr), getattr(cpu, fn)(arr)) < 1e4 * TOL * tol_scale, (fn, m)
