@@ -192,6 +192,7 @@ class IterTimer:
                 dev_ms, h2d, d2h = dev_ms + d2, h2d + a2, d2h + b2
             if hasattr(solver.syssolver, "last_assemble_ms"):  # single-process multi-GPU: slowest device's assembly
                 tw, ts = 0.0, solver.syssolver.last_assemble_ms
+                dev_ms += ts  # the shards' kernels run in contexts of their own: count the slowest one's device time
             lc = self.ctx.launch_count()
             red = getattr(solver.syssolver, "time_reduce_ms", 0.0)
             row.update(dev_ms=dev_ms, h2d=h2d, d2h=d2h, t_w=tw, t_syrk=ts, t_fact=tf, launches=lc - self._launch0,
