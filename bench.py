@@ -225,7 +225,7 @@ def cublas_dgemm_tflops(n=8192, reps=3):
 def ncu_traffic(N, K):
     """DRAM bytes per launch of the syrk kernel from the committed ncu capture (None if the
     shape was not captured)."""
-    path = os.path.join(ROOT, "profiles", "r01_syrk_N8192_ncu_full.json")
+    path = os.path.join(ROOT, "profiles", "r02_syrk_N8192_ncu_full.json")
     try:
         d = json.load(open(path))
         if f"N={N}, K={K}," in d["kernel"]:
@@ -531,7 +531,7 @@ def main():
             "peak_source": "cuBLAS DGEMM 8192^3 measured in this run (MEASURED_PEAKS.json has no FP64 figure; FP64 tensor work on sm_100a is DMMA, not tcgen05)",
             "algorithmic_flops_per_launch": syrk_flops, "avg_launch_ms": t_syrk,
             "traffic": ncu_traffic(N, q_sqrt),
-            "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full capture in profiles/r01_syrk_N8192_ncu_full.json (same N, K)",
+            "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full capture in profiles/r02_syrk_N8192_ncu_full.json (same N, K)",
         },
     }
     if not args.no_cpu_baseline and world == 1:

@@ -31,6 +31,46 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
                  : "d"(a), "d"(b));
 }
 
+// Tile enumeration of the UPPER (syrk) form.  sb == 0: plain column-major walk of the triangle.  sb > 0: the
+// triangle is cut into sb x sb super-blocks (walked column-major, tiles inside one column-major too), so the ~148
+// CTAs that run at the same time cover a compact square of tiles and share 2 sb operand panels instead of one
+// panel per tile row: with the contraction index in lock-step across CTAs that is what the L2 can actually reuse
+// (a K x 128 panel is 16.7 MB at K = 16368; the L2 holds seven).  DRAM traffic per wave ~ (distinct panels) x panel.
+__device__ __forceinline__ void upper_tile_of(int idx, int T, int sb, int& ti, int& tj) {
+    if (sb <= 0) {
+        tj = (int)((sqrt(8.0 * idx + 1.0) - 1.0) * 0.5);
+        while (tj * (tj + 1) / 2 > idx) --tj;
+        while ((tj + 1) * (tj + 2) / 2 <= idx) ++tj;
+        ti = idx - tj * (tj + 1) / 2;
+        return;
+    }
+    const int nsb = (T + sb - 1) / sb;
+    for (int J = 0; J < nsb; ++J) {
+        const int w = min(sb, T - J * sb);
+        for (int I = 0; I <= J; ++I) {
+            const int h = min(sb, T - I * sb);
+            const int cnt = (I == J) ? w * (w + 1) / 2 : h * w;
+            if (idx < cnt) {
+                int li, lj;
+                if (I == J) {
+                    lj = (int)((sqrtf(8.0f * idx + 1.0f) - 1.0f) * 0.5f);
+                    while (lj * (lj + 1) / 2 > idx) --lj;
+                    while ((lj + 1) * (lj + 2) / 2 <= idx) ++lj;
+                    li = idx - lj * (lj + 1) / 2;
+                } else {
+                    lj = idx / h;
+                    li = idx - lj * h;
+                }
+                ti = I * sb + li;
+                tj = J * sb + lj;
+                return;
+            }
+            idx -= cnt;
+        }
+    }
+    ti = tj = 0;  // not reached
+}
+
 // 12 warps = 3 per SM sub-partition (16K registers each) => 168 registers per thread at launch;
 // the producer warpgroup then gives registers back (setmaxnreg.dec) and the two consumer
 // warpgroups take them (setmaxnreg.inc 232), the Hopper/Blackwell warp-specialisation idiom.
@@ -58,11 +98,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     int ti, tj;
     if (flags & HYB_GEMM_UPPER) {
-        const int idx = tile_idx;
-        tj = (int)((sqrt(8.0 * idx + 1.0) - 1.0) * 0.5);
-        while (tj * (tj + 1) / 2 > idx) --tj;
-        while ((tj + 1) * (tj + 2) / 2 <= idx) ++tj;
-        ti = idx - tj * (tj + 1) / 2;
+        upper_tile_of(tile_idx, (N + BN - 1) / BN, (flags >> 8) & 0xff, ti, tj);
     } else {
         ti = tile_idx % tiles_m;
         tj = tile_idx / tiles_m;
@@ -226,10 +262,7 @@ gemm_tail_reduce_kernel(int M, int N, double alpha, double beta, double* __restr
     const int tile_idx = n_main + blockIdx.x;
     int ti, tj;
     if (flags & HYB_GEMM_UPPER) {
-        tj = (int)((sqrt(8.0 * tile_idx + 1.0) - 1.0) * 0.5);
-        while (tj * (tj + 1) / 2 > tile_idx) --tj;
-        while ((tj + 1) * (tj + 2) / 2 <= tile_idx) ++tj;
-        ti = tile_idx - tj * (tj + 1) / 2;
+        upper_tile_of(tile_idx, (N + BN - 1) / BN, (flags >> 8) & 0xff, ti, tj);
     } else {
         ti = tile_idx % tiles_m;
         tj = tile_idx / tiles_m;
@@ -287,6 +320,14 @@ int hyb_gemm_tn(cudaStream_t st, int64_t M, int64_t N, int64_t K, double alpha, 
         ntiles = (int64_t)tiles_m * tiles_n;
     }
     if (((uintptr_t)C & 15) == 0 && (ldc & 1) == 0) flags |= HYB_GEMM_CVEC;
+    if (flags & HYB_GEMM_UPPER) {  // super-block rasterisation of the triangle (HYB_GEMM_SB, default 12; 0 = plain walk)
+        static const int sb = [] {
+            const char* e = getenv("HYB_GEMM_SB");
+            const int v = e ? atoi(e) : 12;
+            return (v < 0 || v > 255) ? 12 : v;
+        }();
+        flags |= sb << 8;
+    }
     // split the tiles of a small last wave along K (long contractions only: the Schur syrk)
     int dev = 0;
     HYB_CUDA(cudaGetDevice(&dev));
