@@ -442,6 +442,13 @@ struct HybDenseWsos {
     std::vector<HybChol> chLam;
     double *PD = nullptr;                             // U x Lmax scratch
     double *H = nullptr, *Hf = nullptr, *Lh = nullptr, *UU = nullptr;
+    // the K chains Lambda_k -> chol -> F_k -> F_k'F_k are independent of each other (wsosinterpnonnegative.jl:
+    // 99-166 loops over k) and each is a string of latency-bound launches on small matrices: they run side by
+    // side on one stream per k, with scratch of their own, and are joined in k order (fixed summation order)
+    std::vector<double*> PDk, UUk;
+    std::vector<cudaStream_t> sk;
+    std::vector<cudaEvent_t> evk;
+    cudaEvent_t ev_fork = nullptr;
     HybChol chH;
     double *v1 = nullptr, *v2 = nullptr, *v3 = nullptr, *scal = nullptr;
     int *dual_ok = nullptr, *slow = nullptr, *sqrt_ok = nullptr;
@@ -502,6 +509,20 @@ int hybd_wsos_create(HybDenseWsos** out, int64_t U, int nPs, const double* const
     }
     HYB_CUDA(cudaMalloc(&c->PD, sizeof(double) * c->ldU * Lmax));
     const size_t ub = sizeof(double) * c->ldU * U;
+    HYB_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+    for (int k = 0; k < nPs; ++k) {
+        double *pd = nullptr, *uu = nullptr;
+        HYB_CUDA(cudaMalloc(&pd, sizeof(double) * c->ldU * c->L[k]));
+        HYB_CUDA(cudaMalloc(&uu, ub));
+        c->PDk.push_back(pd);
+        c->UUk.push_back(uu);
+        cudaStream_t s2 = nullptr;
+        cudaEvent_t e2 = nullptr;
+        HYB_CUDA(cudaStreamCreateWithFlags(&s2, cudaStreamNonBlocking));
+        HYB_CUDA(cudaEventCreateWithFlags(&e2, cudaEventDisableTiming));
+        c->sk.push_back(s2);
+        c->evk.push_back(e2);
+    }
     double** mats[] = {&c->H, &c->Hf, &c->Lh, &c->UU};
     for (double** m : mats) {
         HYB_CUDA(cudaMalloc(m, ub));
@@ -541,6 +562,11 @@ void hybd_wsos_destroy(HybDenseWsos* c) {
         cudaFree(c->LU[k]);
     }
     hyb_chol_free(c->chH);
+    for (double* b : c->PDk) cudaFree(b);
+    for (double* b : c->UUk) cudaFree(b);
+    for (cudaStream_t s2 : c->sk) cudaStreamDestroy(s2);
+    for (cudaEvent_t e2 : c->evk) cudaEventDestroy(e2);
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     cudaFree(c->PD);
     cudaFree(c->H);
     cudaFree(c->Hf);
@@ -580,16 +606,29 @@ int hybd_wsos_update(cudaStream_t st, HybDenseWsos* c, const double* primal, con
     all_gt_eps_kernel<<<1, 1024, 0, st>>>(U, dual_out, c->dual_ok);
     g_dense_launches += 4;
     HYB_CUDA(cudaGetLastError());
+    // fork: Lambda_k = P_k' diag(s) P_k (upper) and its Cholesky, one stream per k
+    HYB_CUDA(cudaEventRecord(c->ev_fork, st));
     for (int k = 0; k < c->nPs; ++k) {
         const int64_t L = c->L[k], ldL = c->ldL[k];
-        // Lambda_k = P_k' diag(s) P_k, upper, Cholesky
-        rowscale_kernel<<<nb1(U * L), 256, 0, st>>>(c->P[k], c->v3, U, L, ldU, c->PD);
+        cudaStream_t s2 = c->sk[k];
+        HYB_CUDA(cudaStreamWaitEvent(s2, c->ev_fork, 0));
+        rowscale_kernel<<<nb1(U * L), 256, 0, s2>>>(c->P[k], c->v3, U, L, ldU, c->PDk[k]);
         DLAUNCHED();
-        HYB_CHECK(hyb_gemm_tn(st, L, L, U, 1.0, c->P[k], ldU, c->PD, ldU, 0.0, c->Lam[k], ldL, HYB_GEMM_UPPER));
-        int inf = 0;
-        HYB_CHECK(hyb_potrf(st, c->chLam[k], &inf));
-        if (inf != 0) {
-            // not in the cone: update_feas stops at the first Lambda_k that is not positive definite
+        HYB_CHECK(hyb_gemm_tn(s2, L, L, U, 1.0, c->P[k], ldU, c->PDk[k], ldU, 0.0, c->Lam[k], ldL, HYB_GEMM_UPPER));
+        HYB_CHECK(hyb_potrf(s2, c->chLam[k], nullptr));
+        HYB_CUDA(cudaEventRecord(c->evk[k], s2));
+        HYB_CUDA(cudaStreamWaitEvent(st, c->evk[k], 0));
+    }
+    {
+        int infs[16] = {0};
+        const int nk = c->nPs < 16 ? c->nPs : 16;
+        for (int k = 0; k < nk; ++k)
+            HYB_CUDA(cudaMemcpyAsync(&infs[k], c->chLam[k].info, sizeof(int), cudaMemcpyDeviceToHost, st));
+        HYB_CUDA(cudaStreamSynchronize(st));
+        bool infeasible = false;
+        for (int k = 0; k < nk; ++k) infeasible = infeasible || infs[k] != 0;
+        if (infeasible) {
+            // not in the cone: update_feas reports the first Lambda_k that is not positive definite
             // (wsosinterpnonnegative.jl:99-128) and the line search rejects the candidate before any
             // gradient / Hessian oracle is asked for (search.jl:146-150) -- skip that work (3/4 of it)
             wsos_finalize_kernel<<<1, 1, 0, st>>>(c->lam_infos_dev, c->nPs, c->chH.info, c->dual_ok, c->scal, c->nu, U, flag,
@@ -599,20 +638,26 @@ int hybd_wsos_update(cudaStream_t st, HybDenseWsos* c, const double* primal, con
             return 0;
         }
     }
+    // fork again: F_k = R_k^-T P_k' and UU_k = F_k' F_k
+    HYB_CUDA(cudaEventRecord(c->ev_fork, st));
     for (int k = 0; k < c->nPs; ++k) {
         const int64_t L = c->L[k], ldL = c->ldL[k];
-        // F_k = R_k^-T P_k'
-        copy_mat_kernel<<<nb1(L * U), 256, 0, st>>>(c->Pt[k], ldL, c->F[k], ldL, L, U);
+        cudaStream_t s2 = c->sk[k];
+        HYB_CUDA(cudaStreamWaitEvent(s2, c->ev_fork, 0));
+        copy_mat_kernel<<<nb1(L * U), 256, 0, s2>>>(c->Pt[k], ldL, c->F[k], ldL, L, U);
         DLAUNCHED();
-        HYB_CHECK(hyb_trsm_fwd(st, c->Lam[k], ldL, L, c->F[k], ldL, U));
-        HYB_CHECK(hyb_transpose(st, c->F[k], ldL, L, U, c->Ft[k], ldU, 0));
-        // grad_j -= |F_k[:, j]|^2
+        HYB_CHECK(hyb_trsm_fwd(s2, c->Lam[k], ldL, L, c->F[k], ldL, U));
+        HYB_CHECK(hyb_transpose(s2, c->F[k], ldL, L, U, c->Ft[k], ldU, 0));
+        HYB_CHECK(hyb_gemm_tn(s2, U, U, L, 1.0, c->F[k], ldL, c->F[k], ldL, 0.0, c->UUk[k], ldU, HYB_GEMM_UPPER));
+        HYB_CUDA(cudaEventRecord(c->evk[k], s2));
+    }
+    // join in k order: grad_j -= |F_k[:, j]|^2 and H (+)= (F_k' F_k) .^ 2, fixed summation order
+    for (int k = 0; k < c->nPs; ++k) {
+        const int64_t L = c->L[k], ldL = c->ldL[k];
+        HYB_CUDA(cudaStreamWaitEvent(st, c->evk[k], 0));
         coldot_kernel<<<nb1(U, 8), 256, 0, st>>>(c->F[k], c->F[k], L, U, ldL, -1.0, k == 0 ? 0.0 : 1.0, grad);
-        DLAUNCHED();
-        // H (+)= (F_k' F_k) .^ 2
-        HYB_CHECK(hyb_gemm_tn(st, U, U, L, 1.0, c->F[k], ldL, c->F[k], ldL, 0.0, c->UU, ldU, HYB_GEMM_UPPER));
-        sq_accum_kernel<<<nb1(U * U), 256, 0, st>>>(c->UU, c->H, U, ldU, k == 0);
-        DLAUNCHED();
+        sq_accum_kernel<<<nb1(U * U), 256, 0, st>>>(c->UUk[k], c->H, U, ldU, k == 0);
+        g_dense_launches += 2;
         HYB_CUDA(cudaGetLastError());
     }
     symmetrize_kernel<<<nb1(U * U), 256, 0, st>>>(c->H, U, ldU);
