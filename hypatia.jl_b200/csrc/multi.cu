@@ -140,6 +140,24 @@ hyb_multi* hyb_multi_create(int ndev, const int* devices) {
 
 hyb_ctx* hyb_multi_root(hyb_multi* m) { return m ? m->root : nullptr; }
 
+// The partition hyb_multi_model_load would use, without touching a GPU: row ranges per device and the number of
+// (possibly split) cones each device gets.  Pure host code -- lets a caller size its buffers, and lets the CPU
+// test-suite check the partition rules.
+int hyb_multi_plan(int64_t q, int64_t ncones, const hyb_cone_desc* descs, int ndev, int64_t* row_lo, int64_t* row_hi,
+                   int64_t* cones_per_dev) {
+    if (ndev < 1 || (ncones > 0 && !descs)) {
+        hyb_set_error("hyb_multi_plan: bad arguments");
+        return -3;
+    }
+    const ShardPlan plan = plan_shards(q, ncones, descs, ndev);
+    for (int d = 0; d < ndev; ++d) {
+        if (row_lo) row_lo[d] = plan.lo[d];
+        if (row_hi) row_hi[d] = plan.hi[d];
+        if (cones_per_dev) cones_per_dev[d] = (int64_t)plan.descs[d].size();
+    }
+    return 0;
+}
+
 int hyb_multi_shard_rows(hyb_multi* m, int64_t* row_lo, int64_t* row_hi) {
     if (!m || !m->loaded) return -1;
     for (int d = 0; d < m->ndev; ++d) {

@@ -100,6 +100,8 @@ SIGNATURES = {
     "hyb_multi_destroy": (None, [C.c_void_p]),
     "hyb_multi_root": (C.c_void_p, [C.c_void_p]),
     "hyb_multi_model_load": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, c_double_p, C.c_int64, C.POINTER(ConeDesc)]),
+    "hyb_multi_plan": (C.c_int, [C.c_int64, C.c_int64, C.POINTER(ConeDesc), C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64),
+                                 C.POINTER(C.c_int64)]),
     "hyb_multi_shard_rows": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "hyb_multi_schur_update": (C.c_int, [C.c_void_p, c_double_p, c_double_p, c_double_p, c_int_p]),
     "hyb_ctx_set_assemble_only": (C.c_int, [C.c_void_p, C.c_int]),

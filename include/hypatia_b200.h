@@ -240,6 +240,10 @@ hyb_ctx* hyb_multi_root(hyb_multi* m);
 /* Solvers.load(syssolver, solver), qrchol.jl:145-187: the full model on the root plus every device's row range
  * (Nonnegative cones are cut at the range boundaries so that LPs shard too) */
 int hyb_multi_model_load(hyb_multi* m, int64_t q, int64_t N, const double* GQ2, int64_t ncones, const hyb_cone_desc* descs);
+/* the partition hyb_multi_model_load would make, computed on the host alone (no GPU is touched): row ranges and
+ * the number of (possibly split) cones per device; arrays of ndev entries, NULL = not wanted */
+int hyb_multi_plan(int64_t q, int64_t ncones, const hyb_cone_desc* descs, int ndev, int64_t* row_lo, int64_t* row_hi,
+                   int64_t* cones_per_dev);
 /* rows [row_lo[d], row_hi[d]) of s / z owned by device d (arrays of ndev entries) */
 int hyb_multi_shard_rows(hyb_multi* m, int64_t* row_lo, int64_t* row_hi);
 /* update_lhs_fact (qrchol.jl:209-265) for the point loaded in the root context: t_assemble_ms = slowest device's
