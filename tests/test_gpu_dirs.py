@@ -188,3 +188,75 @@ def test_device_resident_stepper_matches_host_vector_protocol(name, monkeypatch)
         a = np.array([r[key] for r in dev.trace[:n]])
         b = np.array([r[key] for r in host.trace[:n]])
         assert np.all(np.abs(a - b) <= 1e-8 * np.maximum(np.abs(b), 1e-5)), key
+
+
+def _at_point(solver, model_fn, point_vec):
+    """Bring a freshly loaded solver to the state the top of CombinedStepper.step sees at the given iterate:
+    point set, mu, cones loaded at point / sqrt(mu) (search.jl:144-145), convergence parameters, cutoff."""
+    import math
+
+    solver.load(model_fn())
+    solver._setup_solver()
+    solver._setup_loaded()
+    solver._initialize_point()
+    solver._setup_stepping()
+    solver.point.vec[:] = point_vec
+    solver.calc_mu()
+    cones, pt = solver.cones, solver.point
+    cones.load_point(cones.primal_of(pt.z, pt.s), 1.0 / math.sqrt(solver.mu))
+    cones.load_dual_point(cones.dual_of(pt.z, pt.s))
+    cones.reset_data()
+    assert cones.is_feas()
+    solver._calc_convergence_params()
+    solver.res_norm_cutoff = 1e-4 * max(solver.x_norm_res, solver.y_norm_res, solver.z_norm_res, solver.tau_feas)
+    solver.syssolver.update_lhs(solver)
+
+
+@pytest.mark.parametrize("name", ["block_multicone", "linearopt", "wsos_dual_barrier", "epipersquare4"])
+@pytest.mark.parametrize("n_iters", [2, 5])
+def test_directions_against_the_oracle_at_the_same_iterate(name, n_iters, monkeypatch):
+    """The four directions of one iteration (cent, pred, centadj, predadj; systemsolvers/common.jl:22-189,
+    steppers/common.jl:14-119) computed by the CUDA path and by the CPU oracle from the SAME iterate (the oracle's
+    after n_iters iterations): same right-hand sides, same directions up to the conditioning of the system, same
+    residual quality."""
+    from hypatia_b200.host.solver import Solver
+    from oracle.cones import CpuConeSet
+    from oracle.qrchol import QRCholDenseSystemSolver
+
+    ref = Solver(CpuConeSet, QRCholDenseSystemSolver(), iter_limit=n_iters)
+    ref.load(MODELS[name]())
+    ref.solve()
+    point_vec = ref.point.vec.copy()
+    cpu = Solver(CpuConeSet, QRCholDenseSystemSolver())
+    _at_point(cpu, MODELS[name], point_vec)
+    monkeypatch.setenv("HYB_HOST_STEPPER", "1")  # right-hand sides from the host builders on both sides
+    gpu = make_gpu_solver(0)
+    _at_point(gpu, MODELS[name], point_vec)
+    assert abs(gpu.mu - cpu.mu) <= 1e-14 * cpu.mu
+    m = cpu.model
+    dirs = {}
+    for s in (cpu, gpu):
+        stp = s.stepper
+        out = []
+        for builder, base in ((st.update_rhs_cent, None), (st.update_rhs_pred, None), (st.update_rhs_centadj, 0),
+                              (st.update_rhs_predadj, 1)):
+            if base is None:
+                builder(s, stp.rhs)
+            else:
+                builder(s, stp.rhs, out[base][1])
+            rhs = stp.rhs.vec.copy()
+            get_directions(stp, s)
+            d = Point(m.n, m.p, m.q)
+            d.vec[:] = stp.dir.vec
+            out.append((rhs, d))
+        dirs[id(s)] = out
+    for (rhs_c, d_c), (rhs_g, d_g) in zip(dirs[id(cpu)], dirs[id(gpu)]):
+        scale_r = np.max(np.abs(rhs_c)) + 1e-300
+        assert np.max(np.abs(rhs_g - rhs_c)) <= 1e-9 * scale_r  # oracle products (grad, H d, dder3) agree
+        scale = np.max(np.abs(d_c.vec)) + 1e-300
+        assert np.max(np.abs(d_g.vec - d_c.vec)) <= 1e-6 * scale
+        # both satisfy the 6 x 6 system equally well (residual evaluated by the ORACLE's apply_lhs)
+        r_g = _host_residual(cpu.stepper, cpu, d_g.vec, rhs_c)
+        r_c = _host_residual(cpu.stepper, cpu, d_c.vec, rhs_c)
+        floor = 1e-13 * max(1.0, scale_r, scale)
+        assert r_g <= 10.0 * r_c + floor, (r_g, r_c)
