@@ -255,8 +255,13 @@ def test_directions_against_the_oracle_at_the_same_iterate(name, n_iters, monkey
         assert np.max(np.abs(rhs_g - rhs_c)) <= 1e-9 * scale_r  # oracle products (grad, H d, dder3) agree
         scale = np.max(np.abs(d_c.vec)) + 1e-300
         assert np.max(np.abs(d_g.vec - d_c.vec)) <= 1e-6 * scale
-        # both satisfy the 6 x 6 system equally well (residual evaluated by the ORACLE's apply_lhs)
-        r_g = _host_residual(cpu.stepper, cpu, d_g.vec, rhs_c)
+        # both satisfy their 6 x 6 system equally well.  Each residual is evaluated with the backend's own
+        # oracles: the two backends' Hessians differ by ~1e-13 relative (the cancellation in dist = (u^2 - |w|^2)/2
+        # and in X^-1 near the boundary amplifies the summation-order difference; measured, tools/diag_dir_acc.py),
+        # so a direction is only self-consistent to that level with the OTHER backend's operator
+        r_g = _host_residual(gpu.stepper, gpu, d_g.vec, rhs_g)
         r_c = _host_residual(cpu.stepper, cpu, d_c.vec, rhs_c)
         floor = 1e-13 * max(1.0, scale_r, scale)
         assert r_g <= 10.0 * r_c + floor, (r_g, r_c)
+        r_x = _host_residual(cpu.stepper, cpu, d_g.vec, rhs_c)  # cross check, at the operators' own agreement
+        assert r_x <= 10.0 * r_c + 1e-10 * max(1.0, scale_r, scale), (r_x, r_c)
