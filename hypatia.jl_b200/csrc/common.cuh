@@ -92,6 +92,9 @@ struct HybChol {
     double* work = nullptr;   // N doubles
     cudaStream_t panel_stream = nullptr;  // look-ahead panels (high priority)
     cudaEvent_t ev_head = nullptr, ev_panel = nullptr;
+    cudaStream_t upd_stream = nullptr;    // rank-128 updates of the rows a panel leaves behind (high priority)
+    cudaEvent_t ev_trsm = nullptr, ev_upd = nullptr;
+    cudaEvent_t ev_far[3] = {nullptr, nullptr, nullptr};  // far update of outer block b reached block b + 2's rows
     // symmetric-indefinite fallback (sytrf.cu): kind 0 = F holds the Cholesky factor, 1 = F holds the
     // rook-pivoted Bunch-Kaufman factorization U D U' with pivot vector ipiv (LAPACK dsytrf_rook layout)
     int kind = 0;

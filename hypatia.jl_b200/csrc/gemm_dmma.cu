@@ -155,6 +155,19 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int arow = (wm * 64 + g) * BK;  // + mt*8*BK
     const int brow = (wn * 32 + g) * BK;  // + nt*8*BK
 
+    // The epilogue reads the C tile (beta != 0): ask the L2 for it now, a whole main loop ahead, so those
+    // reads do not pay the DRAM latency once per round after the last DMMA (1024 lines of 128 bytes, 4 per thread).
+    if (beta != 0.0 && !partial) {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int id = threadIdx.x * 4 + u, col = id >> 3, row = (id & 7) * 16;
+            if (n0 + col < N && m0 + row < M) {
+                const double* p = C + (m0 + row) + (int64_t)(n0 + col) * ldc;
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+            }
+        }
+    }
+
     for (int kt = 0; kt < nk; ++kt) {
         const int s = kt % STAGES;
         mbar_wait(&full[s], (kt / STAGES) & 1);

@@ -62,24 +62,49 @@ __device__ __noinline__ void potf2_diag_block(double* S, double* rdiag, int jb, 
             bad = true;
             badj = j;
         }
-        double r, rinv;
         if (FAST) {
+            double r, rinv;
             double y = rsqrt(d);
             const double e = fma(-d * y, y, 1.0);
             rinv = fma(0.5 * y, e, y);
             r = d * rinv;
             r = fma(fma(-r, r, d), 0.5 * rinv, r);
-        } else {
-            r = sqrt(d);
-            rinv = 1.0 / r;
-        }
-        const double ujc = (c == j) ? r : col[j] * rinv;
-        if (c >= j) col[j] = ujc;
-        if (lane == j) rdiag[j] = rinv;
+            const double ujc = (c == j) ? r : col[j] * rinv;
+            if (c >= j) col[j] = ujc;
+            if (lane == j) rdiag[j] = rinv;
 #pragma unroll
-        for (int i = j + 1; i < IB; ++i) {
-            const double uji = __shfl_sync(0xffffffffu, ujc, i);
-            if (c >= i) col[i] -= uji * ujc;
+            for (int i = j + 1; i < IB; ++i) {
+                const double uji = __shfl_sync(0xffffffffu, ujc, i);
+                if (c >= i) col[i] -= uji * ujc;
+            }
+        } else {
+            // The recurrence from one pivot to the next only needs a_ji a_jc / d, one reciprocal per pivot:
+            // (a_ji * (1/d)) * a_jc.  The square roots and their reciprocals, which scale the rows of the
+            // factor (u_jc = a_jc * (1 / sqrt(d_j)): IEEE sqrt, IEEE reciprocal, one multiplication -- what
+            // LAPACK's dpotf2 computes for row j), are taken for all 16 pivots at once after the loop.
+            const double dinv = __drcp_rn(d);
+            const double ajc = col[j];
+            const double ljc = ajc * dinv;
+#pragma unroll
+            for (int i = j + 1; i < IB; ++i) {
+                const double lji = __shfl_sync(0xffffffffu, ljc, i);
+                if (c >= i) col[i] -= lji * ajc;
+            }
+        }
+    }
+    if (!FAST) {
+        // lane c holds pivot d_c in col[c]
+        double dc = col[0];
+#pragma unroll
+        for (int i = 1; i < IB; ++i)
+            if (c == i) dc = col[i];
+        const double rc = sqrt(dc), rinvc = 1.0 / rc;
+        if (lane < IB) rdiag[c] = rinvc;
+#pragma unroll
+        for (int j = 0; j < IB; ++j) {
+            const double rj = __shfl_sync(0xffffffffu, rinvc, j);
+            if (c > j) col[j] *= rj;
+            if (c == j) col[j] = rc;
         }
     }
     if (bad) {
@@ -120,11 +145,11 @@ __device__ __forceinline__ void dmma884_sub(double& c0, double& c1, double a, do
                  : "+d"(c0), "+d"(c1)
                  : "d"(a), "d"(b));
 }
-__device__ __forceinline__ void potf2_trailing_update(double* S, int jb, int t0, int nbp, int warp, int lane, int nwarps) {
+__device__ __forceinline__ void potf2_trailing_update(double* S, int jb, int t0, int nbp, int first, int lane, int stride) {
     const int nt = (nbp - t0) >> 4;  // 16-wide blocks per side
     const int cnt = nt * (nt + 1) / 2;
     const int g = lane >> 2, t = lane & 3;
-    for (int idx = warp; idx < cnt; idx += nwarps) {
+    for (int idx = first; idx < cnt; idx += stride) {
         int bj = (int)((sqrtf(8.0f * idx + 1.0f) - 1.0f) * 0.5f);
         while (bj * (bj + 1) / 2 > idx) --bj;
         while ((bj + 1) * (bj + 2) / 2 <= idx) ++bj;
@@ -154,6 +179,95 @@ __device__ __forceinline__ void potf2_trailing_update(double* S, int jb, int t0,
     }
 }
 
+// Prologue of the panel kernel: S -= T' T on the block upper triangle, T = the 128 x nb block right above the
+// diagonal block in global memory (the rows of the factor the previous panel's row solve just produced).  With it
+// the rank-128 update of the NEXT diagonal block is part of the panel kernel, so that update of the rest of the
+// block row (a separate launch on another stream) runs beside the panel factorization instead of before it.
+// T passes through shared memory in chunks of 32 rows, transposed (TcT[col * TLD + k], TLD = 36: the staging
+// stores and the m8n8k4 fragment loads are both conflict-free), the next chunk prefetched into registers while
+// the current one feeds the tensor pipe; every warp keeps the accumulators of its (at most three) 16 x 16
+// blocks in registers across the four chunks.
+constexpr int PTLD = 36;
+constexpr int TCHUNK = 32;
+__device__ __forceinline__ void potf2_block_of(int idx, int& bi, int& bj) {
+    bj = (int)((sqrtf(8.0f * idx + 1.0f) - 1.0f) * 0.5f);
+    while (bj * (bj + 1) / 2 > idx) --bj;
+    while ((bj + 1) * (bj + 2) / 2 <= idx) ++bj;
+    bi = idx - bj * (bj + 1) / 2;
+}
+__device__ __noinline__ void potf2_prologue(double* S, double* TcT, const double* __restrict__ T, int64_t ldt, int nb,
+                                            int tid, int warp, int lane) {
+    constexpr int PER = TCHUNK * NB / 512;  // elements of a chunk per thread
+    constexpr int NBLK = (NB / 16) * (NB / 16 + 1) / 2;
+    const int g = lane >> 2, t = lane & 3;
+    double acc[3][2][2][2];
+#pragma unroll
+    for (int b = 0; b < 3; ++b)
+#pragma unroll
+        for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+            for (int ni = 0; ni < 2; ++ni) acc[b][mi][ni][0] = acc[b][mi][ni][1] = 0.0;
+    int i0[3], c0[3];
+#pragma unroll
+    for (int b = 0; b < 3; ++b) {
+        const int idx = warp + 16 * b;
+        int bi = 0, bj = 0;
+        if (idx < NBLK) potf2_block_of(idx, bi, bj);
+        i0[b] = 16 * bi;
+        c0[b] = 16 * bj;
+    }
+    double v[PER];
+    auto fetch = [&](int chunk) {
+#pragma unroll
+        for (int u = 0; u < PER; ++u) {
+            const int e = tid + u * 512, k = e & (TCHUNK - 1), c = e >> 5;
+            v[u] = (c < nb) ? __ldg(T + chunk * TCHUNK + k + (int64_t)c * ldt) : 0.0;
+        }
+    };
+    fetch(0);
+    for (int chunk = 0; chunk < NB / TCHUNK; ++chunk) {
+#pragma unroll
+        for (int u = 0; u < PER; ++u) {
+            const int e = tid + u * 512, k = e & (TCHUNK - 1), c = e >> 5;
+            TcT[c * PTLD + k] = v[u];
+        }
+        __syncthreads();
+        if (chunk + 1 < NB / TCHUNK) fetch(chunk + 1);
+#pragma unroll
+        for (int b = 0; b < 3; ++b) {
+            if (warp + 16 * b >= NBLK) continue;
+            const double* pa0 = TcT + (i0[b] + g) * PTLD + t;
+            const double* pa1 = pa0 + 8 * PTLD;
+            const double* pb0 = TcT + (c0[b] + g) * PTLD + t;
+            const double* pb1 = pb0 + 8 * PTLD;
+#pragma unroll
+            for (int kk = 0; kk < TCHUNK / 4; ++kk) {
+                const double a0 = pa0[4 * kk], a1 = pa1[4 * kk], b0 = pb0[4 * kk], b1 = pb1[4 * kk];
+                dmma884_sub(acc[b][0][0][0], acc[b][0][0][1], a0, b0);
+                dmma884_sub(acc[b][0][1][0], acc[b][0][1][1], a0, b1);
+                dmma884_sub(acc[b][1][0][0], acc[b][1][0][1], a1, b0);
+                dmma884_sub(acc[b][1][1][0], acc[b][1][1][1], a1, b1);
+            }
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int b = 0; b < 3; ++b) {
+        if (warp + 16 * b >= NBLK) continue;
+#pragma unroll
+        for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+            for (int ni = 0; ni < 2; ++ni) {
+                double2* pc = (double2*)(S + (i0[b] + 8 * mi + g) * PLD + c0[b] + 8 * ni + 2 * t);
+                double2 w = *pc;
+                w.x -= acc[b][mi][ni][0];
+                w.y -= acc[b][mi][ni][1];
+                *pc = w;
+            }
+    }
+    __syncthreads();
+}
+
 #ifdef HYB_PROFILE_POTF2
 __device__ long long g_potf2_ts[64];
 __device__ long long g_trsm_ts[16];
@@ -164,10 +278,11 @@ __device__ long long g_trsm_ts[16];
 
 template <bool FAST>
 __global__ void __launch_bounds__(512, 1)
-potf2_kernel(double* __restrict__ A, int64_t lda, int nb, int* __restrict__ info, int k0) {
+potf2_kernel(double* __restrict__ A, int64_t lda, int nb, int* __restrict__ info, int k0, int pending) {
     extern __shared__ double sm[];
     double* S = sm;               // S[r * PLD + c]
     double* rdiag = sm + NB * PLD;  // reciprocals of the current diagonal block's pivots
+    double* TcT = rdiag + IB;       // staging of the prologue (NB x TLD)
     __shared__ int fail;
     const int tid = threadIdx.x, nth = blockDim.x, lane = tid & 31, warp = tid >> 5;
     if (*info != 0) return;  // an earlier panel failed: nothing meaningful to do
@@ -189,27 +304,38 @@ potf2_kernel(double* __restrict__ A, int64_t lda, int nb, int* __restrict__ info
         }
     }
     __syncthreads();
+    // rank-128 update from the previous panel's rows, when the caller left this block out of that update
+    if (pending) potf2_prologue(S, TcT, A - NB, lda, nb, tid, warp, lane);
 
     POTF2_TS(1);
     // identity padding makes every IB x IB step full-size: no tail cases below
     const int nbp = (nb + IB - 1) / IB * IB;
+    // Pipelined over the 16-column blocks: warp 0 owns the serial part.  After the row panel of block b it
+    // updates the next diagonal block alone and factors it at once, while the other 15 warps apply the rest of
+    // the rank-16 update; one barrier later the next row panel finds both done.
+    if (warp == 0) potf2_diag_block<FAST>(S, rdiag, 0, lane, &fail, info, k0);
+    __syncthreads();
+    POTF2_TS(2);
+    if (fail) return;
     for (int jb = 0; jb < nbp; jb += IB) {
-        // (1) IB x IB diagonal block
-        if (warp == 0) potf2_diag_block<FAST>(S, rdiag, jb, lane, &fail, info, k0);
-        __syncthreads();
-        POTF2_TS(2 + 3 * (jb / IB));
-        if (fail) return;
         const int t0 = jb + IB;   // first trailing column
         const int m = nbp - t0;   // trailing size
         if (m <= 0) break;
-        // (2) row panel: U[jb:jb+IB, c] = U11^-T A[jb:jb+IB, c], thread per trailing column
+        // row panel: U[jb:jb+IB, c] = U11^-T A[jb:jb+IB, c], thread per trailing column
         if (tid < m) potf2_row_panel(S, rdiag, jb, t0 + tid);
         __syncthreads();
         POTF2_TS(3 + 3 * (jb / IB));
-        // (3) trailing update
-        potf2_trailing_update(S, jb, t0, nbp, warp, lane, nth >> 5);
+        if (warp == 0) {
+            potf2_trailing_update(S, jb, t0, nbp, 0, lane, 1 << 30);  // block (t0, t0) only
+            __syncwarp();
+            POTF2_TS(4 + 3 * (jb / IB));
+            potf2_diag_block<FAST>(S, rdiag, t0, lane, &fail, info, k0);
+        } else {
+            potf2_trailing_update(S, jb, t0, nbp, warp, lane, (nth >> 5) - 1);
+        }
         __syncthreads();
-        POTF2_TS(4 + 3 * (jb / IB));
+        POTF2_TS(5 + 3 * (jb / IB));
+        if (fail) return;
     }
     POTF2_TS(40);
     // write back: U in the upper triangle, zeros strictly below (the block is workspace)
@@ -225,10 +351,10 @@ void hyb_potf2_dump_ts() {
     long long ts[64];
     cudaDeviceSynchronize();
     cudaMemcpyFromSymbol(ts, g_potf2_ts, sizeof(ts));
-    fprintf(stderr, "potf2 clocks: stage %lld", ts[1] - ts[0]);
-    for (int b = 0; b < NB / IB; ++b)
-        fprintf(stderr, " | diag %lld panel %lld upd %lld", ts[2 + 3 * b] - (b ? ts[1 + 3 * b] : ts[1]),
-                ts[3 + 3 * b] - ts[2 + 3 * b], ts[4 + 3 * b] - ts[3 + 3 * b]);
+    fprintf(stderr, "potf2 clocks: stage+prologue %lld | diag0 %lld", ts[1] - ts[0], ts[2] - ts[1]);
+    for (int b = 0; b + 1 < NB / IB; ++b)
+        fprintf(stderr, " | panel %lld upd0 %lld diag+join %lld", ts[3 + 3 * b] - ts[2 + 3 * b], ts[4 + 3 * b] - ts[3 + 3 * b],
+                ts[5 + 3 * b] - ts[4 + 3 * b]);
     fprintf(stderr, " | writeback %lld | total %lld\n", ts[41] - ts[40], ts[41] - ts[0]);
     long long tt[16];
     cudaMemcpyFromSymbol(tt, g_trsm_ts, sizeof(tt));
@@ -753,6 +879,10 @@ int hyb_chol_alloc(HybChol& ch, int64_t N) {
     HYB_CUDA(cudaStreamCreateWithPriority(&ch.panel_stream, cudaStreamNonBlocking, hi));
     HYB_CUDA(cudaEventCreateWithFlags(&ch.ev_head, cudaEventDisableTiming));
     HYB_CUDA(cudaEventCreateWithFlags(&ch.ev_panel, cudaEventDisableTiming));
+    HYB_CUDA(cudaStreamCreateWithPriority(&ch.upd_stream, cudaStreamNonBlocking, hi));
+    HYB_CUDA(cudaEventCreateWithFlags(&ch.ev_trsm, cudaEventDisableTiming));
+    HYB_CUDA(cudaEventCreateWithFlags(&ch.ev_upd, cudaEventDisableTiming));
+    for (auto& e : ch.ev_far) HYB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     HYB_CUDA(cudaMalloc(&ch.work, sizeof(double) * (N > 0 ? N : 1)));
     ch.epoch = 0;
     return 0;
@@ -765,6 +895,11 @@ void hyb_chol_free(HybChol& ch) {
     if (ch.panel_stream) cudaStreamDestroy(ch.panel_stream);
     if (ch.ev_head) cudaEventDestroy(ch.ev_head);
     if (ch.ev_panel) cudaEventDestroy(ch.ev_panel);
+    if (ch.upd_stream) cudaStreamDestroy(ch.upd_stream);
+    if (ch.ev_trsm) cudaEventDestroy(ch.ev_trsm);
+    if (ch.ev_upd) cudaEventDestroy(ch.ev_upd);
+    for (auto& e : ch.ev_far)
+        if (e) cudaEventDestroy(e);
     cudaFree(ch.work);
     cudaFree(ch.ipiv);
     cudaFree(ch.bk_ws);
@@ -772,26 +907,24 @@ void hyb_chol_free(HybChol& ch) {
     ch = HybChol();
 }
 
-constexpr int PANEL_SMEM = (NB * PLD + IB) * (int)sizeof(double);
+constexpr int PANEL_SMEM = (NB * PLD + IB + NB * PTLD) * (int)sizeof(double);
 constexpr int TRSM_SMEM = TrsmCfg<TRSM_COLS>::SMEM;
 constexpr int TRSV_SMEM = (NB * LDS + NB + 5 * HYB_MAX_RHS * NB) * (int)sizeof(double);
 hyb_counter g_potrf_launches{0};
 
-// Right-looking factorization, two-level blocking with look-ahead.
-//  * Outer blocks of OB columns (OB = 128 * 2^k, default 256, HYB_POTRF_OB): the trailing matrix
-//    is updated once per outer block with a rank-OB gemm, so its N^2/2 entries are read and
-//    written N/OB times instead of N/128 times (at K = 128 the update is bound by that traffic and
-//    by the number of launches, not by the DMMA pipe).
-//  * Inside an outer block the 128-column panels are factored left to right (potf2 + row trsm),
-//    each followed by a rank-128 update of the remaining block rows OF THE OUTER BLOCK only.
-//  * Look-ahead: after an outer block is done, the next outer block's rows get their rank-OB
-//    update first; the (latency-bound) panels of that block then run on a second, high-priority
-//    stream while the bulk of the rank-OB update proceeds on the main stream.
+// Right-looking factorization, two-level blocking, look-ahead of two outer blocks.
+//  * Outer blocks of OB columns (default 512, HYB_POTRF_OB): everything further than one outer block below a
+//    block is updated once per outer block with a rank-OB contraction, so those entries are read and written
+//    N/OB times instead of N/128 times (a K = 128 update runs at half the DMMA rate of a K = 512 one: its
+//    128 x 128 tile costs as much in launch, pipeline fill and read-modify-write of C as in DMMA work).
+//  * Inside an outer block the 128-column panels are factored left to right: panel kernel (diagonal block,
+//    including the rank-128 update the previous panel owes it) -> row solve -> rank-128 "near" update of the
+//    rest of the outer block and of the whole next one.  See the choreography comment in hyb_potrf.
 // The strictly lower triangle of ch.F is workspace (the rectangular updates write there).
 static int potrf_outer_block() {
     static int ob = 0;
     if (ob == 0) {
-        ob = 256;
+        ob = 512;
         const char* e = getenv("HYB_POTRF_OB");
         if (e) {
             const int v = atoi(e);
@@ -848,17 +981,22 @@ int hyb_potrf(cudaStream_t st, HybChol& ch, int* info_out) {
     ch.kind = 0;
     cudaStream_t sp = ch.panel_stream;
     HYB_CUDA(cudaMemsetAsync(ch.info, 0, sizeof(int), st));
-    auto panel = [&](cudaStream_t s, int64_t k0) -> int {
+    cudaStream_t su = ch.upd_stream;
+    auto factor_block = [&](int64_t k0, int pending) -> int {  // diagonal block, on the panel stream
         const int nb = (int)((N - k0 < NB) ? (N - k0) : NB);
         double* A11 = ch.F + k0 + k0 * ld;
         if (fast)
-            potf2_kernel<true><<<1, 512, PANEL_SMEM, s>>>(A11, ld, nb, ch.info, (int)k0);
+            potf2_kernel<true><<<1, 512, PANEL_SMEM, sp>>>(A11, ld, nb, ch.info, (int)k0, pending);
         else
-            potf2_kernel<false><<<1, 512, PANEL_SMEM, s>>>(A11, ld, nb, ch.info, (int)k0);
+            potf2_kernel<false><<<1, 512, PANEL_SMEM, sp>>>(A11, ld, nb, ch.info, (int)k0, pending);
         ++g_potrf_launches;
         HYB_CUDA(cudaGetLastError());
+        return 0;
+    };
+    auto solve_row = [&](int64_t k0) -> int {  // the block row right of it, on the panel stream
+        const int nb = (int)((N - k0 < NB) ? (N - k0) : NB);
         const int64_t n2 = N - k0 - nb;
-        if (n2 > 0) HYB_CHECK(launch_row_trsm(s, A11, ld, nb, ch.F + k0 + (k0 + nb) * ld, ld, n2));
+        if (n2 > 0) HYB_CHECK(launch_row_trsm(sp, ch.F + k0 + k0 * ld, ld, nb, ch.F + k0 + (k0 + nb) * ld, ld, n2));
         return 0;
     };
     // HYB_POTRF_TRACE=1: time stamps (CUDA events) of every outer block's phases on both streams, printed
@@ -874,60 +1012,82 @@ int hyb_potrf(cudaStream_t st, HybChol& ch, int* info_out) {
     };
     stamp(st);
     HYB_CUDA(cudaEventRecord(ch.ev_head, st));
-    // Once the trailing matrix is small the bulk update no longer hides the (latency-bound) panel chain, and the
-    // in-block rank-128 update plus the rank-OB head update are two serial launches where one rank-128 head
-    // update would do: the last `late` columns use outer blocks of 128 (HYB_POTRF_LATE, default 3072; 0 = off).
+    // Outer block width by remaining size (measurement knobs; both off by default: with the near / far split
+    // below the serial chain is the same whatever the width, and 512 everywhere measured best at N = 465 ... 16384):
+    // HYB_POTRF_LATE = n: blocks of 128 once n or fewer columns remain.
     static const int64_t late = [] {
         const char* e = getenv("HYB_POTRF_LATE");
-        return (int64_t)(e ? atoi(e) : 3072);
+        return (int64_t)(e ? atoi(e) : 0);
     }();
-    // ... and while the trailing matrix is large the step is bound by the bulk update, which runs closer to the
-    // DMMA peak the longer its contraction: outer blocks of 2 OB there (HYB_POTRF_EARLY, default 5120; 0 = off).
+    // HYB_POTRF_EARLY = n: blocks of 2 OB while more than n columns remain.
     static const int64_t early = [] {
         const char* e = getenv("HYB_POTRF_EARLY");
-        return (int64_t)(e ? atoi(e) : 5120);
+        return (int64_t)(e ? atoi(e) : 0);
     }();
     auto block_width = [&](int64_t remaining) -> int64_t {
         if (remaining <= late) return NB;
         if (early > 0 && remaining > early) return 2 * OB;
         return OB;
     };
-    int64_t obc = OB;
-    for (int64_t K0 = 0; K0 < N; K0 += obc) {
-        obc = block_width(N - K0);
-        const int64_t ob = (N - K0 < obc) ? (N - K0) : obc;
-        const int64_t K1 = K0 + ob;
-        // the panels of this outer block, on the panel stream, once its rows are up to date
-        HYB_CUDA(cudaStreamWaitEvent(sp, ch.ev_head, 0));
-        stamp(sp);  // [1 + 5b] panels start
-        for (int64_t j0 = K0; j0 < K1; j0 += NB) {
-            HYB_CHECK(panel(sp, j0));
-            const int64_t r1 = j0 + NB;
-            if (r1 < K1) {  // rank-128 update of the outer block's remaining rows: all columns >= r1
-                const double* U = ch.F + j0 + r1 * ld;
-                HYB_CHECK(hyb_gemm_tn(sp, K1 - r1, N - r1, NB, -1.0, U, ld, U, ld, 1.0, ch.F + r1 + r1 * ld, ld, 0));
-            }
+    // Choreography.  Three streams: `sp` (high priority) carries the serial chain  panel kernel -> row solve
+    // per 128 columns; `su` (high priority) the rank-128 "near" updates; `st` the rank-ob updates of everything
+    // further away.  Outer blocks b = [K0, K1), next block [K1, K2), the one after [K2, K3):
+    //  * near(j0): right after the row solve of panel j0, its 128 rows update rows [j0 + 128, K2) -- the rest of
+    //    its own outer block and ALL rows of the next one -- in columns >= j0 + 256.  The tile column it leaves
+    //    out holds the next diagonal block, which the next panel kernel updates itself (potf2_prologue), so that
+    //    kernel starts at once and runs beside near(j0); only the next row solve waits for near(j0).
+    //  * far(b), after the last row solve of block b: rank-ob update of rows [K2, K3) first (`ev_far[b % 3]`:
+    //    near updates from block b + 1 reach into those rows and must follow it), then of the triangle below K3.
+    // The chain never waits for a far update younger than two outer blocks, so the latency-bound chain and the
+    // DMMA-bound far updates overlap instead of alternating, and the chain is the same whatever `ob` is.
+    {
+        std::vector<int64_t> edge{0};  // outer block boundaries
+        while (edge.back() < N) {
+            const int64_t w = block_width(N - edge.back());
+            edge.push_back(edge.back() + w < N ? edge.back() + w : N);
         }
-        stamp(sp);  // [2 + 5b] panels end
-        HYB_CUDA(cudaEventRecord(ch.ev_panel, sp));
-        HYB_CUDA(cudaStreamWaitEvent(st, ch.ev_panel, 0));
-        stamp(st);  // [3 + 5b] main stream has the panels (and its own previous bulk update)
-        const int64_t n2 = N - K1;  // trailing size
-        if (n2 <= 0) break;
-        const double* U12 = ch.F + K0 + K1 * ld;  // ob x n2: block rows of this outer block
-        double* A22 = ch.F + K1 + K1 * ld;
-        // look-ahead: the next outer block's rows first
-        const int64_t obn = block_width(n2);  // width of the next outer block
-        const int64_t nh = n2 < obn ? n2 : obn;
-        HYB_CHECK(hyb_gemm_tn(st, nh, n2, ob, -1.0, U12, ld, U12, ld, 1.0, A22, ld, 0));
-        stamp(st);  // [4 + 5b] head update done
-        HYB_CUDA(cudaEventRecord(ch.ev_head, st));
-        // bulk: everything below, upper triangle only
-        const int64_t n3 = n2 - nh;
-        if (n3 > 0)
-            HYB_CHECK(hyb_gemm_tn(st, n3, n3, ob, -1.0, U12 + nh * ld, ld, U12 + nh * ld, ld, 1.0, A22 + nh + nh * ld, ld,
-                                  HYB_GEMM_UPPER));
-        stamp(st);  // [5 + 5b] bulk update done
+        const int64_t nblocks = (int64_t)edge.size() - 1;
+        auto edge_at = [&](int64_t i) { return i < (int64_t)edge.size() ? edge[i] : N; };
+        bool upd_pending = false;  // a near update the next row solve has to wait for
+        HYB_CUDA(cudaStreamWaitEvent(sp, ch.ev_head, 0));  // the matrix and the cleared info word
+        for (int64_t b = 0; b < nblocks; ++b) {
+            const int64_t K0 = edge[b], K1 = edge[b + 1], K2 = edge_at(b + 2), K3 = edge_at(b + 3), ob = K1 - K0;
+            if (b >= 2) HYB_CUDA(cudaStreamWaitEvent(sp, ch.ev_far[(b - 2) % 3], 0));  // far(b - 2) reached these rows
+            stamp(sp);  // [1 + 5b] panels start
+            bool su_has_far = (b == 0);  // `su` has waited for far(b - 1), which reached the next block's rows
+            for (int64_t j0 = K0; j0 < K1; j0 += NB) {
+                HYB_CHECK(factor_block(j0, j0 > 0 ? 1 : 0));
+                if (upd_pending) HYB_CUDA(cudaStreamWaitEvent(sp, ch.ev_upd, 0));
+                upd_pending = false;
+                HYB_CHECK(solve_row(j0));
+                const int64_t r1 = j0 + NB, nc = N - r1 - NB, M = K2 - r1;
+                if (M > 0 && nc > 0) {
+                    HYB_CUDA(cudaEventRecord(ch.ev_trsm, sp));
+                    HYB_CUDA(cudaStreamWaitEvent(su, ch.ev_trsm, 0));
+                    if (!su_has_far) HYB_CUDA(cudaStreamWaitEvent(su, ch.ev_far[(b - 1) % 3], 0));
+                    su_has_far = true;
+                    const double* U = ch.F + j0 + r1 * ld;
+                    HYB_CHECK(hyb_gemm_tn(su, M, nc, NB, -1.0, U, ld, U + NB * ld, ld, 1.0, ch.F + r1 + (r1 + NB) * ld, ld, 0));
+                    HYB_CUDA(cudaEventRecord(ch.ev_upd, su));
+                    upd_pending = true;
+                }
+            }
+            stamp(sp);  // [2 + 5b] panels end
+            HYB_CUDA(cudaEventRecord(ch.ev_panel, sp));
+            HYB_CUDA(cudaStreamWaitEvent(st, ch.ev_panel, 0));
+            stamp(st);  // [3 + 5b] main stream has the panels (and its own previous far update)
+            if (K2 < N) {
+                const double* Ub = ch.F + K0 + K2 * ld;
+                HYB_CHECK(hyb_gemm_tn(st, K3 - K2, N - K2, ob, -1.0, Ub, ld, Ub, ld, 1.0, ch.F + K2 + K2 * ld, ld, 0));
+            }
+            HYB_CUDA(cudaEventRecord(ch.ev_far[b % 3], st));
+            stamp(st);  // [4 + 5b] rows of block b + 2 done
+            if (K3 < N) {
+                const double* Ub = ch.F + K0 + K3 * ld;
+                HYB_CHECK(hyb_gemm_tn(st, N - K3, N - K3, ob, -1.0, Ub, ld, Ub, ld, 1.0, ch.F + K3 + K3 * ld, ld, HYB_GEMM_UPPER));
+            }
+            stamp(st);  // [5 + 5b] far update done
+        }
     }
     if (trace) {
         cudaStreamSynchronize(sp);

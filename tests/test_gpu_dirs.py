@@ -55,6 +55,12 @@ def _capture_state(model_fn, n_iters, **kw):
     return s
 
 
+# The two-solver protocol comparisons below run under the tolerances of the reference's own benchmark
+# protocol (benchmarks/natvsext/run.jl:44-60): at the default eps^0.5 tolerances the last iterations of
+# block_multicone sit on the rounding floor, where the iteration count depends on the last bits of every
+# kernel, and "the same solve on two paths" stops being a well-posed comparison.
+KW = dict(tol_rel_opt=1e-7, tol_feas=1e-7, tol_abs_opt=1e-10, tol_infeas=1e-10)
+
 MODELS = {
     "block_multicone": lambda: instances.block_multicone(N=96, seed=3, psd_side=8),
     "linearopt": lambda: instances.linearopt(m=30, n=80, seed=1),
@@ -145,10 +151,10 @@ def test_multi_rhs_wavefront_solves(N, R):
 def test_device_line_search_matches_host_loop(name, monkeypatch):
     """check_cone_points on the device (hyb_search_gates / hyb_search_check) takes the same
     accept / reject decisions as the host loop of search.jl:72-162."""
-    dev = make_gpu_solver(0, trace=True)
+    dev = make_gpu_solver(0, trace=True, **KW)
     assert dev.syssolver.device_search
     monkeypatch.setenv("HYB_HOST_SEARCH", "1")
-    host = make_gpu_solver(0, trace=True)
+    host = make_gpu_solver(0, trace=True, **KW)
     assert not host.syssolver.device_search
     for s in (dev, host):
         s.load(MODELS[name]())
@@ -169,10 +175,10 @@ def test_device_line_search_matches_host_loop(name, monkeypatch):
 def test_device_resident_stepper_matches_host_vector_protocol(name, monkeypatch):
     """hyb_step_* (iterate, right-hand-side builders, point update on the device) against the same solve with
     the host building the right-hand sides and holding the iterate (steppers/common.jl:14-119, combined.jl:129-177)."""
-    dev = make_gpu_solver(0, trace=True)
+    dev = make_gpu_solver(0, trace=True, **KW)
     assert dev.syssolver.device_stepper
     monkeypatch.setenv("HYB_HOST_STEPPER", "1")
-    host = make_gpu_solver(0, trace=True)
+    host = make_gpu_solver(0, trace=True, **KW)
     assert not host.syssolver.device_stepper and host.syssolver.device_search
     for s in (dev, host):
         s.load(MODELS[name]())
@@ -250,9 +256,12 @@ def test_directions_against_the_oracle_at_the_same_iterate(name, n_iters, monkey
             d.vec[:] = stp.dir.vec
             out.append((rhs, d))
         dirs[id(s)] = out
-    for (rhs_c, d_c), (rhs_g, d_g) in zip(dirs[id(cpu)], dirs[id(gpu)]):
+    for i, ((rhs_c, d_c), (rhs_g, d_g)) in enumerate(zip(dirs[id(cpu)], dirs[id(gpu)])):
         scale_r = np.max(np.abs(rhs_c)) + 1e-300
-        assert np.max(np.abs(rhs_g - rhs_c)) <= 1e-9 * scale_r  # oracle products (grad, H d, dder3) agree
+        # oracle products agree: grad alone in the cent / pred right-hand sides; the adjustment right-hand sides
+        # are dder3 of the backend's OWN cent / pred direction, so they inherit those directions' agreement
+        # (1e-6 of their scale, below) through a product that is linear in it
+        assert np.max(np.abs(rhs_g - rhs_c)) <= (1e-9 if i < 2 else 1e-7) * scale_r
         scale = np.max(np.abs(d_c.vec)) + 1e-300
         assert np.max(np.abs(d_g.vec - d_c.vec)) <= 1e-6 * scale
         # both satisfy their 6 x 6 system equally well.  Each residual is evaluated with the backend's own
