@@ -95,6 +95,7 @@ static void free_model(hyb_ctx* c) {
         hybi_cones_free(c->cones);
     }
     hyb_dirs_free(c);
+    hyb_symindef_free(c);
     for (auto& r : c->stage) cudaFree(r.buf);
     c->stage.clear();
     if (c->peer_ipc_base) cudaIpcCloseMemHandle(c->peer_ipc_base);
@@ -971,12 +972,15 @@ int hyb_bench_gemm_tn(hyb_ctx* c, int64_t M, int64_t N, int64_t K, int upper, in
     fill_pattern_kernel<<<dim3((unsigned)((K + 255) / 256), (unsigned)N), 256, 0, c->st>>>(K, N, ldA, B, 0);
     HYB_CUDA(cudaMemsetAsync(C, 0, sizeof(double) * ldC * N, c->st));
     const int flags = upper ? HYB_GEMM_UPPER : 0;
+    // HYB_BENCH_GEMM_BETA=1: time the update form C += A'B (the Cholesky's trailing updates read C back)
+    const char* be = getenv("HYB_BENCH_GEMM_BETA");
+    const double beta = be ? atof(be) : 0.0;
     int rc = 0;
-    for (int i = 0; i < 2 && rc == 0; ++i) rc = hyb_gemm_tn(c->st, M, N, K, 1.0, A, ldA, upper ? A : B, ldA, 0.0, C, ldC, flags);
+    for (int i = 0; i < 2 && rc == 0; ++i) rc = hyb_gemm_tn(c->st, M, N, K, 1.0, A, ldA, upper ? A : B, ldA, beta, C, ldC, flags);
     if (rc == 0) {
         cudaEventRecord(c->ev0, c->st);
         for (int i = 0; i < reps && rc == 0; ++i)
-            rc = hyb_gemm_tn(c->st, M, N, K, 1.0, A, ldA, upper ? A : B, ldA, 0.0, C, ldC, flags);
+            rc = hyb_gemm_tn(c->st, M, N, K, 1.0, A, ldA, upper ? A : B, ldA, beta, C, ldC, flags);
         cudaEventRecord(c->ev1, c->st);
         cudaError_t e = cudaEventSynchronize(c->ev1);
         float ms = 0;

@@ -1127,6 +1127,7 @@ int hybi_cones_prod(cudaStream_t st, HybCones& cs, int which, const double* arr,
         if (which == 4) op = b.use_dual ? HYB_OP_INV_HESS : HYB_OP_HESS;
         else if (which == 5 || (which == 7 && cs.block_sqrt[bi])) op = b.use_dual ? HYB_OP_INV_SQRT_HESS : HYB_OP_SQRT_HESS;
         else if (which == 7) op = b.use_dual ? HYB_OP_INV_HESS : HYB_OP_HESS;
+        else if (which == 8) op = b.use_dual ? HYB_OP_HESS : HYB_OP_INV_HESS;  // z-z block of the symmetric-indefinite system
         else if (which == 6)  // hess_prod_slow! is hess_prod! except for the WSOS cones (Cones.jl:229-231)
             op = (b.type == HYB_WSOSINTERPNONNEGATIVE || b.type == HYB_WSOSINTERPPOSSEMIDEFTRI) ? 6 : HYB_OP_HESS;
         else op = which;

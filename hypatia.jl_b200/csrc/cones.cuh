@@ -66,7 +66,8 @@ int hybi_cones_reduce(cudaStream_t st, HybCones& cs, int use_max_prox, int* all_
 // prod = op(H) * arr for every cone; arr/prod are q x m column-major device arrays (ld >= q).
 // which: 0 hess, 1 inv_hess, 2 sqrt_hess, 3 inv_sqrt_hess, 4 block (inv_hess for dual-barrier cones, else hess),
 //        5 block sqrt (inv_sqrt for dual-barrier cones, else sqrt), 6 hess_prod_slow,
-//        7 Schur assembly: per block 5 or 4 as cs.block_sqrt says (qrchol.jl:228-252)
+//        7 Schur assembly: per block 5 or 4 as cs.block_sqrt says (qrchol.jl:228-252),
+//        8 the inverse of 4 (hess for dual-barrier cones, else inv_hess): symindef.jl:255-259
 int hybi_cones_prod(cudaStream_t st, HybCones& cs, int which, const double* arr, int64_t lda, double* prod, int64_t ldp,
                    int64_t m);
 int hybi_cones_dder3(cudaStream_t st, HybCones& cs, const double* dir, double* out);

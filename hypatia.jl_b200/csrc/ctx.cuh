@@ -16,6 +16,8 @@ struct HybStageRun {
 };
 
 // ----------------------------------------------------------------------------- context
+struct HybSymIndef;  // symindef.cu
+
 struct hyb_ctx {
     int device = 0;
     cudaStream_t st = nullptr;
@@ -48,6 +50,7 @@ struct hyb_ctx {
     void* peer_ipc_base = nullptr;  // non-root: pointer returned by cudaIpcOpenMemHandle
     int peer_world = 0, peer_rank = 0;
     HybDirs* dirs = nullptr;  // direction engine state (allocated by hyb_dirs_setup)
+    HybSymIndef* symindef = nullptr;  // dense symmetric-indefinite system solver state (hyb_symindef_load)
     std::vector<HybStageRun> stage;
     // contexts that only assemble partial Schur matrices into another context's memory (multi.cu, rootworker.py)
     bool want_assemble_only = false;  // request: skip the Schur matrix and the Cholesky workspace at load
@@ -77,3 +80,4 @@ int hyb_model_load_impl(hyb_ctx* c, int64_t q, int64_t N, const double* GQ2, int
                         const hyb_cone_desc* descs, hyb_ctx* borrow, int64_t borrow_row);
 int hyb_schur_assemble_into(hyb_ctx* c, double* Sdst, double* t_assemble_ms);
 void hyb_dirs_free(hyb_ctx* c);
+void hyb_symindef_free(hyb_ctx* c);

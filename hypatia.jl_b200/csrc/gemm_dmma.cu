@@ -224,13 +224,16 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         return;
     }
     const bool vec_ok = (flags & HYB_GEMM_CVEC) != 0;
+    // EPI row pairs per thread and round: the accumulators already sit in shared memory, so registers are free
+    // to keep 16 loads of C in flight (two exposed round trips per tile instead of four)
+    constexpr int EPI = 16;
 #pragma unroll 1
-    for (int round = 0; round < 4; ++round) {
-        double2 cv[8];
+    for (int round = 0; round < 32 / EPI; ++round) {
+        double2 cv[EPI];
         // item = (column, row pair); consecutive threads take consecutive row pairs of a column
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const int idx = (round * 8 + j) * 256 + ctid;
+        for (int j = 0; j < EPI; ++j) {
+            const int idx = (round * EPI + j) * 256 + ctid;
             const int col = idx >> 6, row = (idx & 63) * 2;
             const int grow = m0 + row, gcol = n0 + col;
             cv[j] = make_double2(0.0, 0.0);
@@ -247,8 +250,8 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
         }
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const int idx = (round * 8 + j) * 256 + ctid;
+        for (int j = 0; j < EPI; ++j) {
+            const int idx = (round * EPI + j) * 256 + ctid;
             const int col = idx >> 6, row = (idx & 63) * 2;
             const int grow = m0 + row, gcol = n0 + col;
             if (gcol < N) {

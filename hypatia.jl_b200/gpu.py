@@ -433,6 +433,57 @@ class B200QRCholSystemSolver(QRCholSystemSolver):
         pass
 
 
+class B200SymIndefDenseSystemSolver(B200QRCholSystemSolver):
+    """Drop-in for SymIndefDenseSystemSolver (symindef.jl:216-280) on one B200: cone oracles, the assembly of
+    the (n + q) x (n + q) system, its rook-pivoted Bunch-Kaufman factorization and the solves run on the device
+    (hyb_symindef_*); the stepper follows the reference's one-direction-at-a-time call pattern
+    (systemsolvers/common.jl) on host vectors."""
+
+    def __init__(self, ctx: Context):
+        super().__init__(ctx, batched_dirs=False)
+        self.device_search = self.device_stepper = False
+
+    def load(self, solver) -> None:  # symindef.jl:231-247
+        super().load(solver)
+        self.ctx.check(self.lib.hyb_symindef_load(self.ctx.ptr), "hyb_symindef_load")
+
+    def update_lhs(self, solver) -> None:  # symindef.jl:249-270
+        solver.cones._sync()
+        tf, kind = C.c_double(0), C.c_int(0)
+        rc = self.ctx.check(self.lib.hyb_symindef_update(self.ctx.ptr, C.byref(tf), C.byref(kind)), "hyb_symindef_update")
+        self.time_fact_ms += tf.value
+        self.num_updates += 1
+        self.last_fact_kind = kind.value
+        solver.time_upfact += tf.value * 1e-3
+        if rc > 0:
+            print("symmetric linear system factorization failed")
+        self.solve_subsystem3(solver, self.sol_const, self.rhs_const)
+
+    def solve_subsystem4(self, solver, sol, rhs) -> None:  # common.jl:161-189, no QRChol constant-system laziness
+        QRCholSystemSolver.solve_subsystem4(self, solver, sol, rhs)
+
+    def setup_rhs3(self, solver, rhs, sol, rhs_sub) -> None:  # symindef.jl:38-62
+        cones = solver.cones
+        prod = cones.inv_hess_prod(rhs.s)
+        if cones.any_dual:
+            rhs_sub.z[:] = np.where(cones.dual_rows, -rhs.z - rhs.s, -prod - rhs.z)
+        else:
+            rhs_sub.z[:] = -prod - rhs.z
+
+    def solve_subsystem3(self, solver, sol, rhs) -> None:  # symindef.jl:272-280
+        solver.cones._sync()
+        r = f64(rhs.vec)
+        out = np.empty_like(r)
+        self.ctx.check(self.lib.hyb_symindef_solve(self.ctx.ptr, dptr(r), dptr(out), 1), "hyb_symindef_solve")
+        sol.vec[:] = out
+
+    def system_matrix(self) -> np.ndarray:
+        d = self.N + self.q
+        out = np.zeros((d, d), order="F")
+        self.ctx.check(self.lib.hyb_symindef_get(self.ctx.ptr, dptr(out)), "hyb_symindef_get")
+        return out
+
+
 class B200MultiQRCholSystemSolver(B200QRCholSystemSolver):
     """`B200QRCholSystemSolver{Float64}(devices = 0:7)` of INTEGRATION.md: one host process, several GPUs, through
     hyb_multi_* alone (no torch.distributed).  Only `load` and `update_lhs` differ from the single-GPU solver:
@@ -472,7 +523,7 @@ class B200MultiQRCholSystemSolver(B200QRCholSystemSolver):
 
 
 def make_gpu_solver(device: int = 0, dist=None, use_peer: bool = True, mode: str = "rootworker", batched_dirs: bool = True,
-                    devices=None, **solver_kwargs):
+                    devices=None, syssolver: str = "qrchol", **solver_kwargs):
     """Solver wired to the GPU backends (what `Hypatia.Optimizer(syssolver =
     B200QRCholSystemSolver{Float64}(), use_dense_model = true)` selects in Julia).
 
@@ -482,6 +533,13 @@ def make_gpu_solver(device: int = 0, dist=None, use_peer: bool = True, mode: str
     instead drives several GPUs from THIS process through hyb_multi_* (no torch.distributed at all)."""
     from .host.solver import Solver
 
+    if syssolver == "symindef":  # syssolver = SymIndefDenseSystemSolver{Float64}() in Julia; one GPU
+        ctx = Context(device)
+        ss = B200SymIndefDenseSystemSolver(ctx)
+        solver = Solver(ss.cones_factory, ss, **solver_kwargs)
+        attach_gpu_qr(solver, ctx)
+        return solver
+    assert syssolver == "qrchol", syssolver
     if dist is not None and dist.get_world_size() > 1 and mode == "rootworker":
         from .rootworker import make_rootworker_solver
 

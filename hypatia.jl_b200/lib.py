@@ -110,6 +110,10 @@ SIGNATURES = {
         [C.c_void_p, C.c_int64, c_double_p, C.c_int64, c_int_p, c_double_p, C.c_int64, C.c_int64, c_int_p],
     ),
     "hyb_schur_set": (C.c_int, [C.c_void_p, c_double_p]),
+    "hyb_symindef_load": (C.c_int, [C.c_void_p]),
+    "hyb_symindef_update": (C.c_int, [C.c_void_p, c_double_p, c_int_p]),
+    "hyb_symindef_solve": (C.c_int, [C.c_void_p, c_double_p, c_double_p, C.c_int64]),
+    "hyb_symindef_get": (C.c_int, [C.c_void_p, c_double_p]),
     "hyb_gemv_n_noalloc": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
     "hyb_stats": (C.c_int, [C.c_void_p, C.c_int, c_double_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "hyb_last_schur_timings": (C.c_int, [C.c_void_p, c_double_p, c_double_p, c_double_p]),

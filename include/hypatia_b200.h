@@ -225,6 +225,22 @@ int hyb_symm_solve(hyb_ctx* ctx, int64_t N, double* A, int64_t lda, int* ipiv, d
  * overwrite, and the tests use it to drive posdef_fact_copy!'s fallback chain with an indefinite matrix. */
 int hyb_schur_set(hyb_ctx* ctx, const double* lhs);
 
+/* ---- dense symmetric-indefinite system solver ------------------------------------------
+ * Drop-in for SymIndefDenseSystemSolver (src/Solvers/systemsolvers/symindef.jl:216-280) on the model loaded by
+ * hyb_model_load (reduced: p = 0).  The (n + q) x (n + q) system  [0 G'; G -H~]  (symindef.jl:8-37; H~_k =
+ * inv_hess for primal-barrier cones, hess for dual-barrier ones, :255-259) lives on the device.
+ *   hyb_symindef_load    load (:231-247): storage for the system and its factorization.
+ *   hyb_symindef_update  update_lhs (:249-265) for the point last loaded into the cones: assemble, then
+ *                        symm_fact_copy! (dense.jl:205-219): rook-pivoted Bunch-Kaufman, on failure the diagonal
+ *                        shift and a second attempt.  *fact_kind = 1, 2 (shifted) or -1 (failed; returns 1).
+ *   hyb_symindef_solve   solve_subsystem3 (:272-280): sol = fact \ rhs for nrhs <= 4 host vectors of length n + q
+ *                        laid out [x; z] (column-major, leading dimension n + q).
+ *   hyb_symindef_get     the assembled system (upper triangle valid, (n + q)^2 doubles) for the parity tests. */
+int hyb_symindef_load(hyb_ctx* ctx);
+int hyb_symindef_update(hyb_ctx* ctx, double* t_ms, int* fact_kind);
+int hyb_symindef_solve(hyb_ctx* ctx, const double* rhs, double* sol, int64_t nrhs);
+int hyb_symindef_get(hyb_ctx* ctx, double* lhs);
+
 /* ---- several GPUs from one host process ----------------------------------------------
  * a Julia host uses a whole node with ccalls alone.  The cones are partitioned by block over the
  * devices; each device assembles the partial Schur matrix of its cones (update_lhs_fact, qrchol.jl:209-254, is

@@ -37,9 +37,9 @@ def _dp(a):
     return a.ctypes.data_as(C.POINTER(C.c_double))
 
 
-def dsytrf_rook(A: np.ndarray):
-    """Upper-triangle rook Bunch-Kaufman of symmetric A.  Returns (ldu, ipiv, info), LAPACK conventions
-    (ipiv 1-based, negative entries mark 2 x 2 pivots)."""
+def dsytrf_rook(A: np.ndarray, uplo: bytes = b"U"):
+    """Rook Bunch-Kaufman of symmetric A from its `uplo` triangle.  Returns (ldu, ipiv, info), LAPACK
+    conventions (ipiv 1-based, negative entries mark 2 x 2 pivots)."""
     lib = _load()
     a = np.array(A, dtype=np.float64, order="F")
     n = a.shape[0]
@@ -47,12 +47,12 @@ def dsytrf_rook(A: np.ndarray):
     info = C.c_int(0)
     lwork = max(1, 64 * n)
     work = np.zeros(lwork)
-    lib.scipy_dsytrf_rook_(C.c_char_p(b"U"), _i(n), _dp(a), _i(max(n, 1)), ipiv.ctypes.data_as(C.POINTER(C.c_int)), _dp(work),
+    lib.scipy_dsytrf_rook_(C.c_char_p(uplo), _i(n), _dp(a), _i(max(n, 1)), ipiv.ctypes.data_as(C.POINTER(C.c_int)), _dp(work),
                            _i(lwork), C.byref(info), C.c_size_t(1))
     return a, ipiv[:n], int(info.value)
 
 
-def dsytrs_rook(ldu: np.ndarray, ipiv: np.ndarray, B: np.ndarray) -> np.ndarray:
+def dsytrs_rook(ldu: np.ndarray, ipiv: np.ndarray, B: np.ndarray, uplo: bytes = b"U") -> np.ndarray:
     lib = _load()
     b = np.array(B, dtype=np.float64, order="F")
     one_d = b.ndim == 1
@@ -61,7 +61,7 @@ def dsytrs_rook(ldu: np.ndarray, ipiv: np.ndarray, B: np.ndarray) -> np.ndarray:
     n, nrhs = b.shape
     info = C.c_int(0)
     ip = np.ascontiguousarray(ipiv, dtype=np.int32)
-    lib.scipy_dsytrs_rook_(C.c_char_p(b"U"), _i(n), _i(nrhs), _dp(ldu), _i(max(n, 1)), ip.ctypes.data_as(C.POINTER(C.c_int)),
+    lib.scipy_dsytrs_rook_(C.c_char_p(uplo), _i(n), _i(nrhs), _dp(ldu), _i(max(n, 1)), ip.ctypes.data_as(C.POINTER(C.c_int)),
                            _dp(b), _i(max(n, 1)), C.byref(info), C.c_size_t(1))
     assert info.value == 0
     return b[:, 0] if one_d else b
