@@ -33,7 +33,12 @@ __device__ __forceinline__ double red_sum(double v) {
 // ------------------------------------------------------------------ Nonnegative
 __global__ void nonneg_update_kernel(int64_t n, const double* __restrict__ primal, const double* __restrict__ dual_in,
                                      double scal, double irtmu, double* __restrict__ point, double* __restrict__ dual,
-                                     double* __restrict__ grad, int* __restrict__ flag, double* __restrict__ prox) {
+                                     double* __restrict__ grad, int* __restrict__ flag, double* __restrict__ prox,
+                                     const double* __restrict__ ctl) {
+    if (ctl) {  // speculative line search (dirs.cu): a decided sequence skips; the scaling comes from the device
+        if (ctl[0] != 0.0) return;
+        scal = irtmu = ctl[1];
+    }
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const double p = scal * primal[i], d = dual_in[i];
@@ -105,7 +110,12 @@ template <int TYPE, bool WARP>
 __global__ void soc_update_kernel(int64_t count, int d, int64_t offset, int64_t cone0, const double* __restrict__ primal,
                                   const double* __restrict__ dual_in, double scal, double irtmu,
                                   double* __restrict__ point, double* __restrict__ dual, double* __restrict__ grad,
-                                  double* __restrict__ aux, int* __restrict__ flag, double* __restrict__ prox) {
+                                  double* __restrict__ aux, int* __restrict__ flag, double* __restrict__ prox,
+                                  const double* __restrict__ ctl) {
+    if (ctl) {  // speculative line search (dirs.cu): a decided sequence skips; the scaling comes from the device
+        if (ctl[0] != 0.0) return;
+        scal = irtmu = ctl[1];
+    }
     const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t c = WARP ? (gt >> 5) : gt;
     const int i0 = WARP ? (int)(gt & 31) : 0;
@@ -446,7 +456,12 @@ template <bool WARP>
 __global__ void ninf_update_kernel(int64_t count, int d, int64_t offset, int64_t cone0, const double* __restrict__ primal,
                                    const double* __restrict__ dual_in, double scal, double irtmu,
                                    double* __restrict__ point, double* __restrict__ dual, double* __restrict__ grad,
-                                   double* __restrict__ aux, int* __restrict__ flag, double* __restrict__ prox) {
+                                   double* __restrict__ aux, int* __restrict__ flag, double* __restrict__ prox,
+                                   const double* __restrict__ ctl) {
+    if (ctl) {  // speculative line search (dirs.cu): a decided sequence skips; the scaling comes from the device
+        if (ctl[0] != 0.0) return;
+        scal = irtmu = ctl[1];
+    }
     const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t c = WARP ? (gt >> 5) : gt;
     const int i0 = WARP ? (int)(gt & 31) : 0;
@@ -734,8 +749,12 @@ __global__ void __launch_bounds__(PSD_WARPS * 32)
 psd_update_kernel(int64_t count, int side, int64_t offset, int64_t mat_off, const double* __restrict__ primal,
                   const double* __restrict__ dual_in, double scal, double irtmu, double* __restrict__ point,
                   double* __restrict__ dual, double* __restrict__ grad, double* __restrict__ mats,
-                  int* __restrict__ flag, double* __restrict__ prox) {
+                  int* __restrict__ flag, double* __restrict__ prox, const double* __restrict__ ctl) {
     extern __shared__ double sm[];
+    if (ctl) {  // speculative line search (dirs.cu): a decided sequence skips; the scaling comes from the device
+        if (ctl[0] != 0.0) return;
+        scal = irtmu = ctl[1];
+    }
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t c = (int64_t)blockIdx.x * PSD_WARPS + warp;
     if (c >= count) return;
@@ -906,7 +925,8 @@ psd_dder3_kernel(int64_t count, int side, int64_t offset, int64_t mat_off, const
 // ------------------------------------------------------------------ reduction over items
 __global__ void __launch_bounds__(1024)
 reduce_items_kernel(int64_t q, const int* __restrict__ flag, const double* __restrict__ prox, int use_max,
-                    int* __restrict__ out_flag, double* __restrict__ out_prox) {
+                    int* __restrict__ out_flag, double* __restrict__ out_prox, const double* __restrict__ ctl) {
+    if (ctl && ctl[0] != 0.0) return;
     __shared__ int sf[1024];
     __shared__ double sp[1024];
     int f = HYB_ST_ALL;
@@ -1034,9 +1054,20 @@ void hybi_cones_free(HybCones& cs) {
     cs = HybCones();
 }
 
+// every block is served by one closed-form kernel family (no host-sequenced dense engine)
+bool hybi_cones_all_batched(const HybCones& cs) {
+    for (const auto& b : cs.blocks)
+        if (b.dense || b.type == HYB_WSOSINTERPNONNEGATIVE || b.type == HYB_WSOSINTERPPOSSEMIDEFTRI) return false;
+    return true;
+}
+
 int hybi_cones_update(cudaStream_t st, HybCones& cs, const double* primal, const double* dual_in, double scal,
-                     double irtmu, int use_max_prox) {
+                     double irtmu, int use_max_prox, const double* ctl) {
     (void)use_max_prox;
+    if (ctl && !hybi_cones_all_batched(cs)) {
+        hyb_set_error("device-controlled cone update: the model has cones of the dense engines");
+        return -2;
+    }
     for (const auto& b : cs.blocks) {
         const int64_t rows = b.count * b.dim;
         switch (b.type) {
@@ -1044,7 +1075,7 @@ int hybi_cones_update(cudaStream_t st, HybCones& cs, const double* primal, const
                 nonneg_update_kernel<<<nblocks(rows, 256), 256, 0, st>>>(rows, primal + b.offset, dual_in + b.offset, scal,
                                                                          irtmu, cs.point + b.offset, cs.dual + b.offset,
                                                                          cs.grad + b.offset, cs.item_flag + b.offset,
-                                                                         cs.item_prox + b.offset);
+                                                                         cs.item_prox + b.offset, ctl);
                 break;
             case HYB_EPINORMEUCL:
             case HYB_EPIPERSQUARE: {
@@ -1053,7 +1084,7 @@ int hybi_cones_update(cudaStream_t st, HybCones& cs, const double* primal, const
 #define SOC_UPD(T, W)                                                                                              \
     soc_update_kernel<T, W><<<nblocks(threads, 128), 128, 0, st>>>(b.count, b.dim, b.offset, b.cone0, primal, dual_in, \
                                                                    scal, irtmu, cs.point, cs.dual, cs.grad, cs.aux,   \
-                                                                   cs.item_flag, cs.item_prox)
+                                                                   cs.item_flag, cs.item_prox, ctl)
                 if (b.type == HYB_EPINORMEUCL) {
                     if (warp) SOC_UPD(1, true); else SOC_UPD(1, false);
                 } else {
@@ -1068,11 +1099,11 @@ int hybi_cones_update(cudaStream_t st, HybCones& cs, const double* primal, const
                 if (warp)
                     ninf_update_kernel<true><<<nblocks(threads, 128), 128, 0, st>>>(b.count, b.dim, b.offset, b.cone0, primal,
                                                                                   dual_in, scal, irtmu, cs.point, cs.dual,
-                                                                                  cs.grad, cs.aux, cs.item_flag, cs.item_prox);
+                                                                                  cs.grad, cs.aux, cs.item_flag, cs.item_prox, ctl);
                 else
                     ninf_update_kernel<false><<<nblocks(threads, 128), 128, 0, st>>>(b.count, b.dim, b.offset, b.cone0, primal,
                                                                                    dual_in, scal, irtmu, cs.point, cs.dual,
-                                                                                   cs.grad, cs.aux, cs.item_flag, cs.item_prox);
+                                                                                   cs.grad, cs.aux, cs.item_flag, cs.item_prox, ctl);
                 break;
             }
             case HYB_POSSEMIDEFTRI:
@@ -1085,7 +1116,7 @@ int hybi_cones_update(cudaStream_t st, HybCones& cs, const double* primal, const
                 psd_update_kernel<<<nblocks(b.count, PSD_WARPS), PSD_WARPS * 32,
                                     PSD_WARPS * 4 * PSD_MAT * sizeof(double), st>>>(
                     b.count, b.side, b.offset, b.mat_off, primal, dual_in, scal, irtmu, cs.point, cs.dual, cs.grad,
-                    cs.mats, cs.item_flag, cs.item_prox);
+                    cs.mats, cs.item_flag, cs.item_prox, ctl);
                 break;
             case HYB_WSOSINTERPNONNEGATIVE:
                 HYB_CHECK(hybd_wsos_update(st, (HybDenseWsos*)b.dense, primal + b.offset, dual_in + b.offset, scal, irtmu,
@@ -1107,8 +1138,16 @@ int hybi_cones_update(cudaStream_t st, HybCones& cs, const double* primal, const
     return 0;
 }
 
+// device-side form of hybi_cones_reduce: red_flag / red_prox stay on the device (skipped when ctl[0] != 0)
+int hybi_cones_reduce_dev(cudaStream_t st, HybCones& cs, int use_max_prox, const double* ctl) {
+    reduce_items_kernel<<<1, 1024, 0, st>>>(cs.q, cs.item_flag, cs.item_prox, use_max_prox, cs.red_flag, cs.red_prox, ctl);
+    LAUNCHED();
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}
+
 int hybi_cones_reduce(cudaStream_t st, HybCones& cs, int use_max_prox, int* all_flags, double* agg) {
-    reduce_items_kernel<<<1, 1024, 0, st>>>(cs.q, cs.item_flag, cs.item_prox, use_max_prox, cs.red_flag, cs.red_prox);
+    reduce_items_kernel<<<1, 1024, 0, st>>>(cs.q, cs.item_flag, cs.item_prox, use_max_prox, cs.red_flag, cs.red_prox, nullptr);
     LAUNCHED();
     HYB_CUDA(cudaGetLastError());
     HYB_CUDA(cudaMemcpyAsync(all_flags, cs.red_flag, sizeof(int), cudaMemcpyDeviceToHost, st));

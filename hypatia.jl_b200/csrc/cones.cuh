@@ -59,8 +59,12 @@ void hybi_cones_free(HybCones& cs);
 
 // point <- scal * primal, dual <- dual_in (device vectors), then feas / dual feas / grad /
 // check_numerics / proxsqr per item.
+// ctl (device, optional): control block of a speculative line-search sequence (dirs.cu): ctl[0] != 0 -> every
+// kernel returns at once; else ctl[1] replaces scal and irtmu.  Only for models without dense-engine cones.
 int hybi_cones_update(cudaStream_t st, HybCones& cs, const double* primal, const double* dual_in, double scal,
-                     double irtmu, int use_max_prox);
+                     double irtmu, int use_max_prox, const double* ctl = nullptr);
+bool hybi_cones_all_batched(const HybCones& cs);
+int hybi_cones_reduce_dev(cudaStream_t st, HybCones& cs, int use_max_prox, const double* ctl);
 // reduce the per-item results: *all_flags = AND of status bits, *agg = max / sum of proxsqr (host outputs, synchronous)
 int hybi_cones_reduce(cudaStream_t st, HybCones& cs, int use_max_prox, int* all_flags, double* agg);
 // prod = op(H) * arr for every cone; arr/prod are q x m column-major device arrays (ld >= q).

@@ -290,6 +290,7 @@ void hyb_dirs_free(hyb_ctx* c) {
     cudaFree(d->cone_dim);
     cudaFree(d->sred);
     cudaFree(d->sflag);
+    cudaFree(d->sctl);
     delete d;
     c->dirs = nullptr;
 }
@@ -530,6 +531,7 @@ int hyb_dirs_setup(hyb_ctx* c, const double* cvec, const double* hvec) {
     HYB_CUDA(cudaMalloc(&d->cone_dim, sizeof(int) * Ka));
     HYB_CUDA(cudaMalloc(&d->sred, sizeof(double) * 2));
     HYB_CUDA(cudaMalloc(&d->sflag, sizeof(int)));
+    HYB_CUDA(cudaMalloc(&d->sctl, sizeof(double) * 8));
     std::vector<int64_t> off((size_t)Ka, 0);
     std::vector<int> dm((size_t)Ka, 0);
     for (const HybConeBlock& b : c->cones.blocks)
@@ -616,7 +618,8 @@ namespace {
 __global__ void cand_kernel(int64_t q, int64_t ldq, double c0, double c1, double c2, double c3,
                             const double* __restrict__ pz, const double* __restrict__ ps, const double* __restrict__ kz,
                             const double* __restrict__ ks, const unsigned char* __restrict__ dual_row,
-                            double* __restrict__ primal, double* __restrict__ dual) {
+                            double* __restrict__ primal, double* __restrict__ dual, const double* __restrict__ ctl) {
+    if (ctl && ctl[2] >= 0.0) return;  // speculative search: an earlier candidate was accepted
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= q) return;
     double z = pz[i], s = ps[i];
@@ -645,7 +648,8 @@ __global__ void cand_kernel(int64_t q, int64_t ldq, double c0, double c1, double
 // <primal_k, dual_k> per cone, one warp per cone
 __global__ void __launch_bounds__(256)
 cone_dots_kernel(int64_t K, const int64_t* __restrict__ off, const int* __restrict__ dim, const double* __restrict__ a,
-                 const double* __restrict__ b, double* __restrict__ out) {
+                 const double* __restrict__ b, double* __restrict__ out, const double* __restrict__ ctl) {
+    if (ctl && ctl[2] >= 0.0) return;
     const int lane = threadIdx.x & 31;
     const int64_t k = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
     if (k >= K) return;
@@ -657,9 +661,8 @@ cone_dots_kernel(int64_t K, const int64_t* __restrict__ off, const int* __restri
     for (int w = 16; w > 0; w >>= 1) s += __shfl_xor_sync(0xffffffffu, s, w);
     if (lane == 0) out[k] = s;
 }
-// min and sum of szk (one CTA, fixed order)
-__global__ void __launch_bounds__(1024)
-szk_reduce_kernel(int64_t K, const double* __restrict__ szk, double* __restrict__ out) {
+// min and sum of szk (one CTA of 1024 threads, fixed order); valid in thread 0
+__device__ __forceinline__ void szk_reduce_block(int64_t K, const double* __restrict__ szk, double& mn_out, double& sm_out) {
     __shared__ double smin[32], ssum[32];
     double mn = INFINITY, sm = 0.0;
     bool nan = false;
@@ -691,10 +694,74 @@ szk_reduce_kernel(int64_t K, const double* __restrict__ szk, double* __restrict_
             mn = (mn != mn || om != om) ? NAN : fmin(mn, om);
             sm += __shfl_xor_sync(0xffffffffu, sm, o);
         }
-        if (lane == 0) {
-            out[0] = mn;
-            out[1] = sm;
-        }
+    }
+    mn_out = mn;
+    sm_out = sm;
+}
+__global__ void __launch_bounds__(1024)
+szk_reduce_kernel(int64_t K, const double* __restrict__ szk, double* __restrict__ out) {
+    double mn, sm;
+    szk_reduce_block(K, szk, mn, sm);
+    if (threadIdx.x == 0) {
+        out[0] = mn;
+        out[1] = sm;
+    }
+}
+// Speculative line search, first decision of candidate `idx` on the device: the scalar gates of search.jl:108-130
+// that the sequential path takes on the host between hyb_search_gates and hyb_search_check, with the same
+// arithmetic.  ctl[0] <- 1 to skip the oracle update of this candidate (rejected, or an earlier one accepted).
+__global__ void __launch_bounds__(1024)
+search_decide1_kernel(int64_t K, const double* __restrict__ szk, const double* __restrict__ nus, double taukap, double nup1,
+                      double min_prox, double bound, double* __restrict__ ctl) {
+    __shared__ int any;
+    __shared__ double mu_s;
+    if (ctl[2] >= 0.0) {  // uniform: written only by one thread of an earlier kernel
+        if (threadIdx.x == 0) ctl[0] = 1.0;
+        return;
+    }
+    double mn, sm;
+    szk_reduce_block(K, szk, mn, sm);
+    if (threadIdx.x == 0) {
+        any = 0;
+        const double eps = 2.220446049250313e-16;
+        const double mu = (sm + taukap) / nup1;
+        mu_s = mu;
+        int reject = 0;
+        if (mn < eps) reject = 1;
+        if (mu < eps) reject = 1;
+        const double rel = taukap / mu;
+        if (rel < min_prox) reject = 1;
+        const double tp = (rel - 1.0) * (rel - 1.0);
+        if (tp > bound) reject = 1;
+        any = reject;
+        ctl[1] = 1.0 / sqrt(mu);
+        ctl[3] = mu;
+        ctl[5] = tp;
+        ctl[6] += 1.0;
+    }
+    __syncthreads();
+    const double mu = mu_s;
+    int bad = 0;
+    for (int64_t k = threadIdx.x; k < K; k += 1024) {
+        const double nu = nus[k];
+        const double rel = szk[k] / (mu * nu);
+        const double dv = rel - 1.0;
+        if (rel < min_prox || nu * (dv * dv) > bound) bad = 1;
+    }
+    if (bad) atomicOr(&any, 1);
+    __syncthreads();
+    if (threadIdx.x == 0) ctl[0] = any ? 1.0 : 0.0;
+}
+// ... and the last one (search.jl:141-158 after the oracle checks): accept candidate `idx` or go on
+__global__ void search_decide2_kernel(int idx, const int* __restrict__ red_flag, const double* __restrict__ red_prox,
+                                      int use_max, double bound, double* __restrict__ ctl) {
+    if (ctl[0] != 0.0) return;
+    const double a = *red_prox, agg0 = ctl[5];
+    const double total = use_max ? fmax(agg0, a) : agg0 + a;
+    if (*red_flag == HYB_ST_ALL && total < bound) {
+        ctl[2] = (double)idx;
+        ctl[4] = total;
+        ctl[0] = 1.0;
     }
 }
 // per-cone gates of search.jl:124-130: sz_rel < min_prox or nu (sz_rel - 1)^2 > bound
@@ -777,8 +844,8 @@ int hyb_search_gates(hyb_ctx* c, const double* coef, double* min_szk, double* su
     if (q == 0 || K == 0) return 0;
     KBEGIN(c);
     cand_kernel<<<(unsigned)((q + 255) / 256), 256, 0, st>>>(q, d.ldq, coef[0], coef[1], coef[2], coef[3], d.pz, d.ps, d.kz, d.ks,
-                                                           d.dual_row, c->in_primal, c->in_dual);
-    cone_dots_kernel<<<(unsigned)((K + 7) / 8), 256, 0, st>>>(K, d.cone_off, d.cone_dim, c->in_primal, c->in_dual, d.szk);
+                                                           d.dual_row, c->in_primal, c->in_dual, nullptr);
+    cone_dots_kernel<<<(unsigned)((K + 7) / 8), 256, 0, st>>>(K, d.cone_off, d.cone_dim, c->in_primal, c->in_dual, d.szk, nullptr);
     szk_reduce_kernel<<<1, 1024, 0, st>>>(K, d.szk, d.sred);
     HYB_CUDA(cudaGetLastError());
     g_misc_launches += 3;
@@ -792,6 +859,66 @@ int hyb_search_gates(hyb_ctx* c, const double* coef, double* min_szk, double* su
     ksync(c);
     *min_szk = out[0];
     *sum_szk = out[1];
+    return 0;
+}
+
+int hyb_search_alpha_supported(hyb_ctx* c) {
+    if (!c || !c->loaded) return 0;
+    return hybi_cones_all_batched(c->cones) ? 1 : 0;
+}
+
+int hyb_search_alpha(hyb_ctx* c, int ncand, const double* coefs, const double* taukap, double nup1, double min_prox,
+                     double proxsqr_bound, int use_max_prox, int* accepted, double* mu, double* agg) {
+    if (!c || !c->loaded || !c->dirs || !c->dirs->search_ready) {
+        hyb_set_error("hyb_search_alpha: call hyb_search_setup first");
+        return -3;
+    }
+    HybDirs& d = *c->dirs;
+    HYB_CUDA(cudaSetDevice(c->device));
+    cudaStream_t st = c->st;
+    const int64_t q = d.q, K = d.K;
+    *accepted = -1;
+    *mu = *agg = NAN;
+    if (ncand <= 0) return 0;
+    if (q == 0 || K == 0 || !hybi_cones_all_batched(c->cones)) {
+        hyb_set_error("hyb_search_alpha: needs a model whose cones are all served by the closed-form kernel families");
+        return -3;
+    }
+    const double init[8] = {0.0, 0.0, -1.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    HYB_CUDA(h2d(c, d.sctl, init, sizeof(init)));
+    KBEGIN(c);
+    for (int i = 0; i < ncand; ++i) {
+        const double* cf = coefs + 4 * i;
+        cand_kernel<<<(unsigned)((q + 255) / 256), 256, 0, st>>>(q, d.ldq, cf[0], cf[1], cf[2], cf[3], d.pz, d.ps, d.kz, d.ks,
+                                                               d.dual_row, c->in_primal, c->in_dual, d.sctl);
+        cone_dots_kernel<<<(unsigned)((K + 7) / 8), 256, 0, st>>>(K, d.cone_off, d.cone_dim, c->in_primal, c->in_dual, d.szk,
+                                                                d.sctl);
+        search_decide1_kernel<<<1, 1024, 0, st>>>(K, d.szk, d.nus, taukap[i], nup1, min_prox, proxsqr_bound, d.sctl);
+        HYB_CUDA(cudaGetLastError());
+        g_misc_launches += 3;
+        // load_point(cone, primal, irtmu), load_dual_point, reset_data, the oracle checks (search.jl:141-158)
+        HYB_CHECK(hybi_cones_update(st, c->cones, c->in_primal, c->in_dual, 0.0, 0.0, 1, d.sctl));
+        HYB_CHECK(hybi_cones_reduce_dev(st, c->cones, use_max_prox, d.sctl));
+        search_decide2_kernel<<<1, 1, 0, st>>>(i, c->cones.red_flag, c->cones.red_prox, use_max_prox, proxsqr_bound, d.sctl);
+        HYB_CUDA(cudaGetLastError());
+        ++g_misc_launches;
+    }
+    KEND(c);
+    double out[8];
+    HYB_CUDA(d2h(c, out, d.sctl, sizeof(out)));
+    HYB_CUDA(cudaStreamSynchronize(st));
+    ksync(c);
+    if (out[2] >= 0.0) {  // the device holds the accepted candidate, oracles updated at its scaling
+        *accepted = (int)out[2];
+        *mu = out[3];
+        *agg = out[4];
+        c->loaded_scal = out[1];
+        c->point_loaded = true;
+        c->updated_irtmu = out[1];
+    } else {  // the loaded cone state is some rejected candidate's
+        c->point_loaded = false;
+        c->updated_irtmu = NAN;
+    }
     return 0;
 }
 

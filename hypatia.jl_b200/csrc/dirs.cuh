@@ -30,6 +30,7 @@ struct HybDirs {
     int* cone_dim = nullptr;                   // K
     double* sred = nullptr;                    // [0] min szk, [1] sum szk ; int flag in sflag
     int* sflag = nullptr;
+    double* sctl = nullptr;                    // 8 : control block of the speculative line search (hyb_search_alpha)
     int64_t K = 0;
     bool search_ready = false;
 };

@@ -11,6 +11,7 @@ oracle / assembly / factorization / solve is a C-ABI call into CUDA kernels.
 from __future__ import annotations
 
 import ctypes as C
+import os
 import time
 from typing import List
 
@@ -229,6 +230,10 @@ class B200QRCholSystemSolver(QRCholSystemSolver):
             self.lib.hyb_model_load(self.ctx.ptr, model.q, model.n, dptr(G), cones.K, cones.descs), "hyb_model_load"
         )
         cones.mark_model_loaded()
+        # several schedule entries per call with the decisions on the device (hyb_search_alpha); HYB_SPEC_SEARCH=0
+        # keeps one candidate per call
+        self.spec_search = (self.device_search and not os.environ.get("HYB_SPEC_SEARCH") == "0"
+                            and bool(self.lib.hyb_search_alpha_supported(self.ctx.ptr)))
         self.setup_point_sub(solver)
 
     def set_point_sub_rhs(self, solver) -> None:  # common.jl:211-220 (also on modify)
@@ -294,6 +299,18 @@ class B200QRCholSystemSolver(QRCholSystemSolver):
             "hyb_search_check",
         )
         return bool(ok.value), float(agg.value)
+
+    def search_alpha(self, coefs, taukaps, nup1, min_prox, proxsqr_bound, use_max_prox):
+        """First accepted of several schedule entries, decided on the device (hyb_search_alpha)."""
+        cf = f64(np.asarray(coefs, dtype=np.float64).reshape(-1))
+        tk = f64(np.asarray(taukaps, dtype=np.float64))
+        acc, mu, agg = C.c_int(-1), C.c_double(0), C.c_double(0)
+        self.ctx.check(
+            self.lib.hyb_search_alpha(self.ctx.ptr, int(tk.size), dptr(cf), dptr(tk), float(nup1), float(min_prox),
+                                      float(proxsqr_bound), int(use_max_prox), C.byref(acc), C.byref(mu), C.byref(agg)),
+            "hyb_search_alpha",
+        )
+        return int(acc.value), float(mu.value), float(agg.value)
 
     # ---- device-resident stepper (hyb_step_*): steppers/common.jl, combined.jl, Solvers.jl:631-693 ------
     def step_point_set(self, point) -> None:

@@ -207,6 +207,8 @@ class CombinedStepper:
     def search_alpha(self, point: Point, solver) -> float:
         searcher = self.searcher
         sched = self.start_sched()
+        if getattr(self, "_device_search", False) and getattr(solver.syssolver, "spec_search", False):
+            return self._search_alpha_speculative(point, solver, sched)
         while sched <= len(searcher.alpha_sched):
             alpha = searcher.alpha_sched[sched - 1]
             self.last_num_cand += 1
@@ -222,6 +224,50 @@ class CombinedStepper:
         searcher.prev_sched = sched
         if getattr(self, "_device_search", False) and not getattr(self, "_device_stepper", False):
             solver.cones.reset_data()  # the device holds a rejected candidate: reload on next use
+        return 0.0
+
+    def _search_alpha_speculative(self, point: Point, solver, sched: int) -> float:
+        """search.jl:72-98 with several schedule entries per device call (hyb_search_alpha): the entries are
+        evaluated in schedule order with every accept / reject decision taken on the device; the first accepted
+        one wins, exactly as in the one-at-a-time loop.  The first window reaches one entry past the one accepted
+        by the previous search (step lengths change slowly between iterations), later windows take four."""
+        searcher, ss, cones = self.searcher, solver.syssolver, solver.cones
+        n = len(searcher.alpha_sched)
+        min_prox, bound = searcher.min_prox, searcher.prox_bound**2
+        hi = min(n, max(sched + 1, getattr(searcher, "prev_sched", sched) + 1))
+        while sched <= n:
+            cands = []
+            for k in range(sched, hi + 1):
+                alpha = searcher.alpha_sched[k - 1]
+                cf = self._coefs(alpha)
+                dtau, dkap = self._combine_taukap(cf)
+                tau, kap = point.tau + dtau, point.kap + dkap
+                taukap = tau * kap
+                if min(tau, kap, taukap) < EPS:  # search.jl:108-111, decided without the device
+                    continue
+                cands.append((k, alpha, cf, taukap))
+            if cands:
+                idx, mu, agg = ss.search_alpha([c[2] for c in cands], [c[3] for c in cands], searcher.nup1, min_prox, bound,
+                                               searcher.use_max_prox)
+                if idx >= 0:
+                    k, alpha = cands[idx][0], cands[idx][1]
+                    self.last_num_cand += k - sched + 1
+                    searcher.prox = math.sqrt(agg)
+                    searcher.prev_sched = k
+                    if getattr(self, "_device_stepper", False):
+                        cones.note_device_resident(1.0 / math.sqrt(mu))
+                    else:  # the device holds the candidate; refresh the host mirror of the cone batch once
+                        self.update_stepper_points(alpha, point, True)
+                        cand = self.temp
+                        cones.note_device_point(cones.primal_of(cand.z, cand.s), cones.dual_of(cand.z, cand.s),
+                                                1.0 / math.sqrt(mu))
+                    return alpha
+            self.last_num_cand += hi - sched + 1
+            sched = hi + 1
+            hi = min(n, sched + 3)
+        searcher.prev_sched = sched
+        if not getattr(self, "_device_stepper", False):
+            cones.reset_data()  # the device holds a rejected candidate: reload on next use
         return 0.0
 
     def _coefs(self, alpha: float):

@@ -73,6 +73,11 @@ SIGNATURES = {
     "hyb_search_load_point": (C.c_int, [C.c_void_p, c_double_p, c_double_p]),
     "hyb_search_gates": (C.c_int, [C.c_void_p, c_double_p, c_double_p, c_double_p]),
     "hyb_search_check": (C.c_int, [C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_int, C.c_double, c_int_p, c_double_p]),
+    "hyb_search_alpha_supported": (C.c_int, [C.c_void_p]),
+    "hyb_search_alpha": (
+        C.c_int,
+        [C.c_void_p, C.c_int, c_double_p, c_double_p, C.c_double, C.c_double, C.c_double, C.c_int, c_int_p, c_double_p, c_double_p],
+    ),
     "hyb_step_point_set": (C.c_int, [C.c_void_p, c_double_p, c_double_p, c_double_p]),
     "hyb_step_point_get": (C.c_int, [C.c_void_p, c_double_p, c_double_p, c_double_p]),
     "hyb_step_convergence": (C.c_int, [C.c_void_p, C.c_double, c_double_p]),

@@ -168,6 +168,19 @@ int hyb_search_gates(hyb_ctx* ctx, const double* coef, double* min_szk, double* 
 int hyb_search_check(hyb_ctx* ctx, double mu, double min_prox, double proxsqr_bound, int use_max_prox, double agg0,
                      int* ok, double* agg);
 
+/* Several entries of the step-length schedule in one call (search_alpha, search.jl:72-98): candidates
+ * i = 0 .. ncand-1 (coefs[4 i .. 4 i + 3] as for hyb_search_gates, taukap[i] = tau_i * kap_i of the candidate) are
+ * enqueued back to back -- candidate point, <s_k, z_k>, the scalar and per-cone gates, the oracle update, the
+ * neighbourhood check -- with every decision taken on the device: once a candidate is accepted the kernels
+ * of the later ones return at once, so the outcome (*accepted = index of the first accepted candidate or -1, its
+ * mu and proximity aggregate, the state of the cone batch) is that of evaluating them one after the other with
+ * hyb_search_gates / hyb_search_check, at one host synchronisation instead of up to three per candidate.
+ * For models all of whose cones are served by the closed-form kernel families
+ * (hyb_search_alpha_supported() == 1: no PosSemidefTri of side > 32, no WSOS cone). */
+int hyb_search_alpha_supported(hyb_ctx* ctx);
+int hyb_search_alpha(hyb_ctx* ctx, int ncand, const double* coefs, const double* taukap, double nup1, double min_prox,
+                     double proxsqr_bound, int use_max_prox, int* accepted, double* mu, double* agg);
+
 /* ---- device-resident stepper: src/Solvers/Solvers.jl, steppers/common.jl, steppers/combined.jl ----
  * The iterate's x (N), z (q), s (q) stay on the device for the whole solve; tau, kap, mu stay with the caller.
  * With these and the line search above an iteration moves only scalars across PCIe.  Needs hyb_dirs_setup. */

@@ -274,3 +274,28 @@ def test_directions_against_the_oracle_at_the_same_iterate(name, n_iters, monkey
         assert r_g <= 10.0 * r_c + floor, (r_g, r_c)
         r_x = _host_residual(cpu.stepper, cpu, d_g.vec, rhs_c)  # cross check, at the operators' own agreement
         assert r_x <= 10.0 * r_c + 1e-10 * max(1.0, scale_r, scale), (r_x, r_c)
+
+
+@pytest.mark.parametrize("name", ["block_multicone", "linearopt", "epipersquare4"])
+@pytest.mark.parametrize("host_stepper", [False, True])
+def test_speculative_line_search_is_the_sequential_one(name, host_stepper, monkeypatch):
+    """hyb_search_alpha (several schedule entries per call, decisions on the device, search.jl:72-98) takes the
+    same decisions with the same numbers as one candidate per call through hyb_search_gates / hyb_search_check:
+    identical step lengths, candidate counts and mu over the whole solve."""
+    if host_stepper:
+        monkeypatch.setenv("HYB_HOST_STEPPER", "1")
+    spec = make_gpu_solver(0, trace=True, **KW)
+    spec.load(MODELS[name]())
+    spec.solve()
+    assert spec.syssolver.spec_search
+    monkeypatch.setenv("HYB_SPEC_SEARCH", "0")
+    seq = make_gpu_solver(0, trace=True, **KW)
+    seq.load(MODELS[name]())
+    seq.solve()
+    assert not seq.syssolver.spec_search
+    assert spec.status == seq.status and spec.num_iters == seq.num_iters
+    assert [r["alpha"] for r in spec.trace] == [r["alpha"] for r in seq.trace]
+    assert [r["n_cand"] for r in spec.trace] == [r["n_cand"] for r in seq.trace]
+    assert [r["mu"] for r in spec.trace] == [r["mu"] for r in seq.trace]
+    assert [r["prox"] for r in spec.trace] == [r["prox"] for r in seq.trace]
+    assert spec.primal_obj == seq.primal_obj
