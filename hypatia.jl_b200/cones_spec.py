@@ -25,6 +25,7 @@ POSSEMIDEFTRI = 3
 WSOSINTERPNONNEGATIVE = 4
 WSOSINTERPPOSSEMIDEFTRI = 5
 EPINORMINF = 6
+DOUBLYNONNEGATIVETRI = 7
 
 RT2 = math.sqrt(2.0)
 
@@ -223,6 +224,58 @@ class PosSemidefTri(ConeSpec):
         k = 0
         for i in range(1, self.side + 1):  # possemideftri.jl:78-87
             arr[k] = 1.0
+            k += i + 1
+        return arr
+
+
+@dataclass
+class DoublyNonnegativeTri(ConeSpec):
+    """Real svec doubly nonnegative cone (PSD and entrywise nonnegative), src/Cones/doublynonnegativetri.jl:17-59."""
+
+    use_dual: bool = False
+    side: int = field(init=False, default=0)
+
+    def __post_init__(self):
+        assert self.dim >= 1
+        self.type_code = DOUBLYNONNEGATIVETRI
+        self.side = svec_side(self.dim)
+        self.use_dual_barrier = bool(self.use_dual)
+
+    @property
+    def nu(self):
+        return float(self.dim)  # doublynonnegativetri.jl:79
+
+    def offdiag_idxs(self) -> np.ndarray:
+        """0-based svec positions of the strictly upper-triangular entries (doublynonnegativetri.jl:55)."""
+        return np.array([svec_length(i - 1) + j for i in range(2, self.side + 1) for j in range(i - 1)], dtype=np.int64)
+
+    def initial_point(self):  # doublynonnegativetri.jl:81-132
+        side, d = self.side, float(self.dim)
+        if side == 1:
+            on_diag = off_diag = 1.0
+        elif side == 2:
+            on_diag, off_diag = math.sqrt(5.0) / 2.0, 1.0 / RT2
+        else:
+            n = float(side)
+            # ascending coefficients in the reference; numpy.roots wants them descending
+            p1 = [-n - 1, 0, n * n + n + 7, 0, -2 * n * n - 8, 0, n * n]
+            on_diag, off_diag = n + 1, 1.0
+            rtol = math.sqrt(np.finfo(np.float64).eps)
+            close = lambda a, b: abs(a - b) <= rtol * max(abs(a), abs(b))  # noqa: E731  (isapprox)
+            for r in np.roots(p1[::-1]):
+                offd = float(np.real(r))
+                if offd > 0:
+                    temp = d - (d - n) * offd * offd
+                    if temp > rtol:
+                        ond = math.sqrt(temp / n)
+                        denom = ond * ond + (n - 2) / RT2 * ond * offd - (n - 1) * offd * offd / 2
+                        if close(ond * RT2 + (n - 2) * offd, ond * denom * RT2) and close(denom, offd * offd * (denom + 1)):
+                            on_diag, off_diag = ond, offd
+                            break
+        arr = np.full(self.dim, off_diag)
+        k = 0
+        for i in range(1, side + 1):
+            arr[k] = on_diag
             k += i + 1
         return arr
 

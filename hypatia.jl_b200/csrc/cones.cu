@@ -1004,6 +1004,10 @@ int hybi_cones_alloc(HybCones& cs) {
             HybDenseWsosPsd* d = nullptr;
             HYB_CHECK(hybd_wsospsd_create(&d, b.side, b.U, b.nPs, b.Ps, b.Ls));
             b.dense = d;
+        } else if (b.type == HYB_DOUBLYNONNEGATIVETRI) {
+            HybDenseDnn* d = nullptr;
+            HYB_CHECK(hybd_dnn_create(&d, b.side));
+            b.dense = d;
         } else if (b.type != HYB_NONNEGATIVE && b.type != HYB_EPINORMEUCL && b.type != HYB_EPIPERSQUARE &&
                    b.type != HYB_EPINORMINF) {
             hyb_set_error("cone type %d is not supported by the GPU path yet", b.type);
@@ -1037,6 +1041,7 @@ void hybi_cones_free(HybCones& cs) {
         if (b.dense) {
             if (b.type == HYB_WSOSINTERPNONNEGATIVE) hybd_wsos_destroy((HybDenseWsos*)b.dense);
             else if (b.type == HYB_WSOSINTERPPOSSEMIDEFTRI) hybd_wsospsd_destroy((HybDenseWsosPsd*)b.dense);
+            else if (b.type == HYB_DOUBLYNONNEGATIVETRI) hybd_dnn_destroy((HybDenseDnn*)b.dense);
             else hybd_psd_destroy((HybDensePsd*)b.dense);
             b.dense = nullptr;
         }
@@ -1127,6 +1132,11 @@ int hybi_cones_update(cudaStream_t st, HybCones& cs, const double* primal, const
                 HYB_CHECK(hybd_wsospsd_update(st, (HybDenseWsosPsd*)b.dense, primal + b.offset, dual_in + b.offset, scal,
                                               irtmu, cs.point + b.offset, cs.dual + b.offset, cs.grad + b.offset,
                                               cs.item_flag + b.offset, cs.item_prox + b.offset));
+                break;
+            case HYB_DOUBLYNONNEGATIVETRI:
+                HYB_CHECK(hybd_dnn_update(st, (HybDenseDnn*)b.dense, primal + b.offset, dual_in + b.offset, scal, irtmu,
+                                          cs.point + b.offset, cs.dual + b.offset, cs.grad + b.offset,
+                                          cs.item_flag + b.offset, cs.item_prox + b.offset));
                 break;
             default:
                 hyb_set_error("cone type %d unsupported", b.type);
@@ -1264,6 +1274,9 @@ int hybi_cones_prod(cudaStream_t st, HybCones& cs, int which, const double* arr,
             case HYB_WSOSINTERPPOSSEMIDEFTRI:
                 HYB_CHECK(hybd_wsospsd_prod(st, (HybDenseWsosPsd*)b.dense, op, arr + b.offset, lda, prod + b.offset, ldp, m));
                 break;
+            case HYB_DOUBLYNONNEGATIVETRI:
+                HYB_CHECK(hybd_dnn_prod(st, (HybDenseDnn*)b.dense, op, arr + b.offset, lda, prod + b.offset, ldp, m));
+                break;
             default:
                 hyb_set_error("cone type %d unsupported", b.type);
                 return -2;
@@ -1319,6 +1332,9 @@ int hybi_cones_dder3(cudaStream_t st, HybCones& cs, const double* dir, double* o
                 break;
             case HYB_WSOSINTERPPOSSEMIDEFTRI:
                 HYB_CHECK(hybd_wsospsd_dder3(st, (HybDenseWsosPsd*)b.dense, dir + b.offset, out + b.offset));
+                break;
+            case HYB_DOUBLYNONNEGATIVETRI:
+                HYB_CHECK(hybd_dnn_dder3(st, (HybDenseDnn*)b.dense, dir + b.offset, out + b.offset));
                 break;
             default:
                 hyb_set_error("cone type %d unsupported", b.type);

@@ -1137,3 +1137,268 @@ int hybd_wsospsd_dder3(cudaStream_t st, HybDenseWsosPsd* c, const double* dir, d
     HYB_CUDA(cudaGetLastError());
     return 0;
 }
+
+// =======================================================================================
+// DoublyNonnegativeTri: src/Cones/doublynonnegativetri.jl  (barrier -logdet(S) - sum log(off-diagonal s))
+//   update_feas :134-147   all(point > eps), then the Cholesky of smat(point)
+//   is_dual_feas           true (Cones.jl:71)
+//   update_grad :149-160   -svec(S^-1) - 1 ./ s_offdiag
+//   update_hess :162-175   symm_kron(S^-1) (arrayutilities.jl:287-324) + diag(1 ./ s_offdiag.^2)
+//   dder3       :198-212   svec(T T'), T = S^-1 D U^-1, plus (d ./ s).^2 ./ s on the off-diagonal entries
+//   every Hessian product goes through the stored Hessian and its Cholesky (generic oracles of Cones.jl:
+//   108-125, 202-214, 233-252); hess_prod!(:177-196) is the same linear map evaluated from S^-1 instead.
+// Same eager evaluation at load time and the same engine as for the WSOS cones.
+// =======================================================================================
+namespace {
+
+__global__ void dnn_grad_offdiag_kernel(int64_t dim, const double* __restrict__ point, double* __restrict__ grad) {
+    const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= dim) return;
+    int r, c;
+    svec_rc(k, r, c);
+    if (r != c) grad[k] -= 1.0 / point[k];
+}
+
+// H[a, b] for svec positions a = (i, j), b = (k, l), i <= j, k <= l (full symmetric matrix, both triangles)
+__global__ void dnn_hess_kernel(int64_t dim, const double* __restrict__ Xi, int64_t ld, const double* __restrict__ point,
+                                double* __restrict__ H, int64_t ldH) {
+    const int64_t a = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t b = blockIdx.y;
+    if (a >= dim) return;
+    int i, j, k, l;
+    svec_rc(a, i, j);
+    svec_rc(b, k, l);
+    double v;
+    if (k == l) {
+        v = (i == j) ? Xi[j + (int64_t)l * ld] * Xi[j + (int64_t)l * ld] : RT2 * Xi[i + (int64_t)l * ld] * Xi[j + (int64_t)l * ld];
+    } else {
+        v = (i == j) ? RT2 * Xi[j + (int64_t)k * ld] * Xi[j + (int64_t)l * ld]
+                     : Xi[i + (int64_t)k * ld] * Xi[j + (int64_t)l * ld] + Xi[i + (int64_t)l * ld] * Xi[j + (int64_t)k * ld];
+    }
+    if (a == b && i != j) {
+        const double inv = 1.0 / point[a];
+        v += inv * inv;
+    }
+    H[a + b * ldH] = v;
+}
+
+__global__ void dnn_dder3_offdiag_kernel(int64_t dim, const double* __restrict__ point, const double* __restrict__ dir,
+                                         double* __restrict__ out) {
+    const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= dim) return;
+    int r, c;
+    svec_rc(k, r, c);
+    if (r != c) {
+        const double t = dir[k] / point[k];
+        out[k] += t * t / point[k];
+    }
+}
+
+// scal: [0] <g,p>  [1] <Hinv g, g>  [2] psi' Hinv psi  [3] p' H p
+__global__ void dnn_finalize_kernel(const int* pt_ok, const int* info_x, const int* info_h, const double* scal, double nu,
+                                    int64_t dim, int* flag, double* prox, int* slow, int* sqrt_ok) {
+    int f = HYB_ST_DUAL_FEAS;
+    double p = 0.0;
+    const bool feas = (*pt_ok != 0) && (*info_x == 0);
+    *sqrt_ok = (feas && *info_h == 0) ? 1 : 0;
+    *slow = 0;
+    if (feas) {
+        f |= HYB_ST_FEAS;
+        bool ok = (*info_h == 0);
+        if (fabs(1.0 + scal[0] / nu) > 1.220703125e-4 * (double)dim) ok = false;
+        if (fabs(1.0 - scal[1] / nu) > 1.104854345603981e-1 * (double)dim) ok = false;
+        if (ok) f |= HYB_ST_NUMERICS;
+        p = (scal[2] < -1.4901161193847656e-08 * (double)dim) ? INFINITY : fabs(scal[2]);
+    }
+    *flag = f;
+    *prox = p;
+}
+
+}  // namespace
+
+struct HybDenseDnn {
+    int s = 0;
+    int64_t dim = 0, ld = 0, ldD = 0;
+    double nu = 0.0;
+    double *X = nullptr, *Ux = nullptr, *Lx = nullptr, *Xinv = nullptr, *W2 = nullptr, *W3 = nullptr;  // s x s
+    HybChol chX;
+    double *H = nullptr, *Hf = nullptr, *Lh = nullptr;  // dim x dim
+    HybChol chH;
+    double *v1 = nullptr, *v2 = nullptr, *v3 = nullptr, *scal = nullptr;
+    int *pt_ok = nullptr, *slow = nullptr, *sqrt_ok = nullptr;
+    double *big1 = nullptr, *big2 = nullptr;
+    int64_t big_cols = 0;
+};
+
+static int dnn_ensure_big(HybDenseDnn* c, int64_t m) {
+    if (m <= c->big_cols) return 0;
+    cudaFree(c->big1);
+    cudaFree(c->big2);
+    c->big1 = c->big2 = nullptr;
+    HYB_CUDA(cudaMalloc(&c->big1, sizeof(double) * c->ldD * m));
+    HYB_CUDA(cudaMalloc(&c->big2, sizeof(double) * c->ldD * m));
+    c->big_cols = m;
+    return 0;
+}
+
+int hybd_dnn_create(HybDenseDnn** out, int side) {
+    HybDenseDnn* c = new HybDenseDnn();
+    c->s = side;
+    c->dim = (int64_t)side * (side + 1) / 2;
+    c->nu = (double)c->dim;
+    c->ld = hyb_round_up(side, 16);
+    c->ldD = hyb_round_up(c->dim, 16);
+    const size_t sb = sizeof(double) * c->ld * side;
+    double** smats[] = {&c->X, &c->Ux, &c->Lx, &c->Xinv, &c->W2, &c->W3};
+    for (double** m : smats) {
+        HYB_CUDA(cudaMalloc(m, sb));
+        HYB_CUDA(cudaMemset(*m, 0, sb));
+    }
+    const size_t db = sizeof(double) * c->ldD * c->dim;
+    double** dmats[] = {&c->H, &c->Hf, &c->Lh};
+    for (double** m : dmats) {
+        HYB_CUDA(cudaMalloc(m, db));
+        HYB_CUDA(cudaMemset(*m, 0, db));
+    }
+    double** vecs[] = {&c->v1, &c->v2, &c->v3};
+    for (double** v : vecs) HYB_CUDA(cudaMalloc(v, sizeof(double) * c->ldD));
+    HYB_CUDA(cudaMalloc(&c->scal, sizeof(double) * 8));
+    HYB_CUDA(cudaMemset(c->scal, 0, sizeof(double) * 8));
+    HYB_CUDA(cudaMalloc(&c->pt_ok, sizeof(int)));
+    HYB_CUDA(cudaMalloc(&c->slow, sizeof(int)));
+    HYB_CUDA(cudaMalloc(&c->sqrt_ok, sizeof(int)));
+    HYB_CUDA(cudaMemset(c->sqrt_ok, 0, sizeof(int)));
+    HYB_CHECK(hyb_chol_attach(c->chX, c->Ux, c->ld, side));
+    HYB_CHECK(hyb_chol_attach(c->chH, c->Hf, c->ldD, c->dim));
+    *out = c;
+    return 0;
+}
+
+void hybd_dnn_destroy(HybDenseDnn* c) {
+    if (!c) return;
+    hyb_chol_free(c->chX);
+    hyb_chol_free(c->chH);
+    double* ptrs[] = {c->X, c->Ux, c->Lx, c->Xinv, c->W2, c->W3, c->H, c->Hf, c->Lh, c->v1, c->v2, c->v3, c->scal, c->big1, c->big2};
+    for (double* p : ptrs) cudaFree(p);
+    cudaFree(c->pt_ok);
+    cudaFree(c->slow);
+    cudaFree(c->sqrt_ok);
+    delete c;
+}
+
+int hybd_dnn_update(cudaStream_t st, HybDenseDnn* c, const double* primal, const double* dual_in, double scal, double irtmu,
+                    double* point, double* dual_out, double* grad, int* flag, double* prox) {
+    const int s = c->s;
+    const int64_t ld = c->ld, dim = c->dim, ldD = c->ldD;
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, scal, primal, 0.0, nullptr, point);
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, dual_in, 0.0, nullptr, dual_out);
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, point, 0.0, nullptr, c->v3);  // aligned copy of the point
+    all_gt_eps_kernel<<<1, 1024, 0, st>>>(dim, c->v3, c->pt_ok);
+    svec_unpack_kernel<<<dim3(nb1(dim), 1), 256, 0, st>>>(c->v3, 0, s, c->X, ld, 0, 1.0);
+    copy_block_kernel<<<nb1((int64_t)s * s), 256, 0, st>>>(c->X, c->Ux, ld, s, s);
+    g_dense_launches += 6;
+    HYB_CUDA(cudaGetLastError());
+    int inf_x = 0, pt_ok = 0;
+    HYB_CHECK(hyb_potrf(st, c->chX, nullptr));
+    HYB_CUDA(cudaMemcpyAsync(&inf_x, c->chX.info, sizeof(int), cudaMemcpyDeviceToHost, st));
+    HYB_CUDA(cudaMemcpyAsync(&pt_ok, c->pt_ok, sizeof(int), cudaMemcpyDeviceToHost, st));
+    HYB_CUDA(cudaStreamSynchronize(st));
+    if (inf_x != 0 || !pt_ok) {  // infeasible candidate: rejected before grad / Hessian are needed (search.jl:146-150)
+        dnn_finalize_kernel<<<1, 1, 0, st>>>(c->pt_ok, c->chX.info, c->chH.info, c->scal, c->nu, dim, flag, prox, c->slow,
+                                             c->sqrt_ok);
+        DLAUNCHED();
+        HYB_CUDA(cudaGetLastError());
+        return 0;
+    }
+    HYB_CHECK(hyb_transpose(st, c->Ux, ld, s, s, c->Lx, ld, 1));
+    set_identity_kernel<<<nb1((int64_t)s * s), 256, 0, st>>>(c->Xinv, ld, s);
+    DLAUNCHED();
+    HYB_CHECK(hyb_trsm_fwd(st, c->Ux, ld, s, c->Xinv, ld, s));
+    HYB_CHECK(hyb_trsm_bwd(st, c->Ux, c->Lx, ld, s, c->Xinv, ld, s));
+    svec_pack_kernel<<<dim3(nb1(dim), 1), 256, 0, st>>>(c->Xinv, ld, 0, s, c->v1, 0, -1.0);
+    dnn_grad_offdiag_kernel<<<nb1(dim), 256, 0, st>>>(dim, c->v3, c->v1);
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, c->v1, 0.0, nullptr, grad);
+    // Hessian, its Cholesky and the transposed factor for the backward solves
+    dnn_hess_kernel<<<dim3(nb1(dim), (unsigned)dim), 256, 0, st>>>(dim, c->Xinv, ld, c->v3, c->H, ldD);
+    copy_upper_dense_kernel<<<nb1(dim * dim), 256, 0, st>>>(c->H, c->Hf, dim, ldD);
+    g_dense_launches += 5;
+    HYB_CUDA(cudaGetLastError());
+    HYB_CHECK(hyb_potrf(st, c->chH, nullptr));
+    HYB_CHECK(hyb_transpose(st, c->Hf, ldD, dim, dim, c->Lh, ldD, 1));
+    // scalars for check_numerics / proxsqr (Cones.jl:267-304); v1 still holds the gradient
+    dot_kernel<<<1, 1024, 0, st>>>(dim, c->v1, c->v3, c->scal + 0);
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, c->v1, 0.0, nullptr, c->v2);  // g
+    HYB_CHECK(hyb_potrs(st, c->chH, c->v1));                                         // Hinv g
+    dot_kernel<<<1, 1024, 0, st>>>(dim, c->v1, c->v2, c->scal + 1);
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, irtmu, dual_out, 1.0, grad, c->v2);  // psi
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, c->v2, 0.0, nullptr, c->v1);
+    HYB_CHECK(hyb_potrs(st, c->chH, c->v1));
+    dot_kernel<<<1, 1024, 0, st>>>(dim, c->v1, c->v2, c->scal + 2);
+    dnn_finalize_kernel<<<1, 1, 0, st>>>(c->pt_ok, c->chX.info, c->chH.info, c->scal, c->nu, dim, flag, prox, c->slow,
+                                         c->sqrt_ok);
+    g_dense_launches += 7;
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int hybd_dnn_sqrt_ok(cudaStream_t st, HybDenseDnn* c, int* ok) {
+    HYB_CUDA(cudaMemcpyAsync(ok, c->sqrt_ok, sizeof(int), cudaMemcpyDeviceToHost, st));
+    HYB_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int hybd_dnn_prod(cudaStream_t st, HybDenseDnn* c, int op, const double* arr, int64_t lda, double* prod, int64_t ldp,
+                  int64_t m) {
+    if (m <= 0) return 0;
+    const int64_t U = c->dim, ldU = c->ldD;
+    HYB_CHECK(dnn_ensure_big(c, m));
+    double *A = c->big1, *B = c->big2;
+    copy_mat_kernel<<<nb1(U * m), 256, 0, st>>>(arr, lda, A, ldU, U, m);
+    DLAUNCHED();
+    HYB_CUDA(cudaGetLastError());
+    const double* result = nullptr;
+    if (op == HYB_OP_HESS || op == 6) {
+        if (m == 1) HYB_CHECK(hyb_gemv_t(st, U, U, c->H, ldU, A, B));
+        else HYB_CHECK(hyb_gemm_tn(st, U, m, U, 1.0, c->H, ldU, A, ldU, 0.0, B, ldU, 0));
+        result = B;
+    } else if (op == HYB_OP_INV_HESS) {
+        if (m == 1) {
+            HYB_CHECK(hyb_potrs(st, c->chH, A));
+        } else {
+            HYB_CHECK(hyb_trsm_fwd(st, c->Hf, ldU, U, A, ldU, m));
+            HYB_CHECK(hyb_trsm_bwd(st, c->Hf, c->Lh, ldU, U, A, ldU, m));
+        }
+        result = A;
+    } else if (op == HYB_OP_SQRT_HESS) {  // chol(H).U * arr = Lh' arr
+        if (m == 1) HYB_CHECK(hyb_gemv_t(st, U, U, c->Lh, ldU, A, B));
+        else HYB_CHECK(hyb_gemm_tn(st, U, m, U, 1.0, c->Lh, ldU, A, ldU, 0.0, B, ldU, 0));
+        result = B;
+    } else {  // chol(H).U' \ arr
+        HYB_CHECK(hyb_trsm_fwd(st, c->Hf, ldU, U, A, ldU, m));
+        result = A;
+    }
+    copy_mat_kernel<<<nb1(U * m), 256, 0, st>>>(result, ldU, prod, ldp, U, m);
+    DLAUNCHED();
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int hybd_dnn_dder3(cudaStream_t st, HybDenseDnn* c, const double* dir, double* out) {
+    const int s = c->s;
+    const int64_t ld = c->ld, dim = c->dim;
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, dir, 0.0, nullptr, c->v1);
+    svec_unpack_kernel<<<dim3(nb1(dim), 1), 256, 0, st>>>(c->v1, 0, s, c->W2, ld, 0, 1.0);
+    g_dense_launches += 2;
+    HYB_CUDA(cudaGetLastError());
+    HYB_CHECK(hyb_trsm_fwd(st, c->Ux, ld, s, c->W2, ld, s));
+    HYB_CHECK(hyb_trsm_bwd(st, c->Ux, c->Lx, ld, s, c->W2, ld, s));  // S^-1 D
+    HYB_CHECK(hyb_transpose(st, c->W2, ld, s, s, c->W3, ld, 0));      // D S^-1
+    HYB_CHECK(hyb_trsm_fwd(st, c->Ux, ld, s, c->W3, ld, s));          // V = U^-T D S^-1 = T'
+    HYB_CHECK(hyb_gemm_tn(st, s, s, s, 1.0, c->W3, ld, c->W3, ld, 0.0, c->W2, ld, 0));
+    svec_pack_kernel<<<dim3(nb1(dim), 1), 256, 0, st>>>(c->W2, ld, 0, s, c->v2, 0, 1.0);
+    dnn_dder3_offdiag_kernel<<<nb1(dim), 256, 0, st>>>(dim, c->v3, c->v1, c->v2);
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, c->v2, 0.0, nullptr, out);
+    g_dense_launches += 3;
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}

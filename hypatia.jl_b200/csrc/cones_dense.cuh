@@ -37,3 +37,13 @@ int hybd_wsospsd_prod(cudaStream_t st, HybDenseWsosPsd* c, int op, const double*
                       int64_t ldp, int64_t m);
 int hybd_wsospsd_dder3(cudaStream_t st, HybDenseWsosPsd* c, const double* dir, double* out);
 int hybd_wsospsd_sqrt_ok(cudaStream_t st, HybDenseWsosPsd* c, int* ok);
+
+struct HybDenseDnn;  // DoublyNonnegativeTri (doublynonnegativetri.jl)
+int hybd_dnn_create(HybDenseDnn** out, int side);
+void hybd_dnn_destroy(HybDenseDnn* c);
+int hybd_dnn_update(cudaStream_t st, HybDenseDnn* c, const double* primal, const double* dual_in, double scal, double irtmu,
+                    double* point, double* dual_out, double* grad, int* flag, double* prox);
+int hybd_dnn_prod(cudaStream_t st, HybDenseDnn* c, int op, const double* arr, int64_t lda, double* prod, int64_t ldp,
+                  int64_t m);
+int hybd_dnn_dder3(cudaStream_t st, HybDenseDnn* c, const double* dir, double* out);
+int hybd_dnn_sqrt_ok(cudaStream_t st, HybDenseDnn* c, int* ok);

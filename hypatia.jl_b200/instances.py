@@ -255,12 +255,23 @@ def wsosinterppossemideftri3():  # :2615-2638
     return m, dict(status="Optimal", primal_obj=0.0)
 
 
+def doublynonnegativetri1():  # test/nativeinstances.jl:558-576 (the loop body pins use_dual = false)
+    m = Model([0, 1, 0], [[1, 0, 0], [0, 0, 1]], [1, 1], -_I(3), np.zeros(3), [cs.DoublyNonnegativeTri(3)])
+    return m, dict(status="Optimal", primal_obj=0.0, x=[1, 0, 1], s=[1, 0, 1])
+
+
+def doublynonnegativetri2():  # :578-591
+    m = Model([0, -1, 0], [[1, 0, 0], [0, 0, 1]], [1.0, 1.5], -_I(3), [-0.5, 0, -0.5], [cs.DoublyNonnegativeTri(3)])
+    return m, dict(status="Optimal", primal_obj=-1.0, x_at={1: 1.0})
+
+
 KNOWN_ANSWER = {
     f.__name__: f
     for f in (
         dimension1, primalinfeas1, primalinfeas2, dualinfeas2, dualinfeas3, nonnegative4,
         possemideftri1, possemideftri2, possemideftri8, possemideftri9,
         epinorminf1, epinorminf2, epinorminf3, epinorminf3_dual, epinorminf4,
+        doublynonnegativetri1, doublynonnegativetri2,
         epinormeucl1, epinormeucl2, epinormeucl3,
         epipersquare1, epipersquare2, epipersquare3, epipersquare4,
         wsosinterpnonnegative1, wsosinterpnonnegative2, wsosinterpnonnegative3,
@@ -307,6 +318,22 @@ def nearestpsd(side: int = 300, seed: int = 1) -> Model:
         idx = cs.svec_idx(i, j) - 1
         G[idx, k] = -1.0 if i == j else -RT2
     return Model(c, A, b, G, np.zeros(dim), [cs.PosSemidefTri(dim)])
+
+
+def nearestdnn(side: int = 12, seed: int = 1) -> Model:
+    """Doubly nonnegative relaxation test model (synthetic): max <C, X> s.t. tr(X) = 1, <J, X> = side / 2, X in the
+    doubly nonnegative cone, lowered like nearestpsd (svec with sqrt2 scaling)."""
+    rng = np.random.default_rng(seed)
+    dim = cs.svec_length(side)
+    Cm = rng.standard_normal((side, side))
+    Cm = 0.5 * (Cm + Cm.T)
+    c = -cs.smat_to_svec(Cm)
+    # variables are the svec coordinates themselves: G = -I, h = 0
+    tr = cs.smat_to_svec(np.eye(side))
+    ones = cs.smat_to_svec(np.ones((side, side)))
+    A = np.vstack([tr, ones])
+    b = [1.0, 1.0 + 0.25 * (side - 1)]
+    return Model(c, A, b, -_I(dim), np.zeros(dim), [cs.DoublyNonnegativeTri(dim)])
 
 
 def polymin(n: int = 2, halfdeg: int = 30, seed: int = 1) -> Model:

@@ -31,7 +31,8 @@ enum hyb_cone_type {
     HYB_CONE_POSSEMIDEFTRI = 3,           /* possemideftri.jl (real svec) */
     HYB_CONE_WSOSINTERPNONNEGATIVE = 4,   /* wsosinterpnonnegative.jl */
     HYB_CONE_WSOSINTERPPOSSEMIDEFTRI = 5, /* wsosinterppossemideftri.jl */
-    HYB_CONE_EPINORMINF = 6               /* epinorminf.jl (real; use_dual_barrier: epigraph of the 1-norm) */
+    HYB_CONE_EPINORMINF = 6,              /* epinorminf.jl (real; use_dual_barrier: epigraph of the 1-norm) */
+    HYB_CONE_DOUBLYNONNEGATIVETRI = 7     /* doublynonnegativetri.jl (real svec; side_or_R = side) */
 };
 
 /* One entry per cone of model.cones, in order; offsets follow build_cone_idxs

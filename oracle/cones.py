@@ -706,6 +706,74 @@ class PosSemidefTri(Cone):
         return cs.smat_to_svec(S @ S.T)
 
 
+class DoublyNonnegativeTri(PosSemidefTri):
+    """src/Cones/doublynonnegativetri.jl: -logdet(S) - sum log(off-diagonal entries).  The products other than
+    hess_prod! and the factorization-based oracles are the generic ones of Cones.jl (stored Hessian + its
+    Cholesky), like for the WSOS cones."""
+
+    uses_generic_hess = True
+
+    def use_sqrt_hess_oracles(self, arr_dim):  # Cones.jl:193-199 (generic)
+        return Cone.use_sqrt_hess_oracles(self, arr_dim)
+
+    def setup_extra_data(self):
+        self.side = self.spec.side
+        self.offdiag = self.spec.offdiag_idxs()
+
+    def update_feas(self):  # :134-147
+        if np.all(self.point > EPS):
+            return PosSemidefTri.update_feas(self)
+        self.is_feas_flag = False
+        self.feas_updated = True
+        return False
+
+    def is_dual_feas(self):  # Cones.jl:71
+        return True
+
+    def update_grad(self):  # :149-160
+        PosSemidefTri.update_grad(self)
+        self.inv_vec = 1.0 / self.point[self.offdiag]
+        self.grad_vec[self.offdiag] -= self.inv_vec
+        return self.grad_vec
+
+    def update_hess(self):  # :162-175
+        self.grad()
+        H = _symm_kron(self.inv_mat)
+        H[self.offdiag, self.offdiag] += self.inv_vec**2
+        self.hess_mat = H
+        self.hess_updated = True
+
+    def update_inv_hess(self):  # Cones.jl:246-252
+        Cone.update_inv_hess(self)
+
+    def hess_prod(self, arr):  # :177-196
+        prod = PosSemidefTri.hess_prod(self, arr)
+        od = self.offdiag
+        s_off = self.point[od]
+        a = np.asarray(arr, dtype=np.float64)
+        if a.ndim == 1:
+            prod[od] += a[od] / s_off / s_off
+        else:
+            prod[od, :] += a[od, :] / s_off[:, None] / s_off[:, None]
+        return prod
+
+    def inv_hess_prod(self, arr):  # Cones.jl:115-119
+        return Cone.inv_hess_prod(self, arr)
+
+    def sqrt_hess_prod(self, arr):  # Cones.jl:202-206
+        return Cone.sqrt_hess_prod(self, arr)
+
+    def inv_sqrt_hess_prod(self, arr):  # Cones.jl:209-214
+        return Cone.inv_sqrt_hess_prod(self, arr)
+
+    def dder3(self, direction):  # :198-212
+        out = PosSemidefTri.dder3(self, direction)
+        od = self.offdiag
+        s_off = self.point[od]
+        out[od] += (direction[od] / s_off) ** 2 / s_off
+        return out
+
+
 # ---------------------------------------------------------------------------
 class _GenericHessCone(Cone):
     """Cones whose products go through a stored Hessian and its Cholesky, with
@@ -925,6 +993,7 @@ _CLASSES = {
     cs.WSOSINTERPNONNEGATIVE: WSOSInterpNonnegative,
     cs.WSOSINTERPPOSSEMIDEFTRI: WSOSInterpPosSemidefTri,
     cs.EPINORMINF: EpiNormInf,
+    cs.DOUBLYNONNEGATIVETRI: DoublyNonnegativeTri,
 }
 
 

@@ -32,6 +32,7 @@ SEEDED = {
     "linearopt_60x200": ("linearopt", dict(m=60, n=200, seed=3)),
     "nearestpsd_side20": ("nearestpsd", dict(side=20, seed=1)),
     "polymin_n2_hd4": ("polymin", dict(n=2, halfdeg=4, seed=1)),
+    "nearestdnn_side12": ("nearestdnn", dict(side=12, seed=1)),
 }
 
 

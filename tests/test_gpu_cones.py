@@ -64,6 +64,9 @@ SPEC_SETS = {
     "norminf_large": [cs.EpiNormInf(40), cs.EpiNormInf(129, use_dual=True), cs.EpiNormInf(33)],
     "norminf_mixed": [cs.Nonnegative(3)] + [cs.EpiNormInf(4)] * 5 + [cs.EpiNormEucl(5), cs.EpiNormInf(6, use_dual=True),
                                                                      cs.PosSemidefTri(6), cs.EpiNormInf(9)],
+    # DoublyNonnegativeTri: stored Hessian + its Cholesky (the generic oracles), odd offsets, next to other families
+    "dnn": [cs.DoublyNonnegativeTri(cs.svec_length(s)) for s in (1, 2, 3)] + [cs.Nonnegative(2)]
+    + [cs.DoublyNonnegativeTri(cs.svec_length(s)) for s in (6, 12)] + [cs.EpiNormEucl(5), cs.DoublyNonnegativeTri(cs.svec_length(20))],
     "mixed": [cs.Nonnegative(10)] + [cs.EpiNormEucl(8)] * 4 + [cs.EpiPerSquare(8)] * 4
     + [cs.PosSemidefTri(136)] * 3 + [cs.Nonnegative(3), cs.EpiNormEucl(5)],
 }

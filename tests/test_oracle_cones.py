@@ -1,6 +1,7 @@
 """Oracle identities of the reference's cone tests (test/cone.jl:31-129) applied to
 the CPU oracle cones at the reference's sizes (test/runconetests.jl).  Tolerance
 1e3*eps as in the reference (:35) unless noted."""
+import math
 import numpy as np
 import pytest
 
@@ -181,3 +182,41 @@ def test_index_maps():
     w = np.ones(12)
     cs.scale_svec_incr(w, 2.0, 4)
     assert np.array_equal(w, [1, 1, 1, 1, 2, 2, 2, 2, 1, 1, 1, 1])
+
+
+@pytest.mark.parametrize("side", [1, 2, 5])
+def test_doublynonnegativetri(side):  # test/cone.jl:373-381 (init_tol = sqrt(eps))
+    run_oracle_identities(cs.DoublyNonnegativeTri(cs.svec_length(side)), init_tol=math.sqrt(EPS))
+
+
+@pytest.mark.parametrize("side", [10, 20])
+def test_doublynonnegativetri_initial_point(side):  # test/cone.jl:378-380 (init_only)
+    spec = cs.DoublyNonnegativeTri(cs.svec_length(side))
+    cone = make_cone(spec)
+    cone.setup_data()
+    point = spec.initial_point()
+    cone.load_point(point)
+    assert cone.is_feas()
+    assert np.allclose(point, -cone.grad(), atol=math.sqrt(EPS), rtol=math.sqrt(EPS))
+
+
+def test_doublynonnegativetri_barrier_derivatives():
+    """test/cone.jl:383-391: -logdet(W) - sum log(off-diagonal s); grad by finite differences of it."""
+    side = 3
+    spec = cs.DoublyNonnegativeTri(cs.svec_length(side))
+    od = spec.offdiag_idxs()
+    rng = np.random.default_rng(7)
+    B = rng.uniform(0.1, 1.0, (side, side))
+    W = B @ B.T + side * np.eye(side)
+    s = cs.smat_to_svec(W)
+
+    def barrier(v):
+        return -np.linalg.slogdet(cs.svec_to_smat(v))[1] - np.sum(np.log(v[od]))
+
+    cone = make_cone(spec)
+    cone.setup_data()
+    cone.load_point(s)
+    assert cone.is_feas()
+    h = 1e-6
+    fd = np.array([(barrier(s + h * e) - barrier(s - h * e)) / (2 * h) for e in np.eye(spec.dim)])
+    assert np.allclose(cone.grad(), fd, rtol=1e-7, atol=1e-7)
