@@ -26,6 +26,7 @@ WSOSINTERPNONNEGATIVE = 4
 WSOSINTERPPOSSEMIDEFTRI = 5
 EPINORMINF = 6
 DOUBLYNONNEGATIVETRI = 7
+POSSEMIDEFTRISPARSE = 8
 
 RT2 = math.sqrt(2.0)
 
@@ -278,6 +279,39 @@ class DoublyNonnegativeTri(ConeSpec):
             arr[k] = on_diag
             k += i + 1
         return arr
+
+
+@dataclass
+class PosSemidefTriSparse(ConeSpec):
+    """Real sparse PSD cone, dense implementation: src/Cones/possemideftrisparse/possemideftrisparse.jl:17-117,
+    denseimpl.jl.  ``rows`` / ``cols`` are the 1-based lower-triangle positions of the pattern (every diagonal entry
+    present), in the order of the point's coordinates; off-diagonal coordinates carry the sqrt2 scaling."""
+
+    side: int = 0
+    rows: Sequence[int] = ()
+    cols: Sequence[int] = ()
+    use_dual: bool = False
+
+    def __post_init__(self):
+        self.type_code = POSSEMIDEFTRISPARSE
+        self.rows0 = np.asarray(self.rows, dtype=np.int64) - 1
+        self.cols0 = np.asarray(self.cols, dtype=np.int64) - 1
+        assert self.rows0.size == self.cols0.size == self.dim >= 1
+        assert np.all(self.cols0 <= self.rows0) and np.all(self.rows0 < self.side) and np.all(self.cols0 >= 0)
+        diag = self.rows0[self.rows0 == self.cols0]
+        assert diag.size == self.side == np.unique(diag).size, "every diagonal entry exactly once"
+        self.use_dual_barrier = bool(self.use_dual)
+
+    @property
+    def nu(self):
+        return float(self.side)
+
+    def initial_point(self):  # possemideftrisparse.jl:103-117
+        return (self.rows0 == self.cols0).astype(np.float64)
+
+
+def psd_sparse(side: int, rows, cols, use_dual: bool = False) -> PosSemidefTriSparse:
+    return PosSemidefTriSparse(dim=len(rows), side=side, rows=list(rows), cols=list(cols), use_dual=use_dual)
 
 
 @dataclass

@@ -1008,6 +1008,10 @@ int hybi_cones_alloc(HybCones& cs) {
             HybDenseDnn* d = nullptr;
             HYB_CHECK(hybd_dnn_create(&d, b.side));
             b.dense = d;
+        } else if (b.type == HYB_POSSEMIDEFTRISPARSE) {
+            HybDenseDnn* d = nullptr;
+            HYB_CHECK(hybd_spsd_create(&d, b.side, b.dim, b.Ls));
+            b.dense = d;
         } else if (b.type != HYB_NONNEGATIVE && b.type != HYB_EPINORMEUCL && b.type != HYB_EPIPERSQUARE &&
                    b.type != HYB_EPINORMINF) {
             hyb_set_error("cone type %d is not supported by the GPU path yet", b.type);
@@ -1041,7 +1045,7 @@ void hybi_cones_free(HybCones& cs) {
         if (b.dense) {
             if (b.type == HYB_WSOSINTERPNONNEGATIVE) hybd_wsos_destroy((HybDenseWsos*)b.dense);
             else if (b.type == HYB_WSOSINTERPPOSSEMIDEFTRI) hybd_wsospsd_destroy((HybDenseWsosPsd*)b.dense);
-            else if (b.type == HYB_DOUBLYNONNEGATIVETRI) hybd_dnn_destroy((HybDenseDnn*)b.dense);
+            else if (b.type == HYB_DOUBLYNONNEGATIVETRI || b.type == HYB_POSSEMIDEFTRISPARSE) hybd_dnn_destroy((HybDenseDnn*)b.dense);
             else hybd_psd_destroy((HybDensePsd*)b.dense);
             b.dense = nullptr;
         }
@@ -1134,6 +1138,7 @@ int hybi_cones_update(cudaStream_t st, HybCones& cs, const double* primal, const
                                               cs.item_flag + b.offset, cs.item_prox + b.offset));
                 break;
             case HYB_DOUBLYNONNEGATIVETRI:
+            case HYB_POSSEMIDEFTRISPARSE:
                 HYB_CHECK(hybd_dnn_update(st, (HybDenseDnn*)b.dense, primal + b.offset, dual_in + b.offset, scal, irtmu,
                                           cs.point + b.offset, cs.dual + b.offset, cs.grad + b.offset,
                                           cs.item_flag + b.offset, cs.item_prox + b.offset));
@@ -1178,7 +1183,8 @@ int hybi_cones_prod(cudaStream_t st, HybCones& cs, int which, const double* arr,
         else if (which == 7) op = b.use_dual ? HYB_OP_INV_HESS : HYB_OP_HESS;
         else if (which == 8) op = b.use_dual ? HYB_OP_HESS : HYB_OP_INV_HESS;  // z-z block of the symmetric-indefinite system
         else if (which == 6)  // hess_prod_slow! is hess_prod! except for the WSOS cones (Cones.jl:229-231)
-            op = (b.type == HYB_WSOSINTERPNONNEGATIVE || b.type == HYB_WSOSINTERPPOSSEMIDEFTRI) ? 6 : HYB_OP_HESS;
+            op = (b.type == HYB_WSOSINTERPNONNEGATIVE || b.type == HYB_WSOSINTERPPOSSEMIDEFTRI ||
+                  b.type == HYB_POSSEMIDEFTRISPARSE) ? 6 : HYB_OP_HESS;
         else op = which;
         const int64_t rows = b.count * b.dim;
         switch (b.type) {
@@ -1275,6 +1281,7 @@ int hybi_cones_prod(cudaStream_t st, HybCones& cs, int which, const double* arr,
                 HYB_CHECK(hybd_wsospsd_prod(st, (HybDenseWsosPsd*)b.dense, op, arr + b.offset, lda, prod + b.offset, ldp, m));
                 break;
             case HYB_DOUBLYNONNEGATIVETRI:
+            case HYB_POSSEMIDEFTRISPARSE:
                 HYB_CHECK(hybd_dnn_prod(st, (HybDenseDnn*)b.dense, op, arr + b.offset, lda, prod + b.offset, ldp, m));
                 break;
             default:
@@ -1334,6 +1341,7 @@ int hybi_cones_dder3(cudaStream_t st, HybCones& cs, const double* dir, double* o
                 HYB_CHECK(hybd_wsospsd_dder3(st, (HybDenseWsosPsd*)b.dense, dir + b.offset, out + b.offset));
                 break;
             case HYB_DOUBLYNONNEGATIVETRI:
+            case HYB_POSSEMIDEFTRISPARSE:
                 HYB_CHECK(hybd_dnn_dder3(st, (HybDenseDnn*)b.dense, dir + b.offset, out + b.offset));
                 break;
             default:

@@ -1194,9 +1194,48 @@ __global__ void dnn_dder3_offdiag_kernel(int64_t dim, const double* __restrict__
     }
 }
 
+// ---- PosSemidefTriSparse, dense implementation (possemideftrisparse/denseimpl.jl, real case): the same engine with
+// pattern-indexed packing (svec_to_smat_sparse! :216-231, smat_to_svec_sparse! :251-267), the pattern-restricted
+// Hessian (update_hess :61-88) and the hess_prod_slow! switch (:142-163, Cones.jl:218-227)
+__global__ void spsd_unpack_kernel(int64_t dim, const double* __restrict__ v, int64_t vstride, const int* __restrict__ ri,
+                                   const int* __restrict__ ci, double* __restrict__ M, int64_t ld, int64_t blk_stride) {
+    const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t j = blockIdx.y;
+    if (k >= dim) return;
+    const int r = ri[k], c = ci[k];
+    const double x = v[k + j * vstride] * ((r == c) ? 1.0 : (1.0 / RT2));
+    double* B = M + j * blk_stride;
+    B[r + (int64_t)c * ld] = x;
+    B[c + (int64_t)r * ld] = x;
+}
+__global__ void spsd_pack_kernel(int64_t dim, const double* __restrict__ M, int64_t ld, int64_t blk_stride,
+                                 const int* __restrict__ ri, const int* __restrict__ ci, double* __restrict__ v,
+                                 int64_t vstride, double scale) {
+    const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t j = blockIdx.y;
+    if (k >= dim) return;
+    const int r = ri[k], c = ci[k];
+    const double x = M[j * blk_stride + r + (int64_t)c * ld];
+    v[k + j * vstride] = scale * ((r == c) ? x : x * RT2);
+}
+__global__ void spsd_hess_kernel(int64_t dim, const double* __restrict__ Xi, int64_t ld, const int* __restrict__ ri,
+                                 const int* __restrict__ ci, double* __restrict__ H, int64_t ldH) {
+    const int64_t a = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t b = blockIdx.y;
+    if (a >= dim) return;
+    const int i1 = ri[a], j1 = ci[a], i2 = ri[b], j2 = ci[b];
+    const bool d1 = (i1 == j1), d2 = (i2 == j2);
+    double v;
+    if (d1 && d2) v = Xi[i1 + (int64_t)i2 * ld] * Xi[i1 + (int64_t)i2 * ld];
+    else if (d1 != d2) v = RT2 * Xi[i1 + (int64_t)i2 * ld] * Xi[j1 + (int64_t)j2 * ld];
+    else v = Xi[i1 + (int64_t)i2 * ld] * Xi[j1 + (int64_t)j2 * ld] + Xi[i1 + (int64_t)j2 * ld] * Xi[j1 + (int64_t)i2 * ld];
+    H[a + b * ldH] = v;
+}
+__global__ void set_int_kernel(int* p, int v) { *p = v; }
+
 // scal: [0] <g,p>  [1] <Hinv g, g>  [2] psi' Hinv psi  [3] p' H p
 __global__ void dnn_finalize_kernel(const int* pt_ok, const int* info_x, const int* info_h, const double* scal, double nu,
-                                    int64_t dim, int* flag, double* prox, int* slow, int* sqrt_ok) {
+                                    int64_t dim, int with_slow, int* flag, double* prox, int* slow, int* sqrt_ok) {
     int f = HYB_ST_DUAL_FEAS;
     double p = 0.0;
     const bool feas = (*pt_ok != 0) && (*info_x == 0);
@@ -1209,6 +1248,8 @@ __global__ void dnn_finalize_kernel(const int* pt_ok, const int* info_x, const i
         if (fabs(1.0 - scal[1] / nu) > 1.104854345603981e-1 * (double)dim) ok = false;
         if (ok) f |= HYB_ST_NUMERICS;
         p = (scal[2] < -1.4901161193847656e-08 * (double)dim) ? INFINITY : fabs(scal[2]);
+        // update_use_hess_prod_slow (Cones.jl:218-227)
+        if (with_slow && fabs(1.0 - scal[3] / nu) > (double)dim * 1.4901161193847656e-08) *slow = 1;
     }
     *flag = f;
     *prox = p;
@@ -1228,7 +1269,32 @@ struct HybDenseDnn {
     int *pt_ok = nullptr, *slow = nullptr, *sqrt_ok = nullptr;
     double *big1 = nullptr, *big2 = nullptr;
     int64_t big_cols = 0;
+    // PosSemidefTriSparse: pattern positions (0-based, row >= col) of the point's coordinates
+    bool sparse = false;
+    int *ri = nullptr, *ci = nullptr;
+    double *sbig1 = nullptr, *sbig2 = nullptr;  // side x side blocks for the factor-based hess_prod_slow!
+    int64_t sbig_cols = 0;
 };
+
+// vector (dim) -> full symmetric side x side matrix, and back (scaled)
+static int dnn_unpack(cudaStream_t st, HybDenseDnn* c, const double* v, double* M) {
+    if (c->sparse) {
+        HYB_CUDA(cudaMemsetAsync(M, 0, sizeof(double) * c->ld * c->s, st));
+        spsd_unpack_kernel<<<dim3(nb1(c->dim), 1), 256, 0, st>>>(c->dim, v, 0, c->ri, c->ci, M, c->ld, 0);
+    } else {
+        svec_unpack_kernel<<<dim3(nb1(c->dim), 1), 256, 0, st>>>(v, 0, c->s, M, c->ld, 0, 1.0);
+    }
+    DLAUNCHED();
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}
+static int dnn_pack(cudaStream_t st, HybDenseDnn* c, const double* M, double* v, double scale) {
+    if (c->sparse) spsd_pack_kernel<<<dim3(nb1(c->dim), 1), 256, 0, st>>>(c->dim, M, c->ld, 0, c->ri, c->ci, v, 0, scale);
+    else svec_pack_kernel<<<dim3(nb1(c->dim), 1), 256, 0, st>>>(M, c->ld, 0, c->s, v, 0, scale);
+    DLAUNCHED();
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}
 
 static int dnn_ensure_big(HybDenseDnn* c, int64_t m) {
     if (m <= c->big_cols) return 0;
@@ -1241,11 +1307,25 @@ static int dnn_ensure_big(HybDenseDnn* c, int64_t m) {
     return 0;
 }
 
+static int dnn_create_common(HybDenseDnn** out, int side, int64_t dim, double nu, const int64_t* rows_cols);
+
 int hybd_dnn_create(HybDenseDnn** out, int side) {
+    return dnn_create_common(out, side, (int64_t)side * (side + 1) / 2, (double)((int64_t)side * (side + 1) / 2), nullptr);
+}
+// PosSemidefTriSparse: rows_cols = dim 0-based rows followed by dim 0-based columns of the pattern (row >= col)
+int hybd_spsd_create(HybDenseDnn** out, int side, int64_t dim, const int64_t* rows_cols) {
+    if (!rows_cols) {
+        hyb_set_error("PosSemidefTriSparse needs its pattern (hyb_cone_desc.Ls)");
+        return -3;
+    }
+    return dnn_create_common(out, side, dim, (double)side, rows_cols);
+}
+
+static int dnn_create_common(HybDenseDnn** out, int side, int64_t dim, double nu, const int64_t* rows_cols) {
     HybDenseDnn* c = new HybDenseDnn();
     c->s = side;
-    c->dim = (int64_t)side * (side + 1) / 2;
-    c->nu = (double)c->dim;
+    c->dim = dim;
+    c->nu = nu;
     c->ld = hyb_round_up(side, 16);
     c->ldD = hyb_round_up(c->dim, 16);
     const size_t sb = sizeof(double) * c->ld * side;
@@ -1270,12 +1350,35 @@ int hybd_dnn_create(HybDenseDnn** out, int side) {
     HYB_CUDA(cudaMemset(c->sqrt_ok, 0, sizeof(int)));
     HYB_CHECK(hyb_chol_attach(c->chX, c->Ux, c->ld, side));
     HYB_CHECK(hyb_chol_attach(c->chH, c->Hf, c->ldD, c->dim));
+    if (rows_cols) {
+        c->sparse = true;
+        std::vector<int> r(dim), cc(dim);
+        for (int64_t k = 0; k < dim; ++k) {
+            r[k] = (int)rows_cols[k];
+            cc[k] = (int)rows_cols[dim + k];
+            if (cc[k] < 0 || cc[k] > r[k] || r[k] >= side) {
+                hyb_set_error("PosSemidefTriSparse: pattern entry %lld = (%d, %d) outside the lower triangle of side %d",
+                              (long long)k, r[k], cc[k], side);
+                return -3;
+            }
+        }
+        HYB_CUDA(cudaMalloc(&c->ri, sizeof(int) * dim));
+        HYB_CUDA(cudaMalloc(&c->ci, sizeof(int) * dim));
+        HYB_CUDA(cudaMemcpy(c->ri, r.data(), sizeof(int) * dim, cudaMemcpyHostToDevice));
+        HYB_CUDA(cudaMemcpy(c->ci, cc.data(), sizeof(int) * dim, cudaMemcpyHostToDevice));
+        set_int_kernel<<<1, 1>>>(c->pt_ok, 1);  // no entrywise condition on the point
+        HYB_CUDA(cudaDeviceSynchronize());
+    }
     *out = c;
     return 0;
 }
 
 void hybd_dnn_destroy(HybDenseDnn* c) {
     if (!c) return;
+    cudaFree(c->ri);
+    cudaFree(c->ci);
+    cudaFree(c->sbig1);
+    cudaFree(c->sbig2);
     hyb_chol_free(c->chX);
     hyb_chol_free(c->chH);
     double* ptrs[] = {c->X, c->Ux, c->Lx, c->Xinv, c->W2, c->W3, c->H, c->Hf, c->Lh, c->v1, c->v2, c->v3, c->scal, c->big1, c->big2};
@@ -1293,10 +1396,10 @@ int hybd_dnn_update(cudaStream_t st, HybDenseDnn* c, const double* primal, const
     lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, scal, primal, 0.0, nullptr, point);
     lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, dual_in, 0.0, nullptr, dual_out);
     lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, point, 0.0, nullptr, c->v3);  // aligned copy of the point
-    all_gt_eps_kernel<<<1, 1024, 0, st>>>(dim, c->v3, c->pt_ok);
-    svec_unpack_kernel<<<dim3(nb1(dim), 1), 256, 0, st>>>(c->v3, 0, s, c->X, ld, 0, 1.0);
+    if (!c->sparse) all_gt_eps_kernel<<<1, 1024, 0, st>>>(dim, c->v3, c->pt_ok);
+    HYB_CHECK(dnn_unpack(st, c, c->v3, c->X));
     copy_block_kernel<<<nb1((int64_t)s * s), 256, 0, st>>>(c->X, c->Ux, ld, s, s);
-    g_dense_launches += 6;
+    g_dense_launches += 5;
     HYB_CUDA(cudaGetLastError());
     int inf_x = 0, pt_ok = 0;
     HYB_CHECK(hyb_potrf(st, c->chX, nullptr));
@@ -1304,8 +1407,8 @@ int hybd_dnn_update(cudaStream_t st, HybDenseDnn* c, const double* primal, const
     HYB_CUDA(cudaMemcpyAsync(&pt_ok, c->pt_ok, sizeof(int), cudaMemcpyDeviceToHost, st));
     HYB_CUDA(cudaStreamSynchronize(st));
     if (inf_x != 0 || !pt_ok) {  // infeasible candidate: rejected before grad / Hessian are needed (search.jl:146-150)
-        dnn_finalize_kernel<<<1, 1, 0, st>>>(c->pt_ok, c->chX.info, c->chH.info, c->scal, c->nu, dim, flag, prox, c->slow,
-                                             c->sqrt_ok);
+        dnn_finalize_kernel<<<1, 1, 0, st>>>(c->pt_ok, c->chX.info, c->chH.info, c->scal, c->nu, dim, c->sparse ? 1 : 0, flag,
+                                             prox, c->slow, c->sqrt_ok);
         DLAUNCHED();
         HYB_CUDA(cudaGetLastError());
         return 0;
@@ -1315,11 +1418,12 @@ int hybd_dnn_update(cudaStream_t st, HybDenseDnn* c, const double* primal, const
     DLAUNCHED();
     HYB_CHECK(hyb_trsm_fwd(st, c->Ux, ld, s, c->Xinv, ld, s));
     HYB_CHECK(hyb_trsm_bwd(st, c->Ux, c->Lx, ld, s, c->Xinv, ld, s));
-    svec_pack_kernel<<<dim3(nb1(dim), 1), 256, 0, st>>>(c->Xinv, ld, 0, s, c->v1, 0, -1.0);
-    dnn_grad_offdiag_kernel<<<nb1(dim), 256, 0, st>>>(dim, c->v3, c->v1);
+    HYB_CHECK(dnn_pack(st, c, c->Xinv, c->v1, -1.0));
+    if (!c->sparse) dnn_grad_offdiag_kernel<<<nb1(dim), 256, 0, st>>>(dim, c->v3, c->v1);
     lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, c->v1, 0.0, nullptr, grad);
     // Hessian, its Cholesky and the transposed factor for the backward solves
-    dnn_hess_kernel<<<dim3(nb1(dim), (unsigned)dim), 256, 0, st>>>(dim, c->Xinv, ld, c->v3, c->H, ldD);
+    if (c->sparse) spsd_hess_kernel<<<dim3(nb1(dim), (unsigned)dim), 256, 0, st>>>(dim, c->Xinv, ld, c->ri, c->ci, c->H, ldD);
+    else dnn_hess_kernel<<<dim3(nb1(dim), (unsigned)dim), 256, 0, st>>>(dim, c->Xinv, ld, c->v3, c->H, ldD);
     copy_upper_dense_kernel<<<nb1(dim * dim), 256, 0, st>>>(c->H, c->Hf, dim, ldD);
     g_dense_launches += 5;
     HYB_CUDA(cudaGetLastError());
@@ -1334,8 +1438,13 @@ int hybd_dnn_update(cudaStream_t st, HybDenseDnn* c, const double* primal, const
     lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, c->v2, 0.0, nullptr, c->v1);
     HYB_CHECK(hyb_potrs(st, c->chH, c->v1));
     dot_kernel<<<1, 1024, 0, st>>>(dim, c->v1, c->v2, c->scal + 2);
-    dnn_finalize_kernel<<<1, 1, 0, st>>>(c->pt_ok, c->chX.info, c->chH.info, c->scal, c->nu, dim, flag, prox, c->slow,
-                                         c->sqrt_ok);
+    if (c->sparse) {  // p' H p for the hess_prod_slow! switch
+        HYB_CHECK(hyb_gemv_t(st, dim, dim, c->H, ldD, c->v3, c->v1));
+        dot_kernel<<<1, 1024, 0, st>>>(dim, c->v1, c->v3, c->scal + 3);
+        DLAUNCHED();
+    }
+    dnn_finalize_kernel<<<1, 1, 0, st>>>(c->pt_ok, c->chX.info, c->chH.info, c->scal, c->nu, dim, c->sparse ? 1 : 0, flag, prox,
+                                         c->slow, c->sqrt_ok);
     g_dense_launches += 7;
     HYB_CUDA(cudaGetLastError());
     return 0;
@@ -1357,6 +1466,39 @@ int hybd_dnn_prod(cudaStream_t st, HybDenseDnn* c, int op, const double* arr, in
     DLAUNCHED();
     HYB_CUDA(cudaGetLastError());
     const double* result = nullptr;
+    if (op == 6 && c->sparse) {  // hess_prod_slow! (denseimpl.jl:142-163): Lambda^-1 A Lambda^-1 through the factor
+        int slow = 0;
+        HYB_CUDA(cudaMemcpyAsync(&slow, c->slow, sizeof(int), cudaMemcpyDeviceToHost, st));
+        HYB_CUDA(cudaStreamSynchronize(st));
+        if (getenv("HYB_FORCE_HESS_PROD_SLOW")) slow = 1;  // test hook: take the factor-based branch at a benign point
+        if (slow) {
+            const int s = c->s;
+            const int64_t ld = c->ld, blk = ld * s, cols = (int64_t)s * m;
+            if (m > c->sbig_cols) {
+                cudaFree(c->sbig1);
+                cudaFree(c->sbig2);
+                c->sbig1 = c->sbig2 = nullptr;
+                HYB_CUDA(cudaMalloc(&c->sbig1, sizeof(double) * blk * m));
+                HYB_CUDA(cudaMalloc(&c->sbig2, sizeof(double) * blk * m));
+                c->sbig_cols = m;
+            }
+            double *SA = c->sbig1, *SB = c->sbig2;
+            HYB_CUDA(cudaMemsetAsync(SA, 0, sizeof(double) * blk * m, st));
+            spsd_unpack_kernel<<<dim3(nb1(U), (unsigned)m), 256, 0, st>>>(U, A, ldU, c->ri, c->ci, SA, ld, blk);
+            DLAUNCHED();
+            HYB_CHECK(hyb_trsm_fwd(st, c->Ux, ld, s, SA, ld, cols));
+            HYB_CHECK(hyb_trsm_bwd(st, c->Ux, c->Lx, ld, s, SA, ld, cols));
+            dim3 tgrid((unsigned)((s + 31) / 32), (unsigned)((s + 31) / 32), (unsigned)m);
+            block_transpose_kernel<<<tgrid, dim3(32, 8), 0, st>>>(SA, SB, ld, blk, s);
+            DLAUNCHED();
+            HYB_CHECK(hyb_trsm_fwd(st, c->Ux, ld, s, SB, ld, cols));
+            HYB_CHECK(hyb_trsm_bwd(st, c->Ux, c->Lx, ld, s, SB, ld, cols));
+            spsd_pack_kernel<<<dim3(nb1(U), (unsigned)m), 256, 0, st>>>(U, SB, ld, blk, c->ri, c->ci, prod, ldp, 1.0);
+            DLAUNCHED();
+            HYB_CUDA(cudaGetLastError());
+            return 0;
+        }
+    }
     if (op == HYB_OP_HESS || op == 6) {
         if (m == 1) HYB_CHECK(hyb_gemv_t(st, U, U, c->H, ldU, A, B));
         else HYB_CHECK(hyb_gemm_tn(st, U, m, U, 1.0, c->H, ldU, A, ldU, 0.0, B, ldU, 0));
@@ -1387,18 +1529,17 @@ int hybd_dnn_dder3(cudaStream_t st, HybDenseDnn* c, const double* dir, double* o
     const int s = c->s;
     const int64_t ld = c->ld, dim = c->dim;
     lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, dir, 0.0, nullptr, c->v1);
-    svec_unpack_kernel<<<dim3(nb1(dim), 1), 256, 0, st>>>(c->v1, 0, s, c->W2, ld, 0, 1.0);
-    g_dense_launches += 2;
-    HYB_CUDA(cudaGetLastError());
+    DLAUNCHED();
+    HYB_CHECK(dnn_unpack(st, c, c->v1, c->W2));
     HYB_CHECK(hyb_trsm_fwd(st, c->Ux, ld, s, c->W2, ld, s));
     HYB_CHECK(hyb_trsm_bwd(st, c->Ux, c->Lx, ld, s, c->W2, ld, s));  // S^-1 D
     HYB_CHECK(hyb_transpose(st, c->W2, ld, s, s, c->W3, ld, 0));      // D S^-1
     HYB_CHECK(hyb_trsm_fwd(st, c->Ux, ld, s, c->W3, ld, s));          // V = U^-T D S^-1 = T'
     HYB_CHECK(hyb_gemm_tn(st, s, s, s, 1.0, c->W3, ld, c->W3, ld, 0.0, c->W2, ld, 0));
-    svec_pack_kernel<<<dim3(nb1(dim), 1), 256, 0, st>>>(c->W2, ld, 0, s, c->v2, 0, 1.0);
-    dnn_dder3_offdiag_kernel<<<nb1(dim), 256, 0, st>>>(dim, c->v3, c->v1, c->v2);
+    HYB_CHECK(dnn_pack(st, c, c->W2, c->v2, 1.0));
+    if (!c->sparse) dnn_dder3_offdiag_kernel<<<nb1(dim), 256, 0, st>>>(dim, c->v3, c->v1, c->v2);
     lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, c->v2, 0.0, nullptr, out);
-    g_dense_launches += 3;
+    g_dense_launches += 2;
     HYB_CUDA(cudaGetLastError());
     return 0;
 }

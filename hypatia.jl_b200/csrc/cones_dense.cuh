@@ -38,8 +38,9 @@ int hybd_wsospsd_prod(cudaStream_t st, HybDenseWsosPsd* c, int op, const double*
 int hybd_wsospsd_dder3(cudaStream_t st, HybDenseWsosPsd* c, const double* dir, double* out);
 int hybd_wsospsd_sqrt_ok(cudaStream_t st, HybDenseWsosPsd* c, int* ok);
 
-struct HybDenseDnn;  // DoublyNonnegativeTri (doublynonnegativetri.jl)
+struct HybDenseDnn;  // DoublyNonnegativeTri (doublynonnegativetri.jl) and PosSemidefTriSparse (dense implementation)
 int hybd_dnn_create(HybDenseDnn** out, int side);
+int hybd_spsd_create(HybDenseDnn** out, int side, int64_t dim, const int64_t* rows_cols);
 void hybd_dnn_destroy(HybDenseDnn* c);
 int hybd_dnn_update(cudaStream_t st, HybDenseDnn* c, const double* primal, const double* dual_in, double scal, double irtmu,
                     double* point, double* dual_out, double* grad, int* flag, double* prox);

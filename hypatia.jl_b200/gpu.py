@@ -57,6 +57,11 @@ class GpuConeBatch(ConeSet):
                 d.Ls = C.cast(Ls, C.POINTER(C.c_int64))
             else:
                 d.nPs = 0
+            if s.type_code == cs.POSSEMIDEFTRISPARSE:  # the pattern travels in Ls: rows then columns, 0-based
+                pat = np.ascontiguousarray(np.concatenate([s.rows0, s.cols0]), dtype=np.int64)
+                Ls = (C.c_int64 * pat.size)(*pat.tolist())
+                self._keep.append(Ls)
+                d.Ls = C.cast(Ls, C.POINTER(C.c_int64))
         return arr
 
     # The device model (G and the cones) is loaded by the system solver's load();

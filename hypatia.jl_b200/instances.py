@@ -265,6 +265,39 @@ def doublynonnegativetri2():  # :578-591
     return m, dict(status="Optimal", primal_obj=-1.0, x_at={1: 1.0})
 
 
+def possemideftrisparse1():  # test/nativeinstances.jl:608-628 (dense implementation, real)
+    cone = cs.psd_sparse(2, [1, 2, 2], [1, 1, 2])
+    m = Model([0, -1, 0], [[1, 0, 0], [0, 0, 1]], [0.5, 1], -_I(3), np.zeros(3), [cone])
+    return m, dict(status="Optimal", primal_obj=-1.0, x_at={1: 1.0})
+
+
+def possemideftrisparse4():  # :703-733
+    G = np.zeros((10, 1))
+    G[[0, 1, 2, 5, 9], 0] = -1
+    h = np.zeros(10)
+    h[[3, 4, 6, 7, 8]] = RT2 * np.array([1, 1, 1, -1, 1.0])
+    cone = cs.psd_sparse(5, [1, 2, 3, 4, 4, 4, 5, 5, 5, 5], [1, 2, 3, 1, 2, 4, 1, 2, 3, 5])
+    m = Model([1], np.zeros((0, 1)), [], G, h, [cone])
+    inv6, invrt6 = 1 / 6, 1 / (RT2 * RT3)
+    s = [RT3, RT3, RT3, RT2, RT2, RT3, RT2, -RT2, RT2, RT3]
+    z = [inv6, inv6, inv6, 0, 0, 0, -invrt6, invrt6, -invrt6, 0.5]
+    return m, dict(status="Optimal", primal_obj=RT3, s=s, z=z)
+
+
+def possemideftrisparse5():  # :735-784 (use_dual = true)
+    G = np.vstack([-_I(6), np.zeros((6, 6))])
+    G[0, 1:] = 0.5
+    h = np.concatenate([np.zeros(6), RT2 * np.array([1, 1, 0, 1, -1, 1.0])])
+    cone = cs.psd_sparse(5, [1, 2, 3, 4, 5, 4, 4, 4, 5, 5, 5], [1, 2, 3, 4, 5, 1, 2, 3, 1, 2, 3], use_dual=True)
+    c = np.concatenate([[1.0], np.zeros(5)])
+    m = Model(c, np.zeros((0, 6)), [], G, h, [cs.Nonnegative(1), cone])
+    invrt2, invrt3 = 1 / RT2, 1 / RT3
+    invrt6 = invrt2 * invrt3
+    s = [0, invrt2 + invrt3, invrt2 + invrt3, invrt3, RT2, RT3, RT2, RT2, 0, RT2, -RT2, RT2]
+    z = [1, 0.5, 0.5, 0.5, 0.5, 0.5, -0.5, -0.5, 0, -invrt6, invrt6, -invrt6]
+    return m, dict(status="Optimal", primal_obj=RT2 + RT3, s=s, z=z)
+
+
 KNOWN_ANSWER = {
     f.__name__: f
     for f in (
@@ -272,6 +305,7 @@ KNOWN_ANSWER = {
         possemideftri1, possemideftri2, possemideftri8, possemideftri9,
         epinorminf1, epinorminf2, epinorminf3, epinorminf3_dual, epinorminf4,
         doublynonnegativetri1, doublynonnegativetri2,
+        possemideftrisparse1, possemideftrisparse4, possemideftrisparse5,
         epinormeucl1, epinormeucl2, epinormeucl3,
         epipersquare1, epipersquare2, epipersquare3, epipersquare4,
         wsosinterpnonnegative1, wsosinterpnonnegative2, wsosinterpnonnegative3,
@@ -334,6 +368,20 @@ def nearestdnn(side: int = 12, seed: int = 1) -> Model:
     A = np.vstack([tr, ones])
     b = [1.0, 1.0 + 0.25 * (side - 1)]
     return Model(c, A, b, -_I(dim), np.zeros(dim), [cs.DoublyNonnegativeTri(dim)])
+
+
+def sparsepsd_maxeig(side: int = 20, seed: int = 1) -> Model:
+    """The model of test/nativeinstances.jl:657-701 (possemideftrisparse3, real case) on a seeded pattern: the largest
+    eigenvalue of a sparse symmetric matrix as a conic program over the sparse PSD cone with the dual barrier."""
+    rng = np.random.default_rng(seed)
+    mask = np.tril(rng.random((side, side)) < 1.0 / math.sqrt(side), -1) | np.eye(side, dtype=bool)
+    cols, rows = np.nonzero(mask.T)
+    vals = rng.random(rows.size) + (rows == cols)
+    dim = rows.size
+    c = -np.where(rows == cols, vals, RT2 * vals)
+    A = (rows == cols).astype(np.float64)[None, :]
+    cone = cs.psd_sparse(side, rows + 1, cols + 1, use_dual=True)
+    return Model(c, A, [1.0], -_I(dim), np.zeros(dim), [cone])
 
 
 def polymin(n: int = 2, halfdeg: int = 30, seed: int = 1) -> Model:

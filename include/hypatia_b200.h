@@ -32,7 +32,9 @@ enum hyb_cone_type {
     HYB_CONE_WSOSINTERPNONNEGATIVE = 4,   /* wsosinterpnonnegative.jl */
     HYB_CONE_WSOSINTERPPOSSEMIDEFTRI = 5, /* wsosinterppossemideftri.jl */
     HYB_CONE_EPINORMINF = 6,              /* epinorminf.jl (real; use_dual_barrier: epigraph of the 1-norm) */
-    HYB_CONE_DOUBLYNONNEGATIVETRI = 7     /* doublynonnegativetri.jl (real svec; side_or_R = side) */
+    HYB_CONE_DOUBLYNONNEGATIVETRI = 7,    /* doublynonnegativetri.jl (real svec; side_or_R = side) */
+    HYB_CONE_POSSEMIDEFTRISPARSE = 8      /* possemideftrisparse/denseimpl.jl (real): side_or_R = side, dim = pattern size,
+                                             Ls = dim 0-based rows then dim 0-based columns of the pattern (row >= col) */
 };
 
 /* One entry per cone of model.cones, in order; offsets follow build_cone_idxs
@@ -47,7 +49,7 @@ typedef struct hyb_cone_desc {
     int32_t nPs;              /* WSOS: number of P matrices */
     int32_t _pad;
     const double* const* Ps;  /* WSOS: nPs column-major U x L[k] matrices */
-    const int64_t* Ls;        /* WSOS: nPs column counts */
+    const int64_t* Ls;        /* WSOS: nPs column counts; PosSemidefTriSparse: the pattern (2 dim entries) */
 } hyb_cone_desc;
 
 /* ---- context --------------------------------------------------------------- */

@@ -794,6 +794,78 @@ class _GenericHessCone(Cone):
         self.use_hess_prod_slow_updated = True
 
 
+class PosSemidefTriSparse(_GenericHessCone):
+    """src/Cones/possemideftrisparse/denseimpl.jl (real case): -logdet of the matrix with the given sparsity
+    pattern; gradient and Hessian restricted to the pattern, every other product generic (stored Hessian + its
+    Cholesky), hess_prod_slow! through the Cholesky factor of the matrix."""
+
+    def setup_extra_data(self):
+        sp = self.spec
+        self.side, self.ri, self.ci = sp.side, sp.rows0, sp.cols0
+        self.offd = self.ri != self.ci
+        self.scale = np.where(self.offd, 1.0 / RT2, 1.0)
+
+    def _to_mat(self, vec):  # svec_to_smat_sparse! (:216-231) + copytri!
+        M = np.zeros((self.side, self.side))
+        x = vec * self.scale
+        M[self.ri, self.ci] = x
+        M[self.ci, self.ri] = x
+        return M
+
+    def _to_vec(self, M):  # smat_to_svec_sparse! (:251-267)
+        return M[self.ri, self.ci] / self.scale
+
+    def update_feas(self):  # :32-44
+        self.mat = self._to_mat(self.point)
+        c, info = lapack.dpotrf(self.mat, lower=0, clean=1)
+        self.fact_U = c
+        self.is_feas_flag = info == 0
+        self.feas_updated = True
+        return self.is_feas_flag
+
+    def update_grad(self):  # :46-59
+        inv_mat, _ = lapack.dpotri(self.fact_U, lower=0)
+        self.inv_mat = np.triu(inv_mat) + np.triu(inv_mat, 1).T
+        self.grad_vec = -self._to_vec(self.inv_mat)
+        self.grad_updated = True
+        return self.grad_vec
+
+    def update_hess(self):  # :61-88
+        self.grad()
+        Li, ri, ci, od = self.inv_mat, self.ri, self.ci, self.offd
+        i1, j1 = ri[:, None], ci[:, None]
+        i2, j2 = ri[None, :], ci[None, :]
+        both_diag = (~od)[:, None] & (~od)[None, :]
+        one_diag = (~od)[:, None] ^ (~od)[None, :]
+        H = Li[i1, i2] * Li[j1, j2] + Li[i1, j2] * Li[j1, i2]
+        H = np.where(one_diag, RT2 * Li[i1, i2] * Li[j1, j2], H)
+        H = np.where(both_diag, Li[i1, i2] ** 2, H)
+        self.hess_mat = H
+        self.hess_updated = True
+
+    def hess_prod_slow(self, arr):  # :142-163
+        if not self.use_hess_prod_slow_updated:
+            self.update_use_hess_prod_slow()
+        if not self.use_hess_prod_slow:
+            return self.hess_prod(arr)
+        a, one_d = _as2d(arr)
+        out = np.empty_like(a)
+        for j in range(a.shape[1]):
+            L = self._to_mat(a[:, j])
+            L = sla.cho_solve((self.fact_U, False), L)
+            L = sla.cho_solve((self.fact_U, False), L.T).T
+            out[:, j] = self._to_vec(L)
+        return out[:, 0] if one_d else out
+
+    def dder3(self, direction):  # :165-176: columns of L^-1 D Lambda^-1, pairwise dot products on the pattern
+        U = self.fact_U
+        D = self._to_mat(direction)
+        M = sla.solve_triangular(U, D, trans="T", lower=False)  # L^-1 D  (L = U')
+        M = sla.cho_solve((U, False), M.T).T  # (L^-1 D) Lambda^-1
+        x = np.einsum("ki,ki->i", M[:, self.ri], M[:, self.ci])
+        return x / self.scale
+
+
 class WSOSInterpNonnegative(_GenericHessCone):
     def setup_extra_data(self):
         self.Ps = self.spec.Ps
@@ -994,6 +1066,7 @@ _CLASSES = {
     cs.WSOSINTERPPOSSEMIDEFTRI: WSOSInterpPosSemidefTri,
     cs.EPINORMINF: EpiNormInf,
     cs.DOUBLYNONNEGATIVETRI: DoublyNonnegativeTri,
+    cs.POSSEMIDEFTRISPARSE: PosSemidefTriSparse,
 }
 
 

@@ -33,6 +33,7 @@ SEEDED = {
     "nearestpsd_side20": ("nearestpsd", dict(side=20, seed=1)),
     "polymin_n2_hd4": ("polymin", dict(n=2, halfdeg=4, seed=1)),
     "nearestdnn_side12": ("nearestdnn", dict(side=12, seed=1)),
+    "sparsepsd_maxeig_side20": ("sparsepsd_maxeig", dict(side=20, seed=1)),
 }
 
 

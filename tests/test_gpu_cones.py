@@ -19,7 +19,9 @@ def interior_point(specs, rng, noise=0.1, scale=1.0):
     out = []
     for s in specs:
         p = s.initial_point()
-        if s.type_code == cs.POSSEMIDEFTRI:
+        if s.type_code == cs.POSSEMIDEFTRISPARSE:
+            p = p * 2.0 + noise * (2 * rng.random(s.dim) - 1) / max(1.0, np.sqrt(s.side))
+        elif s.type_code == cs.POSSEMIDEFTRI:
             B = rng.standard_normal((s.side, s.side)) * noise
             p = p + cs.smat_to_svec(B @ B.T)
         else:
@@ -40,6 +42,13 @@ def _wsospsd(n, halfdeg, R):
 
     U, _, Ps = pu.interpolate(pu.BoxDomain(-np.ones(n), np.ones(n)), halfdeg, sample=False)
     return cs.wsos_psd(R, U, Ps)
+
+
+def _spsd(side, seed, use_dual=False):
+    rng = np.random.default_rng(seed)
+    mask = np.tril(rng.random((side, side)) < 1.0 / np.sqrt(side), -1) | np.eye(side, dtype=bool)
+    cols, rows = np.nonzero(mask.T)
+    return cs.psd_sparse(side, rows + 1, cols + 1, use_dual=use_dual)
 
 
 SPEC_SETS = {
@@ -67,6 +76,9 @@ SPEC_SETS = {
     # DoublyNonnegativeTri: stored Hessian + its Cholesky (the generic oracles), odd offsets, next to other families
     "dnn": [cs.DoublyNonnegativeTri(cs.svec_length(s)) for s in (1, 2, 3)] + [cs.Nonnegative(2)]
     + [cs.DoublyNonnegativeTri(cs.svec_length(s)) for s in (6, 12)] + [cs.EpiNormEucl(5), cs.DoublyNonnegativeTri(cs.svec_length(20))],
+    # PosSemidefTriSparse, dense implementation: seeded patterns (test/cone.jl:296-300), primal and dual barrier
+    "psd_sparse": [_spsd(1, 0), _spsd(2, 1), cs.Nonnegative(1), _spsd(10, 2), _spsd(25, 3, use_dual=True), cs.EpiNormEucl(4),
+                   _spsd(40, 4)],
     "mixed": [cs.Nonnegative(10)] + [cs.EpiNormEucl(8)] * 4 + [cs.EpiPerSquare(8)] * 4
     + [cs.PosSemidefTri(136)] * 3 + [cs.Nonnegative(3), cs.EpiNormEucl(5)],
 }
@@ -202,3 +214,25 @@ def test_many_small_cones_batch():
     ok_c, agg_c = cpu.check_neighborhood(0.9, True, 0.0, 1e9)
     ok_g, agg_g = gpu.check_neighborhood(0.9, True, 0.0, 1e9)
     assert ok_c == ok_g and abs(agg_c - agg_g) <= 1e-10 * max(1, abs(agg_c))
+
+
+def test_sparse_psd_factor_based_hess_prod_slow(monkeypatch):
+    """hess_prod_slow! of PosSemidefTriSparse through the Cholesky factor of the pattern matrix
+    (possemideftrisparse/denseimpl.jl:142-163), forced on at a benign point, against the stored-Hessian product."""
+    specs = SPEC_SETS["psd_sparse"]
+    rng = np.random.default_rng(11)
+    cpu, gpu = make_pair(specs)
+    primal = interior_point(specs, rng, scale=0.9)
+    dual = interior_point(specs, rng, scale=1.1)
+    for c in (cpu, gpu):
+        c.load_point(primal, 1.0)
+        c.load_dual_point(dual)
+        c.reset_data()
+    assert cpu.is_feas() and gpu.is_feas()
+    arr = np.asfortranarray(rng.standard_normal((cpu.q, 5)))
+    want = cpu.hess_prod(arr)
+    monkeypatch.setenv("HYB_FORCE_HESS_PROD_SLOW", "1")
+    got = gpu.hess_prod_slow(arr)
+    assert rel_err(got, want) < 1e4 * TOL
+    got1 = gpu.hess_prod_slow(arr[:, 0].copy())
+    assert rel_err(got1, want[:, 0]) < 1e4 * TOL

@@ -220,3 +220,42 @@ def test_doublynonnegativetri_barrier_derivatives():
     h = 1e-6
     fd = np.array([(barrier(s + h * e) - barrier(s - h * e)) / (2 * h) for e in np.eye(spec.dim)])
     assert np.allclose(cone.grad(), fd, rtol=1e-7, atol=1e-7)
+
+
+def rand_sppsd_pattern(side, rng):
+    """test/cone.jl:296-300: lower triangle of a random pattern of density 1/sqrt(side) plus the diagonal,
+    column-major order (findnz); 1-based."""
+    mask = np.tril(rng.random((side, side)) < 1.0 / math.sqrt(side), -1) | np.eye(side, dtype=bool)
+    cols, rows = np.nonzero(mask.T)
+    return (rows + 1).tolist(), (cols + 1).tolist()
+
+
+@pytest.mark.parametrize("side", [1, 2, 10, 25, 40])
+def test_possemideftrisparse(side):  # test/cone.jl:396-400
+    rows, cols = rand_sppsd_pattern(side, np.random.default_rng(side))
+    run_oracle_identities(cs.psd_sparse(side, rows, cols))
+
+
+def test_possemideftrisparse_barrier_derivatives():
+    """test/cone.jl:402-415: -logdet of the pattern matrix; gradient by finite differences of it."""
+    side = 8
+    rng = np.random.default_rng(2)
+    rows, cols = rand_sppsd_pattern(side, rng)
+    spec = cs.psd_sparse(side, rows, cols)
+    r0, c0 = spec.rows0, spec.cols0
+    scale = np.where(r0 != c0, 1 / math.sqrt(2.0), 1.0)
+
+    def mat(v):
+        M = np.zeros((side, side))
+        M[r0, c0] = v * scale
+        M[c0, r0] = v * scale
+        return M
+
+    s = spec.initial_point() * 3.0 + 0.2 * rng.uniform(-1, 1, spec.dim)
+    cone = make_cone(spec)
+    cone.setup_data()
+    cone.load_point(s)
+    assert cone.is_feas()
+    h = 1e-6
+    fd = np.array([(-np.linalg.slogdet(mat(s + h * e))[1] + np.linalg.slogdet(mat(s - h * e))[1]) / (2 * h) for e in np.eye(spec.dim)])
+    assert np.allclose(cone.grad(), fd, rtol=1e-6, atol=1e-7)
