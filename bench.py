@@ -87,10 +87,47 @@ class ClockSampler:
     def __init__(self, index=0):
         self.index = index
         self.samples = []
+        self.source = "nvidia-smi --query-gpu"
         self._stop = threading.Event()
         self._thread = None
 
+    def _run_nvml(self) -> bool:
+        """In-process NVML queries (the library nvidia-smi itself reads): no process spawn and no enumeration of
+        every GPU of the node five times a second beside the timed iterations.  False if NVML is unavailable."""
+        try:
+            import pynvml as nv
+
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            smax = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            bits = {"hw_slowdown": nv.nvmlClocksEventReasonHwSlowdown if hasattr(nv, "nvmlClocksEventReasonHwSlowdown") else nv.nvmlClocksThrottleReasonHwSlowdown,
+                    "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", None) or nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                    "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", None) or nv.nvmlClocksThrottleReasonSwThermalSlowdown,
+                    "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap", None) or nv.nvmlClocksThrottleReasonSwPowerCap}
+            get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+            nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+            get_reasons(h)
+        except Exception:
+            return False
+        self.source = "NVML in-process (nvmlDeviceGetClockInfo / nvmlDeviceGetCurrentClocksEventReasons, what nvidia-smi reads)"
+        while not self._stop.is_set():
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                r = get_reasons(h)
+                try:
+                    pw = nv.nvmlDeviceGetPowerUsage(h) / 1000.0
+                except Exception:
+                    pw = 0.0
+                self.samples.append([str(sm), str(smax), str(pw)] + ["Active" if (r & bits[k]) else "Not Active" for k in
+                                                                       ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")])
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+        return True
+
     def _run(self):
+        if os.environ.get("HYB_CLOCKS_NVIDIA_SMI") != "1" and self._run_nvml():
+            return
         while not self._stop.is_set():
             try:
                 out = subprocess.run(
@@ -122,8 +159,9 @@ class ClockSampler:
                 if val.lower().startswith("active"):
                     reasons.add(name)
         if not sm:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(smax)), "reasons": sorted(reasons), "samples": len(sm)}
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0, "source": self.source}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(smax)), "reasons": sorted(reasons), "samples": len(sm),
+                "source": self.source}
 
 
 # Solver options of the reference's own benchmark protocol (benchmarks/natvsext/run.jl:44-60), used by both
@@ -425,13 +463,20 @@ def main():
         orig_init()
         if threadpool_limits is not None:
             threadpool_limits(loop_threads)
+        if solves and not rootworker:
+            # A later solve starts after a second or so of host-only set-up with idle GPUs (and idle NVLink): its
+            # first iterations would run 2-6 ms slower than the steady state the W warm-up iterations of the first
+            # solve are there to reach.  Re-warm, untimed, with what iteration 0 does first: update_lhs at the
+            # initial point (assembly on every GPU + factorization), twice; iteration 0 recomputes it.
+            for _ in range(2):
+                gpu.syssolver.update_lhs(gpu)
         timer.start()
 
     gpu._initialize_point = init_and_start
     if rootworker:
         timer.shard_ctx = lambda: gpu.syssolver.shard.ctx
     # The model converges in fewer iterations than warm-up + steps may ask for: the timed iterations
-    # then continue into a fresh solve of the same model (its set-up is outside the timed iterations,
+    # then continue into another solve of the same model (its set-up is outside the timed iterations,
     # like the first solve's), until exactly `steps` iterations have been timed.
     solves = []
     setup_s = {}
@@ -439,7 +484,13 @@ def main():
         if threadpool_limits is not None:
             threadpool_limits(cores if rank == 0 else 1)
         gpu.iter_limit = max(1, warmup + steps - len(timer.rows))
-        gpu.load(model)
+        if rootworker or not solves:
+            gpu.load(model)
+        else:
+            # another solve of the same model through the reference's warm re-solve path (Solvers.modify_c!,
+            # Solvers.jl:296-311, then setup_modified :431-452): the system solver stays loaded, the initial point
+            # is rebuilt -- no device buffer is freed and reallocated between two timed iterations
+            gpu.modify_c(model.c)
         gpu.solve()
         sync()
         solves.append({"status": gpu.status, "iterations": int(gpu.num_iters)})
@@ -520,6 +571,10 @@ def main():
         # dual-equality pivoted QR (hyb_geqp3 on the GPU) + initial point, upload of G*Q2
         "setup_s": setup_s,
         "phase_ms": {name: float(np.mean([r["ph_" + name] for r in rows])) for name in ("upsys", "uprhs", "getdir", "search")},
+        # spread of the timed iterations (wall, ms): a host-side stall in one iteration shows here, not in the mean
+        "step_ms_min_median_max": [float(1e3 * f([r["wall_s"] for r in rows])) for f in (np.min, np.median, np.max)],
+        "step_ms": [round(1e3 * r["wall_s"], 2) for r in rows],
+        "step_upsys_ms": [round(r["ph_upsys"], 2) for r in rows],
         "schur_assemble_ms": t_w + t_syrk,
         "schur_reduce_ms": reduce_ms,
         "cholesky_ms": t_fact,

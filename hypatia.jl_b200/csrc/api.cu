@@ -96,6 +96,9 @@ static void free_model(hyb_ctx* c) {
     }
     hyb_dirs_free(c);
     hyb_symindef_free(c);
+    cudaFree(c->own_bases_dev);
+    c->own_bases_dev = nullptr;
+    c->own_bases_host.clear();
     for (auto& r : c->stage) cudaFree(r.buf);
     c->stage.clear();
     if (c->peer_ipc_base) cudaIpcCloseMemHandle(c->peer_ipc_base);
@@ -488,13 +491,21 @@ int hyb_schur_assemble_into(hyb_ctx* c, double* Sdst, double* t_assemble_ms) {
             } else {
                 HYB_CHECK(staged_rows(c, c->GQ2, off, rows, true, &Ak, &lda));
             }
-            HYB_CHECK(hyb_gemm_tn(c->st, N, N, rows, 1.0, Ak, lda, Bk, ldb, first ? 0.0 : 1.0, Sdst, c->ldS, HYB_GEMM_UPPER));
+            HybTileOwners own;
+            own.bases = c->own_bases_dev;
+            own.n = (int)c->own_bases_host.size();
+            HYB_CHECK(hyb_gemm_tn(c->st, N, N, rows, 1.0, Ak, lda, Bk, ldb, first ? 0.0 : 1.0, Sdst, c->ldS, HYB_GEMM_UPPER,
+                                  (own.bases && Sdst == nullptr) ? &own : nullptr));
             first = false;
             b0 = b1;
         }
     } else {
         HYB_CUDA(cudaEventRecord(c->ev3, c->st));
-        HYB_CUDA(cudaMemsetAsync(Sdst, 0, sizeof(double) * c->ldS * N, c->st));
+        if (Sdst) {
+            HYB_CUDA(cudaMemsetAsync(Sdst, 0, sizeof(double) * c->ldS * N, c->st));
+        } else {  // an empty shard contributes zeros to every owner
+            for (double* b : c->own_bases_host) HYB_CUDA(cudaMemsetAsync(b, 0, sizeof(double) * c->own_slot_elems, c->st));
+        }
     }
     HYB_CUDA(cudaEventRecord(c->ev1, c->st));
     HYB_CUDA(cudaEventSynchronize(c->ev1));

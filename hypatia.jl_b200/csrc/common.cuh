@@ -73,8 +73,16 @@ static inline int hyb_num_sms() {
 // flags: HYB_GEMM_UPPER -> only tiles/entries with col >= row are computed/stored
 // (requires the A and B tile grids to coincide, i.e. SYRK-like use).
 enum { HYB_GEMM_UPPER = 1, HYB_GEMM_CVEC = 2 /* internal: C is 16-byte aligned with even ldc */ };
+// own (optional): the result is scattered by tile column over `n` owners (the reduce-scatter of the multi-GPU
+// Schur assembly, multi.cu): tile column tj goes to bases[tj % n] at column block tj / n (compact storage,
+// leading dimension ldc); `bases` is a DEVICE array of n device pointers (local or peer memory); C is ignored.
+struct HybTileOwners {
+    double* const* bases = nullptr;
+    int n = 0;
+};
 int hyb_gemm_tn(cudaStream_t st, int64_t M, int64_t N, int64_t K, double alpha, const double* A, int64_t lda,
-                const double* B, int64_t ldb, double beta, double* C, int64_t ldc, int flags);
+                const double* B, int64_t ldb, double beta, double* C, int64_t ldc, int flags,
+                const HybTileOwners* own = nullptr);
 int hyb_gemm_tn_blockdiag(cudaStream_t st, int64_t M, int64_t N, int64_t K, int64_t step, int64_t batch, double alpha,
                           const double* A, int64_t lda, const double* B, int64_t ldb, double beta, double* C,
                           int64_t ldc);

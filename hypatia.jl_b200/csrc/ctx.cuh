@@ -49,6 +49,11 @@ struct hyb_ctx {
     double* peer_slot = nullptr;    // this rank's slot (local pointer on root, IPC-mapped elsewhere)
     void* peer_ipc_base = nullptr;  // non-root: pointer returned by cudaIpcOpenMemHandle
     int peer_world = 0, peer_rank = 0;
+    // reduce-scatter form (multi.cu): tile column tj of this context's partial Schur matrix goes to owner tj % n,
+    // into this source's compact slot there (own_bases: device array of the n slot bases; host copy for memsets)
+    double** own_bases_dev = nullptr;
+    std::vector<double*> own_bases_host;
+    int64_t own_slot_elems = 0;
     HybDirs* dirs = nullptr;  // direction engine state (allocated by hyb_dirs_setup)
     HybSymIndef* symindef = nullptr;  // dense symmetric-indefinite system solver state (hyb_symindef_load)
     std::vector<HybStageRun> stage;

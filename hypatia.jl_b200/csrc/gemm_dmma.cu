@@ -77,7 +77,8 @@ __device__ __forceinline__ void upper_tile_of(int idx, int T, int sb, int& ti, i
 __global__ void __launch_bounds__(THREADS, 1)
 gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
                double alpha, double beta, double* __restrict__ C, int64_t ldc, int flags, int tiles_m, int a_step,
-               int b_step, int64_t c_step, int n_main, int nsplit, double* __restrict__ ws) {
+               int b_step, int64_t c_step, int n_main, int nsplit, double* __restrict__ ws, double* const* __restrict__ own,
+               int nown) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     double* sA = (double*)base;
@@ -108,6 +109,9 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // b_step along its inner (K) coordinate, C by c_step doubles
     const int a_off = blockIdx.y * a_step, b_off = blockIdx.y * b_step;
     C += (int64_t)blockIdx.y * c_step;
+    // owner-scattered result (multi-GPU reduce-scatter): this tile column lives in owner tj % nown's memory at
+    // compact column block tj / nown; shifting the base keeps the epilogue's addressing unchanged
+    if (own) C = own[tj % nown] + ((int64_t)(tj / nown) - tj) * BN * ldc;
     const int nk_all = (K + BK - 1) / BK;
     int kt0 = 0, nk = nk_all;  // this CTA's k-steps: [kt0, kt0 + nk)
     if (partial) {
@@ -274,7 +278,8 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 // C tile = alpha * (sum of the nsplit partial tiles, in split order) + beta * C for the split tail tiles
 __global__ void __launch_bounds__(256)
 gemm_tail_reduce_kernel(int M, int N, double alpha, double beta, double* __restrict__ C, int64_t ldc, int flags,
-                        int tiles_m, int n_main, int nsplit, const double* __restrict__ ws) {
+                        int tiles_m, int n_main, int nsplit, const double* __restrict__ ws, double* const* __restrict__ own,
+                        int nown) {
     const int tile_idx = n_main + blockIdx.x;
     int ti, tj;
     if (flags & HYB_GEMM_UPPER) {
@@ -285,6 +290,7 @@ gemm_tail_reduce_kernel(int M, int N, double alpha, double beta, double* __restr
     }
     const int m0 = ti * BM, n0 = tj * BN;
     const bool upper = flags & HYB_GEMM_UPPER;
+    if (own) C = own[tj % nown] + ((int64_t)(tj / nown) - tj) * BN * ldc;
     const double* w0 = ws + (int64_t)blockIdx.x * nsplit * (BM * BN);
     for (int e = threadIdx.x; e < BM * BN; e += 256) {
         const int row = e & (BM - 1), col = e >> 7;
@@ -307,7 +313,7 @@ std::mutex g_tail_mutex;  // one workspace per (device, stream) that ever needed
 int64_t hyb_gemm_launch_count() { return g_gemm_launches; }
 
 int hyb_gemm_tn(cudaStream_t st, int64_t M, int64_t N, int64_t K, double alpha, const double* A, int64_t lda,
-                const double* B, int64_t ldb, double beta, double* C, int64_t ldc, int flags) {
+                const double* B, int64_t ldb, double beta, double* C, int64_t ldc, int flags, const HybTileOwners* own) {
     if (M <= 0 || N <= 0) return 0;
     if (K <= 0) {
         hyb_set_error("hyb_gemm_tn: K must be positive");
@@ -335,7 +341,11 @@ int hyb_gemm_tn(cudaStream_t st, int64_t M, int64_t N, int64_t K, double alpha, 
     } else {
         ntiles = (int64_t)tiles_m * tiles_n;
     }
-    if (((uintptr_t)C & 15) == 0 && (ldc & 1) == 0) flags |= HYB_GEMM_CVEC;
+    double* const* own_bases = own ? own->bases : nullptr;
+    const int nown = own ? own->n : 0;
+    if (own_bases) {  // owner bases are cudaMalloc'd (256-byte aligned); the compact blocks keep ldc
+        if ((ldc & 1) == 0) flags |= HYB_GEMM_CVEC;
+    } else if (((uintptr_t)C & 15) == 0 && (ldc & 1) == 0) flags |= HYB_GEMM_CVEC;
     if (flags & HYB_GEMM_UPPER) {  // super-block rasterisation of the triangle (HYB_GEMM_SB, default 12; 0 = plain walk)
         static const int sb = [] {
             const char* e = getenv("HYB_GEMM_SB");
@@ -376,12 +386,12 @@ int hyb_gemm_tn(cudaStream_t st, int64_t M, int64_t N, int64_t K, double alpha, 
     }
     const int64_t grid = n_main + (ntiles - n_main) * nsplit;
     gemm_tn_kernel<<<(unsigned)grid, THREADS, SMEM_BYTES, st>>>(tmA, tmB, (int)M, (int)N, (int)K, alpha, beta, C, ldc, flags,
-                                                              tiles_m, 0, 0, 0, (int)n_main, nsplit, ws);
+                                                              tiles_m, 0, 0, 0, (int)n_main, nsplit, ws, own_bases, nown);
     ++g_gemm_launches;
     HYB_CUDA(cudaGetLastError());
     if (n_main < ntiles) {
         gemm_tail_reduce_kernel<<<(unsigned)(ntiles - n_main), 256, 0, st>>>((int)M, (int)N, alpha, beta, C, ldc, flags, tiles_m,
-                                                                            (int)n_main, nsplit, ws);
+                                                                            (int)n_main, nsplit, ws, own_bases, nown);
         ++g_gemm_launches;
         HYB_CUDA(cudaGetLastError());
     }
@@ -419,7 +429,7 @@ int hyb_gemm_tn_blockdiag(cudaStream_t st, int64_t M, int64_t N, int64_t K, int6
     if (((uintptr_t)C & 15) == 0 && (ldc & 1) == 0) flags |= HYB_GEMM_CVEC;
     dim3 grid((unsigned)(tiles_m * tiles_n), (unsigned)batch);
     gemm_tn_kernel<<<grid, THREADS, SMEM_BYTES, st>>>(tmA, tmB, (int)M, (int)N, (int)K, alpha, beta, C, ldc, flags, tiles_m,
-                                                      (int)step, (int)step, step, (int)(tiles_m * tiles_n), 1, nullptr);
+                                                      (int)step, (int)step, step, (int)(tiles_m * tiles_n), 1, nullptr, nullptr, 0);
     ++g_gemm_launches;
     HYB_CUDA(cudaGetLastError());
     return 0;

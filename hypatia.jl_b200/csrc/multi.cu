@@ -13,6 +13,7 @@
 // Host threading: the per-device work of one update is issued from one short-lived host thread per
 // device (the existing entry points synchronise at return, so sequential calls from one thread would
 // serialise the GPUs).
+#include <chrono>
 #include <thread>
 
 #include "ctx.cuh"
@@ -24,10 +25,29 @@ struct hyb_multi {
     std::vector<hyb_ctx*> shard;         // shard[d] lives on devices[d]; shard[0] shares the root's G*Q2 rows
     std::vector<int64_t> row_lo, row_hi; // rows of s / z owned by shard d
     std::vector<double> t_asm;
+    // reduce-scatter of the partial Schur matrices: device o owns the tile columns j with j % ndev == o and holds
+    // ndev compact slots (one per source shard) of slot_elems doubles for them
+    std::vector<double*> own_slots;
+    int64_t slot_elems = 0;
     bool loaded = false;
 };
 
 namespace {
+
+// Owner `o` adds the ndev partial copies of its tile columns in source order (deterministic) and stores the sums
+// into the factorizing GPU's Schur matrix S (peer memory unless o is that GPU).  Compact column block jb of the
+// slots is global column block jb * nown + o; upper triangle only.
+__global__ void sum_owned_kernel(const double* __restrict__ slots, int nsrc, int64_t slot_elems, int64_t N, int64_t ld, int o,
+                                 int nown, double* __restrict__ S) {
+    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t cc = blockIdx.y;  // compact column
+    const int64_t jb = cc >> 7, gcol = ((jb * nown + o) << 7) + (cc & 127);
+    if (gcol >= N || r > gcol) return;
+    const int64_t off = r + cc * ld;
+    double acc = 0.0;
+    for (int k = 0; k < nsrc; ++k) acc += slots[k * slot_elems + off];
+    S[r + gcol * ld] = acc;
+}
 
 // Contiguous partition of the cones into ndev row ranges of about q / ndev rows each.  Cones are atoms,
 // except Nonnegative cones: the orthant is a product of 1-dimensional cones, so it is cut exactly at the
@@ -86,6 +106,11 @@ extern "C" {
 
 void hyb_multi_destroy(hyb_multi* m) {
     if (!m) return;
+    for (size_t o = 0; o < m->own_slots.size(); ++o)
+        if (m->own_slots[o]) {
+            cudaSetDevice(m->devices[o]);
+            cudaFree(m->own_slots[o]);
+        }
     for (hyb_ctx* s : m->shard) hyb_ctx_destroy(s);
     hyb_ctx_destroy(m->root);
     delete m;
@@ -112,19 +137,22 @@ hyb_multi* hyb_multi_create(int ndev, const int* devices) {
         }
         s->want_assemble_only = true;
         m->shard.push_back(s);
-        if (devices[d] != devices[0]) {  // kernels on device d store into the root's memory
+        // kernels on device d store tiles into every other device's memory (reduce-scatter of the partial Schur
+        // matrices) and the owners store their sums into the first device's
+        for (int e2 = 0; e2 < ndev; ++e2) {
+            if (devices[e2] == devices[d]) continue;
             int can = 0;
-            cudaDeviceCanAccessPeer(&can, devices[d], devices[0]);
+            cudaDeviceCanAccessPeer(&can, devices[d], devices[e2]);
             if (!can) {
                 hyb_set_error("hyb_multi_create: device %d cannot access the memory of device %d (no P2P / NVLink path)", devices[d],
-                              devices[0]);
+                              devices[e2]);
                 hyb_multi_destroy(m);
                 return nullptr;
             }
             cudaSetDevice(devices[d]);
-            cudaError_t e = cudaDeviceEnablePeerAccess(devices[0], 0);
+            cudaError_t e = cudaDeviceEnablePeerAccess(devices[e2], 0);
             if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
-                hyb_set_error("hyb_multi_create: cudaDeviceEnablePeerAccess(%d -> %d): %s", devices[d], devices[0],
+                hyb_set_error("hyb_multi_create: cudaDeviceEnablePeerAccess(%d -> %d): %s", devices[d], devices[e2],
                               cudaGetErrorString(e));
                 hyb_multi_destroy(m);
                 return nullptr;
@@ -176,10 +204,21 @@ int hyb_multi_model_load(hyb_multi* m, int64_t q, int64_t N, const double* GQ2, 
         for (int d = 0; d < m->ndev; ++d) m->row_lo[d] = m->row_hi[d] = 0;
         return 0;
     }
-    unsigned char handle[64];
-    HYB_CHECK(hyb_peer_root_create(m->root, m->ndev, handle));  // ndev slots of ldS x N doubles on the root
+    // owner slots: ceil(T / ndev) column blocks of 128 columns x ldS rows per (owner, source)
+    const int64_t T = (N + 127) / 128, ncb = (T + m->ndev - 1) / m->ndev;
+    m->slot_elems = ncb * 128 * m->root->ldS;
+    for (size_t o = 0; o < m->own_slots.size(); ++o)
+        if (m->own_slots[o]) {
+            cudaSetDevice(m->devices[o]);
+            cudaFree(m->own_slots[o]);
+        }
+    m->own_slots.assign(m->ndev, nullptr);
+    for (int o = 0; o < m->ndev; ++o) {
+        HYB_CUDA(cudaSetDevice(m->devices[o]));
+        HYB_CUDA(cudaMalloc(&m->own_slots[o], sizeof(double) * m->slot_elems * m->ndev));
+        HYB_CUDA(cudaMemset(m->own_slots[o], 0, sizeof(double) * m->slot_elems * m->ndev));
+    }
     const ShardPlan plan = plan_shards(q, ncones, descs, m->ndev);
-    const int64_t slot = m->root->ldS * N;
     for (int d = 0; d < m->ndev; ++d) {
         hyb_ctx* s = m->shard[d];
         const int64_t lo = plan.lo[d], rows = plan.hi[d] - plan.lo[d];
@@ -190,7 +229,15 @@ int hyb_multi_model_load(hyb_multi* m, int64_t q, int64_t N, const double* GQ2, 
             HYB_CHECK(hyb_model_load_impl(s, rows, N, nullptr, q, (int64_t)ds.size(), ds.data(), m->root, lo));
         else
             HYB_CHECK(hyb_model_load_impl(s, rows, N, GQ2 + lo, q, (int64_t)ds.size(), ds.data(), nullptr, 0));
-        s->peer_slot = m->root->peer_slots + (int64_t)d * slot;  // same process: a plain (peer) device pointer
+        // where this shard's tile columns go: its slot in every owner's memory (same process: plain peer pointers)
+        s->own_bases_host.resize(m->ndev);
+        for (int o = 0; o < m->ndev; ++o) s->own_bases_host[o] = m->own_slots[o] + (int64_t)d * m->slot_elems;
+        s->own_slot_elems = m->slot_elems;
+        HYB_CUDA(cudaSetDevice(s->device));
+        cudaFree(s->own_bases_dev);
+        HYB_CUDA(cudaMalloc(&s->own_bases_dev, sizeof(double*) * m->ndev));
+        HYB_CUDA(cudaMemcpy(s->own_bases_dev, s->own_bases_host.data(), sizeof(double*) * m->ndev, cudaMemcpyHostToDevice));
+        s->peer_slot = nullptr;
         s->peer_world = m->ndev;
         s->peer_rank = d;
     }
@@ -209,7 +256,13 @@ int hyb_multi_schur_update(hyb_multi* m, double* t_assemble_ms, double* t_reduce
         return -3;
     }
     HYB_CUDA(cudaSetDevice(r->device));
+    // HYB_MULTI_TRACE=1: host wall-clock stamps of this call's phases on stderr (a measurement aid)
+    static const bool trace = getenv("HYB_MULTI_TRACE") != nullptr;
+    const auto t0 = std::chrono::steady_clock::now();
+    auto since = [&]() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); };
     HYB_CUDA(cudaStreamSynchronize(r->st));
+    const double t_sync = since();
+    std::vector<double> t_copy(m->ndev, 0.0), t_upd(m->ndev, 0.0), t_done(m->ndev, 0.0);
     std::vector<int> rc(m->ndev, 0);
     std::vector<std::string> err(m->ndev);
     auto work = [&](int d) {
@@ -237,14 +290,18 @@ int hyb_multi_schur_update(hyb_multi* m, double* t_assemble_ms, double* t_reduce
         s->loaded_scal = r->loaded_scal;
         s->point_loaded = true;
         s->updated_irtmu = NAN;
+        t_copy[d] = since();
         int c = hyb_ensure_updated(s, s->loaded_scal);
-        if (c == 0) c = hyb_schur_assemble_into(s, s->peer_slot, &m->t_asm[d]);
+        t_upd[d] = since();
+        if (c == 0) c = hyb_schur_assemble_into(s, nullptr, &m->t_asm[d]);  // tiles go straight to their owners
+        t_done[d] = since();
         if (c != 0) fail(c);
     };
     std::vector<std::thread> th;
     for (int d = 1; d < m->ndev; ++d) th.emplace_back(work, d);
     work(0);
     for (auto& t : th) t.join();
+    const double t_join = since();
     for (int d = 0; d < m->ndev; ++d)
         if (rc[d] != 0) {
             hyb_set_error("device %d: %s", m->devices[d], err[d].c_str());
@@ -253,8 +310,36 @@ int hyb_multi_schur_update(hyb_multi* m, double* t_assemble_ms, double* t_reduce
     double ta = 0.0;
     for (int d = 0; d < m->ndev; ++d) ta = ta > m->t_asm[d] ? ta : m->t_asm[d];
     if (t_assemble_ms) *t_assemble_ms = ta;
-    HYB_CHECK(hyb_peer_root_sum(r, t_reduce_ms));
-    return hyb_schur_factor(r, t_fact_ms, fact_kind);
+    // every owner sums its tile columns and stores them into the root's Schur matrix
+    {
+        const double t_before = since();
+        const int64_t N = r->N, ncols = (m->slot_elems / r->ldS);
+        for (int o = 0; o < m->ndev; ++o) {
+            hyb_ctx* s = m->shard[o];
+            HYB_CUDA(cudaSetDevice(s->device));
+            dim3 grid((unsigned)((N + 255) / 256), (unsigned)ncols);
+            sum_owned_kernel<<<grid, 256, 0, s->st>>>(m->own_slots[o], m->ndev, m->slot_elems, N, r->ldS, o, m->ndev, r->S);
+            HYB_CUDA(cudaGetLastError());
+            ++g_misc_launches;
+        }
+        for (int o = 0; o < m->ndev; ++o) {
+            HYB_CUDA(cudaSetDevice(m->shard[o]->device));
+            HYB_CUDA(cudaStreamSynchronize(m->shard[o]->st));
+        }
+        HYB_CUDA(cudaSetDevice(r->device));
+        r->fact_ok = false;
+        if (t_reduce_ms) *t_reduce_ms = since() - t_before;
+        r->dev_ms += since() - t_before;
+    }
+    const double t_sum = since();
+    const int rcf = hyb_schur_factor(r, t_fact_ms, fact_kind);
+    if (trace) {
+        fprintf(stderr, "multi trace (ms): sync %.3f | joined %.3f | summed %.3f | factored %.3f | per device copy/update/done:", t_sync,
+                t_join, t_sum, since());
+        for (int d = 0; d < m->ndev; ++d) fprintf(stderr, " [%.3f %.3f %.3f asm %.3f]", t_copy[d], t_upd[d], t_done[d], m->t_asm[d]);
+        fprintf(stderr, "\n");
+    }
+    return rcf;
 }
 
 }  // extern "C"
