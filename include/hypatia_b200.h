@@ -260,9 +260,11 @@ int hyb_symindef_get(hyb_ctx* ctx, double* lhs);
 /* ---- several GPUs from one host process ----------------------------------------------
  * a Julia host uses a whole node with ccalls alone.  The cones are partitioned by block over the
  * devices; each device assembles the partial Schur matrix of its cones (update_lhs_fact, qrchol.jl:209-254, is
- * a sum over cones) and its syrk epilogue stores the tiles into the FIRST device's memory over NVLink (peer
- * access); that device adds the partials in device order, factorizes (posdef_fact_copy!, qrchol.jl:257-258) and
- * serves everything else.  devices[0] is the factorizing GPU.  hyb_multi_root() is its ordinary context: load
+ * a sum over cones) and its syrk epilogue stores every tile into the memory of the tile's OWNER device over NVLink
+ * (peer access; tile column j belongs to device j mod ndev); every owner adds the ndev partial copies of its columns
+ * in device order and stores the sums into the FIRST device's Schur matrix, which factorizes (posdef_fact_copy!,
+ * qrchol.jl:257-258) and serves everything else.  devices[0] is the factorizing GPU; every pair of devices needs a
+ * peer-access path.  hyb_multi_root() is its ordinary context: load
  * points, run oracles, directions and the line search through it exactly as on one GPU, and call
  * hyb_multi_schur_update where a single GPU calls hyb_schur_update. */
 typedef struct hyb_multi hyb_multi;
