@@ -27,6 +27,7 @@ WSOSINTERPPOSSEMIDEFTRI = 5
 EPINORMINF = 6
 DOUBLYNONNEGATIVETRI = 7
 POSSEMIDEFTRISPARSE = 8
+WSOSINTERPEPINORMEUCL = 9
 
 RT2 = math.sqrt(2.0)
 
@@ -364,6 +365,38 @@ class WSOSInterpPosSemidefTri(ConeSpec):
             arr[block_idxs(self.U, block).start : block_idxs(self.U, block).stop] = 1.0
             block += i + 1
         return arr
+
+
+@dataclass
+class WSOSInterpEpiNormEucl(ConeSpec):
+    """src/Cones/wsosinterpepinormeucl.jl:17-88: polynomial epigraph of the Euclidean norm of R - 1 polynomials in
+    the interpolant basis; dim = U * R; dual barrier unless use_dual."""
+
+    R: int = 2
+    U: int = 0
+    Ps: Sequence[np.ndarray] = ()
+    use_dual: bool = False
+
+    def __post_init__(self):
+        self.type_code = WSOSINTERPEPINORMEUCL
+        self.Ps = [np.asfortranarray(P, dtype=np.float64) for P in self.Ps]
+        for P in self.Ps:
+            assert P.shape[0] == self.U
+        assert self.R >= 2 and self.dim == self.U * self.R
+        self.use_dual_barrier = not self.use_dual
+
+    @property
+    def nu(self):
+        return float(2 * sum(P.shape[1] for P in self.Ps))
+
+    def initial_point(self):  # wsosinterpepinormeucl.jl:125-129
+        arr = np.zeros(self.dim)
+        arr[: self.U] = 1.0
+        return arr
+
+
+def wsos_epinormeucl(R: int, U: int, Ps, use_dual: bool = False) -> WSOSInterpEpiNormEucl:
+    return WSOSInterpEpiNormEucl(dim=U * R, R=R, U=U, Ps=Ps, use_dual=use_dual)
 
 
 def wsos_psd(R: int, U: int, Ps, use_dual: bool = False) -> WSOSInterpPosSemidefTri:

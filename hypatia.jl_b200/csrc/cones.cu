@@ -1004,6 +1004,10 @@ int hybi_cones_alloc(HybCones& cs) {
             HybDenseWsosPsd* d = nullptr;
             HYB_CHECK(hybd_wsospsd_create(&d, b.side, b.U, b.nPs, b.Ps, b.Ls));
             b.dense = d;
+        } else if (b.type == HYB_WSOSINTERPEPINORMEUCL) {
+            HybDenseWsosEuc* d = nullptr;
+            HYB_CHECK(hybd_wsoseuc_create(&d, b.side, b.U, b.nPs, b.Ps, b.Ls));
+            b.dense = d;
         } else if (b.type == HYB_DOUBLYNONNEGATIVETRI) {
             HybDenseDnn* d = nullptr;
             HYB_CHECK(hybd_dnn_create(&d, b.side));
@@ -1045,6 +1049,7 @@ void hybi_cones_free(HybCones& cs) {
         if (b.dense) {
             if (b.type == HYB_WSOSINTERPNONNEGATIVE) hybd_wsos_destroy((HybDenseWsos*)b.dense);
             else if (b.type == HYB_WSOSINTERPPOSSEMIDEFTRI) hybd_wsospsd_destroy((HybDenseWsosPsd*)b.dense);
+            else if (b.type == HYB_WSOSINTERPEPINORMEUCL) hybd_wsoseuc_destroy((HybDenseWsosEuc*)b.dense);
             else if (b.type == HYB_DOUBLYNONNEGATIVETRI || b.type == HYB_POSSEMIDEFTRISPARSE) hybd_dnn_destroy((HybDenseDnn*)b.dense);
             else hybd_psd_destroy((HybDensePsd*)b.dense);
             b.dense = nullptr;
@@ -1135,6 +1140,11 @@ int hybi_cones_update(cudaStream_t st, HybCones& cs, const double* primal, const
             case HYB_WSOSINTERPPOSSEMIDEFTRI:
                 HYB_CHECK(hybd_wsospsd_update(st, (HybDenseWsosPsd*)b.dense, primal + b.offset, dual_in + b.offset, scal,
                                               irtmu, cs.point + b.offset, cs.dual + b.offset, cs.grad + b.offset,
+                                              cs.item_flag + b.offset, cs.item_prox + b.offset));
+                break;
+            case HYB_WSOSINTERPEPINORMEUCL:
+                HYB_CHECK(hybd_wsoseuc_update(st, (HybDenseWsosEuc*)b.dense, primal + b.offset, dual_in + b.offset, scal, irtmu,
+                                              cs.point + b.offset, cs.dual + b.offset, cs.grad + b.offset,
                                               cs.item_flag + b.offset, cs.item_prox + b.offset));
                 break;
             case HYB_DOUBLYNONNEGATIVETRI:
@@ -1280,6 +1290,9 @@ int hybi_cones_prod(cudaStream_t st, HybCones& cs, int which, const double* arr,
             case HYB_WSOSINTERPPOSSEMIDEFTRI:
                 HYB_CHECK(hybd_wsospsd_prod(st, (HybDenseWsosPsd*)b.dense, op, arr + b.offset, lda, prod + b.offset, ldp, m));
                 break;
+            case HYB_WSOSINTERPEPINORMEUCL:
+                HYB_CHECK(hybd_wsoseuc_prod(st, (HybDenseWsosEuc*)b.dense, op, arr + b.offset, lda, prod + b.offset, ldp, m));
+                break;
             case HYB_DOUBLYNONNEGATIVETRI:
             case HYB_POSSEMIDEFTRISPARSE:
                 HYB_CHECK(hybd_dnn_prod(st, (HybDenseDnn*)b.dense, op, arr + b.offset, lda, prod + b.offset, ldp, m));
@@ -1339,6 +1352,9 @@ int hybi_cones_dder3(cudaStream_t st, HybCones& cs, const double* dir, double* o
                 break;
             case HYB_WSOSINTERPPOSSEMIDEFTRI:
                 HYB_CHECK(hybd_wsospsd_dder3(st, (HybDenseWsosPsd*)b.dense, dir + b.offset, out + b.offset));
+                break;
+            case HYB_WSOSINTERPEPINORMEUCL:
+                HYB_CHECK(hybd_wsoseuc_dder3(st, (HybDenseWsosEuc*)b.dense, dir + b.offset, out + b.offset));
                 break;
             case HYB_DOUBLYNONNEGATIVETRI:
             case HYB_POSSEMIDEFTRISPARSE:

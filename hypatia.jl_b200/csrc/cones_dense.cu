@@ -1543,3 +1543,417 @@ int hybd_dnn_dder3(cudaStream_t st, HybDenseDnn* c, const double* dir, double* o
     HYB_CUDA(cudaGetLastError());
     return 0;
 }
+
+// =======================================================================================
+// WSOSInterpEpiNormEucl: src/Cones/wsosinterpepinormeucl.jl   (point = R blocks of length U)
+//   update_feas :131-178   per P_k: Lam11 = P' diag(p_1) P = R11' R11;  M_r = R11^-T (P' diag(p_r) P);
+//                          mat = Lam11 - sum_r M_r' M_r = Rm' Rm
+//   is_dual_feas :180-183  first block of the dual point > eps
+//   update_grad :185-223   A = R11^-T P', B = Rm^-T P', E_r = Rm^-T (-M_r' A)
+//   update_hess :225-296   U x U blocks of P Lam^-1 P from A, B, E_r, combined entrywise (wsoseuc_hess_kernel)
+//   dder3       :298-396   the two parts restated with every product X Y' taken as (X')' (Y') on stored transposes
+//   generic Hessian-based products as for WSOSInterpNonnegative (Cones.jl:108-125, 202-252)
+// =======================================================================================
+namespace {
+
+// out[r, c] = d1[r] * X1[r, c] + (X2 ? d2[r] * X2[r, c] : 0)   (rows x cols, one leading dimension)
+__global__ void rowscale2_kernel(const double* __restrict__ X1, const double* __restrict__ d1, const double* __restrict__ X2,
+                                 const double* __restrict__ d2, int64_t rows, int64_t cols, int64_t ld, double beta,
+                                 double* __restrict__ out) {
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= rows * cols) return;
+    const int64_t r = e % rows, c = e / rows, o = r + c * ld;
+    double v = d1[r] * X1[o];
+    if (X2) v += d2[r] * X2[o];
+    out[o] = (beta == 0.0 ? 0.0 : beta * out[o]) + v;
+}
+
+// One P_k's contribution to the upper triangle of H (update_hess :248-292) from its blocks
+// Bk(r, s), r >= s, stored at blk[(r (r + 1) / 2 + s) * bstride] (U x U, ld), Bk(s, r) = Bk(r, s)'; P11 = A'A.
+__global__ void wsoseuc_hess_kernel(int64_t U, int R, const double* __restrict__ blk, int64_t bstride, int64_t ld,
+                                    const double* __restrict__ P11, double* __restrict__ H, int64_t ldH, int first) {
+    const int64_t a = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t b = blockIdx.y;
+    const int64_t dim = U * R;
+    if (a >= dim || a > b) return;
+    const int ra = (int)(a / U), rb = (int)(b / U);
+    const int64_t i = a - ra * U, j = b - rb * U;
+    auto B = [&](int r, int s, int64_t x, int64_t y) -> double {  // block (r, s) entry (x, y)
+        return (r >= s) ? blk[((int64_t)r * (r + 1) / 2 + s) * bstride + x + y * ld]
+                        : blk[((int64_t)s * (s + 1) / 2 + r) * bstride + y + x * ld];
+    };
+    double v = 0.0;
+    if (ra == 0 && rb == 0) {
+        const double p = P11[i + j * ld];
+        v = -(double)(R - 2) * p * p;
+        const double b00 = B(0, 0, i, j);
+        v += b00 * b00;
+        for (int r = 1; r < R; ++r) {
+            for (int s = 0; s < r; ++s) {
+                const double x = B(r, s, i, j), y = B(r, s, j, i);
+                v += x * x + y * y;
+            }
+            const double d = B(r, r, i, j);
+            v += d * d;
+        }
+    } else if (ra == 0) {
+        for (int s = 0; s < R; ++s) v += B(s, 0, i, j) * B(s, rb, i, j);
+        v *= 2.0;
+    } else if (ra == rb) {
+        v = 2.0 * (B(ra, 0, i, j) * B(ra, 0, j, i) + B(0, 0, i, j) * B(ra, ra, i, j));
+    } else {  // 1 <= ra < rb
+        v = 2.0 * (B(ra, 0, i, j) * B(rb, 0, j, i) + B(0, 0, i, j) * B(rb, ra, j, i));
+    }
+    H[a + b * ldH] = (first ? 0.0 : H[a + b * ldH]) + v;
+}
+
+__global__ void scale_vec_kernel(int64_t n, double a, double* __restrict__ x) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) x[i] *= a;
+}
+
+}  // namespace
+
+struct HybDenseWsosEuc {
+    int R = 0, nPs = 0;
+    int64_t U = 0, ldU = 0, dim = 0, ldD = 0;
+    double nu = 0.0;
+    std::vector<int64_t> L, ldL;
+    // per k: U x L (ld ldU): P, PD, At, Bmt, SPt, S1t, S2t;  L x U (ld ldL): A, Bm;  L x L (ld ldL): Lam, Mat, X, diagT
+    std::vector<double*> P, PD, At, Bmt, SPt, S1t, S2t, A, Bm, Lam, Mat, X, diagT;
+    std::vector<std::vector<double*>> M, E, Et, SRt, SAt, colT, rowT, half;  // [k][...]
+    std::vector<HybChol> chLam, chMat;
+    double *blk = nullptr, *P11 = nullptr;  // U x U blocks of the current k
+    int64_t bstride = 0;
+    double *H = nullptr, *Hf = nullptr, *Lh = nullptr;
+    HybChol chH;
+    double *v1 = nullptr, *v2 = nullptr, *v3 = nullptr, *scal = nullptr;
+    int *dual_ok = nullptr, *slow = nullptr, *sqrt_ok = nullptr;
+    const int** infos_dev = nullptr;
+    double *big1 = nullptr, *big2 = nullptr;
+    int64_t big_cols = 0;
+    std::vector<double*> owned;  // everything cudaMalloc'd, for destroy
+};
+
+static int euc_alloc(HybDenseWsosEuc* c, double** p, size_t elems) {
+    HYB_CUDA(cudaMalloc(p, sizeof(double) * (elems > 0 ? elems : 1)));
+    HYB_CUDA(cudaMemset(*p, 0, sizeof(double) * (elems > 0 ? elems : 1)));
+    c->owned.push_back(*p);
+    return 0;
+}
+
+int hybd_wsoseuc_create(HybDenseWsosEuc** out, int R, int64_t U, int nPs, const double* const* Ps_host, const int64_t* Ls) {
+    HybDenseWsosEuc* c = new HybDenseWsosEuc();
+    c->R = R;
+    c->U = U;
+    c->nPs = nPs;
+    c->ldU = hyb_round_up(U, 16);
+    c->dim = U * R;
+    c->ldD = hyb_round_up(c->dim, 16);
+    const int R1 = R - 1;
+    auto resize = [&](std::vector<double*>& v) { v.assign(nPs, nullptr); };
+    for (auto* v : {&c->P, &c->PD, &c->At, &c->Bmt, &c->SPt, &c->S1t, &c->S2t, &c->A, &c->Bm, &c->Lam, &c->Mat, &c->X, &c->diagT})
+        resize(*v);
+    for (auto* v : {&c->M, &c->E, &c->Et, &c->SRt, &c->SAt, &c->colT, &c->rowT, &c->half}) v->assign(nPs, {});
+    c->chLam.resize(nPs);
+    c->chMat.resize(nPs);
+    double sumL = 0;
+    for (int k = 0; k < nPs; ++k) {
+        const int64_t L = Ls[k], ldL = hyb_round_up(L, 16), ldU = c->ldU;
+        c->L.push_back(L);
+        c->ldL.push_back(ldL);
+        sumL += (double)L;
+        for (double** p : {&c->P[k], &c->PD[k], &c->At[k], &c->Bmt[k], &c->SPt[k], &c->S1t[k], &c->S2t[k]})
+            HYB_CHECK(euc_alloc(c, p, ldU * L));
+        for (double** p : {&c->A[k], &c->Bm[k]}) HYB_CHECK(euc_alloc(c, p, ldL * U));
+        for (double** p : {&c->Lam[k], &c->Mat[k], &c->X[k], &c->diagT[k]}) HYB_CHECK(euc_alloc(c, p, ldL * L));
+        auto many = [&](std::vector<double*>& v, int n, size_t elems) -> int {
+            v.assign(n, nullptr);
+            for (int i = 0; i < n; ++i) HYB_CHECK(euc_alloc(c, &v[i], elems));
+            return 0;
+        };
+        HYB_CHECK(many(c->M[k], R1, ldL * L));
+        HYB_CHECK(many(c->E[k], R1, ldL * U));
+        HYB_CHECK(many(c->Et[k], R1, ldU * L));
+        HYB_CHECK(many(c->SRt[k], R1, ldU * L));
+        HYB_CHECK(many(c->SAt[k], R, ldU * L));
+        HYB_CHECK(many(c->colT[k], R, ldL * L));
+        HYB_CHECK(many(c->rowT[k], R1, ldL * L));
+        HYB_CHECK(many(c->half[k], R * R, ldL * U));
+        HYB_CUDA(cudaMemcpy2D(c->P[k], sizeof(double) * ldU, Ps_host[k], sizeof(double) * U, sizeof(double) * U, L,
+                              cudaMemcpyHostToDevice));
+        HYB_CHECK(hyb_chol_attach(c->chLam[k], c->Lam[k], ldL, L));
+        HYB_CHECK(hyb_chol_attach(c->chMat[k], c->Mat[k], ldL, L));
+    }
+    c->nu = 2.0 * sumL;
+    c->bstride = c->ldU * U;
+    HYB_CHECK(euc_alloc(c, &c->blk, c->bstride * (R * (R + 1) / 2)));
+    HYB_CHECK(euc_alloc(c, &c->P11, c->bstride));
+    for (double** p : {&c->H, &c->Hf, &c->Lh}) HYB_CHECK(euc_alloc(c, p, c->ldD * c->dim));
+    for (double** p : {&c->v1, &c->v2, &c->v3}) HYB_CHECK(euc_alloc(c, p, c->ldD));
+    HYB_CHECK(euc_alloc(c, &c->scal, 8));
+    HYB_CUDA(cudaMalloc(&c->dual_ok, sizeof(int)));
+    HYB_CUDA(cudaMalloc(&c->slow, sizeof(int)));
+    HYB_CUDA(cudaMalloc(&c->sqrt_ok, sizeof(int)));
+    HYB_CUDA(cudaMemset(c->sqrt_ok, 0, sizeof(int)));
+    HYB_CHECK(hyb_chol_attach(c->chH, c->Hf, c->ldD, c->dim));
+    std::vector<const int*> infos;
+    for (int k = 0; k < nPs; ++k) {
+        infos.push_back(c->chLam[k].info);
+        infos.push_back(c->chMat[k].info);
+    }
+    HYB_CUDA(cudaMalloc(&c->infos_dev, sizeof(int*) * infos.size()));
+    HYB_CUDA(cudaMemcpy(c->infos_dev, infos.data(), sizeof(int*) * infos.size(), cudaMemcpyHostToDevice));
+    *out = c;
+    return 0;
+}
+
+void hybd_wsoseuc_destroy(HybDenseWsosEuc* c) {
+    if (!c) return;
+    for (auto& ch : c->chLam) hyb_chol_free(ch);
+    for (auto& ch : c->chMat) hyb_chol_free(ch);
+    hyb_chol_free(c->chH);
+    for (double* p : c->owned) cudaFree(p);
+    cudaFree(c->dual_ok);
+    cudaFree(c->slow);
+    cudaFree(c->sqrt_ok);
+    cudaFree((void*)c->infos_dev);
+    cudaFree(c->big1);
+    cudaFree(c->big2);
+    delete c;
+}
+
+int hybd_wsoseuc_update(cudaStream_t st, HybDenseWsosEuc* c, const double* primal, const double* dual_in, double scal,
+                        double irtmu, double* point, double* dual_out, double* grad, int* flag, double* prox) {
+    const int64_t U = c->U, ldU = c->ldU, dim = c->dim, ldD = c->ldD;
+    const int R = c->R;
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, scal, primal, 0.0, nullptr, point);
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, dual_in, 0.0, nullptr, dual_out);
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, point, 0.0, nullptr, c->v3);
+    all_gt_eps_kernel<<<1, 1024, 0, st>>>(U, dual_out, c->dual_ok);
+    g_dense_launches += 4;
+    HYB_CUDA(cudaGetLastError());
+    // update_feas
+    for (int k = 0; k < c->nPs; ++k) {
+        const int64_t L = c->L[k], ldL = c->ldL[k];
+        rowscale_kernel<<<nb1(U * L), 256, 0, st>>>(c->P[k], c->v3, U, L, ldU, c->PD[k]);
+        DLAUNCHED();
+        HYB_CHECK(hyb_gemm_tn(st, L, L, U, 1.0, c->P[k], ldU, c->PD[k], ldU, 0.0, c->Lam[k], ldL, HYB_GEMM_UPPER));
+        copy_mat_kernel<<<nb1(L * L), 256, 0, st>>>(c->Lam[k], ldL, c->Mat[k], ldL, L, L);
+        DLAUNCHED();
+        HYB_CHECK(hyb_potrf(st, c->chLam[k], nullptr));
+        for (int r = 1; r < R; ++r) {
+            rowscale_kernel<<<nb1(U * L), 256, 0, st>>>(c->P[k], c->v3 + r * U, U, L, ldU, c->PD[k]);
+            DLAUNCHED();
+            HYB_CHECK(hyb_gemm_tn(st, L, L, U, 1.0, c->P[k], ldU, c->PD[k], ldU, 0.0, c->M[k][r - 1], ldL, 0));
+            HYB_CHECK(hyb_trsm_fwd(st, c->Lam[k], ldL, L, c->M[k][r - 1], ldL, L));
+            HYB_CHECK(hyb_gemm_tn(st, L, L, L, -1.0, c->M[k][r - 1], ldL, c->M[k][r - 1], ldL, 1.0, c->Mat[k], ldL, HYB_GEMM_UPPER));
+        }
+        HYB_CHECK(hyb_potrf(st, c->chMat[k], nullptr));
+    }
+    {
+        std::vector<int> infs(2 * c->nPs, 0);
+        for (int k = 0; k < c->nPs; ++k) {
+            HYB_CUDA(cudaMemcpyAsync(&infs[2 * k], c->chLam[k].info, sizeof(int), cudaMemcpyDeviceToHost, st));
+            HYB_CUDA(cudaMemcpyAsync(&infs[2 * k + 1], c->chMat[k].info, sizeof(int), cudaMemcpyDeviceToHost, st));
+        }
+        HYB_CUDA(cudaStreamSynchronize(st));
+        bool infeasible = false;
+        for (int v : infs) infeasible = infeasible || v != 0;
+        if (infeasible) {  // rejected before any gradient / Hessian oracle is asked for (search.jl:146-150)
+            wsos_finalize_kernel<<<1, 1, 0, st>>>(c->infos_dev, 2 * c->nPs, c->chH.info, c->dual_ok, c->scal, c->nu, dim, flag, prox,
+                                                  c->slow, c->sqrt_ok);
+            DLAUNCHED();
+            HYB_CUDA(cudaGetLastError());
+            return 0;
+        }
+    }
+    // update_grad + update_hess
+    for (int k = 0; k < c->nPs; ++k) {
+        const int64_t L = c->L[k], ldL = c->ldL[k];
+        HYB_CHECK(hyb_transpose(st, c->P[k], ldU, U, L, c->A[k], ldL, 0));  // P' (L x U)
+        copy_mat_kernel<<<nb1(L * U), 256, 0, st>>>(c->A[k], ldL, c->Bm[k], ldL, L, U);
+        DLAUNCHED();
+        HYB_CHECK(hyb_trsm_fwd(st, c->Lam[k], ldL, L, c->A[k], ldL, U));   // A = R11^-T P'
+        HYB_CHECK(hyb_trsm_fwd(st, c->Mat[k], ldL, L, c->Bm[k], ldL, U));  // B = Rm^-T P'
+        HYB_CHECK(hyb_transpose(st, c->A[k], ldL, L, U, c->At[k], ldU, 0));
+        HYB_CHECK(hyb_transpose(st, c->Bm[k], ldL, L, U, c->Bmt[k], ldU, 0));
+        coldot_kernel<<<nb1(U, 8), 256, 0, st>>>(c->A[k], c->A[k], L, U, ldL, -1.0, k == 0 ? 0.0 : 1.0, grad);
+        coldot_kernel<<<nb1(U, 8), 256, 0, st>>>(c->Bm[k], c->Bm[k], L, U, ldL, -1.0, 1.0, grad);
+        g_dense_launches += 2;
+        for (int r = 1; r < R; ++r) {
+            double* E = c->E[k][r - 1];
+            HYB_CHECK(hyb_gemm_tn(st, L, U, L, -1.0, c->M[k][r - 1], ldL, c->A[k], ldL, 0.0, E, ldL, 0));  // -M_r' A
+            HYB_CHECK(hyb_trsm_fwd(st, c->Mat[k], ldL, L, E, ldL, U));
+            HYB_CHECK(hyb_transpose(st, E, ldL, L, U, c->Et[k][r - 1], ldU, 0));
+            coldot_kernel<<<nb1(U, 8), 256, 0, st>>>(E, c->Bm[k], L, U, ldL, -2.0, k == 0 ? 0.0 : 1.0, grad + r * U);
+            coldot_kernel<<<nb1(U, 8), 256, 0, st>>>(E, E, L, U, ldL, -1.0, 1.0, grad);
+            g_dense_launches += 2;
+        }
+        HYB_CUDA(cudaGetLastError());
+        // U x U blocks of P Lam^-1 P (update_hess :236-247)
+        auto B = [&](int r, int s) { return c->blk + ((int64_t)r * (r + 1) / 2 + s) * c->bstride; };
+        HYB_CHECK(hyb_gemm_tn(st, U, U, L, 1.0, c->A[k], ldL, c->A[k], ldL, 0.0, c->P11, ldU, 0));
+        HYB_CHECK(hyb_gemm_tn(st, U, U, L, 1.0, c->Bm[k], ldL, c->Bm[k], ldL, 0.0, B(0, 0), ldU, 0));
+        for (int r = 1; r < R; ++r) {
+            const double* Er = c->E[k][r - 1];
+            HYB_CHECK(hyb_gemm_tn(st, U, U, L, 1.0, Er, ldL, c->Bm[k], ldL, 0.0, B(r, 0), ldU, 0));
+            HYB_CHECK(hyb_gemm_tn(st, U, U, L, 1.0, Er, ldL, Er, ldL, 0.0, B(r, r), ldU, 0));
+            lincomb_kernel<<<nb1(c->bstride), 256, 0, st>>>(c->bstride, 1.0, B(r, r), 1.0, c->P11, B(r, r));
+            DLAUNCHED();
+            for (int r2 = 1; r2 < r; ++r2)
+                HYB_CHECK(hyb_gemm_tn(st, U, U, L, 1.0, Er, ldL, c->E[k][r2 - 1], ldL, 0.0, B(r, r2), ldU, 0));
+        }
+        wsoseuc_hess_kernel<<<dim3(nb1(dim), (unsigned)dim), 256, 0, st>>>(U, R, c->blk, c->bstride, ldU, c->P11, c->H, ldD, k == 0);
+        DLAUNCHED();
+        HYB_CUDA(cudaGetLastError());
+    }
+    symmetrize_kernel<<<nb1(dim * dim), 256, 0, st>>>(c->H, dim, ldD);
+    copy_upper_dense_kernel<<<nb1(dim * dim), 256, 0, st>>>(c->H, c->Hf, dim, ldD);
+    g_dense_launches += 2;
+    HYB_CHECK(hyb_potrf(st, c->chH, nullptr));
+    HYB_CHECK(hyb_transpose(st, c->Hf, ldD, dim, dim, c->Lh, ldD, 1));
+    // scalars for check_numerics / proxsqr / the hess_prod_slow switch (Cones.jl:218-227, 267-304)
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, grad, 0.0, nullptr, c->v1);
+    dot_kernel<<<1, 1024, 0, st>>>(dim, c->v1, c->v3, c->scal + 0);
+    HYB_CHECK(hyb_potrs(st, c->chH, c->v1));
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, grad, 0.0, nullptr, c->v2);
+    dot_kernel<<<1, 1024, 0, st>>>(dim, c->v1, c->v2, c->scal + 1);
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, irtmu, dual_out, 1.0, grad, c->v2);
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, c->v2, 0.0, nullptr, c->v1);
+    HYB_CHECK(hyb_potrs(st, c->chH, c->v1));
+    dot_kernel<<<1, 1024, 0, st>>>(dim, c->v1, c->v2, c->scal + 2);
+    HYB_CHECK(hyb_gemv_t(st, dim, dim, c->H, ldD, c->v3, c->v1));
+    dot_kernel<<<1, 1024, 0, st>>>(dim, c->v1, c->v3, c->scal + 3);
+    wsos_finalize_kernel<<<1, 1, 0, st>>>(c->infos_dev, 2 * c->nPs, c->chH.info, c->dual_ok, c->scal, c->nu, dim, flag, prox, c->slow,
+                                          c->sqrt_ok);
+    g_dense_launches += 10;
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int hybd_wsoseuc_sqrt_ok(cudaStream_t st, HybDenseWsosEuc* c, int* ok) {
+    HYB_CUDA(cudaMemcpyAsync(ok, c->sqrt_ok, sizeof(int), cudaMemcpyDeviceToHost, st));
+    HYB_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int hybd_wsoseuc_prod(cudaStream_t st, HybDenseWsosEuc* c, int op, const double* arr, int64_t lda, double* prod, int64_t ldp,
+                      int64_t m) {
+    if (m <= 0) return 0;
+    const int64_t D = c->dim, ldD = c->ldD;
+    if (m > c->big_cols) {
+        cudaFree(c->big1);
+        cudaFree(c->big2);
+        c->big1 = c->big2 = nullptr;
+        HYB_CUDA(cudaMalloc(&c->big1, sizeof(double) * ldD * m));
+        HYB_CUDA(cudaMalloc(&c->big2, sizeof(double) * ldD * m));
+        c->big_cols = m;
+    }
+    double *A = c->big1, *B = c->big2;
+    copy_mat_kernel<<<nb1(D * m), 256, 0, st>>>(arr, lda, A, ldD, D, m);
+    DLAUNCHED();
+    HYB_CUDA(cudaGetLastError());
+    const double* result = nullptr;
+    if (op == HYB_OP_HESS || op == 6) {  // no factor-based hess_prod_slow! for this cone: Cones.jl:229-231
+        if (m == 1) HYB_CHECK(hyb_gemv_t(st, D, D, c->H, ldD, A, B));
+        else HYB_CHECK(hyb_gemm_tn(st, D, m, D, 1.0, c->H, ldD, A, ldD, 0.0, B, ldD, 0));
+        result = B;
+    } else if (op == HYB_OP_INV_HESS) {
+        if (m == 1) {
+            HYB_CHECK(hyb_potrs(st, c->chH, A));
+        } else {
+            HYB_CHECK(hyb_trsm_fwd(st, c->Hf, ldD, D, A, ldD, m));
+            HYB_CHECK(hyb_trsm_bwd(st, c->Hf, c->Lh, ldD, D, A, ldD, m));
+        }
+        result = A;
+    } else if (op == HYB_OP_SQRT_HESS) {
+        if (m == 1) HYB_CHECK(hyb_gemv_t(st, D, D, c->Lh, ldD, A, B));
+        else HYB_CHECK(hyb_gemm_tn(st, D, m, D, 1.0, c->Lh, ldD, A, ldD, 0.0, B, ldD, 0));
+        result = B;
+    } else {
+        HYB_CHECK(hyb_trsm_fwd(st, c->Hf, ldD, D, A, ldD, m));
+        result = A;
+    }
+    copy_mat_kernel<<<nb1(D * m), 256, 0, st>>>(result, ldD, prod, ldp, D, m);
+    DLAUNCHED();
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int hybd_wsoseuc_dder3(cudaStream_t st, HybDenseWsosEuc* c, const double* dir, double* out) {
+    const int64_t U = c->U, ldU = c->ldU, dim = c->dim;
+    const int R = c->R;
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, dir, 0.0, nullptr, c->v1);  // aligned copy of the direction
+    DLAUNCHED();
+    const double* d = c->v1;
+    double* acc = c->v2;
+    auto scale = [&](const double* X, const double* dv, int64_t L, double* dst) {  // dst = diag(dv) X  (U x L)
+        rowscale2_kernel<<<nb1(U * L), 256, 0, st>>>(X, dv, nullptr, nullptr, U, L, ldU, 0.0, dst);
+        DLAUNCHED();
+    };
+    // part 1 (:305-319): -(R - 2) * sum_k |Herm(A D0 A') A|^2 column norms
+    for (int k = 0; k < c->nPs; ++k) {
+        const int64_t L = c->L[k], ldL = c->ldL[k];
+        scale(c->At[k], d, L, c->SAt[k][0]);
+        HYB_CHECK(hyb_gemm_tn(st, L, L, U, 1.0, c->SAt[k][0], ldU, c->At[k], ldU, 0.0, c->X[k], ldL, 0));   // A D0 A'
+        HYB_CHECK(hyb_gemm_tn(st, L, U, L, 1.0, c->X[k], ldL, c->A[k], ldL, 0.0, c->half[k][0], ldL, 0));  // (A D0 A')' A
+        coldot_kernel<<<nb1(U, 8), 256, 0, st>>>(c->half[k][0], c->half[k][0], L, U, ldL, 1.0, k == 0 ? 0.0 : 1.0, acc);
+        DLAUNCHED();
+    }
+    scale_vec_kernel<<<nb1(U), 256, 0, st>>>(U, (double)(2 - R), acc);
+    for (int r = 1; r < R; ++r) HYB_CUDA(cudaMemsetAsync(acc + r * U, 0, sizeof(double) * U, st));
+    DLAUNCHED();
+    // part 2 (:321-393)
+    for (int k = 0; k < c->nPs; ++k) {
+        const int64_t L = c->L[k], ldL = c->ldL[k];
+        double *At = c->At[k], *Bmt = c->Bmt[k];
+        // transposes of scaled_pt, scaled_row_r, scaled_col_r, scaled_diag (U x L each)
+        for (int r = 1; r < R; ++r) scale(At, d + r * U, L, c->SAt[k][r]);  // SAt[0] = diag(d0) A' from part 1
+        rowscale2_kernel<<<nb1(U * L), 256, 0, st>>>(Bmt, d, nullptr, nullptr, U, L, ldU, 0.0, c->SPt[k]);
+        DLAUNCHED();
+        for (int r = 1; r < R; ++r) {
+            rowscale2_kernel<<<nb1(U * L), 256, 0, st>>>(c->Et[k][r - 1], d + r * U, nullptr, nullptr, U, L, ldU, 1.0, c->SPt[k]);
+            rowscale2_kernel<<<nb1(U * L), 256, 0, st>>>(Bmt, d + r * U, c->Et[k][r - 1], d, U, L, ldU, 0.0, c->SRt[k][r - 1]);
+            g_dense_launches += 2;
+        }
+        HYB_CUDA(cudaGetLastError());
+        // colT[0] = (scaled_pt B' + sum_r scaled_row_r E_r')' ; rowT_r = (scaled_row_r A')' ; colT[r] = (scaled_col_r B' +
+        // scaled_diag E_r')' ; diagT = (scaled_diag A')'   -- X Y' = (X')' (Y'), its transpose = (Y')' (X')
+        HYB_CHECK(hyb_gemm_tn(st, L, L, U, 1.0, Bmt, ldU, c->SPt[k], ldU, 0.0, c->colT[k][0], ldL, 0));
+        HYB_CHECK(hyb_gemm_tn(st, L, L, U, 1.0, At, ldU, c->SAt[k][0], ldU, 0.0, c->diagT[k], ldL, 0));
+        for (int r = 1; r < R; ++r) {
+            HYB_CHECK(hyb_gemm_tn(st, L, L, U, 1.0, c->Et[k][r - 1], ldU, c->SRt[k][r - 1], ldU, 1.0, c->colT[k][0], ldL, 0));
+            HYB_CHECK(hyb_gemm_tn(st, L, L, U, 1.0, At, ldU, c->SRt[k][r - 1], ldU, 0.0, c->rowT[k][r - 1], ldL, 0));
+            HYB_CHECK(hyb_gemm_tn(st, L, L, U, 1.0, Bmt, ldU, c->SAt[k][r], ldU, 0.0, c->colT[k][r], ldL, 0));
+            HYB_CHECK(hyb_gemm_tn(st, L, L, U, 1.0, c->Et[k][r - 1], ldU, c->SAt[k][0], ldU, 1.0, c->colT[k][r], ldL, 0));
+        }
+        // half[rho][sigma] = col[rho] * ctg[sigma] (+ row_sigma A at rho = 0, + diag A at rho = sigma), L x U each
+        for (int rho = 0; rho < R; ++rho)
+            for (int sg = 0; sg < R; ++sg) {
+                const double* ctg = sg == 0 ? c->Bm[k] : c->E[k][sg - 1];
+                double* hb = c->half[k][rho * R + sg];
+                HYB_CHECK(hyb_gemm_tn(st, L, U, L, 1.0, c->colT[k][rho], ldL, ctg, ldL, 0.0, hb, ldL, 0));
+                if (sg >= 1 && rho == 0)
+                    HYB_CHECK(hyb_gemm_tn(st, L, U, L, 1.0, c->rowT[k][sg - 1], ldL, c->A[k], ldL, 1.0, hb, ldL, 0));
+                if (sg >= 1 && rho == sg)
+                    HYB_CHECK(hyb_gemm_tn(st, L, U, L, 1.0, c->diagT[k], ldL, c->A[k], ldL, 1.0, hb, ldL, 0));
+            }
+        for (int rho = 0; rho < R; ++rho) {
+            const double* h0 = c->half[k][rho * R];
+            coldot_kernel<<<nb1(U, 8), 256, 0, st>>>(h0, h0, L, U, ldL, 1.0, 1.0, acc);
+            DLAUNCHED();
+            for (int sg = 1; sg < R; ++sg) {
+                const double* hs = c->half[k][rho * R + sg];
+                coldot_kernel<<<nb1(U, 8), 256, 0, st>>>(hs, h0, L, U, ldL, 2.0, 1.0, acc + sg * U);
+                coldot_kernel<<<nb1(U, 8), 256, 0, st>>>(hs, hs, L, U, ldL, 1.0, 1.0, acc);
+                g_dense_launches += 2;
+            }
+        }
+        HYB_CUDA(cudaGetLastError());
+    }
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, acc, 0.0, nullptr, out);
+    DLAUNCHED();
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}

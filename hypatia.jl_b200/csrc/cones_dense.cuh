@@ -48,3 +48,13 @@ int hybd_dnn_prod(cudaStream_t st, HybDenseDnn* c, int op, const double* arr, in
                   int64_t m);
 int hybd_dnn_dder3(cudaStream_t st, HybDenseDnn* c, const double* dir, double* out);
 int hybd_dnn_sqrt_ok(cudaStream_t st, HybDenseDnn* c, int* ok);
+
+struct HybDenseWsosEuc;  // WSOSInterpEpiNormEucl (wsosinterpepinormeucl.jl)
+int hybd_wsoseuc_create(HybDenseWsosEuc** out, int R, int64_t U, int nPs, const double* const* Ps_host, const int64_t* Ls);
+void hybd_wsoseuc_destroy(HybDenseWsosEuc* c);
+int hybd_wsoseuc_update(cudaStream_t st, HybDenseWsosEuc* c, const double* primal, const double* dual_in, double scal,
+                        double irtmu, double* point, double* dual_out, double* grad, int* flag, double* prox);
+int hybd_wsoseuc_prod(cudaStream_t st, HybDenseWsosEuc* c, int op, const double* arr, int64_t lda, double* prod, int64_t ldp,
+                      int64_t m);
+int hybd_wsoseuc_dder3(cudaStream_t st, HybDenseWsosEuc* c, const double* dir, double* out);
+int hybd_wsoseuc_sqrt_ok(cudaStream_t st, HybDenseWsosEuc* c, int* ok);

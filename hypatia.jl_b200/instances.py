@@ -298,6 +298,24 @@ def possemideftrisparse5():  # :735-784 (use_dual = true)
     return m, dict(status="Optimal", primal_obj=RT2 + RT3, s=s, z=z)
 
 
+def wsosinterpepinormeucl1():  # test/nativeinstances.jl:2715-2737: min t : t^2 >= x^4 on [-1, 1], t constant
+    U, pts, Ps = _wsos_box([-1], [1], 1)
+    assert U == 3
+    h = np.concatenate([np.zeros(U), pts[:, 0] ** 2])
+    G = np.vstack([-_I(U), np.zeros((U, U))])
+    m = Model(np.ones(U), [[1, -1, 0], [1, 0, -1]], [0, 0], G, h, [cs.wsos_epinormeucl(2, U, Ps)])
+    return m, dict(status="Optimal", primal_obj=float(U), x=np.ones(U))
+
+
+def wsosinterpepinormeucl2():  # :2739-2766: min t : t^2 >= x^4 + (x - 1)^2 on [-1, 1]
+    U, pts, Ps = _wsos_box([-1], [1], 1)
+    x = pts[:, 0]
+    h = np.concatenate([np.zeros(U), x**2, x - 1])
+    G = np.vstack([-_I(U), np.zeros((U, U)), np.zeros((U, U))])
+    m = Model(np.ones(U), [[1, -1, 0], [1, 0, -1]], [0, 0], G, h, [cs.wsos_epinormeucl(3, U, Ps)])
+    return m, dict(status="Optimal", primal_obj=math.sqrt(5.0) * U, x=np.full(U, math.sqrt(5.0)))
+
+
 KNOWN_ANSWER = {
     f.__name__: f
     for f in (
@@ -310,6 +328,7 @@ KNOWN_ANSWER = {
         epipersquare1, epipersquare2, epipersquare3, epipersquare4,
         wsosinterpnonnegative1, wsosinterpnonnegative2, wsosinterpnonnegative3,
         wsosinterppossemideftri1, wsosinterppossemideftri2, wsosinterppossemideftri3,
+        wsosinterpepinormeucl1, wsosinterpepinormeucl2,
     )
 }
 
@@ -368,6 +387,18 @@ def nearestdnn(side: int = 12, seed: int = 1) -> Model:
     A = np.vstack([tr, ones])
     b = [1.0, 1.0 + 0.25 * (side - 1)]
     return Model(c, A, b, -_I(dim), np.zeros(dim), [cs.DoublyNonnegativeTri(dim)])
+
+
+def polynormeucl(n: int = 1, halfdeg: int = 3, R: int = 3, seed: int = 1) -> Model:
+    """Seeded model over WSOSInterpEpiNormEucl in the shape of wsosinterpepinormeucl2: the smallest constant t with
+    t^2 >= sum_i f_i(x)^2 on the box [-1, 1]^n for R - 1 random polynomials given by their values at the points."""
+    rng = np.random.default_rng(seed)
+    U, pts, Ps = pu.interpolate(pu.BoxDomain(-np.ones(n), np.ones(n)), halfdeg, sample=False)
+    fs = [rng.standard_normal(n + 1) for _ in range(R - 1)]
+    vals = [f[0] + pts @ f[1:] for f in fs]  # affine polynomials: inside the degree the basis represents
+    h = np.concatenate([np.zeros(U)] + vals)
+    G = np.vstack([-np.ones((U, 1))] + [np.zeros((U, 1))] * (R - 1))
+    return Model([1.0], np.zeros((0, 1)), [], G, h, [cs.wsos_epinormeucl(R, U, Ps)])
 
 
 def sparsepsd_maxeig(side: int = 20, seed: int = 1) -> Model:

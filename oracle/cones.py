@@ -1057,6 +1057,147 @@ class WSOSInterpPosSemidefTri(_GenericHessCone):
         return self._partial_prod(direction, True)
 
 
+class WSOSInterpEpiNormEucl(_GenericHessCone):
+    """src/Cones/wsosinterpepinormeucl.jl: the arrow matrix [Lam(p_1) Lam(p_r)'; Lam(p_r) Lam(p_1) ...] is handled
+    through the Cholesky of Lam(p_1) and of its Schur complement `mat`, per P_k.  Products go through the stored
+    Hessian (generic oracles of Cones.jl)."""
+
+    def setup_extra_data(self):  # :90-123
+        self.R, self.U, self.Ps = self.spec.R, self.spec.U, self.spec.Ps
+
+    def _views(self, vec):
+        U = self.U
+        return [vec[r * U : (r + 1) * U] for r in range(self.R)]
+
+    def update_feas(self):  # :131-178
+        pv = self._views(self.point)
+        self.L11, self.Lm, self.LiL = [], [], []
+        self.is_feas_flag = True
+        for P in self.Ps:
+            Lam11 = P.T @ (pv[0][:, None] * P)
+            c, info = lapack.dpotrf(Lam11, lower=1, clean=1)
+            if info != 0:
+                self.is_feas_flag = False
+                break
+            mat = Lam11.copy()
+            LiL_k = []
+            for r in range(1, self.R):
+                M = sla.solve_triangular(c, P.T @ (pv[r][:, None] * P), lower=True)  # L11 \ Lam(p_r)
+                LiL_k.append(M)
+                mat -= M.T @ M
+            cm, info = lapack.dpotrf(mat, lower=1, clean=1)
+            if info != 0:
+                self.is_feas_flag = False
+                break
+            self.L11.append(c)
+            self.Lm.append(cm)
+            self.LiL.append(LiL_k)
+        self.feas_updated = True
+        return self.is_feas_flag
+
+    def is_dual_feas(self):  # :180-183
+        return bool(np.all(self.dual_point[: self.U] > EPS))
+
+    def update_grad(self):  # :185-223
+        U, R = self.U, self.R
+        g = np.zeros(self.dim)
+        self.L11iP, self.matLiP, self.edge = [], [], []
+        for k, P in enumerate(self.Ps):
+            A = sla.solve_triangular(self.L11[k], P.T, lower=True)  # Lam11 L^-1 P'
+            B = sla.solve_triangular(self.Lm[k], P.T, lower=True)  # mat L^-1 P'
+            E = [sla.solve_triangular(self.Lm[k], -(self.LiL[k][r].T @ A), lower=True) for r in range(R - 1)]
+            self.L11iP.append(A)
+            self.matLiP.append(B)
+            self.edge.append(E)
+            g[:U] -= np.sum(A * A, axis=0) + np.sum(B * B, axis=0)
+            for r in range(1, R):
+                g[r * U : (r + 1) * U] -= 2.0 * np.sum(E[r - 1] * B, axis=0)
+                g[:U] -= np.sum(E[r - 1] * E[r - 1], axis=0)
+        self.grad_vec = g
+        self.grad_updated = True
+        return g
+
+    def update_hess(self):  # :225-296
+        self.grad()
+        U, R = self.U, self.R
+        R2 = R - 2
+        H = np.zeros((self.dim, self.dim))
+        blk = lambda r: slice(r * U, (r + 1) * U)  # noqa: E731  (0-based block r)
+        for k in range(len(self.Ps)):
+            A, Bm, E = self.L11iP[k], self.matLiP[k], self.edge[k]
+            P11 = A.T @ A
+            Bk = [[None] * R for _ in range(R)]  # P Lam^-1 P blocks, (r, s)
+            Bk[0][0] = Bm.T @ Bm
+            for r in range(1, R):
+                Bk[r][0] = E[r - 1].T @ Bm
+                Bk[r][r] = E[r - 1].T @ E[r - 1] + P11
+                for r2 in range(1, r):
+                    Bk[r][r2] = E[r - 1].T @ E[r2 - 1]
+            for r in range(R):
+                for s_ in range(r + 1, R):
+                    Bk[r][s_] = Bk[s_][r].T
+            H[blk(0), blk(0)] -= np.triu(P11 * P11) * R2
+            H[blk(0), blk(0)] += Bk[0][0] ** 2
+            for r in range(1, R):
+                for s_ in range(0, r):
+                    UU = Bk[r][s_] ** 2
+                    H[blk(0), blk(0)] += UU + UU.T
+                    H[blk(0), blk(r)] += Bk[s_][0] * Bk[s_][r]
+                H[blk(0), blk(0)] += Bk[r][r] ** 2
+                H[blk(0), blk(r)] += Bk[r][0] * Bk[r][r]
+                for s_ in range(r + 1, R):
+                    H[blk(0), blk(r)] += Bk[s_][0] * Bk[s_][r]
+                H[blk(r), blk(r)] += Bk[r][0] * Bk[r][0].T
+                H[blk(r), blk(r)] += Bk[0][0] * Bk[r][r]
+                for r2 in range(r + 1, R):
+                    H[blk(r), blk(r2)] += Bk[r][0] * Bk[r2][0].T
+                    H[blk(r), blk(r2)] += Bk[0][0] * Bk[r2][r].T
+        H[:, U:] *= 2.0
+        self.hess_mat = np.triu(H) + np.triu(H, 1).T  # Symmetric(H, :U)
+        self.hess_updated = True
+
+    def dder3(self, direction):  # :298-396
+        U, R = self.U, self.R
+        d = self._views(np.asarray(direction, dtype=np.float64))
+        out = np.zeros(self.dim)
+        for k in range(len(self.Ps)):
+            A = self.L11iP[k]
+            LL = (A * d[0][None, :]) @ A.T
+            LU = (np.triu(LL) + np.triu(LL, 1).T) @ A  # Hermitian(LL): its upper triangle
+            out[:U] += np.sum(LU * LU, axis=0)
+        out[:U] *= 2 - R
+        for k in range(len(self.Ps)):
+            A, Bm, E = self.L11iP[k], self.matLiP[k], self.edge[k]
+            L = A.shape[0]
+            scaled_diag = A * d[0][None, :]
+            scaled_pt = Bm * d[0][None, :]
+            scaled_row, scaled_col = [], []
+            for r in range(1, R):
+                scaled_pt = scaled_pt + E[r - 1] * d[r][None, :]
+                scaled_row.append(Bm * d[r][None, :] + E[r - 1] * d[0][None, :])
+                scaled_col.append(A * d[r][None, :])
+            col = np.zeros((R * L, L))
+            row = []
+            col[:L] = scaled_pt @ Bm.T
+            diag = np.zeros((L, L))
+            for r in range(1, R):
+                col[:L] += scaled_row[r - 1] @ E[r - 1].T
+                row.append(scaled_row[r - 1] @ A.T)
+                col[r * L : (r + 1) * L] = scaled_col[r - 1] @ Bm.T + scaled_diag @ E[r - 1].T
+                diag = scaled_diag @ A.T
+            ctgs = np.hstack([Bm] + [E[r - 1] for r in range(1, R)])  # L x (U R)
+            half = col @ ctgs  # (R L) x (U R)
+            for r in range(1, R):
+                half[:L, r * U : (r + 1) * U] += row[r - 1] @ A
+                half[r * L : (r + 1) * L, r * U : (r + 1) * U] += diag @ A
+            out[:U] += np.sum(half[:, :U] ** 2, axis=0)
+            for r in range(1, R):
+                hb = half[:, r * U : (r + 1) * U]
+                out[r * U : (r + 1) * U] += 2.0 * np.sum(hb * half[:, :U], axis=0)
+                out[:U] += np.sum(hb * hb, axis=0)
+        return out
+
+
 _CLASSES = {
     cs.NONNEGATIVE: Nonnegative,
     cs.EPINORMEUCL: EpiNormEucl,
@@ -1067,6 +1208,7 @@ _CLASSES = {
     cs.EPINORMINF: EpiNormInf,
     cs.DOUBLYNONNEGATIVETRI: DoublyNonnegativeTri,
     cs.POSSEMIDEFTRISPARSE: PosSemidefTriSparse,
+    cs.WSOSINTERPEPINORMEUCL: WSOSInterpEpiNormEucl,
 }
 
 

@@ -34,6 +34,7 @@ SEEDED = {
     "polymin_n2_hd4": ("polymin", dict(n=2, halfdeg=4, seed=1)),
     "nearestdnn_side12": ("nearestdnn", dict(side=12, seed=1)),
     "sparsepsd_maxeig_side20": ("sparsepsd_maxeig", dict(side=20, seed=1)),
+    "polynormeucl_n2_hd2_R3": ("polynormeucl", dict(n=2, halfdeg=2, R=3, seed=1)),
 }
 
 

@@ -117,7 +117,8 @@ def test_known_answer_instances_on_gpu(name):
 # and objective are identical and the trajectories agree to 1e-5 until iteration 12).
 # nonnegative4 with the device-resident stepper: see DEVICE_STEPPER_ITER_SLACK in tests/test_golden.py (the
 # host-vector protocol is held to +-1 there).
-ITER_SLACK = {"wsosinterppossemideftri3": 2, "nonnegative4": 3}
+# wsosinterpepinormeucl1: see ITER_SLACK in tests/test_golden.py (the last two iterations sit on the rounding floor).
+ITER_SLACK = {"wsosinterppossemideftri3": 2, "nonnegative4": 3, "wsosinterpepinormeucl1": 2}
 
 
 @pytest.mark.parametrize("N,seed", [(64, 0), (96, 1), (256, 2)])

@@ -259,3 +259,60 @@ def test_possemideftrisparse_barrier_derivatives():
     h = 1e-6
     fd = np.array([(-np.linalg.slogdet(mat(s + h * e))[1] + np.linalg.slogdet(mat(s - h * e))[1]) / (2 * h) for e in np.eye(spec.dim)])
     assert np.allclose(cone.grad(), fd, rtol=1e-6, atol=1e-7)
+
+
+def _interp(n, halfdeg):
+    from hypatia_b200 import polyutils as pu
+
+    U, _, Ps = pu.interpolate(pu.BoxDomain(-np.ones(n), np.ones(n)), halfdeg, sample=False)
+    return U, Ps
+
+
+@pytest.mark.parametrize("n,halfdeg,ds", [(1, 1, 1), (1, 2, 3), (2, 2, 2), (3, 1, 1)])
+def test_wsosinterpepinormeucl(n, halfdeg, ds):  # test/cone.jl:848-853 (init_tol = Inf)
+    U, Ps = _interp(n, halfdeg)
+    run_oracle_identities(cs.wsos_epinormeucl(1 + ds, U, Ps), init_tol=np.inf, tol=1e5 * EPS)
+
+
+def test_wsosinterpepinormeucl_barrier_derivatives():
+    """test/cone.jl:855-873: the barrier as a function of the point; gradient and Hessian-vector product of the
+    oracle against finite differences of it."""
+    U, Ps = _interp(1, 1)
+    ds = 2
+    spec = cs.wsos_epinormeucl(1 + ds, U, Ps)
+
+    def barrier(s):
+        tot = 0.0
+        for P in Ps:
+            Lam = P.T @ (s[:U, None] * P)
+            L1 = np.linalg.cholesky(Lam)
+            PL1 = np.linalg.solve(L1, P.T)
+            for i in range(ds):
+                LLi = PL1 @ (s[(1 + i) * U : (2 + i) * U, None] * P)
+                Lam = Lam - LLi.T @ LLi
+            tot += -2.0 * np.sum(np.log(np.diag(L1))) - np.linalg.slogdet(Lam)[1]
+        return tot
+
+    rng = np.random.default_rng(3)
+    s = spec.initial_point() + 0.1 * rng.uniform(-1, 1, spec.dim)
+    cone = make_cone(spec)
+    cone.setup_data()
+    cone.load_point(s)
+    assert cone.is_feas()
+    h = 1e-5
+    eye = np.eye(spec.dim)
+    fd = np.array([(barrier(s + h * e) - barrier(s - h * e)) / (2 * h) for e in eye])
+    assert np.allclose(cone.grad(), fd, rtol=1e-6, atol=1e-6)
+    d = rng.standard_normal(spec.dim)
+
+    def grad_at(v):
+        c = make_cone(spec)
+        c.setup_data()
+        c.load_point(v)
+        assert c.is_feas()
+        return c.grad().copy()
+
+    fd_h = (grad_at(s + h * d) - grad_at(s - h * d)) / (2 * h)
+    assert np.allclose(cone.hess_prod(d), fd_h, rtol=1e-5, atol=1e-5)
+    fd_3 = (grad_at(s + h * d) - 2 * grad_at(s) + grad_at(s - h * d)) / (h * h)  # = grad'''[d, d]
+    assert np.allclose(-0.5 * fd_3, cone.dder3(d), rtol=1e-3, atol=1e-3)
