@@ -23,7 +23,8 @@
 struct HybSymIndef {
     HybChol fact;          // (n + q) x (n + q): the system matrix, then its factorization
     double* eye = nullptr; // q x q identity (ld = ldq)
-    int64_t n = 0, q = 0, ldq = 0;
+    double* rhs = nullptr; // (n + q) x HYB_MAX_RHS staging of the right-hand sides (ld = ldr)
+    int64_t n = 0, q = 0, ldq = 0, ldr = 0;
     bool ok = false;
 };
 
@@ -71,6 +72,7 @@ void hyb_symindef_free(hyb_ctx* c) {
     if (!c->symindef) return;
     hyb_chol_free(c->symindef->fact);
     cudaFree(c->symindef->eye);
+    cudaFree(c->symindef->rhs);
     delete c->symindef;
     c->symindef = nullptr;
 }
@@ -85,6 +87,11 @@ int hyb_symindef_load(hyb_ctx* c) {
     }
     HYB_CUDA(cudaSetDevice(c->device));
     hyb_symindef_free(c);
+    if (c->q > 65535 || c->N + c->q > 65535) {  // the dense (n + q)^2 system: a solver for moderate sizes (grid.y limits too)
+        hyb_set_error("hyb_symindef_load: n + q = %lld is beyond what the dense symmetric-indefinite solver is meant for",
+                      (long long)(c->N + c->q));
+        return -3;
+    }
     HybSymIndef* si = new HybSymIndef();
     c->symindef = si;
     si->n = c->N;
@@ -92,6 +99,8 @@ int hyb_symindef_load(hyb_ctx* c) {
     si->ldq = hyb_round_up(c->q > 0 ? c->q : 1, 16);
     HYB_CHECK(hyb_chol_alloc(si->fact, si->n + si->q));
     HYB_CUDA(cudaMalloc(&si->eye, sizeof(double) * si->ldq * (si->q > 0 ? si->q : 1)));
+    si->ldr = hyb_round_up(si->n + si->q > 0 ? si->n + si->q : 1, 16);
+    HYB_CUDA(cudaMalloc(&si->rhs, sizeof(double) * si->ldr * HYB_MAX_RHS));
     if (si->q > 0) {
         dim3 grid((unsigned)((si->q + 255) / 256), (unsigned)si->q);
         eye_kernel<<<grid, 256, 0, c->st>>>(si->q, si->ldq, si->eye);
@@ -153,9 +162,8 @@ int hyb_symindef_solve(hyb_ctx* c, const double* rhs, double* sol, int64_t nrhs)
     HYB_CUDA(cudaSetDevice(c->device));
     const int64_t dim = si.n + si.q;
     if (dim == 0 || nrhs == 0) return 0;
-    const int64_t ldb = hyb_round_up(dim, 16);
-    double* dB = nullptr;
-    HYB_CUDA(cudaMalloc(&dB, sizeof(double) * ldb * nrhs));
+    const int64_t ldb = si.ldr;
+    double* dB = si.rhs;  // persistent staging: no allocation on the solve path
     cudaError_t e = cudaMemcpy2DAsync(dB, sizeof(double) * ldb, rhs, sizeof(double) * dim, sizeof(double) * dim, nrhs,
                                       cudaMemcpyHostToDevice, c->st);
     c->h2d_bytes += (int64_t)sizeof(double) * dim * nrhs;
@@ -172,7 +180,6 @@ int hyb_symindef_solve(hyb_ctx* c, const double* rhs, double* sol, int64_t nrhs)
         if (e == cudaSuccess) e = cudaStreamSynchronize(c->st);
         if (e == cudaSuccess) ksync(c);
     }
-    cudaFree(dB);
     if (e != cudaSuccess) {
         hyb_set_error("hyb_symindef_solve: %s", cudaGetErrorString(e));
         return -1;
