@@ -28,6 +28,7 @@ EPINORMINF = 6
 DOUBLYNONNEGATIVETRI = 7
 POSSEMIDEFTRISPARSE = 8
 WSOSINTERPEPINORMEUCL = 9
+WSOSINTERPEPINORMONE = 10
 
 RT2 = math.sqrt(2.0)
 
@@ -397,6 +398,38 @@ class WSOSInterpEpiNormEucl(ConeSpec):
 
 def wsos_epinormeucl(R: int, U: int, Ps, use_dual: bool = False) -> WSOSInterpEpiNormEucl:
     return WSOSInterpEpiNormEucl(dim=U * R, R=R, U=U, Ps=Ps, use_dual=use_dual)
+
+
+@dataclass
+class WSOSInterpEpiNormOne(ConeSpec):
+    """src/Cones/wsosinterpepinormone.jl:17-99: polynomial epigraph of the 1-norm of R - 1 polynomials in the
+    interpolant basis; dim = U * R; dual barrier unless use_dual."""
+
+    R: int = 2
+    U: int = 0
+    Ps: Sequence[np.ndarray] = ()
+    use_dual: bool = False
+
+    def __post_init__(self):
+        self.type_code = WSOSINTERPEPINORMONE
+        self.Ps = [np.asfortranarray(P, dtype=np.float64) for P in self.Ps]
+        for P in self.Ps:
+            assert P.shape[0] == self.U
+        assert self.R >= 2 and self.dim == self.U * self.R
+        self.use_dual_barrier = not self.use_dual
+
+    @property
+    def nu(self):
+        return float(self.R * sum(P.shape[1] for P in self.Ps))
+
+    def initial_point(self):  # wsosinterpepinormone.jl:155-159
+        arr = np.zeros(self.dim)
+        arr[: self.U] = 1.0
+        return arr
+
+
+def wsos_epinormone(R: int, U: int, Ps, use_dual: bool = False) -> WSOSInterpEpiNormOne:
+    return WSOSInterpEpiNormOne(dim=U * R, R=R, U=U, Ps=Ps, use_dual=use_dual)
 
 
 def wsos_psd(R: int, U: int, Ps, use_dual: bool = False) -> WSOSInterpPosSemidefTri:

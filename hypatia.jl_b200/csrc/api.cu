@@ -241,7 +241,7 @@ int hyb_model_load_impl(hyb_ctx* c, int64_t q, int64_t N, const double* GQ2, int
         }
         expect += d.dim;
         const bool mergeable = d.type != HYB_CONE_WSOSINTERPNONNEGATIVE && d.type != HYB_CONE_WSOSINTERPPOSSEMIDEFTRI &&
-                               d.type != HYB_CONE_WSOSINTERPEPINORMEUCL &&
+                               d.type != HYB_CONE_WSOSINTERPEPINORMEUCL && d.type != HYB_CONE_WSOSINTERPEPINORMONE &&
                                d.type != HYB_CONE_DOUBLYNONNEGATIVETRI && d.type != HYB_CONE_POSSEMIDEFTRISPARSE &&
                                !(d.type == HYB_CONE_POSSEMIDEFTRI && d.side_or_R > 32);  // large PSD: one dense engine each
         if (!cs.blocks.empty() && mergeable) {
@@ -455,6 +455,10 @@ int hyb_schur_assemble_into(hyb_ctx* c, double* Sdst, double* t_assemble_ms) {
                     HYB_CHECK(hybd_wsos_sqrt_ok(c->st, (HybDenseWsos*)cs.blocks[bi].dense, &ok));
                 else
                     HYB_CHECK(hybd_wsospsd_sqrt_ok(c->st, (HybDenseWsosPsd*)cs.blocks[bi].dense, &ok));
+                sqrt_mask[bi] = (char)ok;
+            } else if (ty == HYB_WSOSINTERPEPINORMONE) {
+                int ok = 0;
+                HYB_CHECK(hybd_wsosone_sqrt_ok(c->st, (HybDenseWsosOne*)cs.blocks[bi].dense, &ok));
                 sqrt_mask[bi] = (char)ok;
             } else if (ty == HYB_WSOSINTERPEPINORMEUCL) {
                 int ok = 0;

@@ -1004,6 +1004,10 @@ int hybi_cones_alloc(HybCones& cs) {
             HybDenseWsosPsd* d = nullptr;
             HYB_CHECK(hybd_wsospsd_create(&d, b.side, b.U, b.nPs, b.Ps, b.Ls));
             b.dense = d;
+        } else if (b.type == HYB_WSOSINTERPEPINORMONE) {
+            HybDenseWsosOne* d = nullptr;
+            HYB_CHECK(hybd_wsosone_create(&d, b.side, b.U, b.nPs, b.Ps, b.Ls));
+            b.dense = d;
         } else if (b.type == HYB_WSOSINTERPEPINORMEUCL) {
             HybDenseWsosEuc* d = nullptr;
             HYB_CHECK(hybd_wsoseuc_create(&d, b.side, b.U, b.nPs, b.Ps, b.Ls));
@@ -1050,6 +1054,7 @@ void hybi_cones_free(HybCones& cs) {
             if (b.type == HYB_WSOSINTERPNONNEGATIVE) hybd_wsos_destroy((HybDenseWsos*)b.dense);
             else if (b.type == HYB_WSOSINTERPPOSSEMIDEFTRI) hybd_wsospsd_destroy((HybDenseWsosPsd*)b.dense);
             else if (b.type == HYB_WSOSINTERPEPINORMEUCL) hybd_wsoseuc_destroy((HybDenseWsosEuc*)b.dense);
+            else if (b.type == HYB_WSOSINTERPEPINORMONE) hybd_wsosone_destroy((HybDenseWsosOne*)b.dense);
             else if (b.type == HYB_DOUBLYNONNEGATIVETRI || b.type == HYB_POSSEMIDEFTRISPARSE) hybd_dnn_destroy((HybDenseDnn*)b.dense);
             else hybd_psd_destroy((HybDensePsd*)b.dense);
             b.dense = nullptr;
@@ -1140,6 +1145,11 @@ int hybi_cones_update(cudaStream_t st, HybCones& cs, const double* primal, const
             case HYB_WSOSINTERPPOSSEMIDEFTRI:
                 HYB_CHECK(hybd_wsospsd_update(st, (HybDenseWsosPsd*)b.dense, primal + b.offset, dual_in + b.offset, scal,
                                               irtmu, cs.point + b.offset, cs.dual + b.offset, cs.grad + b.offset,
+                                              cs.item_flag + b.offset, cs.item_prox + b.offset));
+                break;
+            case HYB_WSOSINTERPEPINORMONE:
+                HYB_CHECK(hybd_wsosone_update(st, (HybDenseWsosOne*)b.dense, primal + b.offset, dual_in + b.offset, scal, irtmu,
+                                              cs.point + b.offset, cs.dual + b.offset, cs.grad + b.offset,
                                               cs.item_flag + b.offset, cs.item_prox + b.offset));
                 break;
             case HYB_WSOSINTERPEPINORMEUCL:
@@ -1290,6 +1300,9 @@ int hybi_cones_prod(cudaStream_t st, HybCones& cs, int which, const double* arr,
             case HYB_WSOSINTERPPOSSEMIDEFTRI:
                 HYB_CHECK(hybd_wsospsd_prod(st, (HybDenseWsosPsd*)b.dense, op, arr + b.offset, lda, prod + b.offset, ldp, m));
                 break;
+            case HYB_WSOSINTERPEPINORMONE:
+                HYB_CHECK(hybd_wsosone_prod(st, (HybDenseWsosOne*)b.dense, op, arr + b.offset, lda, prod + b.offset, ldp, m));
+                break;
             case HYB_WSOSINTERPEPINORMEUCL:
                 HYB_CHECK(hybd_wsoseuc_prod(st, (HybDenseWsosEuc*)b.dense, op, arr + b.offset, lda, prod + b.offset, ldp, m));
                 break;
@@ -1352,6 +1365,9 @@ int hybi_cones_dder3(cudaStream_t st, HybCones& cs, const double* dir, double* o
                 break;
             case HYB_WSOSINTERPPOSSEMIDEFTRI:
                 HYB_CHECK(hybd_wsospsd_dder3(st, (HybDenseWsosPsd*)b.dense, dir + b.offset, out + b.offset));
+                break;
+            case HYB_WSOSINTERPEPINORMONE:
+                HYB_CHECK(hybd_wsosone_dder3(st, (HybDenseWsosOne*)b.dense, dir + b.offset, out + b.offset));
                 break;
             case HYB_WSOSINTERPEPINORMEUCL:
                 HYB_CHECK(hybd_wsoseuc_dder3(st, (HybDenseWsosEuc*)b.dense, dir + b.offset, out + b.offset));

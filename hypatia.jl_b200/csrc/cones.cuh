@@ -13,6 +13,7 @@ enum HybConeType {
     HYB_DOUBLYNONNEGATIVETRI = 7,
     HYB_POSSEMIDEFTRISPARSE = 8,
     HYB_WSOSINTERPEPINORMEUCL = 9,
+    HYB_WSOSINTERPEPINORMONE = 10,
 };
 
 enum HybProdOp { HYB_OP_HESS = 0, HYB_OP_INV_HESS = 1, HYB_OP_SQRT_HESS = 2, HYB_OP_INV_SQRT_HESS = 3 };

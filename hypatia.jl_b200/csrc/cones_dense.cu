@@ -1957,3 +1957,388 @@ int hybd_wsoseuc_dder3(cudaStream_t st, HybDenseWsosEuc* c, const double* dir, d
     HYB_CUDA(cudaGetLastError());
     return 0;
 }
+
+// =======================================================================================
+// WSOSInterpEpiNormOne: src/Cones/wsosinterpepinormone.jl   (point = R blocks of length U)
+//   update_feas :161-218   per P_k: Lam11 = P' diag(p_1) P = R11' R11; per r: M_r = R11^-T (P' diag(p_r) P),
+//                          mat_r = Lam11 - M_r' M_r = Rm_r' Rm_r
+//   update_grad :226-265   A = R11^-T P', S12_r = Rm_r^-T (-M_r' A), S11_r = Rm_r^-T P'
+//   update_hess(_prod) :267-330  diagonal and edge blocks of the arrow-shaped Hessian from U x U contractions
+//   dder3 :429-521
+//   hess_prod! / inv_hess_prod! (:332-427) exploit the arrow shape in the reference; here they are the generic
+//   products with the stored Hessian and its Cholesky (the same linear maps)
+// =======================================================================================
+namespace {
+
+// upper triangles (i <= j): d0 += uu, dr += uu, er += 4 P1 P2 with uu = 2 (P1^2 + P2^2)   (:316-323)
+__global__ void wsosone_accum_kernel(int64_t U, int64_t ld, const double* __restrict__ P1, const double* __restrict__ P2,
+                                     double* __restrict__ d0, double* __restrict__ dr, double* __restrict__ er, int first0,
+                                     int firstr) {
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= U * U) return;
+    const int64_t i = e % U, j = e / U, o = i + j * ld;
+    if (i > j) return;
+    const double a = P1[o], b = P2[o], uu = 2.0 * (a * a + b * b);
+    d0[o] = (first0 ? 0.0 : d0[o]) + uu;
+    dr[o] = (firstr ? 0.0 : dr[o]) + uu;
+    er[o] = (firstr ? 0.0 : er[o]) + 4.0 * a * b;
+}
+__global__ void wsosone_sub11_kernel(int64_t U, int64_t ld, const double* __restrict__ P11, double fac, double* __restrict__ d0) {
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= U * U) return;
+    const int64_t i = e % U, j = e / U, o = i + j * ld;
+    if (i <= j) d0[o] -= fac * P11[o] * P11[o];
+}
+// upper triangle of H from the R diagonal blocks and the R - 1 edge blocks (update_hess :267-284)
+__global__ void wsosone_hess_kernel(int64_t U, int R, const double* __restrict__ diag, const double* __restrict__ edge,
+                                    int64_t bstride, int64_t ld, double* __restrict__ H, int64_t ldH) {
+    const int64_t a = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t b = blockIdx.y;
+    if (a >= U * R || a > b) return;
+    const int ra = (int)(a / U), rb = (int)(b / U);
+    const int64_t i = a - ra * U, j = b - rb * U;
+    double v = 0.0;
+    if (ra == rb) v = diag[ra * bstride + i + j * ld];
+    else if (ra == 0) v = (i <= j) ? edge[(rb - 1) * bstride + i + j * ld] : edge[(rb - 1) * bstride + j + i * ld];
+    H[a + b * ldH] = v;
+}
+
+}  // namespace
+
+struct HybDenseWsosOne {
+    int R = 0, nPs = 0;
+    int64_t U = 0, ldU = 0, dim = 0, ldD = 0;
+    double nu = 0.0;
+    std::vector<int64_t> L, ldL;
+    std::vector<double*> P, PD, At, D22t, A, LUlast, Lam, Lam0, XT, LLt;          // per k
+    std::vector<std::vector<double*>> M, Mat, S11, S12, S11t, S12t, D11t, D12t, D21t, half;  // [k][r] (half: 4 per r)
+    std::vector<HybChol> chLam;
+    std::vector<std::vector<HybChol>> chMat;
+    double *P11 = nullptr, *P1 = nullptr, *P2 = nullptr, *diag = nullptr, *edge = nullptr;
+    int64_t bstride = 0;
+    double *H = nullptr, *Hf = nullptr, *Lh = nullptr;
+    HybChol chH;
+    double *v1 = nullptr, *v2 = nullptr, *v3 = nullptr, *scal = nullptr;
+    int *dual_ok = nullptr, *slow = nullptr, *sqrt_ok = nullptr;
+    const int** infos_dev = nullptr;
+    int ninfos = 0;
+    double *big1 = nullptr, *big2 = nullptr;
+    int64_t big_cols = 0;
+    std::vector<double*> owned;
+};
+
+static int one_alloc(HybDenseWsosOne* c, double** p, size_t elems) {
+    HYB_CUDA(cudaMalloc(p, sizeof(double) * (elems > 0 ? elems : 1)));
+    HYB_CUDA(cudaMemset(*p, 0, sizeof(double) * (elems > 0 ? elems : 1)));
+    c->owned.push_back(*p);
+    return 0;
+}
+
+int hybd_wsosone_create(HybDenseWsosOne** out, int R, int64_t U, int nPs, const double* const* Ps_host, const int64_t* Ls) {
+    HybDenseWsosOne* c = new HybDenseWsosOne();
+    c->R = R;
+    c->U = U;
+    c->nPs = nPs;
+    c->ldU = hyb_round_up(U, 16);
+    c->dim = U * R;
+    c->ldD = hyb_round_up(c->dim, 16);
+    const int R1 = R - 1;
+    for (auto* v : {&c->P, &c->PD, &c->At, &c->D22t, &c->A, &c->LUlast, &c->Lam, &c->Lam0, &c->XT, &c->LLt}) v->assign(nPs, nullptr);
+    for (auto* v : {&c->M, &c->Mat, &c->S11, &c->S12, &c->S11t, &c->S12t, &c->D11t, &c->D12t, &c->D21t, &c->half}) v->assign(nPs, {});
+    c->chLam.resize(nPs);
+    c->chMat.resize(nPs);
+    double sumL = 0;
+    std::vector<const int*> infos;
+    for (int k = 0; k < nPs; ++k) {
+        const int64_t L = Ls[k], ldL = hyb_round_up(L, 16), ldU = c->ldU;
+        c->L.push_back(L);
+        c->ldL.push_back(ldL);
+        sumL += (double)L;
+        for (double** p : {&c->P[k], &c->PD[k], &c->At[k], &c->D22t[k]}) HYB_CHECK(one_alloc(c, p, ldU * L));
+        for (double** p : {&c->A[k], &c->LUlast[k]}) HYB_CHECK(one_alloc(c, p, ldL * U));
+        for (double** p : {&c->Lam[k], &c->Lam0[k], &c->XT[k], &c->LLt[k]}) HYB_CHECK(one_alloc(c, p, ldL * L));
+        auto many = [&](std::vector<double*>& v, int n, size_t elems) -> int {
+            v.assign(n, nullptr);
+            for (int i = 0; i < n; ++i) HYB_CHECK(one_alloc(c, &v[i], elems));
+            return 0;
+        };
+        HYB_CHECK(many(c->M[k], R1, ldL * L));
+        HYB_CHECK(many(c->Mat[k], R1, ldL * L));
+        for (auto* v : {&c->S11[k], &c->S12[k]}) HYB_CHECK(many(*v, R1, ldL * U));
+        for (auto* v : {&c->S11t[k], &c->S12t[k], &c->D11t[k], &c->D12t[k], &c->D21t[k]}) HYB_CHECK(many(*v, R1, ldU * L));
+        HYB_CHECK(many(c->half[k], 4 * R1, ldL * U));
+        HYB_CUDA(cudaMemcpy2D(c->P[k], sizeof(double) * ldU, Ps_host[k], sizeof(double) * U, sizeof(double) * U, L,
+                              cudaMemcpyHostToDevice));
+        HYB_CHECK(hyb_chol_attach(c->chLam[k], c->Lam[k], ldL, L));
+        infos.push_back(c->chLam[k].info);
+        c->chMat[k].resize(R1);
+        for (int r = 0; r < R1; ++r) {
+            HYB_CHECK(hyb_chol_attach(c->chMat[k][r], c->Mat[k][r], ldL, L));
+            infos.push_back(c->chMat[k][r].info);
+        }
+    }
+    c->nu = (double)R * sumL;
+    c->bstride = c->ldU * U;
+    for (double** p : {&c->P11, &c->P1, &c->P2}) HYB_CHECK(one_alloc(c, p, c->bstride));
+    HYB_CHECK(one_alloc(c, &c->diag, c->bstride * R));
+    HYB_CHECK(one_alloc(c, &c->edge, c->bstride * (R1 > 0 ? R1 : 1)));
+    for (double** p : {&c->H, &c->Hf, &c->Lh}) HYB_CHECK(one_alloc(c, p, c->ldD * c->dim));
+    for (double** p : {&c->v1, &c->v2, &c->v3}) HYB_CHECK(one_alloc(c, p, c->ldD));
+    HYB_CHECK(one_alloc(c, &c->scal, 8));
+    HYB_CUDA(cudaMalloc(&c->dual_ok, sizeof(int)));
+    HYB_CUDA(cudaMalloc(&c->slow, sizeof(int)));
+    HYB_CUDA(cudaMalloc(&c->sqrt_ok, sizeof(int)));
+    HYB_CUDA(cudaMemset(c->sqrt_ok, 0, sizeof(int)));
+    HYB_CHECK(hyb_chol_attach(c->chH, c->Hf, c->ldD, c->dim));
+    c->ninfos = (int)infos.size();
+    HYB_CUDA(cudaMalloc(&c->infos_dev, sizeof(int*) * infos.size()));
+    HYB_CUDA(cudaMemcpy(c->infos_dev, infos.data(), sizeof(int*) * infos.size(), cudaMemcpyHostToDevice));
+    *out = c;
+    return 0;
+}
+
+void hybd_wsosone_destroy(HybDenseWsosOne* c) {
+    if (!c) return;
+    for (auto& ch : c->chLam) hyb_chol_free(ch);
+    for (auto& v : c->chMat)
+        for (auto& ch : v) hyb_chol_free(ch);
+    hyb_chol_free(c->chH);
+    for (double* p : c->owned) cudaFree(p);
+    cudaFree(c->dual_ok);
+    cudaFree(c->slow);
+    cudaFree(c->sqrt_ok);
+    cudaFree((void*)c->infos_dev);
+    cudaFree(c->big1);
+    cudaFree(c->big2);
+    delete c;
+}
+
+int hybd_wsosone_update(cudaStream_t st, HybDenseWsosOne* c, const double* primal, const double* dual_in, double scal,
+                        double irtmu, double* point, double* dual_out, double* grad, int* flag, double* prox) {
+    const int64_t U = c->U, ldU = c->ldU, dim = c->dim, ldD = c->ldD;
+    const int R = c->R, R1 = c->R - 1;
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, scal, primal, 0.0, nullptr, point);
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, dual_in, 0.0, nullptr, dual_out);
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, point, 0.0, nullptr, c->v3);
+    all_gt_eps_kernel<<<1, 1024, 0, st>>>(U, dual_out, c->dual_ok);
+    g_dense_launches += 4;
+    HYB_CUDA(cudaGetLastError());
+    for (int k = 0; k < c->nPs; ++k) {  // update_feas
+        const int64_t L = c->L[k], ldL = c->ldL[k];
+        rowscale_kernel<<<nb1(U * L), 256, 0, st>>>(c->P[k], c->v3, U, L, ldU, c->PD[k]);
+        DLAUNCHED();
+        HYB_CHECK(hyb_gemm_tn(st, L, L, U, 1.0, c->P[k], ldU, c->PD[k], ldU, 0.0, c->Lam[k], ldL, HYB_GEMM_UPPER));
+        copy_mat_kernel<<<nb1(L * L), 256, 0, st>>>(c->Lam[k], ldL, c->Lam0[k], ldL, L, L);
+        DLAUNCHED();
+        HYB_CHECK(hyb_potrf(st, c->chLam[k], nullptr));
+        for (int r = 0; r < R1; ++r) {
+            rowscale_kernel<<<nb1(U * L), 256, 0, st>>>(c->P[k], c->v3 + (r + 1) * U, U, L, ldU, c->PD[k]);
+            DLAUNCHED();
+            HYB_CHECK(hyb_gemm_tn(st, L, L, U, 1.0, c->P[k], ldU, c->PD[k], ldU, 0.0, c->M[k][r], ldL, 0));
+            HYB_CHECK(hyb_trsm_fwd(st, c->Lam[k], ldL, L, c->M[k][r], ldL, L));
+            copy_mat_kernel<<<nb1(L * L), 256, 0, st>>>(c->Lam0[k], ldL, c->Mat[k][r], ldL, L, L);
+            DLAUNCHED();
+            HYB_CHECK(hyb_gemm_tn(st, L, L, L, -1.0, c->M[k][r], ldL, c->M[k][r], ldL, 1.0, c->Mat[k][r], ldL, HYB_GEMM_UPPER));
+            HYB_CHECK(hyb_potrf(st, c->chMat[k][r], nullptr));
+        }
+    }
+    {
+        std::vector<int> infs(c->ninfos, 0);
+        int t = 0;
+        for (int k = 0; k < c->nPs; ++k) {
+            HYB_CUDA(cudaMemcpyAsync(&infs[t++], c->chLam[k].info, sizeof(int), cudaMemcpyDeviceToHost, st));
+            for (int r = 0; r < R1; ++r)
+                HYB_CUDA(cudaMemcpyAsync(&infs[t++], c->chMat[k][r].info, sizeof(int), cudaMemcpyDeviceToHost, st));
+        }
+        HYB_CUDA(cudaStreamSynchronize(st));
+        bool infeasible = false;
+        for (int v : infs) infeasible = infeasible || v != 0;
+        if (infeasible) {
+            wsos_finalize_kernel<<<1, 1, 0, st>>>(c->infos_dev, c->ninfos, c->chH.info, c->dual_ok, c->scal, c->nu, dim, flag, prox,
+                                                  c->slow, c->sqrt_ok);
+            DLAUNCHED();
+            HYB_CUDA(cudaGetLastError());
+            return 0;
+        }
+    }
+    for (int k = 0; k < c->nPs; ++k) {  // update_grad + the Hessian blocks
+        const int64_t L = c->L[k], ldL = c->ldL[k];
+        HYB_CHECK(hyb_transpose(st, c->P[k], ldU, U, L, c->A[k], ldL, 0));
+        for (int r = 0; r < R1; ++r) {
+            copy_mat_kernel<<<nb1(L * U), 256, 0, st>>>(c->A[k], ldL, c->S11[k][r], ldL, L, U);  // P'
+            DLAUNCHED();
+        }
+        HYB_CHECK(hyb_trsm_fwd(st, c->Lam[k], ldL, L, c->A[k], ldL, U));
+        HYB_CHECK(hyb_transpose(st, c->A[k], ldL, L, U, c->At[k], ldU, 0));
+        coldot_kernel<<<nb1(U, 8), 256, 0, st>>>(c->A[k], c->A[k], L, U, ldL, -(double)R, k == 0 ? 0.0 : 1.0, grad);
+        DLAUNCHED();
+        HYB_CHECK(hyb_gemm_tn(st, U, U, L, 1.0, c->A[k], ldL, c->A[k], ldL, 0.0, c->P11, ldU, 0));
+        for (int r = 0; r < R1; ++r) {
+            double *S12 = c->S12[k][r], *S11 = c->S11[k][r];
+            HYB_CHECK(hyb_gemm_tn(st, L, U, L, -1.0, c->M[k][r], ldL, c->A[k], ldL, 0.0, S12, ldL, 0));
+            HYB_CHECK(hyb_trsm_fwd(st, c->Mat[k][r], ldL, L, S12, ldL, U));
+            HYB_CHECK(hyb_trsm_fwd(st, c->Mat[k][r], ldL, L, S11, ldL, U));
+            HYB_CHECK(hyb_transpose(st, S12, ldL, L, U, c->S12t[k][r], ldU, 0));
+            HYB_CHECK(hyb_transpose(st, S11, ldL, L, U, c->S11t[k][r], ldU, 0));
+            coldot_kernel<<<nb1(U, 8), 256, 0, st>>>(S12, S12, L, U, ldL, -2.0, 1.0, grad);
+            coldot_kernel<<<nb1(U, 8), 256, 0, st>>>(S12, S11, L, U, ldL, -2.0, k == 0 ? 0.0 : 1.0, grad + (r + 1) * U);
+            g_dense_launches += 2;
+            HYB_CHECK(hyb_gemm_tn(st, U, U, L, 1.0, S12, ldL, S11, ldL, 0.0, c->P2, ldU, 0));
+            HYB_CHECK(hyb_gemm_tn(st, U, U, L, 1.0, S12, ldL, S12, ldL, 0.0, c->P1, ldU, 0));
+            lincomb_kernel<<<nb1(c->bstride), 256, 0, st>>>(c->bstride, 1.0, c->P1, 1.0, c->P11, c->P1);
+            wsosone_accum_kernel<<<nb1(U * U), 256, 0, st>>>(U, ldU, c->P1, c->P2, c->diag, c->diag + (r + 1) * c->bstride,
+                                                            c->edge + r * c->bstride, (k == 0 && r == 0) ? 1 : 0, k == 0 ? 1 : 0);
+            g_dense_launches += 2;
+        }
+        if (R1 == 0 && k == 0) HYB_CUDA(cudaMemsetAsync(c->diag, 0, sizeof(double) * c->bstride, st));
+        wsosone_sub11_kernel<<<nb1(U * U), 256, 0, st>>>(U, ldU, c->P11, (double)(R - 2), c->diag);
+        DLAUNCHED();
+        HYB_CUDA(cudaGetLastError());
+    }
+    wsosone_hess_kernel<<<dim3(nb1(dim), (unsigned)dim), 256, 0, st>>>(U, R, c->diag, c->edge, c->bstride, ldU, c->H, ldD);
+    symmetrize_kernel<<<nb1(dim * dim), 256, 0, st>>>(c->H, dim, ldD);
+    copy_upper_dense_kernel<<<nb1(dim * dim), 256, 0, st>>>(c->H, c->Hf, dim, ldD);
+    g_dense_launches += 3;
+    HYB_CHECK(hyb_potrf(st, c->chH, nullptr));
+    HYB_CHECK(hyb_transpose(st, c->Hf, ldD, dim, dim, c->Lh, ldD, 1));
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, grad, 0.0, nullptr, c->v1);
+    dot_kernel<<<1, 1024, 0, st>>>(dim, c->v1, c->v3, c->scal + 0);
+    HYB_CHECK(hyb_potrs(st, c->chH, c->v1));
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, grad, 0.0, nullptr, c->v2);
+    dot_kernel<<<1, 1024, 0, st>>>(dim, c->v1, c->v2, c->scal + 1);
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, irtmu, dual_out, 1.0, grad, c->v2);
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, c->v2, 0.0, nullptr, c->v1);
+    HYB_CHECK(hyb_potrs(st, c->chH, c->v1));
+    dot_kernel<<<1, 1024, 0, st>>>(dim, c->v1, c->v2, c->scal + 2);
+    HYB_CHECK(hyb_gemv_t(st, dim, dim, c->H, ldD, c->v3, c->v1));
+    dot_kernel<<<1, 1024, 0, st>>>(dim, c->v1, c->v3, c->scal + 3);
+    wsos_finalize_kernel<<<1, 1, 0, st>>>(c->infos_dev, c->ninfos, c->chH.info, c->dual_ok, c->scal, c->nu, dim, flag, prox, c->slow,
+                                          c->sqrt_ok);
+    g_dense_launches += 10;
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int hybd_wsosone_sqrt_ok(cudaStream_t st, HybDenseWsosOne* c, int* ok) {
+    HYB_CUDA(cudaMemcpyAsync(ok, c->sqrt_ok, sizeof(int), cudaMemcpyDeviceToHost, st));
+    HYB_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int hybd_wsosone_prod(cudaStream_t st, HybDenseWsosOne* c, int op, const double* arr, int64_t lda, double* prod, int64_t ldp,
+                      int64_t m) {
+    if (m <= 0) return 0;
+    const int64_t D = c->dim, ldD = c->ldD;
+    if (m > c->big_cols) {
+        cudaFree(c->big1);
+        cudaFree(c->big2);
+        c->big1 = c->big2 = nullptr;
+        HYB_CUDA(cudaMalloc(&c->big1, sizeof(double) * ldD * m));
+        HYB_CUDA(cudaMalloc(&c->big2, sizeof(double) * ldD * m));
+        c->big_cols = m;
+    }
+    double *A = c->big1, *B = c->big2;
+    copy_mat_kernel<<<nb1(D * m), 256, 0, st>>>(arr, lda, A, ldD, D, m);
+    DLAUNCHED();
+    HYB_CUDA(cudaGetLastError());
+    const double* result = nullptr;
+    if (op == HYB_OP_HESS || op == 6) {
+        if (m == 1) HYB_CHECK(hyb_gemv_t(st, D, D, c->H, ldD, A, B));
+        else HYB_CHECK(hyb_gemm_tn(st, D, m, D, 1.0, c->H, ldD, A, ldD, 0.0, B, ldD, 0));
+        result = B;
+    } else if (op == HYB_OP_INV_HESS) {
+        if (m == 1) {
+            HYB_CHECK(hyb_potrs(st, c->chH, A));
+        } else {
+            HYB_CHECK(hyb_trsm_fwd(st, c->Hf, ldD, D, A, ldD, m));
+            HYB_CHECK(hyb_trsm_bwd(st, c->Hf, c->Lh, ldD, D, A, ldD, m));
+        }
+        result = A;
+    } else if (op == HYB_OP_SQRT_HESS) {
+        if (m == 1) HYB_CHECK(hyb_gemv_t(st, D, D, c->Lh, ldD, A, B));
+        else HYB_CHECK(hyb_gemm_tn(st, D, m, D, 1.0, c->Lh, ldD, A, ldD, 0.0, B, ldD, 0));
+        result = B;
+    } else {
+        HYB_CHECK(hyb_trsm_fwd(st, c->Hf, ldD, D, A, ldD, m));
+        result = A;
+    }
+    copy_mat_kernel<<<nb1(D * m), 256, 0, st>>>(result, ldD, prod, ldp, D, m);
+    DLAUNCHED();
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int hybd_wsosone_dder3(cudaStream_t st, HybDenseWsosOne* c, const double* dir, double* out) {
+    const int64_t U = c->U, ldU = c->ldU, dim = c->dim;
+    const int R = c->R, R1 = c->R - 1;
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, dir, 0.0, nullptr, c->v1);
+    DLAUNCHED();
+    const double* d = c->v1;
+    double* acc = c->v2;
+    // part 1 (:437-450) and the pieces of part 2 that depend on Lam11 only
+    for (int k = 0; k < c->nPs; ++k) {
+        const int64_t L = c->L[k], ldL = c->ldL[k];
+        rowscale2_kernel<<<nb1(U * L), 256, 0, st>>>(c->At[k], d, nullptr, nullptr, U, L, ldU, 0.0, c->D22t[k]);
+        DLAUNCHED();
+        HYB_CHECK(hyb_gemm_tn(st, L, L, U, 1.0, c->At[k], ldU, c->D22t[k], ldU, 0.0, c->XT[k], ldL, 0));   // (A D0 A')'
+        HYB_CHECK(hyb_gemm_tn(st, L, U, L, 1.0, c->XT[k], ldL, c->A[k], ldL, 0.0, c->LUlast[k], ldL, 0));  // A D0 A' A
+        coldot_kernel<<<nb1(U, 8), 256, 0, st>>>(c->LUlast[k], c->LUlast[k], L, U, ldL, 1.0, k == 0 ? 0.0 : 1.0, acc);
+        DLAUNCHED();
+    }
+    scale_vec_kernel<<<nb1(U), 256, 0, st>>>(U, (double)(2 - R), acc);
+    DLAUNCHED();
+    for (int r = 1; r < R; ++r) HYB_CUDA(cudaMemsetAsync(acc + r * U, 0, sizeof(double) * U, st));
+    // part 2 (:452-518)
+    for (int k = 0; k < c->nPs; ++k) {
+        const int64_t L = c->L[k], ldL = c->ldL[k];
+        double *At = c->At[k], *A = c->A[k], *LLt = c->LLt[k], *D22t = c->D22t[k];
+        for (int s = 0; s < R1; ++s) {
+            const double* ds = d + (s + 1) * U;
+            double *S11 = c->S11[k][s], *S12 = c->S12[k][s], *S11t = c->S11t[k][s], *S12t = c->S12t[k][s];
+            double *D11t = c->D11t[k][s], *D12t = c->D12t[k][s], *D21t = c->D21t[k][s];
+            double *h00 = c->half[k][4 * s], *h01 = c->half[k][4 * s + 1], *h10 = c->half[k][4 * s + 2], *h11 = c->half[k][4 * s + 3];
+            rowscale2_kernel<<<nb1(U * L), 256, 0, st>>>(S11t, d, S12t, ds, U, L, ldU, 0.0, D11t);
+            rowscale2_kernel<<<nb1(U * L), 256, 0, st>>>(S11t, ds, S12t, d, U, L, ldU, 0.0, D12t);
+            rowscale2_kernel<<<nb1(U * L), 256, 0, st>>>(At, ds, nullptr, nullptr, U, L, ldU, 0.0, D21t);
+            g_dense_launches += 3;
+            HYB_CUDA(cudaGetLastError());
+            auto llt = [&](const double* Yt, const double* Xt) {  // LLt = (X Y')' = (Y')' (X')
+                return hyb_gemm_tn(st, L, L, U, 1.0, Yt, ldU, Xt, ldU, 0.0, LLt, ldL, 0);
+            };
+            auto mul = [&](const double* Z, double beta, double* hb) {  // hb (+)= LL Z
+                return hyb_gemm_tn(st, L, U, L, 1.0, LLt, ldL, Z, ldL, beta, hb, ldL, 0);
+            };
+            HYB_CHECK(llt(S12t, D11t));
+            HYB_CHECK(mul(S12, 0.0, h00));
+            HYB_CHECK(mul(S11, 0.0, h01));
+            HYB_CHECK(llt(S12t, D12t));
+            HYB_CHECK(mul(S11, 1.0, h00));
+            HYB_CHECK(mul(S12, 1.0, h01));
+            HYB_CHECK(llt(S12t, D21t));
+            HYB_CHECK(mul(S12, 0.0, h10));
+            HYB_CHECK(mul(S11, 0.0, h11));
+            HYB_CHECK(llt(S12t, D22t));
+            HYB_CHECK(mul(S11, 1.0, h10));
+            HYB_CHECK(mul(S12, 1.0, h11));
+            HYB_CHECK(llt(At, D11t));
+            HYB_CHECK(mul(A, 1.0, h00));
+            HYB_CHECK(llt(At, D12t));
+            HYB_CHECK(mul(A, 1.0, h01));
+            HYB_CHECK(llt(At, D21t));
+            HYB_CHECK(mul(A, 1.0, h10));
+            lincomb_kernel<<<nb1(ldL * U), 256, 0, st>>>(ldL * U, 1.0, h11, 1.0, c->LUlast[k], h11);
+            coldot_kernel<<<nb1(U, 8), 256, 0, st>>>(h00, h00, L, U, ldL, 1.0, 1.0, acc);
+            coldot_kernel<<<nb1(U, 8), 256, 0, st>>>(h10, h10, L, U, ldL, 1.0, 1.0, acc);
+            coldot_kernel<<<nb1(U, 8), 256, 0, st>>>(h01, h01, L, U, ldL, 1.0, 1.0, acc);
+            coldot_kernel<<<nb1(U, 8), 256, 0, st>>>(h11, h11, L, U, ldL, 1.0, 1.0, acc);
+            coldot_kernel<<<nb1(U, 8), 256, 0, st>>>(h01, h00, L, U, ldL, 2.0, 1.0, acc + (s + 1) * U);
+            coldot_kernel<<<nb1(U, 8), 256, 0, st>>>(h11, h10, L, U, ldL, 2.0, 1.0, acc + (s + 1) * U);
+            g_dense_launches += 7;
+            HYB_CUDA(cudaGetLastError());
+        }
+    }
+    lincomb_kernel<<<nb1(dim), 256, 0, st>>>(dim, 1.0, acc, 0.0, nullptr, out);
+    DLAUNCHED();
+    HYB_CUDA(cudaGetLastError());
+    return 0;
+}

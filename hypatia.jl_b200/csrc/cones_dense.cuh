@@ -58,3 +58,13 @@ int hybd_wsoseuc_prod(cudaStream_t st, HybDenseWsosEuc* c, int op, const double*
                       int64_t m);
 int hybd_wsoseuc_dder3(cudaStream_t st, HybDenseWsosEuc* c, const double* dir, double* out);
 int hybd_wsoseuc_sqrt_ok(cudaStream_t st, HybDenseWsosEuc* c, int* ok);
+
+struct HybDenseWsosOne;  // WSOSInterpEpiNormOne (wsosinterpepinormone.jl)
+int hybd_wsosone_create(HybDenseWsosOne** out, int R, int64_t U, int nPs, const double* const* Ps_host, const int64_t* Ls);
+void hybd_wsosone_destroy(HybDenseWsosOne* c);
+int hybd_wsosone_update(cudaStream_t st, HybDenseWsosOne* c, const double* primal, const double* dual_in, double scal,
+                        double irtmu, double* point, double* dual_out, double* grad, int* flag, double* prox);
+int hybd_wsosone_prod(cudaStream_t st, HybDenseWsosOne* c, int op, const double* arr, int64_t lda, double* prod, int64_t ldp,
+                      int64_t m);
+int hybd_wsosone_dder3(cudaStream_t st, HybDenseWsosOne* c, const double* dir, double* out);
+int hybd_wsosone_sqrt_ok(cudaStream_t st, HybDenseWsosOne* c, int* ok);

@@ -316,6 +316,23 @@ def wsosinterpepinormeucl2():  # :2739-2766: min t : t^2 >= x^4 + (x - 1)^2 on [
     return m, dict(status="Optimal", primal_obj=math.sqrt(5.0) * U, x=np.full(U, math.sqrt(5.0)))
 
 
+def wsosinterpepinormone1():  # test/nativeinstances.jl:2640-2660: min t : t >= |x^2| on [-1, 1], t constant
+    U, pts, Ps = _wsos_box([-1], [1], 1)
+    h = np.concatenate([np.zeros(U), pts[:, 0] ** 2])
+    G = np.vstack([-_I(U), np.zeros((U, U))])
+    m = Model(np.ones(U), [[1, -1, 0], [1, 0, -1]], [0, 0], G, h, [cs.wsos_epinormone(2, U, Ps)])
+    return m, dict(status="Optimal", primal_obj=float(U), x=np.ones(U))
+
+
+def wsosinterpepinormone2():  # :2662-2688: min t : t >= |x^2| + |x - 1| on [-1, 1]
+    U, pts, Ps = _wsos_box([-1], [1], 1)
+    x = pts[:, 0]
+    h = np.concatenate([np.zeros(U), x**2, x - 1])
+    G = np.vstack([-_I(U), np.zeros((U, U)), np.zeros((U, U))])
+    m = Model(np.ones(U), [[1, -1, 0], [1, 0, -1]], [0, 0], G, h, [cs.wsos_epinormone(3, U, Ps)])
+    return m, dict(status="Optimal", primal_obj=3.0 * U, x=np.full(U, 3.0))
+
+
 KNOWN_ANSWER = {
     f.__name__: f
     for f in (
@@ -329,6 +346,7 @@ KNOWN_ANSWER = {
         wsosinterpnonnegative1, wsosinterpnonnegative2, wsosinterpnonnegative3,
         wsosinterppossemideftri1, wsosinterppossemideftri2, wsosinterppossemideftri3,
         wsosinterpepinormeucl1, wsosinterpepinormeucl2,
+        wsosinterpepinormone1, wsosinterpepinormone2,
     )
 }
 
@@ -399,6 +417,17 @@ def polynormeucl(n: int = 1, halfdeg: int = 3, R: int = 3, seed: int = 1) -> Mod
     h = np.concatenate([np.zeros(U)] + vals)
     G = np.vstack([-np.ones((U, 1))] + [np.zeros((U, 1))] * (R - 1))
     return Model([1.0], np.zeros((0, 1)), [], G, h, [cs.wsos_epinormeucl(R, U, Ps)])
+
+
+def polynormone(n: int = 1, halfdeg: int = 3, R: int = 3, seed: int = 1) -> Model:
+    """polynormeucl with the 1-norm: the smallest constant t with t >= sum_i |f_i(x)| on the box (WSOSInterpEpiNormOne)."""
+    rng = np.random.default_rng(seed)
+    U, pts, Ps = pu.interpolate(pu.BoxDomain(-np.ones(n), np.ones(n)), halfdeg, sample=False)
+    fs = [rng.standard_normal(n + 1) for _ in range(R - 1)]
+    vals = [f[0] + pts @ f[1:] for f in fs]
+    h = np.concatenate([np.zeros(U)] + vals)
+    G = np.vstack([-np.ones((U, 1))] + [np.zeros((U, 1))] * (R - 1))
+    return Model([1.0], np.zeros((0, 1)), [], G, h, [cs.wsos_epinormone(R, U, Ps)])
 
 
 def sparsepsd_maxeig(side: int = 20, seed: int = 1) -> Model:

@@ -35,7 +35,8 @@ enum hyb_cone_type {
     HYB_CONE_DOUBLYNONNEGATIVETRI = 7,    /* doublynonnegativetri.jl (real svec; side_or_R = side) */
     HYB_CONE_POSSEMIDEFTRISPARSE = 8,     /* possemideftrisparse/denseimpl.jl (real): side_or_R = side, dim = pattern size,
                                              Ls = dim 0-based rows then dim 0-based columns of the pattern (row >= col) */
-    HYB_CONE_WSOSINTERPEPINORMEUCL = 9    /* wsosinterpepinormeucl.jl: side_or_R = R, U, Ps / Ls as for the other WSOS cones */
+    HYB_CONE_WSOSINTERPEPINORMEUCL = 9,   /* wsosinterpepinormeucl.jl: side_or_R = R, U, Ps / Ls as for the other WSOS cones */
+    HYB_CONE_WSOSINTERPEPINORMONE = 10    /* wsosinterpepinormone.jl: the same fields */
 };
 
 /* One entry per cone of model.cones, in order; offsets follow build_cone_idxs

@@ -1198,6 +1198,135 @@ class WSOSInterpEpiNormEucl(_GenericHessCone):
         return out
 
 
+class WSOSInterpEpiNormOne(_GenericHessCone):
+    """src/Cones/wsosinterpepinormone.jl: one Schur complement mat_r = Lam(p_1) - Lam(p_r) Lam(p_1)^-1 Lam(p_r) per
+    polynomial r and P_k.  The reference's hess_prod! / inv_hess_prod! exploit the arrow shape of the Hessian
+    (:332-427); here they are the generic products with the same stored Hessian."""
+
+    def setup_extra_data(self):  # :101-142
+        self.R, self.U, self.Ps = self.spec.R, self.spec.U, self.spec.Ps
+
+    def _views(self, vec):
+        U = self.U
+        return [vec[r * U : (r + 1) * U] for r in range(self.R)]
+
+    def update_feas(self):  # :161-218
+        pv = self._views(self.point)
+        self.L11, self.Lm, self.LiL = [], [], []
+        self.is_feas_flag = True
+        for P in self.Ps:
+            Lam11 = P.T @ (pv[0][:, None] * P)
+            c, info = lapack.dpotrf(Lam11, lower=1, clean=1)
+            if info != 0:
+                self.is_feas_flag = False
+                break
+            LiL_k, Lm_k = [], []
+            for r in range(1, self.R):
+                M = sla.solve_triangular(c, P.T @ (pv[r][:, None] * P), lower=True)
+                cm, info = lapack.dpotrf(Lam11 - M.T @ M, lower=1, clean=1)
+                if info != 0:
+                    self.is_feas_flag = False
+                    break
+                LiL_k.append(M)
+                Lm_k.append(cm)
+            if not self.is_feas_flag:
+                break
+            self.L11.append(c)
+            self.LiL.append(LiL_k)
+            self.Lm.append(Lm_k)
+        self.feas_updated = True
+        return self.is_feas_flag
+
+    def is_dual_feas(self):  # :220-224
+        return bool(np.all(self.dual_point[: self.U] > EPS))
+
+    def update_grad(self):  # :226-265
+        U, R = self.U, self.R
+        g = np.zeros(self.dim)
+        self.L11iP, self.S11, self.S12 = [], [], []
+        for k, P in enumerate(self.Ps):
+            A = sla.solve_triangular(self.L11[k], P.T, lower=True)
+            S12 = [sla.solve_triangular(self.Lm[k][r], -(self.LiL[k][r].T @ A), lower=True) for r in range(R - 1)]
+            S11 = [sla.solve_triangular(self.Lm[k][r], P.T, lower=True) for r in range(R - 1)]
+            self.L11iP.append(A)
+            self.S11.append(S11)
+            self.S12.append(S12)
+            g[:U] -= R * np.sum(A * A, axis=0)
+            for r in range(R - 1):
+                g[:U] -= 2.0 * np.sum(S12[r] * S12[r], axis=0)
+                g[(r + 1) * U : (r + 2) * U] -= 2.0 * np.sum(S12[r] * S11[r], axis=0)
+        self.grad_vec = g
+        self.grad_updated = True
+        return g
+
+    def update_hess(self):  # :267-330
+        self.grad()
+        U, R = self.U, self.R
+        diag = [np.zeros((U, U)) for _ in range(R)]
+        edge = [np.zeros((U, U)) for _ in range(R - 1)]
+        for k in range(len(self.Ps)):
+            A = self.L11iP[k]
+            P11 = A.T @ A
+            for r in range(R - 1):
+                P2 = self.S12[k][r].T @ self.S11[k][r]
+                P1 = self.S12[k][r].T @ self.S12[k][r] + P11
+                uu = np.triu(2.0 * (P1 * P1 + P2 * P2))
+                diag[0] += uu
+                diag[r + 1] += uu
+                edge[r] += np.triu(4.0 * P1 * P2)
+            diag[0] -= np.triu(P11 * P11) * (R - 2)
+        H = np.zeros((self.dim, self.dim))
+        H[:U, :U] = diag[0]
+        for r in range(R - 1):
+            sl = slice((r + 1) * U, (r + 2) * U)
+            H[:U, sl] = edge[r] + np.triu(edge[r], 1).T  # copytri!(edge, 'U')
+            H[sl, sl] = diag[r + 1]
+        self.hess_mat = np.triu(H) + np.triu(H, 1).T
+        self.hess_updated = True
+
+    def dder3(self, direction):  # :429-521
+        U, R = self.U, self.R
+        d = self._views(np.asarray(direction, dtype=np.float64))
+        out = np.zeros(self.dim)
+        for k in range(len(self.Ps)):
+            A = self.L11iP[k]
+            LL = (A * d[0][None, :]) @ A.T
+            LU = (np.triu(LL) + np.triu(LL, 1).T) @ A
+            out[:U] += np.sum(LU * LU, axis=0)
+        out[:U] *= 2 - R
+        for k in range(len(self.Ps)):
+            A, S11, S12 = self.L11iP[k], self.S11[k], self.S12[k]
+            L = A.shape[0]
+            dir22 = A * d[0][None, :]
+            dir22_A = dir22 @ A.T
+            LU_last = dir22_A @ A
+            for s_ in range(R - 1):
+                D = d[s_ + 1][None, :]
+                d11 = S11[s_] * d[0][None, :] + S12[s_] * D
+                d12 = S11[s_] * D + S12[s_] * d[0][None, :]
+                d21 = A * D
+                half = np.zeros((2 * L, 2 * U))
+                LL = d11 @ S12[s_].T
+                half[:L, :U] = LL @ S12[s_]
+                half[:L, U:] = LL @ S11[s_]
+                LL = d12 @ S12[s_].T
+                half[:L, :U] += LL @ S11[s_]
+                half[:L, U:] += LL @ S12[s_]
+                LL = d21 @ S12[s_].T
+                half[L:, :U] = LL @ S12[s_]
+                half[L:, U:] = LL @ S11[s_]
+                LL = dir22 @ S12[s_].T
+                half[L:, :U] += LL @ S11[s_]
+                half[L:, U:] += LL @ S12[s_]
+                half[:L, :U] += (d11 @ A.T) @ A
+                half[:L, U:] += (d12 @ A.T) @ A
+                half[L:, :U] += (d21 @ A.T) @ A
+                half[L:, U:] += LU_last
+                out[:U] += np.sum(half[:, :U] ** 2, axis=0) + np.sum(half[:, U:] ** 2, axis=0)
+                out[(s_ + 1) * U : (s_ + 2) * U] += 2.0 * np.sum(half[:, U:] * half[:, :U], axis=0)
+        return out
+
+
 _CLASSES = {
     cs.NONNEGATIVE: Nonnegative,
     cs.EPINORMEUCL: EpiNormEucl,
@@ -1209,6 +1338,7 @@ _CLASSES = {
     cs.DOUBLYNONNEGATIVETRI: DoublyNonnegativeTri,
     cs.POSSEMIDEFTRISPARSE: PosSemidefTriSparse,
     cs.WSOSINTERPEPINORMEUCL: WSOSInterpEpiNormEucl,
+    cs.WSOSINTERPEPINORMONE: WSOSInterpEpiNormOne,
 }
 
 

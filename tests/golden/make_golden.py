@@ -35,6 +35,7 @@ SEEDED = {
     "nearestdnn_side12": ("nearestdnn", dict(side=12, seed=1)),
     "sparsepsd_maxeig_side20": ("sparsepsd_maxeig", dict(side=20, seed=1)),
     "polynormeucl_n2_hd2_R3": ("polynormeucl", dict(n=2, halfdeg=2, R=3, seed=1)),
+    "polynormone_n2_hd2_R3": ("polynormone", dict(n=2, halfdeg=2, R=3, seed=1)),
 }
 
 

@@ -51,6 +51,13 @@ def _wsoseuc(n, halfdeg, R, use_dual=False):
     return cs.wsos_epinormeucl(R, U, Ps, use_dual=use_dual)
 
 
+def _wsosone(n, halfdeg, R, use_dual=False):
+    from hypatia_b200 import polyutils as pu
+
+    U, _, Ps = pu.interpolate(pu.BoxDomain(-np.ones(n), np.ones(n)), halfdeg, sample=False)
+    return cs.wsos_epinormone(R, U, Ps, use_dual=use_dual)
+
+
 def _spsd(side, seed, use_dual=False):
     rng = np.random.default_rng(seed)
     mask = np.tril(rng.random((side, side)) < 1.0 / np.sqrt(side), -1) | np.eye(side, dtype=bool)
@@ -89,6 +96,8 @@ SPEC_SETS = {
     # WSOSInterpEpiNormEucl (test/cone.jl:848-853 shapes), dual barrier by default, one primal-barrier instance
     "wsos_epinormeucl": [_wsoseuc(1, 1, 2), cs.Nonnegative(3), _wsoseuc(1, 2, 4), _wsoseuc(2, 2, 3), _wsoseuc(3, 1, 2),
                          _wsoseuc(1, 3, 3, use_dual=True)],
+    "wsos_epinormone": [_wsosone(1, 1, 2), cs.Nonnegative(3), _wsosone(1, 2, 4), _wsosone(2, 2, 3), _wsosone(3, 1, 2),
+                        _wsosone(1, 3, 3, use_dual=True)],
     "mixed": [cs.Nonnegative(10)] + [cs.EpiNormEucl(8)] * 4 + [cs.EpiPerSquare(8)] * 4
     + [cs.PosSemidefTri(136)] * 3 + [cs.Nonnegative(3), cs.EpiNormEucl(5)],
 }

@@ -316,3 +316,48 @@ def test_wsosinterpepinormeucl_barrier_derivatives():
     assert np.allclose(cone.hess_prod(d), fd_h, rtol=1e-5, atol=1e-5)
     fd_3 = (grad_at(s + h * d) - 2 * grad_at(s) + grad_at(s - h * d)) / (h * h)  # = grad'''[d, d]
     assert np.allclose(-0.5 * fd_3, cone.dder3(d), rtol=1e-3, atol=1e-3)
+
+
+@pytest.mark.parametrize("n,halfdeg,ds", [(1, 1, 1), (1, 2, 3), (2, 2, 2), (3, 1, 1)])
+def test_wsosinterpepinormone(n, halfdeg, ds):  # test/cone.jl:880-885 (init_tol = Inf)
+    U, Ps = _interp(n, halfdeg)
+    run_oracle_identities(cs.wsos_epinormone(1 + ds, U, Ps), init_tol=np.inf, tol=1e5 * EPS)
+
+
+def test_wsosinterpepinormone_barrier_derivatives():
+    """test/cone.jl:887-903: the barrier; gradient, Hessian product and dder3 against finite differences."""
+    U, Ps = _interp(1, 1)
+    ds = 2
+    spec = cs.wsos_epinormone(1 + ds, U, Ps)
+
+    def barrier(s):
+        tot = 0.0
+        for P in Ps:
+            Lam = P.T @ (s[:U, None] * P)
+            L1 = np.linalg.cholesky(Lam)
+            PL1 = np.linalg.solve(L1, P.T)
+            tot += -2.0 * np.sum(np.log(np.diag(L1)))
+            for i in range(ds):
+                LLi = PL1 @ (s[(1 + i) * U : (2 + i) * U, None] * P)
+                tot -= np.linalg.slogdet(Lam - LLi.T @ LLi)[1]
+        return tot
+
+    rng = np.random.default_rng(5)
+    s = spec.initial_point() + 0.1 * rng.uniform(-1, 1, spec.dim)
+
+    def cone_at(v):
+        c = make_cone(spec)
+        c.setup_data()
+        c.load_point(v)
+        assert c.is_feas()
+        return c
+
+    cone = cone_at(s)
+    h = 1e-5
+    fd = np.array([(barrier(s + h * e) - barrier(s - h * e)) / (2 * h) for e in np.eye(spec.dim)])
+    assert np.allclose(cone.grad(), fd, rtol=1e-6, atol=1e-6)
+    d = rng.standard_normal(spec.dim)
+    fd_h = (cone_at(s + h * d).grad() - cone_at(s - h * d).grad()) / (2 * h)
+    assert np.allclose(cone.hess_prod(d), fd_h, rtol=1e-5, atol=1e-5)
+    fd_3 = (cone_at(s + h * d).grad() - 2 * cone.grad() + cone_at(s - h * d).grad()) / (h * h)
+    assert np.allclose(-0.5 * fd_3, cone.dder3(d), rtol=1e-3, atol=1e-3)
