@@ -36,6 +36,11 @@ SEEDED = {
     "sparsepsd_maxeig_side20": ("sparsepsd_maxeig", dict(side=20, seed=1)),
     "polynormeucl_n2_hd2_R3": ("polynormeucl", dict(n=2, halfdeg=2, R=3, seed=1)),
     "polynormone_n2_hd2_R3": ("polynormone", dict(n=2, halfdeg=2, R=3, seed=1)),
+    # the same families at sizes where the stored Hessian is a few hundred rows
+    "nearestdnn_side30": ("nearestdnn", dict(side=30, seed=2)),
+    "sparsepsd_maxeig_side80": ("sparsepsd_maxeig", dict(side=80, seed=2)),
+    "polynormeucl_n2_hd5_R3": ("polynormeucl", dict(n=2, halfdeg=5, R=3, seed=2)),
+    "polynormone_n2_hd5_R4": ("polynormone", dict(n=2, halfdeg=5, R=4, seed=2)),
 }
 
 

@@ -32,10 +32,12 @@ def _devices(n):
     return [k % have for k in range(n)]
 
 
-@pytest.mark.parametrize("ndev", [2, 3])
-def test_partial_schur_matrices_sum_to_the_single_gpu_matrix(ndev):
+# (N, ndev): N = 160 is two tile columns (with three devices one owner holds nothing); 520 and 700 spread five and six
+# tile columns, the last one ragged, over three and four owners with two compact column blocks each
+@pytest.mark.parametrize("N,ndev", [(160, 2), (160, 3), (520, 3), (700, 4)])
+def test_partial_schur_matrices_sum_to_the_single_gpu_matrix(N, ndev):
     def model():
-        return instances.block_multicone(N=160, seed=5, psd_side=8)
+        return instances.block_multicone(N=N, seed=5, psd_side=8)
 
     def prepared(**kw):
         s = make_gpu_solver(0, **kw)
