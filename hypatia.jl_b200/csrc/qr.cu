@@ -288,3 +288,96 @@ extern "C" int hyb_geqp3(hyb_ctx* c, int64_t m, int64_t n, double* A, int64_t ld
     cleanup();
     return rc;
 }
+
+// --------------------------------------------------------------------------------
+// C <- C Q for the Q of a Householder QR in factored form (LAPACK dormqr 'R', 'N'): the G * Ap_Q of the reduce
+// (src/Solvers/process.jl:310-338, `rmul!(G, Ap_fact.Q)`).  Q = H_0 H_1 ... H_{k-1}, H_j = I - tau_j v_j v_j' with
+// v_j = [0 .. 0, 1, V[j+1:n, j]].  The rows of C are independent of each other under a right multiplication, so one
+// thread owns one row and walks through ALL reflectors without any grid-wide step: per reflector w = C[r, j:] v_j,
+// then C[r, j:] -= tau_j w v_j'; consecutive threads own consecutive rows, so every access of the column-major C is
+// coalesced; v_j passes through shared memory in chunks.
+// --------------------------------------------------------------------------------
+namespace {
+constexpr int ORM_THREADS = 256, ORM_CHUNK = 2048;
+
+__global__ void __launch_bounds__(ORM_THREADS)
+ormqr_right_kernel(int64_t m, int64_t n, int64_t k, const double* __restrict__ V, int64_t ldv, const double* __restrict__ tau,
+                   double* __restrict__ C, int64_t ldc) {
+    __shared__ double vs[ORM_CHUNK];
+    const int64_t r = (int64_t)blockIdx.x * ORM_THREADS + threadIdx.x;
+    const bool live = r < m;
+    for (int64_t j = 0; j < k; ++j) {
+        const int64_t len = n - j;  // v_j[0] = 1, v_j[i] = V[j + i, j]
+        const double tj = tau[j];
+        if (tj == 0.0) continue;  // H_j = I (uniform over the grid)
+        double w = 0.0;
+        for (int64_t c0 = 0; c0 < len; c0 += ORM_CHUNK) {
+            const int64_t cl = len - c0 < ORM_CHUNK ? len - c0 : ORM_CHUNK;
+            __syncthreads();
+            for (int64_t i = threadIdx.x; i < cl; i += ORM_THREADS) vs[i] = (c0 + i == 0) ? 1.0 : V[j + c0 + i + j * ldv];
+            __syncthreads();
+            if (live) {
+                const double* row = C + r + (j + c0) * ldc;
+                for (int64_t i = 0; i < cl; ++i) w += row[i * ldc] * vs[i];
+            }
+        }
+        const double tw = tj * w;
+        for (int64_t c0 = 0; c0 < len; c0 += ORM_CHUNK) {
+            const int64_t cl = len - c0 < ORM_CHUNK ? len - c0 : ORM_CHUNK;
+            __syncthreads();
+            for (int64_t i = threadIdx.x; i < cl; i += ORM_THREADS) vs[i] = (c0 + i == 0) ? 1.0 : V[j + c0 + i + j * ldv];
+            __syncthreads();
+            if (live) {
+                double* row = C + r + (j + c0) * ldc;
+                for (int64_t i = 0; i < cl; ++i) row[i * ldc] -= tw * vs[i];
+            }
+        }
+    }
+}
+}  // namespace
+
+extern "C" int hyb_ormqr_right(hyb_ctx* c, int64_t m, int64_t n, int64_t k, const double* V, int64_t ldv, const double* tau,
+                               double* C, int64_t ldc) {
+    if (!c) return -1;
+    if (m < 0 || n < 0 || k < 0 || k > n || ldv < (n > 1 ? n : 1) || ldc < (m > 1 ? m : 1)) {
+        hyb_set_error("hyb_ormqr_right: bad dimensions m=%lld n=%lld k=%lld ldv=%lld ldc=%lld", (long long)m, (long long)n,
+                      (long long)k, (long long)ldv, (long long)ldc);
+        return -3;
+    }
+    if (m == 0 || n == 0 || k == 0) return 0;
+    HYB_CUDA(cudaSetDevice(c->device));
+    cudaStream_t st = c->st;
+    const int64_t ldV = hyb_round_up(n, 16), ldC = hyb_round_up(m, 16);
+    double *dV = nullptr, *dtau = nullptr, *dC = nullptr;
+    cudaError_t e = cudaMalloc(&dV, sizeof(double) * ldV * k);
+    if (e == cudaSuccess) e = cudaMalloc(&dtau, sizeof(double) * k);
+    if (e == cudaSuccess) e = cudaMalloc(&dC, sizeof(double) * ldC * n);
+    if (e == cudaSuccess)
+        e = cudaMemcpy2DAsync(dV, sizeof(double) * ldV, V, sizeof(double) * ldv, sizeof(double) * n, k, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dtau, tau, sizeof(double) * k, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess)
+        e = cudaMemcpy2DAsync(dC, sizeof(double) * ldC, C, sizeof(double) * ldc, sizeof(double) * m, n, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) {
+        c->h2d_bytes += (int64_t)sizeof(double) * (n * k + k + m * n);
+        KBEGIN(c);
+        ormqr_right_kernel<<<(unsigned)((m + ORM_THREADS - 1) / ORM_THREADS), ORM_THREADS, 0, st>>>(m, n, k, dV, ldV, dtau, dC, ldC);
+        ++g_misc_launches;
+        e = cudaGetLastError();
+        KEND(c);
+    }
+    if (e == cudaSuccess)
+        e = cudaMemcpy2DAsync(C, sizeof(double) * ldc, dC, sizeof(double) * ldC, sizeof(double) * m, n, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e == cudaSuccess) {
+        c->d2h_bytes += (int64_t)sizeof(double) * m * n;
+        ksync(c);
+    }
+    cudaFree(dV);
+    cudaFree(dtau);
+    cudaFree(dC);
+    if (e != cudaSuccess) {
+        hyb_set_error("hyb_ormqr_right: %s", cudaGetErrorString(e));
+        return -1;
+    }
+    return 0;
+}

@@ -86,10 +86,14 @@ class _PivotedQR:
         return out.ravel() if one_d else out
 
     def right_apply_q(self, M: np.ndarray) -> np.ndarray:
-        """M <- M Q."""
+        """M <- M Q.  ``ormqr_backend(refl, tau, M) -> M Q`` (set by the GPU path next to the QR backend) replaces
+        LAPACK's dormqr for the O(q n k) product G * Ap_Q of the reduce (process.jl:310-338)."""
         M2 = np.array(M, dtype=np.float64, order="F")
         if self.tau.size == 0:
             return M2
+        be = getattr(self, "ormqr_backend", None)
+        if be is not None:
+            return be(self.refl, self.tau, M2)
         _, lw, info = lapack.dormqr("R", "N", self.refl, self.tau, M2, -1)
         out, _, info = lapack.dormqr("R", "N", self.refl, self.tau, M2, int(lw[0]), overwrite_c=1)
         assert info == 0
@@ -412,6 +416,8 @@ class Solver:
             self.y_keep_idxs = np.zeros(0, dtype=np.int64)
             return
         fact = self.Ap_fact = _PivotedQR(model.A.T, self._qr_backend_for(model.A.T.shape))
+        if self._qr_backend_for(model.A.T.shape) is not None:
+            fact.ormqr_backend = getattr(self, "ormqr_backend", None)
         rank = self.Ap_rank = fact.rank_est(self.init_tol_qr)
         Ap_R = fact.R(rank)
         y_keep = fact.piv[:rank].copy()

@@ -88,6 +88,7 @@ SIGNATURES = {
     ),
     "hyb_step_point_update": (C.c_int, [C.c_void_p, c_double_p, c_double_p]),
     "hyb_geqp3": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, c_double_p, C.c_int64, c_int_p, c_double_p]),
+    "hyb_ormqr_right": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, c_double_p, C.c_int64, c_double_p, c_double_p, C.c_int64]),
     "hyb_outer_prod": (
         C.c_int,
         [C.c_void_p, C.c_int64, C.c_int64, C.c_double, c_double_p, C.c_int64, C.c_double, c_double_p, C.c_int64],
@@ -227,6 +228,16 @@ class Context:
             "hyb_geqp3",
         )
         return A, tau, piv[:n].astype(np.int64)
+
+    def ormqr_right(self, refl: np.ndarray, tau: np.ndarray, M: np.ndarray) -> np.ndarray:
+        """M Q for the Q of a factored QR (reflectors below the diagonal of ``refl``, n x k): dormqr('R', 'N') on the GPU."""
+        V, t = f64(refl), f64(tau)
+        out = np.array(M, dtype=np.float64, order="F")
+        m, n = out.shape
+        assert V.shape[0] == n and V.shape[1] >= t.size
+        self.check(self.lib.hyb_ormqr_right(self.ptr, m, n, t.size, dptr(V), max(n, 1), dptr(t), dptr(out), max(m, 1)),
+                   "hyb_ormqr_right")
+        return out
 
     # ---- dense helpers -----------------------------------------------------
     def outer_prod(self, A: np.ndarray, C_: Optional[np.ndarray] = None, alpha=1.0, beta=0.0) -> np.ndarray:

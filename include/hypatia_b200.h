@@ -219,6 +219,12 @@ int hyb_step_point_update(hyb_ctx* ctx, const double* coef, double* zs);
  * first entry implicit), tau (min(m,n)), jpvt (n, 0-based: column j of A*P is column jpvt[j] of A)
  * -- so dormqr / triangular solves on the host consume it unchanged.  Needs no loaded model. */
 int hyb_geqp3(hyb_ctx* ctx, int64_t m, int64_t n, double* A, int64_t lda, int* jpvt, double* tau);
+/* C (m x n, host, in / out) <- C Q with the Q of a Householder QR in factored form: LAPACK dormqr('R', 'N', ...).
+ * V (n x k, leading dimension ldv) holds the reflectors below its diagonal as dgeqrf / dgeqp3 / hyb_geqp3 leave them,
+ * tau their k scalars.  Replaces `rmul!(G, Ap_fact.Q)` of the reduce, src/Solvers/process.jl:310-338 (the
+ * reference's own comment there: "very inefficient method used for sparse Ap_fact"). */
+int hyb_ormqr_right(hyb_ctx* ctx, int64_t m, int64_t n, int64_t k, const double* V, int64_t ldv, const double* tau, double* C,
+                    int64_t ldc);
 
 /* ---- dense helpers: src/linearalgebra/dense.jl ---------------------------------- */
 /* outer_prod!(A, B, alpha, beta) = BLAS.syrk!('U','T'), dense.jl:72-79:

@@ -91,3 +91,25 @@ def test_solves_with_gpu_preprocessing_qr(build, monkeypatch):
     if ref.status == "Optimal":
         assert abs(gpu.primal_obj - ref.primal_obj) <= 1e-7 * (1 + abs(ref.primal_obj))
         assert np.abs(gpu.get_x() - ref.get_x()).max() <= 1e-5 * (1 + np.abs(ref.get_x()).max())
+
+
+@pytest.mark.parametrize("m,n,k", [(1, 1, 1), (5, 7, 3), (300, 130, 130), (257, 300, 64), (1000, 64, 64), (70, 2500, 700)])
+def test_ormqr_right_matches_lapack(m, n, k):
+    """hyb_ormqr_right (C <- C Q, the G * Ap_Q of the reduce, process.jl:310-338) against LAPACK dormqr('R', 'N') on
+    the reflectors of a QR of a random n x k matrix; n = 2500 walks the reflector through shared memory in chunks."""
+    from scipy.linalg import lapack
+
+    rng = np.random.default_rng(m + 7 * n + 13 * k)
+    (qr, tau), _, _ = sla.qr(rng.standard_normal((n, k)), mode="raw", pivoting=True)
+    refl = np.asfortranarray(qr[:, :k])
+    if k > 2:
+        tau = tau.copy()
+        tau[k // 2] = 0.0  # an identity reflector (what dlarfg returns for a zero column)
+    C0 = np.asfortranarray(rng.standard_normal((m, n)))
+    _, lw, _ = lapack.dormqr("R", "N", refl, tau, C0.copy(order="F"), -1)
+    want, _, info = lapack.dormqr("R", "N", refl, tau, C0.copy(order="F"), int(lw[0]))
+    assert info == 0
+    got = context().ormqr_right(refl, tau, C0)
+    assert np.abs(got - want).max() <= 50 * k * EPS * max(1.0, np.abs(want).max())
+    # Q is orthogonal: row norms are preserved
+    assert np.allclose(np.linalg.norm(got, axis=1), np.linalg.norm(C0, axis=1), rtol=1e-12)
