@@ -598,5 +598,6 @@ def attach_gpu_qr(solver, ctx: Context) -> None:
     import os
 
     solver.qr_backend = ctx.geqp3
-    solver.ormqr_backend = ctx.ormqr_right  # G * Ap_Q of the reduce (process.jl:310-338), same size threshold
+    solver.ormqr_backend = ctx.ormqr_right  # G * Ap_Q of the reduce (process.jl:310-338), same size threshold ...
+    solver.ormqr_min_size = int(os.environ.get("HYB_GPU_ORMQR_MIN_SIZE", str(1 << 22)))  # ... or G of 4M entries and more
     solver.qr_backend_min_cols = int(os.environ.get("HYB_GPU_QR_MIN", "256"))

@@ -74,8 +74,13 @@ class ConeSet:
     def initial_point(self) -> np.ndarray:
         """set_initial_point! per cone, concatenated."""
         out = np.zeros(self.q)
+        cache = {}  # the initial point depends on the cone's type and shape only (10^5 equal cones: one evaluation)
         for k, spec in enumerate(self.specs):
-            out[self.offs[k] : self.offs[k + 1]] = spec.initial_point()
+            key = (spec.type_code, spec.dim, getattr(spec, "R", 0), getattr(spec, "U", 0), id(spec) if hasattr(spec, "rows0") else 0)
+            v = cache.get(key)
+            if v is None:
+                v = cache[key] = spec.initial_point()
+            out[self.offs[k] : self.offs[k + 1]] = v
         return out
 
     # ---- oracle interface (Cones.jl) ------------------------------------

@@ -57,7 +57,10 @@ class _PivotedQR:
             self.piv = np.arange(self.ncols)
             return
         if backend is not None:
-            qr, tau, piv = backend(M)
+            try:
+                qr, tau, piv = backend(M, overwrite_a=True)  # M is this object's private copy
+            except TypeError:
+                qr, tau, piv = backend(M)
         else:
             (qr, tau), _, piv = sla.qr(M, mode="raw", pivoting=True, overwrite_a=True)
         self.qr, self.tau, self.piv = np.asfortranarray(qr), tau, piv
@@ -93,7 +96,10 @@ class _PivotedQR:
             return M2
         be = getattr(self, "ormqr_backend", None)
         if be is not None:
-            return be(self.refl, self.tau, M2)
+            try:
+                return be(self.refl, self.tau, M2, overwrite=True)  # M2 is a private copy
+            except TypeError:
+                return be(self.refl, self.tau, M2)
         _, lw, info = lapack.dormqr("R", "N", self.refl, self.tau, M2, -1)
         out, _, info = lapack.dormqr("R", "N", self.refl, self.tau, M2, int(lw[0]), overwrite_c=1)
         assert info == 0
@@ -308,27 +314,38 @@ class Solver:
         c, A, b, G, h = model.c, model.A, model.b, model.G, model.h
         minval = math.sqrt(EPS)
 
-        def colmax(M):
-            return np.maximum(np.max(np.abs(M), axis=0), minval) if M.shape[0] else np.full(M.shape[1], minval)
+        # one |.| pass per matrix; row and column maxima from the same temporary (G can be gigabytes)
+        def absmax(M):
+            if M.size == 0:
+                return np.full(M.shape[1], minval), np.full(M.shape[0], minval)
+            aM = np.abs(M)
+            return np.maximum(aM.max(axis=0), minval), np.maximum(aM.max(axis=1), minval)
 
-        def rowmax(M):
-            return np.maximum(np.max(np.abs(M), axis=1), minval) if M.shape[1] else np.full(M.shape[0], minval)
-
-        self.c_scale = c_scale = np.sqrt(np.maximum(np.abs(c), np.maximum(colmax(A), colmax(G))))
-        self.b_scale = b_scale = np.sqrt(np.maximum(np.abs(b), rowmax(A)))
+        Acol, Arow = absmax(A)
+        Gcol, Grow = absmax(G)
+        self.c_scale = c_scale = np.sqrt(np.maximum(np.abs(c), np.maximum(Acol, Gcol)))
+        self.b_scale = b_scale = np.sqrt(np.maximum(np.abs(b), Arow))
         h_scale = self.h_scale = np.ones(model.q)
-        Grow = rowmax(G)
-        offs = model.cone_offs
-        for k, cone in enumerate(model.cones):
-            lo, hi = offs[k], offs[k + 1]
-            if cone.per_row_h_scale:
-                h_scale[lo:hi] = np.sqrt(np.maximum(np.abs(h[lo:hi]), Grow[lo:hi]))
-            else:
-                hmax = max(float(np.max(np.abs(h[lo:hi]))), minval)
-                h_scale[lo:hi] = math.sqrt(max(hmax, float(np.max(Grow[lo:hi]))))
+        offs = np.asarray(model.cone_offs, dtype=np.int64)
+        if len(model.cones):
+            # per-row cones (Nonnegative) scale row by row, every other cone by the maximum over its rows
+            # (process.jl:36-52); segment maxima instead of a Python loop over 10^5 cones
+            habs = np.abs(h)
+            per_row = np.repeat(np.array([bool(cn.per_row_h_scale) for cn in model.cones]), np.diff(offs))
+            hmax = np.maximum(np.maximum.reduceat(habs, offs[:-1]), minval)
+            gmax = np.maximum.reduceat(Grow, offs[:-1])
+            cone_scale = np.sqrt(np.maximum(hmax, gmax))
+            h_scale[:] = np.where(per_row, np.sqrt(np.maximum(habs, Grow)), np.repeat(cone_scale, np.diff(offs)))
         model.c = c / c_scale
-        model.A = np.asfortranarray((A / c_scale[None, :]) / b_scale[:, None])
-        model.G = np.asfortranarray((G / c_scale[None, :]) / h_scale[:, None])
+        # (M ./ c_scale') ./ row_scale with one result array (same two roundings per entry as the two-temporary form)
+        def scaled(M, row_scale):
+            out = np.empty(M.shape, order="F")
+            np.divide(M, c_scale[None, :], out=out)
+            np.divide(out, row_scale[:, None], out=out)
+            return out
+
+        model.A = scaled(A, b_scale)
+        model.G = scaled(G, h_scale)
         model.b = b / b_scale
         model.h = h / h_scale
         return True
@@ -416,7 +433,9 @@ class Solver:
             self.y_keep_idxs = np.zeros(0, dtype=np.int64)
             return
         fact = self.Ap_fact = _PivotedQR(model.A.T, self._qr_backend_for(model.A.T.shape))
-        if self._qr_backend_for(model.A.T.shape) is not None:
+        # G * Ap_Q on the same backend as the QR, and in any case when G is large (the product is O(q n rank): one
+        # pass over a multi-gigabyte G per reflector on the host)
+        if self._qr_backend_for(model.A.T.shape) is not None or model.G.size >= getattr(self, "ormqr_min_size", 1 << 62):
             fact.ormqr_backend = getattr(self, "ormqr_backend", None)
         rank = self.Ap_rank = fact.rank_est(self.init_tol_qr)
         Ap_R = fact.R(rank)

@@ -215,10 +215,14 @@ class Context:
         return mf.value, ms.value
 
     # ---- preprocessing -------------------------------------------------------
-    def geqp3(self, M: np.ndarray):
+    def geqp3(self, M: np.ndarray, overwrite_a: bool = False):
         """Column-pivoted QR on the GPU; returns (qr, tau, piv) like
-        scipy.linalg.qr(M, mode="raw", pivoting=True)."""
-        A = np.array(M, dtype=np.float64, order="F")
+        scipy.linalg.qr(M, mode="raw", pivoting=True).  ``overwrite_a``: factor in M's own storage when M is a
+        Fortran-ordered float64 array (no second host copy of a multi-gigabyte matrix)."""
+        if overwrite_a and isinstance(M, np.ndarray) and M.dtype == np.float64 and M.flags.f_contiguous and M.flags.writeable:
+            A = M
+        else:
+            A = np.array(M, dtype=np.float64, order="F")
         m, n = A.shape
         k = min(m, n)
         tau = np.zeros(k)
@@ -229,10 +233,14 @@ class Context:
         )
         return A, tau, piv[:n].astype(np.int64)
 
-    def ormqr_right(self, refl: np.ndarray, tau: np.ndarray, M: np.ndarray) -> np.ndarray:
-        """M Q for the Q of a factored QR (reflectors below the diagonal of ``refl``, n x k): dormqr('R', 'N') on the GPU."""
+    def ormqr_right(self, refl: np.ndarray, tau: np.ndarray, M: np.ndarray, overwrite: bool = False) -> np.ndarray:
+        """M Q for the Q of a factored QR (reflectors below the diagonal of ``refl``, n x k): dormqr('R', 'N') on the GPU.
+        ``overwrite``: work in M's own storage when it is a Fortran-ordered float64 array."""
         V, t = f64(refl), f64(tau)
-        out = np.array(M, dtype=np.float64, order="F")
+        if overwrite and isinstance(M, np.ndarray) and M.dtype == np.float64 and M.flags.f_contiguous and M.flags.writeable:
+            out = M
+        else:
+            out = np.array(M, dtype=np.float64, order="F")
         m, n = out.shape
         assert V.shape[0] == n and V.shape[1] >= t.size
         self.check(self.lib.hyb_ormqr_right(self.ptr, m, n, t.size, dptr(V), max(n, 1), dptr(t), dptr(out), max(m, 1)),
