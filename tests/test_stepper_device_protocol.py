@@ -105,3 +105,55 @@ def test_protocol_path_reproduces_classic_path(name):
         assert [r[key] for r in proto.trace] == [r[key] for r in classic.trace], key
     assert np.allclose([r["mu"] for r in proto.trace], [r["mu"] for r in classic.trace], rtol=1e-10)
     assert np.allclose(proto.get_x(), classic.get_x(), rtol=1e-9, atol=1e-12)
+
+
+class SpeculativeSystemSolver(ProtocolSystemSolver):
+    """... plus hyb_search_alpha: several schedule entries per call, the first accepted one wins; every decision the
+    device takes (scalar gates of search.jl:108-130, neighbourhood check) restated here with the same arithmetic."""
+
+    spec_search = True
+
+    def __init__(self):
+        super().__init__()
+        self.calls["alpha"] = 0
+        self.windows = []
+
+    def search_alpha(self, coefs, taukaps, nup1, min_prox, proxsqr_bound, use_max_prox):
+        self.calls["alpha"] += 1
+        self.windows.append(len(taukaps))
+        eps = float(np.finfo(np.float64).eps)
+        for i, (cf, taukap) in enumerate(zip(coefs, taukaps)):
+            min_szk, sum_szk = self.search_gates(cf)
+            if min_szk < eps:
+                continue
+            mu = (sum_szk + taukap) / nup1
+            if mu < eps:
+                continue
+            rel = taukap / mu
+            tp = (rel - 1.0) ** 2
+            if rel < min_prox or tp > proxsqr_bound:
+                continue
+            ok, agg = self.search_check(mu, min_prox, proxsqr_bound, use_max_prox, tp)
+            if ok:
+                return i, mu, agg
+        return -1, float("nan"), float("nan")
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_speculative_search_windows_reproduce_the_sequential_search(name):
+    """host/stepper.py:_search_alpha_speculative (window sizes, candidate counting, prev_sched, the fall-back chain of
+    combined.jl:93-118 when a whole schedule is rejected) against the one-candidate-per-call loop of search.jl:72-98."""
+    seq_ss = ProtocolSystemSolver()
+    seq = Solver(ProtocolConeSet, seq_ss, trace=True)
+    seq.load(CASES[name]())
+    seq.solve()
+    ss = SpeculativeSystemSolver()
+    spec = Solver(ProtocolConeSet, ss, trace=True)
+    spec.load(CASES[name]())
+    spec.solve()
+    assert ss.calls["alpha"] > 0 and max(ss.windows) >= 2
+    assert ss.calls["alpha"] < seq_ss.calls["gates"]  # fewer host round trips than candidates
+    assert spec.status == seq.status and spec.num_iters == seq.num_iters
+    for key in ("alpha", "n_cand", "n_ref", "mu", "prox"):
+        assert [r[key] for r in spec.trace] == [r[key] for r in seq.trace], key
+    assert np.array_equal(spec.get_x(), seq.get_x())
