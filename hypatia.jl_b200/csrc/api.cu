@@ -292,6 +292,7 @@ int hyb_cones_load_point(hyb_ctx* c, const double* primal, const double* dual, d
     c->loaded_scal = scal;
     c->point_loaded = true;
     c->updated_irtmu = NAN;
+    c->hess_fact_lazy = true;
     // in the line search scal == irtmu (search.jl:144), so this is normally the only update
     KBEGIN(c);
     HYB_CHECK(hyb_ensure_updated(c, scal));
@@ -318,6 +319,7 @@ int hyb_cones_check(hyb_ctx* c, double irtmu, int use_max_prox, double agg0, dou
     if (!c || !c->loaded) return -1;
     HYB_CUDA(cudaSetDevice(c->device));
     HYB_CHECK(hyb_ensure_updated(c, irtmu));
+    c->hess_fact_lazy = false;  // check_numerics / get_proxsqr go through inv_hess_prod! (Cones.jl:267-304)
     int flags = 0;
     double a = 0.0;
     HYB_CHECK(hybi_cones_reduce(c->st, c->cones, use_max_prox, &flags, &a));
@@ -447,6 +449,15 @@ int hyb_schur_assemble_into(hyb_ctx* c, double* Sdst, double* t_assemble_ms) {
         HybCones& cs = c->cones;
         const size_t nb = cs.blocks.size();
         std::vector<char> sqrt_mask(nb, 1);
+        // opt-in (HYB_LAZY_SQRT_RULE=1): with the stored-Hessian engines both branches give the same matrix up to
+        // rounding, and the default keeps the syrk branch, whose trajectories the committed fixtures were checked
+        // against (on nearestdnn_side12 the gemm branch at iteration 0 moves the count of the last, rounding-bound
+        // iterations from 15 to 17)
+        static const bool lazy_rule = [] {
+            const char* e = getenv("HYB_LAZY_SQRT_RULE");
+            return e && atoi(e) != 0;
+        }();
+        const bool lazy = lazy_rule && c->hess_fact_lazy;
         for (size_t bi = 0; bi < nb; ++bi) {
             const int ty = cs.blocks[bi].type;
             if (ty == HYB_WSOSINTERPNONNEGATIVE || ty == HYB_WSOSINTERPPOSSEMIDEFTRI) {
@@ -472,6 +483,15 @@ int hyb_schur_assemble_into(hyb_ctx* c, double* Sdst, double* t_assemble_ms) {
                 sqrt_mask[bi] = 0;
             }
         }
+        if (lazy)  // Cones.jl:195: "array is small" -> no factorization is started for it, the cone takes the gemm branch
+            for (size_t bi = 0; bi < nb; ++bi) {
+                const int ty = cs.blocks[bi].type;
+                const bool generic = ty == HYB_WSOSINTERPNONNEGATIVE || ty == HYB_WSOSINTERPPOSSEMIDEFTRI ||
+                                     ty == HYB_WSOSINTERPEPINORMEUCL || ty == HYB_WSOSINTERPEPINORMONE ||
+                                     ty == HYB_DOUBLYNONNEGATIVETRI || ty == HYB_POSSEMIDEFTRISPARSE;
+                if (generic && N < (int64_t)cs.blocks[bi].dim) sqrt_mask[bi] = 0;
+            }
+        c->hess_fact_lazy = false;  // the assembly itself (block_hess_prod! / the sqrt oracles) leaves the factor behind
         // one pass of product kernels: rows of sqrt cones get W_k GQ2_k with W'W = H~ (qrchol.jl:228-241),
         // rows of the other cones H~_k GQ2_k (block_hess_prod!, qrchol.jl:248-252); H~ = H or H^-1 by barrier side
         cs.block_sqrt = sqrt_mask;

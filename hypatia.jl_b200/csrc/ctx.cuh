@@ -36,6 +36,11 @@ struct hyb_ctx {
     double updated_irtmu = NAN;
     bool point_loaded = false;
     bool fact_ok = false;
+    // Cones.jl:193-199: a generic-Hessian cone whose Hessian factorization has not been asked for since the point
+    // was loaded (true after hyb_cones_load_point, false once a neighbourhood check or an inverse-Hessian product
+    // ran) takes the gemm branch of the Schur assembly when N < dim.  The engines here always have the factor;
+    // this flag reproduces the reference's choice (iteration 0 of a solve).
+    bool hess_fact_lazy = false;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr, evA = nullptr, evB = nullptr;
     // statistics (hyb_stats): device milliseconds between the last H2D and the first D2H of every
     // compute call, and the bytes moved across PCIe by the calls

@@ -265,6 +265,8 @@ int hyb_multi_schur_update(hyb_multi* m, double* t_assemble_ms, double* t_reduce
     std::vector<double> t_copy(m->ndev, 0.0), t_upd(m->ndev, 0.0), t_done(m->ndev, 0.0);
     std::vector<int> rc(m->ndev, 0);
     std::vector<std::string> err(m->ndev);
+    const bool root_lazy = r->hess_fact_lazy;
+    r->hess_fact_lazy = false;
     auto work = [&](int d) {
         hyb_ctx* s = m->shard[d];
         const int64_t lo = m->row_lo[d], rows = m->row_hi[d] - lo;
@@ -290,6 +292,7 @@ int hyb_multi_schur_update(hyb_multi* m, double* t_assemble_ms, double* t_reduce
         s->loaded_scal = r->loaded_scal;
         s->point_loaded = true;
         s->updated_irtmu = NAN;
+        s->hess_fact_lazy = root_lazy;  // the shards take the branch the full model would (Cones.jl:193-199)
         t_copy[d] = since();
         int c = hyb_ensure_updated(s, s->loaded_scal);
         t_upd[d] = since();
